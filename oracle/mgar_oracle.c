@@ -1,0 +1,308 @@
+/*
+ * TEST INFRASTRUCTURE ONLY.  CPU restatement (plain C) of the reference algorithms on the
+ * LiDAR hot path of kdu3613/Multimodal_GAR (vendored OpenPCDet ops).  Only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may call this;
+ * the product (multimodal_gar_b200/csrc) never links or loads it.
+ *
+ * Build: gcc -O2 -ffp-contract=off -fno-fast-math -shared -fPIC (see oracle/Makefile).
+ * -ffp-contract=off matters: every fused multiply-add the reference's compiled GPU code
+ * performs is written as an explicit fmaf() here, everything else must stay unfused.
+ *
+ * Parity pinning: the reference ships no tests / golden vectors, so this
+ * oracle is pinned against the reference itself: (i) orc_points_in_boxes_mask against the
+ * reference's points_in_boxes_cpu compiled unmodified into oracle/_ref (tests/test_oracle_pin.py,
+ * runs on CPU), (ii) every other function against the reference CUDA extensions in oracle/_ref on
+ * the GPU box (tests/test_ref_gpu_parity.py, -m gpu), and the committed fixtures in tests/golden/.
+ *
+ * All citations are relative to /root/reference/pcdet/ops/.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ---- in-box test -------------------------------------------------------------------------
+ * roiaware_pool3d/src/roiaware_pool3d_kernel.cu:16-36 (GPU, MARGIN 1e-5; identical copy at
+ * roipoint_pool3d/src/roipoint_pool3d_kernel.cu:15-35) and roiaware_pool3d/src/roiaware_pool3d.cpp:121-140
+ * (CPU twin, MARGIN 1e-2).  gpu_contract=1 reproduces the FMA contraction nvcc emits for the
+ * GPU kernels (checked in SASS: lx = fma(sx,cos, sy*(-sin)), ly = fma(sy,cos, sx*sin));
+ * gpu_contract=0 is the host build (x86-64 baseline, no FMA contraction).
+ * cosa/sina are passed in so callers can perturb them (ambiguity analysis below). */
+static int in_box_cs(const float *pt, const float *box, float margin_f, int gpu_contract,
+                     float cosa, float sina)
+{
+    float x = pt[0], y = pt[1], z = pt[2];
+    float cx = box[0], cy = box[1], cz = box[2];
+    float dx = box[3], dy = box[4], dz = box[5];
+    if ((double)fabsf(z - cz) > (double)dz / 2.0) return 0;
+    float sx = x - cx, sy = y - cy;
+    float lx, ly;
+    if (gpu_contract) {
+        lx = fmaf(sx, cosa, sy * (-sina));
+        ly = fmaf(sy, cosa, sx * sina);
+    } else {
+        float a = sx * cosa, b = sy * (-sina);
+        lx = a + b;
+        float c = sx * sina, d = sy * cosa;
+        ly = c + d;
+    }
+    double m = (double)margin_f;
+    int fx = (double)fabsf(lx) < (double)dx / 2.0 + m;
+    int fy = (double)fabsf(ly) < (double)dy / 2.0 + m;
+    return fx & fy;
+}
+
+static int in_box(const float *pt, const float *box, float margin_f, int gpu_contract)
+{
+    float rz = box[6];
+    return in_box_cs(pt, box, margin_f, gpu_contract, cosf(-rz), sinf(-rz));
+}
+
+/* 1 when the in-box decision could flip if cosf/sinf differed by one ulp (glibc here versus
+ * libdevice on the GPU): such (point, box) pairs are reported, not compared, by the CPU-side
+ * parity tests; the GPU-vs-reference-GPU tests compare every pair. */
+static int in_box_ambiguous(const float *pt, const float *box, float margin_f, int gpu_contract)
+{
+    float rz = box[6];
+    float c = cosf(-rz), s = sinf(-rz);
+    int base = in_box_cs(pt, box, margin_f, gpu_contract, c, s);
+    float cs[3] = { nextafterf(c, -2.0f), c, nextafterf(c, 2.0f) };
+    float ss[3] = { nextafterf(s, -2.0f), s, nextafterf(s, 2.0f) };
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++)
+            if (in_box_cs(pt, box, margin_f, gpu_contract, cs[i], ss[j]) != base) return 1;
+    return 0;
+}
+
+/* points_in_boxes_gpu semantics: roiaware_pool3d_kernel.cu:313-336.  out (B,N) is pre-filled
+ * with -1 by the caller (roiaware_pool3d_utils.py:38); only hits are written. */
+void orc_points_in_boxes_first(const float *boxes, const float *pts, int *out, int B, int M, int N)
+{
+    const float margin = 1e-5f;
+    for (int b = 0; b < B; b++)
+        for (int i = 0; i < N; i++) {
+            const float *p = pts + ((size_t)b * N + i) * 3;
+            for (int k = 0; k < M; k++)
+                if (in_box(p, boxes + ((size_t)b * M + k) * 7, margin, 1)) {
+                    out[(size_t)b * N + i] = k;
+                    break;
+                }
+        }
+}
+
+/* points_in_boxes_cpu semantics: roiaware_pool3d.cpp:143-168. out (M,N) 0/1, margin 1e-2. */
+void orc_points_in_boxes_mask(const float *boxes, const float *pts, int *out, int M, int N)
+{
+    const float margin = 1e-2f;
+    for (int i = 0; i < M; i++)
+        for (int j = 0; j < N; j++)
+            out[(size_t)i * N + j] = in_box(pts + (size_t)j * 3, boxes + (size_t)i * 7, margin, 0);
+}
+
+/* (M,N) 0/1 mask with the GPU kernel's semantics (margin 1e-5, FMA contraction):
+ * roipoint_pool3d_kernel.cu:38-60 transposed to (M,N). */
+void orc_in_box_mask_gpu_sem(const float *boxes, const float *pts, int *out, int M, int N)
+{
+    for (int i = 0; i < M; i++)
+        for (int j = 0; j < N; j++)
+            out[(size_t)i * N + j] = in_box(pts + (size_t)j * 3, boxes + (size_t)i * 7, 1e-5f, 1);
+}
+
+/* ambiguity map, same layout; cpu_sem selects margin 1e-2 / no contraction. */
+void orc_in_box_ambiguous(const float *boxes, const float *pts, int *out, int M, int N, int cpu_sem)
+{
+    for (int i = 0; i < M; i++)
+        for (int j = 0; j < N; j++)
+            out[(size_t)i * N + j] = in_box_ambiguous(pts + (size_t)j * 3, boxes + (size_t)i * 7,
+                                                      cpu_sem ? 1e-2f : 1e-5f, cpu_sem ? 0 : 1);
+}
+
+/* ---- roipoint_pool3d ---------------------------------------------------------------------
+ * roipoint_pool3d_kernel.cu:38-134 (assign_pts_to_box3d, get_pooled_idx, roipool3d_forward).
+ * boxes are the already-enlarged boxes (enlarge_box3d is applied by the Python wrapper,
+ * roipoint_pool3d_utils.py:48).  pooled (B,M,S,3+C) and empty (B,M) are zero-filled by the caller.
+ * pts_idx (B,M,S) may be NULL; when given it receives the pooled point indices (scratch in the
+ * reference, exposed here for tests). */
+void orc_roipoint_pool(const float *xyz, const float *boxes, const float *feat, float *pooled,
+                       int *empty, int *pts_idx, int B, int N, int M, int S, int C)
+{
+    int *idx = (int *)malloc(sizeof(int) * (size_t)(S > 0 ? S : 1));
+    for (int b = 0; b < B; b++)
+        for (int m = 0; m < M; m++) {
+            const float *box = boxes + ((size_t)b * M + m) * 7;
+            int cnt = 0;
+            for (int k = 0; k < N; k++) {
+                if (in_box(xyz + ((size_t)b * N + k) * 3, box, 1e-5f, 1)) {
+                    if (cnt < S) idx[cnt++] = k;
+                    else break;
+                }
+            }
+            size_t bm = (size_t)b * M + m;
+            if (cnt == 0) {
+                empty[bm] = 1;
+                continue;           /* pooled stays zero; pts_idx row is uninitialised in the reference */
+            }
+            for (int k = cnt; k < S; k++) idx[k] = idx[k % cnt];
+            for (int s = 0; s < S; s++) {
+                int src = idx[s];
+                float *dst = pooled + (bm * S + s) * (size_t)(3 + C);
+                for (int j = 0; j < 3; j++) dst[j] = xyz[((size_t)b * N + src) * 3 + j];
+                for (int j = 0; j < C; j++) dst[3 + j] = feat[((size_t)b * N + src) * C + j];
+                if (pts_idx) pts_idx[bm * S + s] = src;
+            }
+        }
+    free(idx);
+}
+
+/* ---- farthest point sampling ---------------------------------------------------------------
+ * pointnet2/pointnet2_stack/src/sampling_gpu.cu:9-13 (opt_n_threads), :16-21 (__update),
+ * :25-140 (batch kernel), :188-319 (stack kernel, block fixed at 1024, :340).
+ * The block is simulated literally: thread tid scans k = tid, tid+bs, ... keeping the first
+ * strict maximum, then the shared-memory tree halves with strict '>' (ties keep the lower slot).
+ * Squared distance as compiled for the GPU: fma(dz,dz, fma(dy,dy, dx*dx)), d = x2 - x1. */
+int orc_opt_n_threads(int work_size)
+{
+    int pow_2 = (int)(log((double)work_size) / log(2.0));
+    int v = 1 << pow_2;
+    if (v > 1024) v = 1024;
+    if (v < 1) v = 1;
+    return v;
+}
+
+static void fps_one(const float *xyz, float *temp, int n, int m, int bs, int *idxs, int idx_base)
+{
+    if (m <= 0) return;
+    float *dists = (float *)malloc(sizeof(float) * bs);
+    int *dists_i = (int *)malloc(sizeof(int) * bs);
+    int old = 0;
+    idxs[0] = idx_base;
+    for (int j = 1; j < m; j++) {
+        float x1 = xyz[old * 3 + 0], y1 = xyz[old * 3 + 1], z1 = xyz[old * 3 + 2];
+        for (int tid = 0; tid < bs; tid++) {
+            int besti = 0;
+            float best = -1.0f;
+            for (int k = tid; k < n; k += bs) {
+                float dx = xyz[k * 3 + 0] - x1, dy = xyz[k * 3 + 1] - y1, dz = xyz[k * 3 + 2] - z1;
+                float d = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                float d2 = fminf(d, temp[k]);
+                temp[k] = d2;
+                if (d2 > best) { besti = k; best = d2; }
+            }
+            dists[tid] = best;
+            dists_i[tid] = besti;
+        }
+        for (int half = bs / 2; half >= 1; half /= 2)
+            for (int tid = 0; tid < half; tid++) {
+                float v1 = dists[tid], v2 = dists[tid + half];
+                int i1 = dists_i[tid], i2 = dists_i[tid + half];
+                dists[tid] = v1 > v2 ? v1 : (v2 > v1 ? v2 : v1);   /* max(v1, v2) */
+                dists_i[tid] = v2 > v1 ? i2 : i1;
+            }
+        old = dists_i[0];
+        idxs[j] = old + idx_base;
+    }
+    free(dists);
+    free(dists_i);
+}
+
+/* batch layout: xyz (b,n,3), temp (b,n) pre-filled 1e10 by the caller (pointnet2_utils.py:178),
+ * idx (b,m) local indices. */
+void orc_fps_batch(int b, int n, int m, const float *xyz, float *temp, int *idx)
+{
+    int bs = orc_opt_n_threads(n);
+    for (int i = 0; i < b; i++)
+        fps_one(xyz + (size_t)i * n * 3, temp + (size_t)i * n, n, m, bs, idx + (size_t)i * m, 0);
+}
+
+/* stack layout: xyz (sum n_i,3), idx (sum m_i) GLOBAL row indices (sampling_gpu.cu:225,317). */
+void orc_fps_stack(int batch, const float *xyz, float *temp, const int *xyz_batch_cnt, int *idx,
+                   const int *num_sampled)
+{
+    size_t start = 0, istart = 0;
+    for (int i = 0; i < batch; i++) {
+        fps_one(xyz + start * 3, temp + start, xyz_batch_cnt[i], num_sampled[i], 1024, idx + istart,
+                (int)start);
+        start += xyz_batch_cnt[i];
+        istart += num_sampled[i];
+    }
+}
+
+/* ---- ball query (stack) ------------------------------------------------------------------
+ * pointnet2/pointnet2_stack/src/ball_query_gpu.cu:16-66.  idx (M,nsample) is zero-filled by
+ * the caller (pointnet2_utils.py:33); slots the kernel does not write keep the caller's value. */
+void orc_ball_query_stack(int B, int M, float radius, int nsample, const float *new_xyz,
+                          const int *new_xyz_batch_cnt, const float *xyz, const int *xyz_batch_cnt,
+                          int *idx)
+{
+    float radius2 = radius * radius;
+    for (int pt = 0; pt < M; pt++) {
+        int bs_idx = 0, pt_cnt = new_xyz_batch_cnt[0];
+        for (int k = 1; k < B; k++) {
+            if (pt < pt_cnt) break;
+            pt_cnt += new_xyz_batch_cnt[k];
+            bs_idx = k;
+        }
+        size_t start = 0;
+        for (int k = 0; k < bs_idx; k++) start += xyz_batch_cnt[k];
+        const float *q = new_xyz + (size_t)pt * 3;
+        const float *p = xyz + start * 3;
+        int *o = idx + (size_t)pt * nsample;
+        int n = xyz_batch_cnt[bs_idx], cnt = 0;
+        for (int k = 0; k < n; k++) {
+            float dx = q[0] - p[k * 3 + 0], dy = q[1] - p[k * 3 + 1], dz = q[2] - p[k * 3 + 2];
+            float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+            if (d2 < radius2) {
+                if (cnt == 0)
+                    for (int l = 0; l < nsample; l++) o[l] = k;
+                o[cnt] = k;
+                if (++cnt >= nsample) break;
+            }
+        }
+        if (cnt == 0) o[0] = -1;
+    }
+}
+
+/* ---- grouping (stack) ----------------------------------------------------------------------
+ * pointnet2/pointnet2_stack/src/group_points_gpu.cu:71-102 (forward), :15-44 (grad).
+ * out (M,C,nsample); idx holds batch-local indices. */
+static size_t batch_of(int pt, int B, const int *idx_batch_cnt, const int *features_batch_cnt)
+{
+    int bs_idx = 0, pt_cnt = idx_batch_cnt[0];
+    for (int k = 1; k < B; k++) {
+        if (pt < pt_cnt) break;
+        pt_cnt += idx_batch_cnt[k];
+        bs_idx = k;
+    }
+    size_t start = 0;
+    for (int k = 0; k < bs_idx; k++) start += features_batch_cnt[k];
+    return start;
+}
+
+void orc_group_points_stack(int B, int M, int C, int nsample, const float *features,
+                            const int *features_batch_cnt, const int *idx, const int *idx_batch_cnt,
+                            float *out)
+{
+    for (int pt = 0; pt < M; pt++) {
+        size_t start = batch_of(pt, B, idx_batch_cnt, features_batch_cnt);
+        for (int c = 0; c < C; c++)
+            for (int s = 0; s < nsample; s++)
+                out[((size_t)pt * C + c) * nsample + s] =
+                    features[(start + idx[(size_t)pt * nsample + s]) * C + c];
+    }
+}
+
+/* grad_features (N,C) zero-filled by the caller (pointnet2_utils.py:101); the reference uses
+ * float atomicAdd (order-nondeterministic); this restatement sums in (pt, c, s) order. */
+void orc_group_points_grad_stack(int B, int M, int C, int N, int nsample, const float *grad_out,
+                                 const int *idx, const int *idx_batch_cnt,
+                                 const int *features_batch_cnt, float *grad_features)
+{
+    (void)N;
+    for (int pt = 0; pt < M; pt++) {
+        size_t start = batch_of(pt, B, idx_batch_cnt, features_batch_cnt);
+        for (int c = 0; c < C; c++)
+            for (int s = 0; s < nsample; s++)
+                grad_features[(start + idx[(size_t)pt * nsample + s]) * C + c] +=
+                    grad_out[((size_t)pt * C + c) * nsample + s];
+    }
+}
