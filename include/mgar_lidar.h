@@ -1,0 +1,132 @@
+/*
+ * mgar_lidar.h - C ABI of libmgar_lidar.so: the B200 (sm_100a) LiDAR hot path of MGAR-net.
+ *
+ * Every entry point replaces one function the reference binds through pybind11 in its
+ * pcdet/ops extensions (citations: file:line under /root/reference/pcdet/ops/).  Plain
+ * pointers and sizes only; no torch types.  Unless a name ends in _host, every pointer is
+ * a DEVICE pointer, outputs are caller-allocated (the reference's convention),
+ * and work is enqueued on `stream` (a cudaStream_t passed as void*; NULL = legacy default).
+ *
+ * Return value: 0 on success, negative MGAR_E* on failure; mgar_last_error() returns a
+ * thread-local message.  (The reference prints and calls exit(-1); we never do.)
+ * There is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef MGAR_LIDAR_H
+#define MGAR_LIDAR_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MGAR_OK 0
+#define MGAR_EINVAL (-1)  /* bad argument (shape, null pointer, unsupported size) */
+#define MGAR_ECUDA (-2)   /* CUDA runtime / launch error                           */
+#define MGAR_ENOMEM (-3)  /* workspace too small / allocation failure              */
+
+#define MGAR_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define MGAR_API __attribute__((visibility("default")))
+#else
+#define MGAR_API
+#endif
+
+MGAR_API int mgar_abi_version(void);
+MGAR_API const char *mgar_last_error(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+MGAR_API unsigned long long mgar_launch_count(void);
+
+/* ---- roiaware_pool3d: in-box tests -------------------------------------------------------- */
+
+/* points_in_boxes_gpu: roiaware_pool3d/src/roiaware_pool3d.cpp:98-118 (kernel .cu:313-336).
+ * boxes (B,M,7) [cx,cy,cz,dx,dy,dz,heading], pts (B,N,3) -> box_idx (B,N) int32: index of the
+ * FIRST box containing the point (margin 1e-5), else -1.  Every element is written. */
+MGAR_API int mgar_points_in_boxes(const float *boxes, const float *pts, int *box_idx, int B, int M, int N,
+                         void *stream);
+
+/* (M,N) 0/1 in-box matrix on the device.  cpu_semantics=0: the GPU kernels' arithmetic
+ * (margin 1e-5, FMA-contracted rotation, device cosf/sinf; roipoint_pool3d_kernel.cu:38-60,
+ * transposed).  cpu_semantics=1: the arithmetic of points_in_boxes_cpu (margin 1e-2, unfused
+ * rotation) and `cs` (M,2) must hold the host-computed cosf(-heading), sinf(-heading). */
+MGAR_API int mgar_in_box_mask(const float *boxes, const float *pts, const float *cs, int *mask, int M, int N,
+                     int cpu_semantics, void *stream);
+
+/* points_in_boxes_cpu: roiaware_pool3d.cpp:143-168.  HOST buffers in and out: boxes (M,7),
+ * pts (N,3) -> mask (M,N) int32 0/1 with the CPU function's margin (1e-2).  Runs on the GPU
+ * (H2D, kernel, D2H, synchronous); only the M box headings are pre-processed on the host so the
+ * result is bit-identical to the reference's glibc trig. */
+MGAR_API int mgar_points_in_boxes_mask_host(const float *boxes_host, const float *pts_host, int *mask_host,
+                                   int M, int N);
+
+/* ---- roipoint_pool3d ------------------------------------------------------------------------ */
+
+/* roipool3d_gpu: roipoint_pool3d/src/roipoint_pool3d.cpp:23-54 (kernels .cu:38-134).
+ * xyz (B,N,3), boxes (B,M,7) ALREADY enlarged by the caller, feat (B,N,C) ->
+ * pooled (B,M,S,3+C), empty (B,M) int32 (every element of both is written; empty boxes give
+ * zeros and flag 1).  pts_idx (B,M,S) optional (may be NULL): the pooled point indices.
+ * canonical != 0 additionally applies pointrcnn_head.py:121-129 (subtract centre, rotate by
+ * -heading) to the xyz columns using `boxes` as the RoIs. */
+MGAR_API int mgar_roipoint_pool(const float *xyz, const float *boxes, const float *feat, float *pooled,
+                       int *empty, int *pts_idx, int B, int N, int M, int S, int C, int canonical,
+                       void *stream);
+
+/* ---- pointnet2_stack: farthest point sampling ------------------------------------------------- */
+
+/* farthest_point_sampling_wrapper: pointnet2/pointnet2_stack/src/sampling.cpp:21-34
+ * (kernel sampling_gpu.cu:25-140).  xyz (b,n,3), temp (b,n) pre-filled by the caller (1e10;
+ * clobbered with the final min-distances) -> idx (b,m) int32.  Tie order follows the
+ * reference's block reduction for block size opt_n_threads(n). */
+MGAR_API int mgar_fps_batch(int b, int n, int m, const float *xyz, float *temp, int *idx, void *stream);
+
+/* stack_farthest_point_sampling_wrapper: sampling.cpp:37-56 (kernel sampling_gpu.cu:188-319).
+ * xyz (sum n_i,3), temp (sum n_i), xyz_batch_cnt (batch) int32 device, num_sampled (batch)
+ * int32 device -> idx (sum m_i) GLOBAL row indices.  max_n = upper bound of n_i (host knows
+ * the total N; pass N when unknown).  Block size is fixed at 1024 as in the reference. */
+MGAR_API int mgar_fps_stack(int batch, int max_n, const float *xyz, float *temp, const int *xyz_batch_cnt,
+                   int *idx, const int *num_sampled, void *stream);
+
+/* ---- pointnet2_stack: ball query / grouping ----------------------------------------------------- */
+
+/* ball_query_wrapper_stack: ball_query.cpp:29-45 (kernel ball_query_gpu.cu:16-66).
+ * idx (M,nsample) is zero-filled by the caller; rows without neighbours get idx[0] = -1. */
+MGAR_API int mgar_ball_query_stack(int B, int M, float radius, int nsample, const float *new_xyz,
+                          const int *new_xyz_batch_cnt, const float *xyz, const int *xyz_batch_cnt,
+                          int *idx, void *stream);
+
+/* group_points_wrapper_stack: group_points.cpp:50-67 (kernel group_points_gpu.cu:71-102).
+ * out (M,C,nsample), every element written. */
+MGAR_API int mgar_group_points_stack(int B, int M, int C, int nsample, const float *features,
+                            const int *features_batch_cnt, const int *idx, const int *idx_batch_cnt,
+                            float *out, void *stream);
+
+/* group_points_grad_wrapper_stack: group_points.cpp:29-47 (kernel group_points_gpu.cu:15-44).
+ * grad_features (N,C) zero-filled by the caller, accumulated with atomics. */
+MGAR_API int mgar_group_points_grad_stack(int B, int M, int C, int N, int nsample, const float *grad_out,
+                                 const int *idx, const int *idx_batch_cnt,
+                                 const int *features_batch_cnt, float *grad_features, void *stream);
+
+/* ---- set-abstraction shared MLP (QueryAndGroup + [Conv1x1,BN,ReLU] x L + pool, fused) ------------ */
+
+/* StackSAModuleMSG.forward for ONE scale, eval-mode BatchNorm: pointnet2_stack/pointnet2_modules.py:78-112
+ * with QueryAndGroup (pointnet2_utils.py:123-159) fused in.  Inputs as for ball query plus
+ * features (sum n_i, C_in) (NULL when C_in = 0) and idx (M,nsample) from ball query (rows whose
+ * idx[0] < 0, or whose empty_mask byte is set, are empty balls: all-zero inputs, as
+ * pointnet2_utils.py:146-150).  Ragged layout: pass both count arrays and uniform_n = 0.  Uniform
+ * layout (every cloud uniform_n points and uniform_m centroids): count arrays may be NULL.
+ * channels_host[0..n_layers] with channels_host[0] = 3 + C_in (HOST array).  params (DEVICE):
+ * per layer W^T [c_in][c_out] then scale[c_out], shift[c_out] (BatchNorm folded:
+ * scale = gamma/sqrt(var+eps), shift = beta - mean*scale).  out (M, C_last) with row stride
+ * ld_out floats (so several scales can be written side by side).  pool_avg = 0: max, 1: mean.
+ * Exact fp32 (FFMA) arithmetic. */
+MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const float *xyz, const int *xyz_batch_cnt,
+                                  const float *new_xyz, const int *new_xyz_batch_cnt, int uniform_n,
+                                  int uniform_m, const float *features, const int *idx,
+                                  const unsigned char *empty_mask, int n_layers, const int *channels_host,
+                                  const float *params, float *out, int ld_out, int pool_avg, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MGAR_LIDAR_H */

@@ -1,0 +1,76 @@
+"""ctypes face of libmgar_lidar.so (the C ABI declared in include/mgar_lidar.h).
+
+The library is the product: if it is missing or fails to load, importing any op raises - there
+is no CPU or PyTorch fallback behind these calls.
+"""
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmgar_lidar.so")
+_lib = None
+
+c_fp = ctypes.c_void_p  # device/host pointers travel as integers (tensor.data_ptr())
+_i = ctypes.c_int
+_f = ctypes.c_float
+_p = ctypes.c_void_p
+
+# name -> argtypes; mirrors include/mgar_lidar.h one to one (tests check the export list).
+SIGNATURES = {
+    "mgar_abi_version": [],
+    "mgar_last_error": [],
+    "mgar_launch_count": [],
+    "mgar_points_in_boxes": [_p, _p, _p, _i, _i, _i, _p],
+    "mgar_in_box_mask": [_p, _p, _p, _p, _i, _i, _i, _p],
+    "mgar_points_in_boxes_mask_host": [_p, _p, _p, _i, _i],
+    "mgar_roipoint_pool": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
+    "mgar_fps_batch": [_i, _i, _i, _p, _p, _p, _p],
+    "mgar_fps_stack": [_i, _i, _p, _p, _p, _p, _p, _p],
+    "mgar_ball_query_stack": [_i, _i, _f, _i, _p, _p, _p, _p, _p, _p],
+    "mgar_group_points_stack": [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
+    "mgar_group_points_grad_stack": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
+    "mgar_sa_mlp_fwd_fp32": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _i, _i, _p],
+}
+
+
+class MgarError(RuntimeError):
+    pass
+
+
+def build(verbose=False):
+    """Compile libmgar_lidar.so in-tree with nvcc for sm_100a (no GPU needed)."""
+    cmd = ["make", "-C", os.path.join(_HERE, "csrc"), "-j8"]
+    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if out.returncode != 0 or verbose:
+        print(out.stdout)
+    if out.returncode != 0:
+        raise MgarError("building libmgar_lidar.so failed")
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise MgarError(
+                "libmgar_lidar.so is not built (%s): run `python -c 'import __graft_entry__ as g; g.build()'`; "
+                "there is no fallback path" % LIB_PATH)
+        L = ctypes.CDLL(LIB_PATH)
+        for name, args in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.argtypes = args
+            fn.restype = _i
+        L.mgar_last_error.restype = ctypes.c_char_p
+        L.mgar_launch_count.restype = ctypes.c_ulonglong
+        _lib = L
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = lib().mgar_last_error().decode("utf-8", "replace")
+        raise MgarError("%s failed (code %d): %s" % (what or "libmgar_lidar call", rc, msg))
+
+
+def launch_count():
+    return int(lib().mgar_launch_count())

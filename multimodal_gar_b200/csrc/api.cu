@@ -1,0 +1,39 @@
+// Error plumbing and bookkeeping shared by every entry point of libmgar_lidar.so.
+#include <stdarg.h>
+
+#include <atomic>
+
+#include "mgar_common.cuh"
+
+namespace mgar {
+
+static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+int check_launch(const char *what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: kernel launch failed: %s", what, cudaGetErrorString(e));
+        return MGAR_ECUDA;
+    }
+    return MGAR_OK;
+}
+
+}  // namespace mgar
+
+extern "C" {
+
+int mgar_abi_version(void) { return MGAR_ABI_VERSION; }
+const char *mgar_last_error(void) { return mgar::g_err; }
+unsigned long long mgar_launch_count(void) { return mgar::g_launches.load(); }
+
+}  // extern "C"

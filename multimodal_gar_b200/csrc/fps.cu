@@ -1,0 +1,283 @@
+// Farthest point sampling (batch and stack layouts), bit-exact with the reference's tie order.
+//
+// Reference: pointnet2/pointnet2_stack/src/sampling_gpu.cu:25-140 (batch) and :188-319 (stack):
+// one CTA per cloud, every one of the m-1 rounds re-reads xyz and temp from global memory and
+// runs a 10-level shared-memory tree with ~10 block barriers.
+//
+// Here the cloud and its running min-distances live in REGISTERS for the whole kernel; a round is
+// a handful of FFMA per owned point, two warp REDUX (max of the distance bits, min of the
+// tie-break rank) and - only when a cloud is spread over several warps - one block barrier.
+//
+// Tie order.  The reference's winner among equal distances is decided by its launch geometry:
+// thread t scans k = t, t+bs, ... keeping the FIRST maximum (strict >), then the tree keeps the
+// LOWER slot on ties at strides bs/2 ... 1.  Two tied threads first meet at the stride of their
+// lowest differing bit and the one with that bit clear survives, i.e. the winner minimises
+// (bitrev_L(k mod bs), k div bs) lexicographically, L = log2(bs).  bs = opt_n_threads(n) =
+// min(1024, 2^floor(log2 n)) for the batch kernel (sampling_gpu.cu:9-13,150) and 1024 for the
+// stack kernel (:340).  We enumerate the points in exactly that order ("rank" r) and hand rank r
+// to thread r / PPL, slot r % PPL: the first strict maximum in (thread, slot) order is then the
+// reference's winner, with no per-element tie handling in the hot loop.
+#include <limits.h>
+#include <stdlib.h>
+
+#include "mgar_common.cuh"
+
+namespace mgar {
+
+struct FpsGeom {
+    int L;    // log2(bs)
+    int SH;   // log2(stripes padded to a power of two)
+};
+
+__device__ __forceinline__ int rank_to_index(int r, int L, int SH) {
+    const int t = L == 0 ? 0 : (int)(__brev((unsigned)(r >> SH)) >> (32 - L));
+    return ((r & ((1 << SH) - 1)) << L) + t;
+}
+
+// One CTA of W warps per cloud; each thread owns PPL ranks (registers).
+template <int W, int PPL>
+__global__ void __launch_bounds__(W * 32)
+fps_reg_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *__restrict__ idxs,
+               const int *__restrict__ xyz_batch_cnt, const int *__restrict__ num_sampled,
+               int n_uniform, int m_uniform, int L_uniform, int stack, int smem_pts) {
+    extern __shared__ float sxyz[];               // [n][3] staged cloud (lookup of the current point)
+    __shared__ int s_red[2][W > 1 ? W : 1][2];    // double-buffered per-warp (value bits, rank)
+    __shared__ int s_off[2];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bi = blockIdx.x;
+    int n, m, L;
+    long long start, istart;
+    if (stack) {
+        // exclusive prefix of the ragged counts (the reference loops serially: sampling_gpu.cu:207-211)
+        int a = 0, c = 0;
+        for (int k = tid; k < bi; k += W * 32) { a += xyz_batch_cnt[k]; c += num_sampled[k]; }
+        a = __reduce_add_sync(0xffffffffu, a);
+        c = __reduce_add_sync(0xffffffffu, c);
+        if (tid == 0) { s_off[0] = 0; s_off[1] = 0; }
+        __syncthreads();
+        if (lane == 0) { atomicAdd(&s_off[0], a); atomicAdd(&s_off[1], c); }
+        __syncthreads();
+        start = s_off[0]; istart = s_off[1];
+        n = xyz_batch_cnt[bi]; m = num_sampled[bi]; L = 10;
+    } else {
+        n = n_uniform; m = m_uniform; L = L_uniform;
+        start = (long long)bi * n; istart = (long long)bi * m;
+    }
+    if (m <= 0) return;
+    xyz += start * 3; temp += start; idxs += istart;
+    if (n > smem_pts || n < 1) {  // caller broke the max_n contract: make it visible, never overrun
+        for (int j = tid; j < m; j += W * 32) idxs[j] = -1;
+        return;
+    }
+    const int base = stack ? (int)start : 0;
+    const int bs = 1 << L;
+    int stripes = (n + bs - 1) >> L, SH = 0;
+    while ((1 << SH) < stripes) SH++;
+
+    for (int i = tid; i < n * 3; i += W * 32) sxyz[i] = xyz[i];
+    __syncthreads();
+
+    float px[PPL], py[PPL], pz[PPL], pt[PPL];
+#pragma unroll
+    for (int i = 0; i < PPL; i++) {
+        const int k = rank_to_index(tid * PPL + i, L, SH);
+        const bool valid = (tid * PPL + i) < (bs << SH) && k < n;
+        px[i] = valid ? sxyz[k * 3 + 0] : 0.f;
+        py[i] = valid ? sxyz[k * 3 + 1] : 0.f;
+        pz[i] = valid ? sxyz[k * 3 + 2] : 0.f;
+        pt[i] = valid ? temp[k] : -1.f;  // -1 never beats the reference's initial best = -1 either
+    }
+
+    int cur = 0;
+    if (tid == 0) idxs[0] = base;
+    for (int j = 1; j < m; j++) {
+        const float cx = sxyz[cur * 3 + 0], cy = sxyz[cur * 3 + 1], cz = sxyz[cur * 3 + 2];
+        float best = -1.f;
+        int bslot = 0;
+#pragma unroll
+        for (int i = 0; i < PPL; i++) {
+            const float d = sqdist(__fsub_rn(px[i], cx), __fsub_rn(py[i], cy), __fsub_rn(pz[i], cz));
+            pt[i] = fminf(d, pt[i]);
+            if (pt[i] > best) { best = pt[i]; bslot = i; }
+        }
+        // distances are >= 0 (or the -1 filler): their int bit patterns order like the floats
+        const int vb = __float_as_int(best);
+        int vmax = __reduce_max_sync(0xffffffffu, vb);
+        int rmin = __reduce_min_sync(0xffffffffu, vb == vmax ? tid * PPL + bslot : INT_MAX);
+        if (W > 1) {
+            const int buf = j & 1;
+            if (lane == 0) { s_red[buf][warp][0] = vmax; s_red[buf][warp][1] = rmin; }
+            __syncthreads();
+            if (W <= 8) {
+                vmax = s_red[buf][0][0]; rmin = s_red[buf][0][1];
+#pragma unroll
+                for (int w = 1; w < W; w++) {
+                    const int v = s_red[buf][w][0], r = s_red[buf][w][1];
+                    if (v > vmax) { vmax = v; rmin = r; }   // warps are in rank order: ties keep the earlier
+                }
+            } else {
+                const int v = lane < W ? s_red[buf][lane][0] : INT_MIN;
+                const int r = lane < W ? s_red[buf][lane][1] : INT_MAX;
+                vmax = __reduce_max_sync(0xffffffffu, v);
+                rmin = __reduce_min_sync(0xffffffffu, v == vmax ? r : INT_MAX);
+            }
+        }
+        cur = rank_to_index(rmin, L, SH);
+        if (tid == 0) idxs[j] = cur + base;
+    }
+    // the reference leaves the final min-distances in temp (caller scratch): keep that contract
+#pragma unroll
+    for (int i = 0; i < PPL; i++) {
+        const int k = rank_to_index(tid * PPL + i, L, SH);
+        if ((tid * PPL + i) < (bs << SH) && k < n) temp[k] = pt[i];
+    }
+}
+
+// Any-size path: 1024 threads, cloud and temp stay in global/L2 (same traffic pattern as the
+// reference) but the 10-barrier tree is replaced by REDUX + one barrier.  bs is 1024 for every
+// n >= 1024 in both layouts, so thread t owns k = t, t+1024, ... exactly like the reference.
+__global__ void __launch_bounds__(1024)
+fps_global_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *__restrict__ idxs,
+                  const int *__restrict__ xyz_batch_cnt, const int *__restrict__ num_sampled,
+                  int n_uniform, int m_uniform, int L_uniform, int stack) {
+    __shared__ int s_red[2][32][2];
+    __shared__ int s_win[2];
+    __shared__ long long s_off[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bi = blockIdx.x;
+    int n, m, L;
+    long long start, istart;
+    if (stack) {
+        if (tid == 0) {
+            long long a = 0, c = 0;
+            for (int k = 0; k < bi; k++) { a += xyz_batch_cnt[k]; c += num_sampled[k]; }
+            s_off[0] = a; s_off[1] = c;
+        }
+        __syncthreads();
+        start = s_off[0]; istart = s_off[1];
+        n = xyz_batch_cnt[bi]; m = num_sampled[bi]; L = 10;
+    } else {
+        n = n_uniform; m = m_uniform; L = L_uniform;
+        start = (long long)bi * n; istart = (long long)bi * m;
+    }
+    if (m <= 0) return;
+    xyz += start * 3; temp += start; idxs += istart;
+    const int base = stack ? (int)start : 0;
+    const int bs = 1 << L;
+    // rank of this thread among threads = bit-reversed id; threads >= bs own nothing
+    const int trank = (tid < bs) ? (L == 0 ? 0 : (int)(__brev((unsigned)tid) >> (32 - L))) : INT_MAX;
+
+    int cur = 0;
+    if (tid == 0) idxs[0] = base;
+    for (int j = 1; j < m; j++) {
+        const float cx = xyz[cur * 3 + 0], cy = xyz[cur * 3 + 1], cz = xyz[cur * 3 + 2];
+        float best = -1.f;
+        int besti = 0;
+        if (tid < bs)
+            for (int k = tid; k < n; k += bs) {
+                const float d = sqdist(__fsub_rn(xyz[k * 3 + 0], cx), __fsub_rn(xyz[k * 3 + 1], cy),
+                                       __fsub_rn(xyz[k * 3 + 2], cz));
+                const float d2 = fminf(d, temp[k]);
+                temp[k] = d2;
+                if (d2 > best) { best = d2; besti = k; }
+            }
+        const int vb = __float_as_int(best);
+        int vmax = __reduce_max_sync(0xffffffffu, vb);
+        int rmin = __reduce_min_sync(0xffffffffu, vb == vmax ? trank : INT_MAX);
+        int kwin = __shfl_sync(0xffffffffu, besti, __ffs(__ballot_sync(0xffffffffu, vb == vmax && trank == rmin)) - 1);
+        const int buf = j & 1;
+        if (lane == 0) { s_red[buf][warp][0] = vmax; s_red[buf][warp][1] = rmin; }
+        __syncthreads();
+        const int v = s_red[buf][lane][0], r = s_red[buf][lane][1];
+        vmax = __reduce_max_sync(0xffffffffu, v);
+        rmin = __reduce_min_sync(0xffffffffu, v == vmax ? r : INT_MAX);
+        const int wwin = __ffs(__ballot_sync(0xffffffffu, v == vmax && r == rmin)) - 1;
+        // broadcast the winning warp's point index (double-buffered: the slot is rewritten two
+        // barriers later; temp[k] is only ever touched by its owning thread)
+        if (warp == wwin && lane == 0) s_win[buf] = kwin;
+        __syncthreads();
+        cur = s_win[buf];
+        if (tid == 0) idxs[j] = cur + base;
+    }
+}
+
+template <int W, int PPL>
+static int launch_reg(int grid, size_t smem, cudaStream_t st, const float *xyz, float *temp, int *idx,
+                      const int *cnt, const int *ms, int n, int m, int L, int stack) {
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(fps_reg_kernel<W, PPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) { set_error("fps: smem opt-in failed: %s", cudaGetErrorString(e)); return MGAR_ECUDA; }
+    }
+    fps_reg_kernel<W, PPL><<<grid, W * 32, smem, st>>>(xyz, temp, idx, cnt, ms, n, m, L, stack, (int)(smem / 12));
+    count_launch();
+    return check_launch("fps");
+}
+
+static int floor_log2(int v) { int l = 0; while ((2 << l) <= v) l++; return l; }
+
+// V = padded rank space.  Geometry table: (warps, ranks per thread) chosen so one round is short
+// for a single cloud yet several clouds still share an SM; overridable for tuning.
+static int fps_dispatch(int grid, int V, int max_n, cudaStream_t st, const float *xyz, float *temp, int *idx,
+                        const int *cnt, const int *ms, int n, int m, int L, int stack) {
+    const size_t smem = (size_t)max_n * 3 * sizeof(float);
+    int W, PPL;
+    if (V <= 32) { W = 1; PPL = 1; }
+    else if (V <= 64) { W = 1; PPL = 2; }
+    else if (V <= 128) { W = 1; PPL = 4; }
+    else if (V <= 256) { W = 2; PPL = 4; }
+    else if (V <= 512) { W = 4; PPL = 4; }
+    else if (V <= 1024) { W = 4; PPL = 8; }
+    else if (V <= 2048) { W = 8; PPL = 8; }
+    else if (V <= 4096) { W = 16; PPL = 8; }
+    else { W = 32; PPL = 8; }
+    if (const char *e = getenv("MGAR_FPS_GEOM")) {  // "W,PPL" tuning override (must cover V)
+        int w = 0, p = 0;
+        if (sscanf(e, "%d,%d", &w, &p) == 2 && w * 32 * p >= V) { W = w; PPL = p; }
+    }
+    if (V > 8192 || smem > 200 * 1024) {
+        fps_global_kernel<<<grid, 1024, 0, st>>>(xyz, temp, idx, cnt, ms, n, m, L, stack);
+        count_launch();
+        return check_launch("fps(global)");
+    }
+#define MGAR_FPS_CASE(w, p) \
+    if (W == w && PPL == p) return launch_reg<w, p>(grid, smem, st, xyz, temp, idx, cnt, ms, n, m, L, stack);
+    MGAR_FPS_CASE(1, 1) MGAR_FPS_CASE(1, 2) MGAR_FPS_CASE(1, 4) MGAR_FPS_CASE(1, 8) MGAR_FPS_CASE(1, 16)
+    MGAR_FPS_CASE(2, 2) MGAR_FPS_CASE(2, 4) MGAR_FPS_CASE(2, 8) MGAR_FPS_CASE(2, 16)
+    MGAR_FPS_CASE(4, 2) MGAR_FPS_CASE(4, 4) MGAR_FPS_CASE(4, 8) MGAR_FPS_CASE(4, 16)
+    MGAR_FPS_CASE(8, 1) MGAR_FPS_CASE(8, 2) MGAR_FPS_CASE(8, 4) MGAR_FPS_CASE(8, 8) MGAR_FPS_CASE(8, 16)
+    MGAR_FPS_CASE(16, 1) MGAR_FPS_CASE(16, 2) MGAR_FPS_CASE(16, 4) MGAR_FPS_CASE(16, 8)
+    MGAR_FPS_CASE(32, 1) MGAR_FPS_CASE(32, 2) MGAR_FPS_CASE(32, 4) MGAR_FPS_CASE(32, 8)
+#undef MGAR_FPS_CASE
+    set_error("fps: unsupported geometry W=%d PPL=%d", W, PPL);
+    return MGAR_EINVAL;
+}
+
+}  // namespace mgar
+
+using namespace mgar;
+
+extern "C" int mgar_fps_batch(int b, int n, int m, const float *xyz, float *temp, int *idx, void *stream) {
+    MGAR_REQUIRE(b >= 0 && n >= 0 && m >= 0, "fps_batch: negative size");
+    if (b == 0 || m == 0) return MGAR_OK;
+    MGAR_REQUIRE(n >= 1, "fps_batch: n must be >= 1 when m > 0");
+    MGAR_REQUIRE(xyz && temp && idx, "fps_batch: null pointer");
+    int L = floor_log2(n);
+    if (L > 10) L = 10;
+    const int bs = 1 << L;
+    int stripes = (n + bs - 1) / bs, SH = 0;
+    while ((1 << SH) < stripes) SH++;
+    return fps_dispatch(b, bs << SH, n, (cudaStream_t)stream, xyz, temp, idx, nullptr, nullptr, n, m, L, 0);
+}
+
+extern "C" int mgar_fps_stack(int batch, int max_n, const float *xyz, float *temp, const int *xyz_batch_cnt,
+                              int *idx, const int *num_sampled, void *stream) {
+    MGAR_REQUIRE(batch >= 0 && max_n >= 0, "fps_stack: negative size");
+    if (batch == 0) return MGAR_OK;
+    MGAR_REQUIRE(xyz && temp && idx && xyz_batch_cnt && num_sampled, "fps_stack: null pointer");
+    int stripes = (max_n + 1023) / 1024, SH = 0;
+    if (stripes < 1) stripes = 1;
+    while ((1 << SH) < stripes) SH++;
+    return fps_dispatch(batch, 1024 << SH, max_n, (cudaStream_t)stream, xyz, temp, idx, xyz_batch_cnt, num_sampled,
+                        0, 0, 10, 1);
+}

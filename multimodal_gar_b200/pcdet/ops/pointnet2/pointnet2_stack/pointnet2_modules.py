@@ -1,0 +1,103 @@
+"""Host-side mirror of StackSAModuleMSG from
+/root/reference/pcdet/ops/pointnet2/pointnet2_stack/pointnet2_modules.py:30-112 (same constructor,
+parameter names `mlps.{k}.{0,1,3,4}.*`, init and forward signature).
+
+eval(): each scale runs as ball query + ONE fused kernel (gather, MLP, BatchNorm folded, ReLU,
+pool).  train(): the reference's own composition (QueryAndGroup -> Conv2d/BN/ReLU -> pool) on the
+new grouping kernels, so batch statistics and autograd behave exactly as upstream.
+"""
+from typing import List
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import pointnet2_utils, sa_mlp_fused
+
+
+def build_local_aggregation_module(input_channels, config):
+    """reference :10-27 (StackSAModuleMSG only; VectorPool is outside this build)."""
+    name = config.get('NAME', 'StackSAModuleMSG')
+    if name != 'StackSAModuleMSG':
+        raise NotImplementedError(name)
+    mlps = config.MLPS
+    for k in range(len(mlps)):
+        mlps[k] = [input_channels] + mlps[k]
+    layer = StackSAModuleMSG(radii=config.POOL_RADIUS, nsamples=config.NSAMPLE, mlps=mlps, use_xyz=True,
+                             pool_method='max_pool')
+    return layer, sum(x[-1] for x in mlps)
+
+
+class StackSAModuleMSG(nn.Module):
+    def __init__(self, *, radii: List[float], nsamples: List[int], mlps: List[List[int]],
+                 use_xyz: bool = True, pool_method='max_pool'):
+        super().__init__()
+        assert len(radii) == len(nsamples) == len(mlps)
+        self.groupers = nn.ModuleList()
+        self.mlps = nn.ModuleList()
+        for radius, nsample, spec in zip(radii, nsamples, mlps):
+            self.groupers.append(pointnet2_utils.QueryAndGroup(radius, nsample, use_xyz=use_xyz))
+            if use_xyz:
+                spec[0] += 3  # in place, as the reference does (:53-54)
+            layers = []
+            for k in range(len(spec) - 1):
+                layers += [nn.Conv2d(spec[k], spec[k + 1], kernel_size=1, bias=False),
+                           nn.BatchNorm2d(spec[k + 1]), nn.ReLU()]
+            self.mlps.append(nn.Sequential(*layers))
+        self.pool_method = pool_method
+        self.use_xyz = use_xyz
+        self._packed = None
+        self.init_weights()
+
+    def init_weights(self):
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight)
+                if m.bias is not None:
+                    nn.init.constant_(m.bias, 0)
+            if isinstance(m, nn.BatchNorm2d):
+                nn.init.constant_(m.weight, 1.0)
+                nn.init.constant_(m.bias, 0)
+
+    def train(self, mode=True):
+        self._packed = None  # parameters may change: re-fold on the next eval forward
+        return super().train(mode)
+
+    def _pack(self, device):
+        if self._packed is None or self._packed[0][1].device != device:
+            self._packed = [tuple(t if isinstance(t, list) else t.to(device) for t in sa_mlp_fused.pack_shared_mlp(m))
+                            for m in self.mlps]
+        return self._packed
+
+    def forward(self, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features=None, empty_voxel_set_zeros=True):
+        """reference :78-112 -> (new_xyz, new_features (M, sum_k mlps[k][-1]))."""
+        fused = (not self.training) and self.use_xyz and self.pool_method in ('max_pool', 'avg_pool') \
+            and not torch.is_grad_enabled()
+        if fused:
+            packed = self._pack(xyz.device)
+            widths = [ch[-1] for ch, _ in packed]
+            out = torch.empty((new_xyz.shape[0], sum(widths)), dtype=torch.float32, device=xyz.device)
+            col = 0
+            for k, (channels, params) in enumerate(packed):
+                g = self.groupers[k]
+                idx, empty = pointnet2_utils.ball_query(g.radius, g.nsample, xyz, xyz_batch_cnt, new_xyz,
+                                                        new_xyz_batch_cnt)
+                sa_mlp_fused.sa_mlp_forward(channels, params, g.nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt,
+                                            features, idx, empty_mask=empty, out=out[:, col:col + widths[k]],
+                                            pool_avg=self.pool_method == 'avg_pool')
+                col += widths[k]
+            return new_xyz, out
+
+        new_features_list = []
+        for k in range(len(self.groupers)):
+            new_features, _ = self.groupers[k](xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features)
+            new_features = new_features.permute(1, 0, 2).unsqueeze(dim=0)      # (1, C, M, nsample)
+            new_features = self.mlps[k](new_features)
+            if self.pool_method == 'max_pool':
+                new_features = F.max_pool2d(new_features, kernel_size=[1, new_features.size(3)]).squeeze(dim=-1)
+            elif self.pool_method == 'avg_pool':
+                new_features = F.avg_pool2d(new_features, kernel_size=[1, new_features.size(3)]).squeeze(dim=-1)
+            else:
+                raise NotImplementedError
+            new_features_list.append(new_features.squeeze(dim=0).permute(1, 0))  # (M, C)
+        return new_xyz, torch.cat(new_features_list, dim=1)

@@ -1,0 +1,60 @@
+"""Fused QueryAndGroup + shared MLP + pool (eval-mode BatchNorm) over libmgar_lidar.so.
+
+This replaces, for inference, the chain in the reference's StackSAModuleMSG.forward
+(/root/reference/pcdet/ops/pointnet2/pointnet2_stack/pointnet2_modules.py:89-110): grouping,
+`cat`, [Conv2d 1x1, BatchNorm2d, ReLU] x L, max_pool2d.
+"""
+import torch
+import torch.nn as nn
+
+from ..... import _lib
+from ....._torch_glue import need_cuda, need_dtype, on_device, ptr, stream_of
+
+
+def pack_shared_mlp(seq):
+    """nn.Sequential([Conv2d(1x1,no bias), BatchNorm2d, ReLU] x L) -> (channels list, packed fp32 tensor).
+
+    Per layer: W^T [c_in][c_out], scale[c_out], shift[c_out] with the running statistics folded:
+    scale = gamma / sqrt(var + eps), shift = beta - mean * scale."""
+    mods = list(seq)
+    assert len(mods) % 3 == 0 and len(mods) > 0
+    channels, parts = [], []
+    for k in range(0, len(mods), 3):
+        conv, bn, act = mods[k], mods[k + 1], mods[k + 2]
+        assert isinstance(conv, nn.Conv2d) and conv.kernel_size == (1, 1) and conv.bias is None
+        assert isinstance(bn, nn.BatchNorm2d) and isinstance(act, nn.ReLU)
+        w = conv.weight.detach().float().reshape(conv.out_channels, conv.in_channels)
+        if not channels:
+            channels.append(conv.in_channels)
+        channels.append(conv.out_channels)
+        gamma = bn.weight.detach().float() if bn.affine else torch.ones_like(bn.running_var)
+        beta = bn.bias.detach().float() if bn.affine else torch.zeros_like(bn.running_var)
+        scale = gamma / torch.sqrt(bn.running_var.detach().float() + bn.eps)
+        shift = beta - bn.running_mean.detach().float() * scale
+        parts += [w.t().contiguous().reshape(-1), scale, shift]
+    return channels, torch.cat(parts).contiguous()
+
+
+def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features, idx,
+                   empty_mask=None, out=None, pool_avg=False, uniform=None):
+    """-> (M, channels[-1]) fp32.  `idx` as returned by ball_query (or the raw kernel output);
+    `uniform=(n, m)` skips the ragged bookkeeping when every cloud has n points and m centroids."""
+    need_cuda(xyz=xyz, new_xyz=new_xyz, features=features, idx=idx, params=params, empty_mask=empty_mask, out=out)
+    need_dtype(torch.float32, xyz=xyz, new_xyz=new_xyz, features=features, params=params)
+    need_dtype(torch.int32, idx=idx)
+    M = new_xyz.shape[0]
+    B = xyz_batch_cnt.shape[0] if xyz_batch_cnt is not None else xyz.shape[0] // uniform[0]
+    C_in = 0 if features is None else features.shape[1]
+    if out is None:
+        out = torch.empty((M, channels[-1]), dtype=torch.float32, device=xyz.device)
+    if empty_mask is not None:
+        empty_mask = empty_mask.to(torch.uint8).contiguous()
+    import ctypes
+    ch = (ctypes.c_int * len(channels))(*channels)
+    un, um = uniform if uniform is not None else (0, 0)
+    with on_device(xyz):
+        _lib.check(_lib.lib().mgar_sa_mlp_fwd_fp32(
+            B, M, nsample, C_in, ptr(xyz), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt), un, um,
+            ptr(features), ptr(idx), ptr(empty_mask), len(channels) - 1, ctypes.addressof(ch), ptr(params),
+            ptr(out), out.stride(0), 1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd")
+    return out
