@@ -1,0 +1,97 @@
+"""The LiDAR hot path of MGAR-net composed from the drop-in pcdet.ops surface: per-person point
+pooling -> canonical frame -> farthest point sampling -> ball query + grouping + shared MLP ->
+per-person feature, i.e. what a point-based `LiDAR_Backbone` (/root/reference/model/gat_model.py:868-971)
+hands to the Distance Aware Fusion Module as `[B, NP, C]` (gat_model.py:1359-1360).
+
+The composition follows the reference's own point pooling head (PointRCNNHead.roipool3d_gpu,
+/root/reference/pcdet/models/roi_heads/pointrcnn_head.py:85-130) followed by a stack-layout SA
+module (pointnet2_stack/pointnet2_modules.py:78-112) with every person as one "batch" of the
+stack layout (xyz_batch_cnt = [S] * persons).
+
+Frames are independent: `shard_frames` hands each rank a contiguous block of frames and no
+collective is needed in the forward pass.
+"""
+import torch
+import torch.nn as nn
+
+from .pcdet.ops.pointnet2.pointnet2_stack import pointnet2_modules, pointnet2_utils
+from .pcdet.ops.roiaware_pool3d import roiaware_pool3d_utils
+from .pcdet.ops.roipoint_pool3d import roipoint_pool3d_cuda, roipoint_pool3d_utils
+from .pcdet.utils import box_utils, common_utils
+
+
+def shard_frames(num_frames, world_size, rank):
+    """Contiguous block partition of frames over ranks: frame f -> rank floor(f * W / B).
+    Returns (first, last_exclusive).  Blocks differ by at most one frame."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError("bad rank %d / world %d" % (rank, world_size))
+    lo = (rank * num_frames + world_size - 1) // world_size
+    hi = ((rank + 1) * num_frames + world_size - 1) // world_size
+    return lo, hi
+
+
+def canonical_transform(pooled_features, rois, pooled_empty_flag):
+    """pointrcnn_head.py:121-129 with the reference's torch ops: (B,M,S,3+C) -> (B*M,S,3+C)."""
+    pooled_features = pooled_features.clone()
+    pooled_features[:, :, :, 0:3] -= rois[:, :, 0:3].unsqueeze(dim=2)
+    pooled_features = pooled_features.view(-1, pooled_features.shape[-2], pooled_features.shape[-1])
+    pooled_features[:, :, 0:3] = common_utils.rotate_points_along_z(
+        pooled_features[:, :, 0:3], -rois.view(-1, rois.shape[-1])[:, 6])
+    pooled_features[pooled_empty_flag.view(-1) > 0] = 0
+    return pooled_features
+
+
+class PointPersonEncoder(nn.Module):
+    """points (B,N,3) + point_features (B,N,C) + person boxes (B,M,7) -> person features (B,M,C_out).
+
+    Defaults are BASELINE.json configs[1]: S=512 pooled points, P=512 FPS centroids, ball query
+    r=0.3 / nsample=32, shared MLP [C,64,128] (+3 for use_xyz), max over samples, max over centroids.
+    """
+
+    def __init__(self, point_feature_channels=1, num_sampled_points=512, npoint=512, radius=0.3, nsample=32,
+                 mlp=(64, 128), pool_extra_width=(0.0, 0.0, 0.0), fused_canonical=True):
+        super().__init__()
+        self.num_sampled_points, self.npoint = num_sampled_points, npoint
+        self.pool_extra_width = tuple(pool_extra_width)
+        self.fused_canonical = fused_canonical
+        self.roipoint_pool3d_layer = roipoint_pool3d_utils.RoIPointPool3d(num_sampled_points, self.pool_extra_width)
+        self.sa = pointnet2_modules.StackSAModuleMSG(radii=[radius], nsamples=[nsample],
+                                                     mlps=[[point_feature_channels] + list(mlp)], use_xyz=True,
+                                                     pool_method='max_pool')
+        self.out_channels = mlp[-1]
+
+    @torch.no_grad()
+    def pool(self, points, point_features, boxes):
+        """-> canonical pooled (B*M,S,3+C), empty flag (B,M) int32."""
+        B, M = boxes.shape[0], boxes.shape[1]
+        C, S = point_features.shape[2], self.num_sampled_points
+        if self.fused_canonical:
+            # one kernel: in-box test + ordered compaction + gather + canonical frame
+            big = box_utils.enlarge_box3d(boxes.reshape(-1, 7), self.pool_extra_width).view(B, M, 7).contiguous()
+            pooled = torch.empty((B, M, S, 3 + C), dtype=torch.float32, device=points.device)
+            empty = torch.empty((B, M), dtype=torch.int32, device=points.device)
+            roipoint_pool3d_cuda.forward(points.contiguous(), big, point_features.contiguous(), pooled, empty,
+                                         canonical=True)
+            return pooled.view(B * M, S, 3 + C), empty
+        pooled, empty = self.roipoint_pool3d_layer(points, point_features, boxes)
+        return canonical_transform(pooled, boxes, empty), empty
+
+    def forward(self, points, point_features, boxes, return_stages=False):
+        B, M = boxes.shape[0], boxes.shape[1]
+        S, P = self.num_sampled_points, self.npoint
+        box_idx = roiaware_pool3d_utils.points_in_boxes_gpu(points, boxes)          # (B,N) first box or -1
+        pooled, empty = self.pool(points, point_features, boxes)                    # (B*M,S,3+C)
+        xyz = pooled[:, :, 0:3].contiguous()                                        # (B*M,S,3)
+        feats = pooled[:, :, 3:].contiguous().view(B * M * S, -1)
+        fps_idx = pointnet2_utils.farthest_point_sample(xyz, P)                     # (B*M,P) int32
+        new_xyz = torch.gather(xyz, 1, fps_idx.long().unsqueeze(-1).expand(-1, -1, 3)).view(B * M * P, 3)
+        cnt = torch.full((B * M,), S, dtype=torch.int32, device=xyz.device)
+        new_cnt = torch.full((B * M,), P, dtype=torch.int32, device=xyz.device)
+        _, sa_feat = self.sa(xyz.view(B * M * S, 3), cnt, new_xyz, new_cnt, feats)  # (B*M*P, C_out)
+        person = sa_feat.view(B * M, P, -1).max(dim=1).values
+        person = person * (empty.view(-1, 1) == 0).to(person.dtype)                 # empty persons -> zeros
+        person = person.view(B, M, -1)
+        if return_stages:
+            return dict(box_idx=box_idx, pooled=pooled, empty=empty, fps_idx=fps_idx, new_xyz=new_xyz,
+                        sa_features=sa_feat, person_features=person)
+        return person
