@@ -88,10 +88,10 @@ __device__ __forceinline__ bool in_box(float x, float y, float z, const BoxP &b)
     return (fabsf(lx) < b.tx) & (fabsf(ly) < b.ty);
 }
 
-// squared distance exactly as the reference kernels compute it (FMUL, FFMA, FFMA):
-// sampling_gpu.cu:64, ball_query_gpu.cu:52.
+// squared distance exactly as the reference kernels compute it once compiled (sampling_gpu.cu:64,
+// ball_query_gpu.cu:52; SASS of every instantiation: FMUL on dy, FFMA dx, FFMA dz).
 __device__ __forceinline__ float sqdist(float dx, float dy, float dz) {
-    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+    return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
 }
 
 }  // namespace mgar

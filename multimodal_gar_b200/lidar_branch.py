@@ -76,21 +76,31 @@ class PointPersonEncoder(nn.Module):
         pooled, empty = self.roipoint_pool3d_layer(points, point_features, boxes)
         return canonical_transform(pooled, boxes, empty), empty
 
-    def forward(self, points, point_features, boxes, return_stages=False):
+    def forward(self, points, point_features, boxes, return_stages=False, mark=None):
+        """`mark(name)` (optional) is called after each stage has been enqueued - bench.py records a
+        CUDA event there to time the stages inside the step."""
+        mark = mark or (lambda name: None)
         B, M = boxes.shape[0], boxes.shape[1]
         S, P = self.num_sampled_points, self.npoint
         box_idx = roiaware_pool3d_utils.points_in_boxes_gpu(points, boxes)          # (B,N) first box or -1
+        mark('points_in_boxes')
         pooled, empty = self.pool(points, point_features, boxes)                    # (B*M,S,3+C)
+        mark('roipoint_pool')
         xyz = pooled[:, :, 0:3].contiguous()                                        # (B*M,S,3)
         feats = pooled[:, :, 3:].contiguous().view(B * M * S, -1)
         fps_idx = pointnet2_utils.farthest_point_sample(xyz, P)                     # (B*M,P) int32
+        mark('fps')
         new_xyz = torch.gather(xyz, 1, fps_idx.long().unsqueeze(-1).expand(-1, -1, 3)).view(B * M * P, 3)
         cnt = torch.full((B * M,), S, dtype=torch.int32, device=xyz.device)
         new_cnt = torch.full((B * M,), P, dtype=torch.int32, device=xyz.device)
+        self.sa.stage_mark = mark
         _, sa_feat = self.sa(xyz.view(B * M * S, 3), cnt, new_xyz, new_cnt, feats)  # (B*M*P, C_out)
+        self.sa.stage_mark = None
+        mark('sa_mlp')
         person = sa_feat.view(B * M, P, -1).max(dim=1).values
         person = person * (empty.view(-1, 1) == 0).to(person.dtype)                 # empty persons -> zeros
         person = person.view(B, M, -1)
+        mark('person_reduce')
         if return_stages:
             return dict(box_idx=box_idx, pooled=pooled, empty=empty, fps_idx=fps_idx, new_xyz=new_xyz,
                         sa_features=sa_feat, person_features=person)

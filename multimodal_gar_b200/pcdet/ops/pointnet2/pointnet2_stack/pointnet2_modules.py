@@ -47,6 +47,7 @@ class StackSAModuleMSG(nn.Module):
         self.pool_method = pool_method
         self.use_xyz = use_xyz
         self._packed = None
+        self.stage_mark = None   # optional callable(name): profiling hook between ball query and the MLP
         self.init_weights()
 
     def init_weights(self):
@@ -82,6 +83,8 @@ class StackSAModuleMSG(nn.Module):
                 g = self.groupers[k]
                 idx, empty = pointnet2_utils.ball_query(g.radius, g.nsample, xyz, xyz_batch_cnt, new_xyz,
                                                         new_xyz_batch_cnt)
+                if self.stage_mark is not None:
+                    self.stage_mark('ball_query')
                 sa_mlp_fused.sa_mlp_forward(channels, params, g.nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt,
                                             features, idx, empty_mask=empty, out=out[:, col:col + widths[k]],
                                             pool_avg=self.pool_method == 'avg_pool')

@@ -4,6 +4,8 @@ This replaces, for inference, the chain in the reference's StackSAModuleMSG.forw
 (/root/reference/pcdet/ops/pointnet2/pointnet2_stack/pointnet2_modules.py:89-110): grouping,
 `cat`, [Conv2d 1x1, BatchNorm2d, ReLU] x L, max_pool2d.
 """
+import ctypes
+
 import torch
 import torch.nn as nn
 
@@ -39,7 +41,9 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
                    empty_mask=None, out=None, pool_avg=False, uniform=None):
     """-> (M, channels[-1]) fp32.  `idx` as returned by ball_query (or the raw kernel output);
     `uniform=(n, m)` skips the ragged bookkeeping when every cloud has n points and m centroids."""
-    need_cuda(xyz=xyz, new_xyz=new_xyz, features=features, idx=idx, params=params, empty_mask=empty_mask, out=out)
+    need_cuda(xyz=xyz, new_xyz=new_xyz, features=features, idx=idx, params=params, empty_mask=empty_mask)
+    if out is not None and (not out.is_cuda or out.dtype != torch.float32 or out.stride(1) != 1):
+        raise _lib.MgarError("out must be a CUDA fp32 tensor with unit column stride")
     need_dtype(torch.float32, xyz=xyz, new_xyz=new_xyz, features=features, params=params)
     need_dtype(torch.int32, idx=idx)
     M = new_xyz.shape[0]
@@ -49,7 +53,6 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
         out = torch.empty((M, channels[-1]), dtype=torch.float32, device=xyz.device)
     if empty_mask is not None:
         empty_mask = empty_mask.to(torch.uint8).contiguous()
-    import ctypes
     ch = (ctypes.c_int * len(channels))(*channels)
     un, um = uniform if uniform is not None else (0, 0)
     with on_device(xyz):

@@ -37,6 +37,8 @@ def make_frame(seed, N=65536, M=40, density_scale=1.0, empty_frac=0.05):
     boxes = make_boxes(rng, M)
     fg = []
     empty = rng.random(M) < empty_frac
+    if M >= 8 and empty_frac > 0 and not empty.any():
+        empty[int(rng.integers(M))] = True       # the empty-flag path is always exercised
     for m in range(M):
         n_p = 0 if empty[m] else int(np.clip(rng.lognormal(np.log(150.0 * density_scale), 0.8), 0, 2000 * density_scale))
         if n_p == 0:
@@ -58,6 +60,11 @@ def make_frame(seed, N=65536, M=40, density_scale=1.0, empty_frac=0.05):
     xyz = np.concatenate([fg, ground, rest], axis=0)
     lo, hi = np.array(POINT_CLOUD_RANGE[:3]), np.array(POINT_CLOUD_RANGE[3:])
     xyz = np.clip(xyz, lo + 1e-3, hi - 1e-3)
+    for m in np.nonzero(empty)[0]:               # lift clutter out of the persons meant to be empty
+        cx, cy, cz, dx, dy, dz, rz = boxes[m]
+        near = (np.abs(xyz[:, 0] - cx) < dx + dy) & (np.abs(xyz[:, 1] - cy) < dx + dy) & \
+               (np.abs(xyz[:, 2] - cz) < dz / 2 + 0.05)
+        xyz[near, 2] = cz + dz / 2 + 0.2
     pts = np.concatenate([xyz, rng.random((N, 1))], axis=1).astype(np.float32)
     rng.shuffle(pts, axis=0)   # DataProcessor shuffle_points (mil3.yaml:51-54)
     return pts, boxes

@@ -159,7 +159,9 @@ void orc_roipoint_pool(const float *xyz, const float *boxes, const float *feat, 
  * :25-140 (batch kernel), :188-319 (stack kernel, block fixed at 1024, :340).
  * The block is simulated literally: thread tid scans k = tid, tid+bs, ... keeping the first
  * strict maximum, then the shared-memory tree halves with strict '>' (ties keep the lower slot).
- * Squared distance as compiled for the GPU: fma(dz,dz, fma(dy,dy, dx*dx)), d = x2 - x1. */
+ * Squared distance as nvcc 12.9 compiles it for sm_100 (SASS of oracle/_ref, every instantiation,
+ * also ball_query_kernel_stack): FMUL on dy, then FFMA dx, then FFMA dz, i.e.
+ * fma(dz,dz, fma(dx,dx, dy*dy)), d = x2 - x1. */
 int orc_opt_n_threads(int work_size)
 {
     int pow_2 = (int)(log((double)work_size) / log(2.0));
@@ -183,7 +185,7 @@ static void fps_one(const float *xyz, float *temp, int n, int m, int bs, int *id
             float best = -1.0f;
             for (int k = tid; k < n; k += bs) {
                 float dx = xyz[k * 3 + 0] - x1, dy = xyz[k * 3 + 1] - y1, dz = xyz[k * 3 + 2] - z1;
-                float d = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                float d = fmaf(dz, dz, fmaf(dx, dx, dy * dy));
                 float d2 = fminf(d, temp[k]);
                 temp[k] = d2;
                 if (d2 > best) { besti = k; best = d2; }
@@ -250,7 +252,7 @@ void orc_ball_query_stack(int B, int M, float radius, int nsample, const float *
         int n = xyz_batch_cnt[bs_idx], cnt = 0;
         for (int k = 0; k < n; k++) {
             float dx = q[0] - p[k * 3 + 0], dy = q[1] - p[k * 3 + 1], dz = q[2] - p[k * 3 + 2];
-            float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+            float d2 = fmaf(dz, dz, fmaf(dx, dx, dy * dy));
             if (d2 < radius2) {
                 if (cnt == 0)
                     for (int l = 0; l < nsample; l++) o[l] = k;

@@ -1,0 +1,117 @@
+"""CPU-only: host-side helpers mirrored from the reference, the synthetic frame generator, frame
+sharding, and the multi-rank path over gloo (world_size 2)."""
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from multimodal_gar_b200 import lidar_branch, synthetic
+from multimodal_gar_b200.pcdet.utils import box_utils, common_utils
+from oracle import oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_enlarge_box3d_matches_oracle_and_accepts_scalar():
+    boxes = synthetic.make_frame(0, N=64, M=9)[1]
+    got = box_utils.enlarge_box3d(torch.from_numpy(boxes), (0.2, 0.1, 0.0)).numpy()
+    np.testing.assert_array_equal(got, O.enlarge_box3d(boxes, (0.2, 0.1, 0.0)))
+    np.testing.assert_array_equal(box_utils.enlarge_box3d(boxes, 1.0), O.enlarge_box3d(boxes, (1.0, 1.0, 1.0)))
+    assert isinstance(box_utils.enlarge_box3d(boxes, (0, 0, 0)), np.ndarray)      # numpy in -> numpy out
+
+
+def test_rotate_points_along_z():
+    rng = np.random.default_rng(0)
+    p = rng.standard_normal((3, 10, 4)).astype(np.float32)
+    a = np.array([0.0, np.pi / 2, -0.3], dtype=np.float32)
+    out = common_utils.rotate_points_along_z(p, a)
+    np.testing.assert_allclose(out[0], p[0], atol=1e-6)
+    np.testing.assert_allclose(out[1, :, 0], -p[1, :, 1], atol=1e-6)              # x' = x cos - y sin
+    np.testing.assert_allclose(out[1, :, 1], p[1, :, 0], atol=1e-6)
+    np.testing.assert_array_equal(out[..., 2:], p[..., 2:])
+
+
+def test_canonical_transform_matches_oracle():
+    rng = np.random.default_rng(1)
+    pooled = rng.standard_normal((2, 5, 16, 4)).astype(np.float32)
+    boxes = synthetic.make_batch(3, 2, N=32, M=5)[1]
+    empty = np.array([[0, 1, 0, 0, 0], [0, 0, 0, 1, 0]], dtype=np.int32)
+    got = lidar_branch.canonical_transform(torch.from_numpy(pooled), torch.from_numpy(boxes), torch.from_numpy(empty))
+    np.testing.assert_allclose(got.numpy(), O.canonical_transform(pooled, boxes, empty), atol=2e-6)
+
+
+def test_synthetic_frame_is_seeded_and_exercises_every_branch():
+    a, ba = synthetic.make_frame(1994)
+    b, bb = synthetic.make_frame(1994)
+    np.testing.assert_array_equal(a, b)
+    np.testing.assert_array_equal(ba, bb)
+    assert a.shape == (65536, 4) and a.dtype == np.float32 and ba.shape == (40, 7)
+    mask = O.in_box_mask_gpu_sem(np.ascontiguousarray(a[:, :3]), ba)
+    per_box = mask.sum(axis=1)
+    assert (per_box == 0).any() and (per_box > 512).any() and ((per_box > 0) & (per_box < 512)).any()
+    assert (mask.sum(axis=0) > 1).any()                                            # overlapping boxes
+
+
+@pytest.mark.parametrize("frames,world", [(64, 1), (64, 2), (64, 8), (10, 4), (3, 8), (0, 2)])
+def test_shard_frames_is_a_partition(frames, world):
+    spans = [lidar_branch.shard_frames(frames, world, r) for r in range(world)]
+    assert spans[0][0] == 0 and spans[-1][1] == frames
+    for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+        assert a1 == b0 and a0 <= a1
+    sizes = [b - a for a, b in spans]
+    assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        lidar_branch.shard_frames(frames, world, world)
+
+
+_WORKER = r"""
+import os, sys
+import numpy as np
+import torch
+import torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from multimodal_gar_b200 import lidar_branch, synthetic
+from oracle import oracle as O
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+B, N, M, S = 6, 2048, 5, 32
+pts, boxes = synthetic.make_batch(7, B, N=N, M=M, density_scale=0.2)
+lo, hi = lidar_branch.shard_frames(B, world, rank)
+# each rank pools ITS frames (oracle stands in for the device here: this checks the sharding plumbing)
+pooled, empty = O.roipoint_pool3d(pts[lo:hi, :, :3], pts[lo:hi, :, 3:4], boxes[lo:hi], (0, 0, 0), S)
+mine = torch.from_numpy(pooled.reshape(hi - lo, -1))
+sizes = [lidar_branch.shard_frames(B, world, r) for r in range(world)]
+parts = [torch.zeros((b - a, mine.shape[1])) for a, b in sizes]
+dist.all_gather(parts, mine) if len(set(b - a for a, b in sizes)) == 1 else None
+t = torch.tensor([float(hi - lo), 1.25 * (rank + 1)])
+dist.all_reduce(t, op=dist.ReduceOp.MAX)          # the bench's max-over-ranks timing reduction
+if rank == 0:
+    full, _ = O.roipoint_pool3d(pts[..., :3], pts[..., 3:4], boxes, (0, 0, 0), S)
+    assert torch.equal(torch.cat(parts), torch.from_numpy(full.reshape(B, -1)))
+    assert t[1].item() == 1.25 * world
+    print("GLOO_OK", world)
+dist.barrier()
+dist.destroy_process_group()
+"""
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def test_frame_sharding_over_gloo_world2(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(_WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", str(_free_port()), str(script), ROOT]
+    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=240)
+    assert out.returncode == 0, out.stdout[-3000:]
+    assert "GLOO_OK 2" in out.stdout

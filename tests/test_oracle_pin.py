@@ -72,8 +72,8 @@ def _fps_block_sim(xyz, m, bs):
             best, besti = f(-1), 0
             for k in range(t, n, bs):
                 dx, dy, dz = f(xyz[k, 0] - x1), f(xyz[k, 1] - y1), f(xyz[k, 2] - z1)
-                # fma(dz,dz, fma(dy,dy, dx*dx)) evaluated exactly in float64 then rounded once per fma
-                d = f(np.float64(dy) * np.float64(dy) + np.float64(f(dx * dx)))
+                # fma(dz,dz, fma(dx,dx, dy*dy)) evaluated exactly in float64 then rounded once per fma
+                d = f(np.float64(dx) * np.float64(dx) + np.float64(f(dy * dy)))
                 d = f(np.float64(dz) * np.float64(dz) + np.float64(d))
                 d2 = min(d, temp[k])
                 temp[k] = d2

@@ -1,0 +1,250 @@
+"""-m gpu: the CUDA path (libmgar_lidar.so through the pcdet.ops mirrors) against the CPU oracle on
+the same seeded inputs.  Bit-exact for masks / indices / gathered values; 1e-5 relative (of the
+feature scale) for the fp32 shared-MLP features and the canonical rotation."""
+import numpy as np
+import pytest
+import torch
+
+import cases
+from multimodal_gar_b200 import synthetic
+from multimodal_gar_b200.pcdet.ops.pointnet2.pointnet2_stack import pointnet2_modules, pointnet2_utils, sa_mlp_fused
+from multimodal_gar_b200.pcdet.ops.roiaware_pool3d import roiaware_pool3d_utils
+from multimodal_gar_b200.pcdet.ops.roipoint_pool3d import roipoint_pool3d_cuda, roipoint_pool3d_utils
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def T(a, dev):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+
+def _assert_in_box_equal(got, want, xyz, boxes):
+    """glibc (oracle) vs libdevice (GPU) cosf/sinf may differ by an ulp: only pairs whose decision is
+    sensitive to that may differ (the reference-GPU tests compare every pair bit-exactly)."""
+    bad = got != want
+    if bad.any():
+        amb = np.stack([O.in_box_ambiguous(xyz[b], boxes[b]).any(axis=0) for b in range(xyz.shape[0])])
+        assert not (bad & ~amb).any(), "%d unambiguous in-box decisions differ" % int((bad & ~amb).sum())
+
+
+@pytest.mark.parametrize("N,M", [(4096, 12), (4099, 7), (1, 1), (65536, 40), (513, 1100)])
+def test_points_in_boxes_gpu(cuda, N, M):
+    pts, boxes = synthetic.make_batch(5, 2, N=N, M=M, density_scale=0.3)
+    xyz = np.ascontiguousarray(pts[..., :3])
+    got = roiaware_pool3d_utils.points_in_boxes_gpu(T(xyz, cuda), T(boxes, cuda)).cpu().numpy()
+    assert got.dtype == np.int32 and got.shape == (2, N)
+    _assert_in_box_equal(got, O.points_in_boxes_gpu(xyz, boxes), xyz, boxes)
+
+
+def test_points_in_boxes_gpu_faces_and_padding(cuda):
+    xyz, _, boxes = cases.frame_case()
+    got = roiaware_pool3d_utils.points_in_boxes_gpu(T(xyz, cuda), T(boxes, cuda)).cpu().numpy()
+    want = O.points_in_boxes_gpu(xyz, boxes)
+    _assert_in_box_equal(got, want, xyz, boxes)
+    M = boxes.shape[1]
+    assert got[1, 0] == M - 2 and got[1, 1] == M - 2 and got[1, 2] != M - 2
+
+
+def test_points_in_boxes_gpu_no_boxes(cuda):
+    out = roiaware_pool3d_utils.points_in_boxes_gpu(torch.zeros(1, 100, 3, device=cuda),
+                                                    torch.zeros(1, 0, 7, device=cuda))
+    assert (out == -1).all()
+
+
+@pytest.mark.parametrize("as_numpy", [True, False])
+def test_points_in_boxes_cpu_api_on_gpu(cuda, as_numpy):
+    """The host-buffer entry: margin 1e-2 semantics, bit-identical to the reference CPU function."""
+    pts, boxes = synthetic.make_frame(1994, N=16384, M=40)
+    xyz = np.ascontiguousarray(pts[:, :3])
+    want = O.points_in_boxes_cpu(xyz, boxes)
+    if as_numpy:
+        got = roiaware_pool3d_utils.points_in_boxes_cpu(xyz, boxes)
+        assert isinstance(got, np.ndarray)
+    else:
+        got = roiaware_pool3d_utils.points_in_boxes_cpu(torch.from_numpy(xyz), torch.from_numpy(boxes)).numpy()
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("extra,S", [((0.0, 0.0, 0.0), 128), ((0.2, 0.2, 0.2), 64), ((0.0, 0.0, 0.0), 512),
+                                     ((1.0, 1.0, 1.0), 2048)])
+def test_roipoint_pool3d(cuda, extra, S):
+    xyz, feat, boxes = cases.frame_case()
+    layer = roipoint_pool3d_utils.RoIPointPool3d(num_sampled_points=S, pool_extra_width=extra)
+    pooled, empty = layer(T(xyz, cuda), T(feat, cuda), T(boxes, cuda))
+    want_p, want_e, want_i = O.roipoint_pool3d(xyz, feat, boxes, extra, S, return_idx=True)
+    assert pooled.shape == want_p.shape and empty.dtype == torch.int32
+    if not np.array_equal(empty.cpu().numpy(), want_e) or not np.array_equal(pooled.cpu().numpy(), want_p):
+        # only ulp-ambiguous pairs may change membership
+        big = O.enlarge_box3d(boxes, extra)
+        amb = sum(int(O.in_box_ambiguous(xyz[b], big[b]).sum()) for b in range(xyz.shape[0]))
+        assert amb > 0, "pooled output differs from the oracle with no ambiguous pair"
+    assert (want_e == 0).sum() > 0 and (want_e.sum() > 0 or extra[0] >= 1.0)      # both branches exercised
+
+
+def test_roipoint_pool3d_multi_channel_and_idx(cuda):
+    xyz, _, boxes = cases.frame_case()
+    rng = np.random.default_rng(3)
+    feat = rng.random((xyz.shape[0], xyz.shape[1], 5)).astype(np.float32)
+    B, M, S = xyz.shape[0], boxes.shape[1], 96
+    pooled = torch.zeros((B, M, S, 8), device=cuda)
+    empty = torch.zeros((B, M), dtype=torch.int32, device=cuda)
+    pidx = torch.zeros((B, M, S), dtype=torch.int32, device=cuda)
+    roipoint_pool3d_cuda.forward(T(xyz, cuda), T(boxes, cuda), T(feat, cuda), pooled, empty, pts_idx=pidx)
+    want_p, want_e, want_i = O.roipoint_pool3d(xyz, feat, boxes, (0, 0, 0), S, return_idx=True)
+    np.testing.assert_array_equal(empty.cpu().numpy(), want_e)
+    np.testing.assert_array_equal(pooled.cpu().numpy(), want_p)
+    live = want_e == 0
+    np.testing.assert_array_equal(pidx.cpu().numpy()[live], want_i[live])
+
+
+def test_roipoint_pool3d_fused_canonical(cuda):
+    xyz, feat, boxes = cases.frame_case()
+    B, M, S = xyz.shape[0], boxes.shape[1], 128
+    pooled = torch.zeros((B, M, S, 4), device=cuda)
+    empty = torch.zeros((B, M), dtype=torch.int32, device=cuda)
+    roipoint_pool3d_cuda.forward(T(xyz, cuda), T(boxes, cuda), T(feat, cuda), pooled, empty, canonical=True)
+    want_p, want_e = O.roipoint_pool3d(xyz, feat, boxes, (0, 0, 0), S)
+    want_c = O.canonical_transform(want_p, boxes, want_e)
+    np.testing.assert_array_equal(empty.cpu().numpy(), want_e)
+    got = pooled.cpu().numpy().reshape(B * M, S, 4)
+    np.testing.assert_allclose(got[..., :3], want_c[..., :3], rtol=0, atol=1e-5 * 2.0)   # 1e-5 of the box scale
+    np.testing.assert_array_equal(got[..., 3], want_c[..., 3])
+
+
+@pytest.mark.parametrize("n,m", [(1, 1), (31, 31), (128, 64), (200, 64), (300, 300), (512, 512), (777, 100),
+                                 (1024, 128), (1500, 96), (2500, 40), (5000, 64), (9000, 33), (20000, 16)])
+def test_fps_batch_with_ties(cuda, n, m):
+    c = cases.cloud_with_ties(n, 3, n)
+    got = pointnet2_utils.farthest_point_sample(T(c, cuda), m).cpu().numpy()
+    np.testing.assert_array_equal(got, O.farthest_point_sample(c, m))
+
+
+def test_fps_batch_temp_contract(cuda):
+    from multimodal_gar_b200.pcdet.ops.pointnet2.pointnet2_stack import pointnet2_stack_cuda as ext
+    c = cases.cloud_with_ties(9, 4, 600)
+    temp = torch.full((4, 600), 1e10, device=cuda)
+    idx = torch.zeros((4, 50), dtype=torch.int32, device=cuda)
+    ext.farthest_point_sampling_wrapper(4, 600, 50, T(c, cuda), temp, idx)
+    want_i, want_t = O.farthest_point_sample(c, 50, return_temp=True)
+    np.testing.assert_array_equal(idx.cpu().numpy(), want_i)
+    np.testing.assert_array_equal(temp.cpu().numpy(), want_t)
+
+
+def test_fps_stack_ragged(cuda):
+    xyz, cnt, _, _, _ = cases.ragged_case()
+    pos = cnt > 0
+    npoint = [32, 64, 16, 40]
+    got = pointnet2_utils.stack_farthest_point_sample(T(xyz, cuda), T(cnt[pos], cuda), npoint).cpu().numpy()
+    np.testing.assert_array_equal(got, O.stack_farthest_point_sample(xyz, cnt[pos], npoint))
+    got = pointnet2_utils.stack_farthest_point_sample(T(xyz, cuda), T(cnt[pos], cuda), 20).cpu().numpy()
+    np.testing.assert_array_equal(got, O.stack_farthest_point_sample(xyz, cnt[pos], 20))
+
+
+def test_fps_stack_large_cloud(cuda):
+    rng = np.random.default_rng(11)
+    cnt = np.array([12000, 3000], dtype=np.int32)
+    xyz = rng.uniform(-5, 5, (int(cnt.sum()), 3)).astype(np.float32)
+    got = pointnet2_utils.stack_farthest_point_sample(T(xyz, cuda), T(cnt, cuda), [64, 32]).cpu().numpy()
+    np.testing.assert_array_equal(got, O.stack_farthest_point_sample(xyz, cnt, [64, 32]))
+
+
+@pytest.mark.parametrize("r,K", [(0.3, 16), (0.6, 32), (0.05, 8), (1.0, 64), (0.2, 1), (3.0, 100)])
+def test_ball_query_and_grouping_ragged(cuda, r, K):
+    xyz, cnt, new_xyz, ncnt, feats = cases.ragged_case()
+    idx, mask = pointnet2_utils.ball_query(r, K, T(xyz, cuda), T(cnt, cuda), T(new_xyz, cuda), T(ncnt, cuda))
+    want_i, want_m = O.ball_query(r, K, xyz, cnt, new_xyz, ncnt)
+    np.testing.assert_array_equal(idx.cpu().numpy(), want_i)
+    np.testing.assert_array_equal(mask.cpu().numpy(), want_m)
+    out = pointnet2_utils.grouping_operation(T(feats, cuda), T(cnt, cuda), idx, T(ncnt, cuda))
+    np.testing.assert_array_equal(out.cpu().numpy(), O.grouping_operation(feats, cnt, want_i, ncnt))
+
+
+def test_ball_query_raw_sentinel(cuda):
+    from multimodal_gar_b200.pcdet.ops.pointnet2.pointnet2_stack import pointnet2_stack_cuda as ext
+    xyz, cnt, new_xyz, ncnt, _ = cases.ragged_case()
+    idx = torch.zeros((new_xyz.shape[0], 8), dtype=torch.int32, device=cuda)
+    ext.ball_query_wrapper(len(cnt), new_xyz.shape[0], 0.05, 8, T(new_xyz, cuda), T(ncnt, cuda), T(xyz, cuda),
+                           T(cnt, cuda), idx)
+    want = O.ball_query_raw(0.05, 8, xyz, cnt, new_xyz, ncnt)
+    assert (want[:, 0] == -1).any()
+    np.testing.assert_array_equal(idx.cpu().numpy(), want)
+
+
+def test_grouping_backward(cuda):
+    xyz, cnt, new_xyz, ncnt, feats = cases.ragged_case()
+    idx, _ = O.ball_query(0.6, 16, xyz, cnt, new_xyz, ncnt)
+    f = T(feats, cuda).requires_grad_(True)
+    out = pointnet2_utils.grouping_operation(f, T(cnt, cuda), T(idx, cuda), T(ncnt, cuda))
+    rng = np.random.default_rng(0)
+    g = rng.standard_normal(out.shape).astype(np.float32)
+    out.backward(T(g, cuda))
+    want = O.grouping_operation_grad(g, idx, ncnt, cnt, feats.shape[0])
+    np.testing.assert_allclose(f.grad.cpu().numpy(), want, rtol=1e-5, atol=1e-5)   # float atomics: order differs
+
+
+def test_query_and_group(cuda):
+    xyz, cnt, new_xyz, ncnt, feats = cases.ragged_case()
+    qg = pointnet2_utils.QueryAndGroup(0.3, 16, use_xyz=True)
+    nf, idx = qg(T(xyz, cuda), T(cnt, cuda), T(new_xyz, cuda), T(ncnt, cuda), T(feats, cuda))
+    want_nf, want_idx = O.query_and_group(0.3, 16, xyz, cnt, new_xyz, ncnt, feats)
+    np.testing.assert_array_equal(idx.cpu().numpy(), want_idx)
+    np.testing.assert_array_equal(nf.cpu().numpy(), want_nf)
+
+
+def _feature_close(got, want):
+    scale = max(1.0, float(np.abs(want).max()))
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5 * scale)   # north_star: 1e-5 relative, fp32
+
+
+@pytest.mark.parametrize("spec,K,r", [([2, 64, 128], 32, 0.6), ([2, 16], 16, 0.3), ([2, 32, 32, 64], 40, 0.6),
+                                      ([2, 13, 7], 8, 0.05)])
+def test_sa_module_eval_fused_mlp(cuda, spec, K, r):
+    xyz, cnt, new_xyz, ncnt, feats = cases.ragged_case()
+    full = [spec[0] + 3] + spec[1:]
+    ref_mlp = O.make_sa_mlp(full, seed=4)
+    mod = pointnet2_modules.StackSAModuleMSG(radii=[r], nsamples=[K], mlps=[list(spec)], use_xyz=True)
+    mod.mlps[0].load_state_dict(ref_mlp.state_dict())
+    mod = mod.to(cuda).eval()
+    with torch.no_grad():
+        _, got = mod(T(xyz, cuda), T(cnt, cuda), T(new_xyz, cuda), T(ncnt, cuda), T(feats, cuda))
+    want = O.stack_sa_module_msg([ref_mlp], [r], [K], xyz, cnt, new_xyz, ncnt, feats)
+    assert got.shape == want.shape
+    _feature_close(got.cpu().numpy(), want)
+
+
+def test_sa_module_two_scales_and_train_mode(cuda):
+    xyz, cnt, new_xyz, ncnt, feats = cases.ragged_case()
+    mlps = [O.make_sa_mlp([5, 16, 32], seed=1), O.make_sa_mlp([5, 8, 24], seed=2)]
+    mod = pointnet2_modules.StackSAModuleMSG(radii=[0.3, 0.6], nsamples=[8, 16], mlps=[[2, 16, 32], [2, 8, 24]])
+    for k in range(2):
+        mod.mlps[k].load_state_dict(mlps[k].state_dict())
+    mod = mod.to(cuda).eval()
+    args = (T(xyz, cuda), T(cnt, cuda), T(new_xyz, cuda), T(ncnt, cuda), T(feats, cuda))
+    with torch.no_grad():
+        _, fused = mod(*args)
+    want = O.stack_sa_module_msg(mlps, [0.3, 0.6], [8, 16], xyz, cnt, new_xyz, ncnt, feats)
+    _feature_close(fused.cpu().numpy(), want)
+    # with autograd on, the reference's own composition runs on the new grouping kernels: same numbers
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    _, composed = mod(*args)
+    _feature_close(composed.detach().cpu().numpy(), want)
+    composed.sum().backward()
+    assert all(p.grad is not None for p in mod.parameters())
+
+
+def test_sa_mlp_uniform_layout(cuda):
+    rng = np.random.default_rng(5)
+    Bp, n, m, K = 6, 256, 64, 16
+    xyz = rng.uniform(-0.5, 0.5, (Bp * n, 3)).astype(np.float32)
+    feats = rng.random((Bp * n, 1)).astype(np.float32)
+    new_xyz = xyz.reshape(Bp, n, 3)[:, :m].reshape(-1, 3).copy()
+    cnt, ncnt = np.full(Bp, n, np.int32), np.full(Bp, m, np.int32)
+    mlp = O.make_sa_mlp([4, 64, 128], seed=9)
+    idx, mask = O.ball_query(0.3, K, xyz, cnt, new_xyz, ncnt)
+    ch, params = sa_mlp_fused.pack_shared_mlp(mlp)
+    got = sa_mlp_fused.sa_mlp_forward(ch, params.to(cuda), K, T(xyz, cuda), None, T(new_xyz, cuda), None,
+                                      T(feats, cuda), T(idx, cuda), uniform=(n, m))
+    want = O.stack_sa_module_msg([mlp], [0.3], [K], xyz, cnt, new_xyz, ncnt, feats)
+    _feature_close(got.cpu().numpy(), want)
