@@ -1,0 +1,344 @@
+// Set-abstraction shared MLP on the 5th-generation tensor cores (tcgen05 + TMEM), fused with the
+// grouping gather and the max-pool: the one dense contraction of the LiDAR hot path.
+//
+// Reference: StackSAModuleMSG.forward (pointnet2_stack/pointnet2_modules.py:78-112) after
+// QueryAndGroup (pointnet2_utils.py:123-159).  Shape handled here: 2 layers, C0 = 3 + C_in <= 8,
+// C1 = 64, C2 = 128, nsample = 32, max-pool (BASELINE configs[1]: 4 -> 64 -> 128); anything else
+// runs on the exact-fp32 kernel in sa_mlp.cu.
+//
+// Layer 1 (K = C0, a few FMAs per output) stays on the CUDA cores in exact fp32.  Layer 2 is
+//     D^T[c, pos] = sum_k W2[c, k] * h1[pos, k]        (M = 128 channels, N = 128 positions, K = 64)
+// as tcgen05.mma kind::tf32 with fp32 accumulation in TMEM.  To keep fp32-level accuracy (the
+// parity bar is 1e-5) every operand is split v = hi + lo with hi = tf32(v) and the product is
+// evaluated as lo*hi + hi*lo + hi*hi (3xTF32: the dropped lo*lo term is ~2^-22 relative).
+// Because the output channel is the M (TMEM lane) dimension, a thread of the epilogue owns one
+// channel and the 32 samples of a centroid are 32 consecutive TMEM columns: BatchNorm, ReLU and
+// the max over samples are a register loop with no shuffles, and the only HBM write is out[m, c].
+//
+// One persistent CTA per SM, warp-specialised:
+//   warps 0-3   epilogue: tcgen05.ld 32x32b.x32 -> scale/shift, max, ReLU -> coalesced store
+//   warp  4     TMEM allocation + the single MMA-issuing thread (24 MMAs per 128-position tile)
+//   warps 5-12  producers (two groups of four, one smem stage each): gather (xyz - centre | feat),
+//               layer 1, hi/lo split, 128B-swizzled K-major store of the B tile
+// mbarriers: full/empty per smem stage, tfull/tempty per TMEM accumulator stage (4 x 128 columns).
+#include "mgar_common.cuh"
+#include "stack_prefix.cuh"
+
+namespace mgar {
+
+constexpr int kTcC1 = 64, kTcC2 = 128, kTcNS = 32;
+constexpr int kTcTilePos = 128;                 // positions per tile = 4 centroids x 32 samples
+constexpr int kTcThreads = 13 * 32;
+constexpr uint32_t kOpBytes = 128 * 64 * 4;     // one 128 x 64 fp32 operand tile: 32 KB
+constexpr uint32_t kTcSmem = 2 * kOpBytes /* W2 hi, lo */ + 2 * 2 * kOpBytes /* 2 stages x (h1 hi, lo) */ + 1024;
+
+struct TcLayer1 {          // layer-1 parameters travel as kernel arguments (constant bank operands)
+    float w[8][kTcC1];     // [c_in][c_out]
+    float sc[kTcC1], sh[kTcC1];
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// hi = tf32(v) (round to nearest, low 13 mantissa bits zero), lo = v - hi (exact in fp32)
+__device__ __forceinline__ void split_tf32(float v, float &hi, float &lo) {
+    uint32_t h;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(v));
+    hi = __uint_as_float(h);
+    lo = __fsub_rn(v, hi);
+}
+
+// Shared-memory matrix descriptor: K-major operand, 128-byte swizzle, rows of 128 B (32 tf32),
+// 8-row atoms 1024 B apart (SBO), descriptor version 1 (sm_100).
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);          // start address       bits [0,14)
+    d |= (uint64_t)1 << 16;                           // leading byte offset bits [16,30) (unused for SW128 K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;                 // stride byte offset  bits [32,46)
+    d |= (uint64_t)1 << 46;                           // version = 1         bits [46,48)
+    d |= (uint64_t)2 << 61;                           // layout SWIZZLE_128B bits [61,64)
+    return d;
+}
+
+// byte offset of element (row r, 16-byte chunk c16 of the 64-wide K extent) inside an operand tile
+__device__ __forceinline__ uint32_t tile_off(int r, int c16) {
+    const int kb = c16 >> 3, cw = c16 & 7;
+    return (uint32_t)(kb * 16384 + (r >> 3) * 1024 + (r & 7) * 128 + ((cw ^ (r & 7)) << 4));
+}
+
+__device__ __forceinline__ int find_batch_tc(const int *__restrict__ pre, int B, int v) {
+    int lo = 0, hi = B;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(pre + mid) <= v) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+template <int C0>
+__global__ void __launch_bounds__(kTcThreads, 1)
+sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, int B, int M, int C_in, const float *__restrict__ xyz,
+                 int xyz_stride, const float *__restrict__ new_xyz, const float *__restrict__ features,
+                 const int *__restrict__ pre_xyz, const int *__restrict__ pre_new, int uniform, int n_u, int m_u,
+                 const int *__restrict__ idx, const unsigned char *__restrict__ empty_mask,
+                 const float *__restrict__ w2t /* [64][128] */, const float *__restrict__ sc2,
+                 const float *__restrict__ sh2, float *__restrict__ out, int ld_out) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t s_bar[12];   // full[2], empty[2], tfull[4], tempty[4]
+    __shared__ uint32_t s_tmem;
+
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024 B alignment
+    const uint32_t a_hi = base, a_lo = base + kOpBytes;
+    const uint32_t b_stage0 = base + 2 * kOpBytes;                  // stage s: hi at +s*2*kOpBytes, lo at +kOpBytes more
+    const uint32_t bar0 = smem_u32(s_bar);
+    auto FULL = [&](int s) { return bar0 + 8u * s; };
+    auto EMPTY = [&](int s) { return bar0 + 8u * (2 + s); };
+    auto TFULL = [&](int t) { return bar0 + 8u * (4 + t); };
+    auto TEMPTY = [&](int t) { return bar0 + 8u * (8 + t); };
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n_tiles = (M + 3) >> 2;
+
+    // ---- one-time setup: barriers, TMEM, W2 split into swizzled hi/lo operand tiles ---------------
+    if (tid == 0) {
+        for (int s = 0; s < 2; s++) { mbar_init(FULL(s), 128); mbar_init(EMPTY(s), 1); }
+        for (int t = 0; t < 4; t++) { mbar_init(TFULL(t), 1); mbar_init(TEMPTY(t), 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    for (int e = tid; e < 128 * 16; e += kTcThreads) {
+        const int c = e & 127, c16 = e >> 7;       // output channel (row), 16-byte chunk of K
+        float hi[4], lo[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) split_tf32(__ldg(w2t + (size_t)(c16 * 4 + j) * kTcC2 + c), hi[j], lo[j]);
+        const uint32_t off = tile_off(c, c16);
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_hi + off), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_lo + off), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (warp < 4) {
+        // ===== epilogue: thread = output channel, 32 consecutive TMEM columns = one centroid ==========
+        const int c = tid;
+        const float scale = __ldg(sc2 + c), shift = __ldg(sh2 + c);
+        int i = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, i++) {
+            const int t = i & 3, u = i >> 2;
+            mbar_wait(TFULL(t), u & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
+            float res[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                uint32_t v[32];
+                tc_ld32(taddr + q * 32, v);
+                tc_wait_ld();
+                float m = __fmaf_rn(__uint_as_float(v[0]), scale, shift);
+#pragma unroll
+                for (int s = 1; s < 32; s++) m = fmaxf(m, __fmaf_rn(__uint_as_float(v[s]), scale, shift));
+                res[q] = fmaxf(m, 0.f);            // ReLU commutes with the max over samples
+            }
+            tc_fence_before();
+            mbar_arrive(TEMPTY(t));
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int m = tile * 4 + q;
+                if (m < M) out[(size_t)m * ld_out + c] = res[q];
+            }
+        }
+    } else if (warp == 4) {
+        // ===== MMA issuer: one thread, 24 x (128x128x8 tf32) per tile ====================================
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            int i = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, i++) {
+                const int s = i & 1, j = i >> 1, t = i & 3, u = i >> 2;
+                mbar_wait(FULL(s), j & 1);
+                mbar_wait(TEMPTY(t), (u & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kOpBytes, b_lo = b_hi + kOpBytes;
+                const uint32_t d = tmem + (uint32_t)(t * 128);
+                // small terms first: W2lo*h1hi, W2hi*h1lo, then W2hi*h1hi
+                const uint32_t a_src[3] = {a_lo, a_hi, a_hi}, b_src[3] = {b_hi, b_lo, b_hi};
+                uint32_t acc = 0;
+#pragma unroll
+                for (int term = 0; term < 3; term++) {
+#pragma unroll
+                    for (int kk = 0; kk < 8; kk++) {
+                        const uint32_t koff = (uint32_t)((kk >> 2) * 16384 + (kk & 3) * 32);
+                        tc_mma_tf32(d, make_desc(a_src[term] + koff), make_desc(b_src[term] + koff), idesc, acc);
+                        acc = 1;
+                    }
+                }
+                tc_commit(EMPTY(s));     // smem stage reusable once these MMAs have read it
+                tc_commit(TFULL(t));     // accumulator ready for the epilogue
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== producers: gather + layer 1 (exact fp32) + hi/lo split + swizzled store =====================
+        const int g = (warp - 5) >> 2, pw = (warp - 5) & 3;     // group (= smem stage), centroid slot in the tile
+        const uint32_t b_hi = b_stage0 + (uint32_t)g * 2 * kOpBytes, b_lo = b_hi + kOpBytes;
+        const int r = pw * 32 + lane;
+        int i = 0, j = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, i++) {
+            if ((i & 1) != g) continue;
+            const int m = tile * 4 + pw;
+            float x[C0];
+#pragma unroll
+            for (int cc = 0; cc < C0; cc++) x[cc] = 0.f;
+            if (m < M) {
+                const bool empty = (__ldg(idx + (size_t)m * kTcNS) < 0) || (empty_mask && empty_mask[m]);
+                if (!empty) {
+                    long long start;
+                    if (uniform) start = (long long)(m / m_u) * n_u;
+                    else start = __ldg(pre_xyz + find_batch_tc(pre_new, B, m));
+                    const long long p = start + __ldg(idx + (size_t)m * kTcNS + lane);
+                    x[0] = __fsub_rn(__ldg(xyz + p * xyz_stride + 0), __ldg(new_xyz + (size_t)m * 3 + 0));
+                    x[1] = __fsub_rn(__ldg(xyz + p * xyz_stride + 1), __ldg(new_xyz + (size_t)m * 3 + 1));
+                    x[2] = __fsub_rn(__ldg(xyz + p * xyz_stride + 2), __ldg(new_xyz + (size_t)m * 3 + 2));
+#pragma unroll
+                    for (int cc = 3; cc < C0; cc++) x[cc] = __ldg(features + p * C_in + (cc - 3));
+                }
+            }
+            mbar_wait(EMPTY(g), (j & 1) ^ 1);
+#pragma unroll
+            for (int c16 = 0; c16 < 16; c16++) {
+                float hi[4], lo[4];
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int o = c16 * 4 + q;
+                    float acc = 0.f;
+#pragma unroll
+                    for (int cc = 0; cc < C0; cc++) acc = __fmaf_rn(x[cc], L1.w[cc][o], acc);
+                    const float y = fmaxf(__fmaf_rn(acc, L1.sc[o], L1.sh[o]), 0.f);
+                    split_tf32(y, hi[q], lo[q]);
+                }
+                const uint32_t off = tile_off(r, c16);
+                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(b_hi + off), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
+                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(b_lo + off), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
+            }
+            fence_async_smem();          // generic-proxy stores -> visible to the tensor core (async proxy)
+            mbar_arrive(FULL(g));
+            j++;
+        }
+    }
+
+    // ---- teardown ------------------------------------------------------------------------------------
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+    }
+}
+
+}  // namespace mgar
+
+using namespace mgar;
+
+template <int C0>
+static int launch_tc(int grid, cudaStream_t st, const TcLayer1 &L1, int B, int M, int C_in, const float *xyz,
+                     int xyz_stride, const float *new_xyz, const float *features, const int *pre_xyz,
+                     const int *pre_new, int uniform, int n_u, int m_u, const int *idx,
+                     const unsigned char *empty_mask, const float *w2t, const float *sc2, const float *sh2,
+                     float *out, int ld_out) {
+    MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc_kernel<C0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmem));
+    sa_mlp_tc_kernel<C0><<<grid, kTcThreads, kTcSmem, st>>>(L1, B, M, C_in, xyz, xyz_stride, new_xyz, features, pre_xyz,
+                                                            pre_new, uniform, n_u, m_u, idx, empty_mask, w2t, sc2, sh2,
+                                                            out, ld_out);
+    count_launch();
+    return check_launch("sa_mlp_tc");
+}
+
+extern "C" int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg) {
+    return nsample == kTcNS && C_in >= 0 && C_in <= 5 && n_layers == 2 && channels_host && channels_host[0] == 3 + C_in &&
+           channels_host[1] == kTcC1 && channels_host[2] == kTcC2 && !pool_avg;
+}
+
+extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float *xyz, int xyz_stride,
+                                  const int *xyz_batch_cnt, const float *new_xyz, const int *new_xyz_batch_cnt,
+                                  int uniform_n, int uniform_m, const float *features, const int *idx,
+                                  const unsigned char *empty_mask, int n_layers, const int *channels_host,
+                                  const float *params, const float *params_host, float *out, int ld_out, int pool_avg,
+                                  void *stream) {
+    MGAR_REQUIRE(B >= 1 && M >= 0, "sa_mlp_tc: bad size");
+    MGAR_REQUIRE(mgar_sa_mlp_tc_supported(nsample, C_in, n_layers, channels_host, pool_avg),
+                 "sa_mlp_tc: only nsample=32, C_in<=5, channels [3+C_in,64,128], max-pool run on the tensor-core path");
+    if (M == 0) return MGAR_OK;
+    MGAR_REQUIRE(xyz && new_xyz && idx && params && params_host && out, "sa_mlp_tc: null pointer");
+    MGAR_REQUIRE(features || C_in == 0, "sa_mlp_tc: features missing");
+    MGAR_REQUIRE(xyz_stride >= 3, "sa_mlp_tc: xyz_stride must be >= 3");
+    const bool uniform = uniform_n > 0;
+    MGAR_REQUIRE(uniform || (xyz_batch_cnt && new_xyz_batch_cnt), "sa_mlp_tc: batch counts missing");
+    const int C0 = 3 + C_in;
+    TcLayer1 L1;
+    for (int c = 0; c < 8; c++)
+        for (int o = 0; o < kTcC1; o++) L1.w[c][o] = c < C0 ? params_host[c * kTcC1 + o] : 0.f;
+    for (int o = 0; o < kTcC1; o++) {
+        L1.sc[o] = params_host[C0 * kTcC1 + o];
+        L1.sh[o] = params_host[C0 * kTcC1 + kTcC1 + o];
+    }
+    const float *w2t = params + C0 * kTcC1 + 2 * kTcC1;
+    const float *sc2 = w2t + kTcC1 * kTcC2, *sh2 = sc2 + kTcC2;
+    cudaStream_t st = (cudaStream_t)stream;
+    PrefixWs ws;
+    if (!uniform) {
+        if (int rc = ws.alloc(B, st)) return rc;
+        if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
+    }
+    const int n_tiles = (M + 3) / 4;
+    const int grid = n_tiles < kNumSMs ? n_tiles : kNumSMs;     // persistent: one CTA per SM
+#define MGAR_TC_CASE(c0)                                                                                          \
+    if (C0 == c0)                                                                                                 \
+        return launch_tc<c0>(grid, st, L1, B, M, C_in, xyz, xyz_stride, new_xyz, features, ws.b, ws.a, uniform ? 1 : 0, \
+                             uniform_n, uniform_m, idx, empty_mask, w2t, sc2, sh2, out, ld_out);
+    MGAR_TC_CASE(3) MGAR_TC_CASE(4) MGAR_TC_CASE(5) MGAR_TC_CASE(6) MGAR_TC_CASE(7) MGAR_TC_CASE(8)
+#undef MGAR_TC_CASE
+    set_error("sa_mlp_tc: unsupported C0=%d", C0);
+    return MGAR_EINVAL;
+}

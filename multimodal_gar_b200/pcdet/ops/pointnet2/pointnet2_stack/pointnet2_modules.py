@@ -66,8 +66,11 @@ class StackSAModuleMSG(nn.Module):
 
     def _pack(self, device):
         if self._packed is None or self._packed[0][1].device != device:
-            self._packed = [tuple(t if isinstance(t, list) else t.to(device) for t in sa_mlp_fused.pack_shared_mlp(m))
-                            for m in self.mlps]
+            self._packed = []
+            for m in self.mlps:
+                channels, params = sa_mlp_fused.pack_shared_mlp(m)
+                host = params.cpu().contiguous()
+                self._packed.append((channels, host.to(device), host))
         return self._packed
 
     def forward(self, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features=None, empty_voxel_set_zeros=True):
@@ -76,10 +79,10 @@ class StackSAModuleMSG(nn.Module):
             and not torch.is_grad_enabled()
         if fused:
             packed = self._pack(xyz.device)
-            widths = [ch[-1] for ch, _ in packed]
+            widths = [p[0][-1] for p in packed]
             out = torch.empty((new_xyz.shape[0], sum(widths)), dtype=torch.float32, device=xyz.device)
             col = 0
-            for k, (channels, params) in enumerate(packed):
+            for k, (channels, params, params_host) in enumerate(packed):
                 g = self.groupers[k]
                 idx, empty = pointnet2_utils.ball_query(g.radius, g.nsample, xyz, xyz_batch_cnt, new_xyz,
                                                         new_xyz_batch_cnt)
@@ -87,7 +90,7 @@ class StackSAModuleMSG(nn.Module):
                     self.stage_mark('ball_query')
                 sa_mlp_fused.sa_mlp_forward(channels, params, g.nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt,
                                             features, idx, empty_mask=empty, out=out[:, col:col + widths[k]],
-                                            pool_avg=self.pool_method == 'avg_pool')
+                                            pool_avg=self.pool_method == 'avg_pool', params_host=params_host)
                 col += widths[k]
             return new_xyz, out
 

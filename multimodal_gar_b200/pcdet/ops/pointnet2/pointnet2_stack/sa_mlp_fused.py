@@ -5,6 +5,7 @@ This replaces, for inference, the chain in the reference's StackSAModuleMSG.forw
 `cat`, [Conv2d 1x1, BatchNorm2d, ReLU] x L, max_pool2d.
 """
 import ctypes
+import os
 
 import torch
 import torch.nn as nn
@@ -37,15 +38,28 @@ def pack_shared_mlp(seq):
     return channels, torch.cat(parts).contiguous()
 
 
+def tc_supported(channels, nsample, C_in, pool_avg=False):
+    """True when the tcgen05 path handles this shape (nsample 32, [3+C_in, 64, 128], max-pool)."""
+    ch = (ctypes.c_int * len(channels))(*channels)
+    return bool(_lib.lib().mgar_sa_mlp_tc_supported(int(nsample), int(C_in), len(channels) - 1, ctypes.addressof(ch),
+                                                    1 if pool_avg else 0))
+
+
 def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features, idx,
-                   empty_mask=None, out=None, pool_avg=False, uniform=None):
+                   empty_mask=None, out=None, pool_avg=False, uniform=None, params_host=None, impl=None):
     """-> (M, channels[-1]) fp32.  `idx` as returned by ball_query (or the raw kernel output);
-    `uniform=(n, m)` skips the ragged bookkeeping when every cloud has n points and m centroids."""
-    need_cuda(xyz=xyz, new_xyz=new_xyz, features=features, idx=idx, params=params, empty_mask=empty_mask)
-    if out is not None and (not out.is_cuda or out.dtype != torch.float32 or out.stride(1) != 1):
-        raise _lib.MgarError("out must be a CUDA fp32 tensor with unit column stride")
+    `uniform=(n, m)` skips the ragged bookkeeping when every cloud has n points and m centroids.
+
+    impl: 'tc' (tcgen05 tensor cores, 3xTF32), 'fp32' (CUDA-core FFMA) or None = tensor cores whenever the
+    shape is supported and `params_host` (CPU copy of `params`) is given; env MGAR_SA_MLP overrides.
+    `xyz` may be a (N,3) array or a strided view of the first three columns of a (N,3+C) array (tc only)."""
+    need_cuda(new_xyz=new_xyz, features=features, idx=idx, params=params, empty_mask=empty_mask)
     need_dtype(torch.float32, xyz=xyz, new_xyz=new_xyz, features=features, params=params)
     need_dtype(torch.int32, idx=idx)
+    if not xyz.is_cuda or xyz.dim() != 2 or xyz.stride(1) != 1:
+        raise _lib.MgarError("xyz must be a CUDA (N,3) tensor with unit column stride")
+    if out is not None and (not out.is_cuda or out.dtype != torch.float32 or out.stride(1) != 1):
+        raise _lib.MgarError("out must be a CUDA fp32 tensor with unit column stride")
     M = new_xyz.shape[0]
     B = xyz_batch_cnt.shape[0] if xyz_batch_cnt is not None else xyz.shape[0] // uniform[0]
     C_in = 0 if features is None else features.shape[1]
@@ -53,11 +67,25 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
         out = torch.empty((M, channels[-1]), dtype=torch.float32, device=xyz.device)
     if empty_mask is not None:
         empty_mask = empty_mask.to(torch.uint8).contiguous()
+    impl = os.environ.get("MGAR_SA_MLP", impl)
+    if impl is None:
+        impl = 'tc' if (params_host is not None and tc_supported(channels, nsample, C_in, pool_avg)) else 'fp32'
     ch = (ctypes.c_int * len(channels))(*channels)
     un, um = uniform if uniform is not None else (0, 0)
+    L = _lib.lib()
     with on_device(xyz):
-        _lib.check(_lib.lib().mgar_sa_mlp_fwd_fp32(
-            B, M, nsample, C_in, ptr(xyz), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt), un, um,
-            ptr(features), ptr(idx), ptr(empty_mask), len(channels) - 1, ctypes.addressof(ch), ptr(params),
-            ptr(out), out.stride(0), 1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd")
+        if impl == 'tc':
+            if params_host is None or params_host.is_cuda or not params_host.is_contiguous():
+                raise _lib.MgarError("the tensor-core path needs params_host (contiguous CPU copy of params)")
+            _lib.check(L.mgar_sa_mlp_fwd_tc(
+                B, M, nsample, C_in, ptr(xyz), xyz.stride(0), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt),
+                un, um, ptr(features), ptr(idx), ptr(empty_mask), len(channels) - 1, ctypes.addressof(ch), ptr(params),
+                ptr(params_host), ptr(out), out.stride(0), 1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd_tc")
+        else:
+            if not xyz.is_contiguous():
+                raise _lib.MgarError("the fp32 path needs a contiguous (N,3) xyz")
+            _lib.check(L.mgar_sa_mlp_fwd_fp32(
+                B, M, nsample, C_in, ptr(xyz), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt), un, um,
+                ptr(features), ptr(idx), ptr(empty_mask), len(channels) - 1, ctypes.addressof(ch), ptr(params),
+                ptr(out), out.stride(0), 1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd")
     return out

@@ -248,3 +248,36 @@ def test_sa_mlp_uniform_layout(cuda):
                                       T(feats, cuda), T(idx, cuda), uniform=(n, m))
     want = O.stack_sa_module_msg([mlp], [0.3], [K], xyz, cnt, new_xyz, ncnt, feats)
     _feature_close(got.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("Bp,n,m,C_in,layout", [(40, 512, 512, 1, "uniform"), (7, 300, 129, 1, "ragged"),
+                                                (5, 256, 64, 0, "ragged"), (3, 128, 50, 5, "uniform"),
+                                                (6, 512, 100, 1, "strided")])
+def test_sa_mlp_tensor_core_path(cuda, Bp, n, m, C_in, layout):
+    """tcgen05 (3xTF32) path against the torch-CPU fp32 oracle AND the exact-fp32 CUDA kernel."""
+    rng = np.random.default_rng(Bp * 1000 + n)
+    K = 32
+    pooled = rng.uniform(-0.5, 0.5, (Bp * n, 3 + max(C_in, 1))).astype(np.float32)
+    pooled[:, :3] *= np.array([0.7, 0.7, 1.8], dtype=np.float32)
+    xyz = np.ascontiguousarray(pooled[:, :3])
+    feats = np.ascontiguousarray(pooled[:, 3:3 + C_in]) if C_in else None
+    new_xyz = xyz.reshape(Bp, n, 3)[:, :m].reshape(-1, 3).copy()
+    new_xyz[::37] += 9.0                                     # empty balls
+    cnt, ncnt = np.full(Bp, n, np.int32), np.full(Bp, m, np.int32)
+    mlp = O.make_sa_mlp([3 + C_in, 64, 128], seed=Bp)
+    idx, mask = O.ball_query(0.3, K, xyz, cnt, new_xyz, ncnt)
+    assert mask.any()
+    want = O.stack_sa_module_msg([mlp], [0.3], [K], xyz, cnt, new_xyz, ncnt, feats)
+    ch, params = sa_mlp_fused.pack_shared_mlp(mlp)
+    assert sa_mlp_fused.tc_supported(ch, K, C_in)
+    dxyz = T(pooled, cuda)[:, :3] if layout == "strided" else T(xyz, cuda)
+    kw = dict(uniform=(n, m)) if layout != "ragged" else {}
+    cn, ncn = (None, None) if layout != "ragged" else (T(cnt, cuda), T(ncnt, cuda))
+    dfe = None if feats is None else T(feats, cuda)
+    got = sa_mlp_fused.sa_mlp_forward(ch, params.to(cuda), K, dxyz, cn, T(new_xyz, cuda), ncn, dfe, T(idx, cuda),
+                                      empty_mask=T(mask, cuda), params_host=params, impl='tc', **kw)
+    _feature_close(got.cpu().numpy(), want)
+    if layout != "strided":
+        ref32 = sa_mlp_fused.sa_mlp_forward(ch, params.to(cuda), K, dxyz, cn, T(new_xyz, cuda), ncn, dfe, T(idx, cuda),
+                                            empty_mask=T(mask, cuda), impl='fp32', **kw)
+        _feature_close(got.cpu().numpy(), ref32.cpu().numpy())
