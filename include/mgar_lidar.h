@@ -130,15 +130,20 @@ MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const flo
  * TMEM, 3xTF32 operand splitting: fp32-level accuracy, within the 1e-5 parity bar) for the shape
  * mgar_sa_mlp_tc_supported() accepts: nsample = 32, C_in <= 5, channels [3+C_in, 64, 128], max-pool
  * (BASELINE configs[1]).  Other shapes must use mgar_sa_mlp_fwd_fp32.  Extra arguments:
- * xyz_stride = floats between consecutive xyz rows (3 for a packed (N,3) array, 4 to read the xyz
- * columns of a pooled (N,3+1) array in place); params_host = HOST copy of `params` (layer 1 is passed
- * to the kernel by value). */
+ * xyz_stride / feat_stride = floats between consecutive rows (3 / C_in for packed arrays; 4 / 4 with
+ * features == xyz + 3 reads a pooled (N,3+1) array in place with one 128-bit load per point);
+ * params_host = HOST copy of `params` (layer 1 is passed to the kernel by value);
+ * out may be NULL when only the group maxima are wanted;
+ * group_max (ceil(M/group_size), 128), optional: max of the output rows over each run of group_size
+ * consecutive centroids (the per-person feature when every person has group_size centroids); rows
+ * whose group_zero[g] != 0 stay zero (empty persons).  The buffer is cleared by this call. */
 MGAR_API int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg);
 MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float *xyz, int xyz_stride,
                                 const int *xyz_batch_cnt, const float *new_xyz, const int *new_xyz_batch_cnt,
-                                int uniform_n, int uniform_m, const float *features, const int *idx,
+                                int uniform_n, int uniform_m, const float *features, int feat_stride, const int *idx,
                                 const unsigned char *empty_mask, int n_layers, const int *channels_host,
-                                const float *params, const float *params_host, float *out, int ld_out, int pool_avg,
+                                const float *params, const float *params_host, float *out, int ld_out,
+                                float *group_max, int group_size, const int *group_zero, int pool_avg,
                                 void *stream);
 
 #ifdef __cplusplus

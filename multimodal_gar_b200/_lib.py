@@ -31,7 +31,8 @@ SIGNATURES = {
     "mgar_group_points_stack": [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_group_points_grad_stack": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_sa_mlp_tc_supported": [_i, _i, _i, _p, _i],
-    "mgar_sa_mlp_fwd_tc": [_i, _i, _i, _i, _p, _i, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _p, _i, _i, _p],
+    "mgar_sa_mlp_fwd_tc": [_i, _i, _i, _i, _p, _i, _p, _p, _p, _i, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _i, _p, _i, _p, _i,
+                           _p],
     "mgar_sa_mlp_fwd_fp32": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _i, _i, _p],
 }
 

@@ -33,8 +33,8 @@ constexpr uint32_t kOpBytes = 128 * 64 * 4;     // one 128 x 64 fp32 operand til
 constexpr uint32_t kTcSmem = 2 * kOpBytes /* W2 hi, lo */ + 2 * 2 * kOpBytes /* 2 stages x (h1 hi, lo) */ + 1024;
 
 struct TcLayer1 {          // layer-1 parameters travel as kernel arguments (constant bank operands)
-    float w[8][kTcC1];     // [c_in][c_out]
-    float sc[kTcC1], sh[kTcC1];
+    float w[8][kTcC1];     // [c_in][c_out], BatchNorm scale folded in: w * gamma / sqrt(var + eps)
+    float sh[kTcC1];       // beta - mean * scale
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------------
@@ -77,11 +77,10 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 }
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// hi = tf32(v) (round to nearest, low 13 mantissa bits zero), lo = v - hi (exact in fp32)
+// hi = tf32(v) (round to nearest by integer arithmetic: cvt.rna.tf32 expands to ~4 instructions),
+// low 13 mantissa bits zero; lo = v - hi (exact in fp32)
 __device__ __forceinline__ void split_tf32(float v, float &hi, float &lo) {
-    uint32_t h;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(v));
-    hi = __uint_as_float(h);
+    hi = __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xffffe000u);
     lo = __fsub_rn(v, hi);
 }
 
@@ -112,14 +111,24 @@ __device__ __forceinline__ int find_batch_tc(const int *__restrict__ pre, int B,
     return lo;
 }
 
+struct TcArgs {
+    int B, M, C_in;
+    const float *xyz; int xyz_stride;
+    const float *new_xyz;
+    const float *features; int feat_stride;
+    const int *pre_xyz, *pre_new; int uniform, n_u, m_u;
+    const int *idx;
+    const unsigned char *empty_mask;
+    const float *w2t /* [64][128] */, *sc2, *sh2;
+    float *out; int ld_out;              // (M, 128) SA features, may be null
+    float *gmax; int group_size;         // (ceil(M / group_size), 128) max over each group of centroids, may be null
+    const int *group_zero;               // per group: non-zero -> the group's row stays zero (empty person)
+    int packed4;                         // xyz/features are columns 0..2 / 3 of one 16B-aligned (N,4) array
+};
+
 template <int C0>
 __global__ void __launch_bounds__(kTcThreads, 1)
-sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, int B, int M, int C_in, const float *__restrict__ xyz,
-                 int xyz_stride, const float *__restrict__ new_xyz, const float *__restrict__ features,
-                 const int *__restrict__ pre_xyz, const int *__restrict__ pre_new, int uniform, int n_u, int m_u,
-                 const int *__restrict__ idx, const unsigned char *__restrict__ empty_mask,
-                 const float *__restrict__ w2t /* [64][128] */, const float *__restrict__ sc2,
-                 const float *__restrict__ sh2, float *__restrict__ out, int ld_out) {
+sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcArgs A) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t s_bar[12];   // full[2], empty[2], tfull[4], tempty[4]
     __shared__ uint32_t s_tmem;
@@ -134,7 +143,13 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, int B, int M, int C_in, co
     auto TEMPTY = [&](int t) { return bar0 + 8u * (8 + t); };
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int M = A.M;
     const int n_tiles = (M + 3) >> 2;
+    // contiguous tile range per CTA: consecutive tiles belong to the same person, so the running
+    // group max of the epilogue is flushed only a handful of times
+    const int t_beg = (int)((long long)blockIdx.x * n_tiles / gridDim.x);
+    const int t_end = (int)((long long)(blockIdx.x + 1) * n_tiles / gridDim.x);
+    const int my_tiles = t_end - t_beg;
 
     // ---- one-time setup: barriers, TMEM, W2 split into swizzled hi/lo operand tiles ---------------
     if (tid == 0) {
@@ -150,7 +165,7 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, int B, int M, int C_in, co
         const int c = e & 127, c16 = e >> 7;       // output channel (row), 16-byte chunk of K
         float hi[4], lo[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) split_tf32(__ldg(w2t + (size_t)(c16 * 4 + j) * kTcC2 + c), hi[j], lo[j]);
+        for (int j = 0; j < 4; j++) split_tf32(__ldg(A.w2t + (size_t)(c16 * 4 + j) * kTcC2 + c), hi[j], lo[j]);
         const uint32_t off = tile_off(c, c16);
         asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_hi + off), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
         asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_lo + off), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
@@ -164,38 +179,56 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, int B, int M, int C_in, co
     if (warp < 4) {
         // ===== epilogue: thread = output channel, 32 consecutive TMEM columns = one centroid ==========
         const int c = tid;
-        const float scale = __ldg(sc2 + c), shift = __ldg(sh2 + c);
-        int i = 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, i++) {
-            const int t = i & 3, u = i >> 2;
+        const float scale = __ldg(A.sc2 + c), shift = __ldg(A.sh2 + c);
+        float gm = 0.f;
+        int cur_group = -1;
+        auto flush = [&]() {
+            if (A.gmax && cur_group >= 0 && !(A.group_zero && __ldg(A.group_zero + cur_group)))
+                atomicMax(reinterpret_cast<int *>(A.gmax + (size_t)cur_group * kTcC2 + c), __float_as_int(gm));
+        };
+        for (int i = 0; i < my_tiles; i++) {
+            const int tile = t_beg + i, t = i & 3, u = i >> 2;
             mbar_wait(TFULL(t), u & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
             float res[4];
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-                uint32_t v[32];
-                tc_ld32(taddr + q * 32, v);
+            for (int h = 0; h < 2; h++) {
+                uint32_t v0[32], v1[32];
+                tc_ld32(taddr + (2 * h) * 32, v0);
+                tc_ld32(taddr + (2 * h + 1) * 32, v1);
                 tc_wait_ld();
-                float m = __fmaf_rn(__uint_as_float(v[0]), scale, shift);
+                float m0 = __fmaf_rn(__uint_as_float(v0[0]), scale, shift);
+                float m1 = __fmaf_rn(__uint_as_float(v1[0]), scale, shift);
 #pragma unroll
-                for (int s = 1; s < 32; s++) m = fmaxf(m, __fmaf_rn(__uint_as_float(v[s]), scale, shift));
-                res[q] = fmaxf(m, 0.f);            // ReLU commutes with the max over samples
+                for (int s = 1; s < 32; s++) {
+                    m0 = fmaxf(m0, __fmaf_rn(__uint_as_float(v0[s]), scale, shift));
+                    m1 = fmaxf(m1, __fmaf_rn(__uint_as_float(v1[s]), scale, shift));
+                }
+                res[2 * h] = fmaxf(m0, 0.f);       // ReLU commutes with the max over samples
+                res[2 * h + 1] = fmaxf(m1, 0.f);
             }
             tc_fence_before();
             mbar_arrive(TEMPTY(t));
 #pragma unroll
             for (int q = 0; q < 4; q++) {
                 const int m = tile * 4 + q;
-                if (m < M) out[(size_t)m * ld_out + c] = res[q];
+                if (m < M) {
+                    if (A.out) A.out[(size_t)m * A.ld_out + c] = res[q];
+                    if (A.gmax) {
+                        const int grp = m / A.group_size;
+                        if (grp != cur_group) { flush(); cur_group = grp; gm = 0.f; }
+                        gm = fmaxf(gm, res[q]);
+                    }
+                }
             }
         }
+        flush();
     } else if (warp == 4) {
         // ===== MMA issuer: one thread, 24 x (128x128x8 tf32) per tile ====================================
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-            int i = 0;
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, i++) {
+            for (int i = 0; i < my_tiles; i++) {
                 const int s = i & 1, j = i >> 1, t = i & 3, u = i >> 2;
                 mbar_wait(FULL(s), j & 1);
                 mbar_wait(TEMPTY(t), (u & 1) ^ 1);
@@ -221,30 +254,67 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, int B, int M, int C_in, co
         __syncwarp();
     } else {
         // ===== producers: gather + layer 1 (exact fp32) + hi/lo split + swizzled store =====================
+        // Two groups of four warps; group g fills smem stage g with every other tile.  The gather is a
+        // two-level dependent load (idx -> point), so it is software-pipelined two tiles ahead: while
+        // tile j is computed, the points of tile j+1 and the indices of tile j+2 are in flight.
         const int g = (warp - 5) >> 2, pw = (warp - 5) & 3;     // group (= smem stage), centroid slot in the tile
         const uint32_t b_hi = b_stage0 + (uint32_t)g * 2 * kOpBytes, b_lo = b_hi + kOpBytes;
         const int r = pw * 32 + lane;
-        int i = 0, j = 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, i++) {
-            if ((i & 1) != g) continue;
-            const int m = tile * 4 + pw;
+
+        auto load_idx = [&](int i, int &iv, int &em) {          // local tile i -> this lane's sample index
+            const int m = (t_beg + i) * 4 + pw;
+            iv = -1; em = 0;
+            if (i < my_tiles && m < M) {
+                iv = __ldg(A.idx + (size_t)m * kTcNS + lane);
+                if (A.empty_mask) em = A.empty_mask[m];
+            }
+        };
+        // raw gathered row (before the centre is subtracted) + centre; live = centroid exists and ball not empty
+        auto load_pt = [&](int i, int iv, int em, float (&v)[C0], float (&q)[3], bool &live) {
+            const int m = (t_beg + i) * 4 + pw;
+            const int first = __shfl_sync(0xffffffffu, iv, 0);
+            live = (i < my_tiles) && (m < M) && first >= 0 && !em;
+            if (live) {
+                long long start;
+                if (A.uniform) start = (long long)(m / A.m_u) * A.n_u;
+                else start = __ldg(A.pre_xyz + find_batch_tc(A.pre_new, A.B, m));
+                const long long p = start + (iv < 0 ? 0 : iv);
+                if (C0 == 4 && A.packed4) {
+                    const float4 t4 = __ldg(reinterpret_cast<const float4 *>(A.xyz + p * 4));
+                    v[0] = t4.x; v[1] = t4.y; v[2] = t4.z; v[C0 - 1] = t4.w;
+                } else {
+                    v[0] = __ldg(A.xyz + p * A.xyz_stride + 0);
+                    v[1] = __ldg(A.xyz + p * A.xyz_stride + 1);
+                    v[2] = __ldg(A.xyz + p * A.xyz_stride + 2);
+#pragma unroll
+                    for (int cc = 3; cc < C0; cc++) v[cc] = __ldg(A.features + p * A.feat_stride + (cc - 3));
+                }
+                q[0] = __ldg(A.new_xyz + (size_t)m * 3 + 0);
+                q[1] = __ldg(A.new_xyz + (size_t)m * 3 + 1);
+                q[2] = __ldg(A.new_xyz + (size_t)m * 3 + 2);
+            }
+        };
+
+        int iv_a, em_a, iv_b, em_b;
+        float vb[C0], qb[3];
+        bool live_b;
+        load_idx(g, iv_b, em_b);
+        load_idx(g + 2, iv_a, em_a);
+        load_pt(g, iv_b, em_b, vb, qb, live_b);
+        int j = 0;
+        for (int i = g; i < my_tiles; i += 2, j++) {
             float x[C0];
 #pragma unroll
             for (int cc = 0; cc < C0; cc++) x[cc] = 0.f;
-            if (m < M) {
-                const bool empty = (__ldg(idx + (size_t)m * kTcNS) < 0) || (empty_mask && empty_mask[m]);
-                if (!empty) {
-                    long long start;
-                    if (uniform) start = (long long)(m / m_u) * n_u;
-                    else start = __ldg(pre_xyz + find_batch_tc(pre_new, B, m));
-                    const long long p = start + __ldg(idx + (size_t)m * kTcNS + lane);
-                    x[0] = __fsub_rn(__ldg(xyz + p * xyz_stride + 0), __ldg(new_xyz + (size_t)m * 3 + 0));
-                    x[1] = __fsub_rn(__ldg(xyz + p * xyz_stride + 1), __ldg(new_xyz + (size_t)m * 3 + 1));
-                    x[2] = __fsub_rn(__ldg(xyz + p * xyz_stride + 2), __ldg(new_xyz + (size_t)m * 3 + 2));
+            if (live_b) {
+                x[0] = __fsub_rn(vb[0], qb[0]); x[1] = __fsub_rn(vb[1], qb[1]); x[2] = __fsub_rn(vb[2], qb[2]);
 #pragma unroll
-                    for (int cc = 3; cc < C0; cc++) x[cc] = __ldg(features + p * C_in + (cc - 3));
-                }
+                for (int cc = 3; cc < C0; cc++) x[cc] = vb[cc];
             }
+            iv_b = iv_a; em_b = em_a;
+            load_pt(i + 2, iv_b, em_b, vb, qb, live_b);     // points of the next tile of this group
+            load_idx(i + 4, iv_a, em_a);                    // indices of the one after
+
             mbar_wait(EMPTY(g), (j & 1) ^ 1);
 #pragma unroll
             for (int c16 = 0; c16 < 16; c16++) {
@@ -252,11 +322,10 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, int B, int M, int C_in, co
 #pragma unroll
                 for (int q = 0; q < 4; q++) {
                     const int o = c16 * 4 + q;
-                    float acc = 0.f;
+                    float acc = L1.sh[o];
 #pragma unroll
                     for (int cc = 0; cc < C0; cc++) acc = __fmaf_rn(x[cc], L1.w[cc][o], acc);
-                    const float y = fmaxf(__fmaf_rn(acc, L1.sc[o], L1.sh[o]), 0.f);
-                    split_tf32(y, hi[q], lo[q]);
+                    split_tf32(fmaxf(acc, 0.f), hi[q], lo[q]);
                 }
                 const uint32_t off = tile_off(r, c16);
                 asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(b_hi + off), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
@@ -264,7 +333,6 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, int B, int M, int C_in, co
             }
             fence_async_smem();          // generic-proxy stores -> visible to the tensor core (async proxy)
             mbar_arrive(FULL(g));
-            j++;
         }
     }
 
@@ -281,20 +349,6 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, int B, int M, int C_in, co
 
 using namespace mgar;
 
-template <int C0>
-static int launch_tc(int grid, cudaStream_t st, const TcLayer1 &L1, int B, int M, int C_in, const float *xyz,
-                     int xyz_stride, const float *new_xyz, const float *features, const int *pre_xyz,
-                     const int *pre_new, int uniform, int n_u, int m_u, const int *idx,
-                     const unsigned char *empty_mask, const float *w2t, const float *sc2, const float *sh2,
-                     float *out, int ld_out) {
-    MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc_kernel<C0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmem));
-    sa_mlp_tc_kernel<C0><<<grid, kTcThreads, kTcSmem, st>>>(L1, B, M, C_in, xyz, xyz_stride, new_xyz, features, pre_xyz,
-                                                            pre_new, uniform, n_u, m_u, idx, empty_mask, w2t, sc2, sh2,
-                                                            out, ld_out);
-    count_launch();
-    return check_launch("sa_mlp_tc");
-}
-
 extern "C" int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg) {
     return nsample == kTcNS && C_in >= 0 && C_in <= 5 && n_layers == 2 && channels_host && channels_host[0] == 3 + C_in &&
            channels_host[1] == kTcC1 && channels_host[2] == kTcC2 && !pool_avg;
@@ -302,41 +356,59 @@ extern "C" int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, con
 
 extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float *xyz, int xyz_stride,
                                   const int *xyz_batch_cnt, const float *new_xyz, const int *new_xyz_batch_cnt,
-                                  int uniform_n, int uniform_m, const float *features, const int *idx,
+                                  int uniform_n, int uniform_m, const float *features, int feat_stride, const int *idx,
                                   const unsigned char *empty_mask, int n_layers, const int *channels_host,
-                                  const float *params, const float *params_host, float *out, int ld_out, int pool_avg,
+                                  const float *params, const float *params_host, float *out, int ld_out,
+                                  float *group_max, int group_size, const int *group_zero, int pool_avg,
                                   void *stream) {
     MGAR_REQUIRE(B >= 1 && M >= 0, "sa_mlp_tc: bad size");
     MGAR_REQUIRE(mgar_sa_mlp_tc_supported(nsample, C_in, n_layers, channels_host, pool_avg),
                  "sa_mlp_tc: only nsample=32, C_in<=5, channels [3+C_in,64,128], max-pool run on the tensor-core path");
     if (M == 0) return MGAR_OK;
-    MGAR_REQUIRE(xyz && new_xyz && idx && params && params_host && out, "sa_mlp_tc: null pointer");
+    MGAR_REQUIRE(xyz && new_xyz && idx && params && params_host && (out || group_max), "sa_mlp_tc: null pointer");
     MGAR_REQUIRE(features || C_in == 0, "sa_mlp_tc: features missing");
-    MGAR_REQUIRE(xyz_stride >= 3, "sa_mlp_tc: xyz_stride must be >= 3");
+    MGAR_REQUIRE(xyz_stride >= 3 && (C_in == 0 || feat_stride >= C_in), "sa_mlp_tc: bad row stride");
+    MGAR_REQUIRE(!group_max || group_size >= 1, "sa_mlp_tc: group_size must be >= 1");
     const bool uniform = uniform_n > 0;
     MGAR_REQUIRE(uniform || (xyz_batch_cnt && new_xyz_batch_cnt), "sa_mlp_tc: batch counts missing");
     const int C0 = 3 + C_in;
     TcLayer1 L1;
-    for (int c = 0; c < 8; c++)
-        for (int o = 0; o < kTcC1; o++) L1.w[c][o] = c < C0 ? params_host[c * kTcC1 + o] : 0.f;
     for (int o = 0; o < kTcC1; o++) {
-        L1.sc[o] = params_host[C0 * kTcC1 + o];
+        const float sc = params_host[C0 * kTcC1 + o];
+        for (int c = 0; c < 8; c++) L1.w[c][o] = c < C0 ? params_host[c * kTcC1 + o] * sc : 0.f;   // BN scale folded
         L1.sh[o] = params_host[C0 * kTcC1 + kTcC1 + o];
     }
-    const float *w2t = params + C0 * kTcC1 + 2 * kTcC1;
-    const float *sc2 = w2t + kTcC1 * kTcC2, *sh2 = sc2 + kTcC2;
     cudaStream_t st = (cudaStream_t)stream;
     PrefixWs ws;
     if (!uniform) {
         if (int rc = ws.alloc(B, st)) return rc;
         if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     }
+    TcArgs A;
+    A.B = B; A.M = M; A.C_in = C_in;
+    A.xyz = xyz; A.xyz_stride = xyz_stride; A.new_xyz = new_xyz;
+    A.features = features; A.feat_stride = feat_stride;
+    A.pre_xyz = ws.b; A.pre_new = ws.a; A.uniform = uniform ? 1 : 0; A.n_u = uniform_n; A.m_u = uniform_m;
+    A.idx = idx; A.empty_mask = empty_mask;
+    A.w2t = params + C0 * kTcC1 + 2 * kTcC1;
+    A.sc2 = A.w2t + kTcC1 * kTcC2; A.sh2 = A.sc2 + kTcC2;
+    A.out = out; A.ld_out = ld_out;
+    A.gmax = group_max; A.group_size = group_size > 0 ? group_size : 1; A.group_zero = group_zero;
+    A.packed4 = (C0 == 4 && xyz_stride == 4 && feat_stride == 4 && features == xyz + 3 &&
+                 (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) ? 1 : 0;
+    if (group_max) {
+        const size_t groups = ((size_t)M + A.group_size - 1) / A.group_size;
+        MGAR_CUDA(cudaMemsetAsync(group_max, 0, groups * kTcC2 * sizeof(float), st));
+    }
     const int n_tiles = (M + 3) / 4;
     const int grid = n_tiles < kNumSMs ? n_tiles : kNumSMs;     // persistent: one CTA per SM
-#define MGAR_TC_CASE(c0)                                                                                          \
-    if (C0 == c0)                                                                                                 \
-        return launch_tc<c0>(grid, st, L1, B, M, C_in, xyz, xyz_stride, new_xyz, features, ws.b, ws.a, uniform ? 1 : 0, \
-                             uniform_n, uniform_m, idx, empty_mask, w2t, sc2, sh2, out, ld_out);
+#define MGAR_TC_CASE(c0)                                                                                        \
+    if (C0 == c0) {                                                                                             \
+        MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc_kernel<c0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmem)); \
+        sa_mlp_tc_kernel<c0><<<grid, kTcThreads, kTcSmem, st>>>(L1, A);                                         \
+        count_launch();                                                                                         \
+        return check_launch("sa_mlp_tc");                                                                       \
+    }
     MGAR_TC_CASE(3) MGAR_TC_CASE(4) MGAR_TC_CASE(5) MGAR_TC_CASE(6) MGAR_TC_CASE(7) MGAR_TC_CASE(8)
 #undef MGAR_TC_CASE
     set_error("sa_mlp_tc: unsupported C0=%d", C0);

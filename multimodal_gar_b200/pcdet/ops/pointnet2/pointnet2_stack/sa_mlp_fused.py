@@ -46,14 +46,17 @@ def tc_supported(channels, nsample, C_in, pool_avg=False):
 
 
 def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features, idx,
-                   empty_mask=None, out=None, pool_avg=False, uniform=None, params_host=None, impl=None):
+                   empty_mask=None, out=None, pool_avg=False, uniform=None, params_host=None, impl=None,
+                   group_max=None, group_size=0, group_zero=None, want_out=True):
     """-> (M, channels[-1]) fp32.  `idx` as returned by ball_query (or the raw kernel output);
     `uniform=(n, m)` skips the ragged bookkeeping when every cloud has n points and m centroids.
 
     impl: 'tc' (tcgen05 tensor cores, 3xTF32), 'fp32' (CUDA-core FFMA) or None = tensor cores whenever the
     shape is supported and `params_host` (CPU copy of `params`) is given; env MGAR_SA_MLP overrides.
-    `xyz` may be a (N,3) array or a strided view of the first three columns of a (N,3+C) array (tc only)."""
-    need_cuda(new_xyz=new_xyz, features=features, idx=idx, params=params, empty_mask=empty_mask)
+    `xyz` / `features` may be strided column views of one (N,3+C) array (tc only).
+    tc only: `group_max` (ceil(M/group_size), C_out) receives the max over every run of `group_size`
+    consecutive centroids (rows with group_zero[g] != 0 stay zero); want_out=False skips the (M, C_out) result."""
+    need_cuda(new_xyz=new_xyz, idx=idx, params=params, empty_mask=empty_mask, group_max=group_max, group_zero=group_zero)
     need_dtype(torch.float32, xyz=xyz, new_xyz=new_xyz, features=features, params=params)
     need_dtype(torch.int32, idx=idx)
     if not xyz.is_cuda or xyz.dim() != 2 or xyz.stride(1) != 1:
@@ -63,7 +66,9 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
     M = new_xyz.shape[0]
     B = xyz_batch_cnt.shape[0] if xyz_batch_cnt is not None else xyz.shape[0] // uniform[0]
     C_in = 0 if features is None else features.shape[1]
-    if out is None:
+    if features is not None and (not features.is_cuda or features.dim() != 2 or features.stride(1) != 1):
+        raise _lib.MgarError("features must be a CUDA (N,C) tensor with unit column stride")
+    if out is None and want_out:
         out = torch.empty((M, channels[-1]), dtype=torch.float32, device=xyz.device)
     if empty_mask is not None:
         empty_mask = empty_mask.to(torch.uint8).contiguous()
@@ -79,13 +84,15 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
                 raise _lib.MgarError("the tensor-core path needs params_host (contiguous CPU copy of params)")
             _lib.check(L.mgar_sa_mlp_fwd_tc(
                 B, M, nsample, C_in, ptr(xyz), xyz.stride(0), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt),
-                un, um, ptr(features), ptr(idx), ptr(empty_mask), len(channels) - 1, ctypes.addressof(ch), ptr(params),
-                ptr(params_host), ptr(out), out.stride(0), 1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd_tc")
+                un, um, ptr(features), 0 if features is None else features.stride(0), ptr(idx), ptr(empty_mask),
+                len(channels) - 1, ctypes.addressof(ch), ptr(params), ptr(params_host), ptr(out),
+                0 if out is None else out.stride(0), ptr(group_max), int(group_size), ptr(group_zero),
+                1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd_tc")
         else:
-            if not xyz.is_contiguous():
-                raise _lib.MgarError("the fp32 path needs a contiguous (N,3) xyz")
+            if not xyz.is_contiguous() or (features is not None and not features.is_contiguous()) or group_max is not None:
+                raise _lib.MgarError("the fp32 path needs contiguous xyz / features and has no group_max output")
             _lib.check(L.mgar_sa_mlp_fwd_fp32(
                 B, M, nsample, C_in, ptr(xyz), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt), un, um,
                 ptr(features), ptr(idx), ptr(empty_mask), len(channels) - 1, ctypes.addressof(ch), ptr(params),
                 ptr(out), out.stride(0), 1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd")
-    return out
+    return out if want_out else group_max

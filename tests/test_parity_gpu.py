@@ -270,13 +270,26 @@ def test_sa_mlp_tensor_core_path(cuda, Bp, n, m, C_in, layout):
     want = O.stack_sa_module_msg([mlp], [0.3], [K], xyz, cnt, new_xyz, ncnt, feats)
     ch, params = sa_mlp_fused.pack_shared_mlp(mlp)
     assert sa_mlp_fused.tc_supported(ch, K, C_in)
-    dxyz = T(pooled, cuda)[:, :3] if layout == "strided" else T(xyz, cuda)
+    dpool = T(pooled, cuda)
+    dxyz = dpool[:, :3] if layout == "strided" else T(xyz, cuda)
     kw = dict(uniform=(n, m)) if layout != "ragged" else {}
     cn, ncn = (None, None) if layout != "ragged" else (T(cnt, cuda), T(ncnt, cuda))
-    dfe = None if feats is None else T(feats, cuda)
+    dfe = None if feats is None else (dpool[:, 3:3 + C_in] if layout == "strided" else T(feats, cuda))
+    zero = np.zeros(Bp, np.int32)
+    zero[1] = 1
+    gmax = torch.full((Bp, 128), -1.0, device=cuda)
     got = sa_mlp_fused.sa_mlp_forward(ch, params.to(cuda), K, dxyz, cn, T(new_xyz, cuda), ncn, dfe, T(idx, cuda),
-                                      empty_mask=T(mask, cuda), params_host=params, impl='tc', **kw)
+                                      empty_mask=T(mask, cuda), params_host=params, impl='tc', group_max=gmax,
+                                      group_size=m, group_zero=T(zero, cuda), **kw)
     _feature_close(got.cpu().numpy(), want)
+    want_g = got.view(Bp, m, 128).max(dim=1).values
+    want_g[1] = 0
+    assert torch.equal(gmax, want_g)                         # fused per-cloud max == max of the rows it wrote
+    only = sa_mlp_fused.sa_mlp_forward(ch, params.to(cuda), K, dxyz, cn, T(new_xyz, cuda), ncn, dfe, T(idx, cuda),
+                                       empty_mask=T(mask, cuda), params_host=params, impl='tc',
+                                       group_max=torch.empty_like(gmax), group_size=m, want_out=False, **kw)
+    want_g[1] = got.view(Bp, m, 128)[1].max(dim=0).values
+    assert torch.equal(only, want_g)
     if layout != "strided":
         ref32 = sa_mlp_fused.sa_mlp_forward(ch, params.to(cuda), K, dxyz, cn, T(new_xyz, cuda), ncn, dfe, T(idx, cuda),
                                             empty_mask=T(mask, cuda), impl='fp32', **kw)
