@@ -77,8 +77,12 @@ MGAR_API int mgar_roipoint_pool(const float *xyz, const float *boxes, const floa
 /* farthest_point_sampling_wrapper: pointnet2/pointnet2_stack/src/sampling.cpp:21-34
  * (kernel sampling_gpu.cu:25-140).  xyz (b,n,3), temp (b,n) pre-filled by the caller (1e10;
  * clobbered with the final min-distances) -> idx (b,m) int32.  Tie order follows the
- * reference's block reduction for block size opt_n_threads(n). */
-MGAR_API int mgar_fps_batch(int b, int n, int m, const float *xyz, float *temp, int *idx, void *stream);
+ * reference's block reduction for block size opt_n_threads(n).
+ * Extensions (the pybind mirror passes 3 / temp / NULL): xyz_stride = floats between rows (4 reads the
+ * xyz columns of a pooled (b,n,4) array in place); temp may be NULL for n <= 8192 (distances start at
+ * 1e10 and are not written back); new_xyz (b,m,3) optional: the sampled coordinates, gathered in-kernel. */
+MGAR_API int mgar_fps_batch(int b, int n, int m, const float *xyz, int xyz_stride, float *temp, int *idx,
+                            float *new_xyz, void *stream);
 
 /* stack_farthest_point_sampling_wrapper: sampling.cpp:37-56 (kernel sampling_gpu.cu:188-319).
  * xyz (sum n_i,3), temp (sum n_i), xyz_batch_cnt (batch) int32 device, num_sampled (batch)
@@ -90,10 +94,16 @@ MGAR_API int mgar_fps_stack(int batch, int max_n, const float *xyz, float *temp,
 /* ---- pointnet2_stack: ball query / grouping ----------------------------------------------------- */
 
 /* ball_query_wrapper_stack: ball_query.cpp:29-45 (kernel ball_query_gpu.cu:16-66).
- * idx (M,nsample) is zero-filled by the caller; rows without neighbours get idx[0] = -1. */
+ * idx (M,nsample): batch-local indices of the first nsample points with d2 < radius^2 in index order,
+ * padded with the first hit; rows without neighbours get idx[0] = -1.  fill = 0 is the reference
+ * contract (idx zero-filled by the caller, the other slots of such rows are left alone); fill = 1
+ * writes every slot (-1, 0, 0, ...) so idx may be uninitialised.
+ * Extensions: xyz_stride (floats between rows); uniform_n > 0: every cloud has uniform_n points and
+ * uniform_m centroids (B * uniform_m == M) and the count arrays may be NULL. */
 MGAR_API int mgar_ball_query_stack(int B, int M, float radius, int nsample, const float *new_xyz,
-                          const int *new_xyz_batch_cnt, const float *xyz, const int *xyz_batch_cnt,
-                          int *idx, void *stream);
+                          const int *new_xyz_batch_cnt, const float *xyz, int xyz_stride,
+                          const int *xyz_batch_cnt, int uniform_n, int uniform_m, int *idx, int fill,
+                          void *stream);
 
 /* group_points_wrapper_stack: group_points.cpp:50-67 (kernel group_points_gpu.cu:71-102).
  * out (M,C,nsample), every element written. */

@@ -25,9 +25,9 @@ SIGNATURES = {
     "mgar_in_box_mask": [_p, _p, _p, _p, _i, _i, _i, _p],
     "mgar_points_in_boxes_mask_host": [_p, _p, _p, _i, _i],
     "mgar_roipoint_pool": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
-    "mgar_fps_batch": [_i, _i, _i, _p, _p, _p, _p],
+    "mgar_fps_batch": [_i, _i, _i, _p, _i, _p, _p, _p, _p],
     "mgar_fps_stack": [_i, _i, _p, _p, _p, _p, _p, _p],
-    "mgar_ball_query_stack": [_i, _i, _f, _i, _p, _p, _p, _p, _p, _p],
+    "mgar_ball_query_stack": [_i, _i, _f, _i, _p, _p, _p, _i, _p, _i, _i, _p, _i, _p],
     "mgar_group_points_stack": [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_group_points_grad_stack": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_sa_mlp_tc_supported": [_i, _i, _i, _p, _i],

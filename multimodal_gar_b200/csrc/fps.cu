@@ -37,9 +37,10 @@ __device__ __forceinline__ int rank_to_index(int r, int L, int SH) {
 // One CTA of W warps per cloud; each thread owns PPL ranks (registers).
 template <int W, int PPL>
 __global__ void __launch_bounds__(W * 32)
-fps_reg_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *__restrict__ idxs,
-               const int *__restrict__ xyz_batch_cnt, const int *__restrict__ num_sampled,
-               int n_uniform, int m_uniform, int L_uniform, int stack, int smem_pts) {
+fps_reg_kernel(const float *__restrict__ xyz, int xs, float *__restrict__ temp, int *__restrict__ idxs,
+               float *__restrict__ new_xyz, const int *__restrict__ xyz_batch_cnt,
+               const int *__restrict__ num_sampled, int n_uniform, int m_uniform, int L_uniform, int stack,
+               int smem_pts) {
     extern __shared__ float sxyz[];               // [n][3] staged cloud (lookup of the current point)
     __shared__ int s_red[2][W > 1 ? W : 1][2];    // double-buffered per-warp (value bits, rank)
     __shared__ int s_off[2];
@@ -65,7 +66,9 @@ fps_reg_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *__r
         start = (long long)bi * n; istart = (long long)bi * m;
     }
     if (m <= 0) return;
-    xyz += start * 3; temp += start; idxs += istart;
+    xyz += start * xs; idxs += istart;
+    if (temp) temp += start;
+    if (new_xyz) new_xyz += istart * 3;
     if (n > smem_pts || n < 1) {  // caller broke the max_n contract: make it visible, never overrun
         for (int j = tid; j < m; j += W * 32) idxs[j] = -1;
         return;
@@ -75,7 +78,11 @@ fps_reg_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *__r
     int stripes = (n + bs - 1) >> L, SH = 0;
     while ((1 << SH) < stripes) SH++;
 
-    for (int i = tid; i < n * 3; i += W * 32) sxyz[i] = xyz[i];
+    if (xs == 3) {
+        for (int i = tid; i < n * 3; i += W * 32) sxyz[i] = xyz[i];
+    } else {   // strided rows (e.g. the xyz columns of a pooled (n,4) array)
+        for (int i = tid; i < n * 3; i += W * 32) sxyz[i] = xyz[(size_t)(i / 3) * xs + (i % 3)];
+    }
     __syncthreads();
 
     float px[PPL], py[PPL], pz[PPL], pt[PPL];
@@ -86,7 +93,7 @@ fps_reg_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *__r
         px[i] = valid ? sxyz[k * 3 + 0] : 0.f;
         py[i] = valid ? sxyz[k * 3 + 1] : 0.f;
         pz[i] = valid ? sxyz[k * 3 + 2] : 0.f;
-        pt[i] = valid ? temp[k] : -1.f;  // -1 never beats the reference's initial best = -1 either
+        pt[i] = valid ? (temp ? temp[k] : 1e10f) : -1.f;  // -1 never beats the reference's initial best = -1 either
     }
 
     int cur = 0;
@@ -130,7 +137,16 @@ fps_reg_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *__r
 #pragma unroll
     for (int i = 0; i < PPL; i++) {
         const int k = rank_to_index(tid * PPL + i, L, SH);
-        if ((tid * PPL + i) < (bs << SH) && k < n) temp[k] = pt[i];
+        if (temp && (tid * PPL + i) < (bs << SH) && k < n) temp[k] = pt[i];
+    }
+    if (new_xyz) {   // optional fused gather of the sampled coordinates
+        __syncthreads();
+        for (int j = tid; j < m; j += W * 32) {
+            const int k = idxs[j] - base;
+            new_xyz[j * 3 + 0] = sxyz[k * 3 + 0];
+            new_xyz[j * 3 + 1] = sxyz[k * 3 + 1];
+            new_xyz[j * 3 + 2] = sxyz[k * 3 + 2];
+        }
     }
 }
 
@@ -138,9 +154,9 @@ fps_reg_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *__r
 // reference) but the 10-barrier tree is replaced by REDUX + one barrier.  bs is 1024 for every
 // n >= 1024 in both layouts, so thread t owns k = t, t+1024, ... exactly like the reference.
 __global__ void __launch_bounds__(1024)
-fps_global_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *__restrict__ idxs,
-                  const int *__restrict__ xyz_batch_cnt, const int *__restrict__ num_sampled,
-                  int n_uniform, int m_uniform, int L_uniform, int stack) {
+fps_global_kernel(const float *__restrict__ xyz, int xs, float *__restrict__ temp, int *__restrict__ idxs,
+                  float *__restrict__ new_xyz, const int *__restrict__ xyz_batch_cnt,
+                  const int *__restrict__ num_sampled, int n_uniform, int m_uniform, int L_uniform, int stack) {
     __shared__ int s_red[2][32][2];
     __shared__ int s_win[2];
     __shared__ long long s_off[2];
@@ -162,7 +178,8 @@ fps_global_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *
         start = (long long)bi * n; istart = (long long)bi * m;
     }
     if (m <= 0) return;
-    xyz += start * 3; temp += start; idxs += istart;
+    xyz += start * xs; temp += start; idxs += istart;
+    if (new_xyz) new_xyz += istart * 3;
     const int base = stack ? (int)start : 0;
     const int bs = 1 << L;
     // rank of this thread among threads = bit-reversed id; threads >= bs own nothing
@@ -171,13 +188,13 @@ fps_global_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *
     int cur = 0;
     if (tid == 0) idxs[0] = base;
     for (int j = 1; j < m; j++) {
-        const float cx = xyz[cur * 3 + 0], cy = xyz[cur * 3 + 1], cz = xyz[cur * 3 + 2];
+        const float cx = xyz[(size_t)cur * xs + 0], cy = xyz[(size_t)cur * xs + 1], cz = xyz[(size_t)cur * xs + 2];
         float best = -1.f;
         int besti = 0;
         if (tid < bs)
             for (int k = tid; k < n; k += bs) {
-                const float d = sqdist(__fsub_rn(xyz[k * 3 + 0], cx), __fsub_rn(xyz[k * 3 + 1], cy),
-                                       __fsub_rn(xyz[k * 3 + 2], cz));
+                const float d = sqdist(__fsub_rn(xyz[(size_t)k * xs + 0], cx), __fsub_rn(xyz[(size_t)k * xs + 1], cy),
+                                       __fsub_rn(xyz[(size_t)k * xs + 2], cz));
                 const float d2 = fminf(d, temp[k]);
                 temp[k] = d2;
                 if (d2 > best) { best = d2; besti = k; }
@@ -200,16 +217,25 @@ fps_global_kernel(const float *__restrict__ xyz, float *__restrict__ temp, int *
         cur = s_win[buf];
         if (tid == 0) idxs[j] = cur + base;
     }
+    if (new_xyz) {
+        __syncthreads();
+        for (int j = tid; j < m; j += 1024) {
+            const int k = idxs[j] - base;
+            new_xyz[j * 3 + 0] = xyz[(size_t)k * xs + 0];
+            new_xyz[j * 3 + 1] = xyz[(size_t)k * xs + 1];
+            new_xyz[j * 3 + 2] = xyz[(size_t)k * xs + 2];
+        }
+    }
 }
 
 template <int W, int PPL>
-static int launch_reg(int grid, size_t smem, cudaStream_t st, const float *xyz, float *temp, int *idx,
-                      const int *cnt, const int *ms, int n, int m, int L, int stack) {
+static int launch_reg(int grid, size_t smem, cudaStream_t st, const float *xyz, int xs, float *temp, int *idx,
+                      float *new_xyz, const int *cnt, const int *ms, int n, int m, int L, int stack) {
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(fps_reg_kernel<W, PPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) { set_error("fps: smem opt-in failed: %s", cudaGetErrorString(e)); return MGAR_ECUDA; }
     }
-    fps_reg_kernel<W, PPL><<<grid, W * 32, smem, st>>>(xyz, temp, idx, cnt, ms, n, m, L, stack, (int)(smem / 12));
+    fps_reg_kernel<W, PPL><<<grid, W * 32, smem, st>>>(xyz, xs, temp, idx, new_xyz, cnt, ms, n, m, L, stack, (int)(smem / 12));
     count_launch();
     return check_launch("fps");
 }
@@ -218,8 +244,8 @@ static int floor_log2(int v) { int l = 0; while ((2 << l) <= v) l++; return l; }
 
 // V = padded rank space.  Geometry table: (warps, ranks per thread) chosen so one round is short
 // for a single cloud yet several clouds still share an SM; overridable for tuning.
-static int fps_dispatch(int grid, int V, int max_n, cudaStream_t st, const float *xyz, float *temp, int *idx,
-                        const int *cnt, const int *ms, int n, int m, int L, int stack) {
+static int fps_dispatch(int grid, int V, int max_n, cudaStream_t st, const float *xyz, int xs, float *temp, int *idx,
+                        float *new_xyz, const int *cnt, const int *ms, int n, int m, int L, int stack) {
     const size_t smem = (size_t)max_n * 3 * sizeof(float);
     int W, PPL;
     if (V <= 32) { W = 1; PPL = 1; }
@@ -236,12 +262,13 @@ static int fps_dispatch(int grid, int V, int max_n, cudaStream_t st, const float
         if (sscanf(e, "%d,%d", &w, &p) == 2 && w * 32 * p >= V) { W = w; PPL = p; }
     }
     if (V > 8192 || smem > 200 * 1024) {
-        fps_global_kernel<<<grid, 1024, 0, st>>>(xyz, temp, idx, cnt, ms, n, m, L, stack);
+        MGAR_REQUIRE(temp, "fps: clouds this large need the caller's temp scratch");
+        fps_global_kernel<<<grid, 1024, 0, st>>>(xyz, xs, temp, idx, new_xyz, cnt, ms, n, m, L, stack);
         count_launch();
         return check_launch("fps(global)");
     }
 #define MGAR_FPS_CASE(w, p) \
-    if (W == w && PPL == p) return launch_reg<w, p>(grid, smem, st, xyz, temp, idx, cnt, ms, n, m, L, stack);
+    if (W == w && PPL == p) return launch_reg<w, p>(grid, smem, st, xyz, xs, temp, idx, new_xyz, cnt, ms, n, m, L, stack);
     MGAR_FPS_CASE(1, 1) MGAR_FPS_CASE(1, 2) MGAR_FPS_CASE(1, 4) MGAR_FPS_CASE(1, 8) MGAR_FPS_CASE(1, 16)
     MGAR_FPS_CASE(2, 2) MGAR_FPS_CASE(2, 4) MGAR_FPS_CASE(2, 8) MGAR_FPS_CASE(2, 16)
     MGAR_FPS_CASE(4, 2) MGAR_FPS_CASE(4, 4) MGAR_FPS_CASE(4, 8) MGAR_FPS_CASE(4, 16)
@@ -257,17 +284,19 @@ static int fps_dispatch(int grid, int V, int max_n, cudaStream_t st, const float
 
 using namespace mgar;
 
-extern "C" int mgar_fps_batch(int b, int n, int m, const float *xyz, float *temp, int *idx, void *stream) {
+extern "C" int mgar_fps_batch(int b, int n, int m, const float *xyz, int xyz_stride, float *temp, int *idx,
+                              float *new_xyz, void *stream) {
     MGAR_REQUIRE(b >= 0 && n >= 0 && m >= 0, "fps_batch: negative size");
     if (b == 0 || m == 0) return MGAR_OK;
     MGAR_REQUIRE(n >= 1, "fps_batch: n must be >= 1 when m > 0");
-    MGAR_REQUIRE(xyz && temp && idx, "fps_batch: null pointer");
+    MGAR_REQUIRE(xyz && idx, "fps_batch: null pointer");
+    MGAR_REQUIRE(xyz_stride >= 3, "fps_batch: xyz_stride must be >= 3");
     int L = floor_log2(n);
     if (L > 10) L = 10;
     const int bs = 1 << L;
     int stripes = (n + bs - 1) / bs, SH = 0;
     while ((1 << SH) < stripes) SH++;
-    return fps_dispatch(b, bs << SH, n, (cudaStream_t)stream, xyz, temp, idx, nullptr, nullptr, n, m, L, 0);
+    return fps_dispatch(b, bs << SH, n, (cudaStream_t)stream, xyz, xyz_stride, temp, idx, new_xyz, nullptr, nullptr, n, m, L, 0);
 }
 
 extern "C" int mgar_fps_stack(int batch, int max_n, const float *xyz, float *temp, const int *xyz_batch_cnt,
@@ -278,6 +307,6 @@ extern "C" int mgar_fps_stack(int batch, int max_n, const float *xyz, float *tem
     int stripes = (max_n + 1023) / 1024, SH = 0;
     if (stripes < 1) stripes = 1;
     while ((1 << SH) < stripes) SH++;
-    return fps_dispatch(batch, 1024 << SH, max_n, (cudaStream_t)stream, xyz, temp, idx, xyz_batch_cnt, num_sampled,
-                        0, 0, 10, 1);
+    return fps_dispatch(batch, 1024 << SH, max_n, (cudaStream_t)stream, xyz, 3, temp, idx, nullptr, xyz_batch_cnt,
+                        num_sampled, 0, 0, 10, 1);
 }

@@ -15,10 +15,8 @@
 
 namespace mgar {
 
-constexpr int kBqTile = 64;       // centroids per CTA
-constexpr int kBqWarps = 8;
-constexpr int kBqPerWarp = kBqTile / kBqWarps;
-constexpr int kBqChunk = 4096;    // cloud points staged per pass (48 KB)
+constexpr int kBqTile = 128;      // centroids (= threads) per CTA
+constexpr int kBqChunk = 1024;    // cloud points staged per pass (16 KB as float4)
 
 // prefix[0..B] for two count arrays + tile prefix for the first one (tiles of `tile` rows).
 // Single CTA; B is small (persons or frames).
@@ -91,16 +89,22 @@ __device__ __forceinline__ int find_batch(const int *__restrict__ pre, int B, in
     return lo;
 }
 
-// uniform != 0: every cloud has n_u points / m_u centroids and the prefix arrays are not read.
-__global__ void __launch_bounds__(kBqWarps * 32)
-ball_query_kernel(int B, float radius, int K, const float *__restrict__ new_xyz, const float *__restrict__ xyz,
+// One THREAD per centroid, one CTA per tile of 128 centroids of one cloud.  The cloud is staged in
+// shared memory as float4 in 1024-point chunks; every lane of a warp reads the SAME point (one
+// broadcast LDS.128 serves 32 distance tests), hits are appended in index order to the thread's own
+// shared-memory row, and a warp stops scanning once all of its 32 centroids are full.  Rows leave as
+// coalesced 4K-byte stores.  uniform != 0: every cloud has n_u points / m_u centroids and the
+// prefix arrays are not read.  fill != 0: rows without a neighbour are written as (-1, 0, 0, ...)
+// instead of relying on the caller's zero fill.
+__global__ void __launch_bounds__(kBqTile)
+ball_query_kernel(int B, float radius, int K, const float *__restrict__ new_xyz, const float *__restrict__ xyz, int xs,
                   const int *__restrict__ pre_new, const int *__restrict__ pre_xyz,
-                  const int *__restrict__ pre_tile, int uniform, int n_u, int m_u, int *__restrict__ idx) {
-    extern __shared__ float smem_f[];
-    float *sx = smem_f;                                              // [kBqChunk][3]
-    int *sidx = reinterpret_cast<int *>(smem_f + kBqChunk * 3);      // [kBqTile][K]
+                  const int *__restrict__ pre_tile, int uniform, int n_u, int m_u, int *__restrict__ idx, int fill) {
+    extern __shared__ float4 smem_q[];
+    float4 *sp = smem_q;                                             // [kBqChunk]
+    int *rows = reinterpret_cast<int *>(smem_q + kBqChunk);          // [kBqTile][K + 1]
 
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int b, c_begin, c_end, n;
     long long p_start;
     if (uniform) {
@@ -120,61 +124,57 @@ ball_query_kernel(int B, float radius, int K, const float *__restrict__ new_xyz,
         n = __ldg(pre_xyz + b + 1) - __ldg(pre_xyz + b);
         p_start = __ldg(pre_xyz + b);
     }
-    xyz += p_start * 3;
+    xyz += p_start * xs;
     const float r2 = __fmul_rn(radius, radius);
+    const bool vec4 = (xs == 4) && ((reinterpret_cast<uintptr_t>(xyz) & 15) == 0);
 
-    float qx[kBqPerWarp], qy[kBqPerWarp], qz[kBqPerWarp];
-    int cnt[kBqPerWarp], kfirst[kBqPerWarp];
-#pragma unroll
-    for (int c = 0; c < kBqPerWarp; c++) {
-        const int ci = c_begin + warp * kBqPerWarp + c;
-        const bool ok = ci < c_end;
-        qx[c] = ok ? __ldg(new_xyz + (size_t)ci * 3 + 0) : 0.f;
-        qy[c] = ok ? __ldg(new_xyz + (size_t)ci * 3 + 1) : 0.f;
-        qz[c] = ok ? __ldg(new_xyz + (size_t)ci * 3 + 2) : 0.f;
-        cnt[c] = ok ? 0 : K;  // out-of-tile slots count as finished
-        kfirst[c] = 0;
-    }
+    const int ci = c_begin + tid;
+    const bool ok = ci < c_end;
+    const float qx = ok ? __ldg(new_xyz + (size_t)ci * 3 + 0) : 0.f;
+    const float qy = ok ? __ldg(new_xyz + (size_t)ci * 3 + 1) : 0.f;
+    const float qz = ok ? __ldg(new_xyz + (size_t)ci * 3 + 2) : 0.f;
+    int cnt = ok ? 0 : K;                                            // out-of-tile threads count as finished
+    int *myrow = rows + tid * (K + 1);
 
     for (int k0 = 0; k0 < n; k0 += kBqChunk) {
         const int kn = min(kBqChunk, n - k0);
         __syncthreads();
-        for (int i = threadIdx.x; i < kn * 3; i += kBqWarps * 32) sx[i] = __ldg(xyz + (size_t)k0 * 3 + i);
-        __syncthreads();
-        bool all_done = true;
-#pragma unroll
-        for (int c = 0; c < kBqPerWarp; c++) {
-            int *row = sidx + (warp * kBqPerWarp + c) * K;
-            for (int base = 0; base < kn && cnt[c] < K; base += 32) {
-                const int k = base + lane;
-                bool hit = false;
-                if (k < kn) {
-                    const float d2 = sqdist(__fsub_rn(qx[c], sx[k * 3 + 0]), __fsub_rn(qy[c], sx[k * 3 + 1]),
-                                            __fsub_rn(qz[c], sx[k * 3 + 2]));
-                    hit = d2 < r2;
-                }
-                const unsigned msk = __ballot_sync(0xffffffffu, hit);
-                if (msk == 0) continue;
-                if (cnt[c] == 0) kfirst[c] = k0 + base + __ffs(msk) - 1;
-                const int pos = cnt[c] + __popc(msk & ((1u << lane) - 1u));
-                if (hit && pos < K) row[pos] = k0 + k;
-                cnt[c] += __popc(msk);
+        if (vec4) {
+            for (int i = tid; i < kn; i += kBqTile) sp[i] = __ldg(reinterpret_cast<const float4 *>(xyz) + k0 + i);
+        } else {
+            for (int i = tid; i < kn; i += kBqTile) {
+                const float *p = xyz + (size_t)(k0 + i) * xs;
+                sp[i] = make_float4(__ldg(p), __ldg(p + 1), __ldg(p + 2), 0.f);
             }
-            all_done &= cnt[c] >= K;
         }
-        if (__syncthreads_and(all_done)) break;
+        __syncthreads();
+        for (int k = 0; k < kn; k += 4) {
+            if (__all_sync(0xffffffffu, cnt >= K)) break;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const float4 p = sp[min(k + u, kn - 1)];
+                const float d2 = sqdist(__fsub_rn(qx, p.x), __fsub_rn(qy, p.y), __fsub_rn(qz, p.z));
+                if (d2 < r2 && k + u < kn && cnt < K) {
+                    myrow[cnt] = k0 + k + u;
+                    cnt++;
+                }
+            }
+        }
+        if (__syncthreads_and(cnt >= K)) break;
     }
     __syncwarp();
-#pragma unroll
-    for (int c = 0; c < kBqPerWarp; c++) {
-        const int ci = c_begin + warp * kBqPerWarp + c;
-        if (ci >= c_end) continue;
-        const int *row = sidx + (warp * kBqPerWarp + c) * K;
-        int *out = idx + (size_t)ci * K;
-        if (cnt[c] == 0) {
-            if (lane == 0) out[0] = -1;  // other slots keep the caller's fill (ball_query_gpu.cu:65)
+    for (int r = 0; r < 32; r++) {
+        const int row = warp * 32 + r;
+        if (c_begin + row >= c_end) break;
+        const int cnt_r = __shfl_sync(0xffffffffu, cnt, r);
+        const int *src = rows + row * (K + 1);
+        int *out = idx + (size_t)(c_begin + row) * K;
+        if (cnt_r == 0) {
+            if (fill) { for (int l = lane; l < K; l += 32) out[l] = l == 0 ? -1 : 0; }
+            else if (lane == 0) out[0] = -1;   // other slots keep the caller's fill (ball_query_gpu.cu:65)
         } else {
-            for (int l = lane; l < K; l += 32) out[l] = l < cnt[c] ? row[l] : kfirst[c];
+            const int first = src[0];
+            for (int l = lane; l < K; l += 32) out[l] = l < cnt_r ? src[l] : first;
         }
     }
 }
@@ -219,20 +219,31 @@ int stack_prefix(const int *cnt_a, const int *cnt_b, int B, int tile, int *pre_a
 using namespace mgar;
 
 extern "C" int mgar_ball_query_stack(int B, int M, float radius, int nsample, const float *new_xyz,
-                                     const int *new_xyz_batch_cnt, const float *xyz, const int *xyz_batch_cnt,
-                                     int *idx, void *stream) {
+                                     const int *new_xyz_batch_cnt, const float *xyz, int xyz_stride,
+                                     const int *xyz_batch_cnt, int uniform_n, int uniform_m, int *idx, int fill,
+                                     void *stream) {
     MGAR_REQUIRE(B >= 1 && M >= 0 && nsample >= 1, "ball_query: bad size B=%d M=%d nsample=%d", B, M, nsample);
     if (M == 0) return MGAR_OK;
-    MGAR_REQUIRE(new_xyz && new_xyz_batch_cnt && xyz && xyz_batch_cnt && idx, "ball_query: null pointer");
-    const size_t smem = (size_t)kBqChunk * 12 + (size_t)kBqTile * nsample * sizeof(int);
+    const bool uniform = uniform_n > 0;
+    MGAR_REQUIRE(new_xyz && xyz && idx, "ball_query: null pointer");
+    MGAR_REQUIRE(uniform || (new_xyz_batch_cnt && xyz_batch_cnt), "ball_query: batch counts missing");
+    MGAR_REQUIRE(!uniform || (uniform_m >= 1 && (long long)B * uniform_m == M), "ball_query: uniform layout needs B*uniform_m == M");
+    MGAR_REQUIRE(xyz_stride >= 3, "ball_query: xyz_stride must be >= 3");
+    const size_t smem = (size_t)kBqChunk * 16 + (size_t)kBqTile * (nsample + 1) * sizeof(int);
     MGAR_REQUIRE(smem <= 200 * 1024, "ball_query: nsample=%d too large", nsample);
     cudaStream_t st = (cudaStream_t)stream;
     PrefixWs ws;
-    if (int rc = ws.alloc(B, st)) return rc;
-    if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, kBqTile, ws.a, ws.b, ws.t, st)) return rc;
+    int grid;
+    if (uniform) {
+        grid = B * div_up(uniform_m, kBqTile);
+    } else {
+        if (int rc = ws.alloc(B, st)) return rc;
+        if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, kBqTile, ws.a, ws.b, ws.t, st)) return rc;
+        grid = div_up(M, kBqTile) + B;  // upper bound of sum_b ceil(M_b / tile)
+    }
     MGAR_CUDA(cudaFuncSetAttribute(ball_query_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int grid = div_up(M, kBqTile) + B;  // upper bound of sum_b ceil(M_b / tile)
-    ball_query_kernel<<<grid, kBqWarps * 32, smem, st>>>(B, radius, nsample, new_xyz, xyz, ws.a, ws.b, ws.t, 0, 0, 0, idx);
+    ball_query_kernel<<<grid, kBqTile, smem, st>>>(B, radius, nsample, new_xyz, xyz, xyz_stride, ws.a, ws.b, ws.t,
+                                                   uniform ? 1 : 0, uniform_n, uniform_m, idx, fill);
     count_launch();
     return check_launch("ball_query");
 }

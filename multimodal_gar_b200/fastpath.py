@@ -1,0 +1,49 @@
+"""Thin wrappers over the C-ABI extensions that have no counterpart in the reference's pybind surface:
+strided inputs (reading the xyz columns of a pooled (.., 3+C) array in place), the uniform stack layout
+(every person S points / P centroids: no count tensors, no prefix kernels) and fused outputs (FPS also
+gathers the sampled coordinates).  Used by lidar_branch.PointPersonEncoder; the drop-in pcdet.ops
+mirrors do not need them."""
+import torch
+
+from . import _lib
+from ._torch_glue import need_cuda, need_dtype, on_device, ptr, stream_of
+
+
+def _rows(t):
+    """(rows, cols>=3) fp32 CUDA view with unit column stride -> row stride in floats."""
+    if not t.is_cuda or t.dtype != torch.float32 or t.stride(-1) != 1:
+        raise _lib.MgarError("expected a CUDA fp32 tensor with unit column stride")
+    return t.stride(-2)
+
+
+def fps_gather(xyz, npoint):
+    """xyz (b,n,3) - possibly a column view of a (b,n,3+C) array - -> idx (b,npoint) int32, new_xyz (b,npoint,3).
+    Same indices as pointnet2_utils.farthest_point_sample (reference tie order); no temp tensor for n <= 8192."""
+    b, n = xyz.shape[0], xyz.shape[1]
+    xs = _rows(xyz)
+    if b > 1 and xyz.stride(0) != n * xs:
+        raise _lib.MgarError("clouds must be densely stacked")
+    idx = torch.empty((b, npoint), dtype=torch.int32, device=xyz.device)
+    new_xyz = torch.empty((b, npoint, 3), dtype=torch.float32, device=xyz.device)
+    temp = torch.full((b, n), 1e10, dtype=torch.float32, device=xyz.device) if n > 8192 else None
+    with on_device(xyz):
+        _lib.check(_lib.lib().mgar_fps_batch(b, n, npoint, ptr(xyz), xs, ptr(temp), ptr(idx), ptr(new_xyz),
+                                             stream_of(xyz)), "fps_gather")
+    return idx, new_xyz
+
+
+def ball_query_uniform(radius, nsample, xyz, new_xyz, n, m):
+    """xyz (B*n, 3) (row-strided view allowed), new_xyz (B*m, 3) contiguous -> raw idx (B*m, nsample) int32 with
+    the -1 sentinel in slot 0 of empty balls (every slot written)."""
+    need_cuda(new_xyz=new_xyz)
+    need_dtype(torch.float32, new_xyz=new_xyz)
+    xs = _rows(xyz)
+    M = new_xyz.shape[0]
+    B = M // m
+    if B * m != M or xyz.shape[0] != B * n:
+        raise _lib.MgarError("uniform layout: expected B*n points and B*m centroids")
+    idx = torch.empty((M, nsample), dtype=torch.int32, device=xyz.device)
+    with on_device(xyz):
+        _lib.check(_lib.lib().mgar_ball_query_stack(B, M, float(radius), int(nsample), ptr(new_xyz), 0, ptr(xyz), xs, 0,
+                                                    int(n), int(m), ptr(idx), 1, stream_of(xyz)), "ball_query_uniform")
+    return idx

@@ -14,7 +14,8 @@ collective is needed in the forward pass.
 import torch
 import torch.nn as nn
 
-from .pcdet.ops.pointnet2.pointnet2_stack import pointnet2_modules, pointnet2_utils
+from . import fastpath
+from .pcdet.ops.pointnet2.pointnet2_stack import pointnet2_modules, pointnet2_utils, sa_mlp_fused
 from .pcdet.ops.roiaware_pool3d import roiaware_pool3d_utils
 from .pcdet.ops.roipoint_pool3d import roipoint_pool3d_cuda, roipoint_pool3d_utils
 from .pcdet.utils import box_utils, common_utils
@@ -84,23 +85,42 @@ class PointPersonEncoder(nn.Module):
         S, P = self.num_sampled_points, self.npoint
         box_idx = roiaware_pool3d_utils.points_in_boxes_gpu(points, boxes)          # (B,N) first box or -1
         mark('points_in_boxes')
-        pooled, empty = self.pool(points, point_features, boxes)                    # (B*M,S,3+C)
+        pooled, empty = self.pool(points, point_features, boxes)                    # (B*M,S,3+C) canonical frame
         mark('roipoint_pool')
-        xyz = pooled[:, :, 0:3].contiguous()                                        # (B*M,S,3)
-        feats = pooled[:, :, 3:].contiguous().view(B * M * S, -1)
-        fps_idx = pointnet2_utils.farthest_point_sample(xyz, P)                     # (B*M,P) int32
-        mark('fps')
-        new_xyz = torch.gather(xyz, 1, fps_idx.long().unsqueeze(-1).expand(-1, -1, 3)).view(B * M * P, 3)
-        cnt = torch.full((B * M,), S, dtype=torch.int32, device=xyz.device)
-        new_cnt = torch.full((B * M,), P, dtype=torch.int32, device=xyz.device)
-        self.sa.stage_mark = mark
-        _, sa_feat = self.sa(xyz.view(B * M * S, 3), cnt, new_xyz, new_cnt, feats)  # (B*M*P, C_out)
-        self.sa.stage_mark = None
-        mark('sa_mlp')
-        person = sa_feat.view(B * M, P, -1).max(dim=1).values
-        person = person * (empty.view(-1, 1) == 0).to(person.dtype)                 # empty persons -> zeros
-        person = person.view(B, M, -1)
-        mark('person_reduce')
+        g = self.sa.groupers[0]
+        packed = None if (self.training or torch.is_grad_enabled()) else self.sa._pack(pooled.device)[0]
+        C = pooled.shape[2] - 3
+        if packed is not None and sa_mlp_fused.tc_supported(packed[0], g.nsample, C):
+            # fused path: every kernel reads the pooled (.., 3+C) rows in place; 5 launches per step
+            flat = pooled.view(B * M * S, 3 + C)
+            fps_idx, new_xyz = fastpath.fps_gather(pooled[:, :, 0:3], P)
+            new_xyz = new_xyz.view(B * M * P, 3)
+            mark('fps')
+            ball_idx = fastpath.ball_query_uniform(g.radius, g.nsample, flat[:, 0:3], new_xyz, S, P)
+            mark('ball_query')
+            person = torch.empty((B * M, self.out_channels), dtype=torch.float32, device=pooled.device)
+            sa_feat = sa_mlp_fused.sa_mlp_forward(packed[0], packed[1], g.nsample, flat[:, 0:3], None, new_xyz, None,
+                                                  flat[:, 3:] if C else None, ball_idx, uniform=(S, P),
+                                                  params_host=packed[2], impl='tc', group_max=person, group_size=P,
+                                                  group_zero=empty.view(-1))
+            mark('sa_mlp')
+            person = person.view(B, M, -1)
+        else:
+            xyz = pooled[:, :, 0:3].contiguous()                                    # (B*M,S,3)
+            feats = pooled[:, :, 3:].contiguous().view(B * M * S, -1)
+            fps_idx = pointnet2_utils.farthest_point_sample(xyz, P)                 # (B*M,P) int32
+            mark('fps')
+            new_xyz = torch.gather(xyz, 1, fps_idx.long().unsqueeze(-1).expand(-1, -1, 3)).view(B * M * P, 3)
+            cnt = torch.full((B * M,), S, dtype=torch.int32, device=xyz.device)
+            new_cnt = torch.full((B * M,), P, dtype=torch.int32, device=xyz.device)
+            self.sa.stage_mark = mark
+            _, sa_feat = self.sa(xyz.view(B * M * S, 3), cnt, new_xyz, new_cnt, feats)  # (B*M*P, C_out)
+            self.sa.stage_mark = None
+            mark('sa_mlp')
+            person = sa_feat.view(B * M, P, -1).max(dim=1).values
+            person = person * (empty.view(-1, 1) == 0).to(person.dtype)             # empty persons -> zeros
+            person = person.view(B, M, -1)
+            mark('person_reduce')
         if return_stages:
             return dict(box_idx=box_idx, pooled=pooled, empty=empty, fps_idx=fps_idx, new_xyz=new_xyz,
                         sa_features=sa_feat, person_features=person)

@@ -16,8 +16,8 @@ def ball_query_wrapper(B, M, radius, nsample, new_xyz, new_xyz_batch_cnt, xyz, x
     need_dtype(torch.int32, new_xyz_batch_cnt=new_xyz_batch_cnt, xyz_batch_cnt=xyz_batch_cnt, idx=idx)
     with on_device(xyz):
         _lib.check(_lib.lib().mgar_ball_query_stack(int(B), int(M), float(radius), int(nsample), ptr(new_xyz),
-                                                    ptr(new_xyz_batch_cnt), ptr(xyz), ptr(xyz_batch_cnt), ptr(idx),
-                                                    stream_of(xyz)), "ball_query_wrapper")
+                                                    ptr(new_xyz_batch_cnt), ptr(xyz), 3, ptr(xyz_batch_cnt), 0, 0,
+                                                    ptr(idx), 0, stream_of(xyz)), "ball_query_wrapper")
     return 1
 
 
@@ -53,7 +53,7 @@ def farthest_point_sampling_wrapper(b, n, m, points, temp, idx):
     need_dtype(torch.float32, points=points, temp=temp)
     need_dtype(torch.int32, idx=idx)
     with on_device(points):
-        _lib.check(_lib.lib().mgar_fps_batch(int(b), int(n), int(m), ptr(points), ptr(temp), ptr(idx),
+        _lib.check(_lib.lib().mgar_fps_batch(int(b), int(n), int(m), ptr(points), 3, ptr(temp), ptr(idx), 0,
                                              stream_of(points)), "farthest_point_sampling_wrapper")
     return 1
 

@@ -1,0 +1,118 @@
+"""-m gpu: the composed LiDAR branch (PointPersonEncoder) at BASELINE sizes: the fused 5-kernel path
+against the op-by-op composition through the drop-in pcdet.ops API, stage-wise against the oracle, and
+size-independent properties (determinism, frame independence / sharding, empty persons)."""
+import numpy as np
+import pytest
+import torch
+
+from multimodal_gar_b200 import lidar_branch, synthetic
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def T(a, dev):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+
+def _inputs(seed, B, N, M, dev, **kw):
+    pts, boxes = synthetic.make_batch(seed, B, N=N, M=M, **kw)
+    return pts, boxes, T(pts[..., :3], dev), T(pts[..., 3:4], dev), T(boxes, dev)
+
+
+def _enc(dev, **kw):
+    torch.manual_seed(7)
+    enc = lidar_branch.PointPersonEncoder(1, **kw).to(dev).eval()
+    with torch.no_grad():                                   # non-trivial eval-mode BatchNorm
+        for mod in enc.sa.mlps[0]:
+            if isinstance(mod, torch.nn.BatchNorm2d):
+                mod.running_mean.normal_(0, 0.1)
+                mod.running_var.uniform_(0.8, 1.2)
+                mod.weight.normal_(1, 0.1)
+                mod.bias.normal_(0, 0.1)
+    return enc
+
+
+def test_fused_path_equals_op_by_op_composition_config2(cuda):
+    pts, boxes, xyz, feat, bx = _inputs(1994, 2, 65536, 40, cuda)
+    enc = _enc(cuda)
+    with torch.no_grad():
+        a = enc(xyz, feat, bx, return_stages=True)
+        enc.sa.mlps[0].float()
+        import os
+        os.environ["MGAR_SA_MLP"] = "fp32"                  # force the exact-fp32 kernel and the composed path
+        try:
+            enc2 = _enc(cuda, nsample=32)
+            enc2.load_state_dict(enc.state_dict())
+            packed_supported = lidar_branch.sa_mlp_fused.tc_supported
+            lidar_branch.sa_mlp_fused.tc_supported = lambda *a_, **k_: False
+            b = enc2(xyz, feat, bx, return_stages=True)
+        finally:
+            lidar_branch.sa_mlp_fused.tc_supported = packed_supported
+            del os.environ["MGAR_SA_MLP"]
+    for key in ("box_idx", "empty", "fps_idx"):
+        assert torch.equal(a[key], b[key]), key
+    assert torch.equal(a["pooled"], b["pooled"])
+    assert torch.equal(a["new_xyz"], b["new_xyz"])
+    scale = float(b["sa_features"].abs().max())
+    assert torch.allclose(a["sa_features"], b["sa_features"], rtol=1e-5, atol=1e-5 * scale)
+    assert torch.allclose(a["person_features"], b["person_features"], rtol=1e-5, atol=1e-5 * scale)
+    e = a["empty"].view(-1) > 0
+    assert e.any() and (a["person_features"].view(-1, 128)[e] == 0).all()
+
+
+def test_stagewise_against_oracle_config2_frame(cuda):
+    pts, boxes, xyz, feat, bx = _inputs(2023, 1, 65536, 40, cuda)
+    enc = _enc(cuda)
+    with torch.no_grad():
+        st = enc(xyz, feat, bx, return_stages=True)
+    S, P, K, r, M = 512, 512, 32, 0.3, 40
+    x_np, f_np = np.ascontiguousarray(pts[..., :3]), np.ascontiguousarray(pts[..., 3:4])
+    amb = int(O.in_box_ambiguous(x_np[0], boxes[0]).sum())
+    if amb == 0:
+        np.testing.assert_array_equal(st["box_idx"].cpu().numpy(), O.points_in_boxes_gpu(x_np, boxes))
+        pooled, empty = O.roipoint_pool3d(x_np, f_np, boxes, (0, 0, 0), S)
+        np.testing.assert_array_equal(st["empty"].cpu().numpy(), empty)
+        np.testing.assert_allclose(st["pooled"].cpu().numpy(), O.canonical_transform(pooled, boxes, empty), rtol=0, atol=2e-5)
+    got_pooled = st["pooled"].cpu().numpy()
+    cxyz = np.ascontiguousarray(got_pooled[..., :3])
+    fps = O.farthest_point_sample(cxyz, P)
+    np.testing.assert_array_equal(st["fps_idx"].cpu().numpy(), fps)
+    new_xyz = np.take_along_axis(cxyz, fps[..., None].astype(np.int64), axis=1).reshape(-1, 3)
+    np.testing.assert_array_equal(st["new_xyz"].cpu().numpy(), new_xyz)
+    cnt, ncnt = np.full(M, S, np.int32), np.full(M, P, np.int32)
+    want = O.stack_sa_module_msg([enc.sa.mlps[0].cpu()], [r], [K], cxyz.reshape(-1, 3), cnt, new_xyz, ncnt,
+                                 np.ascontiguousarray(got_pooled[..., 3:]).reshape(-1, 1))
+    scale = max(1.0, float(np.abs(want).max()))
+    np.testing.assert_allclose(st["sa_features"].cpu().numpy(), want, rtol=1e-5, atol=1e-5 * scale)
+    person = want.reshape(M, P, -1).max(axis=1) * (st["empty"].cpu().numpy().reshape(-1, 1) == 0)
+    np.testing.assert_allclose(st["person_features"].cpu().numpy().reshape(M, -1), person, rtol=1e-5, atol=1e-5 * scale)
+
+
+def test_frames_are_independent_and_deterministic(cuda):
+    """Sharding property: a frame's result does not depend on which other frames share its batch."""
+    pts, boxes, xyz, feat, bx = _inputs(3, 6, 65536, 40, cuda)
+    enc = _enc(cuda)
+    with torch.no_grad():
+        full = enc(xyz, feat, bx)
+        again = enc(xyz, feat, bx)
+        assert torch.equal(full, again)
+        for rank in range(2):
+            lo, hi = lidar_branch.shard_frames(6, 2, rank)
+            part = enc(xyz[lo:hi].contiguous(), feat[lo:hi].contiguous(), bx[lo:hi].contiguous())
+            assert torch.equal(part, full[lo:hi])
+
+
+def test_crowded_scene_stress_config5(cuda):
+    """250k points x 200 boxes: pooled indices bit-exact against the oracle, per-person features finite."""
+    pts, boxes, xyz, feat, bx = _inputs(5, 1, 250000, 200, cuda, density_scale=4.0)
+    enc = _enc(cuda)
+    with torch.no_grad():
+        st = enc(xyz, feat, bx, return_stages=True)
+    x_np, f_np = np.ascontiguousarray(pts[..., :3]), np.ascontiguousarray(pts[..., 3:4])
+    if int(O.in_box_ambiguous(x_np[0], boxes[0]).sum()) == 0:
+        pooled, empty = O.roipoint_pool3d(x_np, f_np, boxes, (0, 0, 0), 512)
+        np.testing.assert_array_equal(st["empty"].cpu().numpy(), empty)
+        np.testing.assert_array_equal(st["pooled"].cpu().numpy()[..., 3], O.canonical_transform(pooled, boxes, empty)[..., 3])
+    assert torch.isfinite(st["person_features"]).all()
+    assert st["person_features"].shape == (1, 200, 128)
