@@ -21,6 +21,8 @@
 //   warps 5-12  producers (two groups of four, one smem stage each): gather (xyz - centre | feat),
 //               layer 1, hi/lo split, 128B-swizzled K-major store of the B tile
 // mbarriers: full/empty per smem stage, tfull/tempty per TMEM accumulator stage (4 x 128 columns).
+#include <type_traits>
+
 #include "mgar_common.cuh"
 #include "stack_prefix.cuh"
 
@@ -29,8 +31,10 @@ namespace mgar {
 constexpr int kTcC1 = 64, kTcC2 = 128, kTcNS = 32;
 constexpr int kTcTilePos = 128;                 // positions per tile = 4 centroids x 32 samples
 constexpr int kTcThreads = 13 * 32;
+constexpr int kTcStages = 3;                  // shared-memory stages of the h1 operand = TMEM accumulator stages
+constexpr uint32_t kTmW2Hi = 384, kTmW2Lo = 448;  // TMEM columns of the W2 operand (3 x 128 accumulator columns first)
 constexpr uint32_t kOpBytes = 128 * 64 * 4;     // one 128 x 64 fp32 operand tile: 32 KB
-constexpr uint32_t kTcSmem = 2 * kOpBytes /* W2 hi, lo */ + 2 * 2 * kOpBytes /* 2 stages x (h1 hi, lo) */ + 1024;
+constexpr uint32_t kTcSmem = kTcStages * 2 * kOpBytes /* stages x (h1 hi, lo) */ + 1024;
 
 struct TcLayer1 {          // layer-1 parameters travel as kernel arguments (constant bank operands)
     float w[8][kTcC1];     // [c_in][c_out], BatchNorm scale folded in: w * gamma / sqrt(var + eps)
@@ -75,6 +79,23 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
                    "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
                  : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accumulate) {   // A operand read from TMEM
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                 "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+                 "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+                   "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+                   "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+                 : "memory");
+}
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // hi = tf32(v) (round to nearest by integer arithmetic: cvt.rna.tf32 expands to ~4 instructions),
@@ -130,17 +151,16 @@ template <int C0>
 __global__ void __launch_bounds__(kTcThreads, 1)
 sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcArgs A) {
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t s_bar[12];   // full[2], empty[2], tfull[4], tempty[4]
+    __shared__ __align__(8) uint64_t s_bar[16];   // full[4], empty[4], tfull[4], tempty[4]
     __shared__ uint32_t s_tmem;
 
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024 B alignment
-    const uint32_t a_hi = base, a_lo = base + kOpBytes;
-    const uint32_t b_stage0 = base + 2 * kOpBytes;                  // stage s: hi at +s*2*kOpBytes, lo at +kOpBytes more
+    const uint32_t b_stage0 = base;                                 // stage s: hi at +s*2*kOpBytes, lo at +kOpBytes more
     const uint32_t bar0 = smem_u32(s_bar);
     auto FULL = [&](int s) { return bar0 + 8u * s; };
-    auto EMPTY = [&](int s) { return bar0 + 8u * (2 + s); };
-    auto TFULL = [&](int t) { return bar0 + 8u * (4 + t); };
-    auto TEMPTY = [&](int t) { return bar0 + 8u * (8 + t); };
+    auto EMPTY = [&](int s) { return bar0 + 8u * (4 + s); };
+    auto TFULL = [&](int t) { return bar0 + 8u * (8 + t); };
+    auto TEMPTY = [&](int t) { return bar0 + 8u * (12 + t); };
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int M = A.M;
@@ -153,28 +173,41 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
 
     // ---- one-time setup: barriers, TMEM, W2 split into swizzled hi/lo operand tiles ---------------
     if (tid == 0) {
-        for (int s = 0; s < 2; s++) { mbar_init(FULL(s), 128); mbar_init(EMPTY(s), 1); }
-        for (int t = 0; t < 4; t++) { mbar_init(TFULL(t), 1); mbar_init(TEMPTY(t), 128); }
+        for (int s = 0; s < kTcStages; s++) { mbar_init(FULL(s), 256); mbar_init(EMPTY(s), 1); }
+        for (int t = 0; t < kTcStages; t++) { mbar_init(TFULL(t), 1); mbar_init(TEMPTY(t), 128); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 4) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    for (int e = tid; e < 128 * 16; e += kTcThreads) {
-        const int c = e & 127, c16 = e >> 7;       // output channel (row), 16-byte chunk of K
-        float hi[4], lo[4];
-#pragma unroll
-        for (int j = 0; j < 4; j++) split_tf32(__ldg(A.w2t + (size_t)(c16 * 4 + j) * kTcC2 + c), hi[j], lo[j]);
-        const uint32_t off = tile_off(c, c16);
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_hi + off), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_lo + off), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
-    }
-    fence_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
+    // W2 lives in TENSOR MEMORY as the A operand (row = output channel = lane, column = k): the MMA then
+    // fetches only the h1 tile from shared memory, halving the smem bandwidth the tensor core needs and
+    // leaving all 192 KB of shared memory to three h1 stages.
+    if (warp < 4) {
+        const int c = tid;
+        const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+#pragma unroll
+        for (int kh = 0; kh < 2; kh++) {
+            uint32_t hi[32], lo[32];
+#pragma unroll
+            for (int k = 0; k < 32; k++) {
+                float h, l;
+                split_tf32(__ldg(A.w2t + (size_t)(kh * 32 + k) * kTcC2 + c), h, l);
+                hi[k] = __float_as_uint(h); lo[k] = __float_as_uint(l);
+            }
+            tc_st32(lane_base + kTmW2Hi + kh * 32, hi);
+            tc_st32(lane_base + kTmW2Lo + kh * 32, lo);
+        }
+        tc_wait_st();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
 
     if (warp < 4) {
         // ===== epilogue: thread = output channel, 32 consecutive TMEM columns = one centroid ==========
@@ -187,7 +220,7 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
                 atomicMax(reinterpret_cast<int *>(A.gmax + (size_t)cur_group * kTcC2 + c), __float_as_int(gm));
         };
         for (int i = 0; i < my_tiles; i++) {
-            const int tile = t_beg + i, t = i & 3, u = i >> 2;
+            const int tile = t_beg + i, t = i % kTcStages, u = i / kTcStages;
             mbar_wait(TFULL(t), u & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
@@ -229,21 +262,21 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
             for (int i = 0; i < my_tiles; i++) {
-                const int s = i & 1, j = i >> 1, t = i & 3, u = i >> 2;
+                const int s = i % kTcStages, j = i / kTcStages, t = s, u = j;
                 mbar_wait(FULL(s), j & 1);
                 mbar_wait(TEMPTY(t), (u & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kOpBytes, b_lo = b_hi + kOpBytes;
                 const uint32_t d = tmem + (uint32_t)(t * 128);
                 // small terms first: W2lo*h1hi, W2hi*h1lo, then W2hi*h1hi
-                const uint32_t a_src[3] = {a_lo, a_hi, a_hi}, b_src[3] = {b_hi, b_lo, b_hi};
+                const uint32_t a_src[3] = {tmem + kTmW2Lo, tmem + kTmW2Hi, tmem + kTmW2Hi}, b_src[3] = {b_hi, b_lo, b_hi};
                 uint32_t acc = 0;
 #pragma unroll
                 for (int term = 0; term < 3; term++) {
 #pragma unroll
                     for (int kk = 0; kk < 8; kk++) {
                         const uint32_t koff = (uint32_t)((kk >> 2) * 16384 + (kk & 3) * 32);
-                        tc_mma_tf32(d, make_desc(a_src[term] + koff), make_desc(b_src[term] + koff), idesc, acc);
+                        tc_mma_tf32_ts(d, a_src[term] + (uint32_t)(kk * 8), make_desc(b_src[term] + koff), idesc, acc);
                         acc = 1;
                     }
                 }
@@ -254,11 +287,12 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
         __syncwarp();
     } else {
         // ===== producers: gather + layer 1 (exact fp32) + hi/lo split + swizzled store =====================
-        // Two groups of four warps; group g fills smem stage g with every other tile.  The gather is a
-        // two-level dependent load (idx -> point), so it is software-pipelined two tiles ahead: while
-        // tile j is computed, the points of tile j+1 and the indices of tile j+2 are in flight.
-        const int g = (warp - 5) >> 2, pw = (warp - 5) & 3;     // group (= smem stage), centroid slot in the tile
-        const uint32_t b_hi = b_stage0 + (uint32_t)g * 2 * kOpBytes, b_lo = b_hi + kOpBytes;
+        // All eight warps work on the same tile: warp = (position block of 32, half of the 64 hidden
+        // channels), so a tile is produced in half the time a 4-warp group would need and the smem stage
+        // goes back to the tensor core sooner.  The gather is a two-level dependent load (idx -> point) and
+        // is software-pipelined: while tile i is computed, the points of tile i+1 and the indices of tile
+        // i+2 are in flight.
+        const int pw = (warp - 5) & 3, half = (warp - 5) >> 2;  // centroid slot in the tile, channel half
         const int r = pw * 32 + lane;
 
         auto load_idx = [&](int i, int &iv, int &em) {          // local tile i -> this lane's sample index
@@ -294,30 +328,12 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
                 q[2] = __ldg(A.new_xyz + (size_t)m * 3 + 2);
             }
         };
-
-        int iv_a, em_a, iv_b, em_b;
-        float vb[C0], qb[3];
-        bool live_b;
-        load_idx(g, iv_b, em_b);
-        load_idx(g + 2, iv_a, em_a);
-        load_pt(g, iv_b, em_b, vb, qb, live_b);
-        int j = 0;
-        for (int i = g; i < my_tiles; i += 2, j++) {
-            float x[C0];
+        // 32 hidden channels [32*H, 32*H+32) of this thread's position -> K block H of the stage
+        auto produce = [&](auto Hc, const float (&x)[C0], uint32_t b_hi, uint32_t b_lo) {
+            constexpr int H = decltype(Hc)::value;
 #pragma unroll
-            for (int cc = 0; cc < C0; cc++) x[cc] = 0.f;
-            if (live_b) {
-                x[0] = __fsub_rn(vb[0], qb[0]); x[1] = __fsub_rn(vb[1], qb[1]); x[2] = __fsub_rn(vb[2], qb[2]);
-#pragma unroll
-                for (int cc = 3; cc < C0; cc++) x[cc] = vb[cc];
-            }
-            iv_b = iv_a; em_b = em_a;
-            load_pt(i + 2, iv_b, em_b, vb, qb, live_b);     // points of the next tile of this group
-            load_idx(i + 4, iv_a, em_a);                    // indices of the one after
-
-            mbar_wait(EMPTY(g), (j & 1) ^ 1);
-#pragma unroll
-            for (int c16 = 0; c16 < 16; c16++) {
+            for (int c8 = 0; c8 < 8; c8++) {
+                const int c16 = H * 8 + c8;
                 float hi[4], lo[4];
 #pragma unroll
                 for (int q = 0; q < 4; q++) {
@@ -331,8 +347,34 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
                 asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(b_hi + off), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
                 asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(b_lo + off), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
             }
+        };
+
+        int iv_a, em_a, iv_b, em_b;
+        float vb[C0], qb[3];
+        bool live_b;
+        load_idx(0, iv_b, em_b);
+        load_idx(1, iv_a, em_a);
+        load_pt(0, iv_b, em_b, vb, qb, live_b);
+        for (int i = 0; i < my_tiles; i++) {
+            const int s = i % kTcStages, j = i / kTcStages;
+            float x[C0];
+#pragma unroll
+            for (int cc = 0; cc < C0; cc++) x[cc] = 0.f;
+            if (live_b) {
+                x[0] = __fsub_rn(vb[0], qb[0]); x[1] = __fsub_rn(vb[1], qb[1]); x[2] = __fsub_rn(vb[2], qb[2]);
+#pragma unroll
+                for (int cc = 3; cc < C0; cc++) x[cc] = vb[cc];
+            }
+            iv_b = iv_a; em_b = em_a;
+            load_pt(i + 1, iv_b, em_b, vb, qb, live_b);     // points of the next tile
+            load_idx(i + 2, iv_a, em_a);                    // indices of the one after
+
+            const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kOpBytes, b_lo = b_hi + kOpBytes;
+            mbar_wait(EMPTY(s), (j & 1) ^ 1);
+            if (half == 0) produce(std::integral_constant<int, 0>{}, x, b_hi, b_lo);
+            else produce(std::integral_constant<int, 1>{}, x, b_hi, b_lo);
             fence_async_smem();          // generic-proxy stores -> visible to the tensor core (async proxy)
-            mbar_arrive(FULL(g));
+            mbar_arrive(FULL(s));
         }
     }
 

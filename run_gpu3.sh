@@ -1,0 +1,12 @@
+#!/bin/bash
+cd "$GRAFT_REPO_ROOT" || exit 1
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_parity_gpu.py tests/test_pipeline_gpu.py -q -m gpu -p no:cacheprovider -x -k "tensor_core or sa_m or pipeline or fused or stagewise" > gpurun_out/pytest_tc.log 2>&1; echo "tc rc=$?"
+tail -5 gpurun_out/pytest_tc.log
+timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_quick.json 2> gpurun_out/bench.err; echo "bench rc=$?"
+python - <<'PY'
+import json
+d=json.load(open('gpurun_out/bench_quick.json'))
+print(d['value'], d['ms_per_step'], {k:v['ms'] for k,v in d['stages'].items()}, 'e2e', d['e2e']['value'], 'lat', d['latency_1frame_ms'])
+PY
+tail -3 gpurun_out/bench.err
