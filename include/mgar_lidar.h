@@ -138,7 +138,7 @@ MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const flo
 
 /* Same operation on the 5th-generation tensor cores (tcgen05.mma kind::tf32, fp32 accumulation in
  * TMEM, 3xTF32 operand splitting: fp32-level accuracy, within the 1e-5 parity bar) for the shape
- * mgar_sa_mlp_tc_supported() accepts: nsample = 32, C_in <= 5, channels [3+C_in, 64, 128], max-pool
+ * mgar_sa_mlp_tc_supported() accepts: nsample = 32, C_in <= 4, channels [3+C_in, 64, 128], max-pool
  * (BASELINE configs[1]).  Other shapes must use mgar_sa_mlp_fwd_fp32.  Extra arguments:
  * xyz_stride / feat_stride = floats between consecutive rows (3 / C_in for packed arrays; 4 / 4 with
  * features == xyz + 3 reads a pooled (N,3+1) array in place with one 128-bit load per point);

@@ -21,6 +21,8 @@
 //   warps 5-12  producers (two groups of four, one smem stage each): gather (xyz - centre | feat),
 //               layer 1, hi/lo split, 128B-swizzled K-major store of the B tile
 // mbarriers: full/empty per smem stage, tfull/tempty per TMEM accumulator stage (4 x 128 columns).
+#include <stdlib.h>
+
 #include <type_traits>
 
 #include "mgar_common.cuh"
@@ -31,10 +33,14 @@ namespace mgar {
 constexpr int kTcC1 = 64, kTcC2 = 128, kTcNS = 32;
 constexpr int kTcTilePos = 128;                 // positions per tile = 4 centroids x 32 samples
 constexpr int kTcThreads = 13 * 32;
-constexpr int kTcStages = 3;                  // shared-memory stages of the h1 operand = TMEM accumulator stages
-constexpr uint32_t kTmW2Hi = 384, kTmW2Lo = 448;  // TMEM columns of the W2 operand (3 x 128 accumulator columns first)
+constexpr int kTcStages = 3;                  // shared-memory stages of the h1 operand
+constexpr int kAccStages = 2;                 // TMEM stages of the layer-2 accumulator (128 columns each)
+// TMEM columns: layer-2 accumulators 0,128; layer-1 accumulators 256,320 (64 each); W2 operand hi 384, lo 448
+constexpr uint32_t kTmD1 = 256, kTmW2Hi = 384, kTmW2Lo = 448;
+constexpr uint32_t kXBytes = 128 * 8 * 4;       // one 128 x 8 fp32 layer-1 input tile (no swizzle): 4 KB
+constexpr uint32_t kW1Bytes = 64 * 8 * 4;       // W1^T operand, 64 x 8: 2 KB
 constexpr uint32_t kOpBytes = 128 * 64 * 4;     // one 128 x 64 fp32 operand tile: 32 KB
-constexpr uint32_t kTcSmem = kTcStages * 2 * kOpBytes /* stages x (h1 hi, lo) */ + 1024;
+constexpr uint32_t kTcSmem = kTcStages * 2 * kOpBytes /* h1 hi,lo */ + 2 * 2 * kXBytes /* x hi,lo x2 */ + 2 * kW1Bytes + 1024;
 
 struct TcLayer1 {          // layer-1 parameters travel as kernel arguments (constant bank operands)
     float w[8][kTcC1];     // [c_in][c_out], BatchNorm scale folded in: w * gamma / sqrt(var + eps)
@@ -49,6 +55,12 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
 }
+// Arrive without release semantics: for barriers that only hand TENSOR MEMORY back to the MMA issuer (the
+// tcgen05 fences order those accesses).  A releasing arrive would also wait for this thread's outstanding
+// global stores / prefetch loads - a full memory round trip per tile.
+__device__ __forceinline__ void mbar_arrive_relaxed(uint32_t bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.relaxed.cta.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok;
     do {
@@ -56,6 +68,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
                      "selp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     } while (!ok);
+}
+__device__ __forceinline__ bool elect_one() {   // one lane of a converged warp; control flow stays warp-uniform
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -78,6 +95,17 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
                    "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
                    "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
                  : "r"(taddr) : "memory");
+}
+// keeps the hi/lo split of a 4-vector and stores both halves with 128-bit shared stores
+__device__ __forceinline__ void sts_split4(uint32_t a_hi, uint32_t a_lo, const float (&v)[4]) {
+    float hi[4], lo[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        hi[q] = __uint_as_float(__float_as_uint(v[q]) & 0xffffe000u);   // truncate to tf32: lo stays exact, 13 bits
+        lo[q] = __fsub_rn(v[q], hi[q]);
+    }
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_hi), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_lo), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
 }
 __device__ __forceinline__ void tc_mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
                                                uint32_t accumulate) {   // A operand read from TMEM
@@ -117,6 +145,18 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
     return d;
 }
 
+// K-major operand with K = 8 tf32 (32 B per row), no swizzle: 8-row x 16-byte core matrices, the two
+// core matrices along K 128 B apart (LBO), 8-row groups 256 B apart (SBO).
+__device__ __forceinline__ uint64_t make_desc_k8(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(128 >> 4) << 16;                  // leading (K) byte offset
+    d |= (uint64_t)(256 >> 4) << 32;                  // stride (M/N) byte offset
+    d |= (uint64_t)1 << 46;                           // version = 1; layout type 0 = no swizzle
+    return d;
+}
+__device__ __forceinline__ uint32_t k8_off(int r, int khalf) { return (uint32_t)((r >> 3) * 256 + khalf * 128 + (r & 7) * 16); }
+
 // byte offset of element (row r, 16-byte chunk c16 of the 64-wide K extent) inside an operand tile
 __device__ __forceinline__ uint32_t tile_off(int r, int c16) {
     const int kb = c16 >> 3, cw = c16 & 7;
@@ -150,17 +190,25 @@ struct TcArgs {
 template <int C0>
 __global__ void __launch_bounds__(kTcThreads, 1)
 sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcArgs A) {
+    static_assert(C0 >= 3 && C0 <= 7, "layer-1 K is padded to 8 with one column for the folded bias");
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t s_bar[16];   // full[4], empty[4], tfull[4], tempty[4]
+    // full[3] empty[3] | tfull[2] tempty[2] | xfull[2] xempty[2] | dfull[2] dempty[2]
+    __shared__ __align__(8) uint64_t s_bar[18];
     __shared__ uint32_t s_tmem;
 
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024 B alignment
-    const uint32_t b_stage0 = base;                                 // stage s: hi at +s*2*kOpBytes, lo at +kOpBytes more
+    const uint32_t b_stage0 = base;                                 // h1 stage s: hi at +s*2*kOpBytes, lo at +kOpBytes more
+    const uint32_t x_stage0 = base + kTcStages * 2 * kOpBytes;      // x stage: hi at +xs*2*kXBytes, lo at +kXBytes more
+    const uint32_t w1_hi = x_stage0 + 2 * 2 * kXBytes, w1_lo = w1_hi + kW1Bytes;
     const uint32_t bar0 = smem_u32(s_bar);
     auto FULL = [&](int s) { return bar0 + 8u * s; };
-    auto EMPTY = [&](int s) { return bar0 + 8u * (4 + s); };
-    auto TFULL = [&](int t) { return bar0 + 8u * (8 + t); };
-    auto TEMPTY = [&](int t) { return bar0 + 8u * (12 + t); };
+    auto EMPTY = [&](int s) { return bar0 + 8u * (3 + s); };
+    auto TFULL = [&](int t) { return bar0 + 8u * (6 + t); };
+    auto TEMPTY = [&](int t) { return bar0 + 8u * (8 + t); };
+    auto XFULL = [&](int x) { return bar0 + 8u * (10 + x); };
+    auto XEMPTY = [&](int x) { return bar0 + 8u * (12 + x); };
+    auto DFULL = [&](int x) { return bar0 + 8u * (14 + x); };
+    auto DEMPTY = [&](int x) { return bar0 + 8u * (16 + x); };
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int M = A.M;
@@ -171,23 +219,41 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
     const int t_end = (int)((long long)(blockIdx.x + 1) * n_tiles / gridDim.x);
     const int my_tiles = t_end - t_beg;
 
-    // ---- one-time setup: barriers, TMEM, W2 split into swizzled hi/lo operand tiles ---------------
+    // ---- one-time setup: barriers, TMEM, weight operands ---------------------------------------------
     if (tid == 0) {
         for (int s = 0; s < kTcStages; s++) { mbar_init(FULL(s), 256); mbar_init(EMPTY(s), 1); }
-        for (int t = 0; t < kTcStages; t++) { mbar_init(TFULL(t), 1); mbar_init(TEMPTY(t), 128); }
+        for (int t = 0; t < kAccStages; t++) { mbar_init(TFULL(t), 1); mbar_init(TEMPTY(t), 128); }
+        for (int x = 0; x < 2; x++) {
+            mbar_init(XFULL(x), 128); mbar_init(XEMPTY(x), 1);
+            mbar_init(DFULL(x), 1); mbar_init(DEMPTY(x), 256);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 4) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    // W1^T (64 channels x K=8: C0 folded weights, the folded BatchNorm shift in column C0, zeros) as the
+    // B operand of the layer-1 MMA, hi/lo split, no-swizzle K-major
+    if (tid >= 160 && tid < 224) {
+        const int ch = tid - 160;
+        float k0[4], k1[4];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const float v = k < C0 ? L1.w[k][ch] : (k == C0 ? L1.sh[ch] : 0.f);
+            if (k < 4) k0[k] = v; else k1[k - 4] = v;
+        }
+        sts_split4(w1_hi + k8_off(ch, 0), w1_lo + k8_off(ch, 0), k0);
+        sts_split4(w1_hi + k8_off(ch, 1), w1_lo + k8_off(ch, 1), k1);
+        fence_async_smem();
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
-    // W2 lives in TENSOR MEMORY as the A operand (row = output channel = lane, column = k): the MMA then
-    // fetches only the h1 tile from shared memory, halving the smem bandwidth the tensor core needs and
-    // leaving all 192 KB of shared memory to three h1 stages.
+    // W2 lives in TENSOR MEMORY as the A operand of the layer-2 MMA (row = output channel = lane,
+    // column = k): the MMA then fetches only the h1 tile from shared memory, and shared memory is left to
+    // three h1 stages.
     if (warp < 4) {
         const int c = tid;
         const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
@@ -220,7 +286,7 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
                 atomicMax(reinterpret_cast<int *>(A.gmax + (size_t)cur_group * kTcC2 + c), __float_as_int(gm));
         };
         for (int i = 0; i < my_tiles; i++) {
-            const int tile = t_beg + i, t = i % kTcStages, u = i / kTcStages;
+            const int tile = t_beg + i, t = i % kAccStages, u = i / kAccStages;
             mbar_wait(TFULL(t), u & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
@@ -242,7 +308,7 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
                 res[2 * h + 1] = fmaxf(m1, 0.f);
             }
             tc_fence_before();
-            mbar_arrive(TEMPTY(t));
+            mbar_arrive_relaxed(TEMPTY(t));
 #pragma unroll
             for (int q = 0; q < 4; q++) {
                 const int m = tile * 4 + q;
@@ -258,41 +324,69 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
         }
         flush();
     } else if (warp == 4) {
-        // ===== MMA issuer: one thread, 24 x (128x128x8 tf32) per tile ====================================
-        if (lane == 0) {
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-            for (int i = 0; i < my_tiles; i++) {
-                const int s = i % kTcStages, j = i / kTcStages, t = s, u = j;
-                mbar_wait(FULL(s), j & 1);
-                mbar_wait(TEMPTY(t), (u & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kOpBytes, b_lo = b_hi + kOpBytes;
-                const uint32_t d = tmem + (uint32_t)(t * 128);
-                // small terms first: W2lo*h1hi, W2hi*h1lo, then W2hi*h1hi
-                const uint32_t a_src[3] = {tmem + kTmW2Lo, tmem + kTmW2Hi, tmem + kTmW2Hi}, b_src[3] = {b_hi, b_lo, b_hi};
-                uint32_t acc = 0;
+        // ===== MMA issuer.  Per tile: layer 1 = 3 x (128x64x8), layer 2 = 24 x (128x128x8) =================
+        // A 128x128x8 tf32 MMA is only 64 tensor-pipe cycles, so the ISSUE path must stay well under that
+        // per instruction: the whole warp runs the (warp-uniform) control flow so descriptors are built on
+        // the uniform datapath, only the tcgen05 instructions are predicated on one elected lane, and a
+        // descriptor step is a single add on its low word.
+        const uint32_t idesc1 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint64_t w1d_hi = make_desc_k8(w1_hi), w1d_lo = make_desc_k8(w1_lo);
+        // layer 1 of local tile i: D1[pos, ch] = x[pos, 0:8] . W1^T[ch, 0:8] (bias rides in column C0)
+        auto layer1 = [&](int i) {
+            const int xs = i & 1, jx = i >> 1;
+            mbar_wait(XFULL(xs), jx & 1);
+            mbar_wait(DEMPTY(xs), (jx & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t x_hi = x_stage0 + (uint32_t)xs * 2 * kXBytes;
+            const uint64_t xd_hi = make_desc_k8(x_hi), xd_lo = make_desc_k8(x_hi + kXBytes);
+            const uint32_t d1 = tmem + kTmD1 + (uint32_t)(xs * 64);
+            if (elect_one()) {
+                tc_mma_tf32(d1, xd_lo, w1d_hi, idesc1, 0);
+                tc_mma_tf32(d1, xd_hi, w1d_lo, idesc1, 1);
+                tc_mma_tf32(d1, xd_hi, w1d_hi, idesc1, 1);
+                tc_commit(XEMPTY(xs));
+                tc_commit(DFULL(xs));
+            }
+            __syncwarp();
+        };
+        if (my_tiles > 0) layer1(0);
+        for (int i = 0; i < my_tiles; i++) {
+            if (i + 1 < my_tiles) layer1(i + 1);   // issued ahead so the converters overlap layer 2 of tile i
+            const int s = i % kTcStages, j = i / kTcStages, t = i % kAccStages, u = i / kAccStages;
+            mbar_wait(FULL(s), j & 1);
+            mbar_wait(TEMPTY(t), (u & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kOpBytes;
+            const uint64_t bd_hi = make_desc(b_hi), bd_lo = make_desc(b_hi + kOpBytes);
+            const uint32_t d = tmem + (uint32_t)(t * 128);
+            if (elect_one()) {
+                // small terms first: W2lo*h1hi, W2hi*h1lo, then W2hi*h1hi.  K step kk: 8 TMEM columns of W2,
+                // 32 bytes inside the 128B-swizzled row (second K block 16 KB further) of h1.
 #pragma unroll
                 for (int term = 0; term < 3; term++) {
+                    const uint32_t a0 = tmem + (term == 0 ? kTmW2Lo : kTmW2Hi);
+                    const uint64_t b0 = term == 1 ? bd_lo : bd_hi;
 #pragma unroll
                     for (int kk = 0; kk < 8; kk++) {
                         const uint32_t koff = (uint32_t)((kk >> 2) * 16384 + (kk & 3) * 32);
-                        tc_mma_tf32_ts(d, a_src[term] + (uint32_t)(kk * 8), make_desc(b_src[term] + koff), idesc, acc);
-                        acc = 1;
+                        tc_mma_tf32_ts(d, a0 + (uint32_t)(kk * 8), b0 + (uint64_t)(koff >> 4), idesc2, (term | kk) ? 1u : 0u);
                     }
                 }
                 tc_commit(EMPTY(s));     // smem stage reusable once these MMAs have read it
                 tc_commit(TFULL(t));     // accumulator ready for the epilogue
             }
+            __syncwarp();
         }
-        __syncwarp();
     } else {
-        // ===== producers: gather + layer 1 (exact fp32) + hi/lo split + swizzled store =====================
-        // All eight warps work on the same tile: warp = (position block of 32, half of the 64 hidden
-        // channels), so a tile is produced in half the time a 4-warp group would need and the smem stage
-        // goes back to the tensor core sooner.  The gather is a two-level dependent load (idx -> point) and
-        // is software-pipelined: while tile i is computed, the points of tile i+1 and the indices of tile
-        // i+2 are in flight.
-        const int pw = (warp - 5) & 3, half = (warp - 5) >> 2;  // centroid slot in the tile, channel half
+        // ===== gather + converters (8 warps) =================================================================
+        // warp = (position block pw = TMEM lane quarter, channel half).  Per tile:
+        //   (a) the 4 warps of half 0 gather (xyz - centre | feat), split hi/lo and store the 128 x 8 layer-1
+        //       input tile (bias column = 1) one tile AHEAD; the gather itself (idx -> point, two dependent
+        //       loads) is software-pipelined two more tiles ahead in registers;
+        //   (b) all 8 warps read their position's 32 layer-1 outputs back from TMEM (tcgen05.ld), apply
+        //       ReLU, split hi/lo and store the 128B-swizzled K-major h1 operand of the layer-2 MMA.
+        const int pw = warp & 3, half = (warp - 5) >> 2;
         const int r = pw * 32 + lane;
 
         auto load_idx = [&](int i, int &iv, int &em) {          // local tile i -> this lane's sample index
@@ -328,51 +422,61 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
                 q[2] = __ldg(A.new_xyz + (size_t)m * 3 + 2);
             }
         };
-        // 32 hidden channels [32*H, 32*H+32) of this thread's position -> K block H of the stage
-        auto produce = [&](auto Hc, const float (&x)[C0], uint32_t b_hi, uint32_t b_lo) {
-            constexpr int H = decltype(Hc)::value;
+        // layer-1 input row of local tile i -> x stage i & 1
+        auto store_x = [&](int i, const float (&v)[C0], const float (&q)[3], bool live) {
+            const int xs = i & 1, jx = i >> 1;
+            float k0[4] = {0.f, 0.f, 0.f, 0.f}, k1[4] = {0.f, 0.f, 0.f, 0.f};
+            if (live) {
+                k0[0] = __fsub_rn(v[0], q[0]); k0[1] = __fsub_rn(v[1], q[1]); k0[2] = __fsub_rn(v[2], q[2]);
 #pragma unroll
-            for (int c8 = 0; c8 < 8; c8++) {
-                const int c16 = H * 8 + c8;
-                float hi[4], lo[4];
-#pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    const int o = c16 * 4 + q;
-                    float acc = L1.sh[o];
-#pragma unroll
-                    for (int cc = 0; cc < C0; cc++) acc = __fmaf_rn(x[cc], L1.w[cc][o], acc);
-                    split_tf32(fmaxf(acc, 0.f), hi[q], lo[q]);
-                }
-                const uint32_t off = tile_off(r, c16);
-                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(b_hi + off), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
-                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(b_lo + off), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
+                for (int cc = 3; cc < C0; cc++) { if (cc < 4) k0[cc] = v[cc]; else k1[cc - 4] = v[cc]; }
             }
+            if (C0 < 4) k0[C0] = 1.f; else k1[C0 - 4] = 1.f;   // multiplies the folded BatchNorm shift
+            const uint32_t x_hi = x_stage0 + (uint32_t)xs * 2 * kXBytes, x_lo = x_hi + kXBytes;
+            mbar_wait(XEMPTY(xs), (jx & 1) ^ 1);
+            sts_split4(x_hi + k8_off(r, 0), x_lo + k8_off(r, 0), k0);
+            sts_split4(x_hi + k8_off(r, 1), x_lo + k8_off(r, 1), k1);
+            fence_async_smem();
+            mbar_arrive(XFULL(xs));
         };
 
-        int iv_a, em_a, iv_b, em_b;
+        int iv_a = -1, em_a = 0, iv_b = -1, em_b = 0;
         float vb[C0], qb[3];
-        bool live_b;
-        load_idx(0, iv_b, em_b);
-        load_idx(1, iv_a, em_a);
-        load_pt(0, iv_b, em_b, vb, qb, live_b);
+        bool live_b = false;
+        if (half == 0) {
+            load_idx(0, iv_b, em_b);
+            load_pt(0, iv_b, em_b, vb, qb, live_b);
+            load_idx(1, iv_b, em_b);
+            load_idx(2, iv_a, em_a);
+            if (my_tiles > 0) store_x(0, vb, qb, live_b);
+            load_pt(1, iv_b, em_b, vb, qb, live_b);
+        }
         for (int i = 0; i < my_tiles; i++) {
-            const int s = i % kTcStages, j = i / kTcStages;
-            float x[C0];
-#pragma unroll
-            for (int cc = 0; cc < C0; cc++) x[cc] = 0.f;
-            if (live_b) {
-                x[0] = __fsub_rn(vb[0], qb[0]); x[1] = __fsub_rn(vb[1], qb[1]); x[2] = __fsub_rn(vb[2], qb[2]);
-#pragma unroll
-                for (int cc = 3; cc < C0; cc++) x[cc] = vb[cc];
+            if (half == 0 && i + 1 < my_tiles) {
+                store_x(i + 1, vb, qb, live_b);                 // gathered during the previous iteration
+                iv_b = iv_a; em_b = em_a;
+                load_pt(i + 2, iv_b, em_b, vb, qb, live_b);     // points two tiles ahead
+                load_idx(i + 3, iv_a, em_a);                    // indices three tiles ahead
             }
-            iv_b = iv_a; em_b = em_a;
-            load_pt(i + 1, iv_b, em_b, vb, qb, live_b);     // points of the next tile
-            load_idx(i + 2, iv_a, em_a);                    // indices of the one after
+            const int xs = i & 1, jx = i >> 1, s = i % kTcStages, j = i / kTcStages;
+            mbar_wait(DFULL(xs), jx & 1);
+            tc_fence_after();
+            uint32_t h[32];
+            tc_ld32(tmem + ((uint32_t)(pw * 32) << 16) + kTmD1 + (uint32_t)(xs * 64 + half * 32), h);
+            tc_wait_ld();
+            tc_fence_before();
+            mbar_arrive_relaxed(DEMPTY(xs));
 
             const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kOpBytes, b_lo = b_hi + kOpBytes;
             mbar_wait(EMPTY(s), (j & 1) ^ 1);
-            if (half == 0) produce(std::integral_constant<int, 0>{}, x, b_hi, b_lo);
-            else produce(std::integral_constant<int, 1>{}, x, b_hi, b_lo);
+#pragma unroll
+            for (int c8 = 0; c8 < 8; c8++) {
+                float y[4];
+#pragma unroll
+                for (int q = 0; q < 4; q++) y[q] = fmaxf(__uint_as_float(h[c8 * 4 + q]), 0.f);
+                const uint32_t off = tile_off(r, half * 8 + c8);
+                sts_split4(b_hi + off, b_lo + off, y);
+            }
             fence_async_smem();          // generic-proxy stores -> visible to the tensor core (async proxy)
             mbar_arrive(FULL(s));
         }
@@ -392,7 +496,7 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
 using namespace mgar;
 
 extern "C" int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg) {
-    return nsample == kTcNS && C_in >= 0 && C_in <= 5 && n_layers == 2 && channels_host && channels_host[0] == 3 + C_in &&
+    return nsample == kTcNS && C_in >= 0 && C_in <= 4 && n_layers == 2 && channels_host && channels_host[0] == 3 + C_in &&
            channels_host[1] == kTcC1 && channels_host[2] == kTcC2 && !pool_avg;
 }
 
@@ -405,7 +509,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
                                   void *stream) {
     MGAR_REQUIRE(B >= 1 && M >= 0, "sa_mlp_tc: bad size");
     MGAR_REQUIRE(mgar_sa_mlp_tc_supported(nsample, C_in, n_layers, channels_host, pool_avg),
-                 "sa_mlp_tc: only nsample=32, C_in<=5, channels [3+C_in,64,128], max-pool run on the tensor-core path");
+                 "sa_mlp_tc: only nsample=32, C_in<=4, channels [3+C_in,64,128], max-pool run on the tensor-core path");
     if (M == 0) return MGAR_OK;
     MGAR_REQUIRE(xyz && new_xyz && idx && params && params_host && (out || group_max), "sa_mlp_tc: null pointer");
     MGAR_REQUIRE(features || C_in == 0, "sa_mlp_tc: features missing");
@@ -451,7 +555,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
         count_launch();                                                                                         \
         return check_launch("sa_mlp_tc");                                                                       \
     }
-    MGAR_TC_CASE(3) MGAR_TC_CASE(4) MGAR_TC_CASE(5) MGAR_TC_CASE(6) MGAR_TC_CASE(7) MGAR_TC_CASE(8)
+    MGAR_TC_CASE(3) MGAR_TC_CASE(4) MGAR_TC_CASE(5) MGAR_TC_CASE(6) MGAR_TC_CASE(7)
 #undef MGAR_TC_CASE
     set_error("sa_mlp_tc: unsupported C0=%d", C0);
     return MGAR_EINVAL;
