@@ -8,7 +8,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmgar_lidar.so")
+LIB_PATH = os.environ.get("MGAR_LIB", os.path.join(_HERE, "libmgar_lidar.so"))   # MGAR_LIB: experiment builds only
 _lib = None
 
 c_fp = ctypes.c_void_p  # device/host pointers travel as integers (tensor.data_ptr())

@@ -17,7 +17,7 @@
 //
 // One persistent CTA per SM, warp-specialised:
 //   warps 0-3   epilogue: tcgen05.ld 32x32b.x32 -> scale/shift, max, ReLU -> coalesced store
-//   warp  4     TMEM allocation + the single MMA-issuing thread (24 MMAs per 128-position tile)
+//   warp  4     TMEM allocation + layer-2 MMA issue (24 MMAs per 128-position tile); warp 13: layer-1 MMA issue
 //   warps 5-12  producers (two groups of four, one smem stage each): gather (xyz - centre | feat),
 //               layer 1, hi/lo split, 128B-swizzled K-major store of the B tile
 // mbarriers: full/empty per smem stage, tfull/tempty per TMEM accumulator stage (4 x 128 columns).
@@ -28,11 +28,15 @@
 #include "mgar_common.cuh"
 #include "stack_prefix.cuh"
 
+#ifndef MGAR_TC_TERMS
+#define MGAR_TC_TERMS 3   // 3xTF32; timing experiments build with fewer
+#endif
+
 namespace mgar {
 
 constexpr int kTcC1 = 64, kTcC2 = 128, kTcNS = 32;
 constexpr int kTcTilePos = 128;                 // positions per tile = 4 centroids x 32 samples
-constexpr int kTcThreads = 13 * 32;
+constexpr int kTcThreads = 14 * 32;
 constexpr int kTcStages = 3;                  // shared-memory stages of the h1 operand
 constexpr int kAccStages = 2;                 // TMEM stages of the layer-2 accumulator (128 columns each)
 // TMEM columns: layer-2 accumulators 0,128; layer-1 accumulators 256,320 (64 each); W2 operand hi 384, lo 448
@@ -184,6 +188,9 @@ struct TcArgs {
     float *out; int ld_out;              // (M, 128) SA features, may be null
     float *gmax; int group_size;         // (ceil(M / group_size), 128) max over each group of centroids, may be null
     const int *group_zero;               // per group: non-zero -> the group's row stays zero (empty person)
+#ifdef MGAR_TC_TRACE
+    long long *trace;                    // timeline stamps of CTA 0, tiles 100..131 (debug build only)
+#endif
     int packed4;                         // xyz/features are columns 0..2 / 3 of one 16B-aligned (N,4) array
 };
 
@@ -211,6 +218,11 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
     auto DEMPTY = [&](int x) { return bar0 + 8u * (16 + x); };
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef MGAR_TC_TRACE
+#define TRACE(slot, i) do { if (blockIdx.x == 0 && lane == 0 && (i) >= 100 && (i) < 132) A.trace[((i) - 100) * 16 + (slot)] = clock64(); } while (0)
+#else
+#define TRACE(slot, i) do { } while (0)
+#endif
     const int M = A.M;
     const int n_tiles = (M + 3) >> 2;
     // contiguous tile range per CTA: consecutive tiles belong to the same person, so the running
@@ -277,17 +289,33 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
 
     if (warp < 4) {
         // ===== epilogue: thread = output channel, 32 consecutive TMEM columns = one centroid ==========
+        // This role is a serial chain per tile (wait, TMEM load, reduce, store), so it is kept free of long
+        // dependent sequences: four independent partial maxima per centroid, no integer division (the
+        // group / person boundary is tracked incrementally), running output pointer.
         const int c = tid;
         const float scale = __ldg(A.sc2 + c), shift = __ldg(A.sh2 + c);
+        const int gs = A.group_size;
+        int m_next = t_beg * 4;                                   // first centroid of the next tile
+        int grp = A.gmax ? m_next / gs : 0, g_end = (grp + 1) * gs;
         float gm = 0.f;
-        int cur_group = -1;
+        float *outp = A.out ? A.out + (size_t)m_next * A.ld_out + c : nullptr;
         auto flush = [&]() {
-            if (A.gmax && cur_group >= 0 && !(A.group_zero && __ldg(A.group_zero + cur_group)))
-                atomicMax(reinterpret_cast<int *>(A.gmax + (size_t)cur_group * kTcC2 + c), __float_as_int(gm));
+            if (!(A.group_zero && __ldg(A.group_zero + grp)))
+                atomicMax(reinterpret_cast<int *>(A.gmax + (size_t)grp * kTcC2 + c), __float_as_int(gm));
+        };
+        auto reduce32 = [&](const uint32_t (&v)[32]) {
+            float a[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) a[q] = __fmaf_rn(__uint_as_float(v[q]), scale, shift);
+#pragma unroll
+            for (int s = 4; s < 32; s++) a[s & 3] = fmaxf(a[s & 3], __fmaf_rn(__uint_as_float(v[s]), scale, shift));
+            return fmaxf(fmaxf(fmaxf(a[0], a[1]), fmaxf(a[2], a[3])), 0.f);   // ReLU commutes with the max
         };
         for (int i = 0; i < my_tiles; i++) {
-            const int tile = t_beg + i, t = i % kAccStages, u = i / kAccStages;
+            const int t = i % kAccStages, u = i / kAccStages;
+            if (warp == 0) TRACE(14, i);
             mbar_wait(TFULL(t), u & 1);
+            if (warp == 0) TRACE(0, i);
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
             float res[4];
@@ -297,43 +325,71 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
                 tc_ld32(taddr + (2 * h) * 32, v0);
                 tc_ld32(taddr + (2 * h + 1) * 32, v1);
                 tc_wait_ld();
-                float m0 = __fmaf_rn(__uint_as_float(v0[0]), scale, shift);
-                float m1 = __fmaf_rn(__uint_as_float(v1[0]), scale, shift);
-#pragma unroll
-                for (int s = 1; s < 32; s++) {
-                    m0 = fmaxf(m0, __fmaf_rn(__uint_as_float(v0[s]), scale, shift));
-                    m1 = fmaxf(m1, __fmaf_rn(__uint_as_float(v1[s]), scale, shift));
-                }
-                res[2 * h] = fmaxf(m0, 0.f);       // ReLU commutes with the max over samples
-                res[2 * h + 1] = fmaxf(m1, 0.f);
+                res[2 * h] = reduce32(v0);
+                res[2 * h + 1] = reduce32(v1);
             }
             tc_fence_before();
             mbar_arrive_relaxed(TEMPTY(t));
+            if (warp == 0) TRACE(1, i);
 #pragma unroll
             for (int q = 0; q < 4; q++) {
-                const int m = tile * 4 + q;
+                const int m = m_next + q;
                 if (m < M) {
-                    if (A.out) A.out[(size_t)m * A.ld_out + c] = res[q];
+                    if (outp) outp[(size_t)q * A.ld_out] = res[q];
                     if (A.gmax) {
-                        const int grp = m / A.group_size;
-                        if (grp != cur_group) { flush(); cur_group = grp; gm = 0.f; }
+                        if (m >= g_end) { flush(); grp++; g_end += gs; gm = 0.f; }
                         gm = fmaxf(gm, res[q]);
                     }
                 }
             }
+            m_next += 4;
+            if (outp) outp += (size_t)4 * A.ld_out;
         }
-        flush();
+        if (A.gmax && my_tiles > 0) flush();
     } else if (warp == 4) {
         // ===== MMA issuer.  Per tile: layer 1 = 3 x (128x64x8), layer 2 = 24 x (128x128x8) =================
         // A 128x128x8 tf32 MMA is only 64 tensor-pipe cycles, so the ISSUE path must stay well under that
         // per instruction: the whole warp runs the (warp-uniform) control flow so descriptors are built on
         // the uniform datapath, only the tcgen05 instructions are predicated on one elected lane, and a
         // descriptor step is a single add on its low word.
-        const uint32_t idesc1 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         const uint32_t idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        for (int i = 0; i < my_tiles; i++) {
+            const int s = i % kTcStages, j = i / kTcStages, t = i % kAccStages, u = i / kAccStages;
+            TRACE(5, i);
+            mbar_wait(FULL(s), j & 1);
+            TRACE(6, i);
+            mbar_wait(TEMPTY(t), (u & 1) ^ 1);
+            TRACE(7, i);
+            tc_fence_after();
+            const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kOpBytes;
+            const uint64_t bd_hi = make_desc(b_hi), bd_lo = make_desc(b_hi + kOpBytes);
+            const uint32_t d = tmem + (uint32_t)(t * 128);
+            if (elect_one()) {
+                // small terms first: W2lo*h1hi, W2hi*h1lo, then W2hi*h1hi.  K step kk: 8 TMEM columns of W2,
+                // 32 bytes inside the 128B-swizzled row (second K block 16 KB further) of h1.
+#pragma unroll
+                for (int term = 0; term < MGAR_TC_TERMS; term++) {
+                    const uint32_t a0 = tmem + (term == 0 ? kTmW2Lo : kTmW2Hi);
+                    const uint64_t b0 = term == 1 ? bd_lo : bd_hi;
+#pragma unroll
+                    for (int kk = 0; kk < 8; kk++) {
+                        const uint32_t koff = (uint32_t)((kk >> 2) * 16384 + (kk & 3) * 32);
+                        tc_mma_tf32_ts(d, a0 + (uint32_t)(kk * 8), b0 + (uint64_t)(koff >> 4), idesc2, (term | kk) ? 1u : 0u);
+                    }
+                }
+                tc_commit(EMPTY(s));     // smem stage reusable once these MMAs have read it
+                tc_commit(TFULL(t));     // accumulator ready for the epilogue
+            }
+            __syncwarp();
+            TRACE(8, i);
+        }
+    } else if (warp == 13) {
+        // ===== layer-1 MMA issuer: its own warp, so these three small MMAs (and their barrier round trips)
+        // are off the serial path of the layer-2 issuer; the tensor pipe interleaves the two streams.
+        const uint32_t idesc1 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         const uint64_t w1d_hi = make_desc_k8(w1_hi), w1d_lo = make_desc_k8(w1_lo);
-        // layer 1 of local tile i: D1[pos, ch] = x[pos, 0:8] . W1^T[ch, 0:8] (bias rides in column C0)
-        auto layer1 = [&](int i) {
+        for (int i = 0; i < my_tiles; i++) {
+            // D1[pos, ch] = x[pos, 0:8] . W1^T[ch, 0:8] (the folded bias rides in column C0)
             const int xs = i & 1, jx = i >> 1;
             mbar_wait(XFULL(xs), jx & 1);
             mbar_wait(DEMPTY(xs), (jx & 1) ^ 1);
@@ -349,34 +405,6 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
                 tc_commit(DFULL(xs));
             }
             __syncwarp();
-        };
-        if (my_tiles > 0) layer1(0);
-        for (int i = 0; i < my_tiles; i++) {
-            if (i + 1 < my_tiles) layer1(i + 1);   // issued ahead so the converters overlap layer 2 of tile i
-            const int s = i % kTcStages, j = i / kTcStages, t = i % kAccStages, u = i / kAccStages;
-            mbar_wait(FULL(s), j & 1);
-            mbar_wait(TEMPTY(t), (u & 1) ^ 1);
-            tc_fence_after();
-            const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kOpBytes;
-            const uint64_t bd_hi = make_desc(b_hi), bd_lo = make_desc(b_hi + kOpBytes);
-            const uint32_t d = tmem + (uint32_t)(t * 128);
-            if (elect_one()) {
-                // small terms first: W2lo*h1hi, W2hi*h1lo, then W2hi*h1hi.  K step kk: 8 TMEM columns of W2,
-                // 32 bytes inside the 128B-swizzled row (second K block 16 KB further) of h1.
-#pragma unroll
-                for (int term = 0; term < 3; term++) {
-                    const uint32_t a0 = tmem + (term == 0 ? kTmW2Lo : kTmW2Hi);
-                    const uint64_t b0 = term == 1 ? bd_lo : bd_hi;
-#pragma unroll
-                    for (int kk = 0; kk < 8; kk++) {
-                        const uint32_t koff = (uint32_t)((kk >> 2) * 16384 + (kk & 3) * 32);
-                        tc_mma_tf32_ts(d, a0 + (uint32_t)(kk * 8), b0 + (uint64_t)(koff >> 4), idesc2, (term | kk) ? 1u : 0u);
-                    }
-                }
-                tc_commit(EMPTY(s));     // smem stage reusable once these MMAs have read it
-                tc_commit(TFULL(t));     // accumulator ready for the epilogue
-            }
-            __syncwarp();
         }
     } else {
         // ===== gather + converters (8 warps) =================================================================
@@ -389,6 +417,7 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
         const int pw = warp & 3, half = (warp - 5) >> 2;
         const int r = pw * 32 + lane;
 
+        int u_cloud = A.uniform ? (t_beg * 4 + pw) / A.m_u : 0, u_end = (u_cloud + 1) * A.m_u;   // one division, then incremental
         auto load_idx = [&](int i, int &iv, int &em) {          // local tile i -> this lane's sample index
             const int m = (t_beg + i) * 4 + pw;
             iv = -1; em = 0;
@@ -404,8 +433,12 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
             live = (i < my_tiles) && (m < M) && first >= 0 && !em;
             if (live) {
                 long long start;
-                if (A.uniform) start = (long long)(m / A.m_u) * A.n_u;
-                else start = __ldg(A.pre_xyz + find_batch_tc(A.pre_new, A.B, m));
+                if (A.uniform) {
+                    while (m >= u_end) { u_cloud++; u_end += A.m_u; }     // tiles arrive in increasing order
+                    start = (long long)u_cloud * A.n_u;
+                } else {
+                    start = __ldg(A.pre_xyz + find_batch_tc(A.pre_new, A.B, m));
+                }
                 const long long p = start + (iv < 0 ? 0 : iv);
                 if (C0 == 4 && A.packed4) {
                     const float4 t4 = __ldg(reinterpret_cast<const float4 *>(A.xyz + p * 4));
@@ -459,16 +492,24 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
                 load_idx(i + 3, iv_a, em_a);                    // indices three tiles ahead
             }
             const int xs = i & 1, jx = i >> 1, s = i % kTcStages, j = i / kTcStages;
+            if (warp == 8) TRACE(9, i);
             mbar_wait(DFULL(xs), jx & 1);
+            if (warp == 8) TRACE(10, i);
             tc_fence_after();
             uint32_t h[32];
+#ifndef MGAR_TC_NOLDTM
             tc_ld32(tmem + ((uint32_t)(pw * 32) << 16) + kTmD1 + (uint32_t)(xs * 64 + half * 32), h);
             tc_wait_ld();
+#else
+            for (int q = 0; q < 32; q++) h[q] = 0x3f800000u + q + i;
+#endif
             tc_fence_before();
             mbar_arrive_relaxed(DEMPTY(xs));
 
             const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kOpBytes, b_lo = b_hi + kOpBytes;
+            if (warp == 8) TRACE(11, i);
             mbar_wait(EMPTY(s), (j & 1) ^ 1);
+            if (warp == 8) TRACE(12, i);
 #pragma unroll
             for (int c8 = 0; c8 < 8; c8++) {
                 float y[4];
@@ -479,6 +520,7 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
             }
             fence_async_smem();          // generic-proxy stores -> visible to the tensor core (async proxy)
             mbar_arrive(FULL(s));
+            if (warp == 8) TRACE(13, i);
         }
     }
 
@@ -542,17 +584,39 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     A.gmax = group_max; A.group_size = group_size > 0 ? group_size : 1; A.group_zero = group_zero;
     A.packed4 = (C0 == 4 && xyz_stride == 4 && feat_stride == 4 && features == xyz + 3 &&
                  (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) ? 1 : 0;
+#ifdef MGAR_TC_TRACE
+    static long long *d_trace = nullptr;
+    if (!d_trace) MGAR_CUDA(cudaMalloc(&d_trace, 32 * 16 * sizeof(long long)));
+    MGAR_CUDA(cudaMemsetAsync(d_trace, 0, 32 * 16 * sizeof(long long), st));
+    A.trace = d_trace;
+#endif
     if (group_max) {
         const size_t groups = ((size_t)M + A.group_size - 1) / A.group_size;
         MGAR_CUDA(cudaMemsetAsync(group_max, 0, groups * kTcC2 * sizeof(float), st));
     }
     const int n_tiles = (M + 3) / 4;
     const int grid = n_tiles < kNumSMs ? n_tiles : kNumSMs;     // persistent: one CTA per SM
+#ifdef MGAR_TC_TRACE
+#define MGAR_TC_TRACE_DUMP                                                                      \
+    {                                                                                           \
+        static long long h[32 * 16];                                                            \
+        cudaStreamSynchronize(st);                                                              \
+        cudaMemcpy(h, d_trace, sizeof(h), cudaMemcpyDeviceToHost);                              \
+        for (int i = 0; i < 32; i++) {                                                          \
+            fprintf(stderr, "tctrace %d", 100 + i);                                             \
+            for (int q = 0; q < 15; q++) fprintf(stderr, " %lld", h[i * 16 + q] ? h[i * 16 + q] - h[5] : -1); \
+            fprintf(stderr, "\n");                                                              \
+        }                                                                                       \
+    }
+#else
+#define MGAR_TC_TRACE_DUMP
+#endif
 #define MGAR_TC_CASE(c0)                                                                                        \
     if (C0 == c0) {                                                                                             \
         MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc_kernel<c0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmem)); \
         sa_mlp_tc_kernel<c0><<<grid, kTcThreads, kTcSmem, st>>>(L1, A);                                         \
         count_launch();                                                                                         \
+        MGAR_TC_TRACE_DUMP                                                                                      \
         return check_launch("sa_mlp_tc");                                                                       \
     }
     MGAR_TC_CASE(3) MGAR_TC_CASE(4) MGAR_TC_CASE(5) MGAR_TC_CASE(6) MGAR_TC_CASE(7)

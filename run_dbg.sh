@@ -1,8 +1,5 @@
 #!/bin/bash
 cd "$GRAFT_REPO_ROOT" || exit 1
 mkdir -p gpurun_out
-for d in 0 2 16 18 22; do
-MGAR_TC_DBG=$d timeout 300 python bench.py --steps 5 --warmup 2 --no-cpu-baseline > gpurun_out/bq.json 2> gpurun_out/bench.err
-python -c "
-import json; d=json.load(open('gpurun_out/bq.json')); print('dbg',$d,'sa_mlp ms', d['stages']['sa_mlp']['ms'])"
-done
+timeout 300 python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/bq.json 2> gpurun_out/bench.err
+grep tctrace gpurun_out/bench.err | awk '$3!=-1' | head -32 > gpurun_out/trace.txt; wc -l gpurun_out/trace.txt
