@@ -36,7 +36,7 @@ namespace mgar {
 
 constexpr int kTcC1 = 64, kTcC2 = 128, kTcNS = 32;
 constexpr int kTcTilePos = 128;                 // positions per tile = 4 centroids x 32 samples
-constexpr int kTcThreads = 14 * 32;
+constexpr int kTcThreads = 15 * 32;
 constexpr int kTcStages = 3;                  // shared-memory stages of the h1 operand
 constexpr int kAccStages = 2;                 // TMEM stages of the layer-2 accumulator (128 columns each)
 // TMEM columns: layer-2 accumulators 0,128; layer-1 accumulators 256,320 (64 each); W2 operand hi 384, lo 448
@@ -346,14 +346,17 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
             if (outp) outp += (size_t)4 * A.ld_out;
         }
         if (A.gmax && my_tiles > 0) flush();
-    } else if (warp == 4) {
+    } else if (warp == 4 || warp == 14) {
+        // ===== layer-2 MMA issuers: warp 4 takes the even tiles, warp 14 the odd ones (different TMEM
+        // accumulators and smem stages), so while one of them is between tiles - commits, barrier round
+        // trips - the other keeps the tensor pipe fed.
         // ===== MMA issuer.  Per tile: layer 1 = 3 x (128x64x8), layer 2 = 24 x (128x128x8) =================
         // A 128x128x8 tf32 MMA is only 64 tensor-pipe cycles, so the ISSUE path must stay well under that
         // per instruction: the whole warp runs the (warp-uniform) control flow so descriptors are built on
         // the uniform datapath, only the tcgen05 instructions are predicated on one elected lane, and a
         // descriptor step is a single add on its low word.
         const uint32_t idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-        for (int i = 0; i < my_tiles; i++) {
+        for (int i = (warp == 4 ? 0 : 1); i < my_tiles; i += 2) {
             const int s = i % kTcStages, j = i / kTcStages, t = i % kAccStages, u = i / kAccStages;
             TRACE(5, i);
             mbar_wait(FULL(s), j & 1);
