@@ -25,8 +25,9 @@
 
 #include <type_traits>
 
-#include "mgar_common.cuh"
+#include "sa_mlp_tc.cuh"
 #include "stack_prefix.cuh"
+#include "tc_ptx.cuh"
 
 #ifndef MGAR_TC_TERMS
 #define MGAR_TC_TERMS 3   // 3xTF32; timing experiments build with fewer
@@ -34,8 +35,6 @@
 
 namespace mgar {
 
-constexpr int kTcC1 = 64, kTcC2 = 128, kTcNS = 32;
-constexpr int kTcTilePos = 128;                 // positions per tile = 4 centroids x 32 samples
 constexpr int kTcThreads = 15 * 32;
 constexpr int kTcStages = 3;                  // shared-memory stages of the h1 operand
 constexpr int kAccStages = 2;                 // TMEM stages of the layer-2 accumulator (128 columns each)
@@ -46,120 +45,6 @@ constexpr uint32_t kW1Bytes = 64 * 8 * 4;       // W1^T operand, 64 x 8: 2 KB
 constexpr uint32_t kOpBytes = 128 * 64 * 4;     // one 128 x 64 fp32 operand tile: 32 KB
 constexpr uint32_t kTcSmem = kTcStages * 2 * kOpBytes /* h1 hi,lo */ + 2 * 2 * kXBytes /* x hi,lo x2 */ + 2 * kW1Bytes + 1024;
 
-struct TcLayer1 {          // layer-1 parameters travel as kernel arguments (constant bank operands)
-    float w[8][kTcC1];     // [c_in][c_out], BatchNorm scale folded in: w * gamma / sqrt(var + eps)
-    float sh[kTcC1];       // beta - mean * scale
-};
-
-// ---- PTX wrappers -----------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
-}
-// Arrive without release semantics: for barriers that only hand TENSOR MEMORY back to the MMA issuer (the
-// tcgen05 fences order those accesses).  A releasing arrive would also wait for this thread's outstanding
-// global stores / prefetch loads - a full memory round trip per tile.
-__device__ __forceinline__ void mbar_arrive_relaxed(uint32_t bar) {
-    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.relaxed.cta.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-                     "selp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-    } while (!ok);
-}
-__device__ __forceinline__ bool elect_one() {   // one lane of a converged warp; control flow stays warp-uniform
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-    return pred != 0;
-}
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                            uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                 : "r"(taddr) : "memory");
-}
-// keeps the hi/lo split of a 4-vector and stores both halves with 128-bit shared stores
-__device__ __forceinline__ void sts_split4(uint32_t a_hi, uint32_t a_lo, const float (&v)[4]) {
-    float hi[4], lo[4];
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-        hi[q] = __uint_as_float(__float_as_uint(v[q]) & 0xffffe000u);   // truncate to tf32: lo stays exact, 13 bits
-        lo[q] = __fsub_rn(v[q], hi[q]);
-    }
-    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_hi), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
-    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_lo), "f"(lo[0]), "f"(lo[1]), "f"(lo[2]), "f"(lo[3]) : "memory");
-}
-__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
-                                               uint32_t accumulate) {   // A operand read from TMEM
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
-                 ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-__device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t (&v)[32]) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-                 "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-                 "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
-                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
-                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
-                   "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
-                   "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
-                 : "memory");
-}
-__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// hi = tf32(v) (round to nearest by integer arithmetic: cvt.rna.tf32 expands to ~4 instructions),
-// low 13 mantissa bits zero; lo = v - hi (exact in fp32)
-__device__ __forceinline__ void split_tf32(float v, float &hi, float &lo) {
-    hi = __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xffffe000u);
-    lo = __fsub_rn(v, hi);
-}
-
-// Shared-memory matrix descriptor: K-major operand, 128-byte swizzle, rows of 128 B (32 tf32),
-// 8-row atoms 1024 B apart (SBO), descriptor version 1 (sm_100).
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);          // start address       bits [0,14)
-    d |= (uint64_t)1 << 16;                           // leading byte offset bits [16,30) (unused for SW128 K-major)
-    d |= (uint64_t)(1024 >> 4) << 32;                 // stride byte offset  bits [32,46)
-    d |= (uint64_t)1 << 46;                           // version = 1         bits [46,48)
-    d |= (uint64_t)2 << 61;                           // layout SWIZZLE_128B bits [61,64)
-    return d;
-}
-
-// K-major operand with K = 8 tf32 (32 B per row), no swizzle: 8-row x 16-byte core matrices, the two
-// core matrices along K 128 B apart (LBO), 8-row groups 256 B apart (SBO).
-__device__ __forceinline__ uint64_t make_desc_k8(uint32_t saddr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
-    d |= (uint64_t)(128 >> 4) << 16;                  // leading (K) byte offset
-    d |= (uint64_t)(256 >> 4) << 32;                  // stride (M/N) byte offset
-    d |= (uint64_t)1 << 46;                           // version = 1; layout type 0 = no swizzle
-    return d;
-}
-__device__ __forceinline__ uint32_t k8_off(int r, int khalf) { return (uint32_t)((r >> 3) * 256 + khalf * 128 + (r & 7) * 16); }
 
 // byte offset of element (row r, 16-byte chunk c16 of the 64-wide K extent) inside an operand tile
 __device__ __forceinline__ uint32_t tile_off(int r, int c16) {
@@ -167,32 +52,6 @@ __device__ __forceinline__ uint32_t tile_off(int r, int c16) {
     return (uint32_t)(kb * 16384 + (r >> 3) * 1024 + (r & 7) * 128 + ((cw ^ (r & 7)) << 4));
 }
 
-__device__ __forceinline__ int find_batch_tc(const int *__restrict__ pre, int B, int v) {
-    int lo = 0, hi = B;
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (__ldg(pre + mid) <= v) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-
-struct TcArgs {
-    int B, M, C_in;
-    const float *xyz; int xyz_stride;
-    const float *new_xyz;
-    const float *features; int feat_stride;
-    const int *pre_xyz, *pre_new; int uniform, n_u, m_u;
-    const int *idx;
-    const unsigned char *empty_mask;
-    const float *w2t /* [64][128] */, *sc2, *sh2;
-    float *out; int ld_out;              // (M, 128) SA features, may be null
-    float *gmax; int group_size;         // (ceil(M / group_size), 128) max over each group of centroids, may be null
-    const int *group_zero;               // per group: non-zero -> the group's row stays zero (empty person)
-#ifdef MGAR_TC_TRACE
-    long long *trace;                    // timeline stamps of CTA 0, tiles 100..131 (debug build only)
-#endif
-    int packed4;                         // xyz/features are columns 0..2 / 3 of one 16B-aligned (N,4) array
-};
 
 template <int C0>
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -599,6 +458,12 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     }
     const int n_tiles = (M + 3) / 4;
     const int grid = n_tiles < kNumSMs ? n_tiles : kNumSMs;     // persistent: one CTA per SM
+#ifndef MGAR_TC_TRACE
+    {   // default: the fp16-split kernel (same accuracy, half the tensor cycles); MGAR_TC_MODE=tf32 keeps 3xTF32
+        const char *mode = getenv("MGAR_TC_MODE");
+        if (!(mode && mode[0] == 't')) return sa_mlp_tc16_launch(L1, A, C0, grid, st);
+    }
+#endif
 #ifdef MGAR_TC_TRACE
 #define MGAR_TC_TRACE_DUMP                                                                      \
     {                                                                                           \

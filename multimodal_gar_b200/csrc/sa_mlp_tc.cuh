@@ -1,0 +1,39 @@
+// Argument blocks shared by the tensor-core SA-MLP kernels (sa_mlp_tc.cu: 3xTF32, sa_mlp_tc16.cu: 3xFP16).
+#pragma once
+#include "mgar_common.cuh"
+
+namespace mgar {
+
+constexpr int kTcC1 = 64, kTcC2 = 128, kTcNS = 32;
+constexpr int kTcTilePos = 128;                 // positions per tile = 4 centroids x 32 samples
+
+struct TcLayer1 {          // layer-1 parameters travel as kernel arguments (constant bank operands)
+    float w[8][kTcC1];     // [c_in][c_out], BatchNorm scale folded in: w * gamma / sqrt(var + eps)
+    float sh[kTcC1];       // beta - mean * scale
+};
+// bound of |layer-1 pre-activation| used by the fp16 kernel to scale a centroid into the fp16 range:
+// |z1[k]| <= sum_c wmax[c] * |x[c]| + shmax
+struct TcBound { float wmax[8]; float shmax; };
+
+struct TcArgs {
+    int B, M, C_in;
+    const float *xyz; int xyz_stride;
+    const float *new_xyz;
+    const float *features; int feat_stride;
+    const int *pre_xyz, *pre_new; int uniform, n_u, m_u;
+    const int *idx;
+    const unsigned char *empty_mask;
+    const float *w2t /* [64][128] */, *sc2, *sh2;
+    float *out; int ld_out;              // (M, 128) SA features, may be null
+    float *gmax; int group_size;         // (ceil(M / group_size), 128) max over each group of centroids, may be null
+    const int *group_zero;               // per group: non-zero -> the group's row stays zero (empty person)
+#ifdef MGAR_TC_TRACE
+    long long *trace;                    // timeline stamps of CTA 0, tiles 100..131 (debug build only)
+#endif
+    int packed4;                         // xyz/features are columns 0..2 / 3 of one 16B-aligned (N,4) array
+};
+
+// sa_mlp_tc16.cu: the 3xFP16 kernel (default); sa_mlp_tc.cu keeps the 3xTF32 kernel (MGAR_TC_MODE=tf32)
+int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);
+
+}  // namespace mgar

@@ -1,0 +1,439 @@
+// Set-abstraction shared MLP on tcgen05 with FP16 operand splitting ("3xFP16"): same contract and the same
+// fp32-level accuracy as sa_mlp_tc.cu (3xTF32), at twice the tensor rate.
+//
+// Reference: StackSAModuleMSG.forward (pointnet2_stack/pointnet2_modules.py:78-112) after
+// QueryAndGroup (pointnet2_utils.py:123-159); shape [3 + C_in, 64, 128], nsample 32, max-pool.
+//
+// The 3xTF32 kernel runs with the tensor pipe 97 % busy (profiles/r01_full_summary_3xtf32.md), so the only
+// way down is fewer tensor cycles per tile.  kind::f16 moves 128x128x16 per instruction in the time
+// kind::tf32 moves 128x128x8, and an fp16 significand (11 bits) is as wide as a tf32 one, so
+//     v = hi + lo,  hi = fp16(v), lo = fp16(v - hi)        W.h ~ Wlo.hhi + Whi.hlo + Whi.hhi
+// carries the same 22 bits per operand as the tf32 split: 12 MMAs of 128x128x16 per tile instead of 24 of
+// 128x128x8.  What fp16 lacks is exponent range, so both operands are moved into it with EXACT
+// power-of-two scales that are undone in the epilogue:
+//   * W2 row c (an output channel) is multiplied by 2^ec so that its largest entry sits in [2^13, 2^14), and by
+//     sign(scale2[c]) so that BatchNorm's affine is non-decreasing in the accumulator: the epilogue then takes
+//     the max over the 32 samples FIRST (one FMNMX per value) and applies scale/shift once per centroid.
+//     fl(a*max(D)+b) == max(fl(a*D+b)) for a >= 0 because rounding is monotone, so nothing changes numerically.
+//   * every centroid (32 positions = one gather warp) gets 2^-e from an a-priori bound of its layer-1 outputs,
+//     |z1[k]| <= sum_c wmax[c]*|x[c]| + shmax, reduced over the warp with one REDUX; the layer-1 input rows
+//     (and the bias column) are multiplied by it, so h1 leaves layer 1 already inside [0, 2^15).  Entries
+//     more than 2^18 below the bound lose bits only below 2^-40 of it.
+// Layer 1 itself stays 3xTF32 (K = 8, three small MMAs).
+//
+// Warp roles, barriers and the software pipeline are those of sa_mlp_tc.cu:
+//   warps 0-3 epilogue | 4, 14 layer-2 issue (even / odd tiles) | 13 layer-1 issue |
+//   warps 5-8 / 9-12 gather + convert of the even / odd tiles (a tile's whole serial chain belongs to one group)
+#include <cuda_fp16.h>
+#include <stdlib.h>
+
+#include "sa_mlp_tc.cuh"
+#include "stack_prefix.cuh"
+#include "tc_ptx.cuh"
+
+namespace mgar {
+
+namespace {
+
+constexpr int kThreads = 15 * 32;
+constexpr int kStages = 4;                      // shared-memory stages of the h1 operand (hi + lo = 32 KB each)
+constexpr int kAcc = 2;                         // TMEM stages of the layer-2 accumulator (128 columns each)
+// TMEM columns: layer-2 accumulators 0,128; layer-1 accumulators 256,320 (64 each); W2 fp16 hi 384, lo 416 (32 each)
+constexpr uint32_t kTmD1 = 256, kTmW2Hi = 384, kTmW2Lo = 416;
+constexpr uint32_t kXBytes = 128 * 8 * 4;       // one 128 x 8 fp32 layer-1 input tile (no swizzle): 4 KB
+constexpr uint32_t kW1Bytes = 64 * 8 * 4;       // W1^T operand, 64 x 8: 2 KB
+constexpr uint32_t kHBytes = 128 * 64 * 2;      // one 128 x 64 fp16 operand tile (one 128-byte swizzled row per position): 16 KB
+constexpr uint32_t kSmem = kStages * 2 * kHBytes + 2 * 2 * kXBytes + 2 * kW1Bytes + 1024;
+constexpr int kRing = 16;                       // per-centroid scale ring (gather runs at most ~9 tiles ahead of the epilogue)
+
+__device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate) {   // fp16 operands, A read from TMEM
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// (a, b) -> packed fp16 pair of the rounded values (a in the low half) and of the remainders
+__device__ __forceinline__ void split_h2(float a, float b, uint32_t &hi, uint32_t &lo) {
+    const __half2 h = __floats2half2_rn(a, b);
+    const float2 f = __half22float2(h);
+    const __half2 l = __floats2half2_rn(__fsub_rn(a, f.x), __fsub_rn(b, f.y));
+    hi = *reinterpret_cast<const uint32_t *>(&h);
+    lo = *reinterpret_cast<const uint32_t *>(&l);
+}
+
+// byte offset of 16-byte chunk c16 (8 fp16 = channels 8*c16 .. 8*c16+7) of position row r in an h1 tile
+__device__ __forceinline__ uint32_t h_off(int r, int c16) {
+    return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c16 ^ (r & 7)) << 4));
+}
+
+__device__ __forceinline__ float max32(const uint32_t (&v)[32]) {
+    float a[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) a[q] = fmaxf(__uint_as_float(v[q]), __uint_as_float(v[q + 4]));
+#pragma unroll
+    for (int s = 8; s < 32; s += 8) {
+#pragma unroll
+        for (int q = 0; q < 4; q++) a[q] = fmaxf(a[q], fmaxf(__uint_as_float(v[s + q]), __uint_as_float(v[s + q + 4])));
+    }
+    return fmaxf(fmaxf(a[0], a[1]), fmaxf(a[2], a[3]));
+}
+
+template <int C0>
+__global__ void __launch_bounds__(kThreads, 1)
+sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcBound BD, const __grid_constant__ TcArgs A) {
+    static_assert(C0 >= 3 && C0 <= 7, "layer-1 K is padded to 8 with one column for the folded bias");
+    extern __shared__ uint8_t smem_raw[];
+    // full[4] empty[4] | tfull[2] tempty[2] | xfull[2] xempty[2] | dfull[2] dempty[2]
+    __shared__ __align__(8) uint64_t s_bar[2 * kStages + 12];
+    __shared__ __align__(16) float s_inv[kRing][4];     // 2^e of the four centroids of tile (i mod kRing)
+    __shared__ uint32_t s_tmem;
+
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024 B alignment
+    const uint32_t b_stage0 = base;                                 // h1 stage s: hi at +s*2*kHBytes, lo at +kHBytes more
+    const uint32_t x_stage0 = base + kStages * 2 * kHBytes;         // x stage: hi at +xs*2*kXBytes, lo at +kXBytes more
+    const uint32_t w1_hi = x_stage0 + 2 * 2 * kXBytes, w1_lo = w1_hi + kW1Bytes;
+    const uint32_t bar0 = smem_u32(s_bar);
+    auto FULL = [&](int s) { return bar0 + 8u * s; };
+    auto EMPTY = [&](int s) { return bar0 + 8u * (kStages + s); };
+    auto TFULL = [&](int t) { return bar0 + 8u * (2 * kStages + t); };
+    auto TEMPTY = [&](int t) { return bar0 + 8u * (2 * kStages + 2 + t); };
+    auto XFULL = [&](int x) { return bar0 + 8u * (2 * kStages + 4 + x); };
+    auto XEMPTY = [&](int x) { return bar0 + 8u * (2 * kStages + 6 + x); };
+    auto DFULL = [&](int x) { return bar0 + 8u * (2 * kStages + 8 + x); };
+    auto DEMPTY = [&](int x) { return bar0 + 8u * (2 * kStages + 10 + x); };
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int M = A.M;
+    const int n_tiles = (M + 3) >> 2;
+    // contiguous tile range per CTA: consecutive tiles belong to the same person, so the running
+    // group max of the epilogue is flushed only a handful of times
+    const int t_beg = (int)((long long)blockIdx.x * n_tiles / gridDim.x);
+    const int t_end = (int)((long long)(blockIdx.x + 1) * n_tiles / gridDim.x);
+    const int my_tiles = t_end - t_beg;
+
+    // ---- one-time setup: barriers, TMEM, weight operands ---------------------------------------------
+    if (tid == 0) {
+        for (int s = 0; s < kStages; s++) { mbar_init(FULL(s), 128); mbar_init(EMPTY(s), 1); }
+        for (int t = 0; t < kAcc; t++) { mbar_init(TFULL(t), 1); mbar_init(TEMPTY(t), 128); }
+        for (int x = 0; x < 2; x++) {
+            mbar_init(XFULL(x), 128); mbar_init(XEMPTY(x), 1);
+            mbar_init(DFULL(x), 1); mbar_init(DEMPTY(x), 128);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // W1^T (64 channels x K=8: C0 folded weights, the folded BatchNorm shift in column C0, zeros) as the
+    // B operand of the layer-1 MMA, tf32 hi/lo split, no-swizzle K-major
+    if (tid >= 160 && tid < 224) {
+        const int ch = tid - 160;
+        float k0[4], k1[4];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const float v = k < C0 ? L1.w[k][ch] : (k == C0 ? L1.sh[ch] : 0.f);
+            if (k < 4) k0[k] = v; else k1[k - 4] = v;
+        }
+        sts_split4(w1_hi + k8_off(ch, 0), w1_lo + k8_off(ch, 0), k0);
+        sts_split4(w1_hi + k8_off(ch, 1), w1_lo + k8_off(ch, 1), k1);
+        fence_async_smem();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+    // W2 lives in TENSOR MEMORY as the A operand of the layer-2 MMA (lane = output channel; a 32-bit column
+    // holds the fp16 pair k = 2j, 2j+1), scaled into the fp16 range and sign-aligned with scale2 (see header).
+    float asc = 0.f, shift = 0.f;        // epilogue: |scale2| * 2^-ec and shift2 of this thread's channel
+    if (warp < 4) {
+        const int c = tid;
+        const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+        const float sc = __ldg(A.sc2 + c);
+        shift = __ldg(A.sh2 + c);
+        float w[kTcC1], amax = 0.f;
+#pragma unroll
+        for (int k = 0; k < kTcC1; k++) { w[k] = __ldg(A.w2t + (size_t)k * kTcC2 + c); amax = fmaxf(amax, fabsf(w[k])); }
+        int eb = (int)(__float_as_uint(amax) >> 23);
+        eb = eb < 14 ? 14 : eb;                                               // (all-zero / denormal rows: any scale works)
+        const float up = __uint_as_float((uint32_t)(267 - eb) << 23);        // 2^(13 - floor(log2 amax))
+        const float down = __uint_as_float((uint32_t)(eb - 13) << 23);       // its inverse
+        const float sup = sc < 0.f ? -up : up;
+        asc = __fmul_rn(fabsf(sc), down);
+        uint32_t hi[32], lo[32];
+#pragma unroll
+        for (int j = 0; j < 32; j++) split_h2(__fmul_rn(w[2 * j], sup), __fmul_rn(w[2 * j + 1], sup), hi[j], lo[j]);
+        tc_st32(lane_base + kTmW2Hi, hi);
+        tc_st32(lane_base + kTmW2Lo, lo);
+        tc_wait_st();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+
+    if (warp < 4) {
+        // ===== epilogue: thread = output channel, 32 consecutive TMEM columns = one centroid ==========
+        const int c = tid;
+        const int gs = A.group_size;
+        int m_next = t_beg * 4;                                   // first centroid of the next tile
+        int grp = A.gmax ? m_next / gs : 0, g_end = (grp + 1) * gs;
+        float gm = 0.f;
+        float *outp = A.out ? A.out + (size_t)m_next * A.ld_out + c : nullptr;
+        auto flush = [&]() {
+            if (!(A.group_zero && __ldg(A.group_zero + grp)))
+                atomicMax(reinterpret_cast<int *>(A.gmax + (size_t)grp * kTcC2 + c), __float_as_int(gm));
+        };
+        for (int i = 0; i < my_tiles; i++) {
+            const int t = i % kAcc, u = i / kAcc;
+            mbar_wait(TFULL(t), u & 1);
+            tc_fence_after();
+            const float4 inv = *reinterpret_cast<const float4 *>(&s_inv[i % kRing][0]);
+            const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
+            float mx[4];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                uint32_t v0[32], v1[32];
+                tc_ld32(taddr + (2 * h) * 32, v0);
+                tc_ld32(taddr + (2 * h + 1) * 32, v1);
+                tc_wait_ld();
+                mx[2 * h] = max32(v0);
+                mx[2 * h + 1] = max32(v1);
+            }
+            tc_fence_before();
+            mbar_arrive_relaxed(TEMPTY(t));
+            const float sq[4] = {inv.x, inv.y, inv.z, inv.w};
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int m = m_next + q;
+                if (m < M) {
+                    // BatchNorm affine + ReLU of the max over the 32 samples (exact power-of-two rescale)
+                    const float res = fmaxf(__fmaf_rn(mx[q], __fmul_rn(asc, sq[q]), shift), 0.f);
+                    if (outp) outp[(size_t)q * A.ld_out] = res;
+                    if (A.gmax) {
+                        if (m >= g_end) { flush(); grp++; g_end += gs; gm = 0.f; }
+                        gm = fmaxf(gm, res);
+                    }
+                }
+            }
+            m_next += 4;
+            if (outp) outp += (size_t)4 * A.ld_out;
+        }
+        if (A.gmax && my_tiles > 0) flush();
+    } else if (warp == 4 || warp == 14) {
+        // ===== layer-2 MMA issuers: warp 4 takes the even tiles, warp 14 the odd ones.  Per tile 12 x (128x128x16):
+        // small terms first (W2lo*h1hi, W2hi*h1lo), then W2hi*h1hi.  K step kk: 8 TMEM columns of W2, 32 bytes
+        // inside the 128B-swizzled row of h1.  The whole warp runs the warp-uniform control flow; only the
+        // tcgen05 instructions are predicated on one elected lane.
+        const uint32_t idesc2 = (1u << 4) /* D fp32 */ | (0u << 7) /* A fp16 */ | (0u << 10) /* B fp16 */ |
+                                ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        for (int i = (warp == 4 ? 0 : 1); i < my_tiles; i += 2) {
+            const int s = i % kStages, j = i / kStages, t = i % kAcc, u = i / kAcc;
+            mbar_wait(FULL(s), j & 1);
+            mbar_wait(TEMPTY(t), (u & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kHBytes;
+            const uint64_t bd_hi = make_desc(b_hi), bd_lo = make_desc(b_hi + kHBytes);
+            const uint32_t d = tmem + (uint32_t)(t * 128);
+            if (elect_one()) {
+#pragma unroll
+                for (int term = 0; term < 3; term++) {
+                    const uint32_t a0 = tmem + (term == 0 ? kTmW2Lo : kTmW2Hi);
+                    const uint64_t b0 = term == 1 ? bd_lo : bd_hi;
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++)
+                        tc_mma_f16_ts(d, a0 + (uint32_t)(kk * 8), b0 + (uint64_t)((kk * 32) >> 4), idesc2, (term | kk) ? 1u : 0u);
+                }
+                tc_commit(EMPTY(s));     // smem stage reusable once these MMAs have read it
+                tc_commit(TFULL(t));     // accumulator ready for the epilogue
+            }
+            __syncwarp();
+        }
+    } else if (warp == 13) {
+        // ===== layer-1 MMA issuer (3xTF32, K = 8): D1[pos, ch] = x[pos, 0:8] . W1^T[ch, 0:8] ===================
+        const uint32_t idesc1 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint64_t w1d_hi = make_desc_k8(w1_hi), w1d_lo = make_desc_k8(w1_lo);
+        for (int i = 0; i < my_tiles; i++) {
+            const int xs = i & 1, jx = i >> 1;
+            mbar_wait(XFULL(xs), jx & 1);
+            mbar_wait(DEMPTY(xs), (jx & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t x_hi = x_stage0 + (uint32_t)xs * 2 * kXBytes;
+            const uint64_t xd_hi = make_desc_k8(x_hi), xd_lo = make_desc_k8(x_hi + kXBytes);
+            const uint32_t d1 = tmem + kTmD1 + (uint32_t)(xs * 64);
+            if (elect_one()) {
+                tc_mma_tf32(d1, xd_lo, w1d_hi, idesc1, 0);
+                tc_mma_tf32(d1, xd_hi, w1d_lo, idesc1, 1);
+                tc_mma_tf32(d1, xd_hi, w1d_hi, idesc1, 1);
+                tc_commit(XEMPTY(xs));
+                tc_commit(DFULL(xs));
+            }
+            __syncwarp();
+        }
+    } else {
+        // ===== gather + converters: two groups of four warps, group g owns the tiles i = g (mod 2) ===========
+        // warp = (group g, position block pw = one centroid = one TMEM lane quarter).  A group has two tile
+        // periods per tile of its own, so the serial chain of a tile (TMEM load -> convert -> swizzled store)
+        // is off the critical path of the tensor pipe.  Per own tile i:
+        //   (a) gather (xyz - centre | feat) of tile i+2, derive the centroid's power-of-two scale, split hi/lo
+        //       (tf32) and store the 128 x 8 layer-1 input tile (bias column = the scale) into x stage g; the
+        //       gather itself is software-pipelined two more own tiles ahead in registers;
+        //   (b) read the position's 64 layer-1 outputs back from TMEM (D1 stage g), ReLU, split into fp16
+        //       hi/lo and store the 128B-swizzled K-major h1 operand of the layer-2 MMA.
+        const int pw = warp & 3, g = (warp - 5) >> 2;
+        const int r = pw * 32 + lane;
+
+        int u_cloud = A.uniform ? (t_beg * 4 + pw) / A.m_u : 0, u_end = (u_cloud + 1) * A.m_u;
+        auto load_idx = [&](int i, int &iv, int &em) {          // local tile i -> this lane's sample index
+            const int m = (t_beg + i) * 4 + pw;
+            iv = -1; em = 0;
+            if (i < my_tiles && m < M) {
+                iv = __ldg(A.idx + (size_t)m * kTcNS + lane);
+                if (A.empty_mask) em = A.empty_mask[m];
+            }
+        };
+        auto load_pt = [&](int i, int iv, int em, float (&v)[C0], float (&q)[3], bool &live) {
+            const int m = (t_beg + i) * 4 + pw;
+            const int first = __shfl_sync(0xffffffffu, iv, 0);
+            live = (i < my_tiles) && (m < M) && first >= 0 && !em;
+            if (live) {
+                long long start;
+                if (A.uniform) {
+                    while (m >= u_end) { u_cloud++; u_end += A.m_u; }     // tiles arrive in increasing order
+                    start = (long long)u_cloud * A.n_u;
+                } else {
+                    start = __ldg(A.pre_xyz + find_batch_tc(A.pre_new, A.B, m));
+                }
+                const long long p = start + (iv < 0 ? 0 : iv);
+                if (C0 == 4 && A.packed4) {
+                    const float4 t4 = __ldg(reinterpret_cast<const float4 *>(A.xyz + p * 4));
+                    v[0] = t4.x; v[1] = t4.y; v[2] = t4.z; v[C0 - 1] = t4.w;
+                } else {
+                    v[0] = __ldg(A.xyz + p * A.xyz_stride + 0);
+                    v[1] = __ldg(A.xyz + p * A.xyz_stride + 1);
+                    v[2] = __ldg(A.xyz + p * A.xyz_stride + 2);
+#pragma unroll
+                    for (int cc = 3; cc < C0; cc++) v[cc] = __ldg(A.features + p * A.feat_stride + (cc - 3));
+                }
+                q[0] = __ldg(A.new_xyz + (size_t)m * 3 + 0);
+                q[1] = __ldg(A.new_xyz + (size_t)m * 3 + 1);
+                q[2] = __ldg(A.new_xyz + (size_t)m * 3 + 2);
+            }
+        };
+        // layer-1 input row of local tile i -> x stage i & 1, scaled by the centroid's 2^-e
+        auto store_x = [&](int i, const float (&v)[C0], const float (&q)[3], bool live) {
+            const int xs = i & 1, jx = i >> 1;               // xs == g for this group's tiles
+            float x[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (live) {
+                x[0] = __fsub_rn(v[0], q[0]); x[1] = __fsub_rn(v[1], q[1]); x[2] = __fsub_rn(v[2], q[2]);
+#pragma unroll
+                for (int cc = 3; cc < C0; cc++) x[cc] = v[cc];
+            }
+            float bound = BD.shmax;
+#pragma unroll
+            for (int cc = 0; cc < C0; cc++) bound = __fmaf_rn(BD.wmax[cc], fabsf(x[cc]), bound);
+            // bound >= 0: the bit patterns order like the values.  bound < 2^(eb - 126); 2^(141 - eb) puts it below 2^15.
+            int eb = (int)(__reduce_max_sync(0xffffffffu, __float_as_uint(bound)) >> 23);
+            eb = eb < 15 ? 15 : (eb > 254 ? 254 : eb);
+            const float down = __uint_as_float((uint32_t)(268 - eb) << 23);    // 2^(141 - eb)
+            const float up = __uint_as_float((uint32_t)(eb - 14) << 23);       // 2^(eb - 141)
+#pragma unroll
+            for (int cc = 0; cc < C0; cc++) x[cc] = __fmul_rn(x[cc], down);
+            x[C0] = down;                                        // multiplies the folded BatchNorm shift
+            const float k0[4] = {x[0], x[1], x[2], x[3]}, k1[4] = {x[4], x[5], x[6], x[7]};
+            const uint32_t x_hi = x_stage0 + (uint32_t)xs * 2 * kXBytes, x_lo = x_hi + kXBytes;
+            mbar_wait(XEMPTY(xs), (jx & 1) ^ 1);
+            sts_split4(x_hi + k8_off(r, 0), x_lo + k8_off(r, 0), k0);
+            sts_split4(x_hi + k8_off(r, 1), x_lo + k8_off(r, 1), k1);
+            if (lane == 0) s_inv[i % kRing][pw] = up;
+            fence_async_smem();
+            mbar_arrive(XFULL(xs));
+        };
+
+        int iv_a = -1, em_a = 0, iv_b = -1, em_b = 0;
+        float vb[C0], qb[3];
+        bool live_b = false;
+        load_idx(g, iv_b, em_b);
+        load_pt(g, iv_b, em_b, vb, qb, live_b);
+        load_idx(g + 2, iv_b, em_b);
+        load_idx(g + 4, iv_a, em_a);
+        if (g < my_tiles) store_x(g, vb, qb, live_b);
+        load_pt(g + 2, iv_b, em_b, vb, qb, live_b);
+        for (int i = g, k = 0; i < my_tiles; i += 2, k++) {
+            if (i + 2 < my_tiles) {
+                store_x(i + 2, vb, qb, live_b);                 // gathered during the previous iteration
+                iv_b = iv_a; em_b = em_a;
+                load_pt(i + 4, iv_b, em_b, vb, qb, live_b);     // points two own tiles ahead
+                load_idx(i + 6, iv_a, em_a);                    // indices three own tiles ahead
+            }
+            const int s = i % kStages, j = i / kStages;
+            mbar_wait(DFULL(g), k & 1);
+            tc_fence_after();
+            uint32_t h0[32], h1[32];
+            const uint32_t d1 = tmem + ((uint32_t)(pw * 32) << 16) + kTmD1 + (uint32_t)(g * 64);
+            tc_ld32(d1, h0);
+            tc_ld32(d1 + 32, h1);
+            tc_wait_ld();
+            tc_fence_before();
+            mbar_arrive_relaxed(DEMPTY(g));                     // layer 1 of tile i+2 may overwrite D1 now
+
+            const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kHBytes, b_lo = b_hi + kHBytes;
+            uint32_t hi[16], lo[16];
+#pragma unroll
+            for (int p = 0; p < 16; p++)
+                split_h2(fmaxf(__uint_as_float(h0[2 * p]), 0.f), fmaxf(__uint_as_float(h0[2 * p + 1]), 0.f), hi[p], lo[p]);
+            mbar_wait(EMPTY(s), (j & 1) ^ 1);
+#pragma unroll
+            for (int half = 0; half < 2; half++) {
+                if (half == 1) {
+#pragma unroll
+                    for (int p = 0; p < 16; p++)
+                        split_h2(fmaxf(__uint_as_float(h1[2 * p]), 0.f), fmaxf(__uint_as_float(h1[2 * p + 1]), 0.f), hi[p], lo[p]);
+                }
+#pragma unroll
+                for (int c4 = 0; c4 < 4; c4++) {
+                    const uint32_t off = h_off(r, half * 4 + c4);
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(b_hi + off), "r"(hi[4 * c4]), "r"(hi[4 * c4 + 1]),
+                                 "r"(hi[4 * c4 + 2]), "r"(hi[4 * c4 + 3]) : "memory");
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(b_lo + off), "r"(lo[4 * c4]), "r"(lo[4 * c4 + 1]),
+                                 "r"(lo[4 * c4 + 2]), "r"(lo[4 * c4 + 3]) : "memory");
+                }
+            }
+            fence_async_smem();          // generic-proxy stores -> visible to the tensor core (async proxy)
+            mbar_arrive(FULL(s));
+        }
+    }
+
+    // ---- teardown ------------------------------------------------------------------------------------
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+    }
+}
+
+}  // namespace
+
+int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st) {
+    TcBound BD;
+    BD.shmax = 0.f;
+    for (int c = 0; c < 8; c++) BD.wmax[c] = 0.f;
+    for (int o = 0; o < kTcC1; o++) {
+        for (int c = 0; c < C0; c++) BD.wmax[c] = fmaxf(BD.wmax[c], fabsf(L1.w[c][o]));
+        BD.shmax = fmaxf(BD.shmax, fabsf(L1.sh[o]));
+    }
+#define MGAR_TC16_CASE(c0)                                                                                          \
+    if (C0 == c0) {                                                                                                 \
+        MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<c0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem)); \
+        sa_mlp_tc16_kernel<c0><<<grid, kThreads, kSmem, st>>>(L1, BD, A);                                           \
+        count_launch();                                                                                             \
+        return check_launch("sa_mlp_tc16");                                                                         \
+    }
+    MGAR_TC16_CASE(3) MGAR_TC16_CASE(4) MGAR_TC16_CASE(5) MGAR_TC16_CASE(6) MGAR_TC16_CASE(7)
+#undef MGAR_TC16_CASE
+    set_error("sa_mlp_tc16: unsupported C0=%d", C0);
+    return MGAR_EINVAL;
+}
+
+}  // namespace mgar
