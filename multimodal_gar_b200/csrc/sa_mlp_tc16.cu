@@ -53,6 +53,14 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, 
                  ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 
+// ReLU(a), ReLU(b) -> packed fp16 pairs hi, lo (a in the low half) with hi + lo = ReLU(.) to 22 bits.
+// hi is rounded TOWARD ZERO so that the remainder of a positive value is >= 0; cvt's .relu then clamps exactly
+// the negative inputs in both conversions (a < 0: hi = 0, remainder = a < 0, lo = 0) and no FMNMX is needed.
+__device__ __forceinline__ void split_relu_h2(float a, float b, uint32_t &hi, uint32_t &lo) {
+    asm("cvt.rz.relu.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(b), "f"(a));
+    const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&hi));
+    asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(__fsub_rn(b, f.y)), "f"(__fsub_rn(a, f.x)));
+}
 // (a, b) -> packed fp16 pair of the rounded values (a in the low half) and of the remainders
 __device__ __forceinline__ void split_h2(float a, float b, uint32_t &hi, uint32_t &lo) {
     const __half2 h = __floats2half2_rn(a, b);
@@ -67,16 +75,17 @@ __device__ __forceinline__ uint32_t h_off(int r, int c16) {
     return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c16 ^ (r & 7)) << 4));
 }
 
+__device__ __forceinline__ float max3(float a, float b, float c) { return fmaxf(a, fmaxf(b, c)); }   // one FMNMX3
+// max of 32 values in 16 three-input operations (two independent chains)
 __device__ __forceinline__ float max32(const uint32_t (&v)[32]) {
-    float a[4];
+    float a = max3(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]));
+    float b = max3(__uint_as_float(v[3]), __uint_as_float(v[4]), __uint_as_float(v[5]));
 #pragma unroll
-    for (int q = 0; q < 4; q++) a[q] = fmaxf(__uint_as_float(v[q]), __uint_as_float(v[q + 4]));
-#pragma unroll
-    for (int s = 8; s < 32; s += 8) {
-#pragma unroll
-        for (int q = 0; q < 4; q++) a[q] = fmaxf(a[q], fmaxf(__uint_as_float(v[s + q]), __uint_as_float(v[s + q + 4])));
+    for (int s = 6; s < 30; s += 4) {
+        a = max3(a, __uint_as_float(v[s]), __uint_as_float(v[s + 1]));
+        b = max3(b, __uint_as_float(v[s + 2]), __uint_as_float(v[s + 3]));
     }
-    return fmaxf(fmaxf(a[0], a[1]), fmaxf(a[2], a[3]));
+    return max3(a, b, fmaxf(__uint_as_float(v[30]), __uint_as_float(v[31])));
 }
 
 template <int C0>
@@ -203,16 +212,27 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             tc_fence_before();
             mbar_arrive_relaxed(TEMPTY(t));
             const float sq[4] = {inv.x, inv.y, inv.z, inv.w};
+            // BatchNorm affine + ReLU of the max over the 32 samples (exact power-of-two rescale)
+            float res[4];
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const int m = m_next + q;
-                if (m < M) {
-                    // BatchNorm affine + ReLU of the max over the 32 samples (exact power-of-two rescale)
-                    const float res = fmaxf(__fmaf_rn(mx[q], __fmul_rn(asc, sq[q]), shift), 0.f);
-                    if (outp) outp[(size_t)q * A.ld_out] = res;
-                    if (A.gmax) {
-                        if (m >= g_end) { flush(); grp++; g_end += gs; gm = 0.f; }
-                        gm = fmaxf(gm, res);
+            for (int q = 0; q < 4; q++) res[q] = fmaxf(__fmaf_rn(mx[q], __fmul_rn(asc, sq[q]), shift), 0.f);
+            if (m_next + 4 <= M && (!A.gmax || m_next + 4 <= g_end)) {
+                // common case: four real centroids of one group
+                if (outp) {
+#pragma unroll
+                    for (int q = 0; q < 4; q++) outp[(size_t)q * A.ld_out] = res[q];
+                }
+                gm = fmaxf(max3(gm, res[0], res[1]), fmaxf(res[2], res[3]));
+            } else {
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int m = m_next + q;
+                    if (m < M) {
+                        if (outp) outp[(size_t)q * A.ld_out] = res[q];
+                        if (A.gmax) {
+                            if (m >= g_end) { flush(); grp++; g_end += gs; gm = 0.f; }
+                            gm = fmaxf(gm, res[q]);
+                        }
                     }
                 }
             }
@@ -381,14 +401,14 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             uint32_t hi[16], lo[16];
 #pragma unroll
             for (int p = 0; p < 16; p++)
-                split_h2(fmaxf(__uint_as_float(h0[2 * p]), 0.f), fmaxf(__uint_as_float(h0[2 * p + 1]), 0.f), hi[p], lo[p]);
+                split_relu_h2(__uint_as_float(h0[2 * p]), __uint_as_float(h0[2 * p + 1]), hi[p], lo[p]);
             mbar_wait(EMPTY(s), (j & 1) ^ 1);
 #pragma unroll
             for (int half = 0; half < 2; half++) {
                 if (half == 1) {
 #pragma unroll
                     for (int p = 0; p < 16; p++)
-                        split_h2(fmaxf(__uint_as_float(h1[2 * p]), 0.f), fmaxf(__uint_as_float(h1[2 * p + 1]), 0.f), hi[p], lo[p]);
+                        split_relu_h2(__uint_as_float(h1[2 * p]), __uint_as_float(h1[2 * p + 1]), hi[p], lo[p]);
                 }
 #pragma unroll
                 for (int c4 = 0; c4 < 4; c4++) {
