@@ -96,9 +96,9 @@ fps_reg_kernel(const float *__restrict__ xyz, int xs, float *__restrict__ temp, 
         pt[i] = valid ? (temp ? temp[k] : 1e10f) : -1.f;  // -1 never beats the reference's initial best = -1 either
     }
 
-    int cur = 0;
+    int cur = 0, j = 1;
     if (tid == 0) idxs[0] = base;
-    for (int j = 1; j < m; j++) {
+    for (; j < m; j++) {
         const float cx = sxyz[cur * 3 + 0], cy = sxyz[cur * 3 + 1], cz = sxyz[cur * 3 + 2];
         float best = -1.f;
         int bslot = 0;
@@ -130,9 +130,11 @@ fps_reg_kernel(const float *__restrict__ xyz, int xs, float *__restrict__ temp, 
                 rmin = __reduce_min_sync(0xffffffffu, v == vmax ? r : INT_MAX);
             }
         }
+        if (vmax == 0) break;   // block-uniform: every point coincides with a sample, the winner is index 0 from here on
         cur = rank_to_index(rmin, L, SH);
         if (tid == 0) idxs[j] = cur + base;
     }
+    for (int q = j + tid; q < m; q += W * 32) idxs[q] = base;
     // the reference leaves the final min-distances in temp (caller scratch): keep that contract
 #pragma unroll
     for (int i = 0; i < PPL; i++) {
@@ -146,6 +148,111 @@ fps_reg_kernel(const float *__restrict__ xyz, int xs, float *__restrict__ temp, 
             new_xyz[j * 3 + 0] = sxyz[k * 3 + 0];
             new_xyz[j * 3 + 1] = sxyz[k * 3 + 1];
             new_xyz[j * 3 + 2] = sxyz[k * 3 + 2];
+        }
+    }
+}
+
+// ---- one WARP per cloud (rank space <= 512): no block barrier, no shared-memory exchange ---------------------
+// Each lane owns P consecutive ranks.  A round is: distance + running minimum per owned point (7 flops), a
+// binary max tree over the lane's P minima (P-1 FMNMX, the tree is kept), one REDUX for the warp maximum, a
+// first-match DESCENT of the kept tree (P-1-log2 P selects: the winner lane's first slot holding the maximum, i.e.
+// the reference's tie order inside the lane) and one REDUX for the smallest winning rank.  ~10 instructions per
+// point and round instead of ~20 for the four-warp geometry with per-element argmax tracking.
+// Once the maximum is +0 every point coincides with a sampled one (pooled clouds wrap their points):
+// the reference keeps returning index 0 from then on, so the remaining indices are 0 and the rounds stop.
+template <int N>
+__device__ __forceinline__ float pick_pow2(const float *v, int p) {   // v[p], p in [0, N), v in registers
+    if constexpr (N == 1) {
+        return v[0];
+    } else {
+        const float lo = pick_pow2<N / 2>(v, p), hi = pick_pow2<N / 2>(v + N / 2, p);
+        return (p & (N / 2)) ? hi : lo;
+    }
+}
+
+template <int P, int LEV>
+__device__ __forceinline__ int descend(const float (&t)[2 * P], int vmax, int p) {
+    if constexpr ((1 << LEV) > P) {
+        return p;
+    } else {
+        constexpr int H = 1 << (LEV - 1);      // nodes of level LEV-1 = left children of level LEV
+        float ev[H];
+#pragma unroll
+        for (int q = 0; q < H; q++) ev[q] = t[(1 << LEV) + 2 * q];
+        const float left = pick_pow2<H>(ev, p);
+        return descend<P, LEV + 1>(t, vmax, 2 * p + (__float_as_int(left) != vmax ? 1 : 0));
+    }
+}
+
+constexpr int kFpsWarpsPerCta = 2;
+
+template <int P>
+__global__ void __launch_bounds__(kFpsWarpsPerCta * 32, 9)   // 18 warps / SM: the 2560 clouds of a 64-frame step are one wave
+fps_warp_kernel(const float *__restrict__ xyz, int xs, float *__restrict__ temp, int *__restrict__ idxs,
+                float *__restrict__ new_xyz, int b, int n, int m, int L, int SH, int f4_per_warp) {
+    extern __shared__ float4 fps_sm4[];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int cloud = blockIdx.x * kFpsWarpsPerCta + w;
+    if (cloud >= b) return;                         // warps are independent: no block-level barrier below
+    float4 *sp = fps_sm4 + (size_t)w * f4_per_warp;  // [n] staged cloud, then [m] sampled indices
+    int *sidx = reinterpret_cast<int *>(sp + n);
+    xyz += (size_t)cloud * n * xs; idxs += (size_t)cloud * m;
+    if (temp) temp += (size_t)cloud * n;
+    if (new_xyz) new_xyz += (size_t)cloud * m * 3;
+
+    if (xs == 4 && (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) {
+        for (int k = lane; k < n; k += 32) sp[k] = __ldg(reinterpret_cast<const float4 *>(xyz) + k);
+    } else {
+        for (int k = lane; k < n; k += 32)
+            sp[k] = make_float4(xyz[(size_t)k * xs], xyz[(size_t)k * xs + 1], xyz[(size_t)k * xs + 2], 0.f);
+    }
+    __syncwarp();
+
+    const int bs = 1 << L;
+    float px[P], py[P], pz[P], t[2 * P];            // t[P + i] = running minimum of rank lane*P + i; t[1..P-1] = max tree
+#pragma unroll
+    for (int i = 0; i < P; i++) {
+        const int r = lane * P + i, k = rank_to_index(r, L, SH);
+        const bool valid = r < (bs << SH) && k < n;
+        const float4 q = sp[valid ? k : 0];
+        px[i] = valid ? q.x : 0.f; py[i] = valid ? q.y : 0.f; pz[i] = valid ? q.z : 0.f;
+        t[P + i] = valid ? (temp ? temp[k] : 1e10f) : -1.f;
+    }
+    int cur = 0, j = 1;
+    if (lane == 0) sidx[0] = 0;
+    for (; j < m; j++) {
+        const float4 c = sp[cur];
+#pragma unroll
+        for (int i = 0; i < P; i++) {
+            const float d = sqdist(__fsub_rn(px[i], c.x), __fsub_rn(py[i], c.y), __fsub_rn(pz[i], c.z));
+            t[P + i] = fminf(d, t[P + i]);
+        }
+#pragma unroll
+        for (int q = P - 1; q >= 1; q--) t[q] = fmaxf(t[2 * q], t[2 * q + 1]);
+        // distances are >= 0 (or the -1 filler): their int bit patterns order like the floats
+        const int vb = __float_as_int(P > 1 ? t[1] : t[P]);
+        const int vmax = __reduce_max_sync(0xffffffffu, vb);
+        if (vmax == 0) break;                       // every point already coincides with a sample: index 0 from here on
+        const int slot = descend<P, 1>(t, vmax, 0);
+        const int rmin = __reduce_min_sync(0xffffffffu, vb == vmax ? lane * P + slot : INT_MAX);
+        cur = rank_to_index(rmin, L, SH);
+        if (lane == 0) sidx[j] = cur;
+    }
+    for (int q = j + lane; q < m; q += 32) sidx[q] = 0;
+    __syncwarp();
+    for (int q = lane; q < m; q += 32) idxs[q] = sidx[q];
+    if (new_xyz) {
+        for (int e = lane; e < m * 3; e += 32) {
+            const int q = e / 3, cc = e - q * 3;
+            const float4 v = sp[sidx[q]];
+            new_xyz[e] = cc == 0 ? v.x : (cc == 1 ? v.y : v.z);
+        }
+    }
+    if (temp) {   // the reference leaves the final min-distances in temp (caller scratch): keep that contract
+#pragma unroll
+        for (int i = 0; i < P; i++) {
+            const int r = lane * P + i, k = rank_to_index(r, L, SH);
+            if (r < (bs << SH) && k < n) temp[k] = t[P + i];
         }
     }
 }
@@ -240,12 +347,32 @@ static int launch_reg(int grid, size_t smem, cudaStream_t st, const float *xyz, 
     return check_launch("fps");
 }
 
+static int SH_of(int V, int L) { int sh = 0; while (((1 << L) << sh) < V) sh++; return sh; }
 static int floor_log2(int v) { int l = 0; while ((2 << l) <= v) l++; return l; }
 
 // V = padded rank space.  Geometry table: (warps, ranks per thread) chosen so one round is short
 // for a single cloud yet several clouds still share an SM; overridable for tuning.
 static int fps_dispatch(int grid, int V, int max_n, cudaStream_t st, const float *xyz, int xs, float *temp, int *idx,
                         float *new_xyz, const int *cnt, const int *ms, int n, int m, int L, int stack) {
+    // many small clouds: one warp per cloud (throughput); a few clouds: several warps per cloud (latency)
+    if (!stack && V <= 512 && grid >= 4 * kNumSMs && !getenv("MGAR_FPS_GEOM")) {
+        int P = 1;
+        while (32 * P < V) P *= 2;
+        const int f4 = n + (m + 3) / 4;
+        const size_t sm = (size_t)kFpsWarpsPerCta * f4 * sizeof(float4);
+        if (sm <= 200 * 1024) {
+            const int ctas = (grid + kFpsWarpsPerCta - 1) / kFpsWarpsPerCta;
+#define MGAR_FPS_WARP(p)                                                                                              \
+    if (P == p) {                                                                                                     \
+        if (sm > 48 * 1024) MGAR_CUDA(cudaFuncSetAttribute(fps_warp_kernel<p>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+        fps_warp_kernel<p><<<ctas, kFpsWarpsPerCta * 32, sm, st>>>(xyz, xs, temp, idx, new_xyz, grid, n, m, L, SH_of(V, L), f4); \
+        count_launch();                                                                                               \
+        return check_launch("fps(warp)");                                                                             \
+    }
+            MGAR_FPS_WARP(1) MGAR_FPS_WARP(2) MGAR_FPS_WARP(4) MGAR_FPS_WARP(8) MGAR_FPS_WARP(16)
+#undef MGAR_FPS_WARP
+        }
+    }
     const size_t smem = (size_t)max_n * 3 * sizeof(float);
     int W, PPL;
     if (V <= 32) { W = 1; PPL = 1; }

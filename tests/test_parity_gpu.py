@@ -120,6 +120,24 @@ def test_fps_batch_with_ties(cuda, n, m):
     np.testing.assert_array_equal(got, O.farthest_point_sample(c, m))
 
 
+@pytest.mark.parametrize("b,n,m", [(600, 512, 512), (600, 300, 100), (640, 77, 77), (600, 33, 8)])
+def test_fps_many_small_clouds(cuda, b, n, m):
+    """Many clouds route to the warp-per-cloud kernel; wrapped clouds exercise its early exit (max distance 0)."""
+    c = cases.cloud_with_ties(n + 1, b, n)
+    c[::3] = np.random.default_rng(b).uniform(-1, 1, c[::3].shape).astype(np.float32)   # every third cloud: no duplicates
+    from multimodal_gar_b200 import fastpath
+    got = pointnet2_utils.farthest_point_sample(T(c, cuda), m).cpu().numpy()
+    pick = list(range(0, b, 25))
+    want = O.farthest_point_sample(np.ascontiguousarray(c[pick]), m)
+    np.testing.assert_array_equal(got[pick], want)
+    # strided in-place variant with the fused gather (what the fused branch calls)
+    c4 = np.concatenate([c, np.zeros((b, n, 1), np.float32)], axis=2)
+    t4 = T(c4, cuda)
+    idx, new_xyz = fastpath.fps_gather(t4[:, :, 0:3], m)
+    np.testing.assert_array_equal(idx.cpu().numpy(), got)
+    np.testing.assert_array_equal(new_xyz.cpu().numpy(), np.take_along_axis(c, got[..., None].astype(np.int64), axis=1))
+
+
 def test_fps_batch_temp_contract(cuda):
     from multimodal_gar_b200.pcdet.ops.pointnet2.pointnet2_stack import pointnet2_stack_cuda as ext
     c = cases.cloud_with_ties(9, 4, 600)
