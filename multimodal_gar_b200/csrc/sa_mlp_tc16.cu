@@ -200,14 +200,22 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             const float4 inv = *reinterpret_cast<const float4 *>(&s_inv[i % kRing][0]);
             const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
             float mx[4];
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
+            {   // two centroids at a time (64 registers).  The second pair of loads is made to depend on the first
+                // pair's maxima: hoisted above them (as ptxas does when left alone) it needs the same 64 registers
+                // and ~45 MOVs per tile to shuffle the first pair out of the way; the epilogue has the slack.
                 uint32_t v0[32], v1[32];
-                tc_ld32(taddr + (2 * h) * 32, v0);
-                tc_ld32(taddr + (2 * h + 1) * 32, v1);
+                tc_ld32(taddr, v0);
+                tc_ld32(taddr + 32, v1);
                 tc_wait_ld();
-                mx[2 * h] = max32(v0);
-                mx[2 * h + 1] = max32(v1);
+                mx[0] = max32(v0);
+                mx[1] = max32(v1);
+                // (a data dependence ptxas cannot fold: 0 unless both maxima are the all-ones NaN)
+                const uint32_t dep = (__float_as_uint(mx[0]) & __float_as_uint(mx[1])) == 0xffffffffu ? 1u : 0u;
+                tc_ld32(taddr + 64 + dep, v0);
+                tc_ld32(taddr + 96 + dep, v1);
+                tc_wait_ld();
+                mx[2] = max32(v0);
+                mx[3] = max32(v1);
             }
             tc_fence_before();
             mbar_arrive_relaxed(TEMPTY(t));

@@ -179,6 +179,76 @@ ball_query_kernel(int B, float radius, int K, const float *__restrict__ new_xyz,
     }
 }
 
+// Uniform layout, clouds of at most 512 points: one CTA per cloud, a WARP per centroid, and the cloud lives in
+// REGISTERS (lane l owns points l, l+32, ...: PPL x 3 floats) for all the centroids the warp serves - the inner
+// loop touches no memory at all.  A step tests 64 points (two per lane), appends the hits in index order with
+// ballot/popc into the warp's shared-memory row and stops as soon as THIS centroid has nsample neighbours; in
+// the thread-per-centroid kernel above a warp scans until the slowest of its 32 centroids is full, which on
+// pooled person clouds (sparse extremities picked by FPS) is nearly always the whole cloud.  The row leaves as
+// one coalesced store (lane = slot).
+constexpr int kBqRegWarps = 8;
+template <int PPL>
+__global__ void __launch_bounds__(kBqRegWarps * 32)
+ball_query_reg_kernel(float radius, int K, const float *__restrict__ new_xyz, const float *__restrict__ xyz, int xs,
+                      int n_u, int m_u, int *__restrict__ idx, int fill) {
+    extern __shared__ int bq_rows[];                                 // [kBqRegWarps][K] rows, then [m_u * 3] centroids
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.x;
+    float *sq = reinterpret_cast<float *>(bq_rows + kBqRegWarps * K);
+    for (int i = threadIdx.x; i < m_u * 3; i += kBqRegWarps * 32) sq[i] = __ldg(new_xyz + (size_t)b * m_u * 3 + i);
+    __syncthreads();
+    xyz += (size_t)b * n_u * xs;
+    const bool vec4 = (xs == 4) && ((reinterpret_cast<uintptr_t>(xyz) & 15) == 0);
+    float px[PPL], py[PPL], pz[PPL];
+#pragma unroll
+    for (int s = 0; s < PPL; s++) {
+        const int k = s * 32 + lane;
+        px[s] = py[s] = pz[s] = __int_as_float(0x7f800000);          // +inf: never inside a ball
+        if (k < n_u) {
+            if (vec4) {
+                const float4 p = __ldg(reinterpret_cast<const float4 *>(xyz) + k);
+                px[s] = p.x; py[s] = p.y; pz[s] = p.z;
+            } else {
+                const float *p = xyz + (size_t)k * xs;
+                px[s] = __ldg(p); py[s] = __ldg(p + 1); pz[s] = __ldg(p + 2);
+            }
+        }
+    }
+    const float r2 = __fmul_rn(radius, radius);
+    const unsigned lt = (1u << lane) - 1u;
+    int *row = bq_rows + warp * K;
+    for (int c = warp; c < m_u; c += kBqRegWarps) {
+        const size_t ci = (size_t)b * m_u + c;
+        const float qx = sq[c * 3 + 0], qy = sq[c * 3 + 1], qz = sq[c * 3 + 2];
+        int cnt = 0;
+#pragma unroll
+        for (int s = 0; s < PPL; s += 2) {
+            const bool h0 = sqdist(__fsub_rn(qx, px[s]), __fsub_rn(qy, py[s]), __fsub_rn(qz, pz[s])) < r2;
+            const bool h1 = (s + 1 < PPL) &&
+                            sqdist(__fsub_rn(qx, px[s + 1 < PPL ? s + 1 : s]), __fsub_rn(qy, py[s + 1 < PPL ? s + 1 : s]),
+                                   __fsub_rn(qz, pz[s + 1 < PPL ? s + 1 : s])) < r2;
+            const unsigned b0 = __ballot_sync(0xffffffffu, h0), b1 = __ballot_sync(0xffffffffu, h1);
+            const int pos0 = cnt + __popc(b0 & lt);
+            const int mid = cnt + __popc(b0);
+            const int pos1 = mid + __popc(b1 & lt);
+            if (h0 && pos0 < K) row[pos0] = s * 32 + lane;
+            if (h1 && pos1 < K) row[pos1] = (s + 1) * 32 + lane;
+            cnt = mid + __popc(b1);
+            if (cnt >= K) break;                                     // warp-uniform
+        }
+        __syncwarp();
+        int *out = idx + ci * K;
+        if (cnt == 0) {
+            if (fill) { for (int l = lane; l < K; l += 32) out[l] = l == 0 ? -1 : 0; }
+            else if (lane == 0) out[0] = -1;   // other slots keep the caller's fill (ball_query_gpu.cu:65)
+        } else {
+            const int first = row[0];
+            for (int l = lane; l < K; l += 32) out[l] = l < cnt ? row[l] : first;
+        }
+        __syncwarp();                                                // the row is rewritten for the next centroid
+    }
+}
+
 __global__ void __launch_bounds__(256)
 group_points_kernel(int B, long long total, int C, int K, const float *__restrict__ features,
                     const int *__restrict__ pre_feat, const int *__restrict__ pre_idx, const int *__restrict__ idx,
@@ -229,9 +299,21 @@ extern "C" int mgar_ball_query_stack(int B, int M, float radius, int nsample, co
     MGAR_REQUIRE(uniform || (new_xyz_batch_cnt && xyz_batch_cnt), "ball_query: batch counts missing");
     MGAR_REQUIRE(!uniform || (uniform_m >= 1 && (long long)B * uniform_m == M), "ball_query: uniform layout needs B*uniform_m == M");
     MGAR_REQUIRE(xyz_stride >= 3, "ball_query: xyz_stride must be >= 3");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (uniform && uniform_n <= 512 && ((size_t)nsample * kBqRegWarps + (size_t)uniform_m * 3) * 4 <= 48 * 1024) {
+        const size_t sm = ((size_t)nsample * kBqRegWarps + (size_t)uniform_m * 3) * 4;
+#define MGAR_BQ_REG(p)                                                                                            \
+    if (uniform_n <= 32 * p) {                                                                                    \
+        ball_query_reg_kernel<p><<<B, kBqRegWarps * 32, sm, st>>>(radius, nsample, new_xyz, xyz, xyz_stride,       \
+                                                                   uniform_n, uniform_m, idx, fill);               \
+        count_launch();                                                                                           \
+        return check_launch("ball_query(reg)");                                                                   \
+    }
+        MGAR_BQ_REG(2) MGAR_BQ_REG(4) MGAR_BQ_REG(8) MGAR_BQ_REG(16)
+#undef MGAR_BQ_REG
+    }
     const size_t smem = (size_t)kBqChunk * 16 + (size_t)kBqTile * (nsample + 1) * sizeof(int);
     MGAR_REQUIRE(smem <= 200 * 1024, "ball_query: nsample=%d too large", nsample);
-    cudaStream_t st = (cudaStream_t)stream;
     PrefixWs ws;
     int grid;
     if (uniform) {

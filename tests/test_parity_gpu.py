@@ -167,6 +167,36 @@ def test_fps_stack_large_cloud(cuda):
     np.testing.assert_array_equal(got, O.stack_farthest_point_sample(xyz, cnt, [64, 32]))
 
 
+@pytest.mark.parametrize("n,m,K,r", [(512, 512, 32, 0.3), (512, 64, 16, 0.1), (512, 100, 64, 1.0), (300, 77, 32, 0.5),
+                                     (256, 256, 32, 0.2), (100, 30, 16, 0.7), (64, 64, 64, 0.3), (20, 7, 8, 0.4),
+                                     (600, 50, 32, 0.3), (512, 33, 100, 2.0)])
+def test_ball_query_uniform_layout(cuda, n, m, K, r):
+    """fastpath.ball_query_uniform (register-resident warp-per-centroid kernel for n <= 512, the tiled kernel
+    above that) against the oracle: wrapped clouds (duplicates), far-away centroids (empty balls), strided rows."""
+    from multimodal_gar_b200 import fastpath
+    Bp = 9
+    rng = np.random.default_rng(n * 7 + K)
+    c = cases.cloud_with_ties(n, Bp, n)
+    c[::2] = rng.uniform(-1, 1, c[::2].shape).astype(np.float32)
+    new_xyz = np.ascontiguousarray(c[:, rng.integers(0, n, m)] + rng.normal(0, 0.05, (Bp, m, 3)).astype(np.float32))
+    new_xyz[:, ::5] += 50.0                                            # empty balls
+    xyz = c.reshape(-1, 3)
+    cnt, ncnt = np.full(Bp, n, np.int32), np.full(Bp, m, np.int32)
+    want = O.ball_query_raw(r, K, xyz, cnt, new_xyz.reshape(-1, 3), ncnt) if hasattr(O, "ball_query_raw") else None
+    wi, wm = O.ball_query(r, K, xyz, cnt, new_xyz.reshape(-1, 3), ncnt)
+    c4 = np.concatenate([c, rng.random((Bp, n, 1)).astype(np.float32)], axis=2).reshape(-1, 4)
+    for src in (T(xyz, cuda), T(c4, cuda)[:, 0:3]):
+        raw = fastpath.ball_query_uniform(r, K, src, T(new_xyz.reshape(-1, 3), cuda), n, m).cpu().numpy()
+        empty = raw[:, 0] == -1
+        np.testing.assert_array_equal(empty, wm)
+        assert (raw[empty, 1:] == 0).all()                             # fill = 1 writes every slot
+        got = raw.copy()
+        got[empty] = 0
+        np.testing.assert_array_equal(got, wi)
+        if want is not None:
+            np.testing.assert_array_equal(raw, want)
+
+
 @pytest.mark.parametrize("r,K", [(0.3, 16), (0.6, 32), (0.05, 8), (1.0, 64), (0.2, 1), (3.0, 100)])
 def test_ball_query_and_grouping_ragged(cuda, r, K):
     xyz, cnt, new_xyz, ncnt, feats = cases.ragged_case()
