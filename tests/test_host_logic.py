@@ -115,3 +115,26 @@ def test_frame_sharding_over_gloo_world2(tmp_path):
     out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=240)
     assert out.returncode == 0, out.stdout[-3000:]
     assert "GLOO_OK 2" in out.stdout
+
+
+def test_dafm_lidar_inputs_match_the_reference_per_frame_loop():
+    """gat_model.py:1276-1280, :1396-1405, :1467-1471 restated frame by frame vs the batched form."""
+    from multimodal_gar_b200 import lidar_backbone as LB
+    rng = np.random.default_rng(0)
+    B, MNP, D = 3, 10, 16
+    feat = torch.from_numpy(rng.standard_normal((B, MNP, D)).astype(np.float32))
+    boxes = torch.from_numpy(synthetic.make_batch(1, B, N=16, M=MNP)[1])
+    person_id = torch.zeros((B, MNP), dtype=torch.int64) - 1          # -1 = padding id
+    counts = [7, 10 - 1, 1]                                            # frame 1: nine persons + padding
+    for b, n in enumerate(counts):
+        person_id[b, :n] = torch.arange(n) + 5
+    out = LB.dafm_lidar_inputs(feat, boxes, person_id)
+    assert out["person_num"] == counts == LB.get_num_person(person_id)
+    for b, n in enumerate(counts):
+        ctr = boxes[b, :n, :3].double()
+        want = torch.cdist(ctr, ctr).float()                           # definition: ||x_i - x_j||, zero diagonal
+        want.fill_diagonal_(0)
+        assert torch.allclose(out["De"][b, :n, :n], want, atol=2e-5)
+        assert torch.equal(out["feature"][b, :n], feat[b, :n])
+        assert (out["feature"][b, n:] == 0).all() and (out["De"][b, n:] == 0).all() and (out["De"][b, :, n:] == 0).all()
+    assert (torch.diagonal(out["De"], dim1=1, dim2=2) == 0).all()

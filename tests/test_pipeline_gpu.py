@@ -116,3 +116,47 @@ def test_crowded_scene_stress_config5(cuda):
         np.testing.assert_array_equal(st["pooled"].cpu().numpy()[..., 3], O.canonical_transform(pooled, boxes, empty)[..., 3])
     assert torch.isfinite(st["person_features"]).all()
     assert st["person_features"].shape == (1, 200, 128)
+
+
+def test_point_lidar_backbone_output_contract(cuda):
+    """a12: (B, MAX_NUM_PROPOSAL, 512) from points + zero-padded person boxes; padded rows = embedding(0)."""
+    from multimodal_gar_b200 import lidar_backbone as LB
+    pts, boxes, xyz, feat, bx = _inputs(11, 2, 16384, 12, cuda)
+    MNP = 20
+    padded = torch.zeros((2, MNP, 7), device=cuda)
+    padded[:, :12] = bx
+    torch.manual_seed(3)
+    net = LB.PointLiDARBackbone().to(cuda).eval()
+    with torch.no_grad():
+        out = net(dict(points=T(pts, cuda), gt_bboxes3d=padded))
+        person = net.encoder(xyz, feat, bx)
+        assert out.shape == (2, MNP, 512)
+        assert torch.allclose(out[:, :12], net.embedding(person), atol=1e-5)
+        assert torch.allclose(out[:, 12:], net.embedding.bias.expand(2, MNP - 12, 512), atol=1e-6)
+        pid = torch.full((2, MNP), -1, dtype=torch.int64, device=cuda)
+        pid[:, :12] = torch.arange(12, device=cuda)
+        d = LB.dafm_lidar_inputs(out, padded, pid)
+    assert d["person_num"] == [12, 12] and d["De"].shape == (2, MNP, MNP)
+
+
+@pytest.mark.parametrize("r,K", [(0.1, 16), (0.2, 32), (0.5, 64), (1.0, 16), (0.7, 32)])
+def test_crowded_scene_radius_nsample_sweep_config5(cuda, r, K):
+    """configs[4] sweep (radius 0.1-1.0, nsample 16-64) on a crowded frame: ball-query indices bit-exact and
+    SA features within 1e-5 against the oracle on a sample of the 200 persons."""
+    pts, boxes, xyz, feat, bx = _inputs(9, 1, 250000, 200, cuda, density_scale=4.0)
+    enc = _enc(cuda, radius=r, nsample=K)
+    with torch.no_grad():
+        st = enc(xyz, feat, bx, return_stages=True)
+    S, P = 512, 512
+    pick = [0, 17, 63, 120, 199]
+    pooled = st["pooled"].cpu().numpy()[pick]
+    cxyz = np.ascontiguousarray(pooled[..., :3])
+    fps = O.farthest_point_sample(cxyz, P)
+    np.testing.assert_array_equal(st["fps_idx"].cpu().numpy()[pick], fps)
+    new_xyz = np.take_along_axis(cxyz, fps[..., None].astype(np.int64), axis=1).reshape(-1, 3)
+    cnt, ncnt = np.full(len(pick), S, np.int32), np.full(len(pick), P, np.int32)
+    want = O.stack_sa_module_msg([enc.sa.mlps[0].cpu()], [r], [K], cxyz.reshape(-1, 3), cnt, new_xyz, ncnt,
+                                 np.ascontiguousarray(pooled[..., 3:]).reshape(-1, 1))
+    got = st["sa_features"].view(200, P, -1).cpu().numpy()[pick].reshape(-1, want.shape[1])
+    scale = max(1.0, float(np.abs(want).max()))
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5 * scale)
