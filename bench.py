@@ -58,6 +58,17 @@ def peaks():
     return dict(hbm=6650.0, bf16=1590.0, bf16_sustained=1400.0, source="fallback (B200_PROFILING.md)")
 
 
+def ncu_traffic(stage, F):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the stage's kernel for one launch, from the committed
+    `ncu --set full` capture of this same command (64 frames per launch); None when no capture matches."""
+    path = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    try:
+        t = json.load(open(path))
+        return t["bytes_per_launch"][stage] if t.get("frames_per_step") == F else None
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -380,19 +391,22 @@ def main():
         if w["flops"] > 0:        # the shared MLP: the one dense contraction -> tensor-pipe roofline
             ach = w["flops"] / (ms * 1e-3) / 1e12
             roof = dict(bound="tensor", achieved=ach, peak=pk["bf16_sustained"], unit="TFLOP/s",
-                        frac=ach / pk["bf16_sustained"], traffic=None, kernel=dom,
-                        note="fp32 FFMA arithmetic (exact-fp32 path) against the %s sustained bf16 tensor peak" % pk["source"])
+                        frac=ach / pk["bf16_sustained"], traffic=ncu_traffic("sa_mlp", F), kernel=dom,
+                        note="algorithmic fp32 FLOPs (2*M*P*K*8448 per frame) over the kernel's CUDA-event time, against the "
+                             "%s sustained bf16 tensor peak; the kernel issues 3 fp16 MMAs per product (3xFP16 split, "
+                             "fp32-faithful), so frac <= 1/3 by construction; traffic = ncu dram bytes per launch "
+                             "(profiles/r01_traffic.json)" % pk["source"])
         else:
             ach = w["bytes"] / (ms * 1e-3) / 1e9
-            roof = dict(bound="hbm", achieved=ach, peak=pk["hbm"], unit="GB/s", frac=ach / pk["hbm"], traffic=None,
-                        kernel=dom, note="of %s" % pk["source"])
+            roof = dict(bound="hbm", achieved=ach, peak=pk["hbm"], unit="GB/s", frac=ach / pk["hbm"],
+                        traffic=ncu_traffic(dom, F), kernel=dom, note="of %s" % pk["source"])
         roof["share_of_step"] = ms / (r["ms_total"] / K)
         pipeline_GBps = algorithmic_bytes_per_frame() * value / 1e9
         line = dict(metric=METRIC, value=value, unit="frames/s", n_gpus=world, steps=K, warmup=args.warmup,
                     ms_per_step=r["ms_total"] / K, higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype="f32", data="synthetic",
                     config=dict(workload="configs[1]: 65536 pts x 40 boxes, S=512 P=512 r=0.3 K=32 MLP 4-64-128",
-                                frames_per_step=F, frames_per_step_per_gpu=F,
+                                frames_per_step=F * world, frames_per_step_per_gpu=F,
                                 l2="two alternating input batches (2 x %d MB) + ~%d MB of stage outputs per step > 126 MB L2"
                                    % (F, F * 14), weights="random-init (seed 1994), eval-mode BatchNorm folded"),
                     e2e=dict(value=frames_total / (r["ms_e2e"] * 1e-3), unit="frames/s",
