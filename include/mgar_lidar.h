@@ -156,6 +156,31 @@ MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float
                                 float *group_max, int group_size, const int *group_zero, int pool_avg,
                                 void *stream);
 
+/* ---- training: the same module with BatchNorm batch statistics, and its backward pass ------------------- */
+
+/* StackSAModuleMSG.forward in train() for ONE scale (pointnet2_modules.py:78-112; BatchNorm2d in training mode:
+ * statistics over all M*nsample positions, biased variance, eps) and the backward pass that autograd derives for
+ * it in the reference (cuDNN / ATen kernels + GroupingOperation.backward, group_points_gpu.cu:15-44).
+ * weights (DEVICE): per layer W^T [c_in][c_out], concatenated.  gamma_beta (DEVICE): per layer gamma[c_out] then
+ * beta[c_out].  batch_stats (optional): per layer mean[c_out] then BIASED variance[c_out] - what the caller needs
+ * to update running_mean / running_var.  workspace: mgar_sa_mlp_train_workspace_bytes() bytes of device memory;
+ * the forward leaves the activations there and mgar_sa_mlp_bwd must be given the SAME, untouched workspace.
+ * Backward outputs: grad_weights / grad_gamma_beta (same layouts, overwritten) and grad_features (N, C_in), which
+ * is ACCUMULATED into (zero it first; may be NULL).  No gradient is produced for xyz / new_xyz.
+ * Geometry arguments as for mgar_sa_mlp_fwd_fp32.  Exact fp32 arithmetic, fp64 batch reductions. */
+MGAR_API size_t mgar_sa_mlp_train_workspace_bytes(int M, int nsample, int n_layers, const int *channels_host);
+MGAR_API int mgar_sa_mlp_fwd_train(int B, int M, int nsample, int C_in, const float *xyz, const int *xyz_batch_cnt,
+                                   const float *new_xyz, const int *new_xyz_batch_cnt, int uniform_n, int uniform_m,
+                                   const float *features, const int *idx, const unsigned char *empty_mask,
+                                   int n_layers, const int *channels_host, const float *weights,
+                                   const float *gamma_beta, float eps, float *out, int ld_out, int pool_avg,
+                                   float *batch_stats, void *workspace, size_t ws_bytes, void *stream);
+MGAR_API int mgar_sa_mlp_bwd(int B, int M, int nsample, int C_in, const int *xyz_batch_cnt, const int *new_xyz_batch_cnt,
+                             int uniform_n, int uniform_m, const int *idx, const unsigned char *empty_mask, int n_layers,
+                             const int *channels_host, const float *weights, const float *gamma_beta,
+                             const float *grad_out, int ld_grad, int pool_avg, void *workspace, size_t ws_bytes,
+                             float *grad_weights, float *grad_gamma_beta, float *grad_features, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

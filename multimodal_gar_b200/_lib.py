@@ -34,6 +34,10 @@ SIGNATURES = {
     "mgar_sa_mlp_fwd_tc": [_i, _i, _i, _i, _p, _i, _p, _p, _p, _i, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _i, _p, _i, _p, _i,
                            _p],
     "mgar_sa_mlp_fwd_fp32": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _i, _i, _p],
+    "mgar_sa_mlp_train_workspace_bytes": [_i, _i, _i, _p],
+    "mgar_sa_mlp_fwd_train": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _f, _p, _i, _i, _p, _p,
+                              ctypes.c_size_t, _p],
+    "mgar_sa_mlp_bwd": [_i, _i, _i, _i, _p, _p, _i, _i, _p, _p, _i, _p, _p, _p, _p, _i, _i, _p, ctypes.c_size_t, _p, _p, _p, _p],
 }
 
 
@@ -65,6 +69,7 @@ def lib():
             fn.restype = _i
         L.mgar_last_error.restype = ctypes.c_char_p
         L.mgar_launch_count.restype = ctypes.c_ulonglong
+        L.mgar_sa_mlp_train_workspace_bytes.restype = ctypes.c_size_t
         _lib = L
     return _lib
 

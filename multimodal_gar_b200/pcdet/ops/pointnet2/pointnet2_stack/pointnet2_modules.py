@@ -3,9 +3,12 @@
 parameter names `mlps.{k}.{0,1,3,4}.*`, init and forward signature).
 
 eval(): each scale runs as ball query + ONE fused kernel (gather, MLP, BatchNorm folded, ReLU,
-pool).  train(): the reference's own composition (QueryAndGroup -> Conv2d/BN/ReLU -> pool) on the
-new grouping kernels, so batch statistics and autograd behave exactly as upstream.
+pool).  train(): ball query + ONE autograd node per scale (sa_mlp_fused.SAMlpTrainFunction: batch-statistics
+BatchNorm forward and the whole backward in libmgar_lidar.so, running statistics updated as nn.BatchNorm2d does).
+eval() with autograd enabled, or MGAR_SA_TRAIN=torch: the reference's own composition (QueryAndGroup ->
+Conv2d/BN/ReLU -> pool) on the new grouping kernels.
 """
+import os
 from typing import List
 
 import torch
@@ -93,6 +96,19 @@ class StackSAModuleMSG(nn.Module):
                                             pool_avg=self.pool_method == 'avg_pool', params_host=params_host)
                 col += widths[k]
             return new_xyz, out
+
+        native_train = self.training and self.use_xyz and self.pool_method in ('max_pool', 'avg_pool') \
+            and os.environ.get("MGAR_SA_TRAIN", "native") != "torch" and new_xyz.shape[0] > 0
+        if native_train:
+            # train(): BatchNorm batch statistics + backward through libmgar_lidar (one autograd node per scale)
+            outs = []
+            for k, g in enumerate(self.groupers):
+                idx, empty = pointnet2_utils.ball_query(g.radius, g.nsample, xyz, xyz_batch_cnt, new_xyz,
+                                                        new_xyz_batch_cnt)
+                outs.append(sa_mlp_fused.sa_mlp_train_forward(self.mlps[k], g.nsample, xyz.contiguous(), xyz_batch_cnt,
+                                                              new_xyz.contiguous(), new_xyz_batch_cnt, features, idx,
+                                                              empty_mask=empty, pool_avg=self.pool_method == 'avg_pool'))
+            return new_xyz, torch.cat(outs, dim=1)
 
         new_features_list = []
         for k in range(len(self.groupers)):

@@ -96,3 +96,95 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
                 ptr(features), ptr(idx), ptr(empty_mask), len(channels) - 1, ctypes.addressof(ch), ptr(params),
                 ptr(out), out.stride(0), 1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd")
     return out if want_out else group_max
+
+
+# ---- training mode: BatchNorm batch statistics + backward, through the C ABI --------------------------------
+def train_workspace_bytes(M, nsample, channels):
+    ch = (ctypes.c_int * len(channels))(*channels)
+    return int(_lib.lib().mgar_sa_mlp_train_workspace_bytes(int(M), int(nsample), len(channels) - 1, ctypes.addressof(ch)))
+
+
+class SAMlpTrainFunction(torch.autograd.Function):
+    """QueryAndGroup + [Conv1x1, BatchNorm (batch statistics), ReLU] x L + pool as ONE autograd node.
+
+    forward(features (N,C_in) or None, weights_flat, gamma_beta_flat, geometry...) -> (out (M,C_last), batch_stats)
+    weights_flat = cat_l W_l^T.reshape(-1) ([c_in][c_out]); gamma_beta_flat = cat_l (gamma_l, beta_l);
+    batch_stats = cat_l (mean_l, biased var_l), not differentiable.  Gradients: features, weights_flat,
+    gamma_beta_flat (the reference's autograd produces the same three; coordinates get none)."""
+
+    @staticmethod
+    def forward(ctx, features, weights_flat, gamma_beta_flat, channels, nsample, eps, pool_avg, xyz, xyz_batch_cnt,
+                new_xyz, new_xyz_batch_cnt, idx, empty_mask, uniform):
+        need_cuda(xyz=xyz, new_xyz=new_xyz, idx=idx, features=features, weights_flat=weights_flat,
+                  gamma_beta_flat=gamma_beta_flat, empty_mask=empty_mask)
+        need_dtype(torch.float32, xyz=xyz, new_xyz=new_xyz, features=features, weights_flat=weights_flat,
+                   gamma_beta_flat=gamma_beta_flat)
+        need_dtype(torch.int32, idx=idx)
+        M = new_xyz.shape[0]
+        C_in = 0 if features is None else features.shape[1]
+        B = xyz_batch_cnt.shape[0] if xyz_batch_cnt is not None else xyz.shape[0] // uniform[0]
+        un, um = uniform if uniform is not None else (0, 0)
+        if empty_mask is not None:
+            empty_mask = empty_mask.to(torch.uint8).contiguous()
+        ch = (ctypes.c_int * len(channels))(*channels)
+        ws_bytes = train_workspace_bytes(M, nsample, channels)
+        ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=xyz.device)
+        out = torch.empty((M, channels[-1]), dtype=torch.float32, device=xyz.device)
+        stats = torch.empty((2 * sum(channels[1:]),), dtype=torch.float32, device=xyz.device)
+        w, gb = weights_flat.detach().contiguous(), gamma_beta_flat.detach().contiguous()
+        with on_device(xyz):
+            _lib.check(_lib.lib().mgar_sa_mlp_fwd_train(
+                B, M, int(nsample), C_in, ptr(xyz), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt), un, um,
+                ptr(features), ptr(idx), ptr(empty_mask), len(channels) - 1, ctypes.addressof(ch), ptr(w), ptr(gb),
+                float(eps), ptr(out), out.stride(0), 1 if pool_avg else 0, ptr(stats), ptr(ws), ws_bytes,
+                stream_of(xyz)), "sa_mlp_fwd_train")
+        ctx.save_for_backward(w, gb, idx, xyz_batch_cnt, new_xyz_batch_cnt, empty_mask, ws)
+        ctx.geom = (B, M, int(nsample), C_in, un, um, list(channels), bool(pool_avg), ws_bytes,
+                    None if features is None else features.shape[0])
+        ctx.mark_non_differentiable(stats)
+        return out, stats
+
+    @staticmethod
+    def backward(ctx, grad_out, _grad_stats):
+        w, gb, idx, xyz_batch_cnt, new_xyz_batch_cnt, empty_mask, ws = ctx.saved_tensors
+        B, M, nsample, C_in, un, um, channels, pool_avg, ws_bytes, N = ctx.geom
+        grad_out = grad_out.contiguous().float()
+        ch = (ctypes.c_int * len(channels))(*channels)
+        gw, ggb = torch.empty_like(w), torch.empty_like(gb)
+        gf = torch.zeros((N, C_in), dtype=torch.float32, device=w.device) if (C_in and ctx.needs_input_grad[0]) else None
+        with on_device(w):
+            _lib.check(_lib.lib().mgar_sa_mlp_bwd(
+                B, M, nsample, C_in, ptr(xyz_batch_cnt), ptr(new_xyz_batch_cnt), un, um, ptr(idx), ptr(empty_mask),
+                len(channels) - 1, ctypes.addressof(ch), ptr(w), ptr(gb), ptr(grad_out), grad_out.stride(0),
+                1 if pool_avg else 0, ptr(ws), ws_bytes, ptr(gw), ptr(ggb), ptr(gf), stream_of(w)), "sa_mlp_bwd")
+        return (gf, gw, ggb) + (None,) * 11
+
+
+def sa_mlp_train_forward(seq, nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features, idx, empty_mask=None,
+                         pool_avg=False, uniform=None):
+    """Training-mode forward of `seq` (= [Conv2d 1x1, BatchNorm2d, ReLU] x L, in train()) through the C ABI: returns
+    the pooled (M, C_last) features as a differentiable tensor and updates the BatchNorm running statistics exactly
+    as nn.BatchNorm2d does (momentum, unbiased running variance, num_batches_tracked)."""
+    mods = list(seq)
+    convs, bns = mods[0::3], mods[1::3]
+    channels = [convs[0].in_channels] + [c.out_channels for c in convs]
+    eps = bns[0].eps
+    if any(bn.eps != eps or not bn.affine for bn in bns):
+        raise _lib.MgarError("training path: BatchNorm layers must be affine and share eps")
+    weights_flat = torch.cat([c.weight.reshape(c.out_channels, c.in_channels).t().reshape(-1) for c in convs])
+    gamma_beta_flat = torch.cat([t for bn in bns for t in (bn.weight, bn.bias)])
+    out, stats = SAMlpTrainFunction.apply(features, weights_flat, gamma_beta_flat, channels, nsample, eps, pool_avg, xyz,
+                                          xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, idx, empty_mask, uniform)
+    P = new_xyz.shape[0] * nsample
+    with torch.no_grad():
+        off = 0
+        for bn in bns:
+            C = bn.num_features
+            mean, var = stats[off:off + C], stats[off + C:off + 2 * C]
+            off += 2 * C
+            if bn.track_running_stats and bn.running_mean is not None:
+                bn.num_batches_tracked += 1
+                mom = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+                bn.running_mean.mul_(1 - mom).add_(mean, alpha=mom)
+                bn.running_var.mul_(1 - mom).add_(var * (P / max(P - 1, 1)), alpha=mom)
+    return out
