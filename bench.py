@@ -330,21 +330,24 @@ def run_native(args, rank, world, local_rank):
             stage_ms[name] = stage_ms.get(name, 0.0) + a.elapsed_time(b) / len(marks)
 
     # ---- end to end through the public API with HOST buffers: `e2e` ---------------------------------
-    out_host = torch.empty((F, CFG["M"], CFG["mlp"][-1]), dtype=torch.float32).pin_memory()
-    stage = [torch.empty_like(t) for t in devb[0]]
+    # The public host-buffer API (multimodal_gar_b200.pipeline.HostFramePipeline): every step copies its pinned host
+    # inputs to the device, runs the branch and copies the person features back; the three legs run on their own
+    # streams, so the copy of step i+1 overlaps the kernels of step i.  All of it is inside the timed region.
+    from multimodal_gar_b200 import pipeline
+    out_host = [torch.empty((F, CFG["M"], CFG["mlp"][-1]), dtype=torch.float32).pin_memory() for _ in range(2)]
+    pipe = pipeline.HostFramePipeline(enc, dev, depth=2)
     with torch.no_grad():
-        def e2e_step(i):
-            for d, h in zip(stage, host[i & 1]):
-                d.copy_(h, non_blocking=True)
-            out_host.copy_(enc(*stage), non_blocking=True)
         for i in range(max(2, args.warmup // 2)):
-            e2e_step(i)
+            pipe.submit(*host[i & 1], out_host[i & 1])
+        pipe.synchronize()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for i in range(args.steps):
-            e2e_step(i)
+            pipe.submit(*host[i & 1], out_host[i & 1])
+        pipe.join()
         e1.record()
+        pipe.synchronize()
         barrier()
         ms_e2e = max_over_ranks(e0.elapsed_time(e1))
         # single-frame latency (F = 1), reported beside the throughput number
@@ -360,7 +363,7 @@ def run_native(args, rank, world, local_rank):
         torch.cuda.synchronize()
         lat_ms = l0.elapsed_time(l1) / 20
     h2d = sum(t.numel() * t.element_size() for t in host[0])
-    d2h = out_host.numel() * out_host.element_size()
+    d2h = out_host[0].numel() * out_host[0].element_size()
     return dict(F=F, ms_total=ms_total, ms_e2e=ms_e2e, stage_ms=stage_ms, launches=launches, clocks=clocks,
                 h2d=h2d, d2h=d2h, lat_ms=lat_ms, work=work, host=host)
 

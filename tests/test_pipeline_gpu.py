@@ -160,3 +160,25 @@ def test_crowded_scene_radius_nsample_sweep_config5(cuda, r, K):
     got = st["sa_features"].view(200, P, -1).cpu().numpy()[pick].reshape(-1, want.shape[1])
     scale = max(1.0, float(np.abs(want).max()))
     np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-5 * scale)
+
+
+def test_host_frame_pipeline_matches_direct_calls(cuda):
+    """The overlapped host-buffer front end returns, batch by batch, exactly what the encoder returns on device
+    tensors (5 batches through 2 slots: slot reuse, stream hand-offs)."""
+    from multimodal_gar_b200 import pipeline
+    enc = _enc(cuda)
+    pipe = pipeline.HostFramePipeline(enc, cuda, depth=2)
+    hosts, outs, want = [], [], []
+    for i in range(5):
+        pts, boxes = synthetic.make_batch(100 + i, 2, N=16384, M=10)
+        h = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in (pts[..., :3], pts[..., 3:4], boxes)]
+        hosts.append(h)
+        outs.append(torch.empty((2, 10, 128)).pin_memory())
+    for h, o in zip(hosts, outs):
+        pipe.submit(*h, o)
+    pipe.synchronize()
+    with torch.no_grad():
+        for h in hosts:
+            want.append(enc(*[t.to(cuda) for t in h]).cpu())
+    for o, w in zip(outs, want):
+        assert torch.equal(o, w)
