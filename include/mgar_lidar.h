@@ -72,6 +72,20 @@ MGAR_API int mgar_roipoint_pool(const float *xyz, const float *boxes, const floa
                        int *empty, int *pts_idx, int B, int N, int M, int S, int C, int canonical,
                        void *stream);
 
+/* Two-pass form of the same pooling for whole batches (the throughput path): pass 1 streams the points once for
+ * ALL boxes of a frame and leaves an in-box bit mask, mask (B, M, mgar_box_mask_words(N)) uint32, bit (n & 31) of
+ * word n >> 5 = point n inside box m of boxes_pool (margin 1e-5, the test of roipoint_pool3d_kernel.cu:38-60); the
+ * buffer is zero-filled by the call.  When box_idx != NULL the same pass also writes points_in_boxes_gpu's
+ * first-hit index (roiaware_pool3d_kernel.cu:313-336) for boxes_first (pass the same pointer as boxes_pool when
+ * the pooling boxes are not enlarged: the tests are then shared).  Pass 2 turns the masks into the pooled rows;
+ * arguments and outputs as mgar_roipoint_pool. */
+MGAR_API size_t mgar_box_mask_words(int N);
+MGAR_API int mgar_box_masks(const float *boxes_first, const float *boxes_pool, const float *pts, int *box_idx,
+                            unsigned *mask, int B, int M, int N, void *stream);
+MGAR_API int mgar_roipoint_pool_from_masks(const float *xyz, const float *boxes, const float *feat, const unsigned *mask,
+                                           float *pooled, int *empty, int *pts_idx, int B, int N, int M, int S, int C,
+                                           int canonical, void *stream);
+
 /* ---- pointnet2_stack: farthest point sampling ------------------------------------------------- */
 
 /* farthest_point_sampling_wrapper: pointnet2/pointnet2_stack/src/sampling.cpp:21-34

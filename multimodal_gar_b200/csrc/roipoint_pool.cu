@@ -20,6 +20,45 @@ struct PoolBox {
     float R;  // conservative xy half-extent: a hit always has |x-cx| <= R and |y-cy| <= R
 };
 
+// wrap (slot k >= cnt copies slot k mod cnt, roipoint_pool3d_kernel.cu:86-97) + gather of xyz | features into the
+// pooled rows, optionally in the box's canonical frame (pointrcnn_head.py:121-129).  flist: the first `total`
+// in-box point indices in index order (shared memory).  Whole-CTA call.
+__device__ __forceinline__ void pool_emit(const float *__restrict__ xyz, const float *__restrict__ feat,
+                                          float *__restrict__ pooled, int *__restrict__ empty, int *__restrict__ pts_idx,
+                                          const int *flist, int total, size_t bm, int S, int C, int canonical,
+                                          const BoxP &bp) {
+    const int D = 3 + C;
+    float *out = pooled + bm * (size_t)S * D;
+    if (threadIdx.x == 0) empty[bm] = total == 0 ? 1 : 0;
+    if (total == 0) {
+        for (size_t i = threadIdx.x; i < (size_t)S * D; i += blockDim.x) out[i] = 0.f;
+        if (pts_idx)
+            for (int s = threadIdx.x; s < S; s += blockDim.x) pts_idx[bm * S + s] = 0;
+        return;
+    }
+    const bool vec4 = (C == 1) && ((reinterpret_cast<uintptr_t>(pooled) & 15) == 0);
+    for (int s = threadIdx.x; s < S; s += blockDim.x) {
+        const int src = flist[s < total ? s : s % total];
+        float px = __ldg(xyz + (size_t)src * 3 + 0);
+        float py = __ldg(xyz + (size_t)src * 3 + 1);
+        float pz = __ldg(xyz + (size_t)src * 3 + 2);
+        if (canonical) {
+            px = __fsub_rn(px, bp.cx); py = __fsub_rn(py, bp.cy); pz = __fsub_rn(pz, bp.cz);
+            const float rx = __fmaf_rn(py, -bp.sina, __fmul_rn(px, bp.cosa));
+            const float ry = __fmaf_rn(py, bp.cosa, __fmul_rn(px, bp.sina));
+            px = rx; py = ry;
+        }
+        if (vec4) {
+            reinterpret_cast<float4 *>(out)[s] = make_float4(px, py, pz, __ldg(feat + src));
+        } else {
+            float *o = out + (size_t)s * D;
+            o[0] = px; o[1] = py; o[2] = pz;
+            for (int j = 0; j < C; j++) o[3 + j] = __ldg(feat + (size_t)src * C + j);
+        }
+        if (pts_idx) pts_idx[bm * S + s] = src;
+    }
+}
+
 __global__ void __launch_bounds__(1024)
 roipoint_pool_kernel(const float *__restrict__ xyz, const float *__restrict__ boxes,
                      const float *__restrict__ feat, float *__restrict__ pooled, int *__restrict__ empty,
@@ -104,37 +143,137 @@ roipoint_pool_kernel(const float *__restrict__ xyz, const float *__restrict__ bo
     }
     __syncthreads();
 
-    // ---- phase 3: wrap (slot k >= cnt copies slot k mod cnt) + gather ---------------------------
-    const int D = 3 + C;
-    float *out = pooled + bm * (size_t)S * D;
-    if (threadIdx.x == 0) empty[bm] = total == 0 ? 1 : 0;
-    if (total == 0) {
-        for (size_t i = threadIdx.x; i < (size_t)S * D; i += blockDim.x) out[i] = 0.f;
-        if (pts_idx)
-            for (int s = threadIdx.x; s < S; s += blockDim.x) pts_idx[bm * S + s] = 0;
-        return;
-    }
-    const bool vec4 = (C == 1) && ((reinterpret_cast<uintptr_t>(pooled) & 15) == 0);
-    for (int s = threadIdx.x; s < S; s += blockDim.x) {
-        const int src = flist[s < total ? s : s % total];
-        float px = __ldg(xyz + (size_t)src * 3 + 0);
-        float py = __ldg(xyz + (size_t)src * 3 + 1);
-        float pz = __ldg(xyz + (size_t)src * 3 + 2);
-        if (canonical) {
-            px = __fsub_rn(px, bp.cx); py = __fsub_rn(py, bp.cy); pz = __fsub_rn(pz, bp.cz);
-            const float rx = __fmaf_rn(py, -bp.sina, __fmul_rn(px, bp.cosa));
-            const float ry = __fmaf_rn(py, bp.cosa, __fmul_rn(px, bp.sina));
-            px = rx; py = ry;
+    pool_emit(xyz, feat, pooled, empty, pts_idx, flist, total, bm, S, C, canonical, bp);
+}
+
+// ---- two-pass pooling over in-box BIT MASKS (the throughput path) -------------------------------------------
+// Pass 1 (box_mask_kernel) streams the points ONCE for all boxes of the frame: every thread owns 4 consecutive
+// points (three 128-bit loads), the pre-processed boxes are broadcast from shared memory, and for each box the
+// 128 in-box bits of a warp's points are assembled with one REDUX.OR per 32-point word - written only when a
+// word has a hit (the mask is zero-filled first; person boxes hold ~0.5 % of a frame).  The same tests give the
+// first-hit index of points_in_boxes_gpu (roiaware_pool3d_kernel.cu:313-336) when the caller wants it.
+// Pass 2 (pool_from_mask_kernel), one CTA per (frame, box), scans the box's N/32 words (8 KB instead of the
+// frame's 786 KB), turns popcounts into ordered positions with one block scan, and emits the pooled rows.
+// The (frame, box) CTA of roipoint_pool_kernel re-reads the whole frame per box: 40x the point traffic.
+constexpr int kMaskThreads = 256;
+constexpr int kMaskBoxTile = 512;
+
+template <bool kSame>
+__global__ void __launch_bounds__(kMaskThreads)
+box_mask_kernel(const float *__restrict__ boxes_first, const float *__restrict__ boxes_pool, const float *__restrict__ pts,
+                int *__restrict__ box_idx, unsigned *__restrict__ mask, int M, int N, int W, int vec_ok) {
+    __shared__ BoxP sbox[kMaskBoxTile];
+    __shared__ BoxP sfirst[kSame ? 1 : kMaskBoxTile];
+    const int b = blockIdx.y, lane = threadIdx.x & 31;
+    boxes_pool += (size_t)b * M * 7;
+    if (boxes_first) boxes_first += (size_t)b * M * 7;
+    pts += (size_t)b * N * 3;
+    mask += (size_t)b * M * W;
+    const long long p0 = ((long long)blockIdx.x * kMaskThreads + threadIdx.x) * 4;
+    const int n_valid = p0 >= N ? 0 : (N - p0 >= 4 ? 4 : (int)(N - p0));
+    float x[4], y[4], z[4];
+    if (vec_ok && n_valid == 4) {
+        const float4 *v = reinterpret_cast<const float4 *>(pts + p0 * 3);
+        const float4 a = __ldg(v), bb = __ldg(v + 1), c = __ldg(v + 2);
+        x[0] = a.x; y[0] = a.y; z[0] = a.z;   x[1] = a.w; y[1] = bb.x; z[1] = bb.y;
+        x[2] = bb.z; y[2] = bb.w; z[2] = c.x; x[3] = c.y; y[3] = c.z; z[3] = c.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const bool ok = j < n_valid;
+            x[j] = ok ? __ldg(pts + (p0 + j) * 3 + 0) : nanf("");   // NaN never tests in-box
+            y[j] = ok ? __ldg(pts + (p0 + j) * 3 + 1) : nanf("");
+            z[j] = ok ? __ldg(pts + (p0 + j) * 3 + 2) : nanf("");
         }
-        if (vec4) {
-            reinterpret_cast<float4 *>(out)[s] = make_float4(px, py, pz, __ldg(feat + src));
+    }
+    const int word0 = (int)((((long long)blockIdx.x * kMaskThreads + (threadIdx.x & ~31)) * 4) >> 5) + (lane >> 3);
+    const unsigned sub = 0xffu << (lane & 24);          // the 8 lanes whose nibbles make one 32-point word
+    const int sh = 4 * (lane & 7);
+    int res[4] = {-1, -1, -1, -1};
+    for (int k0 = 0; k0 < M; k0 += kMaskBoxTile) {
+        const int kt = min(kMaskBoxTile, M - k0);
+        __syncthreads();
+        for (int k = threadIdx.x; k < kt; k += kMaskThreads) {
+            sbox[k] = make_boxp<false>(boxes_pool + (size_t)(k0 + k) * 7, nullptr);
+            if (!kSame) sfirst[k] = make_boxp<false>(boxes_first + (size_t)(k0 + k) * 7, nullptr);
+        }
+        __syncthreads();
+        for (int k = 0; k < kt; k++) {
+            const BoxP bp = sbox[k];
+            unsigned nib = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const bool h = in_box<false>(x[j], y[j], z[j], bp);
+                nib |= (h ? 1u : 0u) << j;
+                if (kSame) { if (box_idx && h && res[j] < 0) res[j] = k0 + k; }
+            }
+            if (!kSame) {
+                const BoxP bf = sfirst[k];
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if (res[j] < 0 && in_box<false>(x[j], y[j], z[j], bf)) res[j] = k0 + k;
+            }
+            if (__any_sync(0xffffffffu, nib != 0)) {
+                const unsigned word = __reduce_or_sync(sub, nib << sh);
+                if ((lane & 7) == 0 && word != 0 && word0 < W) mask[(size_t)(k0 + k) * W + word0] = word;
+            }
+        }
+    }
+    if (box_idx) {
+        box_idx += (size_t)b * N;
+        if (vec_ok && n_valid == 4) {
+            *reinterpret_cast<int4 *>(box_idx + p0) = make_int4(res[0], res[1], res[2], res[3]);
         } else {
-            float *o = out + (size_t)s * D;
-            o[0] = px; o[1] = py; o[2] = pz;
-            for (int j = 0; j < C; j++) o[3 + j] = __ldg(feat + (size_t)src * C + j);
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (j < n_valid) box_idx[p0 + j] = res[j];
         }
-        if (pts_idx) pts_idx[bm * S + s] = src;
     }
+}
+
+__global__ void __launch_bounds__(256)
+pool_from_mask_kernel(const float *__restrict__ xyz, const float *__restrict__ boxes, const float *__restrict__ feat,
+                      const unsigned *__restrict__ mask, float *__restrict__ pooled, int *__restrict__ empty,
+                      int *__restrict__ pts_idx, int N, int M, int W, int S, int C, int canonical) {
+    extern __shared__ int smem_i[];
+    int *flist = smem_i;                  // [S]
+    __shared__ int wsum[8];
+    __shared__ int s_total;
+    __shared__ BoxP sb;
+    const int m = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t bm = (size_t)b * M + m;
+    xyz += (size_t)b * N * 3;
+    feat += (size_t)b * N * C;
+    mask += bm * W;
+    if (tid == 0) sb = make_boxp<false>(boxes + bm * 7, nullptr);
+    // contiguous word range per thread -> ordered positions from one block-wide exclusive scan of popcounts
+    const int per = (W + 255) / 256;
+    const int w0 = min(W, tid * per), w1 = min(W, w0 + per);
+    int cnt = 0;
+    for (int w = w0; w < w1; w++) cnt += __popc(__ldg(mask + w));
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    int base = 0;
+    for (int w = 0; w < warp; w++) base += wsum[w];
+    if (tid == 255) s_total = base + incl;
+    int pos = base + incl - cnt;
+    for (int w = w0; w < w1 && pos < S; w++) {
+        unsigned word = __ldg(mask + w);
+        while (word && pos < S) {
+            const int bit = __ffs(word) - 1;
+            flist[pos++] = w * 32 + bit;
+            word &= word - 1;
+        }
+    }
+    __syncthreads();
+    const int total = min(s_total, S);
+    pool_emit(xyz, feat, pooled, empty, pts_idx, flist, total, bm, S, C, canonical, sb);
 }
 
 }  // namespace mgar
@@ -169,4 +308,47 @@ extern "C" int mgar_roipoint_pool(const float *xyz, const float *boxes, const fl
                                                                         N, M, S, C, cap, canonical);
     count_launch();
     return check_launch("roipoint_pool");
+}
+
+extern "C" size_t mgar_box_mask_words(int N) { return (size_t)((N + 31) / 32); }
+
+extern "C" int mgar_box_masks(const float *boxes_first, const float *boxes_pool, const float *pts, int *box_idx,
+                              unsigned *mask, int B, int M, int N, void *stream) {
+    MGAR_REQUIRE(B >= 0 && M >= 0 && N >= 0, "box_masks: negative size");
+    if (B == 0 || N == 0 || M == 0) {
+        if (box_idx && B > 0 && N > 0) MGAR_CUDA(cudaMemsetAsync(box_idx, 0xff, (size_t)B * N * 4, (cudaStream_t)stream));
+        return MGAR_OK;
+    }
+    MGAR_REQUIRE(pts && boxes_pool && mask, "box_masks: null pointer");
+    MGAR_REQUIRE(!box_idx || boxes_first, "box_masks: box_idx wanted but boxes_first is null");
+    MGAR_REQUIRE(B <= 65535, "box_masks: B=%d exceeds grid.y limit", B);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int W = (N + 31) / 32;
+    MGAR_CUDA(cudaMemsetAsync(mask, 0, (size_t)B * M * W * sizeof(unsigned), st));
+    const int vec_ok = ((reinterpret_cast<uintptr_t>(pts) & 15) == 0) && (!box_idx || (reinterpret_cast<uintptr_t>(box_idx) & 15) == 0) &&
+                       (N % 4 == 0);
+    dim3 grid(div_up(N, kMaskThreads * 4), B);
+    if (!box_idx || boxes_first == boxes_pool)
+        box_mask_kernel<true><<<grid, kMaskThreads, 0, st>>>(boxes_first, boxes_pool, pts, box_idx, mask, M, N, W, vec_ok);
+    else
+        box_mask_kernel<false><<<grid, kMaskThreads, 0, st>>>(boxes_first, boxes_pool, pts, box_idx, mask, M, N, W, vec_ok);
+    count_launch();
+    return check_launch("box_masks");
+}
+
+extern "C" int mgar_roipoint_pool_from_masks(const float *xyz, const float *boxes, const float *feat, const unsigned *mask,
+                                             float *pooled, int *empty, int *pts_idx, int B, int N, int M, int S, int C,
+                                             int canonical, void *stream) {
+    MGAR_REQUIRE(B >= 0 && N >= 0 && M >= 0 && S >= 0 && C >= 0, "roipoint_pool_from_masks: negative size");
+    if (B == 0 || M == 0) return MGAR_OK;
+    MGAR_REQUIRE(pooled && empty && boxes && mask && (xyz || N == 0) && (feat || C == 0 || N == 0), "roipoint_pool_from_masks: null pointer");
+    MGAR_REQUIRE(B <= 65535, "roipoint_pool_from_masks: B=%d exceeds grid.y limit", B);
+    const size_t smem = (size_t)(S > 0 ? S : 1) * sizeof(int);
+    MGAR_REQUIRE(smem <= 200 * 1024, "roipoint_pool_from_masks: num_sampled_points=%d does not fit in shared memory", S);
+    if (smem > 48 * 1024) MGAR_CUDA(cudaFuncSetAttribute(pool_from_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid(M, B);
+    pool_from_mask_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(xyz, boxes, feat, mask, pooled, empty, pts_idx, N, M,
+                                                                     (N + 31) / 32, S, C, canonical);
+    count_launch();
+    return check_launch("roipoint_pool_from_masks");
 }

@@ -47,3 +47,33 @@ def ball_query_uniform(radius, nsample, xyz, new_xyz, n, m):
         _lib.check(_lib.lib().mgar_ball_query_stack(B, M, float(radius), int(nsample), ptr(new_xyz), 0, ptr(xyz), xs, 0,
                                                     int(n), int(m), ptr(idx), 1, stream_of(xyz)), "ball_query_uniform")
     return idx
+
+
+def box_masks(points, boxes, pool_boxes=None, want_box_idx=True):
+    """points (B,N,3), boxes (B,M,7) -> (box_idx (B,N) int32 first-hit or None, mask (B,M,ceil(N/32)) int32 bit mask of
+    the points inside each pooling box).  One pass over the points for all boxes; pool_boxes = enlarged boxes when
+    the pooling boxes differ from the detection boxes."""
+    need_cuda(points=points, boxes=boxes, pool_boxes=pool_boxes)
+    need_dtype(torch.float32, points=points, boxes=boxes, pool_boxes=pool_boxes)
+    B, N, M = points.shape[0], points.shape[1], boxes.shape[1]
+    pool_boxes = boxes if pool_boxes is None else pool_boxes
+    box_idx = torch.empty((B, N), dtype=torch.int32, device=points.device) if want_box_idx else None
+    mask = torch.empty((B, M, (N + 31) // 32), dtype=torch.int32, device=points.device)
+    with on_device(points):
+        _lib.check(_lib.lib().mgar_box_masks(ptr(boxes), ptr(pool_boxes), ptr(points), ptr(box_idx), ptr(mask), B, M, N,
+                                             stream_of(points)), "box_masks")
+    return box_idx, mask
+
+
+def roipoint_pool_from_masks(points, point_features, pool_boxes, mask, num_sampled_points, canonical=True):
+    """-> pooled (B,M,S,3+C) (canonical frame of each box when `canonical`), empty (B,M) int32; same result as
+    roipoint_pool3d_cuda.forward on the same (enlarged) boxes."""
+    need_cuda(points=points, point_features=point_features, pool_boxes=pool_boxes, mask=mask)
+    B, N, M, C, S = points.shape[0], points.shape[1], pool_boxes.shape[1], point_features.shape[2], int(num_sampled_points)
+    pooled = torch.empty((B, M, S, 3 + C), dtype=torch.float32, device=points.device)
+    empty = torch.empty((B, M), dtype=torch.int32, device=points.device)
+    with on_device(points):
+        _lib.check(_lib.lib().mgar_roipoint_pool_from_masks(ptr(points), ptr(pool_boxes), ptr(point_features), ptr(mask),
+                                                            ptr(pooled), ptr(empty), 0, B, N, M, S, C, 1 if canonical else 0,
+                                                            stream_of(points)), "roipoint_pool_from_masks")
+    return pooled, empty

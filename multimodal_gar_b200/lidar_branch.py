@@ -11,6 +11,8 @@ stack layout (xyz_batch_cnt = [S] * persons).
 Frames are independent: `shard_frames` hands each rank a contiguous block of frames and no
 collective is needed in the forward pass.
 """
+import os
+
 import torch
 import torch.nn as nn
 
@@ -83,10 +85,22 @@ class PointPersonEncoder(nn.Module):
         mark = mark or (lambda name: None)
         B, M = boxes.shape[0], boxes.shape[1]
         S, P = self.num_sampled_points, self.npoint
-        box_idx = roiaware_pool3d_utils.points_in_boxes_gpu(points, boxes)          # (B,N) first box or -1
-        mark('points_in_boxes')
-        pooled, empty = self.pool(points, point_features, boxes)                    # (B*M,S,3+C) canonical frame
-        mark('roipoint_pool')
+        if self.fused_canonical and os.environ.get("MGAR_POOL", "mask") == "mask":
+            # one pass over the points for all boxes (first-hit index + in-box bit masks), then per-box gather
+            C = point_features.shape[2]
+            same = all(w == 0 for w in self.pool_extra_width)
+            big = boxes if same else box_utils.enlarge_box3d(boxes.reshape(-1, 7), self.pool_extra_width).view(B, M, 7).contiguous()
+            box_idx, mask = fastpath.box_masks(points.contiguous(), boxes.contiguous(), None if same else big)
+            mark('points_in_boxes')
+            pooled, empty = fastpath.roipoint_pool_from_masks(points.contiguous(), point_features.contiguous(), big.contiguous(),
+                                                              mask, S)
+            pooled = pooled.view(B * M, S, 3 + C)
+            mark('roipoint_pool')
+        else:
+            box_idx = roiaware_pool3d_utils.points_in_boxes_gpu(points, boxes)      # (B,N) first box or -1
+            mark('points_in_boxes')
+            pooled, empty = self.pool(points, point_features, boxes)                # (B*M,S,3+C) canonical frame
+            mark('roipoint_pool')
         g = self.sa.groupers[0]
         packed = None if (self.training or torch.is_grad_enabled()) else self.sa._pack(pooled.device)[0]
         C = pooled.shape[2] - 3

@@ -112,6 +112,36 @@ def test_roipoint_pool3d_fused_canonical(cuda):
     np.testing.assert_array_equal(got[..., 3], want_c[..., 3])
 
 
+@pytest.mark.parametrize("N,M,S,extra", [(4096, 12, 128, 0.0), (4099, 12, 64, 0.2), (65536, 40, 512, 0.0), (1000, 3, 16, 1.0),
+                                         (33, 2, 8, 0.0)])
+def test_mask_pooling_equals_single_kernel_pooling_and_points_in_boxes(cuda, N, M, S, extra):
+    """Two-pass pooling (box_masks + roipoint_pool_from_masks) against the one-kernel path, the first-hit kernel and
+    the oracle: bit masks, box_idx, pooled rows (canonical and raw), empty flags - all bit-exact."""
+    from multimodal_gar_b200 import fastpath
+    from multimodal_gar_b200.pcdet.utils import box_utils
+    pts, boxes = synthetic.make_batch(N + M, 2, N=N, M=M, density_scale=0.5 if N < 60000 else 1.0, empty_frac=0.15)
+    xyz, feat = T(pts[..., :3], cuda), T(pts[..., 3:4], cuda)
+    bx = T(boxes, cuda)
+    big = box_utils.enlarge_box3d(bx.reshape(-1, 7), (extra, extra, extra)).view(2, M, 7).contiguous()
+    box_idx, mask = fastpath.box_masks(xyz, bx, None if extra == 0.0 else big)
+    assert torch.equal(box_idx, roiaware_pool3d_utils.points_in_boxes_gpu(xyz, bx))
+    # masks against the (M,N) in-box matrix of the GPU semantics
+    x_np = np.ascontiguousarray(pts[..., :3])
+    big_np = big.cpu().numpy()
+    bits = np.unpackbits(mask.cpu().numpy().view(np.uint8).reshape(2, M, -1), axis=-1, bitorder="little")[..., :N]
+    for b in range(2):
+        want = O.in_box_mask_gpu_sem(x_np[b], big_np[b])
+        amb = O.in_box_ambiguous(x_np[b], big_np[b])
+        assert ((bits[b] != want) & ~amb.astype(bool)).sum() == 0
+    for canonical in (True, False):
+        pooled, empty = fastpath.roipoint_pool_from_masks(xyz, feat, big, mask, S, canonical=canonical)
+        p2 = torch.zeros((2, M, S, 4), device=cuda)
+        e2 = torch.zeros((2, M), dtype=torch.int32, device=cuda)
+        roipoint_pool3d_cuda.forward(xyz, big, feat, p2, e2, canonical=canonical)
+        assert torch.equal(empty, e2)
+        assert torch.equal(pooled, p2)
+
+
 @pytest.mark.parametrize("n,m", [(1, 1), (31, 31), (128, 64), (200, 64), (300, 300), (512, 512), (777, 100),
                                  (1024, 128), (1500, 96), (2500, 40), (5000, 64), (9000, 33), (20000, 16)])
 def test_fps_batch_with_ties(cuda, n, m):
