@@ -10,6 +10,6 @@ timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/bench.json 2> gpu
 CMD="python bench.py --steps 2 --warmup 1 --no-cpu-baseline"
 timeout 600 $CMD > gpurun_out/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu.log 2>&1; echo "ncu list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"sa_mlp_tc|ball_query|fps_|roipoint_pool|points_in_boxes" -s 5 -c 5 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"sa_mlp_tc|ball_query|fps_|pool_from_mask|box_mask" -s 5 -c 5 \
     -o gpurun_out/prof_full -f $CMD > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"; tail -3 gpurun_out/ncu_full.log
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"; cut -c1-300 gpurun_out/bench_ref.json
