@@ -1,0 +1,99 @@
+"""Distance Aware Fusion Module, batched (the step right after the LiDAR hot path).
+
+Reference: `FusionAttention_mat` (/root/reference/model/gat_model.py:427-511) applied per frame inside a Python
+loop by `GAR_Fusion_Net3.forward` (:1396-1475, FUSION == 'Attention_mat': two modules, then an element-wise max
+of the RGB and LiDAR streams).  Same parameter names and shapes, so reference checkpoints load unchanged.
+
+Here every frame of the batch goes through at once: the six 512x512 projections and the four FFN linears of a
+module are single `(B*n, 512) x (512, 512)` library GEMMs, the n x n attention pieces are batched, and frames with
+fewer persons than the padded width are handled by masking keys with -inf before each softmax, so that
+`out[b, :n_b]` is what the reference loop computes for frame b (tests/test_dafm.py pins this against the
+reference class itself).  Note two reference quirks that are kept: both streams use E_r = softmax(-De/sigma)
+(Dg is accepted but unused, `E_l = Dg` is dead code :499), and softmax runs over keys (dim=1 of the (n, n) map).
+"""
+import torch
+import torch.nn as nn
+
+
+def generalized_box_iou(boxes):
+    """torchvision.ops.generalized_box_iou(b, b) batched: boxes (..., n, 4) as (x1, y1, x2, y2) -> (..., n, n)."""
+    a, b = boxes.unsqueeze(-2), boxes.unsqueeze(-3)
+    area = (boxes[..., 2] - boxes[..., 0]) * (boxes[..., 3] - boxes[..., 1])
+    lt = torch.max(a[..., :2], b[..., :2])
+    rb = torch.min(a[..., 2:], b[..., 2:])
+    wh = (rb - lt).clamp(min=0)
+    inter = wh[..., 0] * wh[..., 1]
+    union = area.unsqueeze(-1) + area.unsqueeze(-2) - inter
+    iou = inter / union
+    lti = torch.min(a[..., :2], b[..., :2])
+    rbi = torch.max(a[..., 2:], b[..., 2:])
+    whi = (rbi - lti).clamp(min=0)
+    areai = whi[..., 0] * whi[..., 1]
+    return iou - (areai - union) / areai
+
+
+def _masked_softmax(x, key_valid):
+    """softmax over the last dim with invalid keys removed; x (B,n,n), key_valid (B,n) bool or None."""
+    if key_valid is not None:
+        x = x.masked_fill(~key_valid.unsqueeze(1), float("-inf"))
+    return torch.softmax(x, dim=-1)
+
+
+class FusionAttentionMat(nn.Module):
+    """`FusionAttention_mat` (gat_model.py:427-511).  forward(R, L, Dg, De[, valid]) -> (R', L').
+
+    Unbatched (n, D) inputs reproduce the reference call exactly; batched (B, n, D) inputs take `valid` (B, n) bool
+    (True = real person); rows of padded persons come out as zeros."""
+
+    def __init__(self, input_dim=512, out_dim=512, sigma=10):
+        super().__init__()
+        self.input_dim, self.out_dim, self.sigma = input_dim, out_dim, sigma
+        shape = [input_dim, out_dim]
+        for s in ("r", "l"):
+            for n in ("WQ", "WK", "WV"):
+                p = nn.Parameter(torch.zeros(shape))
+                torch.nn.init.kaiming_normal_(p)
+                setattr(self, "%s_%s" % (n, s), p)
+            setattr(self, "LN_%s_1" % s, nn.LayerNorm([out_dim]))
+            setattr(self, "FFN_%s" % s, nn.Sequential(nn.Linear(out_dim, out_dim), nn.ReLU(), nn.Linear(out_dim, out_dim)))
+            setattr(self, "LN_%s_2" % s, nn.LayerNorm([out_dim]))
+
+    def _stream(self, q_src, kv_src, E, valid, s):
+        WQ, WK, WV = getattr(self, "WQ_" + s), getattr(self, "WK_" + s), getattr(self, "WV_" + s)
+        Q, K, V = q_src @ WQ, kv_src @ WK, kv_src @ WV
+        att = _masked_softmax((Q @ K.transpose(-1, -2)) * E / self.out_dim ** 0.5, valid)
+        x = getattr(self, "LN_%s_1" % s)(att @ V + kv_src)
+        x = x + getattr(self, "FFN_" + s)(x)
+        return getattr(self, "LN_%s_2" % s)(x)
+
+    def forward(self, R, L, Dg, De, valid=None):
+        squeeze = R.dim() == 2
+        if squeeze:
+            R, L, De = R.unsqueeze(0), L.unsqueeze(0), De.unsqueeze(0)
+            valid = None if valid is None else valid.unsqueeze(0)
+        E = _masked_softmax(-(De / self.sigma), valid)
+        Rp = self._stream(L, R, E, valid, "r")          # queries from LiDAR, keys / values from RGB (:480-482)
+        Lp = self._stream(R, L, E, valid, "l")          # queries from RGB, keys / values from LiDAR (:495-497)
+        if valid is not None:
+            keep = valid.unsqueeze(-1)
+            Rp, Lp = torch.where(keep, Rp, torch.zeros_like(Rp)), torch.where(keep, Lp, torch.zeros_like(Lp))
+        return (Rp[0], Lp[0]) if squeeze else (Rp, Lp)
+
+
+class DistanceAwareFusion(nn.Module):
+    """FUSION == 'Attention_mat' of `GAR_Fusion_Net3.forward` (gat_model.py:1467-1475), all frames at once:
+    (RGB_feature, LiDAR_feature (B,MNP,D), bboxes (B,MNP,4), bboxes3d (B,MNP,7), valid (B,MNP)) -> fused (B,MNP,D),
+    zeros in padded rows.  Module names follow the reference (`AttFusModule1`, `AttFusModule2`)."""
+
+    def __init__(self, dim=512, sigma=10):
+        super().__init__()
+        self.AttFusModule1 = FusionAttentionMat(dim, dim, sigma)
+        self.AttFusModule2 = FusionAttentionMat(dim, dim, sigma)
+
+    def forward(self, rgb, lidar, bboxes, bboxes3d, valid):
+        from .lidar_backbone import pairwise_euclidean_distance
+        Dg = generalized_box_iou(bboxes)
+        De = pairwise_euclidean_distance(bboxes3d[..., :3])
+        R, L = self.AttFusModule1(rgb, lidar, Dg, De, valid)
+        R, L = self.AttFusModule2(R, L, Dg, De, valid)
+        return torch.maximum(R, L)

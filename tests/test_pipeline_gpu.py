@@ -182,3 +182,36 @@ def test_host_frame_pipeline_matches_direct_calls(cuda):
             want.append(enc(*[t.to(cuda) for t in h]).cpu())
     for o, w in zip(outs, want):
         assert torch.equal(o, w)
+
+
+def test_config3_lidar_branch_plus_dafm_forward_is_frame_sharded(cuda):
+    """configs[2] shape at reduced batch: 80 persons per frame (zero-padded to 100 proposals), full LiDAR branch +
+    Linear 128->512 + two batched DAFM modules on synthetic RGB features; a frame's fused features do not depend on
+    the other frames of its batch (what lets frames shard across GPUs with no collective)."""
+    from multimodal_gar_b200 import dafm, lidar_backbone as LB
+    B, M, MNP = 3, 80, 100
+    pts, boxes, xyz, feat, bx = _inputs(21, B, 65536, M, cuda, density_scale=0.6)
+    padded = torch.zeros((B, MNP, 7), device=cuda)
+    padded[:, :M] = bx
+    torch.manual_seed(9)
+    net = LB.PointLiDARBackbone().to(cuda).eval()
+    fus = dafm.DistanceAwareFusion(512).to(cuda).eval()
+    rgb = torch.randn((B, MNP, 512), device=cuda)
+    bb2 = torch.rand((B, MNP, 2), device=cuda) * 500
+    bboxes = torch.cat([bb2, bb2 + 20 + 60 * torch.rand((B, MNP, 2), device=cuda)], dim=-1)
+    pid = torch.full((B, MNP), -1, dtype=torch.int64, device=cuda)
+    pid[:, :M] = torch.arange(M, device=cuda)
+    pid[1, 50:] = -1                                              # frame 1 has only 50 persons
+    with torch.no_grad():
+        lidar = net(dict(points=T(pts, cuda), gt_bboxes3d=padded))
+        d = LB.dafm_lidar_inputs(lidar, padded, pid)
+        assert d["person_num"] == [80, 50, 80]
+        fused = fus(rgb, d["feature"], bboxes, padded, d["valid"])
+        assert fused.shape == (B, MNP, 512) and torch.isfinite(fused).all()
+        assert (fused[1, 50:] == 0).all() and (fused[0, 80:] == 0).all()
+        for b in range(B):
+            one = net(dict(points=T(pts[b:b + 1], cuda), gt_bboxes3d=padded[b:b + 1]))
+            d1 = LB.dafm_lidar_inputs(one, padded[b:b + 1], pid[b:b + 1])
+            f1 = fus(rgb[b:b + 1], d1["feature"], bboxes[b:b + 1], padded[b:b + 1], d1["valid"])
+            assert torch.equal(one, lidar[b:b + 1])
+            assert torch.allclose(f1, fused[b:b + 1], rtol=1e-4, atol=1e-4)   # library GEMMs: batch size changes the kernel
