@@ -88,6 +88,13 @@ __device__ __forceinline__ float max32(const uint32_t (&v)[32]) {
     return max3(a, b, fmaxf(__uint_as_float(v[30]), __uint_as_float(v[31])));
 }
 
+#ifdef MGAR_TC16_TRACE
+__device__ long long g_tc16_trace[32 * 16];        // timeline of CTA 0, local tiles 100..131 (debug build only)
+#define TR(slot, i) do { if (blockIdx.x == 0 && lane == 0 && (i) >= 100 && (i) < 132) g_tc16_trace[((i) - 100) * 16 + (slot)] = clock64(); } while (0)
+#else
+#define TR(slot, i) do { } while (0)
+#endif
+
 template <int C0>
 __global__ void __launch_bounds__(kThreads, 1)
 sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcBound BD, const __grid_constant__ TcArgs A) {
@@ -196,6 +203,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         for (int i = 0; i < my_tiles; i++) {
             const int t = i % kAcc, u = i / kAcc;
             mbar_wait(TFULL(t), u & 1);
+            if (warp == 0) TR(12, i);
             tc_fence_after();
             const float4 inv = *reinterpret_cast<const float4 *>(&s_inv[i % kRing][0]);
             const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
@@ -219,6 +227,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             }
             tc_fence_before();
             mbar_arrive_relaxed(TEMPTY(t));
+            if (warp == 0) TR(13, i);
             const float sq[4] = {inv.x, inv.y, inv.z, inv.w};
             // BatchNorm affine + ReLU of the max over the 32 samples (exact power-of-two rescale)
             float res[4];
@@ -258,7 +267,9 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         for (int i = (warp == 4 ? 0 : 1); i < my_tiles; i += 2) {
             const int s = i % kStages, j = i / kStages, t = i % kAcc, u = i / kAcc;
             mbar_wait(FULL(s), j & 1);
+            TR(10, i);
             mbar_wait(TEMPTY(t), (u & 1) ^ 1);
+            TR(11, i);
             tc_fence_after();
             const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kHBytes;
             const uint64_t bd_hi = make_desc(b_hi), bd_lo = make_desc(b_hi + kHBytes);
@@ -284,7 +295,9 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         for (int i = 0; i < my_tiles; i++) {
             const int xs = i & 1, jx = i >> 1;
             mbar_wait(XFULL(xs), jx & 1);
+            TR(8, i);
             mbar_wait(DEMPTY(xs), (jx & 1) ^ 1);
+            TR(9, i);
             tc_fence_after();
             const uint32_t x_hi = x_stage0 + (uint32_t)xs * 2 * kXBytes;
             const uint64_t xd_hi = make_desc_k8(x_hi), xd_lo = make_desc_k8(x_hi + kXBytes);
@@ -370,12 +383,15 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             x[C0] = down;                                        // multiplies the folded BatchNorm shift
             const float k0[4] = {x[0], x[1], x[2], x[3]}, k1[4] = {x[4], x[5], x[6], x[7]};
             const uint32_t x_hi = x_stage0 + (uint32_t)xs * 2 * kXBytes, x_lo = x_hi + kXBytes;
+            if (pw == 0) TR(0, i);
             mbar_wait(XEMPTY(xs), (jx & 1) ^ 1);
+            if (pw == 0) TR(1, i);
             sts_split4(x_hi + k8_off(r, 0), x_lo + k8_off(r, 0), k0);
             sts_split4(x_hi + k8_off(r, 1), x_lo + k8_off(r, 1), k1);
             if (lane == 0) s_inv[i % kRing][pw] = up;
             fence_async_smem();
             mbar_arrive(XFULL(xs));
+            if (pw == 0) TR(2, i);
         };
 
         int iv_a = -1, em_a = 0, iv_b = -1, em_b = 0;
@@ -395,7 +411,9 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
                 load_idx(i + 6, iv_a, em_a);                    // indices three own tiles ahead
             }
             const int s = i % kStages, j = i / kStages;
+            if (pw == 0) TR(3, i);
             mbar_wait(DFULL(g), k & 1);
+            if (pw == 0) TR(4, i);
             tc_fence_after();
             uint32_t h0[32], h1[32];
             const uint32_t d1 = tmem + ((uint32_t)(pw * 32) << 16) + kTmD1 + (uint32_t)(g * 64);
@@ -404,6 +422,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             tc_wait_ld();
             tc_fence_before();
             mbar_arrive_relaxed(DEMPTY(g));                     // layer 1 of tile i+2 may overwrite D1 now
+            if (pw == 0) TR(5, i);
 
             const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kHBytes, b_lo = b_hi + kHBytes;
             uint32_t hi[16], lo[16];
@@ -411,6 +430,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             for (int p = 0; p < 16; p++)
                 split_relu_h2(__uint_as_float(h0[2 * p]), __uint_as_float(h0[2 * p + 1]), hi[p], lo[p]);
             mbar_wait(EMPTY(s), (j & 1) ^ 1);
+            if (pw == 0) TR(6, i);
 #pragma unroll
             for (int half = 0; half < 2; half++) {
                 if (half == 1) {
@@ -429,6 +449,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             }
             fence_async_smem();          // generic-proxy stores -> visible to the tensor core (async proxy)
             mbar_arrive(FULL(s));
+            if (pw == 0) TR(7, i);
         }
     }
 
@@ -451,11 +472,27 @@ int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cu
         for (int c = 0; c < C0; c++) BD.wmax[c] = fmaxf(BD.wmax[c], fabsf(L1.w[c][o]));
         BD.shmax = fmaxf(BD.shmax, fabsf(L1.sh[o]));
     }
+#ifdef MGAR_TC16_TRACE
+#define TC16_TRACE_DUMP                                                                        \
+    {                                                                                          \
+        static long long h[32 * 16];                                                           \
+        cudaStreamSynchronize(st);                                                             \
+        cudaMemcpyFromSymbol(h, g_tc16_trace, sizeof(h));                                      \
+        for (int i = 0; i < 32; i++) {                                                         \
+            fprintf(stderr, "tc16trace %d", 100 + i);                                          \
+            for (int q = 0; q < 14; q++) fprintf(stderr, " %lld", h[i * 16 + q] ? h[i * 16 + q] - h[10] : -1); \
+            fprintf(stderr, "\n");                                                             \
+        }                                                                                      \
+    }
+#else
+#define TC16_TRACE_DUMP
+#endif
 #define MGAR_TC16_CASE(c0)                                                                                          \
     if (C0 == c0) {                                                                                                 \
         MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<c0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem)); \
         sa_mlp_tc16_kernel<c0><<<grid, kThreads, kSmem, st>>>(L1, BD, A);                                           \
         count_launch();                                                                                             \
+        TC16_TRACE_DUMP                                                                                             \
         return check_launch("sa_mlp_tc16");                                                                         \
     }
     MGAR_TC16_CASE(3) MGAR_TC16_CASE(4) MGAR_TC16_CASE(5) MGAR_TC16_CASE(6) MGAR_TC16_CASE(7)
