@@ -9,6 +9,8 @@
 // warp-step); one barrier later the per-warp lists are concatenated (exclusive scan of 32 counts),
 // the `k mod cnt` wrap is applied and xyz+features are gathered - optionally already in the
 // box's canonical frame (pointrcnn_head.py:121-129).  No (N,M) intermediate, no allocation.
+#include <stdlib.h>
+
 #include "mgar_common.cuh"
 
 namespace mgar {
@@ -231,6 +233,110 @@ box_mask_kernel(const float *__restrict__ boxes_first, const float *__restrict__
     }
 }
 
+// Same outputs with a per-frame BOX GRID: person boxes are small (R ~ 0.6 m) in a scene tens of metres wide, so a
+// point only needs the boxes whose conservative xy square covers its 1 m cell - typically none or one instead of
+// all M.  Every CTA rebuilds the frame's grid in shared memory (64 x 64 cells of 1 m around the origin, border cells
+// absorb everything outside; up to 8 box ids per cell) - M * ~9 shared atomics against 1024 points * M tests saved.
+// A hit sets its mask bit with one atomicOr (hits are ~0.5 % of the pairs); the first-hit index is the minimum hit.
+// Exactness: the cell index is a monotone function of x, and a box is entered into every cell between
+// cell(cx - R') and cell(cx + R') with R' >= |x - cx| of any in-box point (hypot of the half extents + margin, 0.1 %
+// slack), so an in-box point always finds its box; the in-box test itself is unchanged.  A cell that would overflow
+// switches the CTA to the exhaustive loop (crowds of overlapping boxes).
+constexpr int kGridN = 64, kGridCap = 8, kGridMaxBoxes = 255;
+constexpr size_t kGridSmem = (size_t)kGridN * kGridN * (4 + kGridCap) + (size_t)(kGridMaxBoxes + 1) * sizeof(BoxP);
+constexpr float kGridOrigin = -32.f, kGridInv = 1.f;     // cell = floor((x - origin) * inv), clamped to [0, 64)
+
+__device__ __forceinline__ int grid_cell(float x) {
+    const float c = floorf(__fmul_rn(__fsub_rn(x, kGridOrigin), kGridInv));
+    return (int)fminf(fmaxf(c, 0.f), (float)(kGridN - 1));          // NaN -> 0 (fmaxf drops it)
+}
+
+__global__ void __launch_bounds__(kMaskThreads)
+box_mask_grid_kernel(const float *__restrict__ boxes, const float *__restrict__ pts, int *__restrict__ box_idx,
+                     unsigned *__restrict__ mask, int M, int N, int W, int vec_ok) {
+    extern __shared__ int grid_sm[];
+    int *scnt = grid_sm;                                                              // [cells] boxes per cell
+    unsigned char (*sid)[kGridCap] = reinterpret_cast<unsigned char (*)[kGridCap]>(scnt + kGridN * kGridN);   // [cells][cap] box ids
+    BoxP *sbox = reinterpret_cast<BoxP *>(sid + kGridN * kGridN);                     // [M]
+    __shared__ int s_overflow;
+    const int b = blockIdx.y;
+    boxes += (size_t)b * M * 7;
+    pts += (size_t)b * N * 3;
+    mask += (size_t)b * M * W;
+    for (int i = threadIdx.x; i < kGridN * kGridN; i += kMaskThreads) scnt[i] = 0;
+    if (threadIdx.x == 0) s_overflow = 0;
+    __syncthreads();
+    for (int k = threadIdx.x; k < M; k += kMaskThreads) {
+        const BoxP bp = make_boxp<false>(boxes + (size_t)k * 7, nullptr);
+        sbox[k] = bp;
+        const float R = sqrtf(bp.tx * bp.tx + bp.ty * bp.ty) * 1.001f + 1e-6f;
+        const int x0 = grid_cell(bp.cx - R), x1 = grid_cell(bp.cx + R), y0 = grid_cell(bp.cy - R), y1 = grid_cell(bp.cy + R);
+        if (!(R == R) || !(bp.cx == bp.cx) || !(bp.cy == bp.cy) || (x1 - x0 + 1) * (y1 - y0 + 1) > 64) {
+            s_overflow = 1;                                            // NaN box or a huge one: exhaustive loop
+        } else {
+            for (int cy = y0; cy <= y1; cy++)
+                for (int cx = x0; cx <= x1; cx++) {
+                    const int old = atomicAdd(&scnt[cy * kGridN + cx], 1);
+                    if (old >= kGridCap) s_overflow = 1;
+                    else sid[cy * kGridN + cx][old] = (unsigned char)k;
+                }
+        }
+    }
+    __syncthreads();
+    const long long p0 = ((long long)blockIdx.x * kMaskThreads + threadIdx.x) * 4;
+    const int n_valid = p0 >= N ? 0 : (N - p0 >= 4 ? 4 : (int)(N - p0));
+    float x[4], y[4], z[4];
+    if (vec_ok && n_valid == 4) {
+        const float4 *v = reinterpret_cast<const float4 *>(pts + p0 * 3);
+        const float4 a = __ldg(v), bb = __ldg(v + 1), c = __ldg(v + 2);
+        x[0] = a.x; y[0] = a.y; z[0] = a.z;   x[1] = a.w; y[1] = bb.x; z[1] = bb.y;
+        x[2] = bb.z; y[2] = bb.w; z[2] = c.x; x[3] = c.y; y[3] = c.z; z[3] = c.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const bool ok = j < n_valid;
+            x[j] = ok ? __ldg(pts + (p0 + j) * 3 + 0) : nanf("");
+            y[j] = ok ? __ldg(pts + (p0 + j) * 3 + 1) : nanf("");
+            z[j] = ok ? __ldg(pts + (p0 + j) * 3 + 2) : nanf("");
+        }
+    }
+    int res[4] = {-1, -1, -1, -1};
+    if (s_overflow) {
+        for (int k = 0; k < M; k++) {
+            const BoxP bp = sbox[k];
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (in_box<false>(x[j], y[j], z[j], bp)) {
+                    if (res[j] < 0) res[j] = k;
+                    atomicOr(mask + (size_t)k * W + ((p0 + j) >> 5), 1u << ((p0 + j) & 31));
+                }
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int c = grid_cell(y[j]) * kGridN + grid_cell(x[j]);
+            const int cnt = scnt[c];
+            for (int q = 0; q < cnt; q++) {
+                const int k = sid[c][q];
+                if (in_box<false>(x[j], y[j], z[j], sbox[k])) {
+                    res[j] = res[j] < 0 ? k : min(res[j], k);
+                    atomicOr(mask + (size_t)k * W + ((p0 + j) >> 5), 1u << ((p0 + j) & 31));
+                }
+            }
+        }
+    }
+    if (box_idx) {
+        box_idx += (size_t)b * N;
+        if (vec_ok && n_valid == 4) {
+            *reinterpret_cast<int4 *>(box_idx + p0) = make_int4(res[0], res[1], res[2], res[3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (j < n_valid) box_idx[p0 + j] = res[j];
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 pool_from_mask_kernel(const float *__restrict__ xyz, const float *__restrict__ boxes, const float *__restrict__ feat,
                       const unsigned *__restrict__ mask, float *__restrict__ pooled, int *__restrict__ empty,
@@ -328,7 +434,12 @@ extern "C" int mgar_box_masks(const float *boxes_first, const float *boxes_pool,
     const int vec_ok = ((reinterpret_cast<uintptr_t>(pts) & 15) == 0) && (!box_idx || (reinterpret_cast<uintptr_t>(box_idx) & 15) == 0) &&
                        (N % 4 == 0);
     dim3 grid(div_up(N, kMaskThreads * 4), B);
-    if (!box_idx || boxes_first == boxes_pool)
+    if ((!box_idx || boxes_first == boxes_pool) && M <= kGridMaxBoxes && !getenv("MGAR_NO_BOX_GRID"))
+    {
+        MGAR_CUDA(cudaFuncSetAttribute(box_mask_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGridSmem));
+        box_mask_grid_kernel<<<grid, kMaskThreads, kGridSmem, st>>>(boxes_pool, pts, box_idx, mask, M, N, W, vec_ok);
+    }
+    else if (!box_idx || boxes_first == boxes_pool)
         box_mask_kernel<true><<<grid, kMaskThreads, 0, st>>>(boxes_first, boxes_pool, pts, box_idx, mask, M, N, W, vec_ok);
     else
         box_mask_kernel<false><<<grid, kMaskThreads, 0, st>>>(boxes_first, boxes_pool, pts, box_idx, mask, M, N, W, vec_ok);

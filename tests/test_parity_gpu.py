@@ -142,6 +142,52 @@ def test_mask_pooling_equals_single_kernel_pooling_and_points_in_boxes(cuda, N, 
         assert torch.equal(pooled, p2)
 
 
+def test_mask_pooling_box_grid_adversarial(cuda):
+    """The box-grid pass must never lose a hit: boxes stacked in one cell (overflow -> exhaustive loop), boxes and points
+    beyond the grid's +-32 m (border cells), boxes straddling cell borders, a huge box, a zero-padded box."""
+    from multimodal_gar_b200 import fastpath
+    rng = np.random.default_rng(3)
+    N = 20000
+    frames = []
+    # frame 0: twelve boxes on the same spot (cell overflow)
+    b0 = np.tile(np.array([[3.0, 4.0, 0.0, 0.8, 0.7, 1.8, 0.3]], np.float32), (12, 1))
+    b0[:, :2] += rng.normal(0, 0.05, (12, 2)).astype(np.float32)
+    # frame 1: boxes far outside the grid, on cell borders, one huge box, one zero box
+    b1 = np.array([[40.0, -45.0, 0.0, 0.9, 0.6, 1.7, 1.0], [-33.0, 31.9, 0.0, 0.9, 0.9, 1.7, -2.0], [5.0, 5.0, 0.0, 0.6, 0.6, 1.6, 0.0],
+                   [0.0, 0.0, 0.0, 30.0, 20.0, 3.0, 0.4], [0, 0, 0, 0, 0, 0, 0], [-31.99, -32.0, 0.2, 1.0, 1.0, 1.9, 0.7],
+                   [12.0, -7.0, 0.1, 0.5, 0.9, 1.5, 2.5], [12.3, -7.2, 0.1, 0.5, 0.9, 1.5, 2.6], [1e3, 1e3, 0.0, 0.5, 0.5, 1.5, 0.0],
+                   [2.0, 2.0, 0.0, 0.5, 0.5, 1.5, 0.0], [2.0, 3.0, 0.0, 0.5, 0.5, 1.5, 0.0], [3.0, 2.0, 0.0, 0.5, 0.5, 1.5, 0.0]], np.float32)
+    for boxes in (b0, b1):
+        pts = rng.uniform(-50, 50, (N, 3)).astype(np.float32)
+        pts[:, 2] = rng.uniform(-1, 1, N)
+        for k, bx in enumerate(boxes):                          # seed points inside / around every box
+            n = 150
+            loc = rng.uniform(-0.6, 0.6, (n, 3)).astype(np.float32) * np.maximum(bx[3:6], 0.1)
+            c, s_ = np.cos(bx[6]), np.sin(bx[6])
+            pts[k * n:(k + 1) * n, 0] = bx[0] + loc[:, 0] * c - loc[:, 1] * s_
+            pts[k * n:(k + 1) * n, 1] = bx[1] + loc[:, 0] * s_ + loc[:, 1] * c
+            pts[k * n:(k + 1) * n, 2] = bx[2] + loc[:, 2]
+        frames.append((pts, boxes))
+    xyz = T(np.stack([f[0] for f in frames]), cuda)
+    bx = T(np.stack([f[1] for f in frames]), cuda)
+    feat = T(rng.random((2, N, 1)).astype(np.float32), cuda)
+    box_idx, mask = fastpath.box_masks(xyz, bx)
+    assert torch.equal(box_idx, roiaware_pool3d_utils.points_in_boxes_gpu(xyz, bx))
+    assert (box_idx >= 0).sum() > 1000
+    pooled, empty = fastpath.roipoint_pool_from_masks(xyz, feat, bx, mask, 64, canonical=False)
+    p2 = torch.zeros((2, 12, 64, 4), device=cuda)
+    e2 = torch.zeros((2, 12), dtype=torch.int32, device=cuda)
+    roipoint_pool3d_cuda.forward(xyz, bx, feat, p2, e2)
+    assert torch.equal(empty, e2) and torch.equal(pooled, p2)
+    import os
+    os.environ["MGAR_NO_BOX_GRID"] = "1"                        # the exhaustive pass gives the same masks
+    try:
+        _, mask2 = fastpath.box_masks(xyz, bx)
+    finally:
+        del os.environ["MGAR_NO_BOX_GRID"]
+    assert torch.equal(mask, mask2)
+
+
 @pytest.mark.parametrize("n,m", [(1, 1), (31, 31), (128, 64), (200, 64), (300, 300), (512, 512), (777, 100),
                                  (1024, 128), (1500, 96), (2500, 40), (5000, 64), (9000, 33), (20000, 16)])
 def test_fps_batch_with_ties(cuda, n, m):
