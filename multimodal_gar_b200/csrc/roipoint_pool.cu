@@ -244,6 +244,7 @@ box_mask_kernel(const float *__restrict__ boxes_first, const float *__restrict__
 // switches the CTA to the exhaustive loop (crowds of overlapping boxes).
 constexpr int kGridN = 64, kGridCap = 8, kGridMaxBoxes = 255;
 constexpr size_t kGridSmem = (size_t)kGridN * kGridN * (4 + kGridCap) + (size_t)(kGridMaxBoxes + 1) * sizeof(BoxP);
+constexpr int kGridIters = 4;                              // point tiles (1024 points each) per CTA
 constexpr float kGridOrigin = -32.f, kGridInv = 1.f;     // cell = floor((x - origin) * inv), clamped to [0, 64)
 
 __device__ __forceinline__ int grid_cell(float x) {
@@ -283,56 +284,58 @@ box_mask_grid_kernel(const float *__restrict__ boxes, const float *__restrict__ 
         }
     }
     __syncthreads();
-    const long long p0 = ((long long)blockIdx.x * kMaskThreads + threadIdx.x) * 4;
-    const int n_valid = p0 >= N ? 0 : (N - p0 >= 4 ? 4 : (int)(N - p0));
-    float x[4], y[4], z[4];
-    if (vec_ok && n_valid == 4) {
-        const float4 *v = reinterpret_cast<const float4 *>(pts + p0 * 3);
-        const float4 a = __ldg(v), bb = __ldg(v + 1), c = __ldg(v + 2);
-        x[0] = a.x; y[0] = a.y; z[0] = a.z;   x[1] = a.w; y[1] = bb.x; z[1] = bb.y;
-        x[2] = bb.z; y[2] = bb.w; z[2] = c.x; x[3] = c.y; y[3] = c.z; z[3] = c.w;
-    } else {
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const bool ok = j < n_valid;
-            x[j] = ok ? __ldg(pts + (p0 + j) * 3 + 0) : nanf("");
-            y[j] = ok ? __ldg(pts + (p0 + j) * 3 + 1) : nanf("");
-            z[j] = ok ? __ldg(pts + (p0 + j) * 3 + 2) : nanf("");
+    for (int it = 0; it < kGridIters; it++) {   // several point tiles per CTA amortise the grid build
+        const long long p0 = (((long long)blockIdx.x * kGridIters + it) * kMaskThreads + threadIdx.x) * 4;
+        const int n_valid = p0 >= N ? 0 : (N - p0 >= 4 ? 4 : (int)(N - p0));
+        float x[4], y[4], z[4];
+        if (vec_ok && n_valid == 4) {
+            const float4 *v = reinterpret_cast<const float4 *>(pts + p0 * 3);
+            const float4 a = __ldg(v), bb = __ldg(v + 1), c = __ldg(v + 2);
+            x[0] = a.x; y[0] = a.y; z[0] = a.z;   x[1] = a.w; y[1] = bb.x; z[1] = bb.y;
+            x[2] = bb.z; y[2] = bb.w; z[2] = c.x; x[3] = c.y; y[3] = c.z; z[3] = c.w;
+        } else {
+    #pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const bool ok = j < n_valid;
+                x[j] = ok ? __ldg(pts + (p0 + j) * 3 + 0) : nanf("");
+                y[j] = ok ? __ldg(pts + (p0 + j) * 3 + 1) : nanf("");
+                z[j] = ok ? __ldg(pts + (p0 + j) * 3 + 2) : nanf("");
+            }
         }
-    }
-    int res[4] = {-1, -1, -1, -1};
-    if (s_overflow) {
-        for (int k = 0; k < M; k++) {
-            const BoxP bp = sbox[k];
-#pragma unroll
-            for (int j = 0; j < 4; j++)
-                if (in_box<false>(x[j], y[j], z[j], bp)) {
-                    if (res[j] < 0) res[j] = k;
-                    atomicOr(mask + (size_t)k * W + ((p0 + j) >> 5), 1u << ((p0 + j) & 31));
-                }
-        }
-    } else {
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int c = grid_cell(y[j]) * kGridN + grid_cell(x[j]);
-            const int cnt = scnt[c];
-            for (int q = 0; q < cnt; q++) {
-                const int k = sid[c][q];
-                if (in_box<false>(x[j], y[j], z[j], sbox[k])) {
-                    res[j] = res[j] < 0 ? k : min(res[j], k);
-                    atomicOr(mask + (size_t)k * W + ((p0 + j) >> 5), 1u << ((p0 + j) & 31));
+        int res[4] = {-1, -1, -1, -1};
+        if (s_overflow) {
+            for (int k = 0; k < M; k++) {
+                const BoxP bp = sbox[k];
+    #pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if (in_box<false>(x[j], y[j], z[j], bp)) {
+                        if (res[j] < 0) res[j] = k;
+                        atomicOr(mask + (size_t)k * W + ((p0 + j) >> 5), 1u << ((p0 + j) & 31));
+                    }
+            }
+        } else {
+    #pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int c = grid_cell(y[j]) * kGridN + grid_cell(x[j]);
+                const int cnt = scnt[c];
+                for (int q = 0; q < cnt; q++) {
+                    const int k = sid[c][q];
+                    if (in_box<false>(x[j], y[j], z[j], sbox[k])) {
+                        res[j] = res[j] < 0 ? k : min(res[j], k);
+                        atomicOr(mask + (size_t)k * W + ((p0 + j) >> 5), 1u << ((p0 + j) & 31));
+                    }
                 }
             }
         }
-    }
-    if (box_idx) {
-        box_idx += (size_t)b * N;
-        if (vec_ok && n_valid == 4) {
-            *reinterpret_cast<int4 *>(box_idx + p0) = make_int4(res[0], res[1], res[2], res[3]);
-        } else {
-#pragma unroll
-            for (int j = 0; j < 4; j++)
-                if (j < n_valid) box_idx[p0 + j] = res[j];
+        if (box_idx) {
+            int *box_idx_f = box_idx + (size_t)b * N;
+            if (vec_ok && n_valid == 4) {
+                *reinterpret_cast<int4 *>(box_idx_f + p0) = make_int4(res[0], res[1], res[2], res[3]);
+            } else {
+    #pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if (j < n_valid) box_idx_f[p0 + j] = res[j];
+            }
         }
     }
 }
@@ -437,6 +440,7 @@ extern "C" int mgar_box_masks(const float *boxes_first, const float *boxes_pool,
     if ((!box_idx || boxes_first == boxes_pool) && M <= kGridMaxBoxes && !getenv("MGAR_NO_BOX_GRID"))
     {
         MGAR_CUDA(cudaFuncSetAttribute(box_mask_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGridSmem));
+        grid.x = div_up(N, kMaskThreads * 4 * kGridIters);
         box_mask_grid_kernel<<<grid, kMaskThreads, kGridSmem, st>>>(boxes_pool, pts, box_idx, mask, M, N, W, vec_ok);
     }
     else if (!box_idx || boxes_first == boxes_pool)
