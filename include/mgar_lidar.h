@@ -86,6 +86,26 @@ MGAR_API int mgar_roipoint_pool_from_masks(const float *xyz, const float *boxes,
                                            float *pooled, int *empty, int *pts_idx, int B, int N, int M, int S, int C,
                                            int canonical, void *stream);
 
+/* ---- roiaware_pool3d: voxel pooling inside boxes ---------------------------------------------- */
+
+/* roiaware_pool3d_gpu / roiaware_pool3d_gpu_backward: roiaware_pool3d/src/roiaware_pool3d.cpp:20-96 (kernels
+ * roiaware_pool3d_kernel.cu:36-312).  rois (boxes_num,7), pts (pts_num,3), pts_feature (pts_num,channels) ->
+ * pts_idx_of_voxels (boxes_num,out_x,out_y,out_z,max_pts_each_voxel) int32 (slot 0 = count, then point indices in
+ * index order; ZERO-FILLED BY THE CALLER as in roiaware_pool3d_utils.py:71-72), argmax (…,channels) int32 (max
+ * pooling only; -1 = empty voxel), pooled_features (…,channels) written only for non-empty voxels (caller
+ * zero-fills).  pool_method 0 = max, 1 = avg.  workspace: mgar_roiaware_pool3d_workspace_bytes(boxes_num,pts_num)
+ * bytes of device scratch (the in-box bit masks; the reference cudaMallocs 32x as much per call).  out sizes are
+ * limited to 256 per axis: the reference packs the voxel index in 8 bits per axis and silently corrupts larger
+ * grids.  backward: grad_in (pts_num,channels) accumulated with atomics into the caller's zero-filled buffer. */
+MGAR_API size_t mgar_roiaware_pool3d_workspace_bytes(int boxes_num, int pts_num);
+MGAR_API int mgar_roiaware_pool3d_fwd(const float *rois, const float *pts, const float *pts_feature, int *argmax,
+                                      int *pts_idx_of_voxels, float *pooled_features, void *workspace, int boxes_num,
+                                      int pts_num, int channels, int max_pts_each_voxel, int out_x, int out_y,
+                                      int out_z, int pool_method, void *stream);
+MGAR_API int mgar_roiaware_pool3d_bwd(const int *pts_idx_of_voxels, const int *argmax, const float *grad_out,
+                                      float *grad_in, int boxes_num, int out_x, int out_y, int out_z, int channels,
+                                      int max_pts_each_voxel, int pool_method, void *stream);
+
 /* ---- pointnet2_stack: farthest point sampling ------------------------------------------------- */
 
 /* farthest_point_sampling_wrapper: pointnet2/pointnet2_stack/src/sampling.cpp:21-34

@@ -28,6 +28,9 @@ SIGNATURES = {
     "mgar_box_mask_words": [_i],
     "mgar_box_masks": [_p, _p, _p, _p, _p, _i, _i, _i, _p],
     "mgar_roipoint_pool_from_masks": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
+    "mgar_roiaware_pool3d_workspace_bytes": [_i, _i],
+    "mgar_roiaware_pool3d_fwd": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p],
+    "mgar_roiaware_pool3d_bwd": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p],
     "mgar_fps_batch": [_i, _i, _i, _p, _i, _p, _p, _p, _p],
     "mgar_fps_stack": [_i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_ball_query_stack": [_i, _i, _f, _i, _p, _p, _p, _i, _p, _i, _i, _p, _i, _p],
@@ -74,6 +77,7 @@ def lib():
         L.mgar_launch_count.restype = ctypes.c_ulonglong
         L.mgar_sa_mlp_train_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_box_mask_words.restype = ctypes.c_size_t
+        L.mgar_roiaware_pool3d_workspace_bytes.restype = ctypes.c_size_t
         _lib = L
     return _lib
 

@@ -36,9 +36,39 @@ def points_in_boxes_cpu(boxes, pts, pts_indices):
     return 1
 
 
-def forward(*args, **kwargs):
-    raise NotImplementedError("RoIAwarePool3d forward is outside the LiDAR hot path (SURVEY.md 8f-2)")
+def forward(rois, pts, pts_feature, argmax, pts_idx_of_voxels, pooled_features, pool_method):
+    """roiaware_pool3d_gpu (roiaware_pool3d.cpp:20-58).  rois (N,7), pts (npoints,3), pts_feature (npoints,C) f32
+    cuda; argmax (N,ox,oy,oz,C) i32, pts_idx_of_voxels (N,ox,oy,oz,max_pts) i32 ZERO-FILLED, pooled_features
+    (N,ox,oy,oz,C) f32 zero-filled, all caller-allocated; pool_method 0 = max, 1 = avg.  Returns 1."""
+    need_cuda(rois=rois, pts=pts, pts_feature=pts_feature, argmax=argmax, pts_idx_of_voxels=pts_idx_of_voxels,
+              pooled_features=pooled_features)
+    need_dtype(torch.float32, rois=rois, pts=pts, pts_feature=pts_feature, pooled_features=pooled_features)
+    need_dtype(torch.int32, argmax=argmax, pts_idx_of_voxels=pts_idx_of_voxels)
+    boxes_num, pts_num, channels = rois.size(0), pts.size(0), pts_feature.size(1)
+    max_pts = pts_idx_of_voxels.size(4)
+    out_x, out_y, out_z = pts_idx_of_voxels.size(1), pts_idx_of_voxels.size(2), pts_idx_of_voxels.size(3)
+    if pts_feature.size(0) != pts_num:                                       # roiaware_pool3d.cpp:45 assert
+        raise _lib.MgarError("pts_feature has %d rows for %d points" % (pts_feature.size(0), pts_num))
+    L = _lib.lib()
+    with on_device(pts):
+        nbytes = L.mgar_roiaware_pool3d_workspace_bytes(boxes_num, pts_num)
+        ws = torch.empty(max(nbytes, 4) // 4, dtype=torch.int32, device=pts.device)
+        _lib.check(L.mgar_roiaware_pool3d_fwd(ptr(rois), ptr(pts), ptr(pts_feature), ptr(argmax), ptr(pts_idx_of_voxels),
+                                              ptr(pooled_features), ptr(ws), boxes_num, pts_num, channels, max_pts,
+                                              out_x, out_y, out_z, int(pool_method), stream_of(pts)), "roiaware_pool3d forward")
+    return 1
 
 
-def backward(*args, **kwargs):
-    raise NotImplementedError("RoIAwarePool3d backward is outside the LiDAR hot path (SURVEY.md 8f-2)")
+def backward(pts_idx_of_voxels, argmax, grad_out, grad_in, pool_method):
+    """roiaware_pool3d_gpu_backward (roiaware_pool3d.cpp:61-96).  grad_out (N,ox,oy,oz,C) f32 -> accumulated into
+    the caller's zero-filled grad_in (npoints,C).  Returns 1."""
+    need_cuda(pts_idx_of_voxels=pts_idx_of_voxels, argmax=argmax, grad_out=grad_out, grad_in=grad_in)
+    need_dtype(torch.float32, grad_out=grad_out, grad_in=grad_in)
+    need_dtype(torch.int32, argmax=argmax, pts_idx_of_voxels=pts_idx_of_voxels)
+    boxes_num, out_x, out_y, out_z, max_pts = pts_idx_of_voxels.shape
+    channels = grad_out.size(4)
+    with on_device(grad_out):
+        _lib.check(_lib.lib().mgar_roiaware_pool3d_bwd(ptr(pts_idx_of_voxels), ptr(argmax), ptr(grad_out), ptr(grad_in),
+                                                       boxes_num, out_x, out_y, out_z, channels, max_pts, int(pool_method),
+                                                       stream_of(grad_out)), "roiaware_pool3d backward")
+    return 1

@@ -308,3 +308,87 @@ void orc_group_points_grad_stack(int B, int M, int C, int N, int nsample, const 
                     grad_out[((size_t)pt * C + c) * nsample + s];
     }
 }
+
+/* ---- RoI-aware voxel pooling ----------------------------------------------------
+ * roiaware_pool3d/src/roiaware_pool3d_kernel.cu:39-198 (forward) and :236-312 (backward).
+ * voxel index per axis (:62-68): int((local + d/2) / (d/out)) through `unsigned` with min/max against ints:
+ * negative ints wrap and land on out-1.  The CUDA float->int cast saturates and maps NaN to 0; restated here. */
+static unsigned voxel_axis(float local, float d, int out)
+{
+    float res = d / (float)out;
+    float v = (local + d / 2) / res;
+    int i;
+    if (v != v) i = 0;
+    else if (v >= 2147483648.0f) i = 2147483647;
+    else if (v <= -2147483648.0f) i = (-2147483647 - 1);
+    else i = (int)v;
+    unsigned u = (unsigned)i;
+    unsigned hi = (unsigned)(out - 1);
+    return u < hi ? u : hi;
+}
+
+/* lists (boxes,ox,oy,oz,max_pts) zero-filled by the caller; argmax / pooled as the reference leaves them
+ * (pooled only written for non-empty voxels).  pool_method 0 = max, 1 = avg. */
+void orc_roiaware_pool3d(const float *rois, const float *pts, const float *feat, int *argmax, int *lists,
+                         float *pooled, int boxes_num, int pts_num, int C, int max_pts, int ox, int oy, int oz,
+                         int pool_method)
+{
+    unsigned max_num = (unsigned)(max_pts - 1);
+    for (int b = 0; b < boxes_num; b++) {
+        const float *box = rois + (size_t)b * 7;
+        float cosa = cosf(-box[6]), sina = sinf(-box[6]);
+        int *vox = lists + (size_t)b * ox * oy * oz * max_pts;
+        for (int k = 0; k < pts_num; k++) {                        /* :88-103, point-index order */
+            const float *p = pts + (size_t)k * 3;
+            if (!in_box_cs(p, box, 1e-5f, 1, cosa, sina)) continue;
+            float sx = p[0] - box[0], sy = p[1] - box[1];
+            float lx = fmaf(sx, cosa, sy * (-sina)), ly = fmaf(sy, cosa, sx * sina), lz = p[2] - box[2];
+            unsigned xi = voxel_axis(lx, box[3], ox), yi = voxel_axis(ly, box[4], oy), zi = voxel_axis(lz, box[5], oz);
+            size_t base = (((size_t)xi * oy + yi) * oz + zi) * max_pts;
+            unsigned cnt = (unsigned)vox[base];
+            if (cnt < max_num) {
+                vox[base + cnt + 1] = k;
+                vox[base]++;
+            }
+        }
+        for (size_t v = 0; v < (size_t)ox * oy * oz; v++) {
+            const int *l = vox + v * max_pts;
+            size_t o = ((size_t)b * ox * oy * oz + v) * C;
+            for (int c = 0; c < C; c++) {
+                if (pool_method == 0) {                            /* :136-152 */
+                    int arg = -1;
+                    float best = -INFINITY;
+                    for (int k = 1; k <= l[0]; k++) {
+                        float f = feat[(size_t)l[k] * C + c];
+                        if (f > best) { best = f; arg = l[k]; }
+                    }
+                    if (arg != -1) pooled[o + c] = best;
+                    argmax[o + c] = arg;
+                } else {                                           /* :182-191 */
+                    float sum = 0;
+                    for (int k = 1; k <= l[0]; k++) sum += feat[(size_t)l[k] * C + c];
+                    if (l[0] > 0) pooled[o + c] = sum / l[0];
+                }
+            }
+        }
+    }
+}
+
+/* grad_in (pts_num,C) zero-filled by the caller; the reference accumulates with float atomics (order
+ * nondeterministic), this restatement in (box, voxel, channel, k) order. */
+void orc_roiaware_pool3d_backward(const int *lists, const int *argmax, const float *grad_out, float *grad_in,
+                                  int boxes_num, int ox, int oy, int oz, int C, int max_pts, int pool_method)
+{
+    size_t voxels = (size_t)boxes_num * ox * oy * oz;
+    for (size_t v = 0; v < voxels; v++)
+        for (int c = 0; c < C; c++) {
+            if (pool_method == 0) {                                /* :254-256 */
+                int a = argmax[v * C + c];
+                if (a != -1) grad_in[(size_t)a * C + c] += grad_out[v * C + c] * 1;
+            } else {                                               /* :279-283 */
+                const int *l = lists + v * max_pts;
+                float cur = 1 / fmaxf((float)l[0], 1.0f);
+                for (int k = 1; k <= l[0]; k++) grad_in[(size_t)l[k] * C + c] += grad_out[v * C + c] * cur;
+            }
+        }
+}

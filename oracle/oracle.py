@@ -111,6 +111,31 @@ def roipoint_pool3d(points, point_features, boxes3d, pool_extra_width, num_sampl
 
 
 # ---- FPS ---------------------------------------------------------------------------------
+def roiaware_pool3d(rois, pts, pts_feature, out_size, max_pts_each_voxel=128, pool_method="max"):
+    """RoIAwarePool3dFunction.forward, pcdet/ops/roiaware_pool3d/roiaware_pool3d_utils.py:54-92
+    -> pooled (N,ox,oy,oz,C), argmax (same, int32; zeros for avg), pts_idx_of_voxels (N,ox,oy,oz,max_pts)."""
+    rois, pts, feat = _f32(rois), _f32(pts), _f32(pts_feature)
+    ox, oy, oz = (out_size,) * 3 if isinstance(out_size, int) else out_size
+    Nb, P, C = rois.shape[0], pts.shape[0], feat.shape[1]
+    pooled = np.zeros((Nb, ox, oy, oz, C), dtype=np.float32)
+    argmax = np.zeros((Nb, ox, oy, oz, C), dtype=np.int32)
+    lists = np.zeros((Nb, ox, oy, oz, max_pts_each_voxel), dtype=np.int32)
+    lib().orc_roiaware_pool3d(_fp(rois), _fp(pts), _fp(feat), _ip(argmax), _ip(lists), _fp(pooled), Nb, P, C,
+                              max_pts_each_voxel, ox, oy, oz, {"max": 0, "avg": 1}[pool_method])
+    return pooled, argmax, lists
+
+
+def roiaware_pool3d_backward(lists, argmax, grad_out, num_pts, pool_method="max"):
+    """RoIAwarePool3dFunction.backward, roiaware_pool3d_utils.py:94-107 -> grad_in (num_pts, C)."""
+    lists, argmax, grad_out = _i32(lists), _i32(argmax), _f32(grad_out)
+    Nb, ox, oy, oz, max_pts = lists.shape
+    C = grad_out.shape[-1]
+    grad_in = np.zeros((num_pts, C), dtype=np.float32)
+    lib().orc_roiaware_pool3d_backward(_ip(lists), _ip(argmax), _fp(grad_out), _fp(grad_in), Nb, ox, oy, oz, C, max_pts,
+                                       {"max": 0, "avg": 1}[pool_method])
+    return grad_in
+
+
 def opt_n_threads(n):
     return lib().orc_opt_n_threads(int(n))
 

@@ -148,3 +148,22 @@ def test_oracle_equals_reference_gpu_ball_query_and_grouping():
         fixed[fixed[:, 0] == -1] = 0
         np.testing.assert_array_equal(O.grouping_operation(g["r_feat"], g["r_cnt"], fixed, g["r_ncnt"]),
                                       g["grp_%g_%d" % (r, K)])
+
+
+def test_oracle_equals_reference_gpu_roiaware_pool3d():
+    """RoIAwarePool3d: outputs of the unmodified reference kernels on a B200
+    (tests/golden/make_ref_roiaware_golden.py) against the C restatement - forward bit-exact, backward to the
+    order of the reference's float atomics."""
+    path = os.path.join(GOLD, "ref_roiaware.npz")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/ref_roiaware.npz not generated yet (needs one GPU run)")
+    g = np.load(path)
+    size, max_pts = tuple(int(v) for v in g["size"]), int(g["max_pts"])
+    for method in ("max", "avg"):
+        pooled, argmax, lists = O.roiaware_pool3d(g["boxes"], g["pts"], g["feat"], size, max_pts, method)
+        np.testing.assert_array_equal(lists, g[method + "_lists"])
+        np.testing.assert_array_equal(argmax, g[method + "_argmax"])
+        np.testing.assert_array_equal(pooled, g[method + "_pooled"])
+        assert lists[..., 0].max() == max_pts - 1 and (lists[..., 0] == 0).any()      # capped and empty voxels both present
+        gin = O.roiaware_pool3d_backward(lists, argmax, g[method + "_grad_out"], g["pts"].shape[0], method)
+        np.testing.assert_allclose(gin, g[method + "_grad_in"], rtol=1e-5, atol=1e-6)
