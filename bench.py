@@ -26,10 +26,12 @@ CFG = dict(N=65536, M=40, S=512, P=512, radius=0.3, K=32, C_in=1, mlp=(64, 128))
 METRIC = "JRDB-size LiDAR frames/s (box-pool+FPS+ballquery+group+MLP)"
 
 
-def algorithmic_bytes_per_frame(c=CFG):
-    """compulsory traffic, every tensor touched once (fp32/int32)."""
+def algorithmic_bytes_per_frame(c=CFG, keep_sa=True):
+    """compulsory traffic, every tensor touched once (fp32/int32).  keep_sa=False: the
+    (M*P, C2) per-centroid SA features stay on chip (max over a person's centroids inside the MLP kernel) and only
+    the (M, C2) person features are written."""
     N, M, S, P, K, C2 = c["N"], c["M"], c["S"], c["P"], c["K"], c["mlp"][-1]
-    return 16 * N + 28 * M + 4 * N + 16 * M * S + 4 * M * P + 4 * M * P * K + 4 * M * P * C2
+    return 16 * N + 28 * M + 4 * N + 16 * M * S + 4 * M * P + 4 * M * P * K + 4 * M * C2 * (P if keep_sa else 1)
 
 
 def mlp_flops_per_frame(c=CFG):
@@ -235,15 +237,16 @@ def run_reference(args, rank, world):
 
 
 # ---- native arm ---------------------------------------------------------------------------------------
-def stage_work(F):
+def stage_work(F, keep_sa=True):
     """Algorithmic bytes (SURVEY.md 8d per-stage figures) and flops of one step of F frames, per stage."""
     N, M, S, P, K, C2 = CFG["N"], CFG["M"], CFG["S"], CFG["P"], CFG["K"], CFG["mlp"][-1]
+    sa_out = 4 * M * C2 * (P if keep_sa else 1)
     return {
         "points_in_boxes": dict(bytes=F * (12 * N + 28 * M + 4 * N), flops=0),
         "roipoint_pool": dict(bytes=F * (16 * N + 28 * M + 16 * M * S + 4 * M), flops=0),
         "fps": dict(bytes=F * (12 * M * S + 4 * M * P), flops=0),
         "ball_query": dict(bytes=F * (12 * M * S + 12 * M * P + 4 * M * P * K), flops=0),
-        "sa_mlp": dict(bytes=F * (16 * M * S + 12 * M * P + 4 * M * P * K + 4 * M * P * C2), flops=F * mlp_flops_per_frame()),
+        "sa_mlp": dict(bytes=F * (16 * M * S + 12 * M * P + 4 * M * P * K + sa_out), flops=F * mlp_flops_per_frame()),
         "person_reduce": dict(bytes=F * (4 * M * P * C2 + 4 * M * C2), flops=0),
     }
 
@@ -285,7 +288,7 @@ def run_native(args, rank, world, local_rank):
     F = args.frames_per_step
     enc = make_encoder().to(dev)
     host, devb = build_batches(F, rank, dev)
-    work = stage_work(F)
+    work = stage_work(F, enc.keep_sa_features)
 
     def barrier():
         if world > 1:
@@ -365,7 +368,7 @@ def run_native(args, rank, world, local_rank):
         lat_ms = l0.elapsed_time(l1) / 20
     h2d = sum(t.numel() * t.element_size() for t in host[0])
     d2h = out_host[0].numel() * out_host[0].element_size()
-    return dict(F=F, ms_total=ms_total, ms_e2e=ms_e2e, stage_ms=stage_ms, launches=launches, clocks=clocks,
+    return dict(keep_sa=enc.keep_sa_features, F=F, ms_total=ms_total, ms_e2e=ms_e2e, stage_ms=stage_ms, launches=launches, clocks=clocks,
                 h2d=h2d, d2h=d2h, lat_ms=lat_ms, work=work, host=host)
 
 
@@ -405,14 +408,16 @@ def main():
             roof = dict(bound="hbm", achieved=ach, peak=pk["hbm"], unit="GB/s", frac=ach / pk["hbm"],
                         traffic=ncu_traffic(dom, F), kernel=dom, note="of %s" % pk["source"])
         roof["share_of_step"] = ms / (r["ms_total"] / K)
-        pipeline_GBps = algorithmic_bytes_per_frame() * value / 1e9
+        pipeline_GBps = algorithmic_bytes_per_frame(keep_sa=r["keep_sa"]) * value / 1e9
         line = dict(metric=METRIC, value=value, unit="frames/s", n_gpus=world, steps=K, warmup=args.warmup,
                     ms_per_step=r["ms_total"] / K, higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype="f32", data="synthetic",
                     config=dict(workload="configs[1]: 65536 pts x 40 boxes, S=512 P=512 r=0.3 K=32 MLP 4-64-128",
                                 frames_per_step=F * world, frames_per_step_per_gpu=F,
                                 l2="two alternating input batches (2 x %d MB) + ~%d MB of stage outputs per step > 126 MB L2"
-                                   % (F, F * 14), weights="random-init (seed 1994), eval-mode BatchNorm folded"),
+                                   % (F, F * (14 if r["keep_sa"] else 4)),
+                                sa_features="stored" if r["keep_sa"] else "kept on chip (person max fused into the MLP kernel)",
+                                weights="random-init (seed 1994), eval-mode BatchNorm folded"),
                     e2e=dict(value=frames_total / (r["ms_e2e"] * 1e-3), unit="frames/s",
                              h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"]),
                     gpu_launches=r["launches"], clocks=r["clocks"], roofline=roof, stages=stages,

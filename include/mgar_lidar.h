@@ -139,6 +139,15 @@ MGAR_API int mgar_ball_query_stack(int B, int M, float radius, int nsample, cons
                           const int *xyz_batch_cnt, int uniform_n, int uniform_m, int *idx, int fill,
                           void *stream);
 
+/* voxel_query_wrapper_stack: voxel_query.cpp:25-41 (kernel voxel_query_gpu.cu:10-89).  new_xyz (M,3), xyz (N,3),
+ * new_coords (M,4) int32 [batch, z, y, x] (16-byte aligned), point_indices (B,R1,R2,R3) int32 voxel -> point
+ * index or -1.  idx (M,nsample): GLOBAL indices of the first nsample points with !(d2 > radius^2) met while
+ * walking the (2*z_range+1)(2*y_range+1)(2*x_range+1) neighbouring voxels in (dz,dy,dx) order, padded with the
+ * first hit; a query without neighbours gets idx[0] = -1 and its other slots are left alone (caller zero-fills). */
+MGAR_API int mgar_voxel_query_stack(int M, int R1, int R2, int R3, int nsample, float radius, int z_range, int y_range,
+                                    int x_range, const float *new_xyz, const float *xyz, const int *new_coords,
+                                    const int *point_indices, int *idx, void *stream);
+
 /* group_points_wrapper_stack: group_points.cpp:50-67 (kernel group_points_gpu.cu:71-102).
  * out (M,C,nsample), every element written. */
 MGAR_API int mgar_group_points_stack(int B, int M, int C, int nsample, const float *features,

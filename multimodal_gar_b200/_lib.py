@@ -34,6 +34,7 @@ SIGNATURES = {
     "mgar_fps_batch": [_i, _i, _i, _p, _i, _p, _p, _p, _p],
     "mgar_fps_stack": [_i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_ball_query_stack": [_i, _i, _f, _i, _p, _p, _p, _i, _p, _i, _i, _p, _i, _p],
+    "mgar_voxel_query_stack": [_i, _i, _i, _i, _i, _f, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_group_points_stack": [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_group_points_grad_stack": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_sa_mlp_tc_supported": [_i, _i, _i, _p, _i],

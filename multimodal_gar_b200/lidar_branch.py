@@ -62,6 +62,9 @@ class PointPersonEncoder(nn.Module):
                                                      mlps=[[point_feature_channels] + list(mlp)], use_xyz=True,
                                                      pool_method='max_pool')
         self.out_channels = mlp[-1]
+        # the (B*M*P, C_out) per-centroid SA features are an intermediate of the person feature: stored only on
+        # request (return_stages=True or this flag); the max over a person's centroids happens in the MLP kernel
+        self.keep_sa_features = os.environ.get('MGAR_KEEP_SA', '0') != '0'
 
     @torch.no_grad()
     def pool(self, points, point_features, boxes):
@@ -116,7 +119,8 @@ class PointPersonEncoder(nn.Module):
             sa_feat = sa_mlp_fused.sa_mlp_forward(packed[0], packed[1], g.nsample, flat[:, 0:3], None, new_xyz, None,
                                                   flat[:, 3:] if C else None, ball_idx, uniform=(S, P),
                                                   params_host=packed[2], impl='tc', group_max=person, group_size=P,
-                                                  group_zero=empty.view(-1))
+                                                  group_zero=empty.view(-1),
+                                                  want_out=return_stages or self.keep_sa_features)
             mark('sa_mlp')
             person = person.view(B, M, -1)
         else:

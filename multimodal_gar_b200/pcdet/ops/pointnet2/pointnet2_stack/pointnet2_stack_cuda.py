@@ -1,7 +1,7 @@
 """Stand-in for the reference's `pointnet2_stack_cuda` pybind module
 (/root/reference/pcdet/ops/pointnet2/pointnet2_stack/src/pointnet2_api.cpp:12-31): the five
-hot-path wrappers run on libmgar_lidar.so; the other eight names exist (so imports succeed) and
-raise NotImplementedError - they belong to PV-RCNN++ / VoxelRCNN paths outside this build.
+hot-path wrappers and voxel_query_wrapper run on libmgar_lidar.so; the other seven names exist (so imports
+succeed) and raise NotImplementedError - they belong to PV-RCNN++ paths outside this build.
 """
 import torch
 
@@ -81,7 +81,20 @@ def _outside(name):
     return fn
 
 
-voxel_query_wrapper = _outside("voxel_query_wrapper")
+def voxel_query_wrapper(M, R1, R2, R3, nsample, radius, z_range, y_range, x_range, new_xyz, xyz, new_coords,
+                        point_indices, idx):
+    """voxel_query.cpp:25-41.  new_xyz (M,3) f32, xyz (N,3) f32, new_coords (M,4) i32 [batch,z,y,x],
+    point_indices (B,R1,R2,R3) i32, idx (M,nsample) i32 zero-filled by the caller.  Returns 1."""
+    need_cuda(new_xyz=new_xyz, xyz=xyz, new_coords=new_coords, point_indices=point_indices, idx=idx)
+    need_dtype(torch.float32, new_xyz=new_xyz, xyz=xyz)
+    need_dtype(torch.int32, new_coords=new_coords, point_indices=point_indices, idx=idx)
+    with on_device(new_xyz):
+        _lib.check(_lib.lib().mgar_voxel_query_stack(M, R1, R2, R3, nsample, float(radius), z_range, y_range, x_range,
+                                                     ptr(new_xyz), ptr(xyz), ptr(new_coords), ptr(point_indices), ptr(idx),
+                                                     stream_of(new_xyz)), "voxel_query_wrapper")
+    return 1
+
+
 three_nn_wrapper = _outside("three_nn_wrapper")
 three_interpolate_wrapper = _outside("three_interpolate_wrapper")
 three_interpolate_grad_wrapper = _outside("three_interpolate_grad_wrapper")

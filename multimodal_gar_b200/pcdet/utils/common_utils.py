@@ -21,3 +21,19 @@ def rotate_points_along_z(points, angle):
     rot = torch.stack((c, s, z, -s, c, z, z, z, o), dim=1).view(-1, 3, 3).float()
     out = torch.cat((torch.matmul(points[:, :, 0:3], rot), points[:, :, 3:]), dim=-1)
     return out.numpy() if is_numpy else out
+
+
+def scatter_point_inds(indices, point_inds, shape):
+    """pcdet/utils/common_utils.py:235-241: dense tensor of `shape` holding point_inds at `indices`, -1 elsewhere."""
+    ret = torch.full(tuple(shape), -1, dtype=point_inds.dtype, device=point_inds.device)
+    flat = indices.view(-1, indices.shape[-1])
+    ret[tuple(flat[:, i] for i in range(flat.shape[1]))] = point_inds
+    return ret
+
+
+def generate_voxel2pinds(sparse_tensor):
+    """pcdet/utils/common_utils.py:244-252: (B,Z,Y,X) int32 map voxel -> row of `sparse_tensor.indices` (-1 = empty).
+    Accepts anything with `.indices` (V,4) [batch,z,y,x], `.batch_size`, `.spatial_shape` (a spconv tensor has them)."""
+    indices = sparse_tensor.indices.long()
+    rows = torch.arange(indices.shape[0], device=indices.device, dtype=torch.int32)
+    return scatter_point_inds(indices, rows, [sparse_tensor.batch_size] + list(sparse_tensor.spatial_shape))

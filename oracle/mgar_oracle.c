@@ -392,3 +392,44 @@ void orc_roiaware_pool3d_backward(const int *lists, const int *argmax, const flo
             }
         }
 }
+
+/* ---- voxel query ------------------------------------------------------------------
+ * pointnet2_stack/src/voxel_query_gpu.cu:10-89.  idx (M,nsample) zero-filled by the caller
+ * (voxel_query_utils.py:33).  Distance as the kernel's SASS computes it (same contraction as ball query):
+ * fma(dz,dz, fma(dx,dx, dy*dy)) with d = point - query; a candidate is skipped when d2 > radius*radius. */
+void orc_voxel_query_stack(int M, int R1, int R2, int R3, int nsample, float radius, int z_range, int y_range,
+                           int x_range, const float *new_xyz, const float *xyz, const int *new_coords,
+                           const int *point_indices, int *idx)
+{
+    float radius2 = radius * radius;
+    for (int q = 0; q < M; q++) {
+        const float *c = new_xyz + (size_t)q * 3;
+        const int *v = new_coords + (size_t)q * 4;
+        int *row = idx + (size_t)q * nsample;
+        int cnt = 0;
+        for (int dz = -z_range; dz <= z_range; dz++) {
+            int z = v[1] + dz;
+            if (z < 0 || z >= R1) continue;
+            for (int dy = -y_range; dy <= y_range; dy++) {
+                int y = v[2] + dy;
+                if (y < 0 || y >= R2) continue;
+                for (int dx = -x_range; dx <= x_range; dx++) {
+                    int x = v[3] + dx;
+                    if (x < 0 || x >= R3) continue;
+                    int nb = point_indices[(((size_t)v[0] * R1 + z) * R2 + y) * R3 + x];
+                    if (nb < 0) continue;
+                    float ex = xyz[(size_t)nb * 3] - c[0], ey = xyz[(size_t)nb * 3 + 1] - c[1],
+                          ez = xyz[(size_t)nb * 3 + 2] - c[2];
+                    float d2 = fmaf(ez, ez, fmaf(ex, ex, ey * ey));
+                    if (d2 > radius2) continue;
+                    if (cnt < nsample) {
+                        if (cnt == 0)
+                            for (int l = 0; l < nsample; l++) row[l] = nb;
+                        row[cnt++] = nb;
+                    }
+                }
+            }
+        }
+        if (cnt == 0) row[0] = -1;
+    }
+}

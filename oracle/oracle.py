@@ -182,6 +182,44 @@ def ball_query(radius, nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt):
     return idx, mask
 
 
+def voxel_query_raw(max_range, radius, nsample, xyz, new_xyz, new_coords, point_indices):
+    """pointnet2_stack_cuda.voxel_query_wrapper as VoxelQuery.forward calls it
+    (pcdet/ops/pointnet2/pointnet2_stack/voxel_query_utils.py:30-37): raw (M,nsample) rows, global indices."""
+    xyz, new_xyz = _f32(xyz), _f32(new_xyz)
+    new_coords, point_indices = _i32(new_coords), _i32(point_indices)
+    M = new_coords.shape[0]
+    _, Z, Y, X = point_indices.shape
+    idx = np.zeros((M, nsample), dtype=np.int32)
+    lib().orc_voxel_query_stack(M, Z, Y, X, nsample, ctypes.c_float(radius), max_range[0], max_range[1], max_range[2],
+                                _fp(new_xyz), _fp(xyz), _ip(new_coords), _ip(point_indices), _ip(idx))
+    return idx
+
+
+def voxel_query(max_range, radius, nsample, xyz, new_xyz, new_coords, point_indices):
+    """VoxelQuery.forward, voxel_query_utils.py:12-44 -> idx (rows without neighbours zeroed), empty mask."""
+    idx = voxel_query_raw(max_range, radius, nsample, xyz, new_xyz, new_coords, point_indices)
+    empty = idx[:, 0] == -1
+    idx[empty] = 0
+    return idx, empty
+
+
+def voxel_query_and_group(max_range, radius, nsample, new_coords, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt,
+                          features, point_indices):
+    """VoxelQueryAndGrouping.forward, voxel_query_utils.py:63-100 -> grouped_features (M,C,ns), grouped_xyz (M,3,ns),
+    empty (M)."""
+    idx, empty = voxel_query(max_range, radius, nsample, xyz, new_xyz, new_coords, point_indices)
+    B = len(xyz_batch_cnt)
+    idx = idx.reshape(B, -1, nsample)
+    count = 0
+    for b in range(B):
+        idx[b] -= count
+        count += int(xyz_batch_cnt[b])
+    idx = idx.reshape(-1, nsample)
+    idx[empty] = 0
+    return (grouping_operation(features, xyz_batch_cnt, idx, new_xyz_batch_cnt),
+            grouping_operation(xyz, xyz_batch_cnt, idx, new_xyz_batch_cnt), empty)
+
+
 def grouping_operation(features, features_batch_cnt, idx, idx_batch_cnt):
     """pointnet2_utils.py:52-86 -> (M,C,nsample)."""
     features, idx = _f32(features), _i32(idx)

@@ -167,3 +167,21 @@ def test_oracle_equals_reference_gpu_roiaware_pool3d():
         assert lists[..., 0].max() == max_pts - 1 and (lists[..., 0] == 0).any()      # capped and empty voxels both present
         gin = O.roiaware_pool3d_backward(lists, argmax, g[method + "_grad_out"], g["pts"].shape[0], method)
         np.testing.assert_allclose(gin, g[method + "_grad_in"], rtol=1e-5, atol=1e-6)
+
+
+def test_oracle_equals_reference_gpu_voxel_query():
+    """Voxel query: rows written by the unmodified reference kernel on a B200
+    (tests/golden/make_ref_voxel_query_golden.py) against the C restatement, bit-exact."""
+    path = os.path.join(GOLD, "ref_voxel_query.npz")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/ref_voxel_query.npz not generated yet (needs one GPU run)")
+    g = np.load(path)
+    src = open(os.path.join(GOLD, "make_ref_voxel_query_golden.py")).read()
+    scenes = eval(src[src.index("SCENES = ") + 9:src.index("\n\n\ndef main")])      # the scene list of the generating script
+    for i, case in enumerate(scenes):
+        c = dict(case)
+        rng, radius, nsample = c.pop("rng"), c.pop("radius"), c.pop("nsample")
+        sc = cases.voxel_scene(C=1, **c)
+        got = O.voxel_query_raw(rng, radius, nsample, sc["xyz"], sc["new_xyz"], sc["new_coords"], sc["v2p"])
+        np.testing.assert_array_equal(got, g["idx_%d" % i])
+        assert (got[:, 0] == -1).any() and (got[:, 0] >= 0).any()

@@ -215,3 +215,20 @@ def test_config3_lidar_branch_plus_dafm_forward_is_frame_sharded(cuda):
             f1 = fus(rgb[b:b + 1], d1["feature"], bboxes[b:b + 1], padded[b:b + 1], d1["valid"])
             assert torch.equal(one, lidar[b:b + 1])
             assert torch.allclose(f1, fused[b:b + 1], rtol=1e-4, atol=1e-4)   # library GEMMs: batch size changes the kernel
+
+
+def test_person_features_do_not_depend_on_storing_sa_features(cuda):
+    """The (B*M*P, C) per-centroid SA features are an intermediate: with them kept on chip (default) the person
+    features are the bits of max-over-centroids of the stored tensor."""
+    _, _, xyz, feat, bx = _inputs(5, 3, 65536, 40, cuda)
+    enc = _enc(cuda)
+    with torch.no_grad():
+        enc.keep_sa_features = False
+        a = enc(xyz, feat, bx)
+        enc.keep_sa_features = True
+        b = enc(xyz, feat, bx)
+        st = enc(xyz, feat, bx, return_stages=True)
+    assert torch.equal(a, b) and torch.equal(a, st["person_features"])
+    want = st["sa_features"].view(3 * 40, 512, -1).max(dim=1).values
+    want = want * (st["empty"].view(-1, 1) == 0)
+    assert torch.equal(a.view(3 * 40, -1), want)
