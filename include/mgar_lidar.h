@@ -131,7 +131,8 @@ MGAR_API int mgar_fps_stack(int batch, int max_n, const float *xyz, float *temp,
  * idx (M,nsample): batch-local indices of the first nsample points with d2 < radius^2 in index order,
  * padded with the first hit; rows without neighbours get idx[0] = -1.  fill = 0 is the reference
  * contract (idx zero-filled by the caller, the other slots of such rows are left alone); fill = 1
- * writes every slot (-1, 0, 0, ...) so idx may be uninitialised.
+ * writes every slot (-1, 0, 0, ...) so idx may be uninitialised; fill = 2 leaves such rows untouched (the
+ * pointnet2_batch kernel's behaviour, pointnet2_batch/src/ball_query_gpu.cu:15-51: no -1 marker).
  * Extensions: xyz_stride (floats between rows); uniform_n > 0: every cloud has uniform_n points and
  * uniform_m centroids (B * uniform_m == M) and the count arrays may be NULL. */
 MGAR_API int mgar_ball_query_stack(int B, int M, float radius, int nsample, const float *new_xyz,
@@ -159,6 +160,30 @@ MGAR_API int mgar_group_points_stack(int B, int M, int C, int nsample, const flo
 MGAR_API int mgar_group_points_grad_stack(int B, int M, int C, int N, int nsample, const float *grad_out,
                                  const int *idx, const int *idx_batch_cnt,
                                  const int *features_batch_cnt, float *grad_features, void *stream);
+
+/* ---- pointnet2_batch: channel-major gather / scatter, three-nearest interpolation ------------------- */
+
+/* pointnet2_batch/src/pointnet2_api.cpp:11-23.  ball_query_wrapper of that module = mgar_ball_query_stack with
+ * uniform_n = n, uniform_m = m, fill = 2; farthest_point_sampling_wrapper = mgar_fps_batch (same kernel source);
+ * gather_points(_grad)_wrapper = the two entries below with nsample = 1.
+ * group_points_wrapper_fast (group_points.cpp:39-54, kernel group_points_gpu.cu:55-72): points (b,c,n),
+ * idx (b,npoints,nsample) -> out (b,c,npoints,nsample), every element written.  _grad (group_points.cpp:21-36,
+ * kernel :13-31): grad_out (b,c,npoints,nsample) accumulated with atomics into zero-filled grad_points (b,c,n). */
+MGAR_API int mgar_batch_group_points(int b, int c, int n, int npoints, int nsample, const float *points, const int *idx,
+                                     float *out, void *stream);
+MGAR_API int mgar_batch_group_points_grad(int b, int c, int n, int npoints, int nsample, const float *grad_out,
+                                          const int *idx, float *grad_points, void *stream);
+/* three_nn_wrapper_fast (interpolate.cpp:20-34, kernel interpolate_gpu.cu:14-62): unknown (b,n,3), known (b,m,3) ->
+ * dist2 (b,n,3) SQUARED distances ascending, idx (b,n,3); ties keep the lowest index; with m < 3 the missing
+ * slots are (+inf, 0).  three_interpolate_wrapper_fast (interpolate.cpp:37-54, kernel :82-101): points (b,c,m),
+ * idx / weight (b,n,3) -> out (b,c,n); _grad (interpolate.cpp:57-73, kernel :124-146) accumulates into
+ * zero-filled grad_points (b,c,m). */
+MGAR_API int mgar_three_nn(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx,
+                           void *stream);
+MGAR_API int mgar_three_interpolate(int b, int c, int m, int n, const float *points, const int *idx, const float *weight,
+                                    float *out, void *stream);
+MGAR_API int mgar_three_interpolate_grad(int b, int c, int n, int m, const float *grad_out, const int *idx,
+                                         const float *weight, float *grad_points, void *stream);
 
 /* ---- set-abstraction shared MLP (QueryAndGroup + [Conv1x1,BN,ReLU] x L + pool, fused) ------------ */
 

@@ -35,6 +35,11 @@ SIGNATURES = {
     "mgar_fps_stack": [_i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_ball_query_stack": [_i, _i, _f, _i, _p, _p, _p, _i, _p, _i, _i, _p, _i, _p],
     "mgar_voxel_query_stack": [_i, _i, _i, _i, _i, _f, _i, _i, _i, _p, _p, _p, _p, _p, _p],
+    "mgar_batch_group_points": [_i, _i, _i, _i, _i, _p, _p, _p, _p],
+    "mgar_batch_group_points_grad": [_i, _i, _i, _i, _i, _p, _p, _p, _p],
+    "mgar_three_nn": [_i, _i, _i, _p, _p, _p, _p, _p],
+    "mgar_three_interpolate": [_i, _i, _i, _i, _p, _p, _p, _p, _p],
+    "mgar_three_interpolate_grad": [_i, _i, _i, _i, _p, _p, _p, _p, _p],
     "mgar_group_points_stack": [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_group_points_grad_stack": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_sa_mlp_tc_supported": [_i, _i, _i, _p, _i],

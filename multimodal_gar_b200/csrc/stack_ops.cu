@@ -94,8 +94,8 @@ __device__ __forceinline__ int find_batch(const int *__restrict__ pre, int B, in
 // broadcast LDS.128 serves 32 distance tests), hits are appended in index order to the thread's own
 // shared-memory row, and a warp stops scanning once all of its 32 centroids are full.  Rows leave as
 // coalesced 4K-byte stores.  uniform != 0: every cloud has n_u points / m_u centroids and the
-// prefix arrays are not read.  fill != 0: rows without a neighbour are written as (-1, 0, 0, ...)
-// instead of relying on the caller's zero fill.
+// prefix arrays are not read.  fill == 1: rows without a neighbour are written as (-1, 0, 0, ...)
+// instead of relying on the caller's zero fill; fill == 2: such rows are not touched at all (pointnet2_batch).
 __global__ void __launch_bounds__(kBqTile)
 ball_query_kernel(int B, float radius, int K, const float *__restrict__ new_xyz, const float *__restrict__ xyz, int xs,
                   const int *__restrict__ pre_new, const int *__restrict__ pre_xyz,
@@ -170,8 +170,9 @@ ball_query_kernel(int B, float radius, int K, const float *__restrict__ new_xyz,
         const int *src = rows + row * (K + 1);
         int *out = idx + (size_t)(c_begin + row) * K;
         if (cnt_r == 0) {
-            if (fill) { for (int l = lane; l < K; l += 32) out[l] = l == 0 ? -1 : 0; }
-            else if (lane == 0) out[0] = -1;   // other slots keep the caller's fill (ball_query_gpu.cu:65)
+            if (fill == 1) { for (int l = lane; l < K; l += 32) out[l] = l == 0 ? -1 : 0; }
+            else if (fill == 0 && lane == 0) out[0] = -1;   // other slots keep the caller's fill (ball_query_gpu.cu:65)
+            // fill == 2: pointnet2_batch semantics, the whole row keeps the caller's fill (no -1 marker)
         } else {
             const int first = src[0];
             for (int l = lane; l < K; l += 32) out[l] = l < cnt_r ? src[l] : first;
@@ -239,8 +240,9 @@ ball_query_reg_kernel(float radius, int K, const float *__restrict__ new_xyz, co
         __syncwarp();
         int *out = idx + ci * K;
         if (cnt == 0) {
-            if (fill) { for (int l = lane; l < K; l += 32) out[l] = l == 0 ? -1 : 0; }
-            else if (lane == 0) out[0] = -1;   // other slots keep the caller's fill (ball_query_gpu.cu:65)
+            if (fill == 1) { for (int l = lane; l < K; l += 32) out[l] = l == 0 ? -1 : 0; }
+            else if (fill == 0 && lane == 0) out[0] = -1;   // other slots keep the caller's fill (ball_query_gpu.cu:65)
+            // fill == 2: pointnet2_batch semantics, the whole row keeps the caller's fill (no -1 marker)
         } else {
             const int first = row[0];
             for (int l = lane; l < K; l += 32) out[l] = l < cnt ? row[l] : first;

@@ -5,7 +5,8 @@ into this repo) with torch.utils.cpp_extension for sm_100, producing
 
     oracle/_ref/roiaware_pool3d_cuda.so      (points_in_boxes_gpu / points_in_boxes_cpu)
     oracle/_ref/roipoint_pool3d_cuda.so      (forward)
-    oracle/_ref/pointnet2_stack_cuda.so      (ball_query / group_points / FPS wrappers)
+    oracle/_ref/pointnet2_stack_cuda.so      (ball_query / group_points / FPS / voxel_query wrappers)
+    oracle/_ref/pointnet2_batch_cuda.so      (batch-layout ball_query / group / gather / FPS / three_nn / interpolate)
 
 oracle/_ref/ is git-ignored but travels to the GPU box with the gpurun snapshot.  Only
 tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
@@ -26,6 +27,7 @@ EXTS = {
     "roiaware_pool3d_cuda": "roiaware_pool3d/src",
     "roipoint_pool3d_cuda": "roipoint_pool3d/src",
     "pointnet2_stack_cuda": "pointnet2/pointnet2_stack/src",
+    "pointnet2_batch_cuda": "pointnet2/pointnet2_batch/src",
 }
 
 

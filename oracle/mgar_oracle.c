@@ -433,3 +433,68 @@ void orc_voxel_query_stack(int M, int R1, int R2, int R3, int nsample, float rad
         if (cnt == 0) row[0] = -1;
     }
 }
+
+/* ---- pointnet2_batch surface -------------------------------------------------------
+ * ball_query_kernel_fast, pointnet2_batch/src/ball_query_gpu.cu:15-51: like the stack kernel but a centroid
+ * without neighbours leaves its (zero-filled) row untouched.  SASS: d2 = fma(dz,dz, fma(dx,dx, dy*dy)). */
+void orc_ball_query_batch(int b, int n, int m, float radius, int nsample, const float *new_xyz, const float *xyz,
+                          int *idx)
+{
+    float radius2 = radius * radius;
+    for (int bs = 0; bs < b; bs++)
+        for (int pt = 0; pt < m; pt++) {
+            const float *c = new_xyz + ((size_t)bs * m + pt) * 3;
+            const float *p = xyz + (size_t)bs * n * 3;
+            int *row = idx + ((size_t)bs * m + pt) * nsample;
+            int cnt = 0;
+            for (int k = 0; k < n; k++) {
+                float ex = c[0] - p[k * 3], ey = c[1] - p[k * 3 + 1], ez = c[2] - p[k * 3 + 2];
+                float d2 = fmaf(ez, ez, fmaf(ex, ex, ey * ey));
+                if (d2 < radius2) {
+                    if (cnt == 0)
+                        for (int l = 0; l < nsample; l++) row[l] = k;
+                    row[cnt++] = k;
+                    if (cnt >= nsample) break;
+                }
+            }
+        }
+}
+
+/* three_nn_kernel_fast, interpolate_gpu.cu:14-62: bests kept as doubles initialised to 1e40, float distance with
+ * the same contraction; outputs are the squared distances. */
+void orc_three_nn(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx)
+{
+    for (int bs = 0; bs < b; bs++)
+        for (int pt = 0; pt < n; pt++) {
+            const float *u = unknown + ((size_t)bs * n + pt) * 3;
+            const float *kn = known + (size_t)bs * m * 3;
+            double best1 = 1e40, best2 = 1e40, best3 = 1e40;
+            int i1 = 0, i2 = 0, i3 = 0;
+            for (int k = 0; k < m; k++) {
+                float ex = u[0] - kn[k * 3], ey = u[1] - kn[k * 3 + 1], ez = u[2] - kn[k * 3 + 2];
+                float d = fmaf(ez, ez, fmaf(ex, ex, ey * ey));
+                if (d < best1) { best3 = best2; i3 = i2; best2 = best1; i2 = i1; best1 = d; i1 = k; }
+                else if (d < best2) { best3 = best2; i3 = i2; best2 = d; i2 = k; }
+                else if (d < best3) { best3 = d; i3 = k; }
+            }
+            float *o = dist2 + ((size_t)bs * n + pt) * 3;
+            int *oi = idx + ((size_t)bs * n + pt) * 3;
+            o[0] = (float)best1; o[1] = (float)best2; o[2] = (float)best3;
+            oi[0] = i1; oi[1] = i2; oi[2] = i3;
+        }
+}
+
+/* three_interpolate_kernel_fast, interpolate_gpu.cu:82-101; SASS (FMUL, FFMA, FFMA): fma(w2,p2, fma(w0,p0, w1*p1)). */
+void orc_three_interpolate(int b, int c, int m, int n, const float *points, const int *idx, const float *weight,
+                           float *out)
+{
+    for (int bs = 0; bs < b; bs++)
+        for (int ch = 0; ch < c; ch++) {
+            const float *p = points + ((size_t)bs * c + ch) * m;
+            for (int pt = 0; pt < n; pt++) {
+                const int *i = idx + ((size_t)bs * n + pt) * 3;
+                const float *w = weight + ((size_t)bs * n + pt) * 3;
+                out[((size_t)bs * c + ch) * n + pt] = fmaf(w[2], p[i[2]], fmaf(w[0], p[i[0]], w[1] * p[i[1]]));
+            }
+        }
+}

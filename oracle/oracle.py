@@ -325,6 +325,69 @@ def stack_sa_module_msg(mlps, radii, nsamples, xyz, xyz_batch_cnt, new_xyz, new_
 
 
 # ---- the unmodified reference, compiled into oracle/_ref (see build_ref.py) ---------------------
+# ---- pointnet2_batch surface: (B,N,3) coordinates, channel-major (B,C,N) features -------------
+def batch_ball_query(radius, nsample, xyz, new_xyz):
+    """BallQuery.forward, pcdet/ops/pointnet2/pointnet2_batch/pointnet2_utils.py:193-214 -> (B,npoint,nsample) int32."""
+    xyz, new_xyz = _f32(xyz), _f32(new_xyz)
+    B, N, _ = xyz.shape
+    M = new_xyz.shape[1]
+    idx = np.zeros((B, M, nsample), dtype=np.int32)
+    lib().orc_ball_query_batch(B, N, M, ctypes.c_float(radius), nsample, _fp(new_xyz), _fp(xyz), _ip(idx))
+    return idx
+
+
+def batch_grouping_operation(features, idx):
+    """GroupingOperation.forward, pointnet2_batch/pointnet2_utils.py:153-170: (B,C,N), (B,npoint,nsample) ->
+    (B,C,npoint,nsample).  GatherOperation (:39-55) is the nsample-free case."""
+    features, idx = _f32(features), _i32(idx)
+    B, C, _ = features.shape
+    flat = idx.reshape(B, 1, -1).astype(np.int64)
+    return np.take_along_axis(features, np.broadcast_to(flat, (B, C, flat.shape[2])), axis=2).reshape((B, C) + idx.shape[1:])
+
+
+def batch_grouping_grad(grad_out, idx, N):
+    """GroupingOperation.backward / GatherOperation.backward (:172-187, :57-69): scatter-add into (B,C,N)."""
+    grad_out, idx = _f32(grad_out), _i32(idx)
+    B, C = grad_out.shape[:2]
+    g = np.zeros((B, C, N), dtype=np.float32)
+    for b in range(B):
+        for c in range(C):
+            np.add.at(g[b, c], idx[b].reshape(-1), grad_out[b, c].reshape(-1))
+    return g
+
+
+def three_nn(unknown, known):
+    """ThreeNN.forward, pointnet2_batch/pointnet2_utils.py:75-96 -> dist (B,N,3) (sqrt of the kernel's output), idx."""
+    unknown, known = _f32(unknown), _f32(known)
+    B, N, _ = unknown.shape
+    dist2 = np.zeros((B, N, 3), dtype=np.float32)
+    idx = np.zeros((B, N, 3), dtype=np.int32)
+    lib().orc_three_nn(B, N, known.shape[1], _fp(unknown), _fp(known), _fp(dist2), _ip(idx))
+    return np.sqrt(dist2), idx, dist2
+
+
+def three_interpolate(features, idx, weight):
+    """ThreeInterpolate.forward, pointnet2_batch/pointnet2_utils.py:107-128: (B,C,M), (B,N,3) x2 -> (B,C,N)."""
+    features, idx, weight = _f32(features), _i32(idx), _f32(weight)
+    B, C, M = features.shape
+    N = idx.shape[1]
+    out = np.zeros((B, C, N), dtype=np.float32)
+    lib().orc_three_interpolate(B, C, M, N, _fp(features), _ip(idx), _fp(weight), _fp(out))
+    return out
+
+
+def three_interpolate_grad(grad_out, idx, weight, M):
+    """ThreeInterpolate.backward (:130-147): grad_out (B,C,N) * weight scattered into (B,C,M)."""
+    grad_out, idx, weight = _f32(grad_out), _i32(idx), _f32(weight)
+    B, C, N = grad_out.shape
+    g = np.zeros((B, C, M), dtype=np.float32)
+    for b in range(B):
+        for c in range(C):
+            for j in range(3):
+                np.add.at(g[b, c], idx[b, :, j], grad_out[b, c] * weight[b, :, j])
+    return g
+
+
 def load_ref(name):
     """Import oracle/_ref/<name>.so (a torch pybind module built from /root/reference sources)."""
     import torch  # noqa: F401  (the extension links libtorch)

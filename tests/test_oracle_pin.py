@@ -185,3 +185,24 @@ def test_oracle_equals_reference_gpu_voxel_query():
         got = O.voxel_query_raw(rng, radius, nsample, sc["xyz"], sc["new_xyz"], sc["new_coords"], sc["v2p"])
         np.testing.assert_array_equal(got, g["idx_%d" % i])
         assert (got[:, 0] == -1).any() and (got[:, 0] >= 0).any()
+
+
+def test_oracle_equals_reference_gpu_batch_ops():
+    """pointnet2_batch surface: outputs of the unmodified reference kernels on a B200
+    (tests/golden/make_ref_batch_golden.py) against the C restatement, bit-exact."""
+    path = os.path.join(GOLD, "ref_batch_ops.npz")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/ref_batch_ops.npz not generated yet (needs one GPU run)")
+    g = np.load(path)
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_ref_batch_golden", os.path.join(GOLD, "make_ref_batch_golden.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    xyz, new_xyz, feats, weight = gen.inputs()
+    bq = O.batch_ball_query(0.35, 16, xyz, new_xyz)
+    np.testing.assert_array_equal(bq, g["bq"])
+    assert (bq[:, :2] == 0).all() and (bq[:, 2:, 1] > 0).any()
+    _, idx, d2 = O.three_nn(xyz, new_xyz)
+    np.testing.assert_array_equal(idx, g["nn_idx"])
+    np.testing.assert_array_equal(d2, g["d2"])
+    np.testing.assert_array_equal(O.three_interpolate(feats, idx, weight), g["interp"])
