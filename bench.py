@@ -246,6 +246,7 @@ def stage_work(F, keep_sa=True):
         "roipoint_pool": dict(bytes=F * (16 * N + 28 * M + 16 * M * S + 4 * M), flops=0),
         "fps": dict(bytes=F * (12 * M * S + 4 * M * P), flops=0),
         "ball_query": dict(bytes=F * (12 * M * S + 12 * M * P + 4 * M * P * K), flops=0),
+        "fps_ball_query": dict(bytes=F * (12 * M * S + 4 * M * P + 12 * M * P + 4 * M * P * K), flops=0),   # fused: one read of the clouds
         "sa_mlp": dict(bytes=F * (16 * M * S + 12 * M * P + 4 * M * P * K + sa_out), flops=F * mlp_flops_per_frame()),
         "person_reduce": dict(bytes=F * (4 * M * P * C2 + 4 * M * C2), flops=0),
     }

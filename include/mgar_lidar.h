@@ -149,6 +149,17 @@ MGAR_API int mgar_voxel_query_stack(int M, int R1, int R2, int R3, int nsample, 
                                     int x_range, const float *new_xyz, const float *xyz, const int *new_coords,
                                     const int *point_indices, int *idx, void *stream);
 
+/* farthest_point_sampling_wrapper (sampling.cpp:21-34) followed by ball_query_wrapper_stack (ball_query.cpp:29-45)
+ * around the sampled points, in ONE pass for b equally sized clouds: round j of the sampling already measures every
+ * point against sample j-1, which is the distance the ball query around that centroid tests (bit-identical), so the
+ * query costs one ballot per 32 points instead of a second kernel.  xyz (b,n,xyz_stride) -> fps_idx (b,m) int32,
+ * new_xyz (b,m,3), ball_idx (b*m,nsample) cloud-local indices exactly as mgar_fps_batch + mgar_ball_query_stack
+ * (uniform layout, fill = 1) produce them.  Supported (mgar_fps_ball_query_supported != 0): n in {32,64,128,256,512},
+ * nsample <= 64, b >= 592 clouds (one warp per cloud: a throughput kernel); otherwise call the two entries. */
+MGAR_API int mgar_fps_ball_query_supported(int b, int n, int m, int nsample);
+MGAR_API int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xyz_stride, float radius, int nsample,
+                                 int *fps_idx, float *new_xyz, int *ball_idx, void *stream);
+
 /* group_points_wrapper_stack: group_points.cpp:50-67 (kernel group_points_gpu.cu:71-102).
  * out (M,C,nsample), every element written. */
 MGAR_API int mgar_group_points_stack(int B, int M, int C, int nsample, const float *features,

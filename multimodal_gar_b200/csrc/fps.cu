@@ -335,6 +335,141 @@ fps_global_kernel(const float *__restrict__ xyz, int xs, float *__restrict__ tem
     }
 }
 
+// ---- FPS + ball query in one pass (power-of-two clouds of 32*P points, one warp per cloud) -------------------------
+// Round j of the sampling measures every point of the cloud against sample j-1 - and those are exactly the distances
+// the ball query around centroid j-1 tests against radius^2 (same operands up to sign, same contraction, hence the
+// same bits).  So the query rides on the sampling round: one ballot per 32-point block on the distance the round
+// has in a register anyway, a prefix of popcounts over the blocks in index order, an ordered append into a
+// K-entry shared-memory row, one coalesced store of the row.  The centroids never travel through global memory
+// and the second kernel's 7 flops per (centroid, point) pair disappear.
+// Rank space = bit reversal (SH = 0, bs = n): rank brev5(l) * P + i is index brev_p(i) * 32 + l, so with the lanes
+// permuted that way slot i is the 32-point block brev_p(i) in index order.
+template <int PB>
+__device__ __forceinline__ constexpr int brev_bits(int v) {
+    int r = 0;
+    for (int q = 0; q < PB; q++) r |= ((v >> q) & 1) << (PB - 1 - q);
+    return r;
+}
+template <int P> struct Log2P { static constexpr int v = 1 + Log2P<P / 2>::v; };
+template <> struct Log2P<1> { static constexpr int v = 0; };
+
+__device__ __forceinline__ int brev_bits_rt(int v, int bits) { return bits == 0 ? 0 : (int)(__brev((unsigned)v) >> (32 - bits)); }
+
+template <int P>
+__global__ void __maxnreg__(112)   // 9 CTAs x 64 threads x 112 registers = 63 K: one wave of 2560 clouds
+fps_bq_warp_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs, float *__restrict__ new_xyz,
+                   int *__restrict__ ball_idx, float radius, int K, int b, int m, int f4_per_warp) {
+    constexpr int n = 32 * P, L = 5 + Log2P<P>::v;
+    extern __shared__ float4 fps_sm4[];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int cloud = blockIdx.x * kFpsWarpsPerCta + w;
+    if (cloud >= b) return;
+    float4 *sp = fps_sm4 + (size_t)w * f4_per_warp;  // [n] staged cloud, [m] sampled indices, 2 x [K] ball rows
+    int *sidx = reinterpret_cast<int *>(sp + n);
+    int *rows = sidx + m;
+    xyz += (size_t)cloud * n * xs; idxs += (size_t)cloud * m;
+    new_xyz += (size_t)cloud * m * 3;
+    ball_idx += (size_t)cloud * m * K;
+
+    if (xs == 4 && (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) {
+        for (int k = lane; k < n; k += 32) sp[k] = __ldg(reinterpret_cast<const float4 *>(xyz) + k);
+    } else {
+        for (int k = lane; k < n; k += 32)
+            sp[k] = make_float4(xyz[(size_t)k * xs], xyz[(size_t)k * xs + 1], xyz[(size_t)k * xs + 2], 0.f);
+    }
+    __syncwarp();
+
+    // lane l owns the ranks brev5(l) * P + i, i.e. the indices brev_p(i) * 32 + l: inside a 32-point block the lanes
+    // sit in index order, so a ballot over slot i IS the index-ordered hit mask of block brev_p(i)
+    const int rank0 = (int)(__brev((unsigned)lane) >> 27) * P;
+    const float r2 = __fmul_rn(radius, radius);
+    float px[P], py[P], pz[P], t[2 * P];
+#pragma unroll
+    for (int i = 0; i < P; i++) {
+        const float4 q = sp[rank_to_index(rank0 + i, L, 0)];
+        px[i] = q.x; py[i] = q.y; pz[i] = q.z;
+        t[P + i] = 1e10f;
+    }
+    constexpr int PB = Log2P<P>::v;
+    const int my_slot = lane < P ? brev_bits_rt(lane, PB) : -1;     // the register slot that is block `lane`
+    int buf = 0;
+    // The ball of one centroid from the P hit masks: lane s < P takes block s, an inclusive scan of the popcounts
+    // gives its first slot, then it appends its own hits (index order = bit order) until the row is full.  The row
+    // leaves as one coalesced store padded with its first entry; empty rows are (-1, 0, 0, ...) as fill = 1 of
+    // mgar_ball_query_stack.  Rows are double-buffered: the barrier of round j+1 orders round j's reads before
+    // round j+2's writes.
+    auto emit = [&](int c, unsigned mask) {
+        int *row = rows + buf * K;
+        int incl = __popc(mask);
+#pragma unroll
+        for (int o = 1; o < P; o *= 2) {
+            const int up = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += up;
+        }
+        const int cnt = __shfl_sync(0xffffffffu, incl, P - 1);
+        int pos = incl - __popc(mask);
+        while (mask && pos < K) {
+            row[pos++] = lane * 32 + __ffs(mask) - 1;
+            mask &= mask - 1;
+        }
+        __syncwarp();
+        const int first = row[0];
+        const int v0 = lane < K ? row[lane] : 0, v1 = lane + 32 < K ? row[lane + 32] : 0;
+        int *out = ball_idx + (size_t)c * K;
+        if (lane < K) out[lane] = cnt == 0 ? (lane == 0 ? -1 : 0) : (lane < cnt ? v0 : first);
+        if (lane + 32 < K) out[lane + 32] = cnt == 0 ? 0 : (lane + 32 < cnt ? v1 : first);
+        buf ^= 1;
+    };
+    int cur = 0, j = 1;
+    if (lane == 0) sidx[0] = 0;
+    bool done = false;                               // every point coincides with a sample: index 0 from here on
+    for (; j < m; j++) {
+        const float4 c = sp[cur];
+        unsigned mask = 0;                           // lane s < P keeps the hit mask of block s, the others nothing
+#pragma unroll
+        for (int i = 0; i < P; i++) {
+            const float d = sqdist(__fsub_rn(px[i], c.x), __fsub_rn(py[i], c.y), __fsub_rn(pz[i], c.z));
+            const unsigned hb = __ballot_sync(0xffffffffu, d < r2);
+            mask = my_slot == i ? hb : mask;
+            t[P + i] = fminf(d, t[P + i]);
+        }
+#pragma unroll
+        for (int q = P - 1; q >= 1; q--) t[q] = fmaxf(t[2 * q], t[2 * q + 1]);
+        const int vb = __float_as_int(P > 1 ? t[1] : t[P]);
+        const int vmax = __reduce_max_sync(0xffffffffu, vb);
+        const int slot = descend<P, 1>(t, vmax, 0);
+        const int rmin = __reduce_min_sync(0xffffffffu, vb == vmax ? rank0 + slot : INT_MAX);
+        emit(j - 1, mask);                           // the ball of centroid j-1, while the REDUX is in flight
+        if (vmax == 0) { done = true; break; }
+        cur = rank_to_index(rmin, L, 0);
+        if (lane == 0) sidx[j] = cur;
+    }
+    if (!done) {                                     // the last sample has had no round of its own
+        const float4 c = sp[cur];
+        unsigned mask = 0;
+#pragma unroll
+        for (int i = 0; i < P; i++) {
+            const unsigned hb = __ballot_sync(0xffffffffu, sqdist(__fsub_rn(px[i], c.x), __fsub_rn(py[i], c.y), __fsub_rn(pz[i], c.z)) < r2);
+            mask = my_slot == i ? hb : mask;
+        }
+        emit(m - 1, mask);
+    } else {                                         // samples j .. m-1 are point 0 = sample 0: their balls are row 0
+        for (int q = j + lane; q < m; q += 32) sidx[q] = 0;
+        int *row = rows;
+        __syncwarp();
+        for (int l = lane; l < K; l += 32) row[l] = ball_idx[l];   // written by this warp (same lanes) in round 1
+        __syncwarp();
+        for (int e = lane; e < (m - j) * K; e += 32) ball_idx[(size_t)j * K + e] = row[e % K];
+    }
+    __syncwarp();
+    for (int q = lane; q < m; q += 32) idxs[q] = sidx[q];
+    for (int e = lane; e < m * 3; e += 32) {
+        const int q = e / 3, cc = e - q * 3;
+        const float4 v = sp[sidx[q]];
+        new_xyz[e] = cc == 0 ? v.x : (cc == 1 ? v.y : v.z);
+    }
+}
+
 template <int W, int PPL>
 static int launch_reg(int grid, size_t smem, cudaStream_t st, const float *xyz, int xs, float *temp, int *idx,
                       float *new_xyz, const int *cnt, const int *ms, int n, int m, int L, int stack) {
@@ -436,4 +571,32 @@ extern "C" int mgar_fps_stack(int batch, int max_n, const float *xyz, float *tem
     while ((1 << SH) < stripes) SH++;
     return fps_dispatch(batch, 1024 << SH, max_n, (cudaStream_t)stream, xyz, 3, temp, idx, nullptr, xyz_batch_cnt,
                         num_sampled, 0, 0, 10, 1);
+}
+
+extern "C" int mgar_fps_ball_query_supported(int b, int n, int m, int nsample) {
+    if (b < 4 * kNumSMs || m < 1 || nsample < 1 || nsample > 64 || getenv("MGAR_NO_FPS_BQ")) return 0;
+    return n == 32 || n == 64 || n == 128 || n == 256 || n == 512;
+}
+
+extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xyz_stride, float radius, int nsample,
+                                   int *fps_idx, float *new_xyz, int *ball_idx, void *stream) {
+    MGAR_REQUIRE(mgar_fps_ball_query_supported(b, n, m, nsample), "fps_ball_query: unsupported shape b=%d n=%d m=%d nsample=%d "
+                 "(ask mgar_fps_ball_query_supported first)", b, n, m, nsample);
+    MGAR_REQUIRE(xyz && fps_idx && new_xyz && ball_idx, "fps_ball_query: null pointer");
+    MGAR_REQUIRE(xyz_stride >= 3, "fps_ball_query: xyz_stride must be >= 3");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int f4 = n + (m + 2 * nsample + 3) / 4;
+    const size_t sm = (size_t)kFpsWarpsPerCta * f4 * sizeof(float4);
+    MGAR_REQUIRE(sm <= 200 * 1024, "fps_ball_query: m=%d too large for shared memory", m);
+    const int ctas = (b + kFpsWarpsPerCta - 1) / kFpsWarpsPerCta;
+#define MGAR_FPS_BQ(p)                                                                                               \
+    if (n == 32 * p) {                                                                                               \
+        if (sm > 48 * 1024) MGAR_CUDA(cudaFuncSetAttribute(fps_bq_warp_kernel<p>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+        fps_bq_warp_kernel<p><<<ctas, kFpsWarpsPerCta * 32, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, f4); \
+        count_launch();                                                                                              \
+        return check_launch("fps_ball_query");                                                                       \
+    }
+    MGAR_FPS_BQ(1) MGAR_FPS_BQ(2) MGAR_FPS_BQ(4) MGAR_FPS_BQ(8) MGAR_FPS_BQ(16)
+#undef MGAR_FPS_BQ
+    return MGAR_EINVAL;
 }

@@ -32,6 +32,27 @@ def fps_gather(xyz, npoint):
     return idx, new_xyz
 
 
+def fps_ball_query(xyz, npoint, radius, nsample):
+    """FPS + ball query around the sampled points in one kernel, for many equally sized power-of-two clouds.
+    xyz (b,n,3) (column view of a (b,n,3+C) array allowed) -> (idx (b,npoint) int32, new_xyz (b,npoint,3),
+    ball_idx (b*npoint,nsample) int32) - the results of fps_gather + ball_query_uniform - or None when the shape is
+    not covered (the caller then runs the two kernels)."""
+    b, n = xyz.shape[0], xyz.shape[1]
+    L = _lib.lib()
+    if not L.mgar_fps_ball_query_supported(b, n, int(npoint), int(nsample)):
+        return None
+    xs = _rows(xyz)
+    if b > 1 and xyz.stride(0) != n * xs:
+        raise _lib.MgarError("clouds must be densely stacked")
+    idx = torch.empty((b, npoint), dtype=torch.int32, device=xyz.device)
+    new_xyz = torch.empty((b, npoint, 3), dtype=torch.float32, device=xyz.device)
+    ball_idx = torch.empty((b * npoint, nsample), dtype=torch.int32, device=xyz.device)
+    with on_device(xyz):
+        _lib.check(L.mgar_fps_ball_query(b, n, int(npoint), ptr(xyz), xs, float(radius), int(nsample), ptr(idx), ptr(new_xyz),
+                                         ptr(ball_idx), stream_of(xyz)), "fps_ball_query")
+    return idx, new_xyz, ball_idx
+
+
 def ball_query_uniform(radius, nsample, xyz, new_xyz, n, m):
     """xyz (B*n, 3) (row-strided view allowed), new_xyz (B*m, 3) contiguous -> raw idx (B*m, nsample) int32 with
     the -1 sentinel in slot 0 of empty balls (every slot written)."""

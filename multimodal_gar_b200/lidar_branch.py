@@ -110,11 +110,17 @@ class PointPersonEncoder(nn.Module):
         if packed is not None and sa_mlp_fused.tc_supported(packed[0], g.nsample, C):
             # fused path: every kernel reads the pooled (.., 3+C) rows in place; 5 launches per step
             flat = pooled.view(B * M * S, 3 + C)
-            fps_idx, new_xyz = fastpath.fps_gather(pooled[:, :, 0:3], P)
-            new_xyz = new_xyz.view(B * M * P, 3)
-            mark('fps')
-            ball_idx = fastpath.ball_query_uniform(g.radius, g.nsample, flat[:, 0:3], new_xyz, S, P)
-            mark('ball_query')
+            fused = fastpath.fps_ball_query(pooled[:, :, 0:3], P, g.radius, g.nsample)
+            if fused is not None:                  # sampling and ball query share their distances: one kernel
+                fps_idx, new_xyz, ball_idx = fused
+                new_xyz = new_xyz.view(B * M * P, 3)
+                mark('fps_ball_query')
+            else:
+                fps_idx, new_xyz = fastpath.fps_gather(pooled[:, :, 0:3], P)
+                new_xyz = new_xyz.view(B * M * P, 3)
+                mark('fps')
+                ball_idx = fastpath.ball_query_uniform(g.radius, g.nsample, flat[:, 0:3], new_xyz, S, P)
+                mark('ball_query')
             person = torch.empty((B * M, self.out_channels), dtype=torch.float32, device=pooled.device)
             sa_feat = sa_mlp_fused.sa_mlp_forward(packed[0], packed[1], g.nsample, flat[:, 0:3], None, new_xyz, None,
                                                   flat[:, 3:] if C else None, ball_idx, uniform=(S, P),

@@ -418,3 +418,35 @@ def test_sa_mlp_tensor_core_path(cuda, Bp, n, m, C_in, layout):
         ref32 = sa_mlp_fused.sa_mlp_forward(ch, params.to(cuda), K, dxyz, cn, T(new_xyz, cuda), ncn, dfe, T(idx, cuda),
                                             empty_mask=T(mask, cuda), impl='fp32', **kw)
         _feature_close(got.cpu().numpy(), ref32.cpu().numpy())
+
+
+@pytest.mark.parametrize("n,m,K,radius", [(512, 512, 32, 0.3), (512, 100, 16, 0.6), (256, 256, 33, 0.4), (128, 300, 64, 0.25),
+                                          (64, 64, 1, 0.5), (32, 7, 8, 0.2), (512, 1, 32, 0.3), (512, 512, 32, 1e-4)])
+def test_fused_fps_ball_query_equals_the_two_kernels(cuda, n, m, K, radius):
+    """One pass (sampling rounds double as ball-query distance tests) == fps_gather + ball_query_uniform, bit for bit:
+    clouds with exact duplicates (early exit of the sampling, replicated rows), wrapped clouds, m > n, K > 32, a
+    radius that only ever finds the centroid's own duplicates."""
+    from multimodal_gar_b200 import fastpath
+    b = 700
+    c = cases.cloud_with_ties(n + m, b, n)
+    rng = np.random.default_rng(n * 7 + m)
+    c[::3] = rng.uniform(-1, 1, c[::3].shape).astype(np.float32)                 # every third cloud: no duplicates
+    c[1::3, n // 4:] = c[1::3, :n - n // 4]                                     # wrapped clouds (k mod cnt)
+    c4 = np.concatenate([c, rng.standard_normal((b, n, 1)).astype(np.float32)], axis=2)
+    t4 = T(c4, cuda)
+    xyz = t4[:, :, 0:3]
+    fused = fastpath.fps_ball_query(xyz, m, radius, K)
+    assert fused is not None
+    idx, new_xyz = fastpath.fps_gather(xyz, m)
+    ball = fastpath.ball_query_uniform(radius, K, t4.view(b * n, 4)[:, 0:3], new_xyz.view(b * m, 3), n, m)
+    assert torch.equal(fused[0], idx) and torch.equal(fused[1], new_xyz)
+    assert torch.equal(fused[2], ball)
+    assert int((ball[:, 0] >= 0).sum()) == b * m
+    pick = list(range(0, b, 100))                                                # and against the CPU oracle
+    want = O.farthest_point_sample(np.ascontiguousarray(c[pick]), m)
+    np.testing.assert_array_equal(fused[0].cpu().numpy()[pick], want)
+    # contiguous (b,n,3) input and unsupported shapes
+    f3 = fastpath.fps_ball_query(T(c, cuda), m, radius, K)
+    assert all(torch.equal(a, b_) for a, b_ in zip(f3, fused))
+    assert fastpath.fps_ball_query(T(c[:, :n - 1], cuda), m, radius, K) is None
+    assert fastpath.fps_ball_query(T(c[:100], cuda), m, radius, K) is None
