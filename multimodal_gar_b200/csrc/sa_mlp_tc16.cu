@@ -95,10 +95,40 @@ __device__ long long g_tc16_trace[32 * 16];        // timeline of CTA 0, local t
 #define TR(slot, i) do { } while (0)
 #endif
 
+// 2-MMA packing of a 5-column 3xTF32 product (see kPack2 below).  v = columns 0..3, v4 = column 4; hi = tf32
+// truncation, lo = exact remainder, as sts_split4.  a0/a1 = the two 16-byte K-halves of the row in tile A, b0/b1 in B.
+__device__ __forceinline__ void split5(const float (&v)[4], float v4, float (&hi)[5], float (&lo)[5]) {
+#pragma unroll
+    for (int q = 0; q < 5; q++) {
+        const float x = q < 4 ? v[q] : v4;
+        hi[q] = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+        lo[q] = __fsub_rn(x, hi[q]);
+    }
+}
+__device__ __forceinline__ void sts4(uint32_t a, float x, float y, float z, float w) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+__device__ __forceinline__ void sts_pack2_x(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1, const float (&v)[4], float v4) {
+    float hi[5], lo[5];
+    split5(v, v4, hi, lo);
+    sts4(a0, hi[0], hi[1], hi[2], hi[3]); sts4(a1, hi[4], lo[0], lo[1], lo[2]);
+    sts4(b0, hi[0], hi[1], hi[2], hi[3]); sts4(b1, hi[4], lo[3], lo[4], 0.f);
+}
+__device__ __forceinline__ void sts_pack2_w(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1, const float (&v)[4], float v4) {
+    float hi[5], lo[5];
+    split5(v, v4, hi, lo);
+    sts4(a0, hi[0], hi[1], hi[2], hi[3]); sts4(a1, hi[4], hi[0], hi[1], hi[2]);
+    sts4(b0, lo[0], lo[1], lo[2], lo[3]); sts4(b1, lo[4], hi[3], hi[4], 0.f);
+}
+
 template <int C0>
 __global__ void __launch_bounds__(kThreads, 1)
 sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcBound BD, const __grid_constant__ TcArgs A) {
     static_assert(C0 >= 3 && C0 <= 7, "layer-1 K is padded to 8 with one column for the folded bias");
+    // <= 5 used K columns (C0 <= 4): the 15 products xh.wh + xh.wl + xl.wh of the 3xTF32 split fit the 16 K-slots of
+    // TWO MMAs instead of three: tile A = [xh0..xh4, xl0, xl1, xl2] . [wh0..wh4, wh0, wh1, wh2],
+    //                            tile B = [xh0..xh4, xl3, xl4, 0  ] . [wl0..wl4, wh3, wh4, 0  ]
+    constexpr bool kPack2 = C0 + 1 <= 5;
     extern __shared__ uint8_t smem_raw[];
     // full[4] empty[4] | tfull[2] tempty[2] | xfull[2] xempty[2] | dfull[2] dempty[2]
     __shared__ __align__(8) uint64_t s_bar[2 * kStages + 12];
@@ -152,8 +182,11 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             const float v = k < C0 ? L1.w[k][ch] : (k == C0 ? L1.sh[ch] : 0.f);
             if (k < 4) k0[k] = v; else k1[k - 4] = v;
         }
-        sts_split4(w1_hi + k8_off(ch, 0), w1_lo + k8_off(ch, 0), k0);
-        sts_split4(w1_hi + k8_off(ch, 1), w1_lo + k8_off(ch, 1), k1);
+        if (kPack2) sts_pack2_w(w1_hi + k8_off(ch, 0), w1_hi + k8_off(ch, 1), w1_lo + k8_off(ch, 0), w1_lo + k8_off(ch, 1), k0, k1[0]);
+        else {
+            sts_split4(w1_hi + k8_off(ch, 0), w1_lo + k8_off(ch, 0), k0);
+            sts_split4(w1_hi + k8_off(ch, 1), w1_lo + k8_off(ch, 1), k1);
+        }
         fence_async_smem();
     }
     tc_fence_before();
@@ -303,9 +336,14 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             const uint64_t xd_hi = make_desc_k8(x_hi), xd_lo = make_desc_k8(x_hi + kXBytes);
             const uint32_t d1 = tmem + kTmD1 + (uint32_t)(xs * 64);
             if (elect_one()) {
-                tc_mma_tf32(d1, xd_lo, w1d_hi, idesc1, 0);
-                tc_mma_tf32(d1, xd_hi, w1d_lo, idesc1, 1);
-                tc_mma_tf32(d1, xd_hi, w1d_hi, idesc1, 1);
+                if (kPack2) {                                   // 15 products in 2 x 8 K-slots (see sts_pack2_x)
+                    tc_mma_tf32(d1, xd_lo, w1d_lo, idesc1, 0);
+                    tc_mma_tf32(d1, xd_hi, w1d_hi, idesc1, 1);
+                } else {
+                    tc_mma_tf32(d1, xd_lo, w1d_hi, idesc1, 0);
+                    tc_mma_tf32(d1, xd_hi, w1d_lo, idesc1, 1);
+                    tc_mma_tf32(d1, xd_hi, w1d_hi, idesc1, 1);
+                }
                 tc_commit(XEMPTY(xs));
                 tc_commit(DFULL(xs));
             }
@@ -386,8 +424,11 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             if (pw == 0) TR(0, i);
             mbar_wait(XEMPTY(xs), (jx & 1) ^ 1);
             if (pw == 0) TR(1, i);
-            sts_split4(x_hi + k8_off(r, 0), x_lo + k8_off(r, 0), k0);
-            sts_split4(x_hi + k8_off(r, 1), x_lo + k8_off(r, 1), k1);
+            if (kPack2) sts_pack2_x(x_hi + k8_off(r, 0), x_hi + k8_off(r, 1), x_lo + k8_off(r, 0), x_lo + k8_off(r, 1), k0, k1[0]);
+            else {
+                sts_split4(x_hi + k8_off(r, 0), x_lo + k8_off(r, 0), k0);
+                sts_split4(x_hi + k8_off(r, 1), x_lo + k8_off(r, 1), k1);
+            }
             if (lane == 0) s_inv[i % kRing][pw] = up;
             fence_async_smem();
             mbar_arrive(XFULL(xs));
