@@ -248,6 +248,11 @@ MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float
  * is ACCUMULATED into (zero it first; may be NULL).  No gradient is produced for xyz / new_xyz.
  * Geometry arguments as for mgar_sa_mlp_fwd_fp32.  Exact fp32 arithmetic, fp64 batch reductions. */
 MGAR_API size_t mgar_sa_mlp_train_workspace_bytes(int M, int nsample, int n_layers, const int *channels_host);
+/* The same given the pooling method (what mgar_sa_mlp_fwd_train / _bwd need at least for that call): layers
+ * [3+C_in, 64, 128] with C_in 1 or 2, nsample 32 and max-pool - the hot-path shape - run specialised kernels that
+ * keep no (positions x channels) activation, so their workspace is ~30x smaller.  Never larger than the above. */
+MGAR_API size_t mgar_sa_mlp_train_workspace_bytes_for(int M, int nsample, int n_layers, const int *channels_host,
+                                                      int pool_avg);
 MGAR_API int mgar_sa_mlp_fwd_train(int B, int M, int nsample, int C_in, const float *xyz, const int *xyz_batch_cnt,
                                    const float *new_xyz, const int *new_xyz_batch_cnt, int uniform_n, int uniform_m,
                                    const float *features, const int *idx, const unsigned char *empty_mask,

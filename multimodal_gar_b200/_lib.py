@@ -49,6 +49,7 @@ SIGNATURES = {
                            _p],
     "mgar_sa_mlp_fwd_fp32": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _i, _i, _p],
     "mgar_sa_mlp_train_workspace_bytes": [_i, _i, _i, _p],
+    "mgar_sa_mlp_train_workspace_bytes_for": [_i, _i, _i, _p, _i],
     "mgar_sa_mlp_fwd_train": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _f, _p, _i, _i, _p, _p,
                               ctypes.c_size_t, _p],
     "mgar_sa_mlp_bwd": [_i, _i, _i, _i, _p, _p, _i, _i, _p, _p, _i, _p, _p, _p, _p, _i, _i, _p, ctypes.c_size_t, _p, _p, _p, _p],
@@ -84,6 +85,7 @@ def lib():
         L.mgar_last_error.restype = ctypes.c_char_p
         L.mgar_launch_count.restype = ctypes.c_ulonglong
         L.mgar_sa_mlp_train_workspace_bytes.restype = ctypes.c_size_t
+        L.mgar_sa_mlp_train_workspace_bytes_for.restype = ctypes.c_size_t
         L.mgar_box_mask_words.restype = ctypes.c_size_t
         L.mgar_roiaware_pool3d_workspace_bytes.restype = ctypes.c_size_t
         _lib = L

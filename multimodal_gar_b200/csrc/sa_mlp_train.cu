@@ -19,6 +19,7 @@
 // Exact-fp32 FFMA arithmetic; this path favours clarity over speed (it is not the inference hot path).
 #include "mgar_common.cuh"
 #include "stack_prefix.cuh"
+#include "sa_mlp_train_fast.cuh"
 
 namespace mgar {
 
@@ -353,6 +354,13 @@ extern "C" size_t mgar_sa_mlp_train_workspace_bytes(int M, int nsample, int n_la
     return s.total;
 }
 
+// Same, given the pooling method: the hot-path shape with max-pool runs the specialised kernels of
+// sa_mlp_train_fast.cu, which keep no (positions x channels) activation (27 MB instead of 860 MB per JRDB frame).
+extern "C" size_t mgar_sa_mlp_train_workspace_bytes_for(int M, int nsample, int n_layers, const int *channels_host, int pool_avg) {
+    if (trfast::applicable(M, nsample, n_layers, channels_host, pool_avg)) return trfast::workspace_bytes(M, channels_host[0]);
+    return mgar_sa_mlp_train_workspace_bytes(M, nsample, n_layers, channels_host);
+}
+
 static int tr_grid(long long work_items, int per_cta) {
     long long g = (work_items + per_cta - 1) / per_cta;
     const long long cap = (long long)kNumSMs * 8;
@@ -373,10 +381,13 @@ extern "C" int mgar_sa_mlp_fwd_train(int B, int M, int nsample, int C_in, const 
     MGAR_REQUIRE(xyz && new_xyz && idx && weights && gamma_beta && out && workspace, "sa_mlp_train: null pointer");
     MGAR_REQUIRE(features || C_in == 0, "sa_mlp_train: features missing");
     MGAR_REQUIRE(s.ch[0] == 3 + C_in, "sa_mlp_train: channels[0]=%d but 3+C_in=%d", s.ch[0], 3 + C_in);
-    if (ws_bytes < s.total) { set_error("sa_mlp_train: workspace %zu < %zu bytes", ws_bytes, s.total); return MGAR_ENOMEM; }
     const bool uniform = uniform_n > 0;
     MGAR_REQUIRE(uniform || (xyz_batch_cnt && new_xyz_batch_cnt), "sa_mlp_train: batch counts missing");
     cudaStream_t st = (cudaStream_t)stream;
+    if (trfast::applicable(M, nsample, n_layers, channels_host, pool_avg))
+        return trfast::forward(B, M, C_in, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, uniform_n, uniform_m, features, idx,
+                               empty_mask, weights, gamma_beta, eps, out, ld_out, batch_stats, workspace, ws_bytes, st);
+    if (ws_bytes < s.total) { set_error("sa_mlp_train: workspace %zu < %zu bytes", ws_bytes, s.total); return MGAR_ENOMEM; }
     PrefixWs ws;
     if (!uniform) {
         if (int rc = ws.alloc(B, st)) return rc;
@@ -427,8 +438,14 @@ extern "C" int mgar_sa_mlp_bwd(int B, int M, int nsample, int C_in, const int *x
     TrainSpec s;
     MGAR_REQUIRE(make_spec(s, M, nsample, n_layers, channels_host) == 0, "sa_mlp_bwd: bad layer spec");
     MGAR_REQUIRE(weights && gamma_beta && grad_out && workspace && grad_weights && grad_gamma_beta && idx, "sa_mlp_bwd: null pointer");
-    if (ws_bytes < s.total) { set_error("sa_mlp_bwd: workspace %zu < %zu bytes", ws_bytes, s.total); return MGAR_ENOMEM; }
     cudaStream_t st = (cudaStream_t)stream;
+    if (trfast::applicable(M, nsample, n_layers, channels_host, pool_avg)) {
+        MGAR_REQUIRE(uniform_n > 0 || !grad_features || (xyz_batch_cnt && new_xyz_batch_cnt), "sa_mlp_bwd: batch counts missing");
+        return trfast::backward(B, M, C_in, xyz_batch_cnt, new_xyz_batch_cnt, uniform_n, uniform_m, idx, empty_mask, weights,
+                                gamma_beta, grad_out, ld_grad, workspace, ws_bytes, grad_weights, grad_gamma_beta,
+                                grad_features, st);
+    }
+    if (ws_bytes < s.total) { set_error("sa_mlp_bwd: workspace %zu < %zu bytes", ws_bytes, s.total); return MGAR_ENOMEM; }
     int n_w = 0;
     for (int l = 0; l < s.L; l++) n_w += s.ch[l] * s.ch[l + 1];
     MGAR_CUDA(cudaMemsetAsync(grad_weights, 0, (size_t)n_w * 4, st));

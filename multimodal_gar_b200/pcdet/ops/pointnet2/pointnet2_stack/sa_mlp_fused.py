@@ -99,9 +99,10 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
 
 
 # ---- training mode: BatchNorm batch statistics + backward, through the C ABI --------------------------------
-def train_workspace_bytes(M, nsample, channels):
+def train_workspace_bytes(M, nsample, channels, pool_avg=False):
     ch = (ctypes.c_int * len(channels))(*channels)
-    return int(_lib.lib().mgar_sa_mlp_train_workspace_bytes(int(M), int(nsample), len(channels) - 1, ctypes.addressof(ch)))
+    return int(_lib.lib().mgar_sa_mlp_train_workspace_bytes_for(int(M), int(nsample), len(channels) - 1,
+                                                                ctypes.addressof(ch), 1 if pool_avg else 0))
 
 
 class SAMlpTrainFunction(torch.autograd.Function):
@@ -127,7 +128,7 @@ class SAMlpTrainFunction(torch.autograd.Function):
         if empty_mask is not None:
             empty_mask = empty_mask.to(torch.uint8).contiguous()
         ch = (ctypes.c_int * len(channels))(*channels)
-        ws_bytes = train_workspace_bytes(M, nsample, channels)
+        ws_bytes = train_workspace_bytes(M, nsample, channels, pool_avg)
         ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=xyz.device)
         out = torch.empty((M, channels[-1]), dtype=torch.float32, device=xyz.device)
         stats = torch.empty((2 * sum(channels[1:]),), dtype=torch.float32, device=xyz.device)

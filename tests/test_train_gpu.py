@@ -32,15 +32,22 @@ def _run(mod, args, feats, w_out):
     return out.detach(), f.grad.detach(), [p.grad.detach().clone() for p in mod.parameters()]
 
 
-@pytest.mark.parametrize("radii,nsamples,mlps,pool", [
-    ([0.6], [32], [[2, 64, 128]], "max_pool"),
-    ([0.3, 0.8], [8, 16], [[2, 16, 32], [2, 8, 24, 40]], "max_pool"),
-    ([0.5], [12], [[2, 20]], "avg_pool"),
+@pytest.mark.parametrize("radii,nsamples,mlps,pool,kernels", [
+    ([0.6], [32], [[2, 64, 128]], "max_pool", "fast"),       # hot-path shape: sa_mlp_train_fast.cu, C0 = 5
+    ([0.6], [32], [[1, 64, 128]], "max_pool", "fast"),       # the same with one feature channel (intensity), C0 = 4
+    ([0.25], [32], [[1, 64, 128]], "max_pool", "fast"),      # small balls: duplicated samples, empty balls
+    ([0.6], [32], [[2, 64, 128]], "max_pool", "generic"),    # the generic kernels on the same shape
+    ([0.6], [32], [[2, 64, 128]], "avg_pool", "fast"),       # avg-pool is not specialised: falls through to generic
+    ([0.3, 0.8], [8, 16], [[2, 16, 32], [2, 8, 24, 40]], "max_pool", "fast"),
+    ([0.5], [12], [[2, 20]], "avg_pool", "fast"),
 ])
-def test_training_forward_backward_match_torch_composition(cuda, radii, nsamples, mlps, pool):
+def test_training_forward_backward_match_torch_composition(cuda, monkeypatch, radii, nsamples, mlps, pool, kernels):
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
+    if kernels == "generic":
+        monkeypatch.setenv("MGAR_SA_TRAIN_KERNELS", "generic")
     xyz, cnt, new_xyz, ncnt, feats = cases.ragged_case()
+    feats = np.ascontiguousarray(feats[:, :mlps[0][0]])
     torch.manual_seed(11)
     native = pointnet2_modules.StackSAModuleMSG(radii=radii, nsamples=nsamples, mlps=copy.deepcopy(mlps),
                                                 pool_method=pool).to(cuda)
@@ -97,3 +104,40 @@ def test_training_step_changes_weights_and_eval_uses_updated_statistics(cuda):
             del os.environ["MGAR_SA_MLP"]
     assert not torch.allclose(before, after)
     _close(after, after32, 1e-5)
+
+
+def test_fast_training_kernels_negative_gamma_and_uniform_batch(cuda):
+    """Hot-path layout (uniform clouds of 512 points, 512 centroids each, one feature channel) with some NEGATIVE
+    BatchNorm gammas in both layers: the specialised forward then takes the min over the samples for those
+    channels (sa_mlp_train_fast.cu, identity 1).  6 persons -> 3072 centroids, 98 304 positions."""
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(3)
+    Bp, S = 6, 512
+    xyz = (torch.rand(Bp * S, 3, device=cuda) - 0.5) * torch.tensor([0.8, 0.8, 1.8], device=cuda)
+    feats = torch.rand(Bp * S, 1, device=cuda)
+    cnt = torch.full((Bp,), S, dtype=torch.int32, device=cuda)
+    new_xyz = xyz.clone()
+    native = pointnet2_modules.StackSAModuleMSG(radii=[0.3], nsamples=[32], mlps=[[1, 64, 128]]).to(cuda)
+    with torch.no_grad():
+        for m in native.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.weight.normal_(0.3, 1.0)
+                m.bias.normal_(0, 0.3)
+    ref = copy.deepcopy(native)
+    native.train(); ref.train()
+    args = (xyz, cnt, new_xyz, cnt)
+    w_out = torch.randn((Bp * S, 128), device=cuda)
+    out_n, gf_n, gp_n = _run(native, args, feats, w_out)
+    os.environ["MGAR_SA_TRAIN"] = "torch"
+    try:
+        out_r, gf_r, gp_r = _run(ref, args, feats, w_out)
+    finally:
+        del os.environ["MGAR_SA_TRAIN"]
+    _close(out_n, out_r, 1e-5)
+    _close(gf_n, gf_r, 1e-4)
+    for a, b in zip(gp_n, gp_r):
+        _close(a, b, 1e-4)
+    for (na, ba), (nb, bb) in zip(native.named_buffers(), ref.named_buffers()):
+        if ba.dtype.is_floating_point:
+            _close(ba, bb, 1e-5)
