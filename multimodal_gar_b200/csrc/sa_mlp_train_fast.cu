@@ -8,8 +8,9 @@
 // both for this shape (P = M*32 positions, x0 = grouped input rows, h1 = relu(bn1(x0 W1)), z2 = h1 W2):
 //
 //  (1) BatchNorm's affine is monotone, rounding is monotone: max_k relu(a z_k + b) = relu(a zext + b) with
-//      zext = max_k z_k (a >= 0) or min_k z_k (a < 0).  The forward keeps max/min/arg of z2 per (centroid,
-//      channel) and the column sums of z2, z2^2 - z2 itself is never written.  (Tie rule: first k attaining the
+//      zext = max_k z_k (a >= 0) or min_k z_k (a < 0), and sign(a) = sign(gamma2) is known before the statistics.
+//      The forward keeps that extreme and its sample per (centroid, channel) plus the column sums of z2, z2^2 -
+//      z2 itself is never written.  (Tie rule: first k attaining the
 //      extreme z; equal to torch's "first k attaining the max y" except when two DIFFERENT z round to the same
 //      y > 0, or gamma == 0 exactly.)
 //  (2) Layer-1 statistics are a quadratic form: sum_p z1 = W1 . X, sum_p z1^2 = W1^T G0 W1 with X = sum_p x0,
@@ -44,12 +45,12 @@ constexpr int kMaxGrid = kNumSMs * 2;
 constexpr int dX = 0, dG0 = 8, dSum2 = 72, dSq2 = 200, dFwdEnd = 328;
 constexpr int dS1 = 328, dS2 = 456, dD = 584, dS11 = 1096, dRed = 1160, dTotal = dRed + kStatEnt;
 // fp32 block (indices in floats)
-constexpr int fMean1 = 0, fInv1 = 64, fSc1 = 128, fSh1 = 192, fW1f = 256, fAlpha = 768, fMean2 = 1088, fInv2 = 1216,
+constexpr int fMean1 = 0, fInv1 = 64, fSc1 = 128, fSh1 = 192, fAlpha = 768, fMean2 = 1088, fInv2 = 1216,
               fSc2 = 1344, fSh2 = 1472, fQ = 1600, fCvec = 5696, fE = 5760, fU = 5888, fQf = 6016, fCf = 6056,
               fTotal = 6064;
 
 struct Layout {
-    size_t x0, zmax, zmin, arg, t, part, dbl, flt, w2t, total;
+    size_t x0, zmax, gs, arg, t, lst, lgs, lcnt, part, dbl, flt, w2t, total;
 };
 
 size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -60,9 +61,12 @@ Layout make_layout(int M, int C0) {
     size_t off = 0;
     l.x0 = off; off = align_up(off + P * C0 * 4);
     l.zmax = off; off = align_up(off + (size_t)M * kC2 * 4);
-    l.zmin = off; off = align_up(off + (size_t)M * kC2 * 4);
+    l.gs = off;   off = align_up(off + (size_t)M * kC2 * 4);
     l.arg = off; off = align_up(off + (size_t)M * kC2 * 4);
     l.t = off; off = align_up(off + P * (C0 - 3) * 4);
+    l.lst = off; off = align_up(off + (size_t)M * kC2 * 4);
+    l.lgs = off; off = align_up(off + (size_t)M * kC2 * 4);
+    l.lcnt = off; off = align_up(off + (size_t)M * 4);
     l.part = off; off = align_up(off + (size_t)kMaxGrid * kStatEnt * 8);
     l.dbl = off; off = align_up(off + (size_t)dTotal * 8);
     l.flt = off; off = align_up(off + (size_t)fTotal * 4);
@@ -78,6 +82,21 @@ __device__ __forceinline__ int find_batch(const int *__restrict__ pre, int B, in
         if (__ldg(pre + mid) <= v) lo = mid; else hi = mid;
     }
     return lo;
+}
+
+// Packed fp32 pairs: Blackwell's FFMA2 (fma.rn.f32x2) does two IEEE fp32 FMAs per lane per issue slot - the scalar
+// FFMA issues every other cycle per scheduler, so the register-tiled contractions below run on pairs.
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t pack2(float lo, float hi) {
+    f2_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f2_t v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void ffma2(f2_t &d, f2_t a, f2_t b) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
 }
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -211,21 +230,22 @@ __device__ __forceinline__ void load_x_tile(const float *__restrict__ x0, float 
 }
 
 // z2 = h1 W2 per 128-position tile (never stored): column sums of z2 and z2^2 (fp64 slots in shared memory), and
-// per (centroid, channel) the max / min of z2 over the 32 samples with the first sample attaining each.
+// per (centroid, channel) the extreme of z2 over the 32 samples that survives the max-pool, with the first sample
+// attaining it: the max where gamma2 >= 0, the min where gamma2 < 0.  The sign is folded into the W2 columns held in
+// shared memory (exact), so the kernel tracks max(sgn z2) only and zmax holds sgn * z2.
 // Thread tile 8 positions x 8 channels; warp = one centroid x 64 channels.
 template <int C0>
 __global__ void __launch_bounds__(kThreads, 2)
 f_layer2_kernel(long long P, int M, const float *__restrict__ x0, const float *__restrict__ flt,
-                const float *__restrict__ Wt1, const float *__restrict__ Wt2, float *__restrict__ zmax, float *__restrict__ zmin,
-                int *__restrict__ arg, double *__restrict__ dbl) {
+                const float *__restrict__ Wt1, const float *__restrict__ Wt2, const float *__restrict__ gamma2,
+                float *__restrict__ zmax, int *__restrict__ arg, double *__restrict__ dbl) {
     extern __shared__ __align__(16) unsigned char tf_sm[];
     float *sW2 = reinterpret_cast<float *>(tf_sm);            // [64][128]
     float *sH = sW2 + kC1 * kC2;                              // [128][68]
     float *sX = sH + kTP * kLdH;                              // [128][C0] (room for 8)
     double *sD = reinterpret_cast<double *>(sX + kTP * 8);    // [8 warps][8 txl][16]
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    for (int e = t; e < kC1 * kC2 / 4; e += kThreads)
-        reinterpret_cast<float4 *>(sW2)[e] = __ldg(reinterpret_cast<const float4 *>(Wt2) + e);
+    for (int e = t; e < kC1 * kC2; e += kThreads) sW2[e] = __ldg(gamma2 + (e & (kC2 - 1))) < 0.f ? -__ldg(Wt2 + e) : __ldg(Wt2 + e);
     for (int e = t; e < 8 * 8 * 16; e += kThreads) sD[e] = 0.0;
     const int c1 = t & 63, q = t >> 6;
     float w1[C0];
@@ -239,75 +259,76 @@ f_layer2_kernel(long long P, int M, const float *__restrict__ x0, const float *_
         __syncthreads();
         h1_tile<C0>(sX, sH, w1, lp, c1, q, tile * 4 + q < M);
         __syncthreads();
-        float acc[8][8];
+        f2_t acc2[8][4];
 #pragma unroll
         for (int r = 0; r < 8; r++)
 #pragma unroll
-            for (int j = 0; j < 8; j++) acc[r][j] = 0.f;
-        const float *aBase = sH + (wy * kK + tyl * 8) * kLdH;
+            for (int j = 0; j < 4; j++) acc2[r][j] = 0ull;
+        const float *aBase = sH + (wy * kK + tyl) * kLdH;   // samples k = 4 r + tyl: the 4 lane groups read adjacent rows (distinct banks)
         const float *bBase = sW2 + wx * 64 + txl * 4;
 #pragma unroll 1
         for (int k4 = 0; k4 < kC1 / 4; k4++) {
             float4 a[8];
 #pragma unroll
-            for (int r = 0; r < 8; r++) a[r] = *reinterpret_cast<const float4 *>(aBase + r * kLdH + k4 * 4);
+            for (int r = 0; r < 8; r++) a[r] = *reinterpret_cast<const float4 *>(aBase + r * 4 * kLdH + k4 * 4);
 #pragma unroll
             for (int kk = 0; kk < 4; kk++) {
                 const float4 b0 = *reinterpret_cast<const float4 *>(bBase + (k4 * 4 + kk) * kC2);
                 const float4 b1 = *reinterpret_cast<const float4 *>(bBase + (k4 * 4 + kk) * kC2 + 32);
+                const f2_t b01 = pack2(b0.x, b0.y), b23 = pack2(b0.z, b0.w), b45 = pack2(b1.x, b1.y), b67 = pack2(b1.z, b1.w);
 #pragma unroll
                 for (int r = 0; r < 8; r++) {
                     const float av = kk == 0 ? a[r].x : kk == 1 ? a[r].y : kk == 2 ? a[r].z : a[r].w;
-                    acc[r][0] = __fmaf_rn(av, b0.x, acc[r][0]);
-                    acc[r][1] = __fmaf_rn(av, b0.y, acc[r][1]);
-                    acc[r][2] = __fmaf_rn(av, b0.z, acc[r][2]);
-                    acc[r][3] = __fmaf_rn(av, b0.w, acc[r][3]);
-                    acc[r][4] = __fmaf_rn(av, b1.x, acc[r][4]);
-                    acc[r][5] = __fmaf_rn(av, b1.y, acc[r][5]);
-                    acc[r][6] = __fmaf_rn(av, b1.z, acc[r][6]);
-                    acc[r][7] = __fmaf_rn(av, b1.w, acc[r][7]);
+                    const f2_t aa = pack2(av, av);
+                    ffma2(acc2[r][0], aa, b01);
+                    ffma2(acc2[r][1], aa, b23);
+                    ffma2(acc2[r][2], aa, b45);
+                    ffma2(acc2[r][3], aa, b67);
                 }
             }
         }
         // epilogue: statistics over this thread's 8 samples, then over the 4 lanes (tyl) that share the channels
-        float mx[8], mn[8];
-        int ax[8], an[8];
+        float mx[8], s[8], sq[8];
+        int ax[8];
         double *slot = sD + (warp * 8 + txl) * 16;
+        const f2_t one2 = pack2(1.f, 1.f);
+#pragma unroll
+        for (int jp = 0; jp < 4; jp++) {
+            f2_t s2 = 0ull, q2 = 0ull;
+#pragma unroll
+            for (int r = 0; r < 8; r++) { ffma2(s2, acc2[r][jp], one2); ffma2(q2, acc2[r][jp], acc2[r][jp]); }
+            unpack2(s2, s[2 * jp], s[2 * jp + 1]);
+            unpack2(q2, sq[2 * jp], sq[2 * jp + 1]);
+        }
 #pragma unroll
         for (int j = 0; j < 8; j++) {
-            float s = 0.f, sq = 0.f;
-            mx[j] = acc[0][j]; mn[j] = acc[0][j]; ax[j] = 0; an[j] = 0;
+            float v0, v1;
+            unpack2(acc2[0][j >> 1], v0, v1);
+            mx[j] = (j & 1) ? v1 : v0; ax[j] = 0;
 #pragma unroll
-            for (int r = 0; r < 8; r++) {
-                const float v = acc[r][j];
-                s += v;
-                sq = __fmaf_rn(v, v, sq);
-                if (r > 0) {
-                    if (v > mx[j]) { mx[j] = v; ax[j] = r; }
-                    if (v < mn[j]) { mn[j] = v; an[j] = r; }
-                }
+            for (int r = 1; r < 8; r++) {
+                unpack2(acc2[r][j >> 1], v0, v1);
+                const float v = (j & 1) ? v1 : v0;
+                if (v > mx[j]) { mx[j] = v; ax[j] = r; }
             }
-            ax[j] += tyl * 8; an[j] += tyl * 8;
+            ax[j] = ax[j] * 4 + tyl;
 #pragma unroll
             for (int o = 8; o <= 16; o <<= 1) {
-                s += __shfl_xor_sync(0xffffffffu, s, o);
-                sq += __shfl_xor_sync(0xffffffffu, sq, o);
-                const float omx = __shfl_xor_sync(0xffffffffu, mx[j], o), omn = __shfl_xor_sync(0xffffffffu, mn[j], o);
-                const int oax = __shfl_xor_sync(0xffffffffu, ax[j], o), oan = __shfl_xor_sync(0xffffffffu, an[j], o);
+                s[j] += __shfl_xor_sync(0xffffffffu, s[j], o);
+                sq[j] += __shfl_xor_sync(0xffffffffu, sq[j], o);
+                const float omx = __shfl_xor_sync(0xffffffffu, mx[j], o);
+                const int oax = __shfl_xor_sync(0xffffffffu, ax[j], o);
                 if (omx > mx[j] || (omx == mx[j] && oax < ax[j])) { mx[j] = omx; ax[j] = oax; }
-                if (omn < mn[j] || (omn == mn[j] && oan < an[j])) { mn[j] = omn; an[j] = oan; }
             }
-            if (tyl == 0) { slot[j] += (double)s; slot[8 + j] += (double)sq; }
+            if (tyl == 0) { slot[j] += (double)s[j]; slot[8 + j] += (double)sq[j]; }
         }
         const long long m = tile * 4 + wy;
         if (tyl == 0 && m < M) {
             const size_t o = (size_t)m * kC2 + wx * 64 + txl * 4;
             *reinterpret_cast<float4 *>(zmax + o) = make_float4(mx[0], mx[1], mx[2], mx[3]);
             *reinterpret_cast<float4 *>(zmax + o + 32) = make_float4(mx[4], mx[5], mx[6], mx[7]);
-            *reinterpret_cast<float4 *>(zmin + o) = make_float4(mn[0], mn[1], mn[2], mn[3]);
-            *reinterpret_cast<float4 *>(zmin + o + 32) = make_float4(mn[4], mn[5], mn[6], mn[7]);
-            *reinterpret_cast<int4 *>(arg + o) = make_int4(ax[0] | (an[0] << 8), ax[1] | (an[1] << 8), ax[2] | (an[2] << 8), ax[3] | (an[3] << 8));
-            *reinterpret_cast<int4 *>(arg + o + 32) = make_int4(ax[4] | (an[4] << 8), ax[5] | (an[5] << 8), ax[6] | (an[6] << 8), ax[7] | (an[7] << 8));
+            *reinterpret_cast<int4 *>(arg + o) = make_int4(ax[0], ax[1], ax[2], ax[3]);
+            *reinterpret_cast<int4 *>(arg + o + 32) = make_int4(ax[4], ax[5], ax[6], ax[7]);
         }
     }
     __syncthreads();
@@ -317,6 +338,7 @@ f_layer2_kernel(long long P, int M, const float *__restrict__ x0, const float *_
         double v = 0.0;
 #pragma unroll
         for (int w = 0; w < 4; w++) v += sD[((w * 2 + wxx) * 8 + txx) * 16 + jj];
+        if (jj < 8 && __ldg(gamma2 + c) < 0.f) v = -v;      // the columns were negated: sum z2 = -sum(sgn z2)
         atomicAdd(dbl + (jj >= 8 ? dSq2 : dSum2) + c, v);
     }
 }
@@ -337,40 +359,102 @@ __global__ void f_bn2_kernel(long long P, float eps, const float *__restrict__ g
     if (batch_stats) { batch_stats[2 * kC1 + c] = (float)mean; batch_stats[2 * kC1 + kC2 + c] = (float)var; }
 }
 
-// out = relu(scale2 * zext + shift2); zmax <- zext, arg <- its sample
+// out = relu(scale2 * zext + shift2); zmax <- zext (the sign folded by f_layer2_kernel is undone here)
 __global__ void __launch_bounds__(kThreads)
-f_pool_kernel(long long n, const float *__restrict__ flt, float *__restrict__ zmax, const float *__restrict__ zmin,
-              int *__restrict__ arg, float *__restrict__ out, int ld_out) {
+f_pool_kernel(long long n, const float *__restrict__ flt, const float *__restrict__ gamma2, float *__restrict__ zmax,
+              float *__restrict__ out, int ld_out) {
     const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
     if (e >= n) return;
     const int c = (int)(e & (kC2 - 1));
     const long long m = e >> 7;
     const float a = __ldg(flt + fSc2 + c), b = __ldg(flt + fSh2 + c);
-    const int pk = arg[e];
-    const bool up = a >= 0.f;
-    const float z = up ? zmax[e] : zmin[e];
+    const float z = __ldg(gamma2 + c) < 0.f ? -zmax[e] : zmax[e];
     zmax[e] = z;
-    arg[e] = up ? (pk & 255) : (pk >> 8);
     out[m * ld_out + c] = fmaxf(__fmaf_rn(z, a, b), 0.f);
 }
 
 // ---- backward --------------------------------------------------------------------------------------------------
-// g_y at the arg-max samples, s1 = sum g_y, s2 = sum g_y xhat (fp64); gs = coefA * g_y (into the zmin array)
+// g_y at the arg-max samples, s1 = sum g_y, s2 = sum g_y xhat (fp64); gs = coefA * g_y.
+// Warp per centroid, lane l owns channels l + 32 j.  The non-zero (channel, sample) entries of the centroid are also
+// written as a list SORTED BY SAMPLE (stable in the channel; counting sort with match_any ranks): b_layer_kernel
+// turns them into rows of g_h1 with register accumulation, one store per sample.  The list is padded to a multiple
+// of 4 with zero-valued entries of sample 31.
 __global__ void __launch_bounds__(kThreads)
-b_gy_kernel(int M, const float *__restrict__ zsel, const float *__restrict__ flt, const float *__restrict__ grad_out,
-            int ld, float *__restrict__ gs, double *__restrict__ dbl) {
-    const int c = threadIdx.x & (kC2 - 1), half = threadIdx.x >> 7;
-    const float a = __ldg(flt + fSc2 + c), b = __ldg(flt + fSh2 + c), mean = __ldg(flt + fMean2 + c), inv = __ldg(flt + fInv2 + c);
-    double s1 = 0.0, s2 = 0.0;
-    for (long long m = (long long)blockIdx.x * 2 + half; m < M; m += (long long)gridDim.x * 2) {
-        const float z = __ldg(zsel + m * kC2 + c);
-        const float gy = __fmaf_rn(z, a, b) > 0.f ? __ldg(grad_out + m * ld + c) : 0.f;
-        gs[m * kC2 + c] = a * gy;
-        s1 += (double)gy;
-        s2 += (double)gy * (double)((z - mean) * inv);
+b_gy_kernel(int M, const float *__restrict__ zsel, const int *__restrict__ arg, const float *__restrict__ flt,
+            const float *__restrict__ grad_out, int ld, float *__restrict__ gs, unsigned *__restrict__ lst,
+            float *__restrict__ lgs, int *__restrict__ lcnt, double *__restrict__ dbl) {
+    __shared__ double acc_s[2][kC2];
+    __shared__ int cnt_s[kThreads / 32][32], st_s[kThreads / 32][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x < kC2) { acc_s[0][threadIdx.x] = 0.0; acc_s[1][threadIdx.x] = 0.0; }
+    __syncthreads();
+    float a[4], b[4], mean[4], inv[4];
+    double s1[4], s2[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int c = lane + 32 * j;
+        a[j] = __ldg(flt + fSc2 + c); b[j] = __ldg(flt + fSh2 + c);
+        mean[j] = __ldg(flt + fMean2 + c); inv[j] = __ldg(flt + fInv2 + c);
+        s1[j] = 0.0; s2[j] = 0.0;
     }
-    atomicAdd(dbl + dS1 + c, s1);
-    atomicAdd(dbl + dS2 + c, s2);
+    const unsigned lt = (1u << lane) - 1u;
+    for (long long m = (long long)blockIdx.x * (kThreads / 32) + warp; m < M; m += (long long)gridDim.x * (kThreads / 32)) {
+        float gv[4];
+        int kk[4], off[4];
+        cnt_s[warp][lane] = 0;
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int c = lane + 32 * j;
+            const float z = __ldg(zsel + m * kC2 + c);
+            const float gy = __fmaf_rn(z, a[j], b[j]) > 0.f ? __ldg(grad_out + m * ld + c) : 0.f;
+            gv[j] = a[j] * gy;
+            kk[j] = __ldg(arg + m * kC2 + c);
+            gs[m * kC2 + c] = gv[j];
+            s1[j] += (double)gy;
+            s2[j] += (double)gy * (double)((z - mean[j]) * inv[j]);
+            const bool nz = gv[j] != 0.f;
+            const unsigned peers = __match_any_sync(0xffffffffu, nz ? kk[j] : 64 + lane);
+            const int base = cnt_s[warp][kk[j]];
+            __syncwarp();
+            if (nz && (peers & lt) == 0) cnt_s[warp][kk[j]] = base + __popc(peers);
+            __syncwarp();
+            off[j] = base + __popc(peers & lt);
+        }
+        // exclusive scan of the 32 sample buckets
+        const int mine = cnt_s[warp][lane];
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        st_s[warp][lane] = incl - mine;
+        const int n = __shfl_sync(0xffffffffu, incl, 31);
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (gv[j] != 0.f) {
+                const int pos = st_s[warp][kk[j]] + off[j];
+                lst[m * kC2 + pos] = ((unsigned)kk[j] << 8) | (unsigned)(lane + 32 * j);
+                lgs[m * kC2 + pos] = gv[j];
+            }
+        }
+        const int n4 = (n + 3) & ~3;
+        if (lane < n4 - n) { lst[m * kC2 + n + lane] = 31u << 8; lgs[m * kC2 + n + lane] = 0.f; }
+        if (lane == 0) lcnt[m] = n4;
+        __syncwarp();
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        atomicAdd(&acc_s[0][lane + 32 * j], s1[j]);
+        atomicAdd(&acc_s[1][lane + 32 * j], s2[j]);
+    }
+    __syncthreads();
+    if (threadIdx.x < kC2) {
+        atomicAdd(dbl + dS1 + threadIdx.x, acc_s[0][threadIdx.x]);
+        atomicAdd(dbl + dS2 + threadIdx.x, acc_s[1][threadIdx.x]);
+    }
 }
 
 // e[c] = coefA (s2/P) invstd2, u[c] = coefA s1/P; Q = W2 diag(e) W2^T; cvec; W2 transposed; dgamma2, dbeta2
@@ -422,11 +506,10 @@ b_h1stats_kernel(long long P, int M, const float *__restrict__ x0, const float *
     float w1[C0];
     L1Params lp;
     load_l1<C0>(Wt1, flt, ci, w1, lp);
-    float g[4][4], a[32], hs = 0.f;
+    f2_t g2[4][2];
+    float a[32], hs = 0.f;
 #pragma unroll
-    for (int u = 0; u < 4; u++)
-#pragma unroll
-        for (int v = 0; v < 4; v++) g[u][v] = 0.f;
+    for (int u = 0; u < 4; u++) { g2[u][0] = 0ull; g2[u][1] = 0ull; }
 #pragma unroll
     for (int i = 0; i < 32; i++) a[i] = 0.f;
     double *mine = part + (size_t)blockIdx.x * kStatEnt;
@@ -434,7 +517,13 @@ b_h1stats_kernel(long long P, int M, const float *__restrict__ x0, const float *
 #pragma unroll
         for (int u = 0; u < 4; u++)
 #pragma unroll
-            for (int v = 0; v < 4; v++) { mine[(gi * 4 + u) * kC1 + gj * 4 + v] += (double)g[u][v]; g[u][v] = 0.f; }
+            for (int v = 0; v < 2; v++) {
+                float lo, hi;
+                unpack2(g2[u][v], lo, hi);
+                mine[(gi * 4 + u) * kC1 + gj * 4 + 2 * v] += (double)lo;
+                mine[(gi * 4 + u) * kC1 + gj * 4 + 2 * v + 1] += (double)hi;
+                g2[u][v] = 0ull;
+            }
 #pragma unroll
         for (int i = 0; i < 32; i++) { mine[kC1 * kC1 + (cg * 32 + i) * kC1 + ci] += (double)a[i]; a[i] = 0.f; }
         atomicAdd(mine + kC1 * kC1 + kC1 * kC2 + ci, (double)hs);
@@ -457,14 +546,12 @@ b_h1stats_kernel(long long P, int M, const float *__restrict__ x0, const float *
         for (int pos = 0; pos < kTP; pos++) {
             const float4 hi = *reinterpret_cast<const float4 *>(sH + pos * kLdH + gi * 4);
             const float4 hj = *reinterpret_cast<const float4 *>(sH + pos * kLdH + gj * 4);
-            g[0][0] = __fmaf_rn(hi.x, hj.x, g[0][0]); g[0][1] = __fmaf_rn(hi.x, hj.y, g[0][1]);
-            g[0][2] = __fmaf_rn(hi.x, hj.z, g[0][2]); g[0][3] = __fmaf_rn(hi.x, hj.w, g[0][3]);
-            g[1][0] = __fmaf_rn(hi.y, hj.x, g[1][0]); g[1][1] = __fmaf_rn(hi.y, hj.y, g[1][1]);
-            g[1][2] = __fmaf_rn(hi.y, hj.z, g[1][2]); g[1][3] = __fmaf_rn(hi.y, hj.w, g[1][3]);
-            g[2][0] = __fmaf_rn(hi.z, hj.x, g[2][0]); g[2][1] = __fmaf_rn(hi.z, hj.y, g[2][1]);
-            g[2][2] = __fmaf_rn(hi.z, hj.z, g[2][2]); g[2][3] = __fmaf_rn(hi.z, hj.w, g[2][3]);
-            g[3][0] = __fmaf_rn(hi.w, hj.x, g[3][0]); g[3][1] = __fmaf_rn(hi.w, hj.y, g[3][1]);
-            g[3][2] = __fmaf_rn(hi.w, hj.z, g[3][2]); g[3][3] = __fmaf_rn(hi.w, hj.w, g[3][3]);
+            const f2_t j01 = pack2(hj.x, hj.y), j23 = pack2(hj.z, hj.w);
+            const f2_t ix = pack2(hi.x, hi.x), iy = pack2(hi.y, hi.y), iz = pack2(hi.z, hi.z), iw = pack2(hi.w, hi.w);
+            ffma2(g2[0][0], ix, j01); ffma2(g2[0][1], ix, j23);
+            ffma2(g2[1][0], iy, j01); ffma2(g2[1][1], iy, j23);
+            ffma2(g2[2][0], iz, j01); ffma2(g2[2][1], iz, j23);
+            ffma2(g2[3][0], iw, j01); ffma2(g2[3][1], iw, j23);
         }
 #pragma unroll 8
         for (int r = 0; r < kK; r++) hs += sH[(cg * kK + r) * kLdH + ci];
@@ -486,18 +573,19 @@ b_h1stats_kernel(long long P, int M, const float *__restrict__ x0, const float *
 template <int C0>
 __global__ void __launch_bounds__(kThreads, 2)
 b_layer_kernel(long long P, int M, const float *__restrict__ x0, const float *__restrict__ flt,
-               const float *__restrict__ Wt1, const float *__restrict__ W2T, const float *__restrict__ gs, const int *__restrict__ arg,
-               float *__restrict__ tbuf, double *__restrict__ dbl) {
+               const float *__restrict__ Wt1, const float *__restrict__ W2T, const unsigned *__restrict__ lst,
+               const float *__restrict__ lgs, const int *__restrict__ lcnt, float *__restrict__ tbuf, double *__restrict__ dbl) {
     constexpr int C_in = C0 - 3;
     extern __shared__ __align__(16) unsigned char tf_sm[];
     float *sH = reinterpret_cast<float *>(tf_sm);   // [128][68]
     float *sQ = sH + kTP * kLdH;                    // [64][64]
     float *sS = sQ + kC1 * kC1;                     // [128][64]
     float *sX = sS + kTP * kC1;                     // [128][C0] (room for 8)
-    float *sGs = sX + kTP * 8;                      // [4][128]
-    int *sArg = reinterpret_cast<int *>(sGs + 4 * kC2);
-    float *sAl = reinterpret_cast<float *>(sArg + 4 * kC2);  // [C_in][64]
+    float *sLgs = sX + kTP * 8;                     // [4][128] list values (coefA g_y), sorted by sample
+    unsigned *sLst = reinterpret_cast<unsigned *>(sLgs + 4 * kC2);   // [4][128] (sample << 8) | channel
+    float *sAl = reinterpret_cast<float *>(sLst + 4 * kC2);  // [C_in][64]
     float *sCv = sAl + 5 * kC1;                     // [64]
+    __shared__ int sCnt[4];
     const int t = threadIdx.x;
     for (int e = t; e < kC1 * kC1; e += kThreads) sQ[e] = __ldg(flt + fQ + e);
     for (int e = t; e < C_in * kC1; e += kThreads) sAl[e] = __ldg(flt + fAlpha + e);
@@ -517,54 +605,76 @@ b_layer_kernel(long long P, int M, const float *__restrict__ x0, const float *__
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         __syncthreads();
         load_x_tile<C0>(x0, sX, tile * kTP, P);
-        for (int e = t; e < 4 * kC2; e += kThreads) {
+        if (t < 4) sCnt[t] = tile * 4 + t < M ? __ldg(lcnt + tile * 4 + t) : 0;
+        for (int e = t; e < 4 * kC2; e += kThreads) {       // entries past the count are never used
             const long long m = tile * 4 + (e >> 7);
-            sGs[e] = m < M ? __ldg(gs + m * kC2 + (e & 127)) : 0.f;
-            sArg[e] = m < M ? __ldg(arg + m * kC2 + (e & 127)) : 0;
+            sLgs[e] = m < M ? __ldg(lgs + m * kC2 + (e & 127)) : 0.f;
+            sLst[e] = m < M ? __ldg(lst + m * kC2 + (e & 127)) : 0u;
         }
         __syncthreads();
         h1_tile<C0>(sX, sH, w1, lp, c1, q, tile * 4 + q < M);
 #pragma unroll 8
         for (int r = 0; r < kK; r++) sS[(q * kK + r) * kC1 + c1] = 0.f;
-#pragma unroll 4
-        for (int c = 0; c < kC2; c++) {
-            const float gv = sGs[q * kC2 + c];                       // warp-uniform
-            if (gv != 0.f) {
-                float *d = sS + (q * kK + sArg[q * kC2 + c]) * kC1 + c1;
-                *d = __fmaf_rn(gv, __ldg(W2T + c * kC1 + c1), *d);
+        {   // rows of the sparse term: the list is sorted by sample, so a row is accumulated in a register
+            const int n = sCnt[q];
+            int kcur = 0;
+            float racc = 0.f;
+            float *srow = sS + (q * kK) * kC1 + c1;
+            for (int e = 0; e < n; e += 4) {
+                const uint4 pk = *reinterpret_cast<const uint4 *>(sLst + q * kC2 + e);
+                const float4 gv = *reinterpret_cast<const float4 *>(sLgs + q * kC2 + e);
+                const float w0 = __ldg(W2T + (pk.x & 255u) * kC1 + c1), w1v = __ldg(W2T + (pk.y & 255u) * kC1 + c1);
+                const float w2 = __ldg(W2T + (pk.z & 255u) * kC1 + c1), w3 = __ldg(W2T + (pk.w & 255u) * kC1 + c1);
+                int k = (int)(pk.x >> 8);
+                if (k != kcur) { srow[kcur * kC1] = racc; racc = 0.f; kcur = k; }
+                racc = __fmaf_rn(gv.x, w0, racc);
+                k = (int)(pk.y >> 8);
+                if (k != kcur) { srow[kcur * kC1] = racc; racc = 0.f; kcur = k; }
+                racc = __fmaf_rn(gv.y, w1v, racc);
+                k = (int)(pk.z >> 8);
+                if (k != kcur) { srow[kcur * kC1] = racc; racc = 0.f; kcur = k; }
+                racc = __fmaf_rn(gv.z, w2, racc);
+                k = (int)(pk.w >> 8);
+                if (k != kcur) { srow[kcur * kC1] = racc; racc = 0.f; kcur = k; }
+                racc = __fmaf_rn(gv.w, w3, racc);
             }
+            srow[kcur * kC1] = racc;
         }
         __syncthreads();
-        float acc[8][4];
+        f2_t acc2[8][2];
 #pragma unroll
-        for (int r = 0; r < 8; r++)
-#pragma unroll
-            for (int v = 0; v < 4; v++) acc[r][v] = 0.f;
-        const float *aBase = sH + (pg * 8) * kLdH;
+        for (int r = 0; r < 8; r++) { acc2[r][0] = 0ull; acc2[r][1] = 0ull; }
+        const float *aBase = sH + pg * kLdH;                // positions 16 r + pg: the two half-warps read adjacent rows
         const float *bBase = sQ + cg * 4;
 #pragma unroll 1
         for (int k4 = 0; k4 < kC1 / 4; k4++) {
             float4 a[8];
 #pragma unroll
-            for (int r = 0; r < 8; r++) a[r] = *reinterpret_cast<const float4 *>(aBase + r * kLdH + k4 * 4);
+            for (int r = 0; r < 8; r++) a[r] = *reinterpret_cast<const float4 *>(aBase + r * 16 * kLdH + k4 * 4);
 #pragma unroll
             for (int kk = 0; kk < 4; kk++) {
                 const float4 b = *reinterpret_cast<const float4 *>(bBase + (k4 * 4 + kk) * kC1);
+                const f2_t b01 = pack2(b.x, b.y), b23 = pack2(b.z, b.w);
 #pragma unroll
                 for (int r = 0; r < 8; r++) {
                     const float av = kk == 0 ? a[r].x : kk == 1 ? a[r].y : kk == 2 ? a[r].z : a[r].w;
-                    acc[r][0] = __fmaf_rn(av, b.x, acc[r][0]);
-                    acc[r][1] = __fmaf_rn(av, b.y, acc[r][1]);
-                    acc[r][2] = __fmaf_rn(av, b.z, acc[r][2]);
-                    acc[r][3] = __fmaf_rn(av, b.w, acc[r][3]);
+                    const f2_t aa = pack2(av, av);
+                    ffma2(acc2[r][0], aa, b01);
+                    ffma2(acc2[r][1], aa, b23);
                 }
             }
+        }
+        float acc[8][4];
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            unpack2(acc2[r][0], acc[r][0], acc[r][1]);
+            unpack2(acc2[r][1], acc[r][2], acc[r][3]);
         }
         const float4 cv = *reinterpret_cast<const float4 *>(sCv + cg * 4);
         const long long p0 = tile * kTP;
 #pragma unroll
         for (int r = 0; r < 8; r++) {
-            const int pos = pg * 8 + r;
+            const int pos = r * 16 + pg;
             const float4 h4 = *reinterpret_cast<const float4 *>(sH + pos * kLdH + cg * 4);
             const float4 s4 = *reinterpret_cast<const float4 *>(sS + pos * kC1 + cg * 4);
             float gy[4];
@@ -718,7 +828,7 @@ int forward_t(int B, int M, const float *xyz, const float *new_xyz, const float 
     float *x0 = reinterpret_cast<float *>(W + l.x0);
     double *dbl = reinterpret_cast<double *>(W + l.dbl);
     float *flt = reinterpret_cast<float *>(W + l.flt);
-    float *zmax = reinterpret_cast<float *>(W + l.zmax), *zmin = reinterpret_cast<float *>(W + l.zmin);
+    float *zmax = reinterpret_cast<float *>(W + l.zmax);
     int *arg = reinterpret_cast<int *>(W + l.arg);
     MGAR_CUDA(cudaMemsetAsync(dbl, 0, (size_t)dFwdEnd * 8, st));
     int g0 = div_up(M, kThreads / 32);
@@ -727,9 +837,9 @@ int forward_t(int B, int M, const float *xyz, const float *new_xyz, const float 
                                                   empty_mask, x0, dbl);
     f_bn1_kernel<C0><<<1, kC1, 0, st>>>(P, eps, weights, gamma_beta, dbl, flt, batch_stats);
     MGAR_CUDA(cudaFuncSetAttribute(f_layer2_kernel<C0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemF1));
-    f_layer2_kernel<C0><<<grid_tiles(M), kThreads, kSmemF1, st>>>(P, M, x0, flt, weights, weights + C0 * kC1, zmax, zmin, arg, dbl);
+    f_layer2_kernel<C0><<<grid_tiles(M), kThreads, kSmemF1, st>>>(P, M, x0, flt, weights, weights + C0 * kC1, gamma_beta + 2 * kC1, zmax, arg, dbl);
     f_bn2_kernel<<<1, kC2, 0, st>>>(P, eps, gamma_beta, dbl, flt, batch_stats);
-    f_pool_kernel<<<div_up((long long)M * kC2, kThreads), kThreads, 0, st>>>((long long)M * kC2, flt, zmax, zmin, arg, out, ld_out);
+    f_pool_kernel<<<div_up((long long)M * kC2, kThreads), kThreads, 0, st>>>((long long)M * kC2, flt, gamma_beta + 2 * kC1, zmax, out, ld_out);
     count_launch(5);
     return check_launch("sa_mlp_fwd_train (fast)");
 }
@@ -743,7 +853,7 @@ int backward_t(int B, int M, const int *pre_xyz, const int *pre_new, int uniform
     double *dbl = reinterpret_cast<double *>(W + l.dbl);
     float *flt = reinterpret_cast<float *>(W + l.flt);
     const float *zsel = reinterpret_cast<const float *>(W + l.zmax);
-    float *gs = reinterpret_cast<float *>(W + l.zmin);
+    float *gs = reinterpret_cast<float *>(W + l.gs);
     const int *arg = reinterpret_cast<const int *>(W + l.arg);
     float *tbuf = grad_features ? reinterpret_cast<float *>(W + l.t) : nullptr;
     double *part = reinterpret_cast<double *>(W + l.part);
@@ -752,14 +862,17 @@ int backward_t(int B, int M, const int *pre_xyz, const int *pre_new, int uniform
     const int grid = grid_tiles(M);
     MGAR_CUDA(cudaMemsetAsync(dbl + dS1, 0, (size_t)(dRed - dS1) * 8, st));
     MGAR_CUDA(cudaMemsetAsync(part, 0, (size_t)grid * kStatEnt * 8, st));
-    int gg = div_up(M, 2 * 16);
-    if (gg > kNumSMs * 4) gg = kNumSMs * 4;
-    b_gy_kernel<<<gg, kThreads, 0, st>>>(M, zsel, flt, grad_out, ld_grad, gs, dbl);
+    unsigned *lst = reinterpret_cast<unsigned *>(W + l.lst);
+    float *lgs = reinterpret_cast<float *>(W + l.lgs);
+    int *lcnt = reinterpret_cast<int *>(W + l.lcnt);
+    int gg = div_up(M, kThreads / 32);
+    if (gg > kNumSMs * 8) gg = kNumSMs * 8;
+    b_gy_kernel<<<gg, kThreads, 0, st>>>(M, zsel, arg, flt, grad_out, ld_grad, gs, lst, lgs, lcnt, dbl);
     b_prep_kernel<<<17, kThreads, 0, st>>>(P, Wt2, dbl, flt, W2T, gGB);
     MGAR_CUDA(cudaFuncSetAttribute(b_h1stats_kernel<C0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemB1a));
     b_h1stats_kernel<C0><<<grid, kThreads, kSmemB1a, st>>>(P, M, x0, flt, Wt1, gs, arg, part);
     MGAR_CUDA(cudaFuncSetAttribute(b_layer_kernel<C0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemB1));
-    b_layer_kernel<C0><<<grid, kThreads, kSmemB1, st>>>(P, M, x0, flt, Wt1, W2T, gs, arg, tbuf, dbl);
+    b_layer_kernel<C0><<<grid, kThreads, kSmemB1, st>>>(P, M, x0, flt, Wt1, W2T, lst, lgs, lcnt, tbuf, dbl);
     b_reduce_kernel<<<div_up(kStatEnt, kThreads), kThreads, 0, st>>>(grid, part, dbl + dRed);
     b_finalize_kernel<C0><<<33, kThreads, 0, st>>>(P, Wt1, Wt2, flt, dbl, gW, gGB);
     count_launch(6);

@@ -44,7 +44,7 @@ def main():
         out.square().sum().backward()
         mod.zero_grad(set_to_none=True)
 
-    for name in ("native", "native_generic", "torch"):
+    for name in os.environ.get("MODES", "native,native_generic,torch").split(","):
         os.environ["MGAR_SA_TRAIN"] = "torch" if name == "torch" else "native"
         os.environ["MGAR_SA_TRAIN_KERNELS"] = "generic" if name == "native_generic" else "fast"
         if name == "native_generic" and F_ > 16:
