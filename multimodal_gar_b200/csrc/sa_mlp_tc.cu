@@ -444,6 +444,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     A.sc2 = A.w2t + kTcC1 * kTcC2; A.sh2 = A.sc2 + kTcC2;
     A.out = out; A.ld_out = ld_out;
     A.gmax = group_max; A.group_size = group_size > 0 ? group_size : 1; A.group_zero = group_zero;
+    A.tr_zext = nullptr; A.tr_arg = nullptr; A.tr_sum = nullptr; A.tr_sq = nullptr;
     A.packed4 = (C0 == 4 && xyz_stride == 4 && feat_stride == 4 && features == xyz + 3 &&
                  (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) ? 1 : 0;
 #ifdef MGAR_TC_TRACE

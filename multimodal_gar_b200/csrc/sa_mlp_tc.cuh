@@ -31,9 +31,14 @@ struct TcArgs {
     long long *trace;                    // timeline stamps of CTA 0, tiles 100..131 (debug build only)
 #endif
     int packed4;                         // xyz/features are columns 0..2 / 3 of one 16B-aligned (N,4) array
+    // training-statistics variant (sa_mlp_tc16_launch_train): sc2 holds +-1 = sign(gamma2), sh2 zeros, no BatchNorm /
+    // ReLU in the epilogue; per (centroid, channel) the extreme of sign * z2 over the samples and the first sample
+    // attaining it, per channel sum z2 and sum z2^2 (fp64 atomics)
+    float *tr_zext; int *tr_arg; double *tr_sum, *tr_sq;
 };
 
 // sa_mlp_tc16.cu: the 3xFP16 kernel (default); sa_mlp_tc.cu keeps the 3xTF32 kernel (MGAR_TC_MODE=tf32)
 int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);
+int sa_mlp_tc16_launch_train(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);   // C0 = 4, 5
 
 }  // namespace mgar

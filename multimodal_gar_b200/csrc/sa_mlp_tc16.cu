@@ -88,6 +88,22 @@ __device__ __forceinline__ float max32(const uint32_t (&v)[32]) {
     return max3(a, b, fmaxf(__uint_as_float(v[30]), __uint_as_float(v[31])));
 }
 
+// training-statistics epilogue: max, first index attaining it, sum and sum of squares of 32 accumulator values
+__device__ __forceinline__ void tr_reduce32(const uint32_t (&v)[32], float &mx, int &arg, float &s, float &q) {
+    mx = max32(v);
+    arg = 31;
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+    for (int k = 30; k >= 0; k--) arg = __uint_as_float(v[k]) == mx ? k : arg;
+#pragma unroll
+    for (int k = 0; k < 32; k += 2) {
+        const float a = __uint_as_float(v[k]), b = __uint_as_float(v[k + 1]);
+        s0 += a; s1 += b;
+        q0 = __fmaf_rn(a, a, q0); q1 = __fmaf_rn(b, b, q1);
+    }
+    s = s0 + s1; q = q0 + q1;
+}
+
 #ifdef MGAR_TC16_TRACE
 __device__ long long g_tc16_trace[32 * 16];        // timeline of CTA 0, local tiles 100..131 (debug build only)
 #define TR(slot, i) do { if (blockIdx.x == 0 && lane == 0 && (i) >= 100 && (i) < 132) g_tc16_trace[((i) - 100) * 16 + (slot)] = clock64(); } while (0)
@@ -121,7 +137,7 @@ __device__ __forceinline__ void sts_pack2_w(uint32_t a0, uint32_t a1, uint32_t b
     sts4(b0, lo[0], lo[1], lo[2], lo[3]); sts4(b1, lo[4], hi[3], hi[4], 0.f);
 }
 
-template <int C0>
+template <int C0, bool kTrain = false>
 __global__ void __launch_bounds__(kThreads, 1)
 sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcBound BD, const __grid_constant__ TcArgs A) {
     static_assert(C0 >= 3 && C0 <= 7, "layer-1 K is padded to 8 with one column for the folded bias");
@@ -196,6 +212,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
     // W2 lives in TENSOR MEMORY as the A operand of the layer-2 MMA (lane = output channel; a 32-bit column
     // holds the fp16 pair k = 2j, 2j+1), scaled into the fp16 range and sign-aligned with scale2 (see header).
     float asc = 0.f, shift = 0.f;        // epilogue: |scale2| * 2^-ec and shift2 of this thread's channel
+    float sgn = 1.f;
     if (warp < 4) {
         const int c = tid;
         const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
@@ -209,6 +226,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         const float up = __uint_as_float((uint32_t)(267 - eb) << 23);        // 2^(13 - floor(log2 amax))
         const float down = __uint_as_float((uint32_t)(eb - 13) << 23);       // its inverse
         const float sup = sc < 0.f ? -up : up;
+        sgn = sc < 0.f ? -1.f : 1.f;
         asc = __fmul_rn(fabsf(sc), down);
         uint32_t hi[32], lo[32];
 #pragma unroll
@@ -224,6 +242,55 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
     if (warp < 4) {
         // ===== epilogue: thread = output channel, 32 consecutive TMEM columns = one centroid ==========
         const int c = tid;
+        if constexpr (kTrain) {
+            // training statistics (sa_mlp_train_fast.cu, identity 1): no BatchNorm yet - its statistics are what
+            // is being gathered.  The accumulator holds sign(gamma2) * z2 * 2^(ec - e): extreme and its first
+            // sample per centroid, sum and sum of squares per channel (fp32 over 32 samples, fp64 across).
+            double dsum = 0.0, dsq = 0.0;
+            int m_next = t_beg * 4;
+            for (int i = 0; i < my_tiles; i++) {
+                const int t = i % kAcc, u = i / kAcc;
+                mbar_wait(TFULL(t), u & 1);
+                tc_fence_after();
+                const float4 inv = *reinterpret_cast<const float4 *>(&s_inv[i % kRing][0]);
+                const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
+                float zx[4], ps[4], pq[4];
+                int ar[4];
+                {
+                    uint32_t v0[32], v1[32];
+                    tc_ld32(taddr, v0);
+                    tc_ld32(taddr + 32, v1);
+                    tc_wait_ld();
+                    tr_reduce32(v0, zx[0], ar[0], ps[0], pq[0]);
+                    tr_reduce32(v1, zx[1], ar[1], ps[1], pq[1]);
+                    const uint32_t dep = (__float_as_uint(zx[0]) & __float_as_uint(zx[1])) == 0xffffffffu ? 1u : 0u;
+                    tc_ld32(taddr + 64 + dep, v0);
+                    tc_ld32(taddr + 96 + dep, v1);
+                    tc_wait_ld();
+                    tr_reduce32(v0, zx[2], ar[2], ps[2], pq[2]);
+                    tr_reduce32(v1, zx[3], ar[3], ps[3], pq[3]);
+                }
+                tc_fence_before();
+                mbar_arrive_relaxed(TEMPTY(t));
+                const float sq[4] = {inv.x, inv.y, inv.z, inv.w};
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const int m = m_next + q;
+                    if (m < M) {
+                        const float scale = __fmul_rn(asc, sq[q]);            // exact power of two
+                        A.tr_zext[(size_t)m * kTcC2 + c] = __fmul_rn(zx[q], scale);
+                        A.tr_arg[(size_t)m * kTcC2 + c] = ar[q];
+                        dsum += (double)ps[q] * (double)scale;
+                        dsq += (double)pq[q] * (double)scale * (double)scale;
+                    }
+                }
+                m_next += 4;
+            }
+            if (my_tiles > 0) {
+                atomicAdd(A.tr_sum + c, (double)sgn * dsum);
+                atomicAdd(A.tr_sq + c, dsq);
+            }
+        } else {
         const int gs = A.group_size;
         int m_next = t_beg * 4;                                   // first centroid of the next tile
         int grp = A.gmax ? m_next / gs : 0, g_end = (grp + 1) * gs;
@@ -290,6 +357,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             if (outp) outp += (size_t)4 * A.ld_out;
         }
         if (A.gmax && my_tiles > 0) flush();
+        }
     } else if (warp == 4 || warp == 14) {
         // ===== layer-2 MMA issuers: warp 4 takes the even tiles, warp 14 the odd ones.  Per tile 12 x (128x128x16):
         // small terms first (W2lo*h1hi, W2hi*h1lo), then W2hi*h1hi.  K step kk: 8 TMEM columns of W2, 32 bytes
@@ -539,6 +607,27 @@ int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cu
     MGAR_TC16_CASE(3) MGAR_TC16_CASE(4) MGAR_TC16_CASE(5) MGAR_TC16_CASE(6) MGAR_TC16_CASE(7)
 #undef MGAR_TC16_CASE
     set_error("sa_mlp_tc16: unsupported C0=%d", C0);
+    return MGAR_EINVAL;
+}
+
+int sa_mlp_tc16_launch_train(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st) {
+    TcBound BD;
+    BD.shmax = 0.f;
+    for (int c = 0; c < 8; c++) BD.wmax[c] = 0.f;
+    for (int o = 0; o < kTcC1; o++) {
+        for (int c = 0; c < C0; c++) BD.wmax[c] = fmaxf(BD.wmax[c], fabsf(L1.w[c][o]));
+        BD.shmax = fmaxf(BD.shmax, fabsf(L1.sh[o]));
+    }
+#define MGAR_TC16_TRAIN_CASE(c0)                                                                                          \
+    if (C0 == c0) {                                                                                                       \
+        MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<c0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem)); \
+        sa_mlp_tc16_kernel<c0, true><<<grid, kThreads, kSmem, st>>>(L1, BD, A);                                           \
+        count_launch();                                                                                                   \
+        return check_launch("sa_mlp_tc16 (training statistics)");                                                         \
+    }
+    MGAR_TC16_TRAIN_CASE(4) MGAR_TC16_TRAIN_CASE(5)
+#undef MGAR_TC16_TRAIN_CASE
+    set_error("sa_mlp_tc16 (training statistics): unsupported C0=%d", C0);
     return MGAR_EINVAL;
 }
 

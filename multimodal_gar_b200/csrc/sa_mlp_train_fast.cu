@@ -30,6 +30,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include "sa_mlp_tc.cuh"
 #include "stack_prefix.cuh"
 
 namespace mgar {
@@ -47,7 +48,7 @@ constexpr int dS1 = 328, dS2 = 456, dD = 584, dS11 = 1096, dRed = 1160, dTotal =
 // fp32 block (indices in floats)
 constexpr int fMean1 = 0, fInv1 = 64, fSc1 = 128, fSh1 = 192, fAlpha = 768, fMean2 = 1088, fInv2 = 1216,
               fSc2 = 1344, fSh2 = 1472, fQ = 1600, fCvec = 5696, fE = 5760, fU = 5888, fQf = 6016, fCf = 6056,
-              fTotal = 6064;
+              fSgn2 = 6064, fZero2 = 6192, fTotal = 6320;
 
 struct Layout {
     size_t x0, zmax, gs, arg, t, lst, lgs, lcnt, part, dbl, flt, w2t, total;
@@ -197,6 +198,10 @@ __global__ void f_bn1_kernel(long long P, float eps, const float *__restrict__ W
 #pragma unroll
     for (int f = 0; f < C0 - 3; f++) flt[fAlpha + f * kC1 + c] = (float)(sc * w[3 + f]);
     if (batch_stats) { batch_stats[c] = (float)mean; batch_stats[kC1 + c] = (float)var; }
+    for (int k = c; k < kC2; k += kC1) {      // sign(gamma2) and a zero shift: the tensor-core statistics pass
+        flt[fSgn2 + k] = gamma_beta[2 * kC1 + k] < 0.f ? -1.f : 1.f;
+        flt[fZero2 + k] = 0.f;
+    }
 }
 
 // h1 rows of one 128-position tile: thread (c1 = t & 63, q = t >> 6) writes channel c1 of the 32 rows of centroid q.
@@ -836,11 +841,43 @@ int forward_t(int B, int M, const float *xyz, const float *new_xyz, const float 
     f_group_kernel<C0><<<g0, kThreads, 0, st>>>(B, M, xyz, new_xyz, features, pre_xyz, pre_new, uniform, n_u, m_u, idx,
                                                   empty_mask, x0, dbl);
     f_bn1_kernel<C0><<<1, kC1, 0, st>>>(P, eps, weights, gamma_beta, dbl, flt, batch_stats);
-    MGAR_CUDA(cudaFuncSetAttribute(f_layer2_kernel<C0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemF1));
-    f_layer2_kernel<C0><<<grid_tiles(M), kThreads, kSmemF1, st>>>(P, M, x0, flt, weights, weights + C0 * kC1, gamma_beta + 2 * kC1, zmax, arg, dbl);
+    const char *mode = getenv("MGAR_SA_TRAIN_KERNELS");
+    if (!(mode && strcmp(mode, "tc") == 0)) {
+        MGAR_CUDA(cudaFuncSetAttribute(f_layer2_kernel<C0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemF1));
+        f_layer2_kernel<C0><<<grid_tiles(M), kThreads, kSmemF1, st>>>(P, M, x0, flt, weights, weights + C0 * kC1, gamma_beta + 2 * kC1, zmax, arg, dbl);
+        count_launch();
+    } else {
+        // layer 2 on the tensor cores: the inference kernel (sa_mlp_tc16.cu, tcgen05 3xFP16) with the statistics
+        // epilogue.  Its layer-1 parameters are kernel arguments, so BatchNorm 1's batch scale / shift (256 B) and
+        // W1 come back to the host first: one small D2H copy and a stream synchronisation per step.
+        float h_ss[2 * kC1], h_w1[8 * kC1];
+        MGAR_CUDA(cudaMemcpyAsync(h_ss, flt + fSc1, sizeof(h_ss), cudaMemcpyDeviceToHost, st));
+        MGAR_CUDA(cudaMemcpyAsync(h_w1, weights, (size_t)C0 * kC1 * 4, cudaMemcpyDeviceToHost, st));
+        MGAR_CUDA(cudaStreamSynchronize(st));
+        TcLayer1 L1;
+        for (int o = 0; o < kC1; o++) {
+            for (int c = 0; c < 8; c++) L1.w[c][o] = c < C0 ? h_w1[c * kC1 + o] * h_ss[o] : 0.f;
+            L1.sh[o] = h_ss[kC1 + o];
+        }
+        TcArgs A;
+        A.B = B; A.M = M; A.C_in = C0 - 3;
+        A.xyz = xyz; A.xyz_stride = 3; A.new_xyz = new_xyz;
+        A.features = features; A.feat_stride = C0 - 3;
+        A.pre_xyz = pre_xyz; A.pre_new = pre_new; A.uniform = uniform; A.n_u = n_u; A.m_u = m_u;
+        A.idx = idx; A.empty_mask = empty_mask;
+        A.w2t = weights + C0 * kC1; A.sc2 = flt + fSgn2; A.sh2 = flt + fZero2;
+        A.out = nullptr; A.ld_out = 0; A.gmax = nullptr; A.group_size = 1; A.group_zero = nullptr;
+        A.packed4 = 0;
+#ifdef MGAR_TC_TRACE
+        A.trace = nullptr;
+#endif
+        A.tr_zext = zmax; A.tr_arg = arg; A.tr_sum = dbl + dSum2; A.tr_sq = dbl + dSq2;
+        const int n_tiles = (M + 3) / 4;
+        if (int rc = sa_mlp_tc16_launch_train(L1, A, C0, n_tiles < kNumSMs ? n_tiles : kNumSMs, st)) return rc;
+    }
     f_bn2_kernel<<<1, kC2, 0, st>>>(P, eps, gamma_beta, dbl, flt, batch_stats);
     f_pool_kernel<<<div_up((long long)M * kC2, kThreads), kThreads, 0, st>>>((long long)M * kC2, flt, gamma_beta + 2 * kC1, zmax, out, ld_out);
-    count_launch(5);
+    count_launch(4);
     return check_launch("sa_mlp_fwd_train (fast)");
 }
 

@@ -36,6 +36,8 @@ def _run(mod, args, feats, w_out):
     ([0.6], [32], [[2, 64, 128]], "max_pool", "fast"),       # hot-path shape: sa_mlp_train_fast.cu, C0 = 5
     ([0.6], [32], [[1, 64, 128]], "max_pool", "fast"),       # the same with one feature channel (intensity), C0 = 4
     ([0.25], [32], [[1, 64, 128]], "max_pool", "fast"),      # small balls: duplicated samples, empty balls
+    ([0.6], [32], [[2, 64, 128]], "max_pool", "tc"),         # layer-2 forward on tcgen05 (3xFP16) instead of CUDA cores
+    ([0.25], [32], [[1, 64, 128]], "max_pool", "tc"),
     ([0.6], [32], [[2, 64, 128]], "max_pool", "generic"),    # the generic kernels on the same shape
     ([0.6], [32], [[2, 64, 128]], "avg_pool", "fast"),       # avg-pool is not specialised: falls through to generic
     ([0.3, 0.8], [8, 16], [[2, 16, 32], [2, 8, 24, 40]], "max_pool", "fast"),
@@ -44,8 +46,8 @@ def _run(mod, args, feats, w_out):
 def test_training_forward_backward_match_torch_composition(cuda, monkeypatch, radii, nsamples, mlps, pool, kernels):
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
-    if kernels == "generic":
-        monkeypatch.setenv("MGAR_SA_TRAIN_KERNELS", "generic")
+    if kernels != "fast":
+        monkeypatch.setenv("MGAR_SA_TRAIN_KERNELS", kernels)
     xyz, cnt, new_xyz, ncnt, feats = cases.ragged_case()
     feats = np.ascontiguousarray(feats[:, :mlps[0][0]])
     torch.manual_seed(11)
