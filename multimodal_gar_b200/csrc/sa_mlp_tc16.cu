@@ -88,11 +88,15 @@ __device__ __forceinline__ float max32(const uint32_t (&v)[32]) {
     return max3(a, b, fmaxf(__uint_as_float(v[30]), __uint_as_float(v[31])));
 }
 
-// training-statistics epilogue: max, first index attaining it, sum and sum of squares of 32 accumulator values
-__device__ __forceinline__ void tr_reduce32(const uint32_t (&v)[32], float &mx, int &arg, float &s, float &q) {
+// training-statistics epilogue: max, first index attaining it, sum and sum of squares of 32 accumulator values.
+// The 3xFP16 accumulator carries ~2^-22 of the products' magnitude, so two DIFFERENT samples closer than that can
+// swap places against an fp32 evaluation; `near` reports a runner-up within 2^-14 of the centroid's rms (a wide
+// margin over the split's error) and the caller re-evaluates those few entries in exact fp32.
+__device__ __forceinline__ void tr_reduce32(const uint32_t (&v)[32], float &mx, int &arg, float &s, float &q, bool &near) {
     mx = max32(v);
     arg = 31;
     float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+    float r0 = -INFINITY, r1 = -INFINITY;               // runner-up: largest value different from the maximum
 #pragma unroll
     for (int k = 30; k >= 0; k--) arg = __uint_as_float(v[k]) == mx ? k : arg;
 #pragma unroll
@@ -100,8 +104,11 @@ __device__ __forceinline__ void tr_reduce32(const uint32_t (&v)[32], float &mx, 
         const float a = __uint_as_float(v[k]), b = __uint_as_float(v[k + 1]);
         s0 += a; s1 += b;
         q0 = __fmaf_rn(a, a, q0); q1 = __fmaf_rn(b, b, q1);
+        r0 = fmaxf(r0, a == mx ? -INFINITY : a);
+        r1 = fmaxf(r1, b == mx ? -INFINITY : b);
     }
     s = s0 + s1; q = q0 + q1;
+    near = mx - fmaxf(r0, r1) <= 6.1035156e-5f * sqrtf(q * 0.03125f);
 }
 
 #ifdef MGAR_TC16_TRACE
@@ -256,19 +263,20 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
                 const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(t * 128);
                 float zx[4], ps[4], pq[4];
                 int ar[4];
+                bool nr[4];
                 {
                     uint32_t v0[32], v1[32];
                     tc_ld32(taddr, v0);
                     tc_ld32(taddr + 32, v1);
                     tc_wait_ld();
-                    tr_reduce32(v0, zx[0], ar[0], ps[0], pq[0]);
-                    tr_reduce32(v1, zx[1], ar[1], ps[1], pq[1]);
+                    tr_reduce32(v0, zx[0], ar[0], ps[0], pq[0], nr[0]);
+                    tr_reduce32(v1, zx[1], ar[1], ps[1], pq[1], nr[1]);
                     const uint32_t dep = (__float_as_uint(zx[0]) & __float_as_uint(zx[1])) == 0xffffffffu ? 1u : 0u;
                     tc_ld32(taddr + 64 + dep, v0);
                     tc_ld32(taddr + 96 + dep, v1);
                     tc_wait_ld();
-                    tr_reduce32(v0, zx[2], ar[2], ps[2], pq[2]);
-                    tr_reduce32(v1, zx[3], ar[3], ps[3], pq[3]);
+                    tr_reduce32(v0, zx[2], ar[2], ps[2], pq[2], nr[2]);
+                    tr_reduce32(v1, zx[3], ar[3], ps[3], pq[3], nr[3]);
                 }
                 tc_fence_before();
                 mbar_arrive_relaxed(TEMPTY(t));
@@ -279,7 +287,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
                     if (m < M) {
                         const float scale = __fmul_rn(asc, sq[q]);            // exact power of two
                         A.tr_zext[(size_t)m * kTcC2 + c] = __fmul_rn(zx[q], scale);
-                        A.tr_arg[(size_t)m * kTcC2 + c] = ar[q];
+                        A.tr_arg[(size_t)m * kTcC2 + c] = ar[q] | (nr[q] ? 0x100 : 0);   // 0x100: near tie, see tr_reduce32
                         dsum += (double)ps[q] * (double)scale;
                         dsq += (double)pq[q] * (double)scale * (double)scale;
                     }

@@ -348,6 +348,51 @@ f_layer2_kernel(long long P, int M, const float *__restrict__ x0, const float *_
     }
 }
 
+// Entries the tensor-core statistics pass flagged (a runner-up sample within the 3xFP16 split's error of the
+// extreme): the 32 samples are re-evaluated in exact fp32 with f_layer2_kernel's arithmetic (h1 chain, then z2 as an
+// FMA chain over the 64 inputs in ascending order) and the extreme / first sample are rewritten.  Warp per entry,
+// lane = sample; a few entries per thousand.
+template <int C0>
+__global__ void __launch_bounds__(kThreads)
+f_fix_ties_kernel(long long n, const float *__restrict__ x0, const float *__restrict__ flt, const float *__restrict__ Wt1,
+                  const float *__restrict__ Wt2, const float *__restrict__ gamma2, float *__restrict__ zmax,
+                  int *__restrict__ arg) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * kThreads + threadIdx.x) >> 5, nwarps = ((long long)gridDim.x * kThreads) >> 5;
+    for (long long e0 = warp * 32; e0 < n; e0 += nwarps * 32) {
+        const long long e = e0 + lane;
+        const int a = e < n ? arg[e] : 0;
+        unsigned todo = __ballot_sync(0xffffffffu, (a & 0x100) != 0);
+        while (todo) {
+            const int b = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const long long ee = e0 + b, m = ee >> 7;
+            const int c = (int)(ee & (kC2 - 1));
+            float x[C0];
+#pragma unroll
+            for (int i = 0; i < C0; i++) x[i] = __ldg(x0 + (m * kK + lane) * C0 + i);
+            float z2 = 0.f;
+            for (int j = 0; j < kC1; j++) {
+                float z1 = 0.f;
+#pragma unroll
+                for (int i = 0; i < C0; i++) z1 = __fmaf_rn(x[i], __ldg(Wt1 + i * kC1 + j), z1);
+                const float h = fmaxf(__fmaf_rn(z1, __ldg(flt + fSc1 + j), __ldg(flt + fSh1 + j)), 0.f);
+                z2 = __fmaf_rn(h, __ldg(Wt2 + j * kC2 + c), z2);
+            }
+            float v = __ldg(gamma2 + c) < 0.f ? -z2 : z2;
+            int k = lane;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+                const int ok = __shfl_xor_sync(0xffffffffu, k, o);
+                if (ov > v || (ov == v && ok < k)) { v = ov; k = ok; }
+            }
+            if (lane == 0) { zmax[ee] = v; arg[ee] = k; }
+        }
+        __syncwarp();
+    }
+}
+
 __global__ void f_bn2_kernel(long long P, float eps, const float *__restrict__ gamma_beta, const double *__restrict__ dbl,
                              float *__restrict__ flt, float *__restrict__ batch_stats) {
     const int c = threadIdx.x;
@@ -364,18 +409,36 @@ __global__ void f_bn2_kernel(long long P, float eps, const float *__restrict__ g
     if (batch_stats) { batch_stats[2 * kC1 + c] = (float)mean; batch_stats[2 * kC1 + kC2 + c] = (float)var; }
 }
 
-// out = relu(scale2 * zext + shift2); zmax <- zext (the sign folded by f_layer2_kernel is undone here)
+// out = relu(scale2 * zext + shift2); zmax <- zext (the sign folded by the layer-2 pass is undone here).
+// After the tensor-core pass (x0 != nullptr) an entry whose BatchNorm output is within rounding of zero gets its z2
+// re-evaluated in exact fp32 (f_layer2_kernel's arithmetic), so the ReLU decision is the CUDA-core path's.
+template <int C0>
 __global__ void __launch_bounds__(kThreads)
 f_pool_kernel(long long n, const float *__restrict__ flt, const float *__restrict__ gamma2, float *__restrict__ zmax,
-              float *__restrict__ out, int ld_out) {
+              float *__restrict__ out, int ld_out, const float *__restrict__ x0, const int *__restrict__ arg,
+              const float *__restrict__ Wt1, const float *__restrict__ Wt2) {
     const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
     if (e >= n) return;
     const int c = (int)(e & (kC2 - 1));
     const long long m = e >> 7;
     const float a = __ldg(flt + fSc2 + c), b = __ldg(flt + fSh2 + c);
-    const float z = __ldg(gamma2 + c) < 0.f ? -zmax[e] : zmax[e];
+    float z = __ldg(gamma2 + c) < 0.f ? -zmax[e] : zmax[e];
+    float y = __fmaf_rn(z, a, b);
+    if (x0 && fabsf(y) <= 1e-5f * (fabsf(z * a) + fabsf(b))) {
+        const float *x = x0 + (m * kK + __ldg(arg + e)) * C0;
+        float z2 = 0.f;
+        for (int j = 0; j < kC1; j++) {
+            float z1 = 0.f;
+#pragma unroll
+            for (int i = 0; i < C0; i++) z1 = __fmaf_rn(__ldg(x + i), __ldg(Wt1 + i * kC1 + j), z1);
+            const float h = fmaxf(__fmaf_rn(z1, __ldg(flt + fSc1 + j), __ldg(flt + fSh1 + j)), 0.f);
+            z2 = __fmaf_rn(h, __ldg(Wt2 + j * kC2 + c), z2);
+        }
+        z = z2;
+        y = __fmaf_rn(z, a, b);
+    }
     zmax[e] = z;
-    out[m * ld_out + c] = fmaxf(__fmaf_rn(z, a, b), 0.f);
+    out[m * ld_out + c] = fmaxf(y, 0.f);
 }
 
 // ---- backward --------------------------------------------------------------------------------------------------
@@ -842,7 +905,8 @@ int forward_t(int B, int M, const float *xyz, const float *new_xyz, const float 
                                                   empty_mask, x0, dbl);
     f_bn1_kernel<C0><<<1, kC1, 0, st>>>(P, eps, weights, gamma_beta, dbl, flt, batch_stats);
     const char *mode = getenv("MGAR_SA_TRAIN_KERNELS");
-    if (!(mode && strcmp(mode, "tc") == 0)) {
+    const bool tc = mode && strcmp(mode, "tc") == 0;
+    if (!tc) {
         MGAR_CUDA(cudaFuncSetAttribute(f_layer2_kernel<C0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemF1));
         f_layer2_kernel<C0><<<grid_tiles(M), kThreads, kSmemF1, st>>>(P, M, x0, flt, weights, weights + C0 * kC1, gamma_beta + 2 * kC1, zmax, arg, dbl);
         count_launch();
@@ -874,9 +938,14 @@ int forward_t(int B, int M, const float *xyz, const float *new_xyz, const float 
         A.tr_zext = zmax; A.tr_arg = arg; A.tr_sum = dbl + dSum2; A.tr_sq = dbl + dSq2;
         const int n_tiles = (M + 3) / 4;
         if (int rc = sa_mlp_tc16_launch_train(L1, A, C0, n_tiles < kNumSMs ? n_tiles : kNumSMs, st)) return rc;
+        int gf = div_up((long long)M * kC2, kThreads * 4);
+        if (gf > kNumSMs * 8) gf = kNumSMs * 8;
+        f_fix_ties_kernel<C0><<<gf, kThreads, 0, st>>>((long long)M * kC2, x0, flt, weights, weights + C0 * kC1, gamma_beta + 2 * kC1, zmax, arg);
+        count_launch();
     }
     f_bn2_kernel<<<1, kC2, 0, st>>>(P, eps, gamma_beta, dbl, flt, batch_stats);
-    f_pool_kernel<<<div_up((long long)M * kC2, kThreads), kThreads, 0, st>>>((long long)M * kC2, flt, gamma_beta + 2 * kC1, zmax, out, ld_out);
+    f_pool_kernel<C0><<<div_up((long long)M * kC2, kThreads), kThreads, 0, st>>>((long long)M * kC2, flt, gamma_beta + 2 * kC1, zmax, out, ld_out,
+                                                                                   tc ? x0 : nullptr, arg, weights, weights + C0 * kC1);
     count_launch(4);
     return check_launch("sa_mlp_fwd_train (fast)");
 }

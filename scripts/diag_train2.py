@@ -6,7 +6,7 @@ from multimodal_gar_b200.pcdet.ops.pointnet2.pointnet2_stack import pointnet2_mo
 torch.backends.cudnn.allow_tf32 = False
 torch.backends.cuda.matmul.allow_tf32 = False
 dev = torch.device("cuda:0")
-for seed in (3, 4):
+for seed in (3, 4, 5, 6, 7, 8, 9, 10):
     torch.manual_seed(seed)
     Bp, S = 6, 512
     xyz = (torch.rand(Bp * S, 3, device=dev) - 0.5) * torch.tensor([0.8, 0.8, 1.8], device=dev)
@@ -19,7 +19,7 @@ for seed in (3, 4):
                 m.weight.normal_(0.3, 1.0); m.bias.normal_(0, 0.3)
     w_out = torch.randn((Bp * S, 128), device=dev)
     res = {}
-    for name in ("fast", "simt", "generic", "torch"):
+    for name in ("tc", "fast", "generic", "torch"):
         os.environ["MGAR_SA_TRAIN"] = "torch" if name == "torch" else "native"
         os.environ["MGAR_SA_TRAIN_KERNELS"] = name
         mod = copy.deepcopy(native).train()
@@ -28,7 +28,7 @@ for seed in (3, 4):
         (out * w_out).sum().backward()
         res[name] = (out.detach(), f.grad.clone(), [p.grad.clone() for p in mod.parameters()])
     ro, rg, rp = res["torch"]
-    for name in ("fast", "simt", "generic"):
+    for name in ("tc", "fast", "generic"):
         o, g, ps = res[name]
         d = (g - rg).abs().flatten(); sc = float(rg.abs().max())
         print("seed", seed, name, "out %.2e" % (float((o - ro).abs().max()) / float(ro.abs().max())),

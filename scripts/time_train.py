@@ -44,9 +44,9 @@ def main():
         out.square().sum().backward()
         mod.zero_grad(set_to_none=True)
 
-    for name in os.environ.get("MODES", "native,native_generic,torch").split(","):
+    for name in os.environ.get("MODES", "native,native_tc,native_generic,torch").split(","):
         os.environ["MGAR_SA_TRAIN"] = "torch" if name == "torch" else "native"
-        os.environ["MGAR_SA_TRAIN_KERNELS"] = "generic" if name == "native_generic" else "fast"
+        os.environ["MGAR_SA_TRAIN_KERNELS"] = {"native_generic": "generic", "native_tc": "tc"}.get(name, "fast")
         if name == "native_generic" and F_ > 16:
             continue
         torch.cuda.reset_peak_memory_stats()
