@@ -78,17 +78,6 @@ stack_prefix_kernel(const int *__restrict__ cnt_a, const int *__restrict__ cnt_b
     }
 }
 
-// largest b in [0,B) with pre[b] <= v  (pre is a non-decreasing exclusive prefix, pre[B] = total).
-// Matches the reference's batch search for every v < total (empty batches are skipped).
-__device__ __forceinline__ int find_batch(const int *__restrict__ pre, int B, int v) {
-    int lo = 0, hi = B;  // invariant: pre[lo] <= v < pre[hi]
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (__ldg(pre + mid) <= v) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-
 // One THREAD per centroid, one CTA per tile of 128 centroids of one cloud.  The cloud is staged in
 // shared memory as float4 in 1024-point chunks; every lane of a warp reads the SAME point (one
 // broadcast LDS.128 serves 32 distance tests), hits are appended in index order to the thread's own

@@ -29,4 +29,15 @@ struct PrefixWs {
     ~PrefixWs() { if (base) cudaFreeAsync(base, st); }
 };
 
+// largest b in [0,B) with pre[b] <= v  (pre is a non-decreasing exclusive prefix, pre[B] = total).
+// Matches the reference's batch search for every v < total (empty batches are skipped).
+__device__ __forceinline__ int find_batch(const int *__restrict__ pre, int B, int v) {
+    int lo = 0, hi = B;  // invariant: pre[lo] <= v < pre[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(pre + mid) <= v) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
 }  // namespace mgar
