@@ -196,6 +196,20 @@ MGAR_API int mgar_three_interpolate(int b, int c, int m, int n, const float *poi
 MGAR_API int mgar_three_interpolate_grad(int b, int c, int n, int m, const float *grad_out, const int *idx,
                                          const float *weight, float *grad_points, void *stream);
 
+/* Stack (ragged) layout of the same three ops.  three_nn_wrapper (pointnet2_stack/src/interpolate.cpp:32-60, kernel
+ * interpolate_gpu.cu:16-74): unknown (N,3) / unknown_batch_cnt (B), known (M,3) / known_batch_cnt (B) -> dist2 (N,3)
+ * SQUARED distances ascending, idx (N,3) GLOBAL known rows (cloud start added, :70-72); ties keep the lowest index;
+ * a cloud with fewer than three known points leaves (+inf, cloud start).  three_interpolate_wrapper
+ * (interpolate.cpp:63-83, kernel :107-126): features (M,C), idx / weight (N,3) -> out (N,C), every element written.
+ * three_interpolate_grad_wrapper (interpolate.cpp:86-107, kernel :150-170): grad_out (N,C) accumulated with atomics
+ * into zero-filled grad_features (M,C). */
+MGAR_API int mgar_three_nn_stack(int B, int N, int M, const float *unknown, const int *unknown_batch_cnt,
+                                 const float *known, const int *known_batch_cnt, float *dist2, int *idx, void *stream);
+MGAR_API int mgar_three_interpolate_stack(int N, int C, const float *features, const int *idx, const float *weight,
+                                          float *out, void *stream);
+MGAR_API int mgar_three_interpolate_grad_stack(int N, int C, const float *grad_out, const int *idx, const float *weight,
+                                               float *grad_features, void *stream);
+
 /* ---- set-abstraction shared MLP (QueryAndGroup + [Conv1x1,BN,ReLU] x L + pool, fused) ------------ */
 
 /* StackSAModuleMSG.forward for ONE scale, eval-mode BatchNorm: pointnet2_stack/pointnet2_modules.py:78-112

@@ -40,6 +40,9 @@ SIGNATURES = {
     "mgar_three_nn": [_i, _i, _i, _p, _p, _p, _p, _p],
     "mgar_three_interpolate": [_i, _i, _i, _i, _p, _p, _p, _p, _p],
     "mgar_three_interpolate_grad": [_i, _i, _i, _i, _p, _p, _p, _p, _p],
+    "mgar_three_nn_stack": [_i, _i, _i, _p, _p, _p, _p, _p, _p, _p],
+    "mgar_three_interpolate_stack": [_i, _i, _p, _p, _p, _p, _p],
+    "mgar_three_interpolate_grad_stack": [_i, _i, _p, _p, _p, _p, _p],
     "mgar_fps_ball_query_supported": [_i, _i, _i, _i],
     "mgar_fps_ball_query": [_i, _i, _i, _p, _i, _f, _i, _p, _p, _p, _p],
     "mgar_group_points_stack": [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p],

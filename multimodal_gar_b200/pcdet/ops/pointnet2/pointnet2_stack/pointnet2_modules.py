@@ -123,3 +123,35 @@ class StackSAModuleMSG(nn.Module):
                 raise NotImplementedError
             new_features_list.append(new_features.squeeze(dim=0).permute(1, 0))  # (M, C)
         return new_xyz, torch.cat(new_features_list, dim=1)
+
+
+class StackPointnetFPModule(nn.Module):
+    """reference :115-157 (same constructor, sub-module names `mlp.{0,1,2,...}` and forward signature): feature
+    propagation on ragged batches - three nearest known points (libmgar_lidar three_nn), inverse-distance weights,
+    interpolation (libmgar_lidar, autograd through ThreeInterpolate), shared 1x1 MLP (library convolutions)."""
+
+    def __init__(self, *, mlp: List[int]):
+        super().__init__()
+        shared_mlps = []
+        for k in range(len(mlp) - 1):
+            shared_mlps.extend([
+                nn.Conv2d(mlp[k], mlp[k + 1], kernel_size=1, bias=False),
+                nn.BatchNorm2d(mlp[k + 1]),
+                nn.ReLU()
+            ])
+        self.mlp = nn.Sequential(*shared_mlps)
+
+    def forward(self, unknown, unknown_batch_cnt, known, known_batch_cnt, unknown_feats=None, known_feats=None):
+        """unknown (N1+N2..,3), known (M1+M2..,3), unknown_feats (N,C1) or None, known_feats (M,C2) -> (N, C_out)."""
+        dist, idx = pointnet2_utils.three_nn(unknown, unknown_batch_cnt, known, known_batch_cnt)
+        dist_recip = 1.0 / (dist + 1e-8)
+        norm = torch.sum(dist_recip, dim=-1, keepdim=True)
+        weight = dist_recip / norm
+        interpolated_feats = pointnet2_utils.three_interpolate(known_feats, idx, weight)
+        if unknown_feats is not None:
+            new_features = torch.cat([interpolated_feats, unknown_feats], dim=1)   # (N, C2 + C1)
+        else:
+            new_features = interpolated_feats
+        new_features = new_features.permute(1, 0)[None, :, :, None]                # (1, C, N, 1)
+        new_features = self.mlp(new_features)
+        return new_features.squeeze(dim=0).squeeze(dim=-1).permute(1, 0)           # (N, C_out)

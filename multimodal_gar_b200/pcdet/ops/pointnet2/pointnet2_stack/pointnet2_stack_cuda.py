@@ -1,7 +1,8 @@
 """Stand-in for the reference's `pointnet2_stack_cuda` pybind module
 (/root/reference/pcdet/ops/pointnet2/pointnet2_stack/src/pointnet2_api.cpp:12-31): the five
-hot-path wrappers and voxel_query_wrapper run on libmgar_lidar.so; the other seven names exist (so imports
-succeed) and raise NotImplementedError - they belong to PV-RCNN++ paths outside this build.
+hot-path wrappers, voxel_query_wrapper and the three feature-propagation wrappers (three_nn / three_interpolate /
+three_interpolate_grad) run on libmgar_lidar.so; the four vector-pool names exist (so imports succeed) and raise
+NotImplementedError - they belong to PV-RCNN++ paths outside this build.
 """
 import torch
 
@@ -95,9 +96,41 @@ def voxel_query_wrapper(M, R1, R2, R3, nsample, radius, z_range, y_range, x_rang
     return 1
 
 
-three_nn_wrapper = _outside("three_nn_wrapper")
-three_interpolate_wrapper = _outside("three_interpolate_wrapper")
-three_interpolate_grad_wrapper = _outside("three_interpolate_grad_wrapper")
+def three_nn_wrapper(unknown, unknown_batch_cnt, known, known_batch_cnt, dist2, idx):
+    """interpolate.cpp:32-60.  unknown (N,3), known (M,3) f32; *_batch_cnt (B) i32; dist2 (N,3) f32 (squared) and
+    idx (N,3) i32 (global known rows) are filled in place."""
+    need_cuda(unknown=unknown, unknown_batch_cnt=unknown_batch_cnt, known=known, known_batch_cnt=known_batch_cnt,
+              dist2=dist2, idx=idx)
+    need_dtype(torch.float32, unknown=unknown, known=known, dist2=dist2)
+    need_dtype(torch.int32, unknown_batch_cnt=unknown_batch_cnt, known_batch_cnt=known_batch_cnt, idx=idx)
+    with on_device(unknown):
+        _lib.check(_lib.lib().mgar_three_nn_stack(unknown_batch_cnt.numel(), unknown.shape[0], known.shape[0], ptr(unknown),
+                                                  ptr(unknown_batch_cnt), ptr(known), ptr(known_batch_cnt), ptr(dist2),
+                                                  ptr(idx), stream_of(unknown)), "three_nn_wrapper")
+
+
+def three_interpolate_wrapper(features, idx, weight, out):
+    """interpolate.cpp:63-83.  features (M,C) f32, idx (N,3) i32, weight (N,3) f32 -> out (N,C) f32."""
+    need_cuda(features=features, idx=idx, weight=weight, out=out)
+    need_dtype(torch.float32, features=features, weight=weight, out=out)
+    need_dtype(torch.int32, idx=idx)
+    with on_device(features):
+        _lib.check(_lib.lib().mgar_three_interpolate_stack(idx.shape[0], features.shape[1], ptr(features), ptr(idx),
+                                                           ptr(weight), ptr(out), stream_of(features)),
+                   "three_interpolate_wrapper")
+
+
+def three_interpolate_grad_wrapper(grad_out, idx, weight, grad_features):
+    """interpolate.cpp:86-107.  grad_out (N,C) f32 scattered into zero-filled grad_features (M,C)."""
+    need_cuda(grad_out=grad_out, idx=idx, weight=weight, grad_features=grad_features)
+    need_dtype(torch.float32, grad_out=grad_out, weight=weight, grad_features=grad_features)
+    need_dtype(torch.int32, idx=idx)
+    with on_device(grad_out):
+        _lib.check(_lib.lib().mgar_three_interpolate_grad_stack(grad_out.shape[0], grad_out.shape[1], ptr(grad_out),
+                                                                ptr(idx), ptr(weight), ptr(grad_features),
+                                                                stream_of(grad_out)), "three_interpolate_grad_wrapper")
+
+
 query_stacked_local_neighbor_idxs_wrapper_stack = _outside("query_stacked_local_neighbor_idxs_wrapper_stack")
 query_three_nn_by_stacked_local_idxs_wrapper_stack = _outside("query_three_nn_by_stacked_local_idxs_wrapper_stack")
 vector_pool_wrapper = _outside("vector_pool_wrapper")

@@ -484,6 +484,50 @@ void orc_three_nn(int b, int n, int m, const float *unknown, const float *known,
         }
 }
 
+/* three_nn_kernel_stack, pointnet2_stack/src/interpolate_gpu.cu:16-74: ragged batches; the serial walk of one
+ * cloud's known points with double bests (1e40) and strict '<'; indices leave as GLOBAL known rows (:70-72). */
+void orc_three_nn_stack(int batch, const float *unknown, const int *unknown_cnt, const float *known, const int *known_cnt,
+                        float *dist2, int *idx)
+{
+    size_t u0 = 0;
+    int k0 = 0;
+    for (int bs = 0; bs < batch; bs++) {
+        const float *kn = known + (size_t)k0 * 3;
+        const int m = known_cnt[bs];
+        for (int pt = 0; pt < unknown_cnt[bs]; pt++) {
+            const float *u = unknown + (u0 + pt) * 3;
+            double best1 = 1e40, best2 = 1e40, best3 = 1e40;
+            int i1 = 0, i2 = 0, i3 = 0;
+            for (int k = 0; k < m; k++) {
+                float ex = u[0] - kn[k * 3], ey = u[1] - kn[k * 3 + 1], ez = u[2] - kn[k * 3 + 2];
+                float d = fmaf(ez, ez, fmaf(ex, ex, ey * ey));
+                if (d < best1) { best3 = best2; i3 = i2; best2 = best1; i2 = i1; best1 = d; i1 = k; }
+                else if (d < best2) { best3 = best2; i3 = i2; best2 = d; i2 = k; }
+                else if (d < best3) { best3 = d; i3 = k; }
+            }
+            float *o = dist2 + (u0 + pt) * 3;
+            int *oi = idx + (u0 + pt) * 3;
+            o[0] = (float)best1; o[1] = (float)best2; o[2] = (float)best3;
+            oi[0] = i1 + k0; oi[1] = i2 + k0; oi[2] = i3 + k0;
+        }
+        u0 += unknown_cnt[bs];
+        k0 += m;
+    }
+}
+
+/* three_interpolate_kernel_stack, pointnet2_stack/src/interpolate_gpu.cu:107-126: features (M,C) row-major ->
+ * out (N,C); same contraction as the batch kernel (SASS of the reference build: FMUL w1*f1, FFMA w0*f0, FFMA w2*f2). */
+void orc_three_interpolate_stack(int n, int c, const float *features, const int *idx, const float *weight, float *out)
+{
+    for (int pt = 0; pt < n; pt++) {
+        const int *i = idx + (size_t)pt * 3;
+        const float *w = weight + (size_t)pt * 3;
+        for (int ch = 0; ch < c; ch++)
+            out[(size_t)pt * c + ch] = fmaf(w[2], features[(size_t)i[2] * c + ch],
+                                            fmaf(w[0], features[(size_t)i[0] * c + ch], w[1] * features[(size_t)i[1] * c + ch]));
+    }
+}
+
 /* three_interpolate_kernel_fast, interpolate_gpu.cu:82-101; SASS (FMUL, FFMA, FFMA): fma(w2,p2, fma(w0,p0, w1*p1)). */
 void orc_three_interpolate(int b, int c, int m, int n, const float *points, const int *idx, const float *weight,
                            float *out)

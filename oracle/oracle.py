@@ -388,6 +388,35 @@ def three_interpolate_grad(grad_out, idx, weight, M):
     return g
 
 
+def stack_three_nn(unknown, unknown_batch_cnt, known, known_batch_cnt):
+    """ThreeNN.forward, pointnet2_stack/pointnet2_utils.py:228-258 -> dist (N,3) (sqrt of the kernel's output),
+    idx (N,3) global known rows, and the kernel's squared distances."""
+    unknown, known = _f32(unknown), _f32(known)
+    ucnt, kcnt = _i32(unknown_batch_cnt), _i32(known_batch_cnt)
+    assert ucnt.sum() == unknown.shape[0] and kcnt.sum() == known.shape[0] and len(ucnt) == len(kcnt)
+    dist2 = np.zeros(unknown.shape, dtype=np.float32)
+    idx = np.zeros(unknown.shape, dtype=np.int32)
+    lib().orc_three_nn_stack(len(ucnt), _fp(unknown), _ip(ucnt), _fp(known), _ip(kcnt), _fp(dist2), _ip(idx))
+    return np.sqrt(dist2), idx, dist2
+
+
+def stack_three_interpolate(features, idx, weight):
+    """ThreeInterpolate.forward, pointnet2_stack/pointnet2_utils.py:264-284: (M,C), (N,3) x2 -> (N,C)."""
+    features, idx, weight = _f32(features), _i32(idx), _f32(weight)
+    out = np.zeros((idx.shape[0], features.shape[1]), dtype=np.float32)
+    lib().orc_three_interpolate_stack(idx.shape[0], features.shape[1], _fp(features), _ip(idx), _fp(weight), _fp(out))
+    return out
+
+
+def stack_three_interpolate_grad(grad_out, idx, weight, M):
+    """ThreeInterpolate.backward (:286-300): grad_out (N,C) * weight scattered into (M,C)."""
+    grad_out, idx, weight = _f32(grad_out), _i32(idx), _f32(weight)
+    g = np.zeros((M, grad_out.shape[1]), dtype=np.float32)
+    for j in range(3):
+        np.add.at(g, idx[:, j], grad_out * weight[:, j:j + 1])
+    return g
+
+
 def load_ref(name):
     """Import oracle/_ref/<name>.so (a torch pybind module built from /root/reference sources)."""
     import torch  # noqa: F401  (the extension links libtorch)

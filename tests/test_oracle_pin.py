@@ -206,3 +206,23 @@ def test_oracle_equals_reference_gpu_batch_ops():
     np.testing.assert_array_equal(idx, g["nn_idx"])
     np.testing.assert_array_equal(d2, g["d2"])
     np.testing.assert_array_equal(O.three_interpolate(feats, idx, weight), g["interp"])
+
+
+def test_oracle_equals_reference_gpu_stack_interp():
+    """stack three_nn / three_interpolate: outputs of the unmodified reference kernels on a B200
+    (tests/golden/make_ref_stack_interp_golden.py) against the C restatement, bit-exact."""
+    path = os.path.join(GOLD, "ref_stack_interp.npz")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/ref_stack_interp.npz not generated yet (needs one GPU run)")
+    g = np.load(path)
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_ref_stack_interp_golden",
+                                                  os.path.join(GOLD, "make_ref_stack_interp_golden.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    unknown, ucnt, known, kcnt, feats, weight = gen.inputs()
+    _, idx, d2 = O.stack_three_nn(unknown, ucnt, known, kcnt)
+    np.testing.assert_array_equal(idx, g["nn_idx"])
+    np.testing.assert_array_equal(d2, g["d2"])
+    assert np.isinf(d2).any() and (idx[ucnt[0] + ucnt[1]:ucnt[0] + ucnt[1] + ucnt[2], 2] == kcnt[0] + kcnt[1]).all()
+    np.testing.assert_array_equal(O.stack_three_interpolate(feats, np.clip(idx, 0, known.shape[0] - 1), weight), g["interp"])
