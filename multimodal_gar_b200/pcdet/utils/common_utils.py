@@ -37,3 +37,12 @@ def generate_voxel2pinds(sparse_tensor):
     indices = sparse_tensor.indices.long()
     rows = torch.arange(indices.shape[0], device=indices.device, dtype=torch.int32)
     return scatter_point_inds(indices, rows, [sparse_tensor.batch_size] + list(sparse_tensor.spatial_shape))
+
+
+def get_voxel_centers(voxel_coords, downsample_times, voxel_size, point_cloud_range):
+    """pcdet/utils/common_utils.py:66-82: voxel_coords (N,3) [z,y,x] -> centres (N,3) [x,y,z] in metres."""
+    assert voxel_coords.shape[1] == 3
+    centers = voxel_coords[:, [2, 1, 0]].float()
+    size = torch.tensor(voxel_size, device=centers.device).float() * downsample_times
+    origin = torch.tensor(point_cloud_range[0:3], device=centers.device).float()
+    return (centers + 0.5) * size + origin

@@ -62,3 +62,60 @@ def voxel_scene(seed=5, B=2, grid=(6, 24, 24), voxels=1500, queries_per_frame=90
                 new_xyz_batch_cnt=np.full(B, M, dtype=np.int32), new_coords=new_coords,
                 new_coords_xyz=np.ascontiguousarray(new_coords[:, [0, 3, 2, 1]]),
                 features=rng.standard_normal((V, C)).astype(np.float32))
+
+
+class AttrDict(dict):
+    """dict with attribute access (what the reference gets from EasyDict for its yaml configs)."""
+    __getattr__ = dict.__getitem__
+
+    @staticmethod
+    def of(obj):
+        if isinstance(obj, dict):
+            return AttrDict({k: AttrDict.of(v) for k, v in obj.items()})
+        return [AttrDict.of(v) for v in obj] if isinstance(obj, list) else obj
+
+
+def voxelrcnn_head_cfg(channels=16, grid_size=4):
+    """ROI_HEAD block of Multimodal_cfg/mil3.yaml:105-135 at test size (same structure, smaller widths)."""
+    layers = {name: dict(MLPS=[[channels, channels]], QUERY_RANGES=[[4, 4, 4]], POOL_RADIUS=[r], NSAMPLE=[16],
+                         POOL_METHOD="max_pool")
+              for name, r in (("x_conv2", 0.4), ("x_conv3", 0.8), ("x_conv4", 1.6))}
+    return AttrDict.of(dict(NAME="VoxelRCNNHead", CLASS_AGNOSTIC=True, SHARED_FC=[64, 32], DP_RATIO=0.3,
+                            ROI_GRID_POOL=dict(FEATURES_SOURCE=["x_conv2", "x_conv3", "x_conv4"], PRE_MLP=True,
+                                               GRID_SIZE=grid_size, POOL_LAYERS=layers)))
+
+
+def voxelrcnn_scene(seed=11, B=2, rois=4, grid=(16, 96, 96), voxel_size=(0.1, 0.1, 0.2), channels=(8, 12, 16)):
+    """Inputs of VoxelRCNNHead.roi_grid_pool: person boxes (one reaching outside the point-cloud range, one far from
+    every voxel) and three scales (strides 2, 4, 8) of occupied voxels with features, clustered around the boxes."""
+    rng = np.random.default_rng(seed)
+    Z, Y, X = grid
+    vs = np.asarray(voxel_size, dtype=np.float32)
+    pc_range = [0.0, 0.0, 0.0, float(X * vs[0]), float(Y * vs[1]), float(Z * vs[2])]
+    boxes = np.zeros((B, rois, 8), dtype=np.float32)
+    boxes[..., 0] = rng.uniform(1.5, 8.0, (B, rois))
+    boxes[..., 1] = rng.uniform(1.5, 8.0, (B, rois))
+    boxes[..., 2] = rng.uniform(1.0, 2.0, (B, rois))
+    boxes[..., 3:5] = rng.uniform(0.4, 0.9, (B, rois, 2))
+    boxes[..., 5] = rng.uniform(1.4, 1.95, (B, rois))
+    boxes[..., 6] = rng.uniform(-np.pi, np.pi, (B, rois))
+    boxes[..., 7] = 1.0                                                   # class column: rois are (…, 7 + C)
+    boxes[0, 0, :2] = (0.1, 0.2)                                          # grid points with negative voxel coordinates
+    boxes[1, 1, :2] = (9.3, 9.4)                                          # nothing nearby
+    out = dict(gt_boxes=boxes, pc_range=np.asarray(pc_range, np.float32), voxel_size=vs)
+    for name, stride, C in zip(("x_conv2", "x_conv3", "x_conv4"), (2, 4, 8), channels):
+        shape = (Z // stride, Y // stride, X // stride)
+        coords = []
+        for b in range(B):
+            ctr = boxes[b, rng.integers(0, rois, 4000 // stride), :3] + rng.normal(0, 0.5, (4000 // stride, 3))
+            c = np.floor(ctr / (vs * stride)).astype(np.int64)[:, ::-1]    # -> (z, y, x)
+            c = c[((c >= 0) & (c < np.asarray(shape))).all(axis=1)]
+            c = np.unique(c, axis=0)
+            c = c[rng.permutation(len(c))]
+            coords.append(np.concatenate([np.full((len(c), 1), b), c], axis=1))
+        coords = np.concatenate(coords).astype(np.int32)
+        out[name + ".indices"] = coords
+        out[name + ".features"] = rng.standard_normal((len(coords), C)).astype(np.float32)
+        out[name + ".spatial_shape"] = np.asarray(shape, np.int32)
+        out[name + ".stride"] = np.asarray(stride, np.int32)
+    return out
