@@ -210,6 +210,24 @@ MGAR_API int mgar_three_interpolate_stack(int N, int C, const float *features, c
 MGAR_API int mgar_three_interpolate_grad_stack(int N, int C, const float *grad_out, const int *idx, const float *weight,
                                                float *grad_features, void *stream);
 
+/* ---- Distance Aware Fusion Module: everything between the library GEMMs ------------------------- */
+
+/* FusionAttention_mat.forward, model/gat_model.py:485-489 (RGB stream) and :501-505 (LiDAR stream), for B frames of n
+ * persons and n_streams (1 or 2) streams in one launch:
+ *   out[s] (B,n,D) = LayerNorm(softmax_keys((q[s] k[s]^T) * E / sqrt(D)) v[s] + resid[s]) * gamma[s] + beta[s].
+ * q/k/v[s]: (B*n) rows of D floats with row stride ld (they may be column blocks of one projection GEMM output);
+ * resid[s], out[s] (B,n,D) dense; E (B,n,n) = softmax(-De/sigma) (:484); valid (B,n) bytes, 0 = padded person whose
+ * key is removed from the softmax (NULL: all valid); the pointer arrays are HOST arrays of n_streams DEVICE pointers.
+ * n <= 128, D <= 512. */
+MGAR_API int mgar_dafm_attention(int B, int n, int D, int n_streams, int ld, const float *const *q, const float *const *k,
+                                 const float *const *v, const float *const *resid, const float *E,
+                                 const unsigned char *valid, const float *const *gamma, const float *const *beta,
+                                 float eps, float *const *out, void *stream);
+/* out (rows,D) = LayerNorm(x + y) * gamma + beta (:490-491 / :506-507 after the FFN GEMMs); rows whose valid byte is 0
+ * are written as zeros (the reference never computes them: it slices each frame to its person count, :1396-1405). */
+MGAR_API int mgar_dafm_add_layernorm(int rows, int D, const float *x, const float *y, const float *gamma, const float *beta,
+                                     const unsigned char *valid, float eps, float *out, void *stream);
+
 /* ---- set-abstraction shared MLP (QueryAndGroup + [Conv1x1,BN,ReLU] x L + pool, fused) ------------ */
 
 /* StackSAModuleMSG.forward for ONE scale, eval-mode BatchNorm: pointnet2_stack/pointnet2_modules.py:78-112

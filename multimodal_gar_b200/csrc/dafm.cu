@@ -1,0 +1,243 @@
+// Distance Aware Fusion Module, attention core: one CTA per (frame, stream).
+//
+// Reference: FusionAttention_mat.forward, model/gat_model.py:466-511, applied to one frame at a time inside a Python
+// loop (:1396-1475).  Per stream it runs, as separate library kernels on (n,512) / (n,n) tensors with n <= 100 persons:
+//   Att = softmax((Q K^T) * E / sqrt(D), dim=1) ; X = LayerNorm(Att V + residual)          (:485-489 / :501-505)
+// followed by X = LayerNorm(X + FFN(X)) (:490-491 / :506-507).  The (B*n,512)x(512,512) projections and FFN linears are
+// plain library GEMMs; what is fused here is everything between them:
+//   dafm_attention_kernel : scores (fp32 FFMA, 8x8 register tiles over 32-wide D chunks staged in shared memory),
+//                           * E * scale, key mask, row softmax, Att V + residual, LayerNorm - the n x n map never
+//                           leaves shared memory and the pre-LayerNorm rows are re-read by the CTA that wrote them;
+//   dafm_add_ln_kernel    : LayerNorm(x + y) with padded persons zeroed (warp per row, the row in registers).
+// Both streams of a module (RGB <- LiDAR queries, LiDAR <- RGB queries) go in ONE launch (grid.y = stream).
+#include "mgar_common.cuh"
+
+namespace mgar {
+
+constexpr int kDaThreads = 256;
+constexpr int kDaChunk = 32;         // D columns per shared-memory stage
+constexpr int kDaMaxN = 128;         // persons per frame (the reference pads to 100)
+constexpr int kDaMaxStreams = 2;
+
+struct DafmStreams {
+    const float *q[kDaMaxStreams], *k[kDaMaxStreams], *v[kDaMaxStreams], *resid[kDaMaxStreams];
+    const float *gamma[kDaMaxStreams], *beta[kDaMaxStreams];
+    float *out[kDaMaxStreams];
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// LayerNorm of one row held as kPer values per lane (element c = lane + 32 * t): biased variance, eps inside the
+// square root, as torch.nn.LayerNorm.
+template <int kPer>
+__device__ __forceinline__ void ln_row(float (&x)[kPer], int D, float eps, const float *__restrict__ gamma,
+                                       const float *__restrict__ beta, float *__restrict__ dst, int lane) {
+    float s = 0.f;
+#pragma unroll
+    for (int t = 0; t < kPer; ++t) s += (lane + 32 * t < D) ? x[t] : 0.f;
+    const float mean = warp_sum(s) / (float)D;
+    float q = 0.f;
+#pragma unroll
+    for (int t = 0; t < kPer; ++t) {
+        const float d = x[t] - mean;
+        q += (lane + 32 * t < D) ? d * d : 0.f;
+    }
+    const float rstd = 1.0f / sqrtf(warp_sum(q) / (float)D + eps);
+#pragma unroll
+    for (int t = 0; t < kPer; ++t) {
+        const int c = lane + 32 * t;
+        if (c < D) dst[c] = (x[t] - mean) * rstd * __ldg(gamma + c) + __ldg(beta + c);
+    }
+}
+
+constexpr int kLnPer = 16;           // D <= 512
+
+__global__ void __launch_bounds__(kDaThreads)
+dafm_attention_kernel(int n, int D, int ld, DafmStreams P, const float *__restrict__ E, const uint8_t *__restrict__ valid,
+                      float scale, float eps) {
+    extern __shared__ float smem_da[];
+    const int b = blockIdx.x, s = blockIdx.y, tid = threadIdx.x;
+    const int np = n + 1;                                        // padded row of the n x n map
+    float *S = smem_da;                                          // [n][n+1]
+    float *Qs = S + (size_t)n * np;                              // [kDaMaxN][33]  (rows >= n are zero)
+    float *Ks = Qs + kDaMaxN * (kDaChunk + 1);                   // [kDaMaxN][33]; later V stage [n][32]
+    const float *q = P.q[s] + (size_t)b * n * ld, *k = P.k[s] + (size_t)b * n * ld, *v = P.v[s] + (size_t)b * n * ld;
+    const float *resid = P.resid[s] + (size_t)b * n * D;
+    float *out = P.out[s] + (size_t)b * n * D;
+
+    // ---- scores: thread (ty, tx) owns rows ty + 16 a, columns tx + 16 c
+    const int tx = tid & 15, ty = tid >> 4;
+    float acc[8][8];
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[a][c] = 0.f;
+    for (int d0 = 0; d0 < D; d0 += kDaChunk) {
+        __syncthreads();
+        for (int e = tid; e < kDaMaxN * kDaChunk; e += kDaThreads) {
+            const int r = e >> 5, c = e & 31;
+            const bool ok = r < n && d0 + c < D;
+            Qs[r * (kDaChunk + 1) + c] = ok ? __ldg(q + (size_t)r * ld + d0 + c) : 0.f;
+            Ks[r * (kDaChunk + 1) + c] = ok ? __ldg(k + (size_t)r * ld + d0 + c) : 0.f;
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int kk = 0; kk < kDaChunk; ++kk) {
+            float qa[8], kc[8];
+#pragma unroll
+            for (int a = 0; a < 8; ++a) qa[a] = Qs[(ty + 16 * a) * (kDaChunk + 1) + kk];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) kc[c] = Ks[(tx + 16 * c) * (kDaChunk + 1) + kk];
+#pragma unroll
+            for (int a = 0; a < 8; ++a)
+#pragma unroll
+                for (int c = 0; c < 8; ++c) acc[a][c] = fmaf(qa[a], kc[c], acc[a][c]);
+        }
+    }
+    const float *Eb = E + (size_t)b * n * n;
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const int i = ty + 16 * a, j = tx + 16 * c;
+            if (i < n && j < n) S[i * np + j] = acc[a][c] * __ldg(Eb + (size_t)i * n + j) / scale;   // (QK^T * E) / sqrt(D), :485
+        }
+    __syncthreads();
+
+    // ---- row softmax over the valid keys (warp per row)
+    const int lane = tid & 31, warp = tid >> 5;
+    const uint8_t *vb = valid ? valid + (size_t)b * n : nullptr;
+    for (int i = warp; i < n; i += kDaThreads / 32) {
+        float x[kDaMaxN / 32];
+        float m = -INFINITY;
+#pragma unroll
+        for (int t = 0; t < kDaMaxN / 32; ++t) {
+            const int j = lane + 32 * t;
+            x[t] = (j < n && (!vb || vb[j])) ? S[i * np + j] : -INFINITY;
+            m = fmaxf(m, x[t]);
+        }
+        m = warp_max(m);
+        float sum = 0.f;
+#pragma unroll
+        for (int t = 0; t < kDaMaxN / 32; ++t) {
+            x[t] = expf(x[t] - m);
+            sum += x[t];
+        }
+        sum = warp_sum(sum);
+#pragma unroll
+        for (int t = 0; t < kDaMaxN / 32; ++t) {
+            const int j = lane + 32 * t;
+            if (j < n) S[i * np + j] = x[t] / sum;
+        }
+    }
+
+    // ---- Att V + residual, 32 columns at a time: thread (r0 = tid / 32, col = lane) owns rows r0 + 8 t
+    float *Vs = Ks;
+    for (int d0 = 0; d0 < D; d0 += kDaChunk) {
+        __syncthreads();
+        for (int e = tid; e < n * kDaChunk; e += kDaThreads) {
+            const int r = e >> 5, c = e & 31;
+            Vs[e] = d0 + c < D ? __ldg(v + (size_t)r * ld + d0 + c) : 0.f;
+        }
+        __syncthreads();
+        float o[kDaMaxN / 8];
+#pragma unroll
+        for (int t = 0; t < kDaMaxN / 8; ++t) o[t] = 0.f;
+        for (int j = 0; j < n; ++j) {
+            const float vj = Vs[j * kDaChunk + lane];
+#pragma unroll
+            for (int t = 0; t < kDaMaxN / 8; ++t) {
+                const int i = warp + 8 * t;
+                if (i < n) o[t] = fmaf(S[i * np + j], vj, o[t]);
+            }
+        }
+        if (d0 + lane < D) {
+#pragma unroll
+            for (int t = 0; t < kDaMaxN / 8; ++t) {
+                const int i = warp + 8 * t;
+                if (i < n) out[(size_t)i * D + d0 + lane] = o[t] + __ldg(resid + (size_t)i * D + d0 + lane);
+            }
+        }
+    }
+    __syncthreads();                                             // the CTA's own global writes are visible to it
+
+    // ---- LayerNorm in place (warp per row)
+    for (int i = warp; i < n; i += kDaThreads / 32) {
+        float x[kLnPer];
+#pragma unroll
+        for (int t = 0; t < kLnPer; ++t) x[t] = (lane + 32 * t < D) ? out[(size_t)i * D + lane + 32 * t] : 0.f;
+        ln_row<kLnPer>(x, D, eps, P.gamma[s], P.beta[s], out + (size_t)i * D, lane);
+    }
+}
+
+// out = LayerNorm(x + y) row-wise; rows whose valid byte is 0 are written as zeros.
+__global__ void __launch_bounds__(256)
+dafm_add_ln_kernel(int rows, int D, const float *__restrict__ x, const float *__restrict__ y, const float *__restrict__ gamma,
+                   const float *__restrict__ beta, const uint8_t *__restrict__ valid, float eps, float *__restrict__ out) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    float v[kLnPer];
+    if (valid && !valid[row]) {
+        for (int c = lane; c < D; c += 32) out[(size_t)row * D + c] = 0.f;
+        return;
+    }
+#pragma unroll
+    for (int t = 0; t < kLnPer; ++t) {
+        const int c = lane + 32 * t;
+        v[t] = c < D ? __ldg(x + (size_t)row * D + c) + __ldg(y + (size_t)row * D + c) : 0.f;
+    }
+    ln_row<kLnPer>(v, D, eps, gamma, beta, out + (size_t)row * D, lane);
+}
+
+}  // namespace mgar
+
+using namespace mgar;
+
+extern "C" int mgar_dafm_attention(int B, int n, int D, int n_streams, int ld, const float *const *q, const float *const *k,
+                                   const float *const *v, const float *const *resid, const float *E,
+                                   const unsigned char *valid, const float *const *gamma, const float *const *beta,
+                                   float eps, float *const *out, void *stream) {
+    MGAR_REQUIRE(B >= 0 && n >= 1 && n <= kDaMaxN, "dafm_attention: n=%d persons per frame outside [1, %d]", n, kDaMaxN);
+    MGAR_REQUIRE(D >= 1 && D <= 32 * kLnPer && ld >= D, "dafm_attention: D=%d (ld=%d) outside [1, %d]", D, ld, 32 * kLnPer);
+    MGAR_REQUIRE(n_streams >= 1 && n_streams <= kDaMaxStreams, "dafm_attention: n_streams must be 1 or 2");
+    MGAR_REQUIRE(B <= 0x7fffffff / (n * n), "dafm_attention: batch too large");
+    if (B == 0) return MGAR_OK;
+    MGAR_REQUIRE(q && k && v && resid && E && gamma && beta && out, "dafm_attention: null pointer");
+    DafmStreams P;
+    for (int s = 0; s < kDaMaxStreams; ++s) {
+        const int t = s < n_streams ? s : 0;
+        MGAR_REQUIRE(q[t] && k[t] && v[t] && resid[t] && gamma[t] && beta[t] && out[t], "dafm_attention: null pointer (stream %d)", t);
+        P.q[s] = q[t]; P.k[s] = k[t]; P.v[s] = v[t]; P.resid[s] = resid[t];
+        P.gamma[s] = gamma[t]; P.beta[s] = beta[t]; P.out[s] = out[t];
+    }
+    const size_t smem = ((size_t)n * (n + 1) + 2 * (size_t)kDaMaxN * (kDaChunk + 1)) * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+        MGAR_CUDA(cudaFuncSetAttribute(dafm_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)(((size_t)kDaMaxN * (kDaMaxN + 1) + 2 * (size_t)kDaMaxN * (kDaChunk + 1)) * sizeof(float))));
+        attr_set = true;
+    }
+    dafm_attention_kernel<<<dim3(B, n_streams), kDaThreads, smem, (cudaStream_t)stream>>>(n, D, ld, P, E, valid,
+                                                                                           sqrtf((float)D), eps);
+    count_launch();
+    return check_launch("dafm_attention");
+}
+
+extern "C" int mgar_dafm_add_layernorm(int rows, int D, const float *x, const float *y, const float *gamma, const float *beta,
+                                       const unsigned char *valid, float eps, float *out, void *stream) {
+    MGAR_REQUIRE(rows >= 0 && D >= 1 && D <= 32 * kLnPer, "dafm_add_layernorm: D=%d outside [1, %d]", D, 32 * kLnPer);
+    if (rows == 0) return MGAR_OK;
+    MGAR_REQUIRE(x && y && gamma && beta && out, "dafm_add_layernorm: null pointer");
+    dafm_add_ln_kernel<<<div_up(rows, 8), 256, 0, (cudaStream_t)stream>>>(rows, D, x, y, gamma, beta, valid, eps, out);
+    count_launch();
+    return check_launch("dafm_add_layernorm");
+}

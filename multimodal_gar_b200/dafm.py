@@ -8,9 +8,16 @@ Here every frame of the batch goes through at once: the six 512x512 projections 
 module are single `(B*n, 512) x (512, 512)` library GEMMs, the n x n attention pieces are batched, and frames with
 fewer persons than the padded width are handled by masking keys with -inf before each softmax, so that
 `out[b, :n_b]` is what the reference loop computes for frame b (tests/test_dafm.py pins this against the
-reference class itself).  Note two reference quirks that are kept: both streams use E_r = softmax(-De/sigma)
+reference class itself).  On CUDA tensors without autograd everything between the GEMMs runs in libmgar_lidar.so
+(csrc/dafm.cu): the projections become two (B*n, 512) x (512, 1536) GEMMs (the three weights sharing a left operand
+side by side), one launch per module does scores * E / sqrt(D), key mask, softmax, Att V + residual and LayerNorm for
+both streams (the n x n map stays in shared memory), and LayerNorm(x + FFN(x)) with the padded rows zeroed is one more
+kernel per stream.  The torch composition below stays for CPU tensors (the CPU golden test) and for autograd.  Note two reference quirks that are kept: both streams use E_r = softmax(-De/sigma)
 (Dg is accepted but unused, `E_l = Dg` is dead code :499), and softmax runs over keys (dim=1 of the (n, n) map).
 """
+import ctypes
+import os
+
 import torch
 import torch.nn as nn
 
@@ -66,12 +73,59 @@ class FusionAttentionMat(nn.Module):
         x = x + getattr(self, "FFN_" + s)(x)
         return getattr(self, "LN_%s_2" % s)(x)
 
+    def _fused_ok(self, R, L):
+        if not (R.is_cuda and L.is_cuda and R.dtype == L.dtype == torch.float32):
+            return False
+        if os.environ.get("MGAR_DAFM", "fused") == "torch" or self.input_dim != self.out_dim:
+            return False
+        if torch.is_grad_enabled() and (R.requires_grad or L.requires_grad or self.WQ_r.requires_grad):
+            return False
+        return R.shape[1] <= 128 and self.out_dim <= 512
+
+    def _fused(self, R, L, E, valid):
+        """Both streams through libmgar_lidar.so: 2 projection GEMMs, mgar_dafm_attention, FFN GEMMs,
+        mgar_dafm_add_layernorm per stream."""
+        from . import _lib
+        from ._torch_glue import on_device, ptr, stream_of
+        B, n, D = R.shape
+        R, L, E = R.contiguous(), L.contiguous(), E.contiguous()
+        PL = L.view(B * n, D) @ torch.cat([self.WQ_r, self.WK_l, self.WV_l], dim=1)     # Q_r | K_l | V_l
+        PR = R.view(B * n, D) @ torch.cat([self.WK_r, self.WV_r, self.WQ_l], dim=1)     # K_r | V_r | Q_l
+        X = torch.empty((2, B, n, D), dtype=torch.float32, device=R.device)
+        vmask = None if valid is None else valid.contiguous()
+        pl, pr, f4 = PL.data_ptr(), PR.data_ptr(), 4 * D
+
+        def arr(a, b):
+            return (ctypes.c_void_p * 2)(a, b)
+
+        L_ = _lib.lib()
+        with on_device(R):
+            st = stream_of(R)
+            _lib.check(L_.mgar_dafm_attention(B, n, D, 2, 3 * D, arr(pl, pr + 2 * f4), arr(pr, pl + f4), arr(pr + f4, pl + 2 * f4),
+                                              arr(ptr(R), ptr(L)), ptr(E), ptr(vmask),
+                                              arr(ptr(self.LN_r_1.weight), ptr(self.LN_l_1.weight)),
+                                              arr(ptr(self.LN_r_1.bias), ptr(self.LN_l_1.bias)), float(self.LN_r_1.eps),
+                                              arr(X[0].data_ptr(), X[1].data_ptr()), st), "dafm_attention")
+            outs = []
+            for i, s in enumerate(("r", "l")):
+                x = X[i].view(B * n, D)
+                y = getattr(self, "FFN_" + s)(x)
+                ln = getattr(self, "LN_%s_2" % s)
+                o = torch.empty_like(x)
+                _lib.check(L_.mgar_dafm_add_layernorm(B * n, D, ptr(x), ptr(y), ptr(ln.weight), ptr(ln.bias), ptr(vmask),
+                                                      float(ln.eps), ptr(o), st), "dafm_add_layernorm")
+                outs.append(o.view(B, n, D))
+        return outs
+
     def forward(self, R, L, Dg, De, valid=None):
         squeeze = R.dim() == 2
         if squeeze:
             R, L, De = R.unsqueeze(0), L.unsqueeze(0), De.unsqueeze(0)
             valid = None if valid is None else valid.unsqueeze(0)
         E = _masked_softmax(-(De / self.sigma), valid)
+        if self._fused_ok(R, L):
+            Rp, Lp = self._fused(R, L, E, valid)
+            return (Rp[0], Lp[0]) if squeeze else (Rp, Lp)
         Rp = self._stream(L, R, E, valid, "r")          # queries from LiDAR, keys / values from RGB (:480-482)
         Lp = self._stream(R, L, E, valid, "l")          # queries from RGB, keys / values from LiDAR (:495-497)
         if valid is not None:
