@@ -5,7 +5,8 @@
 //   Att = softmax((Q K^T) * E / sqrt(D), dim=1) ; X = LayerNorm(Att V + residual)          (:485-489 / :501-505)
 // followed by X = LayerNorm(X + FFN(X)) (:490-491 / :506-507).  The (B*n,512)x(512,512) projections and FFN linears are
 // plain library GEMMs; what is fused here is everything between them:
-//   dafm_attention_kernel : scores (fp32 FFMA, 8x8 register tiles over 32-wide D chunks staged in shared memory),
+//   dafm_attention_kernel : CTA per (frame, stream, block of 64 query rows), 2-3 CTAs per SM; scores (fp32 FFMA, 4x8
+//                           register tiles, operands staged in shared memory in 32-wide D chunks and read as LDS.128),
 //                           * E * scale, key mask, row softmax, Att V + residual, LayerNorm - the n x n map never
 //                           leaves shared memory and the pre-LayerNorm rows are re-read by the CTA that wrote them;
 //   dafm_add_ln_kernel    : LayerNorm(x + y) with padded persons zeroed (warp per row, the row in registers).
@@ -18,6 +19,8 @@ constexpr int kDaThreads = 256;
 constexpr int kDaChunk = 32;         // D columns per shared-memory stage
 constexpr int kDaMaxN = 128;         // persons per frame (the reference pads to 100)
 constexpr int kDaMaxStreams = 2;
+constexpr int kDaLd = kDaChunk + 4;  // operand row stride: 16-byte aligned rows, conflict-free 128-bit loads per quarter warp
+__host__ __device__ constexpr int da_row(int n) { return ((n + 3) & ~3) + 4; }
 
 struct DafmStreams {
     const float *q[kDaMaxStreams], *k[kDaMaxStreams], *v[kDaMaxStreams], *resid[kDaMaxStreams];
@@ -61,62 +64,95 @@ __device__ __forceinline__ void ln_row(float (&x)[kPer], int D, float eps, const
 
 constexpr int kLnPer = 16;           // D <= 512
 
-__global__ void __launch_bounds__(kDaThreads)
+constexpr int kDaRows = 64;          // query rows per CTA: grid.z = ceil(n / 64) row blocks
+constexpr int kDaVChunk = 64;        // D columns per V stage (two per lane)
+constexpr size_t da_smem_floats(int n) {
+    return (size_t)kDaRows * da_row(n) + (size_t)kDaRows * kDaLd + (size_t)kDaMaxN * kDaVChunk;
+}
+
+__global__ void __launch_bounds__(kDaThreads, 2)
 dafm_attention_kernel(int n, int D, int ld, DafmStreams P, const float *__restrict__ E, const uint8_t *__restrict__ valid,
                       float scale, float eps) {
     extern __shared__ float smem_da[];
     const int b = blockIdx.x, s = blockIdx.y, tid = threadIdx.x;
-    const int np = n + 1;                                        // padded row of the n x n map
-    float *S = smem_da;                                          // [n][n+1]
-    float *Qs = S + (size_t)n * np;                              // [kDaMaxN][33]  (rows >= n are zero)
-    float *Ks = Qs + kDaMaxN * (kDaChunk + 1);                   // [kDaMaxN][33]; later V stage [n][32]
-    const float *q = P.q[s] + (size_t)b * n * ld, *k = P.k[s] + (size_t)b * n * ld, *v = P.v[s] + (size_t)b * n * ld;
-    const float *resid = P.resid[s] + (size_t)b * n * D;
-    float *out = P.out[s] + (size_t)b * n * D;
+    const int r0 = blockIdx.z * kDaRows, rows = min(kDaRows, n - r0);   // this CTA's query rows
+    const int np = da_row(n);                                    // row stride of the rows x n map (multiple of 4 floats)
+    float *S = smem_da;                                          // [64][np], columns n..n4 are zero after the softmax
+    float *Qs = S + (size_t)kDaRows * np;                        // [64][36]   (rows >= rows are zero)
+    float *Ks = Qs + kDaRows * kDaLd;                            // [128][36]  (rows >= n are zero); later the V stage [n4][64]
+    const float *q = P.q[s] + ((size_t)b * n + r0) * ld, *k = P.k[s] + (size_t)b * n * ld, *v = P.v[s] + (size_t)b * n * ld;
+    const float *resid = P.resid[s] + ((size_t)b * n + r0) * D;
+    float *out = P.out[s] + ((size_t)b * n + r0) * D;
 
-    // ---- scores: thread (ty, tx) owns rows ty + 16 a, columns tx + 16 c
+    // ---- scores: thread (ty, tx) owns rows ty + 16 a (a < 4), columns tx + 16 c (c < 8)
     const int tx = tid & 15, ty = tid >> 4;
-    float acc[8][8];
+    float acc[4][8];
 #pragma unroll
-    for (int a = 0; a < 8; ++a)
+    for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int c = 0; c < 8; ++c) acc[a][c] = 0.f;
+    // operand staging: 128-bit loads, all of a chunk's loads in flight together, and the NEXT chunk's loads issued
+    // before the current chunk's FFMAs (registers kq / kk4) so their latency hides behind the arithmetic
+    float4 kq[4], qq[2];
+    auto load_qk = [&](int d0) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int e = tid + u * kDaThreads, r = e >> 3, c = (e & 7) * 4;
+            kq[u] = (r < n && d0 + c < D) ? __ldg(reinterpret_cast<const float4 *>(k + (size_t)r * ld + d0 + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int e = tid + u * kDaThreads, r = e >> 3, c = (e & 7) * 4;
+            qq[u] = (r < rows && d0 + c < D) ? __ldg(reinterpret_cast<const float4 *>(q + (size_t)r * ld + d0 + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    };
+    load_qk(0);
     for (int d0 = 0; d0 < D; d0 += kDaChunk) {
         __syncthreads();
-        for (int e = tid; e < kDaMaxN * kDaChunk; e += kDaThreads) {
-            const int r = e >> 5, c = e & 31;
-            const bool ok = r < n && d0 + c < D;
-            Qs[r * (kDaChunk + 1) + c] = ok ? __ldg(q + (size_t)r * ld + d0 + c) : 0.f;
-            Ks[r * (kDaChunk + 1) + c] = ok ? __ldg(k + (size_t)r * ld + d0 + c) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int e = tid + u * kDaThreads;
+            *reinterpret_cast<float4 *>(Ks + (e >> 3) * kDaLd + (e & 7) * 4) = kq[u];
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int e = tid + u * kDaThreads;
+            *reinterpret_cast<float4 *>(Qs + (e >> 3) * kDaLd + (e & 7) * 4) = qq[u];
         }
         __syncthreads();
-#pragma unroll 4
-        for (int kk = 0; kk < kDaChunk; ++kk) {
-            float qa[8], kc[8];
+        if (d0 + kDaChunk < D) load_qk(d0 + kDaChunk);
+#pragma unroll 2
+        for (int kk = 0; kk < kDaChunk; kk += 4) {
+            float4 qa[4], kc[8];
 #pragma unroll
-            for (int a = 0; a < 8; ++a) qa[a] = Qs[(ty + 16 * a) * (kDaChunk + 1) + kk];
+            for (int a = 0; a < 4; ++a) qa[a] = *reinterpret_cast<const float4 *>(Qs + (ty + 16 * a) * kDaLd + kk);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) kc[c] = Ks[(tx + 16 * c) * (kDaChunk + 1) + kk];
+            for (int c = 0; c < 8; ++c) kc[c] = *reinterpret_cast<const float4 *>(Ks + (tx + 16 * c) * kDaLd + kk);
 #pragma unroll
-            for (int a = 0; a < 8; ++a)
+            for (int a = 0; a < 4; ++a)
 #pragma unroll
-                for (int c = 0; c < 8; ++c) acc[a][c] = fmaf(qa[a], kc[c], acc[a][c]);
+                for (int c = 0; c < 8; ++c) {
+                    acc[a][c] = fmaf(qa[a].x, kc[c].x, acc[a][c]);
+                    acc[a][c] = fmaf(qa[a].y, kc[c].y, acc[a][c]);
+                    acc[a][c] = fmaf(qa[a].z, kc[c].z, acc[a][c]);
+                    acc[a][c] = fmaf(qa[a].w, kc[c].w, acc[a][c]);
+                }
         }
     }
-    const float *Eb = E + (size_t)b * n * n;
+    const float *Eb = E + ((size_t)b * n + r0) * n;
 #pragma unroll
-    for (int a = 0; a < 8; ++a)
+    for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
             const int i = ty + 16 * a, j = tx + 16 * c;
-            if (i < n && j < n) S[i * np + j] = acc[a][c] * __ldg(Eb + (size_t)i * n + j) / scale;   // (QK^T * E) / sqrt(D), :485
+            if (i < rows && j < n) S[i * np + j] = acc[a][c] * __ldg(Eb + (size_t)i * n + j) / scale;   // (QK^T * E) / sqrt(D), :485
         }
     __syncthreads();
 
     // ---- row softmax over the valid keys (warp per row)
     const int lane = tid & 31, warp = tid >> 5;
     const uint8_t *vb = valid ? valid + (size_t)b * n : nullptr;
-    for (int i = warp; i < n; i += kDaThreads / 32) {
+    for (int i = warp; i < rows; i += kDaThreads / 32) {
         float x[kDaMaxN / 32];
         float m = -INFINITY;
 #pragma unroll
@@ -136,42 +172,64 @@ dafm_attention_kernel(int n, int D, int ld, DafmStreams P, const float *__restri
 #pragma unroll
         for (int t = 0; t < kDaMaxN / 32; ++t) {
             const int j = lane + 32 * t;
-            if (j < n) S[i * np + j] = x[t] / sum;
+            if (j < np) S[i * np + j] = j < n ? x[t] / sum : 0.f;      // pad columns are zero: the AV loop reads whole float4s
         }
     }
 
-    // ---- Att V + residual, 32 columns at a time: thread (r0 = tid / 32, col = lane) owns rows r0 + 8 t
+    // ---- Att V + residual, 64 columns at a time: warp w owns rows w + 8 t (t < 8), lane l columns l and l + 32
     float *Vs = Ks;
-    for (int d0 = 0; d0 < D; d0 += kDaChunk) {
+    const int n4 = (n + 3) & ~3;
+    float4 vq[8];
+    auto load_v = [&](int d0) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int e = tid + u * kDaThreads, r = e >> 4, c = (e & 15) * 4;
+            vq[u] = (r < n && d0 + c < D) ? __ldg(reinterpret_cast<const float4 *>(v + (size_t)r * ld + d0 + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    };
+    load_v(0);
+    for (int d0 = 0; d0 < D; d0 += kDaVChunk) {
         __syncthreads();
-        for (int e = tid; e < n * kDaChunk; e += kDaThreads) {
-            const int r = e >> 5, c = e & 31;
-            Vs[e] = d0 + c < D ? __ldg(v + (size_t)r * ld + d0 + c) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int e = tid + u * kDaThreads;
+            if ((e >> 4) < n4) *reinterpret_cast<float4 *>(Vs + (e >> 4) * kDaVChunk + (e & 15) * 4) = vq[u];
         }
         __syncthreads();
-        float o[kDaMaxN / 8];
+        if (d0 + kDaVChunk < D) load_v(d0 + kDaVChunk);
+        float o[kDaRows / 8][2];
 #pragma unroll
-        for (int t = 0; t < kDaMaxN / 8; ++t) o[t] = 0.f;
-        for (int j = 0; j < n; ++j) {
-            const float vj = Vs[j * kDaChunk + lane];
+        for (int t = 0; t < kDaRows / 8; ++t) o[t][0] = o[t][1] = 0.f;
+        for (int j = 0; j < n4; j += 4) {
+            float va[4], vb2[4];
 #pragma unroll
-            for (int t = 0; t < kDaMaxN / 8; ++t) {
-                const int i = warp + 8 * t;
-                if (i < n) o[t] = fmaf(S[i * np + j], vj, o[t]);
+            for (int u = 0; u < 4; ++u) {
+                va[u] = Vs[(j + u) * kDaVChunk + lane];
+                vb2[u] = Vs[(j + u) * kDaVChunk + 32 + lane];
+            }
+#pragma unroll
+            for (int t = 0; t < kDaRows / 8; ++t) {
+                const float4 a = *reinterpret_cast<const float4 *>(S + (warp + 8 * t) * np + j);   // one broadcast LDS.128 per warp
+                o[t][0] = fmaf(a.x, va[0], o[t][0]); o[t][1] = fmaf(a.x, vb2[0], o[t][1]);
+                o[t][0] = fmaf(a.y, va[1], o[t][0]); o[t][1] = fmaf(a.y, vb2[1], o[t][1]);
+                o[t][0] = fmaf(a.z, va[2], o[t][0]); o[t][1] = fmaf(a.z, vb2[2], o[t][1]);
+                o[t][0] = fmaf(a.w, va[3], o[t][0]); o[t][1] = fmaf(a.w, vb2[3], o[t][1]);
             }
         }
-        if (d0 + lane < D) {
 #pragma unroll
-            for (int t = 0; t < kDaMaxN / 8; ++t) {
-                const int i = warp + 8 * t;
-                if (i < n) out[(size_t)i * D + d0 + lane] = o[t] + __ldg(resid + (size_t)i * D + d0 + lane);
+        for (int t = 0; t < kDaRows / 8; ++t) {
+            const int i = warp + 8 * t;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int c = d0 + 32 * h + lane;
+                if (i < rows && c < D) out[(size_t)i * D + c] = o[t][h] + __ldg(resid + (size_t)i * D + c);
             }
         }
     }
     __syncthreads();                                             // the CTA's own global writes are visible to it
 
     // ---- LayerNorm in place (warp per row)
-    for (int i = warp; i < n; i += kDaThreads / 32) {
+    for (int i = warp; i < rows; i += kDaThreads / 32) {
         float x[kLnPer];
 #pragma unroll
         for (int t = 0; t < kLnPer; ++t) x[t] = (lane + 32 * t < D) ? out[(size_t)i * D + lane + 32 * t] : 0.f;
@@ -209,6 +267,7 @@ extern "C" int mgar_dafm_attention(int B, int n, int D, int n_streams, int ld, c
     MGAR_REQUIRE(B >= 0 && n >= 1 && n <= kDaMaxN, "dafm_attention: n=%d persons per frame outside [1, %d]", n, kDaMaxN);
     MGAR_REQUIRE(D >= 1 && D <= 32 * kLnPer && ld >= D, "dafm_attention: D=%d (ld=%d) outside [1, %d]", D, ld, 32 * kLnPer);
     MGAR_REQUIRE(n_streams >= 1 && n_streams <= kDaMaxStreams, "dafm_attention: n_streams must be 1 or 2");
+    MGAR_REQUIRE(D % 4 == 0 && ld % 4 == 0, "dafm_attention: D=%d and ld=%d must be multiples of 4 (128-bit operand loads)", D, ld);
     MGAR_REQUIRE(B <= 0x7fffffff / (n * n), "dafm_attention: batch too large");
     if (B == 0) return MGAR_OK;
     MGAR_REQUIRE(q && k && v && resid && E && gamma && beta && out, "dafm_attention: null pointer");
@@ -216,17 +275,19 @@ extern "C" int mgar_dafm_attention(int B, int n, int D, int n_streams, int ld, c
     for (int s = 0; s < kDaMaxStreams; ++s) {
         const int t = s < n_streams ? s : 0;
         MGAR_REQUIRE(q[t] && k[t] && v[t] && resid[t] && gamma[t] && beta[t] && out[t], "dafm_attention: null pointer (stream %d)", t);
+        MGAR_REQUIRE(((reinterpret_cast<uintptr_t>(q[t]) | reinterpret_cast<uintptr_t>(k[t]) | reinterpret_cast<uintptr_t>(v[t])) & 15) == 0,
+                     "dafm_attention: q / k / v must be 16-byte aligned (stream %d)", t);
         P.q[s] = q[t]; P.k[s] = k[t]; P.v[s] = v[t]; P.resid[s] = resid[t];
         P.gamma[s] = gamma[t]; P.beta[s] = beta[t]; P.out[s] = out[t];
     }
-    const size_t smem = ((size_t)n * (n + 1) + 2 * (size_t)kDaMaxN * (kDaChunk + 1)) * sizeof(float);
+    const size_t smem = da_smem_floats(n) * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
         MGAR_CUDA(cudaFuncSetAttribute(dafm_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)(((size_t)kDaMaxN * (kDaMaxN + 1) + 2 * (size_t)kDaMaxN * (kDaChunk + 1)) * sizeof(float))));
+                                       (int)(da_smem_floats(kDaMaxN) * sizeof(float))));
         attr_set = true;
     }
-    dafm_attention_kernel<<<dim3(B, n_streams), kDaThreads, smem, (cudaStream_t)stream>>>(n, D, ld, P, E, valid,
+    dafm_attention_kernel<<<dim3(B, n_streams, div_up(n, kDaRows)), kDaThreads, smem, (cudaStream_t)stream>>>(n, D, ld, P, E, valid,
                                                                                            sqrtf((float)D), eps);
     count_launch();
     return check_launch("dafm_attention");
