@@ -140,12 +140,20 @@ dafm_attention_kernel(int n, int D, int ld, DafmStreams P, const float *__restri
         }
     }
     const float *Eb = E + ((size_t)b * n + r0) * n;
+    float ev[4][8];                                              // all 32 loads in flight before the first use
 #pragma unroll
     for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
             const int i = ty + 16 * a, j = tx + 16 * c;
-            if (i < rows && j < n) S[i * np + j] = acc[a][c] * __ldg(Eb + (size_t)i * n + j) / scale;   // (QK^T * E) / sqrt(D), :485
+            ev[a][c] = (i < rows && j < n) ? __ldg(Eb + (size_t)i * n + j) : 0.f;
+        }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const int i = ty + 16 * a, j = tx + 16 * c;
+            if (i < rows && j < n) S[i * np + j] = acc[a][c] * ev[a][c] / scale;   // (QK^T * E) / sqrt(D), :485
         }
     __syncthreads();
 
@@ -197,9 +205,14 @@ dafm_attention_kernel(int n, int D, int ld, DafmStreams P, const float *__restri
         }
         __syncthreads();
         if (d0 + kDaVChunk < D) load_v(d0 + kDaVChunk);
-        float o[kDaRows / 8][2];
+        float o[kDaRows / 8][2];                                 // starts from the residual: its loads overlap the FFMAs
 #pragma unroll
-        for (int t = 0; t < kDaRows / 8; ++t) o[t][0] = o[t][1] = 0.f;
+        for (int t = 0; t < kDaRows / 8; ++t)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int i = warp + 8 * t, c = d0 + 32 * h + lane;
+                o[t][h] = (i < rows && c < D) ? __ldg(resid + (size_t)i * D + c) : 0.f;
+            }
         for (int j = 0; j < n4; j += 4) {
             float va[4], vb2[4];
 #pragma unroll
@@ -222,7 +235,7 @@ dafm_attention_kernel(int n, int D, int ld, DafmStreams P, const float *__restri
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int c = d0 + 32 * h + lane;
-                if (i < rows && c < D) out[(size_t)i * D + c] = o[t][h] + __ldg(resid + (size_t)i * D + c);
+                if (i < rows && c < D) out[(size_t)i * D + c] = o[t][h];
             }
         }
     }
