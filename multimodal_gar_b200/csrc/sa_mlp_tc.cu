@@ -21,6 +21,8 @@
 //   warps 5-12  producers (two groups of four, one smem stage each): gather (xyz - centre | feat),
 //               layer 1, hi/lo split, 128B-swizzled K-major store of the B tile
 // mbarriers: full/empty per smem stage, tfull/tempty per TMEM accumulator stage (4 x 128 columns).
+#include <mutex>
+#include <vector>
 #include <stdlib.h>
 
 #include <type_traits>
@@ -399,6 +401,33 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
 
 using namespace mgar;
 
+// Scratch for the live-person list, kept per (device, stream): consecutive calls on a stream are ordered, so they can
+// share one buffer; a stream-ordered allocation per call would hand its memory back to the driver at every
+// synchronisation (default pool threshold) and pay a fresh allocation each step.  Never freed (a few KB per stream).
+static int *live_scratch(cudaStream_t st, size_t n_ints) {
+    struct Slot { int dev; cudaStream_t st; int *p; size_t cap; };
+    static std::mutex mu;
+    static std::vector<Slot> slots;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    for (Slot &s : slots)
+        if (s.dev == dev && s.st == st) {
+            if (s.cap < n_ints) {                      // grow: the old buffer may still be in use by queued work on `st`
+                int *q = nullptr;
+                if (cudaMalloc((void **)&q, 2 * n_ints * sizeof(int)) != cudaSuccess) return nullptr;
+                cudaStreamSynchronize(st);
+                cudaFree(s.p);
+                s.p = q; s.cap = 2 * n_ints;
+            }
+            return s.p;
+        }
+    int *q = nullptr;
+    if (cudaMalloc((void **)&q, 2 * n_ints * sizeof(int)) != cudaSuccess) return nullptr;
+    slots.push_back({dev, st, q, 2 * n_ints});
+    return q;
+}
+
 extern "C" int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg) {
     return nsample == kTcNS && C_in >= 0 && C_in <= 4 && n_layers == 2 && channels_host && channels_host[0] == 3 + C_in &&
            channels_host[1] == kTcC1 && channels_host[2] == kTcC2 && !pool_avg;
@@ -445,6 +474,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     A.out = out; A.ld_out = ld_out;
     A.gmax = group_max; A.group_size = group_size > 0 ? group_size : 1; A.group_zero = group_zero;
     A.tr_zext = nullptr; A.tr_arg = nullptr; A.tr_sum = nullptr; A.tr_sq = nullptr;
+    A.live_groups = nullptr; A.n_live = nullptr;
     A.packed4 = (C0 == 4 && xyz_stride == 4 && feat_stride == 4 && features == xyz + 3 &&
                  (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) ? 1 : 0;
 #ifdef MGAR_TC_TRACE
@@ -462,7 +492,23 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
 #ifndef MGAR_TC_TRACE
     {   // default: the fp16-split kernel (same accuracy, half the tensor cycles); MGAR_TC_MODE=tf32 keeps 3xTF32
         const char *mode = getenv("MGAR_TC_MODE");
-        if (!(mode && mode[0] == 't')) return sa_mlp_tc16_launch(L1, A, C0, grid, st);
+        if (!(mode && mode[0] == 't')) {
+            // Persons flagged empty only produce a zero row: when the per-centroid features are not stored, walk the
+            // live persons only (a list compacted on the device - no host round trip)
+            // Asked for with ld_out == -1 (see the header); MGAR_TC_SKIP_EMPTY=0/1 overrides for A/B runs.  Off by default:
+            // with no empty person the compacted walk measured 8 % slower (1.40 vs 1.29 ms per 64 configs[1] frames).
+            const char *skip = getenv("MGAR_TC_SKIP_EMPTY");
+            const bool want = skip ? skip[0] == '1' : ld_out == -1;
+            int *live = nullptr;
+            if (want && C0 == 4 && !out && group_max && group_zero && uniform && uniform_m == group_size && group_size % 4 == 0) {
+                const int G = M / group_size;
+                live = live_scratch(st, (size_t)G + 1);
+                MGAR_REQUIRE(live, "sa_mlp_tc: scratch for %d persons could not be allocated", G);
+                if (int rc = tc_compact_live_groups(group_zero, G, live + 1, live, st)) return rc;
+                A.live_groups = live + 1; A.n_live = live;
+            }
+            return sa_mlp_tc16_launch(L1, A, C0, grid, st);
+        }
     }
 #endif
 #ifdef MGAR_TC_TRACE

@@ -35,10 +35,18 @@ struct TcArgs {
     // ReLU in the epilogue; per (centroid, channel) the extreme of sign * z2 over the samples and the first sample
     // attaining it, per channel sum z2 and sum z2^2 (fp64 atomics)
     float *tr_zext; int *tr_arg; double *tr_sum, *tr_sq;
+    // empty-person skip (sa_mlp_tc16 only; null = off): live_groups[0 .. *n_live) = indices of the groups (persons)
+    // whose group_zero flag is 0, ascending.  The kernel then walks only n_live * group_size centroids ("virtual"
+    // centroid v -> real centroid live_groups[v / group_size] * group_size + v % group_size).  Needs out == null,
+    // gmax != null (zero-filled: skipped persons keep their zero row), the uniform layout with m_u == group_size,
+    // group_size % 4 == 0 (a tile of 4 centroids never straddles two persons).
+    const int *live_groups, *n_live;
 };
 
 // sa_mlp_tc16.cu: the 3xFP16 kernel (default); sa_mlp_tc.cu keeps the 3xTF32 kernel (MGAR_TC_MODE=tf32)
 int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);
+// live[0 .. *n_live) = ascending indices g < G with group_zero[g] == 0 (one small launch)
+int tc_compact_live_groups(const int *group_zero, int G, int *live, int *n_live, cudaStream_t st);
 int sa_mlp_tc16_launch_train(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);   // C0 = 4, 5
 
 }  // namespace mgar

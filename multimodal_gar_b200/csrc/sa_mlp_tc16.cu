@@ -144,7 +144,7 @@ __device__ __forceinline__ void sts_pack2_w(uint32_t a0, uint32_t a1, uint32_t b
     sts4(b0, lo[0], lo[1], lo[2], lo[3]); sts4(b1, lo[4], hi[3], hi[4], 0.f);
 }
 
-template <int C0, bool kTrain = false>
+template <int C0, bool kTrain = false, bool kCompact = false>
 __global__ void __launch_bounds__(kThreads, 1)
 sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcBound BD, const __grid_constant__ TcArgs A) {
     static_assert(C0 >= 3 && C0 <= 7, "layer-1 K is padded to 8 with one column for the folded bias");
@@ -173,7 +173,9 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
     auto DEMPTY = [&](int x) { return bar0 + 8u * (2 * kStages + 10 + x); };
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int M = A.M;
+    // M counts "virtual" centroids when the live-person list is in use (TcArgs::live_groups): only they are walked
+    constexpr bool compact = kCompact;
+    const int M = compact ? __ldg(A.n_live) * A.group_size : A.M;
     const int n_tiles = (M + 3) >> 2;
     // contiguous tile range per CTA: consecutive tiles belong to the same person, so the running
     // group max of the epilogue is flushed only a handful of times
@@ -305,8 +307,9 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         float gm = 0.f;
         float *outp = A.out ? A.out + (size_t)m_next * A.ld_out + c : nullptr;
         auto flush = [&]() {
-            if (!(A.group_zero && __ldg(A.group_zero + grp)))
-                atomicMax(reinterpret_cast<int *>(A.gmax + (size_t)grp * kTcC2 + c), __float_as_int(gm));
+            const int rg = compact ? __ldg(A.live_groups + grp) : grp;     // virtual -> real person
+            if (!(A.group_zero && __ldg(A.group_zero + rg)))
+                atomicMax(reinterpret_cast<int *>(A.gmax + (size_t)rg * kTcC2 + c), __float_as_int(gm));
         };
         for (int i = 0; i < my_tiles; i++) {
             const int t = i % kAcc, u = i / kAcc;
@@ -439,23 +442,37 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         const int r = pw * 32 + lane;
 
         int u_cloud = A.uniform ? (t_beg * 4 + pw) / A.m_u : 0, u_end = (u_cloud + 1) * A.m_u;
+        int i_cloud = u_cloud, i_end = u_end;                    // the same walk for the index loads (they run ahead)
+        // real person of the current virtual one, re-read only when the walk enters the next person (every 128 tiles)
+        int u_real = 0, i_real = 0;
+        if (compact && my_tiles > 0) u_real = i_real = __ldg(A.live_groups + u_cloud);
         auto load_idx = [&](int i, int &iv, int &em) {          // local tile i -> this lane's sample index
-            const int m = (t_beg + i) * 4 + pw;
+            int m = (t_beg + i) * 4 + pw;
             iv = -1; em = 0;
             if (i < my_tiles && m < M) {
+                if (compact) {                                   // virtual -> real centroid (m_u == group_size)
+                    while (m >= i_end) { i_cloud++; i_end += A.m_u; i_real = __ldg(A.live_groups + i_cloud); }
+                    m = i_real * A.m_u + (m - (i_end - A.m_u));
+                }
                 iv = __ldg(A.idx + (size_t)m * kTcNS + lane);
                 if (A.empty_mask) em = A.empty_mask[m];
             }
         };
         auto load_pt = [&](int i, int iv, int em, float (&v)[C0], float (&q)[3], bool &live) {
-            const int m = (t_beg + i) * 4 + pw;
+            int m = (t_beg + i) * 4 + pw;
             const int first = __shfl_sync(0xffffffffu, iv, 0);
             live = (i < my_tiles) && (m < M) && first >= 0 && !em;
             if (live) {
                 long long start;
                 if (A.uniform) {
-                    while (m >= u_end) { u_cloud++; u_end += A.m_u; }     // tiles arrive in increasing order
-                    start = (long long)u_cloud * A.n_u;
+                    if (compact) {
+                        while (m >= u_end) { u_cloud++; u_end += A.m_u; u_real = __ldg(A.live_groups + u_cloud); }
+                        m = u_real * A.m_u + (m - (u_end - A.m_u));
+                        start = (long long)u_real * A.n_u;
+                    } else {
+                        while (m >= u_end) { u_cloud++; u_end += A.m_u; }     // tiles arrive in increasing order
+                        start = (long long)u_cloud * A.n_u;
+                    }
                 } else {
                     start = __ldg(A.pre_xyz + find_batch_tc(A.pre_new, A.B, m));
                 }
@@ -581,6 +598,36 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
 
 }  // namespace
 
+// live[0 .. *n_live) = ascending g with group_zero[g] == 0: one CTA, 1024 groups per pass (ballot + warp totals)
+__global__ void __launch_bounds__(1024)
+compact_live_groups_kernel(const int *__restrict__ group_zero, int G, int *__restrict__ live, int *__restrict__ n_live) {
+    __shared__ int s_warp[32];
+    __shared__ int s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (int g0 = 0; g0 < G; g0 += 1024) {
+        const int g = g0 + tid;
+        const bool keep = g < G && __ldg(group_zero + g) == 0;
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        int before = 0;
+        for (int w = 0; w < warp; w++) before += s_warp[w];
+        if (keep) live[s_base + before + __popc(bal & ((1u << lane) - 1u))] = g;
+        __syncthreads();
+        if (tid == 1023) s_base += before + __popc(bal);
+        __syncthreads();
+    }
+    if (tid == 0) *n_live = s_base;
+}
+
+int tc_compact_live_groups(const int *group_zero, int G, int *live, int *n_live, cudaStream_t st) {
+    compact_live_groups_kernel<<<1, 1024, 0, st>>>(group_zero, G, live, n_live);
+    count_launch();
+    return check_launch("compact_live_groups");
+}
+
 int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st) {
     TcBound BD;
     BD.shmax = 0.f;
@@ -604,6 +651,12 @@ int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cu
 #else
 #define TC16_TRACE_DUMP
 #endif
+    if (A.live_groups && C0 == 4) {      // live-person walk (the LiDAR branch: xyz + intensity)
+        MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<4, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+        sa_mlp_tc16_kernel<4, false, true><<<grid, kThreads, kSmem, st>>>(L1, BD, A);
+        count_launch();
+        return check_launch("sa_mlp_tc16 (live persons)");
+    }
 #define MGAR_TC16_CASE(c0)                                                                                          \
     if (C0 == c0) {                                                                                                 \
         MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<c0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem)); \

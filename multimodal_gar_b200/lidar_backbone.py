@@ -68,8 +68,9 @@ class PointLiDARBackbone(nn.Module):
     def __init__(self, point_feature_channels=1, num_sampled_points=512, npoint=512, radius=0.3, nsample=32,
                  mlp=(64, 128), out_dim=512):
         super().__init__()
+        # proposals arrive zero-padded to MAX_NUM_PROPOSAL: the padded slots pool nothing and are skipped by the MLP
         self.encoder = lidar_branch.PointPersonEncoder(point_feature_channels, num_sampled_points, npoint, radius,
-                                                       nsample, mlp)
+                                                       nsample, mlp, skip_empty_persons=True)
         self.embedding = nn.Linear(mlp[-1], out_dim)
 
     def forward(self, data_dict):

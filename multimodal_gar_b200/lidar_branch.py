@@ -52,8 +52,11 @@ class PointPersonEncoder(nn.Module):
     """
 
     def __init__(self, point_feature_channels=1, num_sampled_points=512, npoint=512, radius=0.3, nsample=32,
-                 mlp=(64, 128), pool_extra_width=(0.0, 0.0, 0.0), fused_canonical=True):
+                 mlp=(64, 128), pool_extra_width=(0.0, 0.0, 0.0), fused_canonical=True, skip_empty_persons=False):
         super().__init__()
+        # True: the tensor-core MLP walks only the persons that pooled points (same features; pays when many person
+        # slots are empty, e.g. zero-padded proposals, costs ~8 % of the MLP when none is)
+        self.skip_empty_persons = skip_empty_persons
         self.num_sampled_points, self.npoint = num_sampled_points, npoint
         self.pool_extra_width = tuple(pool_extra_width)
         self.fused_canonical = fused_canonical
@@ -126,7 +129,8 @@ class PointPersonEncoder(nn.Module):
                                                   flat[:, 3:] if C else None, ball_idx, uniform=(S, P),
                                                   params_host=packed[2], impl='tc', group_max=person, group_size=P,
                                                   group_zero=empty.view(-1),
-                                                  want_out=return_stages or self.keep_sa_features)
+                                                  want_out=return_stages or self.keep_sa_features,
+                                                  skip_zero_groups=self.skip_empty_persons)
             mark('sa_mlp')
             person = person.view(B, M, -1)
         else:

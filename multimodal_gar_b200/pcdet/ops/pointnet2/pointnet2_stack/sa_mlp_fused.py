@@ -47,7 +47,7 @@ def tc_supported(channels, nsample, C_in, pool_avg=False):
 
 def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features, idx,
                    empty_mask=None, out=None, pool_avg=False, uniform=None, params_host=None, impl=None,
-                   group_max=None, group_size=0, group_zero=None, want_out=True):
+                   group_max=None, group_size=0, group_zero=None, want_out=True, skip_zero_groups=False):
     """-> (M, channels[-1]) fp32.  `idx` as returned by ball_query (or the raw kernel output);
     `uniform=(n, m)` skips the ragged bookkeeping when every cloud has n points and m centroids.
 
@@ -55,7 +55,9 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
     shape is supported and `params_host` (CPU copy of `params`) is given; env MGAR_SA_MLP overrides.
     `xyz` / `features` may be strided column views of one (N,3+C) array (tc only).
     tc only: `group_max` (ceil(M/group_size), C_out) receives the max over every run of `group_size`
-    consecutive centroids (rows with group_zero[g] != 0 stay zero); want_out=False skips the (M, C_out) result."""
+    consecutive centroids (rows with group_zero[g] != 0 stay zero); want_out=False skips the (M, C_out) result;
+    skip_zero_groups (with want_out=False) lets the kernel walk only the groups whose flag is 0 - same result, pays
+    when many groups are flagged (zero-padded person slots), costs ~8 % when none is."""
     need_cuda(new_xyz=new_xyz, idx=idx, params=params, empty_mask=empty_mask, group_max=group_max, group_zero=group_zero)
     need_dtype(torch.float32, xyz=xyz, new_xyz=new_xyz, features=features, params=params)
     need_dtype(torch.int32, idx=idx)
@@ -86,7 +88,8 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
                 B, M, nsample, C_in, ptr(xyz), xyz.stride(0), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt),
                 un, um, ptr(features), 0 if features is None else features.stride(0), ptr(idx), ptr(empty_mask),
                 len(channels) - 1, ctypes.addressof(ch), ptr(params), ptr(params_host), ptr(out),
-                0 if out is None else out.stride(0), ptr(group_max), int(group_size), ptr(group_zero),
+                (-1 if skip_zero_groups else 0) if out is None else out.stride(0), ptr(group_max), int(group_size),
+                ptr(group_zero),
                 1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd_tc")
         else:
             if not xyz.is_contiguous() or (features is not None and not features.is_contiguous()) or group_max is not None:
