@@ -259,8 +259,8 @@ MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const flo
  * consecutive centroids (the per-person feature when every person has group_size centroids); rows
  * whose group_zero[g] != 0 stay zero (empty persons).  The buffer is cleared by this call.  * Empty-person skip: with out == NULL (ld_out is then otherwise unused) ld_out == -1 asks the kernel to walk only the
  * groups whose group_zero flag is 0 (a device-side compacted list; uniform layout with uniform_m == group_size,
- * group_size % 4 == 0, C_in = 1); flagged groups keep their zero row either way, so results are identical - it pays
- * when many groups are empty (zero-padded person slots), and costs ~8 % when none is.
+ * group_size % 4 == 0, C_in = 1); flagged groups keep their zero row either way, so results are identical and
+ * empty or zero-padded person slots cost nothing (one extra 1-CTA launch of ~4 us builds the list).
 */
 MGAR_API int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg);
 MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float *xyz, int xyz_stride,

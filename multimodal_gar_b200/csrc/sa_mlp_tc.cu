@@ -495,8 +495,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
         if (!(mode && mode[0] == 't')) {
             // Persons flagged empty only produce a zero row: when the per-centroid features are not stored, walk the
             // live persons only (a list compacted on the device - no host round trip)
-            // Asked for with ld_out == -1 (see the header); MGAR_TC_SKIP_EMPTY=0/1 overrides for A/B runs.  Off by default:
-            // with no empty person the compacted walk measured 8 % slower (1.40 vs 1.29 ms per 64 configs[1] frames).
+            // Asked for with ld_out == -1 (see the header); MGAR_TC_SKIP_EMPTY=0/1 overrides for A/B runs.
             const char *skip = getenv("MGAR_TC_SKIP_EMPTY");
             const bool want = skip ? skip[0] == '1' : ld_out == -1;
             int *live = nullptr;

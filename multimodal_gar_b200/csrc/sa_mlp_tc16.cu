@@ -444,15 +444,24 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         int u_cloud = A.uniform ? (t_beg * 4 + pw) / A.m_u : 0, u_end = (u_cloud + 1) * A.m_u;
         int i_cloud = u_cloud, i_end = u_end;                    // the same walk for the index loads (they run ahead)
         // real person of the current virtual one, re-read only when the walk enters the next person (every 128 tiles)
-        int u_real = 0, i_real = 0;
-        if (compact && my_tiles > 0) u_real = i_real = __ldg(A.live_groups + u_cloud);
+        // kept as offsets so a tile pays one add: real centroid = virtual + delta, cloud start = u_start
+        int u_delta = 0, i_delta = 0;
+        long long u_start = 0;
+        if (compact && my_tiles > 0) {
+            const int real = __ldg(A.live_groups + u_cloud);
+            u_delta = i_delta = (real - u_cloud) * A.m_u;
+            u_start = (long long)real * A.n_u;
+        }
         auto load_idx = [&](int i, int &iv, int &em) {          // local tile i -> this lane's sample index
             int m = (t_beg + i) * 4 + pw;
             iv = -1; em = 0;
             if (i < my_tiles && m < M) {
                 if (compact) {                                   // virtual -> real centroid (m_u == group_size)
-                    while (m >= i_end) { i_cloud++; i_end += A.m_u; i_real = __ldg(A.live_groups + i_cloud); }
-                    m = i_real * A.m_u + (m - (i_end - A.m_u));
+                    while (m >= i_end) {
+                        i_cloud++; i_end += A.m_u;
+                        i_delta = (__ldg(A.live_groups + i_cloud) - i_cloud) * A.m_u;
+                    }
+                    m += i_delta;
                 }
                 iv = __ldg(A.idx + (size_t)m * kTcNS + lane);
                 if (A.empty_mask) em = A.empty_mask[m];
@@ -466,9 +475,14 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
                 long long start;
                 if (A.uniform) {
                     if (compact) {
-                        while (m >= u_end) { u_cloud++; u_end += A.m_u; u_real = __ldg(A.live_groups + u_cloud); }
-                        m = u_real * A.m_u + (m - (u_end - A.m_u));
-                        start = (long long)u_real * A.n_u;
+                        while (m >= u_end) {
+                            u_cloud++; u_end += A.m_u;
+                            const int real = __ldg(A.live_groups + u_cloud);
+                            u_delta = (real - u_cloud) * A.m_u;
+                            u_start = (long long)real * A.n_u;
+                        }
+                        m += u_delta;
+                        start = u_start;
                     } else {
                         while (m >= u_end) { u_cloud++; u_end += A.m_u; }     // tiles arrive in increasing order
                         start = (long long)u_cloud * A.n_u;

@@ -56,8 +56,8 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
     `xyz` / `features` may be strided column views of one (N,3+C) array (tc only).
     tc only: `group_max` (ceil(M/group_size), C_out) receives the max over every run of `group_size`
     consecutive centroids (rows with group_zero[g] != 0 stay zero); want_out=False skips the (M, C_out) result;
-    skip_zero_groups (with want_out=False) lets the kernel walk only the groups whose flag is 0 - same result, pays
-    when many groups are flagged (zero-padded person slots), costs ~8 % when none is."""
+    skip_zero_groups (with want_out=False) lets the kernel walk only the groups whose flag is 0 - same result, flagged
+    groups (empty or zero-padded person slots) cost nothing."""
     need_cuda(new_xyz=new_xyz, idx=idx, params=params, empty_mask=empty_mask, group_max=group_max, group_zero=group_zero)
     need_dtype(torch.float32, xyz=xyz, new_xyz=new_xyz, features=features, params=params)
     need_dtype(torch.int32, idx=idx)

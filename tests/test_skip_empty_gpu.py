@@ -1,6 +1,6 @@
 """-m gpu: the tensor-core SA MLP walks only the persons that pooled points (device-side live list, TcArgs::live_groups).
 Person features must be the same bits with the skip on (PointPersonEncoder(skip_empty_persons=True), what
-PointLiDARBackbone uses for its zero-padded proposals) and off (the default), for mixed, all-empty, single-live and
+the default) and off, for mixed, all-empty, single-live and
 zero-padded frames."""
 import numpy as np
 import pytest
@@ -66,4 +66,4 @@ def test_person_features_identical_with_and_without_the_skip(cuda, monkeypatch, 
 def test_backbone_for_padded_proposals_uses_the_skip(cuda):
     from multimodal_gar_b200 import lidar_backbone
     assert lidar_backbone.PointLiDARBackbone().encoder.skip_empty_persons
-    assert not lidar_branch.PointPersonEncoder(1).skip_empty_persons
+    assert lidar_branch.PointPersonEncoder(1).skip_empty_persons                # default: on
