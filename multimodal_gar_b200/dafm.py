@@ -117,12 +117,20 @@ class FusionAttentionMat(nn.Module):
                 outs.append(o.view(B, n, D))
         return outs
 
-    def forward(self, R, L, Dg, De, valid=None):
+    def distance_weights(self, De, valid=None):
+        """E_r = softmax(-(De / sigma), dim=1) (:484) over the valid keys; De (B,n,n)."""
+        return _masked_softmax(-(De / self.sigma), valid)
+
+    def forward(self, R, L, Dg, De, valid=None, E=None):
+        """E: optional precomputed `distance_weights(De, valid)` (batched call only) - the two modules of the fusion
+        step share it."""
         squeeze = R.dim() == 2
         if squeeze:
             R, L, De = R.unsqueeze(0), L.unsqueeze(0), De.unsqueeze(0)
             valid = None if valid is None else valid.unsqueeze(0)
-        E = _masked_softmax(-(De / self.sigma), valid)
+            E = None
+        if E is None:
+            E = self.distance_weights(De, valid)
         if self._fused_ok(R, L):
             Rp, Lp = self._fused(R, L, E, valid)
             return (Rp[0], Lp[0]) if squeeze else (Rp, Lp)
@@ -146,8 +154,12 @@ class DistanceAwareFusion(nn.Module):
 
     def forward(self, rgb, lidar, bboxes, bboxes3d, valid):
         from .lidar_backbone import pairwise_euclidean_distance
-        Dg = generalized_box_iou(bboxes)
+        # The reference also builds Dg = generalized_box_iou(bboxes) here (:1470) and hands it to both modules, which
+        # never read it (`E_l = Dg` is dead code, :499): ~15 elementwise launches on (B,n,n) that cannot change the result.
+        Dg = None
         De = pairwise_euclidean_distance(bboxes3d[..., :3])
-        R, L = self.AttFusModule1(rgb, lidar, Dg, De, valid)
-        R, L = self.AttFusModule2(R, L, Dg, De, valid)
+        E1 = self.AttFusModule1.distance_weights(De, valid)
+        E2 = E1 if self.AttFusModule2.sigma == self.AttFusModule1.sigma else None   # same De, same sigma: same weights
+        R, L = self.AttFusModule1(rgb, lidar, Dg, De, valid, E=E1)
+        R, L = self.AttFusModule2(R, L, Dg, De, valid, E=E2)
         return torch.maximum(R, L)
