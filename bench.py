@@ -402,7 +402,7 @@ def main():
                         frac=ach / pk["bf16_sustained"], traffic=ncu_traffic("sa_mlp", F), kernel=dom,
                         note="algorithmic fp32 FLOPs (2*M*P*K*8448 per frame) over the kernel's CUDA-event time, against the "
                              "%s sustained bf16 tensor peak; the kernel issues 3 fp16 MMAs per product (3xFP16 split, "
-                             "fp32-faithful), i.e. the tensor pipe does 3x the algorithmic work (ncu: pipe 85 %% busy, "
+                             "fp32-faithful), i.e. the tensor pipe does 3x the algorithmic work (ncu: pipe 82 %% busy, "
                              "profiles/r01_full_summary_final.md) - frac compares fp32-faithful output with a bf16 library "
                              "GEMM; traffic = ncu dram bytes per launch (profiles/r01_traffic.json)" % pk["source"])
         else:
