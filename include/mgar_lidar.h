@@ -25,7 +25,7 @@ extern "C" {
 #define MGAR_ECUDA (-2)   /* CUDA runtime / launch error                           */
 #define MGAR_ENOMEM (-3)  /* workspace too small / allocation failure              */
 
-#define MGAR_ABI_VERSION 1
+#define MGAR_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define MGAR_API __attribute__((visibility("default")))
@@ -155,10 +155,19 @@ MGAR_API int mgar_voxel_query_stack(int M, int R1, int R2, int R3, int nsample, 
  * query costs one ballot per 32 points instead of a second kernel.  xyz (b,n,xyz_stride) -> fps_idx (b,m) int32,
  * new_xyz (b,m,3), ball_idx (b*m,nsample) cloud-local indices exactly as mgar_fps_batch + mgar_ball_query_stack
  * (uniform layout, fill = 1) produce them.  Supported (mgar_fps_ball_query_supported != 0): n in {32,64,128,256,512},
- * nsample <= 64, b >= 592 clouds (one warp per cloud: a throughput kernel); otherwise call the two entries. */
+ * nsample <= 64, b >= 592 clouds (one warp per cloud: a throughput kernel); otherwise call the two entries.
+ */
 MGAR_API int mgar_fps_ball_query_supported(int b, int n, int m, int nsample);
+/*
+ * live_cnt (b) int32, optional: the number of DISTINCT samples of every cloud.  Pooled clouds repeat their points
+ * (roipoint_pool3d_kernel.cu:86-97), and once every distinct point is taken the reference's arg-max returns index 0
+ * (all min-distances are 0), so fps_idx[live_cnt ..] = 0 and those centroids repeat centroid 0.
+ * write_dup_rows: 1 = every ball_idx row is written (the reference's output); 0 = only the rows of the centroids
+ * [0, round_up(live_cnt, 4)) - for a consumer that walks the distinct centroids only (mgar_sa_mlp_fwd_tc with
+ * group_live_cnt); the other rows are left untouched. */
 MGAR_API int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xyz_stride, float radius, int nsample,
-                                 int *fps_idx, float *new_xyz, int *ball_idx, void *stream);
+                                 int *fps_idx, float *new_xyz, int *ball_idx, int *live_cnt, int write_dup_rows,
+                                 void *stream);
 
 /* group_points_wrapper_stack: group_points.cpp:50-67 (kernel group_points_gpu.cu:71-102).
  * out (M,C,nsample), every element written. */
@@ -261,15 +270,21 @@ MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const flo
  * groups whose group_zero flag is 0 (a device-side compacted list; uniform layout with uniform_m == group_size,
  * group_size % 4 == 0, C_in = 1); flagged groups keep their zero row either way, so results are identical and
  * empty or zero-padded person slots cost nothing (one extra 1-CTA launch of ~4 us builds the list).
-*/
+ * Distinct-centroid walk: group_live_cnt (ceil(M/group_size)) int32, optional, as written by mgar_fps_ball_query:
+ * with the skip above in force the kernel walks, per live group, only the tiles of four centroids that cover its first
+ * group_live_cnt[g] centroids - the others repeat centroid 0 (same ball, same feature row) and cannot change the
+ * group's max, so group_max holds the same bits.
+ * workspace: device scratch of mgar_sa_mlp_tc_workspace_bytes(M, group_size) bytes, needed only when the skip is
+ * asked for (NULL / 0 otherwise); the library allocates nothing. */
+MGAR_API size_t mgar_sa_mlp_tc_workspace_bytes(int M, int group_size);
 MGAR_API int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg);
 MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float *xyz, int xyz_stride,
                                 const int *xyz_batch_cnt, const float *new_xyz, const int *new_xyz_batch_cnt,
                                 int uniform_n, int uniform_m, const float *features, int feat_stride, const int *idx,
                                 const unsigned char *empty_mask, int n_layers, const int *channels_host,
                                 const float *params, const float *params_host, float *out, int ld_out,
-                                float *group_max, int group_size, const int *group_zero, int pool_avg,
-                                void *stream);
+                                float *group_max, int group_size, const int *group_zero, const int *group_live_cnt,
+                                int pool_avg, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---- training: the same module with BatchNorm batch statistics, and its backward pass ------------------- */
 

@@ -358,12 +358,14 @@ __device__ __forceinline__ int brev_bits_rt(int v, int bits) { return bits == 0 
 template <int P>
 __global__ void __maxnreg__(112)   // 9 CTAs x 64 threads x 112 registers = 63 K: one wave of 2560 clouds
 fps_bq_warp_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs, float *__restrict__ new_xyz,
-                   int *__restrict__ ball_idx, float radius, int K, int b, int m, int f4_per_warp) {
+                   int *__restrict__ ball_idx, float radius, int K, int b, int m, int f4_per_warp,
+                   int *__restrict__ live_cnt, int dup_rows) {
     constexpr int n = 32 * P, L = 5 + Log2P<P>::v;
     extern __shared__ float4 fps_sm4[];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int cloud = blockIdx.x * kFpsWarpsPerCta + w;
     if (cloud >= b) return;
+    const int cloud_id = cloud;
     float4 *sp = fps_sm4 + (size_t)w * f4_per_warp;  // [n] staged cloud, [m] sampled indices, 2 x [K] ball rows
     int *sidx = reinterpret_cast<int *>(sp + n);
     int *rows = sidx + m;
@@ -459,8 +461,12 @@ fps_bq_warp_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs
         __syncwarp();
         for (int l = lane; l < K; l += 32) row[l] = ball_idx[l];   // written by this warp (same lanes) in round 1
         __syncwarp();
-        for (int e = lane; e < (m - j) * K; e += 32) ball_idx[(size_t)j * K + e] = row[e % K];
+        // dup_rows == 0: the caller only walks the distinct centroids (live_cnt), rounded up to a tile of four
+        const int lim = dup_rows ? m : min(m, (j + 3) & ~3);
+        for (int e = lane; e < (lim - j) * K; e += 32) ball_idx[(size_t)j * K + e] = row[e % K];
     }
+    // number of DISTINCT samples: centroids live .. m-1 repeat centroid 0 (same ball, same features)
+    if (live_cnt && lane == 0) live_cnt[cloud_id] = done ? j : m;
     __syncwarp();
     for (int q = lane; q < m; q += 32) idxs[q] = sidx[q];
     for (int e = lane; e < m * 3; e += 32) {
@@ -579,7 +585,8 @@ extern "C" int mgar_fps_ball_query_supported(int b, int n, int m, int nsample) {
 }
 
 extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xyz_stride, float radius, int nsample,
-                                   int *fps_idx, float *new_xyz, int *ball_idx, void *stream) {
+                                   int *fps_idx, float *new_xyz, int *ball_idx, int *live_cnt, int write_dup_rows,
+                                   void *stream) {
     MGAR_REQUIRE(mgar_fps_ball_query_supported(b, n, m, nsample), "fps_ball_query: unsupported shape b=%d n=%d m=%d nsample=%d "
                  "(ask mgar_fps_ball_query_supported first)", b, n, m, nsample);
     MGAR_REQUIRE(xyz && fps_idx && new_xyz && ball_idx, "fps_ball_query: null pointer");
@@ -592,7 +599,8 @@ extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xy
 #define MGAR_FPS_BQ(p)                                                                                               \
     if (n == 32 * p) {                                                                                               \
         if (sm > 48 * 1024) MGAR_CUDA(cudaFuncSetAttribute(fps_bq_warp_kernel<p>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
-        fps_bq_warp_kernel<p><<<ctas, kFpsWarpsPerCta * 32, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, f4); \
+        fps_bq_warp_kernel<p><<<ctas, kFpsWarpsPerCta * 32, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, f4, \
+                                                                      live_cnt, write_dup_rows);                     \
         count_launch();                                                                                              \
         return check_launch("fps_ball_query");                                                                       \
     }

@@ -401,31 +401,12 @@ sa_mlp_tc_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ Tc
 
 using namespace mgar;
 
-// Scratch for the live-person list, kept per (device, stream): consecutive calls on a stream are ordered, so they can
-// share one buffer; a stream-ordered allocation per call would hand its memory back to the driver at every
-// synchronisation (default pool threshold) and pay a fresh allocation each step.  Never freed (a few KB per stream).
-static int *live_scratch(cudaStream_t st, size_t n_ints) {
-    struct Slot { int dev; cudaStream_t st; int *p; size_t cap; };
-    static std::mutex mu;
-    static std::vector<Slot> slots;
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
-    std::lock_guard<std::mutex> lock(mu);
-    for (Slot &s : slots)
-        if (s.dev == dev && s.st == st) {
-            if (s.cap < n_ints) {                      // grow: the old buffer may still be in use by queued work on `st`
-                int *q = nullptr;
-                if (cudaMalloc((void **)&q, 2 * n_ints * sizeof(int)) != cudaSuccess) return nullptr;
-                cudaStreamSynchronize(st);
-                cudaFree(s.p);
-                s.p = q; s.cap = 2 * n_ints;
-            }
-            return s.p;
-        }
-    int *q = nullptr;
-    if (cudaMalloc((void **)&q, 2 * n_ints * sizeof(int)) != cudaSuccess) return nullptr;
-    slots.push_back({dev, st, q, 2 * n_ints});
-    return q;
+// Workspace of the live-person / live-tile walk: one counter + the list (the caller owns it: SURVEY 8b).
+extern "C" size_t mgar_sa_mlp_tc_workspace_bytes(int M, int group_size) {
+    if (M <= 0 || group_size <= 0) return 0;
+    const size_t groups = ((size_t)M + group_size - 1) / group_size;
+    const size_t tiles = groups * (size_t)((group_size + 3) / 4);
+    return (4 + (tiles > groups ? tiles : groups)) * sizeof(int);
 }
 
 extern "C" int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg) {
@@ -438,8 +419,8 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
                                   int uniform_n, int uniform_m, const float *features, int feat_stride, const int *idx,
                                   const unsigned char *empty_mask, int n_layers, const int *channels_host,
                                   const float *params, const float *params_host, float *out, int ld_out,
-                                  float *group_max, int group_size, const int *group_zero, int pool_avg,
-                                  void *stream) {
+                                  float *group_max, int group_size, const int *group_zero, const int *group_live_cnt,
+                                  int pool_avg, void *workspace, size_t workspace_bytes, void *stream) {
     MGAR_REQUIRE(B >= 1 && M >= 0, "sa_mlp_tc: bad size");
     MGAR_REQUIRE(mgar_sa_mlp_tc_supported(nsample, C_in, n_layers, channels_host, pool_avg),
                  "sa_mlp_tc: only nsample=32, C_in<=4, channels [3+C_in,64,128], max-pool run on the tensor-core path");
@@ -474,7 +455,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     A.out = out; A.ld_out = ld_out;
     A.gmax = group_max; A.group_size = group_size > 0 ? group_size : 1; A.group_zero = group_zero;
     A.tr_zext = nullptr; A.tr_arg = nullptr; A.tr_sum = nullptr; A.tr_sq = nullptr;
-    A.live_groups = nullptr; A.n_live = nullptr;
+    A.live_groups = nullptr; A.n_live = nullptr; A.live_tiles = nullptr; A.m_shift = -1;
     A.packed4 = (C0 == 4 && xyz_stride == 4 && feat_stride == 4 && features == xyz + 3 &&
                  (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) ? 1 : 0;
 #ifdef MGAR_TC_TRACE
@@ -498,13 +479,24 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
             // Asked for with ld_out == -1 (see the header); MGAR_TC_SKIP_EMPTY=0/1 overrides for A/B runs.
             const char *skip = getenv("MGAR_TC_SKIP_EMPTY");
             const bool want = skip ? skip[0] == '1' : ld_out == -1;
-            int *live = nullptr;
-            if (want && C0 == 4 && !out && group_max && group_zero && uniform && uniform_m == group_size && group_size % 4 == 0) {
+            if (want && C0 == 4 && !out && group_max && group_zero && uniform && uniform_m == group_size && group_size % 4 == 0 &&
+                M % group_size == 0) {
                 const int G = M / group_size;
-                live = live_scratch(st, (size_t)G + 1);
-                MGAR_REQUIRE(live, "sa_mlp_tc: scratch for %d persons could not be allocated", G);
-                if (int rc = tc_compact_live_groups(group_zero, G, live + 1, live, st)) return rc;
-                A.live_groups = live + 1; A.n_live = live;
+                int *live = static_cast<int *>(workspace);
+                if (!live || workspace_bytes < mgar_sa_mlp_tc_workspace_bytes(M, group_size)) {
+                    set_error("sa_mlp_tc: the live-person walk needs a workspace of mgar_sa_mlp_tc_workspace_bytes(M, group_size) "
+                              "= %zu bytes, got %zu", mgar_sa_mlp_tc_workspace_bytes(M, group_size), workspace ? workspace_bytes : (size_t)0);
+                    return MGAR_ENOMEM;
+                }
+                if (group_live_cnt && !getenv("MGAR_TC_NO_LIVE_TILES")) {
+                    // distinct centroids only (see TcArgs::live_tiles): the sampling kernel reported how many each person has
+                    if (int rc = tc_build_live_tiles(group_zero, group_live_cnt, G, group_size, live + 4, live, st)) return rc;
+                    A.live_tiles = live + 4; A.n_live = live;
+                    for (int sft = 0; sft < 31; sft++) if ((1 << sft) == group_size) A.m_shift = sft;
+                } else {
+                    if (int rc = tc_compact_live_groups(group_zero, G, live + 4, live, st)) return rc;
+                    A.live_groups = live + 4; A.n_live = live;
+                }
             }
             return sa_mlp_tc16_launch(L1, A, C0, grid, st);
         }

@@ -41,12 +41,22 @@ struct TcArgs {
     // gmax != null (zero-filled: skipped persons keep their zero row), the uniform layout with m_u == group_size,
     // group_size % 4 == 0 (a tile of 4 centroids never straddles two persons).
     const int *live_groups, *n_live;
+    // distinct-centroid walk (sa_mlp_tc16 only; null = off): live_tiles[0 .. *n_live) = first REAL centroid of every
+    // tile of four centroids worth computing - for each person whose group_zero flag is 0, the tiles covering its
+    // first live_cnt centroids (farthest point sampling returns index 0 once every distinct point has been taken,
+    // so the centroids live_cnt .. group_size-1 repeat centroid 0 and cannot change the person's max).  Same
+    // preconditions as live_groups; m_shift = log2(group_size) or -1.
+    const int *live_tiles; int m_shift;
 };
 
 // sa_mlp_tc16.cu: the 3xFP16 kernel (default); sa_mlp_tc.cu keeps the 3xTF32 kernel (MGAR_TC_MODE=tf32)
 int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);
 // live[0 .. *n_live) = ascending indices g < G with group_zero[g] == 0 (one small launch)
 int tc_compact_live_groups(const int *group_zero, int G, int *live, int *n_live, cudaStream_t st);
+// tiles[0 .. *n_tiles) = g * group_size + 4 q for every g < G with group_zero[g] == 0 and q < ceil(live_cnt[g] / 4),
+// ascending (one small launch)
+int tc_build_live_tiles(const int *group_zero, const int *live_cnt, int G, int group_size, int *tiles, int *n_tiles,
+                        cudaStream_t st);
 int sa_mlp_tc16_launch_train(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);   // C0 = 4, 5
 
 }  // namespace mgar

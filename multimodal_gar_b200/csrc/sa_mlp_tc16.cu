@@ -144,7 +144,8 @@ __device__ __forceinline__ void sts_pack2_w(uint32_t a0, uint32_t a1, uint32_t b
     sts4(b0, lo[0], lo[1], lo[2], lo[3]); sts4(b1, lo[4], hi[3], hi[4], 0.f);
 }
 
-template <int C0, bool kTrain = false, bool kCompact = false>
+// kCompact: 0 = every centroid; 1 = live-person list (TcArgs::live_groups); 2 = live-TILE list (TcArgs::live_tiles)
+template <int C0, bool kTrain = false, int kCompact = 0>
 __global__ void __launch_bounds__(kThreads, 1)
 sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcBound BD, const __grid_constant__ TcArgs A) {
     static_assert(C0 >= 3 && C0 <= 7, "layer-1 K is padded to 8 with one column for the folded bias");
@@ -174,8 +175,9 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // M counts "virtual" centroids when the live-person list is in use (TcArgs::live_groups): only they are walked
-    constexpr bool compact = kCompact;
-    const int M = compact ? __ldg(A.n_live) * A.group_size : A.M;
+    constexpr bool compact = kCompact == 1;
+    constexpr bool tiled = kCompact == 2;      // tile i of the walk = the four real centroids live_tiles[i] .. +3 of ONE person
+    const int M = tiled ? __ldg(A.n_live) * 4 : (compact ? __ldg(A.n_live) * A.group_size : A.M);
     const int n_tiles = (M + 3) >> 2;
     // contiguous tile range per CTA: consecutive tiles belong to the same person, so the running
     // group max of the epilogue is flushed only a handful of times
@@ -303,16 +305,19 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         } else {
         const int gs = A.group_size;
         int m_next = t_beg * 4;                                   // first centroid of the next tile
-        int grp = A.gmax ? m_next / gs : 0, g_end = (grp + 1) * gs;
+        int grp = tiled ? -1 : (A.gmax ? m_next / gs : 0), g_end = (grp + 1) * gs;
         float gm = 0.f;
-        float *outp = A.out ? A.out + (size_t)m_next * A.ld_out + c : nullptr;
+        float *outp = (A.out && !tiled) ? A.out + (size_t)m_next * A.ld_out + c : nullptr;
         auto flush = [&]() {
             const int rg = compact ? __ldg(A.live_groups + grp) : grp;     // virtual -> real person
-            if (!(A.group_zero && __ldg(A.group_zero + rg)))
+            if (tiled || !(A.group_zero && __ldg(A.group_zero + rg)))       // (the tile list holds live persons only)
                 atomicMax(reinterpret_cast<int *>(A.gmax + (size_t)rg * kTcC2 + c), __float_as_int(gm));
         };
         for (int i = 0; i < my_tiles; i++) {
             const int t = i % kAcc, u = i / kAcc;
+            int tile_person = 0;
+            if (tiled) tile_person = A.m_shift >= 0 ? __ldg(A.live_tiles + t_beg + i) >> A.m_shift
+                                                    : __ldg(A.live_tiles + t_beg + i) / gs;
             mbar_wait(TFULL(t), u & 1);
             if (warp == 0) TR(12, i);
             tc_fence_after();
@@ -344,7 +349,13 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             float res[4];
 #pragma unroll
             for (int q = 0; q < 4; q++) res[q] = fmaxf(__fmaf_rn(mx[q], __fmul_rn(asc, sq[q]), shift), 0.f);
-            if (m_next + 4 <= M && (!A.gmax || m_next + 4 <= g_end)) {
+            if (tiled) {
+                if (tile_person != grp) {                     // the walk entered the next person
+                    if (grp >= 0) flush();
+                    grp = tile_person; gm = 0.f;
+                }
+                gm = fmaxf(max3(gm, res[0], res[1]), fmaxf(res[2], res[3]));
+            } else if (m_next + 4 <= M && (!A.gmax || m_next + 4 <= g_end)) {
                 // common case: four real centroids of one group
                 if (outp) {
 #pragma unroll
@@ -452,9 +463,17 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             u_delta = i_delta = (real - u_cloud) * A.m_u;
             u_start = (long long)real * A.n_u;
         }
-        auto load_idx = [&](int i, int &iv, int &em) {          // local tile i -> this lane's sample index
+        auto load_idx = [&](int i, int &iv, int &em, int &mr) {   // local tile i -> this lane's sample index (mr: real centroid)
             int m = (t_beg + i) * 4 + pw;
-            iv = -1; em = 0;
+            iv = -1; em = 0; mr = 0;
+            if (tiled) {
+                if (i < my_tiles) {
+                    mr = __ldg(A.live_tiles + t_beg + i) + pw;
+                    iv = __ldg(A.idx + (size_t)mr * kTcNS + lane);
+                    if (A.empty_mask) em = A.empty_mask[mr];
+                }
+                return;
+            }
             if (i < my_tiles && m < M) {
                 if (compact) {                                   // virtual -> real centroid (m_u == group_size)
                     while (m >= i_end) {
@@ -467,13 +486,15 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
                 if (A.empty_mask) em = A.empty_mask[m];
             }
         };
-        auto load_pt = [&](int i, int iv, int em, float (&v)[C0], float (&q)[3], bool &live) {
-            int m = (t_beg + i) * 4 + pw;
+        auto load_pt = [&](int i, int iv, int em, int mr, float (&v)[C0], float (&q)[3], bool &live) {
+            int m = tiled ? mr : (t_beg + i) * 4 + pw;
             const int first = __shfl_sync(0xffffffffu, iv, 0);
-            live = (i < my_tiles) && (m < M) && first >= 0 && !em;
+            live = (i < my_tiles) && (tiled || m < M) && first >= 0 && !em;
             if (live) {
                 long long start;
-                if (A.uniform) {
+                if (tiled) {
+                    start = (long long)(A.m_shift >= 0 ? m >> A.m_shift : m / A.m_u) * A.n_u;
+                } else if (A.uniform) {
                     if (compact) {
                         while (m >= u_end) {
                             u_cloud++; u_end += A.m_u;
@@ -542,21 +563,21 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             if (pw == 0) TR(2, i);
         };
 
-        int iv_a = -1, em_a = 0, iv_b = -1, em_b = 0;
+        int iv_a = -1, em_a = 0, iv_b = -1, em_b = 0, mr_a = 0, mr_b = 0;
         float vb[C0], qb[3];
         bool live_b = false;
-        load_idx(g, iv_b, em_b);
-        load_pt(g, iv_b, em_b, vb, qb, live_b);
-        load_idx(g + 2, iv_b, em_b);
-        load_idx(g + 4, iv_a, em_a);
+        load_idx(g, iv_b, em_b, mr_b);
+        load_pt(g, iv_b, em_b, mr_b, vb, qb, live_b);
+        load_idx(g + 2, iv_b, em_b, mr_b);
+        load_idx(g + 4, iv_a, em_a, mr_a);
         if (g < my_tiles) store_x(g, vb, qb, live_b);
-        load_pt(g + 2, iv_b, em_b, vb, qb, live_b);
+        load_pt(g + 2, iv_b, em_b, mr_b, vb, qb, live_b);
         for (int i = g, k = 0; i < my_tiles; i += 2, k++) {
             if (i + 2 < my_tiles) {
                 store_x(i + 2, vb, qb, live_b);                 // gathered during the previous iteration
-                iv_b = iv_a; em_b = em_a;
-                load_pt(i + 4, iv_b, em_b, vb, qb, live_b);     // points two own tiles ahead
-                load_idx(i + 6, iv_a, em_a);                    // indices three own tiles ahead
+                iv_b = iv_a; em_b = em_a; mr_b = mr_a;
+                load_pt(i + 4, iv_b, em_b, mr_b, vb, qb, live_b);   // points two own tiles ahead
+                load_idx(i + 6, iv_a, em_a, mr_a);                  // indices three own tiles ahead
             }
             const int s = i % kStages, j = i / kStages;
             if (pw == 0) TR(3, i);
@@ -642,6 +663,55 @@ int tc_compact_live_groups(const int *group_zero, int G, int *live, int *n_live,
     return check_launch("compact_live_groups");
 }
 
+// One CTA: per 1024 persons an exclusive scan of their tile counts, then warp w writes the tile rows of the persons
+// w, w+32, ... (lanes = consecutive tiles: coalesced).
+__global__ void __launch_bounds__(1024)
+build_live_tiles_kernel(const int *__restrict__ group_zero, const int *__restrict__ live_cnt, int G, int gs,
+                        int *__restrict__ tiles, int *__restrict__ n_tiles) {
+    __shared__ int s_warp[32];
+    __shared__ int s_first[1024], s_cnt[1024];
+    __shared__ int s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (int g0 = 0; g0 < G; g0 += 1024) {
+        const int g = g0 + tid;
+        int c = 0;
+        if (g < G && __ldg(group_zero + g) == 0) {
+            int lc = __ldg(live_cnt + g);
+            lc = lc < 1 ? 1 : (lc > gs ? gs : lc);
+            c = (lc + 3) >> 2;
+        }
+        int incl = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        int before = s_base;
+        for (int w = 0; w < warp; w++) before += s_warp[w];
+        s_first[tid] = before + incl - c;
+        s_cnt[tid] = c;
+        __syncthreads();
+        if (tid == 1023) s_base = before + incl;
+        for (int q = warp; q < 1024 && g0 + q < G; q += 32) {
+            const int first = s_first[q], cnt = s_cnt[q], c0 = (g0 + q) * gs;
+            for (int k = lane; k < cnt; k += 32) tiles[first + k] = c0 + 4 * k;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) *n_tiles = s_base;
+}
+
+int tc_build_live_tiles(const int *group_zero, const int *live_cnt, int G, int group_size, int *tiles, int *n_tiles,
+                        cudaStream_t st) {
+    build_live_tiles_kernel<<<1, 1024, 0, st>>>(group_zero, live_cnt, G, group_size, tiles, n_tiles);
+    count_launch();
+    return check_launch("build_live_tiles");
+}
+
 int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st) {
     TcBound BD;
     BD.shmax = 0.f;
@@ -665,9 +735,15 @@ int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cu
 #else
 #define TC16_TRACE_DUMP
 #endif
+    if (A.live_tiles && C0 == 4) {       // live-tile walk: only the distinct centroids of the persons that pooled points
+        MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<4, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+        sa_mlp_tc16_kernel<4, false, 2><<<grid, kThreads, kSmem, st>>>(L1, BD, A);
+        count_launch();
+        return check_launch("sa_mlp_tc16 (live tiles)");
+    }
     if (A.live_groups && C0 == 4) {      // live-person walk (the LiDAR branch: xyz + intensity)
-        MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<4, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
-        sa_mlp_tc16_kernel<4, false, true><<<grid, kThreads, kSmem, st>>>(L1, BD, A);
+        MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<4, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+        sa_mlp_tc16_kernel<4, false, 1><<<grid, kThreads, kSmem, st>>>(L1, BD, A);
         count_launch();
         return check_launch("sa_mlp_tc16 (live persons)");
     }

@@ -32,11 +32,13 @@ def fps_gather(xyz, npoint):
     return idx, new_xyz
 
 
-def fps_ball_query(xyz, npoint, radius, nsample):
+def fps_ball_query(xyz, npoint, radius, nsample, all_rows=True):
     """FPS + ball query around the sampled points in one kernel, for many equally sized power-of-two clouds.
     xyz (b,n,3) (column view of a (b,n,3+C) array allowed) -> (idx (b,npoint) int32, new_xyz (b,npoint,3),
-    ball_idx (b*npoint,nsample) int32) - the results of fps_gather + ball_query_uniform - or None when the shape is
-    not covered (the caller then runs the two kernels)."""
+    ball_idx (b*npoint,nsample) int32, live_cnt (b) int32) - the results of fps_gather + ball_query_uniform, plus the
+    number of distinct samples per cloud (the centroids behind it repeat centroid 0) - or None when the shape is
+    not covered (the caller then runs the two kernels).  all_rows=False: the ball rows of the repeated centroids are
+    not written (only up to the next multiple of four) - for the consumer that walks the distinct centroids."""
     b, n = xyz.shape[0], xyz.shape[1]
     L = _lib.lib()
     if not L.mgar_fps_ball_query_supported(b, n, int(npoint), int(nsample)):
@@ -47,10 +49,11 @@ def fps_ball_query(xyz, npoint, radius, nsample):
     idx = torch.empty((b, npoint), dtype=torch.int32, device=xyz.device)
     new_xyz = torch.empty((b, npoint, 3), dtype=torch.float32, device=xyz.device)
     ball_idx = torch.empty((b * npoint, nsample), dtype=torch.int32, device=xyz.device)
+    live_cnt = torch.empty((b,), dtype=torch.int32, device=xyz.device)
     with on_device(xyz):
         _lib.check(L.mgar_fps_ball_query(b, n, int(npoint), ptr(xyz), xs, float(radius), int(nsample), ptr(idx), ptr(new_xyz),
-                                         ptr(ball_idx), stream_of(xyz)), "fps_ball_query")
-    return idx, new_xyz, ball_idx
+                                         ptr(ball_idx), ptr(live_cnt), 1 if all_rows else 0, stream_of(xyz)), "fps_ball_query")
+    return idx, new_xyz, ball_idx, live_cnt
 
 
 def ball_query_uniform(radius, nsample, xyz, new_xyz, n, m):

@@ -57,6 +57,9 @@ class PointPersonEncoder(nn.Module):
         # True: the tensor-core MLP walks only the persons that pooled points (same feature bits; a padded or empty
         # person slot costs nothing; with no empty person the walk measures on par with the plain one)
         self.skip_empty_persons = skip_empty_persons
+        # True: ... and of those persons only the distinct centroids (a person that pooled c < P points has c distinct
+        # samples; farthest point sampling returns index 0 for the rest, whose features repeat centroid 0's)
+        self.skip_repeated_centroids = os.environ.get('MGAR_TC_NO_LIVE_TILES', '0') == '0'
         self.num_sampled_points, self.npoint = num_sampled_points, npoint
         self.pool_extra_width = tuple(pool_extra_width)
         self.fused_canonical = fused_canonical
@@ -108,14 +111,19 @@ class PointPersonEncoder(nn.Module):
             pooled, empty = self.pool(points, point_features, boxes)                # (B*M,S,3+C) canonical frame
             mark('roipoint_pool')
         g = self.sa.groupers[0]
+        ball_idx = live_cnt = None
         packed = None if (self.training or torch.is_grad_enabled()) else self.sa._pack(pooled.device)[0]
         C = pooled.shape[2] - 3
         if packed is not None and sa_mlp_fused.tc_supported(packed[0], g.nsample, C):
             # fused path: every kernel reads the pooled (.., 3+C) rows in place; 5 launches per step
             flat = pooled.view(B * M * S, 3 + C)
-            fused = fastpath.fps_ball_query(pooled[:, :, 0:3], P, g.radius, g.nsample)
+            want_out = return_stages or self.keep_sa_features
+            # distinct-centroid walk: pooled clouds repeat their points, the sampling kernel reports how many distinct
+            # samples each person has and the MLP computes only those (the others repeat centroid 0: same max)
+            walk = self.skip_empty_persons and self.skip_repeated_centroids and not want_out
+            fused = fastpath.fps_ball_query(pooled[:, :, 0:3], P, g.radius, g.nsample, all_rows=not walk)
             if fused is not None:                  # sampling and ball query share their distances: one kernel
-                fps_idx, new_xyz, ball_idx = fused
+                fps_idx, new_xyz, ball_idx, live_cnt = fused
                 new_xyz = new_xyz.view(B * M * P, 3)
                 mark('fps_ball_query')
             else:
@@ -128,9 +136,9 @@ class PointPersonEncoder(nn.Module):
             sa_feat = sa_mlp_fused.sa_mlp_forward(packed[0], packed[1], g.nsample, flat[:, 0:3], None, new_xyz, None,
                                                   flat[:, 3:] if C else None, ball_idx, uniform=(S, P),
                                                   params_host=packed[2], impl='tc', group_max=person, group_size=P,
-                                                  group_zero=empty.view(-1),
-                                                  want_out=return_stages or self.keep_sa_features,
-                                                  skip_zero_groups=self.skip_empty_persons)
+                                                  group_zero=empty.view(-1), want_out=want_out,
+                                                  skip_zero_groups=self.skip_empty_persons,
+                                                  group_live_cnt=live_cnt if walk else None)
             mark('sa_mlp')
             person = person.view(B, M, -1)
         else:
@@ -150,6 +158,8 @@ class PointPersonEncoder(nn.Module):
             person = person.view(B, M, -1)
             mark('person_reduce')
         if return_stages:
-            return dict(box_idx=box_idx, pooled=pooled, empty=empty, fps_idx=fps_idx, new_xyz=new_xyz,
+            # ball_idx: raw kernel rows (cloud-local indices, -1 in slot 0 of an empty ball), fused path only
+            return dict(box_idx=box_idx, pooled=pooled, empty=empty, fps_idx=fps_idx, new_xyz=new_xyz, ball_idx=ball_idx,
+                        live_cnt=live_cnt,
                         sa_features=sa_feat, person_features=person)
         return person

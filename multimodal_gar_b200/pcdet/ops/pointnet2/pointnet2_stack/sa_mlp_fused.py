@@ -47,7 +47,8 @@ def tc_supported(channels, nsample, C_in, pool_avg=False):
 
 def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features, idx,
                    empty_mask=None, out=None, pool_avg=False, uniform=None, params_host=None, impl=None,
-                   group_max=None, group_size=0, group_zero=None, want_out=True, skip_zero_groups=False):
+                   group_max=None, group_size=0, group_zero=None, want_out=True, skip_zero_groups=False,
+                   group_live_cnt=None):
     """-> (M, channels[-1]) fp32.  `idx` as returned by ball_query (or the raw kernel output);
     `uniform=(n, m)` skips the ragged bookkeeping when every cloud has n points and m centroids.
 
@@ -57,8 +58,11 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
     tc only: `group_max` (ceil(M/group_size), C_out) receives the max over every run of `group_size`
     consecutive centroids (rows with group_zero[g] != 0 stay zero); want_out=False skips the (M, C_out) result;
     skip_zero_groups (with want_out=False) lets the kernel walk only the groups whose flag is 0 - same result, flagged
-    groups (empty or zero-padded person slots) cost nothing."""
-    need_cuda(new_xyz=new_xyz, idx=idx, params=params, empty_mask=empty_mask, group_max=group_max, group_zero=group_zero)
+    groups (empty or zero-padded person slots) cost nothing; group_live_cnt (per group, int32, from
+    fastpath.fps_ball_query) additionally restricts the walk to each group's distinct centroids (same maxima)."""
+    need_cuda(new_xyz=new_xyz, idx=idx, params=params, empty_mask=empty_mask, group_max=group_max, group_zero=group_zero,
+              group_live_cnt=group_live_cnt)
+    need_dtype(torch.int32, group_live_cnt=group_live_cnt, group_zero=group_zero)
     need_dtype(torch.float32, xyz=xyz, new_xyz=new_xyz, features=features, params=params)
     need_dtype(torch.int32, idx=idx)
     if not xyz.is_cuda or xyz.dim() != 2 or xyz.stride(1) != 1:
@@ -84,13 +88,16 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
         if impl == 'tc':
             if params_host is None or params_host.is_cuda or not params_host.is_contiguous():
                 raise _lib.MgarError("the tensor-core path needs params_host (contiguous CPU copy of params)")
+            skip = out is None and skip_zero_groups and group_max is not None
+            ws_bytes = int(L.mgar_sa_mlp_tc_workspace_bytes(M, int(group_size))) if skip else 0
+            ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz.device) if ws_bytes else None
             _lib.check(L.mgar_sa_mlp_fwd_tc(
                 B, M, nsample, C_in, ptr(xyz), xyz.stride(0), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt),
                 un, um, ptr(features), 0 if features is None else features.stride(0), ptr(idx), ptr(empty_mask),
                 len(channels) - 1, ctypes.addressof(ch), ptr(params), ptr(params_host), ptr(out),
                 (-1 if skip_zero_groups else 0) if out is None else out.stride(0), ptr(group_max), int(group_size),
-                ptr(group_zero),
-                1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd_tc")
+                ptr(group_zero), ptr(group_live_cnt) if skip else 0,
+                1 if pool_avg else 0, ptr(ws), ws_bytes, stream_of(xyz)), "sa_mlp_fwd_tc")
         else:
             if not xyz.is_contiguous() or (features is not None and not features.is_contiguous()) or group_max is not None:
                 raise _lib.MgarError("the fp32 path needs contiguous xyz / features and has no group_max output")

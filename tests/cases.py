@@ -119,3 +119,26 @@ def voxelrcnn_scene(seed=11, B=2, rois=4, grid=(16, 96, 96), voxel_size=(0.1, 0.
         out[name + ".spatial_shape"] = np.asarray(shape, np.int32)
         out[name + ".stride"] = np.asarray(stride, np.int32)
     return out
+
+
+def unambiguous(O, xyz, boxes, max_amb=8):
+    """(point_ok (N,), box_ok (M,)) for one frame: the CPU oracle uses glibc cosf/sinf, the GPU libdevice, so a
+    (point, box) pair whose in-box decision flips under a 1-ulp trig change may legitimately differ.  Such pairs are
+    rare (a point within ~1e-6 m of a face): comparisons keep every point / box that has none instead of dropping the
+    whole frame, and the count is asserted small."""
+    amb = O.in_box_ambiguous(np.ascontiguousarray(xyz), np.ascontiguousarray(boxes)) != 0
+    assert int(amb.sum()) <= max_amb, "suspiciously many trig-ambiguous pairs: %d" % int(amb.sum())
+    return ~amb.any(axis=0), ~amb.any(axis=1)
+
+
+def canonical_close(got, want, pooled_raw, boxes, rel=1e-5):
+    """Canonical-frame coordinates (pointrcnn_head.py:121-129): |got - want| <= rel * |(x - cx, y - cy)| per point -
+    north_star's 1e-5 relative, taken against the rotated VECTOR (a rotation cancels, so an element can be ~0 while its
+    error is an ulp of the vector's length); z is a plain subtraction and the features are copies: exact.
+    got / want (M,S,3+C) canonical, pooled_raw (M,S,3+C) sensor frame, boxes (M,7)."""
+    sx = pooled_raw[..., 0] - boxes[:, None, 0]
+    sy = pooled_raw[..., 1] - boxes[:, None, 1]
+    bound = rel * np.hypot(sx, sy) + 1e-30
+    err = np.abs(got[..., :2].astype(np.float64) - want[..., :2].astype(np.float64)).max(axis=-1)
+    assert (err <= bound).all(), "canonical xy off by %g of the vector length" % float((err / bound).max() * rel)
+    np.testing.assert_array_equal(got[..., 2:], want[..., 2:])

@@ -44,7 +44,7 @@ def test_ctypes_table_matches_header():
 
 def test_abi_version_and_error_string():
     L = _lib.lib()
-    assert L.mgar_abi_version() == 1
+    assert L.mgar_abi_version() == 2
     assert isinstance(L.mgar_last_error(), bytes)
 
 

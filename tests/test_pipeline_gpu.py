@@ -5,6 +5,7 @@ import numpy as np
 import pytest
 import torch
 
+import cases
 from multimodal_gar_b200 import lidar_branch, synthetic
 from oracle import oracle as O
 
@@ -68,12 +69,15 @@ def test_stagewise_against_oracle_config2_frame(cuda):
         st = enc(xyz, feat, bx, return_stages=True)
     S, P, K, r, M = 512, 512, 32, 0.3, 40
     x_np, f_np = np.ascontiguousarray(pts[..., :3]), np.ascontiguousarray(pts[..., 3:4])
-    amb = int(O.in_box_ambiguous(x_np[0], boxes[0]).sum())
-    if amb == 0:
-        np.testing.assert_array_equal(st["box_idx"].cpu().numpy(), O.points_in_boxes_gpu(x_np, boxes))
-        pooled, empty = O.roipoint_pool3d(x_np, f_np, boxes, (0, 0, 0), S)
-        np.testing.assert_array_equal(st["empty"].cpu().numpy(), empty)
-        np.testing.assert_allclose(st["pooled"].cpu().numpy(), O.canonical_transform(pooled, boxes, empty), rtol=0, atol=2e-5)
+    # every point / box without a trig-ambiguous pair is compared (never the whole frame dropped)
+    pt_ok, box_ok = cases.unambiguous(O, x_np[0], boxes[0])
+    np.testing.assert_array_equal(st["box_idx"].cpu().numpy()[0][pt_ok], O.points_in_boxes_gpu(x_np, boxes)[0][pt_ok])
+    pooled, empty = O.roipoint_pool3d(x_np, f_np, boxes, (0, 0, 0), S)
+    assert box_ok.sum() >= M - 2
+    np.testing.assert_array_equal(st["empty"].cpu().numpy()[0][box_ok], empty[0][box_ok])
+    live = box_ok & (empty[0] == 0)
+    cases.canonical_close(st["pooled"].cpu().numpy()[live], O.canonical_transform(pooled, boxes, empty)[live],
+                          pooled[0][live], boxes[0][live])
     got_pooled = st["pooled"].cpu().numpy()
     cxyz = np.ascontiguousarray(got_pooled[..., :3])
     fps = O.farthest_point_sample(cxyz, P)
@@ -110,10 +114,12 @@ def test_crowded_scene_stress_config5(cuda):
     with torch.no_grad():
         st = enc(xyz, feat, bx, return_stages=True)
     x_np, f_np = np.ascontiguousarray(pts[..., :3]), np.ascontiguousarray(pts[..., 3:4])
-    if int(O.in_box_ambiguous(x_np[0], boxes[0]).sum()) == 0:
-        pooled, empty = O.roipoint_pool3d(x_np, f_np, boxes, (0, 0, 0), 512)
-        np.testing.assert_array_equal(st["empty"].cpu().numpy(), empty)
-        np.testing.assert_array_equal(st["pooled"].cpu().numpy()[..., 3], O.canonical_transform(pooled, boxes, empty)[..., 3])
+    _, box_ok = cases.unambiguous(O, x_np[0], boxes[0], max_amb=16)
+    assert box_ok.sum() >= 190
+    pooled, empty = O.roipoint_pool3d(x_np, f_np, boxes, (0, 0, 0), 512)
+    np.testing.assert_array_equal(st["empty"].cpu().numpy()[0][box_ok], empty[0][box_ok])
+    np.testing.assert_array_equal(st["pooled"].cpu().numpy()[box_ok][..., 3],
+                                  O.canonical_transform(pooled, boxes, empty)[box_ok][..., 3])
     assert torch.isfinite(st["person_features"]).all()
     assert st["person_features"].shape == (1, 200, 128)
 

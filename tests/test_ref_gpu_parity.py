@@ -70,10 +70,11 @@ def test_roipoint_pool_bit_exact(cuda, seed, N, M, S, extra):
     # and the CPU oracle agrees with the reference kernel wherever no pair is trig-ambiguous
     if N <= 65536:
         op, oe = O.roipoint_pool3d(pts[..., :3], pts[..., 3:4], boxes, (extra, extra, extra), S)
-        amb = sum(int(O.in_box_ambiguous(np.ascontiguousarray(pts[b, :, :3]), big[b]).sum()) for b in range(2))
-        if amb == 0:
-            np.testing.assert_array_equal(pa.cpu().numpy(), op)
-            np.testing.assert_array_equal(ea.cpu().numpy(), oe)
+        for b in range(2):   # every box without a trig-ambiguous pair is compared
+            _, box_ok = cases.unambiguous(O, pts[b, :, :3], big[b])
+            assert box_ok.sum() >= M - 2
+            np.testing.assert_array_equal(pa.cpu().numpy()[b][box_ok], op[b][box_ok])
+            np.testing.assert_array_equal(ea.cpu().numpy()[b][box_ok], oe[b][box_ok])
 
 
 @pytest.mark.parametrize("b,n,m,ties", [(40, 512, 512, True), (40, 512, 512, False), (8, 300, 128, True),
