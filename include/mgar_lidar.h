@@ -78,13 +78,14 @@ MGAR_API int mgar_roipoint_pool(const float *xyz, const float *boxes, const floa
  * buffer is zero-filled by the call.  When box_idx != NULL the same pass also writes points_in_boxes_gpu's
  * first-hit index (roiaware_pool3d_kernel.cu:313-336) for boxes_first (pass the same pointer as boxes_pool when
  * the pooling boxes are not enlarged: the tests are then shared).  Pass 2 turns the masks into the pooled rows;
- * arguments and outputs as mgar_roipoint_pool. */
+ * arguments and outputs as mgar_roipoint_pool, plus pooled_cnt (B,M) int32, optional: min(in-box points, S) - the
+ * number of DISTINCT rows of each pooled cloud (the scheduling weight of mgar_fps_ball_query). */
 MGAR_API size_t mgar_box_mask_words(int N);
 MGAR_API int mgar_box_masks(const float *boxes_first, const float *boxes_pool, const float *pts, int *box_idx,
                             unsigned *mask, int B, int M, int N, void *stream);
 MGAR_API int mgar_roipoint_pool_from_masks(const float *xyz, const float *boxes, const float *feat, const unsigned *mask,
-                                           float *pooled, int *empty, int *pts_idx, int B, int N, int M, int S, int C,
-                                           int canonical, void *stream);
+                                           float *pooled, int *empty, int *pts_idx, int *pooled_cnt, int B, int N, int M,
+                                           int S, int C, int canonical, void *stream);
 
 /* ---- roiaware_pool3d: voxel pooling inside boxes ---------------------------------------------- */
 
@@ -154,8 +155,9 @@ MGAR_API int mgar_voxel_query_stack(int M, int R1, int R2, int R3, int nsample, 
  * point against sample j-1, which is the distance the ball query around that centroid tests (bit-identical), so the
  * query costs one ballot per 32 points instead of a second kernel.  xyz (b,n,xyz_stride) -> fps_idx (b,m) int32,
  * new_xyz (b,m,3), ball_idx (b*m,nsample) cloud-local indices exactly as mgar_fps_batch + mgar_ball_query_stack
- * (uniform layout, fill = 1) produce them.  Supported (mgar_fps_ball_query_supported != 0): n in {32,64,128,256,512},
- * nsample <= 64, b >= 592 clouds (one warp per cloud: a throughput kernel); otherwise call the two entries.
+ * (uniform layout, fill = 1) produce them.  Supported (mgar_fps_ball_query_supported != 0): nsample <= 64 and
+ * n in {128,256,512} (a CTA of four warps per cloud, any number of clouds) or n in {32,64} with b >= 592 clouds (one warp
+ * per cloud); otherwise call the two entries.
  */
 MGAR_API int mgar_fps_ball_query_supported(int b, int n, int m, int nsample);
 /*
@@ -164,10 +166,15 @@ MGAR_API int mgar_fps_ball_query_supported(int b, int n, int m, int nsample);
  * (all min-distances are 0), so fps_idx[live_cnt ..] = 0 and those centroids repeat centroid 0.
  * write_dup_rows: 1 = every ball_idx row is written (the reference's output); 0 = only the rows of the centroids
  * [0, round_up(live_cnt, 4)) - for a consumer that walks the distinct centroids only (mgar_sa_mlp_fwd_tc with
- * group_live_cnt); the other rows are left untouched. */
+ * group_live_cnt); the other rows are left untouched.
+ * cloud_weight (b) int32, optional: an estimate of each cloud's sampling rounds (its number of distinct points, e.g.
+ * pooled_cnt of mgar_roipoint_pool_from_masks).  The clouds are then scheduled heaviest first (a one-CTA counting sort
+ * into `workspace`, mgar_fps_ball_query_workspace_bytes(b) bytes of device scratch) so that the long clouds do not
+ * form a tail; results do not depend on it.  NULL: clouds run in index order, no workspace needed. */
+MGAR_API size_t mgar_fps_ball_query_workspace_bytes(int b);
 MGAR_API int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xyz_stride, float radius, int nsample,
                                  int *fps_idx, float *new_xyz, int *ball_idx, int *live_cnt, int write_dup_rows,
-                                 void *stream);
+                                 const int *cloud_weight, void *workspace, size_t workspace_bytes, void *stream);
 
 /* group_points_wrapper_stack: group_points.cpp:50-67 (kernel group_points_gpu.cu:71-102).
  * out (M,C,nsample), every element written. */

@@ -27,7 +27,7 @@ SIGNATURES = {
     "mgar_roipoint_pool": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
     "mgar_box_mask_words": [_i],
     "mgar_box_masks": [_p, _p, _p, _p, _p, _i, _i, _i, _p],
-    "mgar_roipoint_pool_from_masks": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
+    "mgar_roipoint_pool_from_masks": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
     "mgar_roiaware_pool3d_workspace_bytes": [_i, _i],
     "mgar_roiaware_pool3d_fwd": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p],
     "mgar_roiaware_pool3d_bwd": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p],
@@ -46,7 +46,8 @@ SIGNATURES = {
     "mgar_dafm_attention": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p],
     "mgar_dafm_add_layernorm": [_i, _i, _p, _p, _p, _p, _p, _f, _p, _p],
     "mgar_fps_ball_query_supported": [_i, _i, _i, _i],
-    "mgar_fps_ball_query": [_i, _i, _i, _p, _i, _f, _i, _p, _p, _p, _p, _i, _p],
+    "mgar_fps_ball_query_workspace_bytes": [_i],
+    "mgar_fps_ball_query": [_i, _i, _i, _p, _i, _f, _i, _p, _p, _p, _p, _i, _p, _p, ctypes.c_size_t, _p],
     "mgar_group_points_stack": [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_group_points_grad_stack": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_sa_mlp_tc_supported": [_i, _i, _i, _p, _i],
@@ -94,6 +95,7 @@ def lib():
         L.mgar_sa_mlp_train_workspace_bytes_for.restype = ctypes.c_size_t
         L.mgar_box_mask_words.restype = ctypes.c_size_t
         L.mgar_sa_mlp_tc_workspace_bytes.restype = ctypes.c_size_t
+        L.mgar_fps_ball_query_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_roiaware_pool3d_workspace_bytes.restype = ctypes.c_size_t
         _lib = L
     return _lib

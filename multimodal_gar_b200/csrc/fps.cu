@@ -20,6 +20,7 @@
 #include <limits.h>
 #include <stdlib.h>
 
+#include "fps_bq_cta.cuh"
 #include "mgar_common.cuh"
 
 namespace mgar {
@@ -579,19 +580,79 @@ extern "C" int mgar_fps_stack(int batch, int max_n, const float *xyz, float *tem
                         num_sampled, 0, 0, 10, 1);
 }
 
+// ---- fused sampling + ball query: entry points --------------------------------------------------------------
+// n in {128, 256, 512}: one CTA of W warps per cloud (fps_bq_cta.cuh), any number of clouds;
+// n in {32, 64}: one warp per cloud (fps_bq_warp_kernel), >= 592 clouds.  MGAR_FPS_BQ=warp forces the warp kernel
+// (A/B runs), MGAR_FPS_BQ_GEOM="W,PPL" picks another CTA geometry with 32 * W * PPL == n.
+static bool bq_use_cta(int n) {
+    if (n != 128 && n != 256 && n != 512) return false;
+    const char *e = getenv("MGAR_FPS_BQ");
+    return !(e && e[0] == 'w');
+}
+
 extern "C" int mgar_fps_ball_query_supported(int b, int n, int m, int nsample) {
-    if (b < 4 * kNumSMs || m < 1 || nsample < 1 || nsample > 64 || getenv("MGAR_NO_FPS_BQ")) return 0;
+    if (b < 1 || m < 1 || nsample < 1 || nsample > 64 || getenv("MGAR_NO_FPS_BQ")) return 0;
+    if (bq_use_cta(n)) return (size_t)n * 16 + (size_t)m * 4 + 8 * 2 * (size_t)nsample * 4 <= 200 * 1024;
+    if (b < 4 * kNumSMs) return 0;
     return n == 32 || n == 64 || n == 128 || n == 256 || n == 512;
+}
+
+extern "C" size_t mgar_fps_ball_query_workspace_bytes(int b) { return b > 0 ? (size_t)b * sizeof(int) : 0; }
+
+template <int W, int PPL>
+static int launch_bq_cta(int b, int m, const float *xyz, int xs, float radius, int K, int *fps_idx, float *new_xyz,
+                         int *ball_idx, const int *order, int *live_cnt, int dup_rows, cudaStream_t st) {
+    size_t sm = (size_t)(32 * W * PPL) * sizeof(float4) + (size_t)m * sizeof(int) + (size_t)W * 2 * K * sizeof(int);
+    // Resident CTAs per SM are CAPPED (by asking for more shared memory than the CTA uses): every resident warp gets an
+    // equal share of the issue slots, so a cloud's round lasts (resident warps per scheduler) x (its instructions), and
+    // the step lasts as long as the longest cloud's 512 rounds.  Enough warps to keep the schedulers busy, no more.
+    int ctas_per_sm = 16 / W;                                  // 4 warps per scheduler
+    if (const char *e = getenv("MGAR_FPS_BQ_CTAS")) { const int v = atoi(e); if (v >= 1 && v <= 32) ctas_per_sm = v; }
+    const size_t cap = ((size_t)227 * 1024) / ctas_per_sm - 1024;   // 1 KB per CTA is reserved by the driver
+    if (b > kNumSMs * ctas_per_sm && cap > sm) sm = cap & ~(size_t)127;
+    if (sm > 48 * 1024)
+        MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<W, PPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    fps_bq_cta_kernel<W, PPL><<<b, W * 32, sm, st>>>(xyz, xs, fps_idx, new_xyz, ball_idx, radius, K, b, m, order, live_cnt, dup_rows);
+    count_launch();
+    return check_launch("fps_ball_query(cta)");
 }
 
 extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xyz_stride, float radius, int nsample,
                                    int *fps_idx, float *new_xyz, int *ball_idx, int *live_cnt, int write_dup_rows,
-                                   void *stream) {
+                                   const int *cloud_weight, void *workspace, size_t workspace_bytes, void *stream) {
     MGAR_REQUIRE(mgar_fps_ball_query_supported(b, n, m, nsample), "fps_ball_query: unsupported shape b=%d n=%d m=%d nsample=%d "
                  "(ask mgar_fps_ball_query_supported first)", b, n, m, nsample);
     MGAR_REQUIRE(xyz && fps_idx && new_xyz && ball_idx, "fps_ball_query: null pointer");
     MGAR_REQUIRE(xyz_stride >= 3, "fps_ball_query: xyz_stride must be >= 3");
     cudaStream_t st = (cudaStream_t)stream;
+    if (bq_use_cta(n)) {
+        const int *order = nullptr;
+        if (cloud_weight && b > kNumSMs) {          // longest clouds first (with <= one CTA per SM the order is moot)
+            if (!workspace || workspace_bytes < mgar_fps_ball_query_workspace_bytes(b)) {
+                set_error("fps_ball_query: cloud_weight needs a workspace of mgar_fps_ball_query_workspace_bytes(b) = %zu bytes",
+                          mgar_fps_ball_query_workspace_bytes(b));
+                return MGAR_ENOMEM;
+            }
+            order_clouds_kernel<<<1, 1024, 0, st>>>(cloud_weight, b, static_cast<int *>(workspace));
+            count_launch();
+            if (int rc = check_launch("fps_ball_query(order)")) return rc;
+            order = static_cast<const int *>(workspace);
+        }
+        int W = 2, PPL = n / 64;       // see fps_bq_cta.cuh: the kernel is ALU-issue bound, two warps per cloud cost the least
+        if (const char *e = getenv("MGAR_FPS_BQ_GEOM")) {
+            int w = 0, p = 0;
+            if (sscanf(e, "%d,%d", &w, &p) == 2 && 32 * w * p == n) { W = w; PPL = p; }
+        }
+#define MGAR_BQ_CTA(w, p)                                                                                               \
+    if (W == w && PPL == p)                                                                                             \
+        return launch_bq_cta<w, p>(b, m, xyz, xyz_stride, radius, nsample, fps_idx, new_xyz, ball_idx, order, live_cnt, \
+                                   write_dup_rows, st);
+        MGAR_BQ_CTA(4, 4) MGAR_BQ_CTA(2, 8) MGAR_BQ_CTA(8, 2) MGAR_BQ_CTA(4, 2) MGAR_BQ_CTA(2, 4) MGAR_BQ_CTA(8, 1)
+        MGAR_BQ_CTA(4, 1) MGAR_BQ_CTA(2, 2) MGAR_BQ_CTA(1, 4)
+#undef MGAR_BQ_CTA
+        set_error("fps_ball_query: no kernel for W=%d PPL=%d", W, PPL);
+        return MGAR_EINVAL;
+    }
     const int f4 = n + (m + 2 * nsample + 3) / 4;
     const size_t sm = (size_t)kFpsWarpsPerCta * f4 * sizeof(float4);
     MGAR_REQUIRE(sm <= 200 * 1024, "fps_ball_query: m=%d too large for shared memory", m);

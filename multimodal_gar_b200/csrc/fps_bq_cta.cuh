@@ -10,11 +10,17 @@
 //     rounds.  Here a cloud's round is spread over W warps (PPL points per lane): the chain is one distance + a
 //     (PPL-1)-deep max tree + two REDUX + one 8-byte exchange through shared memory and ONE block barrier.
 //   * the ball rows are not emitted inside the round: a round only stores its 32-point hit masks (one STS per warp)
-//     into a shared-memory ring; every kRing rounds the W warps turn the ring into rows - two centroids per warp pass
+//     into a shared-memory ring; every kBqRing rounds the W warps turn the ring into rows - two centroids per warp pass
 //     (half-warp per centroid: 16 lanes = the 16 blocks of a cloud), so the serial append loop and the row store are
 //     off the round's critical path and amortised.
 //   * clouds are taken in the caller's `order` (longest first: the pooled point count is known before the sampling),
 //     so the short clouds fill in behind the long ones instead of the long ones defining a tail.
+//
+// The kernel is bound by the ALU pipe (FSETP / VOTE / FMNMX / SEL issue at half rate; ncu: 71 % ALU-pipe active,
+// "math pipe throttle" the top stall), so the round is written to a minimum of instructions: shared-memory addresses
+// live in registers (explicit ld/st.shared), stores by one lane are predicated instead of branched, the (value, rank)
+// exchange is one 64-bit word per warp.  W = 2, PPL = 8 is the default for 512-point clouds: half the cross-warp
+// overhead of W = 4 per point, while a round's chain stays ~4x shorter than the one-warp kernel's.
 //
 // Tie order (see the header of fps.cu): the winner among equal maxima minimises rank(k) = brev_L(k), L = log2 n.
 // Lane l of warp w holds, in register slot i, the point k = blk * 32 + l of block blk = brev_NB(w * PPL + i)
@@ -29,13 +35,56 @@
 
 namespace mgar {
 
-constexpr int kBqRing = 8;      // rounds per emission batch (2 centroids per warp pass: W = 4 -> one pass per batch)
+constexpr int kBqRing = 8;      // rounds per emission batch (2 centroids per warp pass)
 
 template <int BITS>
 __device__ __forceinline__ int brev_n(int v) { return BITS == 0 ? 0 : (int)(__brev((unsigned)v) >> (32 - BITS)); }
 
 template <int V> struct CtLog2 { static constexpr int v = 1 + CtLog2<V / 2>::v; };
 template <> struct CtLog2<1> { static constexpr int v = 0; };
+
+__device__ __forceinline__ uint32_t bq_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ float4 bq_lds_f4(uint32_t a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void bq_lds_u4(uint32_t a, unsigned (&v)[4]) {
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(a));
+}
+__device__ __forceinline__ void bq_lds_u2(uint32_t a, unsigned (&v)[2]) {
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v[0]), "=r"(v[1]) : "r"(a));
+}
+// stores executed by the lanes whose `on` is non-zero (predicated: no branch, no reconvergence point)
+__device__ __forceinline__ void bq_sts_u2_if(int on, uint32_t a, unsigned x, unsigned y) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %0, 0;\n\t@p st.shared.v2.u32 [%1], {%2, %3};\n\t}" ::"r"(on), "r"(a), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void bq_sts_u4_if(int on, uint32_t a, unsigned x, unsigned y, unsigned z, unsigned w) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %0, 0;\n\t@p st.shared.v4.u32 [%1], {%2, %3, %4, %5};\n\t}" ::"r"(on), "r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+__device__ __forceinline__ void bq_sts_u1_if(int on, uint32_t a, unsigned x) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %0, 0;\n\t@p st.shared.u32 [%1], %2;\n\t}" ::"r"(on), "r"(a), "r"(x) : "memory");
+}
+
+// a value the compiler must keep in a register (it otherwise re-derives shared-memory addresses and lane predicates
+// from S2R / LEA chains in every round, ~20 instructions of a ~140-instruction round)
+__device__ __forceinline__ uint32_t bq_pin(uint32_t v) {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
+    return r;
+}
+
+template <int PPL>
+__device__ __forceinline__ void bq_store_masks(int on, uint32_t a, const unsigned (&hb)[PPL]) {
+    if constexpr (PPL >= 4) {
+#pragma unroll
+        for (int i = 0; i < PPL; i += 4) bq_sts_u4_if(on, a + 4 * i, hb[i], hb[i + 1], hb[i + 2], hb[i + 3]);
+    } else if constexpr (PPL == 2) {
+        bq_sts_u2_if(on, a, hb[0], hb[1]);
+    } else {
+        bq_sts_u1_if(on, a, hb[0]);
+    }
+}
 
 template <int W, int PPL>
 __global__ void __launch_bounds__(W * 32)
@@ -45,8 +94,8 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     constexpr int NBLK = W * PPL, NB = CtLog2<NBLK>::v, n = 32 * NBLK, L = 5 + NB;
     static_assert(NBLK <= 16 && (NBLK & (NBLK - 1)) == 0, "a cloud is at most 16 blocks of 32 points");
     extern __shared__ float4 bq_sm4[];
-    __shared__ unsigned long long s_key[2][W];
-    __shared__ unsigned s_ring[2][kBqRing][16];
+    __shared__ __align__(16) unsigned s_key[2][W > 1 ? W : 2][2];    // per parity and warp: (max distance bits, ~rank)
+    __shared__ __align__(16) unsigned s_ring[2 * kBqRing][16];       // hit masks of the last 16 centroids
     __shared__ int s_row0[64];
     float4 *sp = bq_sm4;                                   // [n] staged cloud
     int *sidx = reinterpret_cast<int *>(sp + n);           // [m] sampled indices
@@ -68,7 +117,12 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     __syncthreads();
 
     const float r2 = __fmul_rn(radius, radius);
-    const int rank0 = (brev_n<5>(lane) << NB) | (w * PPL);
+    const int rank0 = (int)bq_pin((uint32_t)((brev_n<5>(lane) << NB) | (w * PPL)));
+    const int lane0 = (int)bq_pin(lane == 0 ? 1u : 0u), thread0 = (int)bq_pin(tid == 0 ? 1u : 0u);
+    const uint32_t sp_a = bq_pin(bq_smem_u32(sp)), sidx_a = bq_pin(bq_smem_u32(sidx));
+    const uint32_t key_a = bq_pin(bq_smem_u32(&s_key[0][0][0]));
+    const uint32_t key_w = bq_pin(key_a + (uint32_t)w * 8u);
+    const uint32_t ring_a = bq_pin(bq_smem_u32(&s_ring[0][0]) + (uint32_t)(w * PPL * 4));
     float px[PPL], py[PPL], pz[PPL], t[PPL];
 #pragma unroll
     for (int i = 0; i < PPL; i++) {
@@ -80,13 +134,13 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     // ---- rows of the centroids [c_emitted, c_end) from the ring (same batch: c_end - c_emitted <= kBqRing) ----------
     int c_emitted = 0;
     auto emit_batch = [&](int c_end) {
-        const int c0 = c_emitted, buf = (c0 / kBqRing) & 1;
+        const int c0 = c_emitted;
         const int half = lane >> 4, s = lane & 15;
         int *row = rows + (w * 2 + half) * K;
         for (int rr = 2 * w; rr < kBqRing && c0 + rr < c_end; rr += 2 * W) {
             const int c = c0 + rr + half;
             const bool valid = c < c_end;
-            unsigned mask = (valid && s < NBLK) ? s_ring[buf][rr + half][brev_n<NB>(s)] : 0u;
+            unsigned mask = (valid && s < NBLK) ? s_ring[c & (2 * kBqRing - 1)][brev_n<NB>(s)] : 0u;
             const int pc = __popc(mask);
             int incl = pc;
 #pragma unroll
@@ -122,7 +176,7 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     bool done = false;                                    // every point coincides with a sample: index 0 from here on
     if (tid == 0) sidx[0] = 0;
     for (; j < m; j++) {
-        const float4 c = sp[cur];
+        const float4 c = bq_lds_f4(sp_a + (uint32_t)cur * 16u);
         unsigned hb[PPL];
 #pragma unroll
         for (int i = 0; i < PPL; i++) {
@@ -140,21 +194,34 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
         const int vb = __float_as_int(mx);
         const int vmax_w = __reduce_max_sync(0xffffffffu, vb);
         const int rmin_w = __reduce_min_sync(0xffffffffu, vb == vmax_w ? rank0 + slot : INT_MAX);
-        if (lane == 0) {
-            s_key[j & 1][w] = ((unsigned long long)(unsigned)vmax_w << 32) | (unsigned)(~rmin_w);
-            unsigned *dst = &s_ring[((j - 1) / kBqRing) & 1][(j - 1) % kBqRing][w * PPL];
+        bq_store_masks<PPL>(lane0, ring_a + (uint32_t)((j - 1) & (2 * kBqRing - 1)) * 64u, hb);
+        unsigned vmax, nrank;                              // the cloud's maximum and ~(rank of the winner)
+        if constexpr (W == 1) {
+            vmax = (unsigned)vmax_w; nrank = ~(unsigned)rmin_w;
+        } else {
+            const uint32_t ka = key_a + (uint32_t)(j & 1) * (uint32_t)(W * 8);
+            bq_sts_u2_if(lane0, key_w + (uint32_t)(j & 1) * (uint32_t)(W * 8), ~(unsigned)rmin_w, (unsigned)vmax_w);
+            __syncthreads();
+            // (value << 32 | ~rank) as one unsigned 64-bit key per warp: the largest key wins
+            unsigned long long key = 0;
 #pragma unroll
-            for (int i = 0; i < PPL; i++) dst[i] = hb[i];
+            for (int q = 0; q < W; q += 2) {
+                unsigned kk[4];
+                bq_lds_u4(ka + (uint32_t)q * 8u, kk);
+                const unsigned long long k0 = ((unsigned long long)kk[1] << 32) | kk[0];
+                const unsigned long long k1 = ((unsigned long long)kk[3] << 32) | kk[2];
+                const unsigned long long kq = k1 > k0 ? k1 : k0;
+                key = kq > key ? kq : key;
+            }
+            vmax = (unsigned)(key >> 32); nrank = (unsigned)key;
         }
-        __syncthreads();
-        unsigned long long key = s_key[j & 1][0];
-#pragma unroll
-        for (int q = 1; q < W; q++) { const unsigned long long o = s_key[j & 1][q]; key = o > key ? o : key; }
-        const int vmax = (int)(key >> 32);
-        if ((j % kBqRing) == 0 || vmax == 0) emit_batch(j);
+        if (((j & (kBqRing - 1)) == 0) | (vmax == 0)) {
+            if constexpr (W == 1) __syncwarp();
+            emit_batch(j);
+        }
         if (vmax == 0) { done = true; break; }
-        cur = brev_n<L>((int)~(unsigned)key);
-        if (tid == 0) sidx[j] = cur;
+        cur = brev_n<L>((int)~nrank);
+        bq_sts_u1_if(thread0, sidx_a + (uint32_t)j * 4u, (unsigned)cur);
     }
     if (!done) {                                         // the last sample has had no round of its own
         const float4 c = sp[cur];
@@ -162,11 +229,7 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
 #pragma unroll
         for (int i = 0; i < PPL; i++)
             hb[i] = __ballot_sync(0xffffffffu, sqdist(__fsub_rn(px[i], c.x), __fsub_rn(py[i], c.y), __fsub_rn(pz[i], c.z)) < r2);
-        if (lane == 0) {
-            unsigned *dst = &s_ring[((m - 1) / kBqRing) & 1][(m - 1) % kBqRing][w * PPL];
-#pragma unroll
-            for (int i = 0; i < PPL; i++) dst[i] = hb[i];
-        }
+        bq_store_masks<PPL>(lane0, ring_a + (uint32_t)((m - 1) & (2 * kBqRing - 1)) * 64u, hb);
         __syncthreads();
         emit_batch(m);
     }
@@ -180,10 +243,9 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
         __syncthreads();
     }
     for (int q = tid; q < m; q += W * 32) idxs[q] = sidx[q];
-    for (int e = tid; e < m * 3; e += W * 32) {
-        const int q = e / 3, cc = e - q * 3;
+    for (int q = tid; q < m; q += W * 32) {
         const float4 v = sp[sidx[q]];
-        new_xyz[e] = cc == 0 ? v.x : (cc == 1 ? v.y : v.z);
+        new_xyz[q * 3 + 0] = v.x; new_xyz[q * 3 + 1] = v.y; new_xyz[q * 3 + 2] = v.z;
     }
     // number of DISTINCT samples: centroids live .. m-1 repeat centroid 0 (same ball, same features)
     if (live_cnt && tid == 0) live_cnt[cloud] = done ? j : m;

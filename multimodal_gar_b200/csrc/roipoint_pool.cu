@@ -28,10 +28,13 @@ struct PoolBox {
 __device__ __forceinline__ void pool_emit(const float *__restrict__ xyz, const float *__restrict__ feat,
                                           float *__restrict__ pooled, int *__restrict__ empty, int *__restrict__ pts_idx,
                                           const int *flist, int total, size_t bm, int S, int C, int canonical,
-                                          const BoxP &bp) {
+                                          const BoxP &bp, int *__restrict__ cnt = nullptr) {
     const int D = 3 + C;
     float *out = pooled + bm * (size_t)S * D;
-    if (threadIdx.x == 0) empty[bm] = total == 0 ? 1 : 0;
+    if (threadIdx.x == 0) {
+        empty[bm] = total == 0 ? 1 : 0;
+        if (cnt) cnt[bm] = total;              // distinct pooled points (<= S): slots beyond it repeat them
+    }
     if (total == 0) {
         for (size_t i = threadIdx.x; i < (size_t)S * D; i += blockDim.x) out[i] = 0.f;
         if (pts_idx)
@@ -343,7 +346,7 @@ box_mask_grid_kernel(const float *__restrict__ boxes, const float *__restrict__ 
 __global__ void __launch_bounds__(256)
 pool_from_mask_kernel(const float *__restrict__ xyz, const float *__restrict__ boxes, const float *__restrict__ feat,
                       const unsigned *__restrict__ mask, float *__restrict__ pooled, int *__restrict__ empty,
-                      int *__restrict__ pts_idx, int N, int M, int W, int S, int C, int canonical) {
+                      int *__restrict__ pts_idx, int *__restrict__ cnt_out, int N, int M, int W, int S, int C, int canonical) {
     extern __shared__ int smem_i[];
     int *flist = smem_i;                  // [S]
     __shared__ int wsum[8];
@@ -382,7 +385,7 @@ pool_from_mask_kernel(const float *__restrict__ xyz, const float *__restrict__ b
     }
     __syncthreads();
     const int total = min(s_total, S);
-    pool_emit(xyz, feat, pooled, empty, pts_idx, flist, total, bm, S, C, canonical, sb);
+    pool_emit(xyz, feat, pooled, empty, pts_idx, flist, total, bm, S, C, canonical, sb, cnt_out);
 }
 
 }  // namespace mgar
@@ -452,8 +455,8 @@ extern "C" int mgar_box_masks(const float *boxes_first, const float *boxes_pool,
 }
 
 extern "C" int mgar_roipoint_pool_from_masks(const float *xyz, const float *boxes, const float *feat, const unsigned *mask,
-                                             float *pooled, int *empty, int *pts_idx, int B, int N, int M, int S, int C,
-                                             int canonical, void *stream) {
+                                             float *pooled, int *empty, int *pts_idx, int *pooled_cnt, int B, int N, int M,
+                                             int S, int C, int canonical, void *stream) {
     MGAR_REQUIRE(B >= 0 && N >= 0 && M >= 0 && S >= 0 && C >= 0, "roipoint_pool_from_masks: negative size");
     if (B == 0 || M == 0) return MGAR_OK;
     MGAR_REQUIRE(pooled && empty && boxes && mask && (xyz || N == 0) && (feat || C == 0 || N == 0), "roipoint_pool_from_masks: null pointer");
@@ -462,7 +465,7 @@ extern "C" int mgar_roipoint_pool_from_masks(const float *xyz, const float *boxe
     MGAR_REQUIRE(smem <= 200 * 1024, "roipoint_pool_from_masks: num_sampled_points=%d does not fit in shared memory", S);
     if (smem > 48 * 1024) MGAR_CUDA(cudaFuncSetAttribute(pool_from_mask_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(M, B);
-    pool_from_mask_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(xyz, boxes, feat, mask, pooled, empty, pts_idx, N, M,
+    pool_from_mask_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(xyz, boxes, feat, mask, pooled, empty, pts_idx, pooled_cnt, N, M,
                                                                      (N + 31) / 32, S, C, canonical);
     count_launch();
     return check_launch("roipoint_pool_from_masks");

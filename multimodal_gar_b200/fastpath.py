@@ -32,13 +32,15 @@ def fps_gather(xyz, npoint):
     return idx, new_xyz
 
 
-def fps_ball_query(xyz, npoint, radius, nsample, all_rows=True):
+def fps_ball_query(xyz, npoint, radius, nsample, all_rows=True, cloud_weight=None):
     """FPS + ball query around the sampled points in one kernel, for many equally sized power-of-two clouds.
     xyz (b,n,3) (column view of a (b,n,3+C) array allowed) -> (idx (b,npoint) int32, new_xyz (b,npoint,3),
     ball_idx (b*npoint,nsample) int32, live_cnt (b) int32) - the results of fps_gather + ball_query_uniform, plus the
     number of distinct samples per cloud (the centroids behind it repeat centroid 0) - or None when the shape is
     not covered (the caller then runs the two kernels).  all_rows=False: the ball rows of the repeated centroids are
-    not written (only up to the next multiple of four) - for the consumer that walks the distinct centroids."""
+    not written (only up to the next multiple of four) - for the consumer that walks the distinct centroids.
+    cloud_weight (b) int32: distinct points per cloud (roipoint_pool_from_masks' count) - schedules the long clouds
+    first; results do not depend on it."""
     b, n = xyz.shape[0], xyz.shape[1]
     L = _lib.lib()
     if not L.mgar_fps_ball_query_supported(b, n, int(npoint), int(nsample)):
@@ -50,9 +52,16 @@ def fps_ball_query(xyz, npoint, radius, nsample, all_rows=True):
     new_xyz = torch.empty((b, npoint, 3), dtype=torch.float32, device=xyz.device)
     ball_idx = torch.empty((b * npoint, nsample), dtype=torch.int32, device=xyz.device)
     live_cnt = torch.empty((b,), dtype=torch.int32, device=xyz.device)
+    ws = ws_bytes = None
+    if cloud_weight is not None:
+        need_cuda(cloud_weight=cloud_weight)
+        need_dtype(torch.int32, cloud_weight=cloud_weight)
+        ws_bytes = int(L.mgar_fps_ball_query_workspace_bytes(b))
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz.device)
     with on_device(xyz):
         _lib.check(L.mgar_fps_ball_query(b, n, int(npoint), ptr(xyz), xs, float(radius), int(nsample), ptr(idx), ptr(new_xyz),
-                                         ptr(ball_idx), ptr(live_cnt), 1 if all_rows else 0, stream_of(xyz)), "fps_ball_query")
+                                         ptr(ball_idx), ptr(live_cnt), 1 if all_rows else 0, ptr(cloud_weight), ptr(ws),
+                                         ws_bytes or 0, stream_of(xyz)), "fps_ball_query")
     return idx, new_xyz, ball_idx, live_cnt
 
 
@@ -89,15 +98,16 @@ def box_masks(points, boxes, pool_boxes=None, want_box_idx=True):
     return box_idx, mask
 
 
-def roipoint_pool_from_masks(points, point_features, pool_boxes, mask, num_sampled_points, canonical=True):
+def roipoint_pool_from_masks(points, point_features, pool_boxes, mask, num_sampled_points, canonical=True, want_cnt=False):
     """-> pooled (B,M,S,3+C) (canonical frame of each box when `canonical`), empty (B,M) int32; same result as
-    roipoint_pool3d_cuda.forward on the same (enlarged) boxes."""
+    roipoint_pool3d_cuda.forward on the same (enlarged) boxes.  want_cnt: also (B,M) int32 min(in-box points, S)."""
     need_cuda(points=points, point_features=point_features, pool_boxes=pool_boxes, mask=mask)
     B, N, M, C, S = points.shape[0], points.shape[1], pool_boxes.shape[1], point_features.shape[2], int(num_sampled_points)
     pooled = torch.empty((B, M, S, 3 + C), dtype=torch.float32, device=points.device)
     empty = torch.empty((B, M), dtype=torch.int32, device=points.device)
+    cnt = torch.empty((B, M), dtype=torch.int32, device=points.device) if want_cnt else None
     with on_device(points):
         _lib.check(_lib.lib().mgar_roipoint_pool_from_masks(ptr(points), ptr(pool_boxes), ptr(point_features), ptr(mask),
-                                                            ptr(pooled), ptr(empty), 0, B, N, M, S, C, 1 if canonical else 0,
-                                                            stream_of(points)), "roipoint_pool_from_masks")
-    return pooled, empty
+                                                            ptr(pooled), ptr(empty), 0, ptr(cnt), B, N, M, S, C,
+                                                            1 if canonical else 0, stream_of(points)), "roipoint_pool_from_masks")
+    return (pooled, empty, cnt) if want_cnt else (pooled, empty)

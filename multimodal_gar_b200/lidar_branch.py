@@ -101,8 +101,8 @@ class PointPersonEncoder(nn.Module):
             big = boxes if same else box_utils.enlarge_box3d(boxes.reshape(-1, 7), self.pool_extra_width).view(B, M, 7).contiguous()
             box_idx, mask = fastpath.box_masks(points.contiguous(), boxes.contiguous(), None if same else big)
             mark('points_in_boxes')
-            pooled, empty = fastpath.roipoint_pool_from_masks(points.contiguous(), point_features.contiguous(), big.contiguous(),
-                                                              mask, S)
+            pooled, empty, pooled_cnt = fastpath.roipoint_pool_from_masks(points.contiguous(), point_features.contiguous(),
+                                                                          big.contiguous(), mask, S, want_cnt=True)
             pooled = pooled.view(B * M, S, 3 + C)
             mark('roipoint_pool')
         else:
@@ -110,6 +110,7 @@ class PointPersonEncoder(nn.Module):
             mark('points_in_boxes')
             pooled, empty = self.pool(points, point_features, boxes)                # (B*M,S,3+C) canonical frame
             mark('roipoint_pool')
+            pooled_cnt = None
         g = self.sa.groupers[0]
         ball_idx = live_cnt = None
         packed = None if (self.training or torch.is_grad_enabled()) else self.sa._pack(pooled.device)[0]
@@ -121,7 +122,8 @@ class PointPersonEncoder(nn.Module):
             # distinct-centroid walk: pooled clouds repeat their points, the sampling kernel reports how many distinct
             # samples each person has and the MLP computes only those (the others repeat centroid 0: same max)
             walk = self.skip_empty_persons and self.skip_repeated_centroids and not want_out
-            fused = fastpath.fps_ball_query(pooled[:, :, 0:3], P, g.radius, g.nsample, all_rows=not walk)
+            fused = fastpath.fps_ball_query(pooled[:, :, 0:3], P, g.radius, g.nsample, all_rows=not walk,
+                                            cloud_weight=None if pooled_cnt is None else pooled_cnt.view(-1))
             if fused is not None:                  # sampling and ball query share their distances: one kernel
                 fps_idx, new_xyz, ball_idx, live_cnt = fused
                 new_xyz = new_xyz.view(B * M * P, 3)

@@ -1,5 +1,5 @@
 """-m gpu: THE step bench.py times - 64 configs[1] frames through PointPersonEncoder with its defaults - pinned end
-to end: (a) it really runs the five-kernel path (box-mask grid, pool-from-mask, fused FPS + ball query, live-tile
+to end: (a) it really runs the six-kernel path (box-mask grid, pool-from-mask, cloud order, fused FPS + ball query, live-tile
 list, tcgen05 MLP walking the distinct centroids), (b) its person features are the bits of the all-rows path
 (every ball row written, every centroid through the MLP), (c) every index / pooled value of that batch equals the
 UNMODIFIED reference CUDA extensions (oracle/_ref) on the same GPU, bit for bit, and (d) sampled persons agree with the
@@ -36,8 +36,8 @@ def step(cuda):
     return dict(enc=enc, xyz=xyz, feat=feat, bx=bx, person=person, launches=launches, st=st)
 
 
-def test_default_step_is_the_five_kernel_path_and_matches_the_all_rows_path(step):
-    assert step["launches"] == 5, "expected box masks, pool, FPS+ball query, live tiles, MLP; got %d launches" % step["launches"]
+def test_default_step_is_the_six_kernel_path_and_matches_the_all_rows_path(step):
+    assert step["launches"] == 6, "expected box masks, pool, cloud order, FPS+ball query, live tiles, MLP; got %d launches" % step["launches"]
     assert step["person"].shape == (F, bench.CFG["M"], 128)
     assert torch.equal(step["person"], step["st"]["person_features"])
     sa = step["st"]["sa_features"].view(F * bench.CFG["M"], bench.CFG["P"], 128)

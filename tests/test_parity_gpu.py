@@ -449,4 +449,48 @@ def test_fused_fps_ball_query_equals_the_two_kernels(cuda, n, m, K, radius):
     f3 = fastpath.fps_ball_query(T(c, cuda), m, radius, K)
     assert all(torch.equal(a, b_) for a, b_ in zip(f3, fused))
     assert fastpath.fps_ball_query(T(c[:, :n - 1], cuda), m, radius, K) is None
-    assert fastpath.fps_ball_query(T(c[:100], cuda), m, radius, K) is None
+    few = fastpath.fps_ball_query(T(c[:100], cuda), m, radius, K)
+    if n >= 128:        # a CTA per cloud: any number of clouds
+        assert torch.equal(few[0], idx[:100]) and torch.equal(few[2], ball[:100 * m])
+    else:               # a warp per cloud: a throughput kernel, >= 592 clouds
+        assert few is None
+    # live_cnt = number of distinct samples: the indices behind it are 0, the ones before it distinct
+    lc = fused[3].cpu().numpy()
+    f_np = fused[0].cpu().numpy()
+    for g in range(0, b, 23):
+        assert 1 <= lc[g] <= m and (f_np[g, lc[g]:] == 0).all() and len(set(f_np[g, :lc[g]].tolist())) == lc[g]
+
+
+@pytest.mark.parametrize("n,geom", [(512, "4,4"), (512, "2,8"), (512, "8,2"), (256, "4,2"), (256, "2,4"), (256, "8,1"),
+                                    (128, "4,1"), (128, "2,2"), (128, "1,4"), (512, "warp")])
+def test_fused_fps_ball_query_geometries_schedule_and_partial_rows(cuda, monkeypatch, n, geom):
+    """Every CTA geometry of the fused kernel (and the warp-per-cloud kernel) writes the same bits; scheduling the clouds
+    by weight changes nothing; with all_rows=False the rows of the distinct centroids (rounded up to four) are the same
+    and the sampled indices / coordinates are complete."""
+    from multimodal_gar_b200 import fastpath
+    b, m, K, radius = 640, n, 32, 0.35
+    c = cases.cloud_with_ties(n + 3, b, n)
+    rng = np.random.default_rng(n)
+    c[::2] = rng.uniform(-1, 1, c[::2].shape).astype(np.float32)
+    for g in range(1, b, 4):                                                     # wrapped clouds with few distinct points
+        k = int(rng.integers(1, n // 2))
+        c[g] = c[g][np.arange(n) % k]
+    x = T(c, cuda)
+    monkeypatch.delenv("MGAR_FPS_BQ", raising=False)
+    monkeypatch.delenv("MGAR_FPS_BQ_GEOM", raising=False)
+    idx, new_xyz = fastpath.fps_gather(x, m)
+    ball = fastpath.ball_query_uniform(radius, K, x.view(b * n, 3), new_xyz.view(b * m, 3), n, m)
+    if geom == "warp":
+        monkeypatch.setenv("MGAR_FPS_BQ", "warp")
+    else:
+        monkeypatch.setenv("MGAR_FPS_BQ_GEOM", geom)
+    weight = T(rng.integers(0, 600, b).astype(np.int32), cuda)
+    full = fastpath.fps_ball_query(x, m, radius, K, cloud_weight=weight)
+    assert torch.equal(full[0], idx) and torch.equal(full[1], new_xyz) and torch.equal(full[2], ball)
+    part = fastpath.fps_ball_query(x, m, radius, K, all_rows=False)
+    assert torch.equal(part[0], idx) and torch.equal(part[1], new_xyz) and torch.equal(part[3], full[3])
+    lc = full[3].cpu().numpy()
+    rows = np.arange(m)[None, :] < ((lc + 3) // 4 * 4)[:, None]
+    sel = torch.from_numpy(rows.reshape(-1)).to(cuda)
+    assert torch.equal(part[2][sel], ball[sel])
+    assert (lc[1::4] < n // 2).all() and (lc[0::2] == m).all()
