@@ -604,9 +604,11 @@ static int launch_bq_cta(int b, int m, const float *xyz, int xs, float radius, i
                          int *ball_idx, const int *order, int *live_cnt, int dup_rows, cudaStream_t st) {
     size_t sm = (size_t)(32 * W * PPL) * sizeof(float4) + (size_t)m * sizeof(int) + (size_t)W * 2 * K * sizeof(int);
     // Resident CTAs per SM are CAPPED (by asking for more shared memory than the CTA uses): every resident warp gets an
-    // equal share of the issue slots, so a cloud's round lasts (resident warps per scheduler) x (its instructions), and
-    // the step lasts as long as the longest cloud's 512 rounds.  Enough warps to keep the schedulers busy, no more.
-    int ctas_per_sm = 16 / W;                                  // 4 warps per scheduler
+    // equal share of the issue slots, so a cloud's round lasts (resident warps per scheduler) x (its instructions) and the
+    // step lasts at least as long as the longest cloud's 512 rounds; too few warps leave the schedulers idle instead.
+    // Measured on the bench step (profiles/r02_fps_bq_sweep.txt): W=2: 4 / 6 / 8 / 10 / 14 CTAs per SM -> 0.55 / 0.38 /
+    // 0.311 / 0.311 / 0.313 ms; W=4: 2 / 3 / 4 / 6 / 10 -> 0.95 / 0.54 / 0.41 / 0.33 / 0.314 ms.
+    int ctas_per_sm = 20 / W;                                  // 5 warps per scheduler
     if (const char *e = getenv("MGAR_FPS_BQ_CTAS")) { const int v = atoi(e); if (v >= 1 && v <= 32) ctas_per_sm = v; }
     const size_t cap = ((size_t)227 * 1024) / ctas_per_sm - 1024;   // 1 KB per CTA is reserved by the driver
     if (b > kNumSMs * ctas_per_sm && cap > sm) sm = cap & ~(size_t)127;
