@@ -8,6 +8,13 @@ A step = one pass of the hot path over `frames_per_step` synthetic JRDB-shaped f
 BASELINE.json configs[1] (65 536 points, 40 person boxes, S=512, P=512, r=0.3, K=32, MLP 4-64-128).
 Rank 0 prints ONE JSON line.  Frames are independent: every rank runs its own frames (weak scaling),
 no collective in the data path; timing is CUDA events, max over ranks.
+
+Besides the contract keys (value, e2e, roofline, cpu_baseline, clocks, gpu_launches) the line carries, each in its own
+block: `steady_state` (the same step for >= 5 s with clock / power samples), `configs` (configs[2] = 64 frames x 80
+persons + DAFM, strong-scaled 64/W frames per rank beside the weak number; configs[4] = the 250k x 200 stress at
+three radius / nsample points; configs[0] = the CPU case with the reference's own points_in_boxes_cpu), `train`
+(configs[3]'s share of the hot path: forward + backward + Adam under DistributedDataParallel, all-reduce size and
+exposed communication) and `reference_gpu` (the reference's own CUDA extensions on the same GPU).  --quick skips them.
 """
 import argparse
 import json
@@ -24,6 +31,13 @@ if ROOT not in sys.path:
 
 CFG = dict(N=65536, M=40, S=512, P=512, radius=0.3, K=32, C_in=1, mlp=(64, 128))
 METRIC = "JRDB-size LiDAR frames/s (box-pool+FPS+ballquery+group+MLP)"
+WORKLOAD = "configs[1]: 65536 pts x 40 boxes, S=512 P=512 r=0.3 K=32 MLP 4-64-128"
+
+
+def bench_config(F, world):
+    """The `config` object of the JSON line - the SAME for the native and the reference arm."""
+    return dict(workload=WORKLOAD, frames_per_step=F * world, frames_per_step_per_gpu=F,
+                l2="two alternating input batches (2 x %d MB) + ~%d MB of stage outputs per step > 126 MB L2" % (F, 4 * F))
 
 
 def algorithmic_bytes_per_frame(c=CFG, keep_sa=True):
@@ -48,6 +62,9 @@ def parse_args():
     ap.add_argument("--frames-per-step", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames in the cpu_baseline sample (0: auto)")
+    ap.add_argument("--quick", action="store_true", help="value + e2e only (no steady_state / configs / train / reference_gpu)")
+    ap.add_argument("--steady-seconds", type=float, default=5.0)
+    ap.add_argument("--train-frames", type=int, default=2, help="frames per rank in the training step")
     return ap.parse_args()
 
 
@@ -60,15 +77,15 @@ def peaks():
     return dict(hbm=6650.0, bf16=1590.0, bf16_sustained=1400.0, source="fallback (B200_PROFILING.md)")
 
 
-def ncu_traffic(stage, F):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the stage's kernel for one launch, from the committed
-    `ncu --set full` capture of this same command (64 frames per launch); None when no capture matches."""
-    path = os.path.join(ROOT, "profiles", "r01_traffic.json")
+def ncu_profile(F):
+    """Per-kernel numbers of the committed `ncu --set full` capture of this same command (profiles/r02_traffic.json,
+    written by scripts/ncu_to_json.py): dram bytes per launch, pipe activity.  {} when no capture matches."""
+    path = os.path.join(ROOT, "profiles", "r02_traffic.json")
     try:
         t = json.load(open(path))
-        return t["bytes_per_launch"][stage] if t.get("frames_per_step") == F else None
-    except (OSError, KeyError, ValueError):
-        return None
+        return t if t.get("frames_per_step") == F else {}
+    except (OSError, ValueError):
+        return {}
 
 
 class ClockSampler:
@@ -98,7 +115,7 @@ class ClockSampler:
         except subprocess.TimeoutExpired:
             self.p.kill()
         self.f.seek(0)
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.f.read().splitlines():
             parts = [x.strip() for x in line.split(",")]
@@ -109,13 +126,19 @@ class ClockSampler:
                 mx.append(float(parts[1]))
             except ValueError:
                 continue
+            try:
+                pw.append(float(parts[2]))
+            except ValueError:
+                pass
             for nm, v in zip(names, parts[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(nm)
         self.f.close()
         os.unlink(self.f.name)
         if sm:
-            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+            out.update(sm_mhz=statistics.median(sm), sm_min_mhz=min(sm), sm_max_mhz=max(mx), reasons=sorted(reasons),
+                       samples=len(sm), power_w_median=statistics.median(pw) if pw else None,
+                       power_w_max=max(pw) if pw else None)
         return out
 
 
@@ -183,6 +206,10 @@ def cpu_frame(args):
     return float(person.sum()), (t1 - t0, t2 - t1, t3 - t2, t4 - t3, t5 - t4)
 
 
+def cpu_frames(jobs):
+    return [cpu_frame(j) for j in jobs]
+
+
 def usable_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -206,6 +233,55 @@ def cpu_baseline_inline(frames, n_frames):
                 stage_seconds_per_frame={k: round(v / n_frames, 4) for k, v in zip(names, stage)})
 
 
+def config0_block(frame, dev=None):
+    """BASELINE configs[0] - the reference's own CPU-runnable case: points_in_boxes_cpu + per-person roipoint pooling on
+    one 65 536 x 40 frame.  (i) the REFERENCE's compiled points_in_boxes_cpu (roiaware_pool3d.cpp:143-168, in
+    oracle/_ref/roiaware_pool3d_cuda.so, single thread by construction), (ii) the oracle's per-person pooling on the host,
+    (iii) the same (M,N) matrix through this library's host-buffer entry (mgar_points_in_boxes_mask_host: GPU compute,
+    H2D + D2H inside the call)."""
+    import numpy as np
+    import torch
+    from oracle import oracle as O
+    xyz, feat, boxes = frame
+    out = dict(workload="configs[0]: points_in_boxes_cpu + per-person roipoint pooling, 65536 pts x 40 boxes, one frame",
+               host_cores=usable_cores())
+    ref = O.load_ref("roiaware_pool3d_cuda")
+    tx, tb = torch.from_numpy(np.ascontiguousarray(xyz)), torch.from_numpy(np.ascontiguousarray(boxes))
+    want = None
+    if ref is not None:
+        m = torch.zeros((boxes.shape[0], xyz.shape[0]), dtype=torch.int32)
+        ref.points_in_boxes_cpu(tb, tx, m)
+        ts = []
+        for _ in range(5):
+            m.zero_()
+            t0 = time.perf_counter()
+            ref.points_in_boxes_cpu(tb, tx, m)
+            ts.append(time.perf_counter() - t0)
+        want = m
+        out["ref_points_in_boxes_cpu_ms"] = round(1e3 * statistics.median(ts), 3)
+        out["ref_points_in_boxes_cpu"] = "the reference's own compiled function (oracle/_ref), 1 thread, median of 5"
+    else:
+        out["ref_points_in_boxes_cpu_ms"] = None
+        out["ref_points_in_boxes_cpu"] = "oracle/_ref/roiaware_pool3d_cuda.so not present on this box"
+    O.lib()
+    t0 = time.perf_counter()
+    O.roipoint_pool3d(xyz[None], feat[None], boxes[None], (0.0, 0.0, 0.0), CFG["S"])
+    out["oracle_roipoint_pool_ms"] = round(1e3 * (time.perf_counter() - t0), 3)
+    if dev is not None:
+        from multimodal_gar_b200.pcdet.ops.roiaware_pool3d import roiaware_pool3d_cuda as new_roiaware
+        got = torch.zeros((boxes.shape[0], xyz.shape[0]), dtype=torch.int32)
+        new_roiaware.points_in_boxes_cpu(tb, tx, got)
+        ts = []
+        for _ in range(5):
+            t0 = time.perf_counter()
+            new_roiaware.points_in_boxes_cpu(tb, tx, got)
+            ts.append(time.perf_counter() - t0)
+        out["native_points_in_boxes_host_ms"] = round(1e3 * statistics.median(ts), 3)
+        if want is not None:
+            out["native_equals_reference"] = bool(torch.equal(got, want))
+    return out
+
+
 # ---- reference arm: the path on the box's host cores, all the threads it can use -----------------
 def run_reference(args, rank, world):
     if rank != 0:
@@ -213,25 +289,32 @@ def run_reference(args, rank, world):
     from concurrent.futures import ProcessPoolExecutor
     import multiprocessing as mp
     cores = usable_cores()
-    workers = max(1, min(cores, 32))                  # one frame per worker, 1 thread each; bounded memory
-    frames = make_frames(workers)
-    jobs = [(frames[0][i], frames[1][i], frames[2][i]) for i in range(workers)]
+    workers = max(1, min(cores, 32))                  # one frame per worker at a time, 1 thread each; bounded memory
+    F = args.frames_per_step
+    sample = max(workers, 16)                         # frames actually run per step: a bounded sample of the workload
+    sample = min(sample, F * world)
+    frames = make_frames(min(sample, 16))
+    nb = frames[0].shape[0]
+    jobs = [(frames[0][i % nb], frames[1][i % nb], frames[2][i % nb]) for i in range(sample)]
+    chunks = [jobs[i::workers] for i in range(workers) if jobs[i::workers]]
     with ProcessPoolExecutor(workers, mp_context=mp.get_context("spawn"), initializer=_cpu_init, initargs=(1,)) as ex:
-        for _ in range(max(1, args.warmup)):          # also starts the workers (imports torch in each)
-            list(ex.map(cpu_frame, jobs))
+        for _ in range(max(1, min(args.warmup, 2))):  # also starts the workers (imports torch in each)
+            list(ex.map(cpu_frames, chunks))
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            list(ex.map(cpu_frame, jobs))
+            list(ex.map(cpu_frames, chunks))
         dt = time.perf_counter() - t0
-    value = workers * args.steps / dt
-    sample = "%d frames per step (one per worker process, 1 thread each), oracle C port + torch-CPU shared MLP" % workers
+    value = sample * args.steps / dt
+    txt = ("%d of the step's %d frames per timed step (a bounded sample; frames are independent, value is frames/s), "
+           "%d worker processes x 1 thread, oracle C port + torch-CPU shared MLP" % (sample, F * world, workers))
     line = dict(metric=METRIC, value=value, unit="frames/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
-                ms_per_step=1e3 * dt / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
-                dtype="f32", data="synthetic", impl="reference",
-                config=dict(workload="configs[1]: 65536 pts x 40 boxes, S=512 P=512 r=0.3 K=32 MLP 4-64-128",
-                            frames_per_step=workers),
-                cpu_baseline=dict(value=value, unit="frames/s", cores=workers, kind="port", sample=sample,
-                                  host_cores=cores),
+                ms_per_step=1e3 * F * world / value, higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="f32", data="synthetic", impl="reference", config=bench_config(F, world),
+                cpu_baseline=dict(value=value, unit="frames/s", cores=workers, kind="port", sample=txt,
+                                  host_cores=cores, sample_frames_per_step=sample,
+                                  note="the reference has a CPU implementation only for points_in_boxes_cpu (timed as "
+                                       "configs[0] in the native arm's line); its CUDA kernels cannot run on host cores, "
+                                       "so the other stages are the oracle's C restatement"),
                 e2e=dict(value=value, unit="frames/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line), flush=True)
 
@@ -274,6 +357,265 @@ def build_batches(F, rank, dev):
     return host, devb
 
 
+class Ctx:
+    """Rank plumbing shared by the blocks."""
+
+    def __init__(self, rank, world, local_rank, dev):
+        self.rank, self.world, self.local_rank, self.dev = rank, world, local_rank, dev
+
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+        if self.world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        import torch
+        import torch.distributed as dist
+        if self.world > 1:
+            t = torch.tensor([v], dtype=torch.float64, device=self.dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return v
+
+    def timed(self, fn, iters, warm=2):
+        """ms per call: CUDA events around `iters` calls, barrier + synchronize on both sides, max over ranks."""
+        import torch
+        for _ in range(warm):
+            fn()
+        self.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        self.barrier()
+        return self.max_over_ranks(a.elapsed_time(b)) / iters
+
+
+def block_steady_state(ctx, enc, devb, F, seconds, ms_hint):
+    """The same step back to back for >= `seconds` (about seconds / ms_per_step steps): the burst measurement of `value`
+    lasts ~20 ms and says nothing about clocks or power under sustained load."""
+    import torch
+    steps = max(50, int(seconds * 1e3 / max(ms_hint, 1e-3)))
+    ctx.barrier()
+    sampler = ClockSampler(ctx.local_rank) if ctx.rank == 0 else None
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        a.record()
+        for i in range(steps):
+            enc(*devb[i & 1])
+        b.record()
+    ctx.barrier()
+    wall = time.perf_counter() - t0
+    ms = ctx.max_over_ranks(a.elapsed_time(b))
+    clocks = sampler.stop() if sampler else None
+    return dict(steps=steps, seconds=round(ms * 1e-3, 3), wall_seconds=round(wall, 3), ms_per_step=ms / steps,
+                value=F * ctx.world * steps / (ms * 1e-3), unit="frames/s", clocks=clocks)
+
+
+def block_e2e(ctx, enc, host, F, steps, warmup):
+    """End to end through the public host-buffer API (multimodal_gar_b200.pipeline.HostFramePipeline): every step copies
+    its pinned host inputs to the device, runs the branch and copies the person features back; the three legs run on
+    their own streams.  Also the copies ALONE (same buffers, no kernels): the ceiling the end-to-end number can reach."""
+    import torch
+    from multimodal_gar_b200 import pipeline
+    dev = ctx.dev
+    out_host = [torch.empty((F, CFG["M"], CFG["mlp"][-1]), dtype=torch.float32).pin_memory() for _ in range(3)]
+    pipe = pipeline.HostFramePipeline(enc, dev, depth=3)
+    with torch.no_grad():
+        for i in range(max(3, warmup // 2)):
+            pipe.submit(*host[i & 1], out_host[i % 3])
+        pipe.synchronize()
+        ctx.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            pipe.submit(*host[i & 1], out_host[i % 3])
+        pipe.join()
+        e1.record()
+        pipe.synchronize()
+        ctx.barrier()
+        ms_e2e = ctx.max_over_ranks(e0.elapsed_time(e1))
+    h2d = sum(t.numel() * t.element_size() for t in host[0])
+    d2h = out_host[0].numel() * out_host[0].element_size()
+    # copies alone
+    slots = [[torch.empty_like(t, device=dev) for t in host[0]] for _ in range(2)]
+    s_in = torch.cuda.Stream(dev)
+
+    def copies():
+        with torch.cuda.stream(s_in):
+            for i in range(steps):
+                for d, h in zip(slots[i & 1], host[i & 1]):
+                    d.copy_(h, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(s_in)
+        torch.cuda.current_stream(dev).wait_event(ev)
+    ms_copy = ctx.timed(copies, 1, warm=1)
+    copy_GBps = h2d * steps / (ms_copy * 1e-3) / 1e9
+    e2e_GBps = h2d * steps / (ms_e2e * 1e-3) / 1e9
+    limiter = "h2d copy (PCIe / host memory)" if ms_e2e <= 1.12 * ms_copy else "kernels"
+    return dict(ms=ms_e2e, h2d=h2d, d2h=d2h, extra=dict(
+        ms_per_step=ms_e2e / steps, h2d_GBps_per_gpu=round(e2e_GBps, 2), h2d_only_GBps_per_gpu=round(copy_GBps, 2),
+        h2d_only_GBps_all_gpus=round(copy_GBps * ctx.world, 2), h2d_only_ms_per_step=ms_copy / steps, limiter=limiter,
+        note="h2d_only = the same pinned buffers copied to the device with no kernel running (max over ranks): the "
+             "end-to-end step cannot be shorter than that copy"))
+
+
+def block_config2(ctx, F_total=64, M=80, MNP=100):
+    """BASELINE configs[2]: 64 panoramic frames x 80 persons (zero-padded to 100 proposals), full LiDAR branch + DAFM
+    input path + DistanceAwareFusion forward.  STRONG scaling: rank r takes shard_frames(64, W, r); the weak number
+    (64 frames on every rank) beside it."""
+    import numpy as np
+    import torch
+    from multimodal_gar_b200 import dafm, lidar_backbone as LB, lidar_branch, synthetic
+    dev = ctx.dev
+    base = 16
+    pts, boxes = synthetic.make_batch(1994, base, N=CFG["N"], M=M)
+    idx = np.arange(F_total) % base
+    padded = torch.zeros((F_total, MNP, 7))
+    padded[:, :M] = torch.from_numpy(boxes[idx])
+    points = torch.from_numpy(np.ascontiguousarray(pts[idx]))
+    g = torch.Generator().manual_seed(9)
+    rgb = torch.randn((F_total, MNP, 512), generator=g)
+    bb2 = torch.rand((F_total, MNP, 2), generator=g) * 500
+    bboxes = torch.cat([bb2, bb2 + 20 + 60 * torch.rand((F_total, MNP, 2), generator=g)], dim=-1)
+    pid = torch.full((F_total, MNP), -1, dtype=torch.int64)
+    pid[:, :M] = torch.arange(M)
+    torch.manual_seed(9)
+    net = LB.PointLiDARBackbone().to(dev).eval()
+    fus = dafm.DistanceAwareFusion(512).to(dev).eval()
+    out = dict(workload="configs[2]: %d frames x %d persons (padded to %d proposals), %d points per frame, LiDAR branch + "
+                        "DAFM fusion forward" % (F_total, M, MNP, CFG["N"]))
+
+    def run(lo, hi, tag):
+        t = [x[lo:hi].to(dev) for x in (points, padded, rgb, bboxes, pid)]
+        p_, b3, r_, b2, id_ = t
+        stage = {}
+
+        def whole(marks=None):
+            def mark(n):
+                if marks is not None:
+                    e = torch.cuda.Event(enable_timing=True)
+                    e.record()
+                    marks.append((n, e))
+            mark("start")
+            f = net(dict(points=p_, gt_bboxes3d=b3))
+            mark("lidar_branch")
+            d = LB.dafm_lidar_inputs(f, b3, id_)
+            mark("dafm_inputs")
+            o = fus(r_, d["feature"], b2, b3, d["valid"])
+            mark("dafm_fusion")
+            return o
+        with torch.no_grad():
+            ms = ctx.timed(whole, 8)
+            marks = []
+            for _ in range(4):
+                whole(marks)
+            torch.cuda.synchronize()
+            for (n0, e0), (n1, e1) in zip(marks, marks[1:]):
+                if n1 != "start":
+                    stage[n1] = stage.get(n1, 0.0) + e0.elapsed_time(e1) / 4
+        frames = (hi - lo) if tag == "strong" else (hi - lo) * ctx.world
+        total = F_total if tag == "strong" else frames
+        out[tag] = dict(frames_per_rank=hi - lo, frames_total=total, ms_per_step=round(ms, 4),
+                        value=total / (ms * 1e-3), unit="frames/s", stages_ms_rank0={k: round(v, 4) for k, v in stage.items()})
+    lo, hi = lidar_branch.shard_frames(F_total, ctx.world, ctx.rank)
+    run(lo, hi, "strong")
+    if ctx.world > 1:
+        run(0, F_total, "weak")
+    else:
+        out["weak"] = out["strong"]
+    return out
+
+
+def block_config4(ctx):
+    """BASELINE configs[4]: the crowded-scene stress, one frame of 250 000 points x 200 person boxes, at three points of
+    the ball-query sweep (radius, nsample); per-stage CUDA-event times.  nsample 16 / 64 are outside the tcgen05 kernel's
+    shape (nsample 32): those points run the exact-fp32 CUDA-core MLP kernel - stated per line."""
+    import numpy as np
+    import torch
+    from multimodal_gar_b200 import lidar_branch, synthetic
+    dev = ctx.dev
+    pts, boxes = synthetic.make_batch(5, 1, N=250000, M=200, density_scale=4.0)
+    xyz = torch.from_numpy(np.ascontiguousarray(pts[..., :3])).to(dev)
+    feat = torch.from_numpy(np.ascontiguousarray(pts[..., 3:4])).to(dev)
+    bx = torch.from_numpy(boxes).to(dev)
+    rows = []
+    for r, K in ((0.1, 16), (0.3, 32), (1.0, 64)):
+        torch.manual_seed(1994)
+        enc = lidar_branch.PointPersonEncoder(1, 512, 512, r, K, (64, 128)).to(dev).eval()
+        stage = {}
+        with torch.no_grad():
+            ms = ctx.timed(lambda: enc(xyz, feat, bx), 5)
+            for _ in range(3):
+                evs = [("start", torch.cuda.Event(enable_timing=True))]
+                evs[0][1].record()
+
+                def mark(name, evs=evs):
+                    e = torch.cuda.Event(enable_timing=True)
+                    e.record()
+                    evs.append((name, e))
+                enc(xyz, feat, bx, mark=mark)
+                torch.cuda.synchronize()
+                for (_, a), (n1, b) in zip(evs, evs[1:]):
+                    stage[n1] = stage.get(n1, 0.0) + a.elapsed_time(b) / 3
+        rows.append(dict(radius=r, nsample=K, ms_per_frame=round(ms, 4), frames_per_s=round(1e3 / ms, 1),
+                         mlp_kernel="tcgen05 3xFP16" if K == 32 else "fp32 CUDA cores (nsample != 32)",
+                         stages_ms={k: round(v, 4) for k, v in stage.items()}))
+    return dict(workload="configs[4]: 250000 pts x 200 boxes, one frame, S=512 P=512 MLP 4-64-128", sweep=rows)
+
+
+def block_train(ctx, frames_per_rank, steps=6):
+    """configs[3]'s share of the hot path (multimodal_gar_b200.train_step): forward + backward + Adam step of the LiDAR
+    branch (train-mode SA shared MLP in libmgar_lidar.so) + DAFM + heads under DistributedDataParallel; M = 80 persons
+    padded to 100 proposals, 65 536 points per frame.  exposed_comm = step time with the NCCL gradient all-reduce minus the
+    same step under no_sync()."""
+    import torch
+    from multimodal_gar_b200 import _lib, train_step as TS
+    dev = ctx.dev
+    torch.manual_seed(1994)
+    net = TS.LidarFusionNet().to(dev).train()
+    batch = TS.synthetic_batch(300 + ctx.rank, frames_per_rank, N=CFG["N"], M=80, MNP=100, device=dev)
+    model = TS.make_ddp(net, dev) if ctx.world > 1 else net
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+    losses = []
+    n0 = _lib.launch_count()
+    ms = ctx.timed(lambda: losses.append(TS.train_step(model, opt, batch)), steps, warm=2)
+    launches = (_lib.launch_count() - n0) // (steps + 2)
+    out = dict(workload="configs[3] share: LiDAR branch (train-mode SA MLP) + DAFM + heads, forward+backward+Adam, "
+                        "%d frames per rank x 80 persons (padded to 100), 65536 points per frame" % frames_per_rank,
+               frames_per_step=frames_per_rank * ctx.world, ms_per_step=round(ms, 3),
+               value=frames_per_rank * ctx.world / (ms * 1e-3), unit="frames/s", parallelism="ddp%d" % ctx.world,
+               parameters=sum(p.numel() for p in net.parameters()), allreduce_bytes_per_step=TS.grad_bytes(net),
+               collective="NCCL all-reduce of the fp32 gradients (25 MB buckets, overlapped with backward)" if ctx.world > 1 else "none (1 GPU)",
+               library_launches_per_step=launches, loss_first=float(losses[0]), loss_last=float(losses[-1]))
+    if ctx.world > 1:
+        def nosync():
+            with model.no_sync():
+                opt.zero_grad(set_to_none=True)
+                model(batch).backward()
+                opt.step()
+        ms0 = ctx.timed(nosync, steps, warm=1)
+        out["ms_per_step_no_allreduce"] = round(ms0, 3)
+        out["exposed_comm_ms"] = round(max(0.0, ms - ms0), 3)
+        model(batch).backward()      # leave DDP's reducer in a consistent state (grads synchronised once more)
+    return out
+
+
+def block_reference_gpu(ctx, F=16):
+    """the reference's own CUDA extensions (oracle/_ref, unmodified sources) + its torch / cuDNN composition
+    through the same configs[1] pipeline on this GPU (scripts/time_ref_gpu.py holds the composition)."""
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    try:
+        import time_ref_gpu
+        return time_ref_gpu.measure(F)
+    except Exception as e:          # oracle/_ref missing on this box, or the extension does not load
+        return dict(unavailable="%s: %s" % (type(e).__name__, str(e)[:200]))
+
+
 def run_native(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -286,28 +628,17 @@ def run_native(args, rank, world, local_rank):
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # NCCL's version banner must not share stdout with the JSON line
         dist.init_process_group("nccl", device_id=dev)
+    ctx = Ctx(rank, world, local_rank, dev)
     F = args.frames_per_step
     enc = make_encoder().to(dev)
     host, devb = build_batches(F, rank, dev)
     work = stage_work(F, enc.keep_sa_features)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(ms):
-        if world > 1:
-            t = torch.tensor([ms], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            return float(t.item())
-        return ms
-
     # ---- device-resident: `value` -------------------------------------------------------------------
     with torch.no_grad():
         for i in range(args.warmup):
             enc(*devb[i & 1])
-        barrier()
+        ctx.barrier()
         sampler = ClockSampler(local_rank) if rank == 0 else None
         marks = []
         n0 = _lib.launch_count()
@@ -325,37 +656,28 @@ def run_native(args, rank, world, local_rank):
             marks.append(evs)
         ev1 = torch.cuda.Event(enable_timing=True)
         ev1.record()
-        barrier()
+        ctx.barrier()
         launches = _lib.launch_count() - n0
-        ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+        ms_total = ctx.max_over_ranks(ev0.elapsed_time(ev1))
         clocks = sampler.stop() if sampler else None
+        # how much of the MLP's nominal work the distinct-centroid walk executes (reported, never hidden)
+        st = enc(*devb[0], return_stages=True)
+        live = st["live_cnt"]
+        walked = None
+        if live is not None:
+            tiles = ((live.view(-1) + 3) // 4) * (st["empty"].view(-1) == 0)
+            walked = float(tiles.sum().item()) * 4 / float(live.numel() * CFG["P"])
+        del st
     stage_ms = {}
     for evs in marks:
         for (_, a), (name, b) in zip(evs, evs[1:]):
             stage_ms[name] = stage_ms.get(name, 0.0) + a.elapsed_time(b) / len(marks)
+    r = dict(keep_sa=enc.keep_sa_features, F=F, ms_total=ms_total, stage_ms=stage_ms, launches=launches, clocks=clocks,
+             work=work, host=host, walked=walked)
 
     # ---- end to end through the public API with HOST buffers: `e2e` ---------------------------------
-    # The public host-buffer API (multimodal_gar_b200.pipeline.HostFramePipeline): every step copies its pinned host
-    # inputs to the device, runs the branch and copies the person features back; the three legs run on their own
-    # streams, so the copy of step i+1 overlaps the kernels of step i.  All of it is inside the timed region.
-    from multimodal_gar_b200 import pipeline
-    out_host = [torch.empty((F, CFG["M"], CFG["mlp"][-1]), dtype=torch.float32).pin_memory() for _ in range(2)]
-    pipe = pipeline.HostFramePipeline(enc, dev, depth=2)
-    with torch.no_grad():
-        for i in range(max(2, args.warmup // 2)):
-            pipe.submit(*host[i & 1], out_host[i & 1])
-        pipe.synchronize()
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(args.steps):
-            pipe.submit(*host[i & 1], out_host[i & 1])
-        pipe.join()
-        e1.record()
-        pipe.synchronize()
-        barrier()
-        ms_e2e = max_over_ranks(e0.elapsed_time(e1))
-        # single-frame latency (F = 1), reported beside the throughput number
+    r["e2e"] = block_e2e(ctx, enc, host, F, args.steps, args.warmup)
+    with torch.no_grad():                       # single-frame latency (F = 1), reported beside the throughput number
         one = [t[:1].contiguous() for t in devb[0]]
         for _ in range(5):
             enc(*one)
@@ -366,11 +688,19 @@ def run_native(args, rank, world, local_rank):
             enc(*one)
         l1.record()
         torch.cuda.synchronize()
-        lat_ms = l0.elapsed_time(l1) / 20
-    h2d = sum(t.numel() * t.element_size() for t in host[0])
-    d2h = out_host[0].numel() * out_host[0].element_size()
-    return dict(keep_sa=enc.keep_sa_features, F=F, ms_total=ms_total, ms_e2e=ms_e2e, stage_ms=stage_ms, launches=launches, clocks=clocks,
-                h2d=h2d, d2h=d2h, lat_ms=lat_ms, work=work, host=host)
+        r["lat_ms"] = l0.elapsed_time(l1) / 20
+    if not args.quick:
+        r["steady"] = block_steady_state(ctx, enc, devb, F, args.steady_seconds, ms_total / args.steps)
+        del devb
+        torch.cuda.empty_cache()
+        r["config2"] = block_config2(ctx)
+        torch.cuda.empty_cache()
+        r["train"] = block_train(ctx, args.train_frames)
+        torch.cuda.empty_cache()
+        if world == 1:
+            r["config4"] = block_config4(ctx)
+            r["reference_gpu"] = block_reference_gpu(ctx)
+    return r
 
 
 def main():
@@ -389,47 +719,71 @@ def main():
         F, K = r["F"], args.steps
         frames_total = F * K * world
         value = frames_total / (r["ms_total"] * 1e-3)
+        prof = ncu_profile(F)
         stages = {}
         for name, ms in r["stage_ms"].items():
             w = r["work"].get(name, dict(bytes=0, flops=0))
             stages[name] = dict(ms=round(ms, 4), algorithmic_GBps=round(w["bytes"] / (ms * 1e-3) / 1e9, 2),
+                                hbm_frac=round(w["bytes"] / (ms * 1e-3) / 1e9 / pk["hbm"], 4),
                                 TFLOPs=round(w["flops"] / (ms * 1e-3) / 1e12, 3))
         dom = max(r["stage_ms"], key=r["stage_ms"].get)
         w, ms = r["work"][dom], r["stage_ms"][dom]
+        kprof = prof.get("kernels", {}).get(dom, {})
         if w["flops"] > 0:        # the shared MLP: the one dense contraction -> tensor-pipe roofline
             ach = w["flops"] / (ms * 1e-3) / 1e12
-            roof = dict(bound="tensor", achieved=ach, peak=pk["bf16_sustained"], unit="TFLOP/s",
-                        frac=ach / pk["bf16_sustained"], traffic=ncu_traffic("sa_mlp", F), kernel=dom,
-                        note="algorithmic fp32 FLOPs (2*M*P*K*8448 per frame) over the kernel's CUDA-event time, against the "
-                             "%s sustained bf16 tensor peak; the kernel issues 3 fp16 MMAs per product (3xFP16 split, "
-                             "fp32-faithful), i.e. the tensor pipe does 3x the algorithmic work (ncu: pipe 82 %% busy, "
-                             "profiles/r01_full_summary_final.md) - frac compares fp32-faithful output with a bf16 library "
-                             "GEMM; traffic = ncu dram bytes per launch (profiles/r01_traffic.json)" % pk["source"])
+            walked = r["walked"] if r["walked"] is not None else 1.0
+            roof = dict(bound="tensor", achieved=ach, peak=pk["bf16"], unit="TFLOP/s", frac=ach / pk["bf16"],
+                        frac_burst=ach / pk["bf16"], frac_sustained=ach / pk["bf16_sustained"],
+                        peak_burst=pk["bf16"], peak_sustained=pk["bf16_sustained"],
+                        traffic=kprof.get("dram_bytes"), kernel=dom,
+                        executed_fraction=walked, executed_TFLOPs=ach * walked, executed_frac_burst=ach * walked / pk["bf16"],
+                        tensor_pipe_active_pct=kprof.get("tensor_pipe_active_pct"),
+                        note="achieved = ALGORITHMIC fp32 FLOPs (SURVEY 8d: 2*M*P*K*8448 per frame) over the kernel's "
+                             "CUDA-event time, against the %s bf16 tensor peak (burst: the timed region is tens of ms). "
+                             "Two things make it differ from tensor-pipe utilisation, both stated here: (1) the kernel "
+                             "walks only the DISTINCT centroids of every person (a person that pooled c < 512 points has "
+                             "c distinct samples; the rest repeat centroid 0 and cannot change the person's max): "
+                             "executed_fraction of the nominal tiles run, executed_TFLOPs = achieved x that; (2) each "
+                             "executed product costs 3 fp16 MMAs (3xFP16 split, fp32-faithful), so the pipe does 3x "
+                             "executed_TFLOPs - tensor_pipe_active_pct is ncu's sm__pipe_tensor_cycles_active of the "
+                             "committed capture (profiles/r02_traffic.json), traffic its dram bytes per launch" % pk["source"])
         else:
             ach = w["bytes"] / (ms * 1e-3) / 1e9
             roof = dict(bound="hbm", achieved=ach, peak=pk["hbm"], unit="GB/s", frac=ach / pk["hbm"],
-                        traffic=ncu_traffic(dom, F), kernel=dom, note="of %s" % pk["source"])
+                        traffic=kprof.get("dram_bytes"), kernel=dom, note="of %s" % pk["source"])
         roof["share_of_step"] = ms / (r["ms_total"] / K)
         pipeline_GBps = algorithmic_bytes_per_frame(keep_sa=r["keep_sa"]) * value / 1e9
+        e = r["e2e"]
+        cfg = bench_config(F, world)
         line = dict(metric=METRIC, value=value, unit="frames/s", n_gpus=world, steps=K, warmup=args.warmup,
                     ms_per_step=r["ms_total"] / K, higher_is_better=True, scaling="weak", vs_baseline=None,
-                    dtype="f32", data="synthetic",
-                    config=dict(workload="configs[1]: 65536 pts x 40 boxes, S=512 P=512 r=0.3 K=32 MLP 4-64-128",
-                                frames_per_step=F * world, frames_per_step_per_gpu=F,
-                                l2="two alternating input batches (2 x %d MB) + ~%d MB of stage outputs per step > 126 MB L2"
-                                   % (F, F * (14 if r["keep_sa"] else 4)),
-                                sa_features="stored" if r["keep_sa"] else "kept on chip (person max fused into the MLP kernel)",
-                                weights="random-init (seed 1994), eval-mode BatchNorm folded"),
-                    e2e=dict(value=frames_total / (r["ms_e2e"] * 1e-3), unit="frames/s",
-                             h2d_bytes_per_step=r["h2d"], d2h_bytes_per_step=r["d2h"]),
+                    dtype="f32", data="synthetic", config=cfg,
+                    setup=dict(sa_features="stored" if r["keep_sa"] else "kept on chip (person max fused into the MLP kernel)",
+                               weights="random-init (seed 1994), eval-mode BatchNorm folded",
+                               peaks=pk["source"]),
+                    e2e=dict(value=frames_total / (e["ms"] * 1e-3), unit="frames/s",
+                             h2d_bytes_per_step=e["h2d"], d2h_bytes_per_step=e["d2h"], **e["extra"]),
                     gpu_launches=r["launches"], clocks=r["clocks"], roofline=roof, stages=stages,
                     pipeline_algorithmic_GBps=pipeline_GBps, pipeline_hbm_frac=pipeline_GBps / pk["hbm"] / world,
                     latency_1frame_ms=r["lat_ms"])
+        if "steady" in r:
+            line["steady_state"] = r["steady"]
+            cfgs = {"configs[2]": r["config2"]}
+            if "config4" in r:
+                cfgs["configs[4]"] = r["config4"]
+            line["configs"] = cfgs
+            line["train"] = r["train"]
+            if "reference_gpu" in r:
+                line["reference_gpu"] = r["reference_gpu"]
         if world == 1 and not args.no_cpu_baseline:
             n = args.cpu_frames or 8
             import numpy as np
+            import torch
             frames = tuple(np.ascontiguousarray(t[:n].numpy()) for t in r["host"][0])
             line["cpu_baseline"] = cpu_baseline_inline(frames, min(n, F))
+            c0 = config0_block((frames[0][0], frames[1][0], frames[2][0]), torch.device("cuda", local_rank))
+            line["cpu_baseline"]["ref_points_in_boxes_cpu_ms"] = c0["ref_points_in_boxes_cpu_ms"]
+            line.setdefault("configs", {})["configs[0]"] = c0
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

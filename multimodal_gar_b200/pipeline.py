@@ -30,8 +30,18 @@ class HostFramePipeline:
     def _slot(self, k, tensors):
         s = self.slots[k]
         if s is None or any(a.shape != b.shape for a, b in zip(s["dev"], tensors)):
-            s = dict(dev=[torch.empty(t.shape, dtype=t.dtype, device=self.dev) for t in tensors],
-                     ready=torch.cuda.Event(), consumed=None, flushed=None, out=None)
+            if s is not None:
+                # the kernels / copies still using the old buffers must be done before the allocator may reuse them
+                for ev in (s["consumed"], s["flushed"]):
+                    if ev is not None:
+                        ev.synchronize()
+            # allocated ON the copy stream (the first writer), and announced to the stream whose kernels read them,
+            # so the caching allocator never hands the block to pending work of another stream
+            with torch.cuda.stream(self.s_in):
+                dev = [torch.empty(t.shape, dtype=t.dtype, device=self.dev) for t in tensors]
+            for d in dev:
+                d.record_stream(self.s_run)
+            s = dict(dev=dev, ready=torch.cuda.Event(), consumed=None, flushed=None, out=None)
             self.slots[k] = s
         return s
 

@@ -19,9 +19,9 @@ from multimodal_gar_b200 import lidar_branch  # noqa: E402
 from oracle import oracle as O  # noqa: E402
 
 
-def main():
-    F = int(sys.argv[1]) if len(sys.argv) > 1 else 16
-    dev = torch.device("cuda:0")
+def measure(F=16, dev=None):
+    """-> dict: per-stage and total ms of the reference composition on F configs[1] frames (current CUDA device)."""
+    dev = dev or torch.device("cuda", torch.cuda.current_device())
     roiaware, roipoint, pn2 = (O.load_ref(n) for n in ("roiaware_pool3d_cuda", "roipoint_pool3d_cuda", "pointnet2_stack_cuda"))
     assert roiaware and roipoint and pn2, "oracle/_ref is not built"
     c = bench.CFG
@@ -90,12 +90,16 @@ def main():
         ref = ref_step().view(F, M, -1)
         scale = float(ref.abs().max())
         diff = float((new - ref).abs().max())
-    print(json.dumps(dict(what="reference CUDA extensions (oracle/_ref) + torch/cuDNN composition, configs[1], eval mode",
-                          frames_per_step=F, ms_per_step=ms, frames_per_s=F / ms * 1e3,
-                          stage_ms={k: round(v, 3) for k, v in stage.items()},
-                          max_abs_diff_vs_new_path=diff, feature_scale=scale,
-                          note="cuDNN runs the two 1x1 convolutions in TF32 (torch default), so the difference to the "
-                               "fp32-faithful new path is TF32-sized")))
+    return dict(what="reference CUDA extensions (oracle/_ref) + torch/cuDNN composition, configs[1], eval mode",
+                frames_per_step=F, ms_per_step=ms, frames_per_s=F / ms * 1e3,
+                stage_ms={k: round(v, 3) for k, v in stage.items()},
+                max_abs_diff_vs_new_path=diff, feature_scale=scale,
+                note="cuDNN runs the two 1x1 convolutions in TF32 (torch default), so the difference to the "
+                     "fp32-faithful new path is TF32-sized")
+
+
+def main():
+    print(json.dumps(measure(int(sys.argv[1]) if len(sys.argv) > 1 else 16)))
 
 
 if __name__ == "__main__":
