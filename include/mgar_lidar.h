@@ -38,6 +38,15 @@ MGAR_API const char *mgar_last_error(void);
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 MGAR_API unsigned long long mgar_launch_count(void);
 
+/* Scratch of the stack-layout (ragged) operators.  The reference's kernels re-derive a point's batch with an O(B) loop
+ * per thread (e.g. ball_query_gpu.cu:27-35); here one small launch turns the (B) count arrays into exclusive prefix
+ * arrays that the kernels binary-search.  Those arrays live in CALLER-PROVIDED device scratch of
+ * mgar_stack_workspace_bytes(B) bytes, passed as (workspace, workspace_bytes) to every entry that takes batch counts
+ * (NULL / 0 with the uniform layout).  mgar_sa_mlp_fwd_train / _bwd take it BEHIND their own workspace: their
+ * workspace must then hold round_up(mgar_sa_mlp_train_workspace_bytes_for(..), 16) + mgar_stack_workspace_bytes(B).
+ * The library never allocates device memory. */
+MGAR_API size_t mgar_stack_workspace_bytes(int B);
+
 /* ---- roiaware_pool3d: in-box tests -------------------------------------------------------- */
 
 /* points_in_boxes_gpu: roiaware_pool3d/src/roiaware_pool3d.cpp:98-118 (kernel .cu:313-336).
@@ -56,9 +65,11 @@ MGAR_API int mgar_in_box_mask(const float *boxes, const float *pts, const float 
 /* points_in_boxes_cpu: roiaware_pool3d.cpp:143-168.  HOST buffers in and out: boxes (M,7),
  * pts (N,3) -> mask (M,N) int32 0/1 with the CPU function's margin (1e-2).  Runs on the GPU
  * (H2D, kernel, D2H, synchronous); only the M box headings are pre-processed on the host so the
- * result is bit-identical to the reference's glibc trig. */
+ * result is bit-identical to the reference's glibc trig.  workspace: DEVICE staging (on the current device) of
+ * mgar_points_in_boxes_mask_host_workspace_bytes(M, N) bytes, owned by the caller. */
+MGAR_API size_t mgar_points_in_boxes_mask_host_workspace_bytes(int M, int N);
 MGAR_API int mgar_points_in_boxes_mask_host(const float *boxes_host, const float *pts_host, int *mask_host,
-                                   int M, int N);
+                                   int M, int N, void *workspace, size_t workspace_bytes);
 
 /* ---- roipoint_pool3d ------------------------------------------------------------------------ */
 
@@ -139,7 +150,7 @@ MGAR_API int mgar_fps_stack(int batch, int max_n, const float *xyz, float *temp,
 MGAR_API int mgar_ball_query_stack(int B, int M, float radius, int nsample, const float *new_xyz,
                           const int *new_xyz_batch_cnt, const float *xyz, int xyz_stride,
                           const int *xyz_batch_cnt, int uniform_n, int uniform_m, int *idx, int fill,
-                          void *stream);
+                          void *workspace, size_t workspace_bytes, void *stream);
 
 /* voxel_query_wrapper_stack: voxel_query.cpp:25-41 (kernel voxel_query_gpu.cu:10-89).  new_xyz (M,3), xyz (N,3),
  * new_coords (M,4) int32 [batch, z, y, x] (16-byte aligned), point_indices (B,R1,R2,R3) int32 voxel -> point
@@ -180,13 +191,13 @@ MGAR_API int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xyz_
  * out (M,C,nsample), every element written. */
 MGAR_API int mgar_group_points_stack(int B, int M, int C, int nsample, const float *features,
                             const int *features_batch_cnt, const int *idx, const int *idx_batch_cnt,
-                            float *out, void *stream);
+                            float *out, void *workspace, size_t workspace_bytes, void *stream);
 
 /* group_points_grad_wrapper_stack: group_points.cpp:29-47 (kernel group_points_gpu.cu:15-44).
  * grad_features (N,C) zero-filled by the caller, accumulated with atomics. */
 MGAR_API int mgar_group_points_grad_stack(int B, int M, int C, int N, int nsample, const float *grad_out,
                                  const int *idx, const int *idx_batch_cnt,
-                                 const int *features_batch_cnt, float *grad_features, void *stream);
+                                 const int *features_batch_cnt, float *grad_features, void *workspace, size_t workspace_bytes, void *stream);
 
 /* ---- pointnet2_batch: channel-major gather / scatter, three-nearest interpolation ------------------- */
 
@@ -220,7 +231,7 @@ MGAR_API int mgar_three_interpolate_grad(int b, int c, int n, int m, const float
  * three_interpolate_grad_wrapper (interpolate.cpp:86-107, kernel :150-170): grad_out (N,C) accumulated with atomics
  * into zero-filled grad_features (M,C). */
 MGAR_API int mgar_three_nn_stack(int B, int N, int M, const float *unknown, const int *unknown_batch_cnt,
-                                 const float *known, const int *known_batch_cnt, float *dist2, int *idx, void *stream);
+                                 const float *known, const int *known_batch_cnt, float *dist2, int *idx, void *workspace, size_t workspace_bytes, void *stream);
 MGAR_API int mgar_three_interpolate_stack(int N, int C, const float *features, const int *idx, const float *weight,
                                           float *out, void *stream);
 MGAR_API int mgar_three_interpolate_grad_stack(int N, int C, const float *grad_out, const int *idx, const float *weight,
@@ -261,7 +272,7 @@ MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const flo
                                   const float *new_xyz, const int *new_xyz_batch_cnt, int uniform_n,
                                   int uniform_m, const float *features, const int *idx,
                                   const unsigned char *empty_mask, int n_layers, const int *channels_host,
-                                  const float *params, float *out, int ld_out, int pool_avg, void *stream);
+                                  const float *params, float *out, int ld_out, int pool_avg, void *workspace, size_t workspace_bytes, void *stream);
 
 /* Same operation on the 5th-generation tensor cores (tcgen05.mma kind::tf32, fp32 accumulation in
  * TMEM, 3xTF32 operand splitting: fp32-level accuracy, within the 1e-5 parity bar) for the shape
@@ -281,8 +292,9 @@ MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const flo
  * with the skip above in force the kernel walks, per live group, only the tiles of four centroids that cover its first
  * group_live_cnt[g] centroids - the others repeat centroid 0 (same ball, same feature row) and cannot change the
  * group's max, so group_max holds the same bits.
- * workspace: device scratch of mgar_sa_mlp_tc_workspace_bytes(M, group_size) bytes, needed only when the skip is
- * asked for (NULL / 0 otherwise); the library allocates nothing. */
+ * workspace: device scratch of mgar_sa_mlp_tc_workspace_bytes(M, group_size) bytes when the skip is asked for, of
+ * mgar_stack_workspace_bytes(B) bytes with ragged batch counts (the two never combine: the skip needs the uniform
+ * layout), NULL / 0 otherwise; the library allocates nothing. */
 MGAR_API size_t mgar_sa_mlp_tc_workspace_bytes(int M, int group_size);
 MGAR_API int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg);
 MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float *xyz, int xyz_stride,

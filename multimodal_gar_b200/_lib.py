@@ -23,7 +23,8 @@ SIGNATURES = {
     "mgar_launch_count": [],
     "mgar_points_in_boxes": [_p, _p, _p, _i, _i, _i, _p],
     "mgar_in_box_mask": [_p, _p, _p, _p, _i, _i, _i, _p],
-    "mgar_points_in_boxes_mask_host": [_p, _p, _p, _i, _i],
+    "mgar_points_in_boxes_mask_host_workspace_bytes": [_i, _i],
+    "mgar_points_in_boxes_mask_host": [_p, _p, _p, _i, _i, _p, ctypes.c_size_t],
     "mgar_roipoint_pool": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
     "mgar_box_mask_words": [_i],
     "mgar_box_masks": [_p, _p, _p, _p, _p, _i, _i, _i, _p],
@@ -33,14 +34,15 @@ SIGNATURES = {
     "mgar_roiaware_pool3d_bwd": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p],
     "mgar_fps_batch": [_i, _i, _i, _p, _i, _p, _p, _p, _p],
     "mgar_fps_stack": [_i, _i, _p, _p, _p, _p, _p, _p],
-    "mgar_ball_query_stack": [_i, _i, _f, _i, _p, _p, _p, _i, _p, _i, _i, _p, _i, _p],
+    "mgar_stack_workspace_bytes": [_i],
+    "mgar_ball_query_stack": [_i, _i, _f, _i, _p, _p, _p, _i, _p, _i, _i, _p, _i, _p, ctypes.c_size_t, _p],
     "mgar_voxel_query_stack": [_i, _i, _i, _i, _i, _f, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_batch_group_points": [_i, _i, _i, _i, _i, _p, _p, _p, _p],
     "mgar_batch_group_points_grad": [_i, _i, _i, _i, _i, _p, _p, _p, _p],
     "mgar_three_nn": [_i, _i, _i, _p, _p, _p, _p, _p],
     "mgar_three_interpolate": [_i, _i, _i, _i, _p, _p, _p, _p, _p],
     "mgar_three_interpolate_grad": [_i, _i, _i, _i, _p, _p, _p, _p, _p],
-    "mgar_three_nn_stack": [_i, _i, _i, _p, _p, _p, _p, _p, _p, _p],
+    "mgar_three_nn_stack": [_i, _i, _i, _p, _p, _p, _p, _p, _p, _p, ctypes.c_size_t, _p],
     "mgar_three_interpolate_stack": [_i, _i, _p, _p, _p, _p, _p],
     "mgar_three_interpolate_grad_stack": [_i, _i, _p, _p, _p, _p, _p],
     "mgar_dafm_attention": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p],
@@ -48,13 +50,13 @@ SIGNATURES = {
     "mgar_fps_ball_query_supported": [_i, _i, _i, _i],
     "mgar_fps_ball_query_workspace_bytes": [_i],
     "mgar_fps_ball_query": [_i, _i, _i, _p, _i, _f, _i, _p, _p, _p, _p, _i, _p, _p, ctypes.c_size_t, _p],
-    "mgar_group_points_stack": [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
-    "mgar_group_points_grad_stack": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p],
+    "mgar_group_points_stack": [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p, ctypes.c_size_t, _p],
+    "mgar_group_points_grad_stack": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, ctypes.c_size_t, _p],
     "mgar_sa_mlp_tc_supported": [_i, _i, _i, _p, _i],
     "mgar_sa_mlp_tc_workspace_bytes": [_i, _i],
     "mgar_sa_mlp_fwd_tc": [_i, _i, _i, _i, _p, _i, _p, _p, _p, _i, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _i, _p, _i, _p, _p,
                            _i, _p, ctypes.c_size_t, _p],
-    "mgar_sa_mlp_fwd_fp32": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _i, _i, _p],
+    "mgar_sa_mlp_fwd_fp32": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _i, _i, _p, ctypes.c_size_t, _p],
     "mgar_sa_mlp_train_workspace_bytes": [_i, _i, _i, _p],
     "mgar_sa_mlp_train_workspace_bytes_for": [_i, _i, _i, _p, _i],
     "mgar_sa_mlp_fwd_train": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _f, _p, _i, _i, _p, _p,
@@ -94,6 +96,8 @@ def lib():
         L.mgar_sa_mlp_train_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_sa_mlp_train_workspace_bytes_for.restype = ctypes.c_size_t
         L.mgar_box_mask_words.restype = ctypes.c_size_t
+        L.mgar_stack_workspace_bytes.restype = ctypes.c_size_t
+        L.mgar_points_in_boxes_mask_host_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_sa_mlp_tc_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_fps_ball_query_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_roiaware_pool3d_workspace_bytes.restype = ctypes.c_size_t
@@ -105,6 +109,14 @@ def check(rc, what=""):
     if rc != 0:
         msg = lib().mgar_last_error().decode("utf-8", "replace")
         raise MgarError("%s failed (code %d): %s" % (what or "libmgar_lidar call", rc, msg))
+
+
+def stack_workspace(B, device):
+    """Device scratch of the stack-layout operators (mgar_stack_workspace_bytes(B) bytes from torch's caching allocator:
+    the library itself allocates nothing) -> (tensor, nbytes)."""
+    import torch
+    n = int(lib().mgar_stack_workspace_bytes(int(B)))
+    return torch.empty((max(n, 16),), dtype=torch.uint8, device=device), n
 
 
 def launch_count():

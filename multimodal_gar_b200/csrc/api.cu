@@ -4,6 +4,7 @@
 #include <atomic>
 
 #include "mgar_common.cuh"
+#include "stack_prefix.cuh"
 
 namespace mgar {
 
@@ -35,5 +36,6 @@ extern "C" {
 int mgar_abi_version(void) { return MGAR_ABI_VERSION; }
 const char *mgar_last_error(void) { return mgar::g_err; }
 unsigned long long mgar_launch_count(void) { return mgar::g_launches.load(); }
+size_t mgar_stack_workspace_bytes(int B) { return B > 0 ? mgar::stack_ws_bytes(B) : 0; }
 
 }  // extern "C"

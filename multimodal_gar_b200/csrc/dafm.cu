@@ -294,12 +294,9 @@ extern "C" int mgar_dafm_attention(int B, int n, int D, int n_streams, int ld, c
         P.gamma[s] = gamma[t]; P.beta[s] = beta[t]; P.out[s] = out[t];
     }
     const size_t smem = da_smem_floats(n) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
-        MGAR_CUDA(cudaFuncSetAttribute(dafm_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)(da_smem_floats(kDaMaxN) * sizeof(float))));
-        attr_set = true;
-    }
+    // per call: the attribute belongs to the current device's context (a process may drive several GPUs)
+    MGAR_CUDA(cudaFuncSetAttribute(dafm_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(da_smem_floats(kDaMaxN) * sizeof(float))));
     dafm_attention_kernel<<<dim3(B, n_streams, div_up(n, kDaRows)), kDaThreads, smem, (cudaStream_t)stream>>>(n, D, ld, P, E, valid,
                                                                                            sqrtf((float)D), eps);
     count_launch();

@@ -8,7 +8,6 @@
 // 128-bit loads and writes one 128-bit result; the kernel streams 12N + 4N bytes once (HBM-bound).
 #include <math.h>
 
-#include <mutex>
 
 #include "mgar_common.cuh"
 
@@ -114,13 +113,7 @@ in_box_mask_kernel(const float *__restrict__ boxes, const float *__restrict__ pt
 
 static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-// Grow-only device scratch for the host-buffer entry points (one per process, mutex-guarded).
-struct Scratch {
-    void *dev = nullptr;
-    size_t cap = 0;
-    std::mutex mu;
-};
-static Scratch g_scratch;
+static size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 }  // namespace mgar
 
@@ -156,23 +149,25 @@ extern "C" int mgar_in_box_mask(const float *boxes, const float *pts, const floa
     return check_launch("in_box_mask");
 }
 
+// device staging of the host-buffer entry: boxes | cos, sin | points | (M,N) mask, each rounded up to 256 bytes
+extern "C" size_t mgar_points_in_boxes_mask_host_workspace_bytes(int M, int N) {
+    if (M <= 0 || N <= 0) return 0;
+    return up256((size_t)M * 28) + up256((size_t)M * 8) + up256((size_t)N * 12) + up256((size_t)M * N * 4);
+}
+
 extern "C" int mgar_points_in_boxes_mask_host(const float *boxes_host, const float *pts_host,
-                                              int *mask_host, int M, int N) {
+                                              int *mask_host, int M, int N, void *workspace, size_t workspace_bytes) {
     MGAR_REQUIRE(M >= 0 && N >= 0, "points_in_boxes_mask_host: negative size");
     if (M == 0 || N == 0) return MGAR_OK;
     MGAR_REQUIRE(boxes_host && pts_host && mask_host, "points_in_boxes_mask_host: null pointer");
-    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    const size_t o_box = 0, o_cs = up((size_t)M * 28), o_pts = o_cs + up((size_t)M * 8);
-    const size_t o_mask = o_pts + up((size_t)N * 12), total = o_mask + up((size_t)M * N * 4);
-    std::lock_guard<std::mutex> lock(g_scratch.mu);
-    if (g_scratch.cap < total) {
-        if (g_scratch.dev) cudaFree(g_scratch.dev);
-        g_scratch.dev = nullptr;
-        g_scratch.cap = 0;
-        MGAR_CUDA(cudaMalloc(&g_scratch.dev, total));
-        g_scratch.cap = total;
+    const size_t o_box = 0, o_cs = up256((size_t)M * 28), o_pts = o_cs + up256((size_t)M * 8);
+    const size_t o_mask = o_pts + up256((size_t)N * 12), total = o_mask + up256((size_t)M * N * 4);
+    if (!workspace || workspace_bytes < total) {      // the caller owns the device staging (current device): no hidden allocation
+        set_error("points_in_boxes_mask_host: needs a DEVICE workspace of mgar_points_in_boxes_mask_host_workspace_bytes(M, N) "
+                  "= %zu bytes, got %zu", total, workspace ? workspace_bytes : (size_t)0);
+        return MGAR_ENOMEM;
     }
-    char *d = static_cast<char *>(g_scratch.dev);
+    char *d = static_cast<char *>(workspace);
     // The only host arithmetic: the M box headings go through the host libm so the decision is
     // bit-identical to the reference's CPU build (roiaware_pool3d.cpp:121-125).
     float *cs = new float[(size_t)M * 2];

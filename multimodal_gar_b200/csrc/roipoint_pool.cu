@@ -410,11 +410,9 @@ extern "C" int mgar_roipoint_pool(const float *xyz, const float *boxes, const fl
         if (smem <= 200 * 1024) break;
     }
     MGAR_REQUIRE(nwarps >= 1, "roipoint_pool: num_sampled_points=%d does not fit in shared memory", S);
-    static bool attr_set = false;
-    if (!attr_set) {
-        MGAR_CUDA(cudaFuncSetAttribute(roipoint_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-    }
+    // per call: the attribute belongs to the current device's context (a process may drive several GPUs)
+    if (smem > 48 * 1024)
+        MGAR_CUDA(cudaFuncSetAttribute(roipoint_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(M, B);
     roipoint_pool_kernel<<<grid, nwarps * 32, smem, (cudaStream_t)stream>>>(xyz, boxes, feat, pooled, empty, pts_idx,
                                                                         N, M, S, C, cap, canonical);

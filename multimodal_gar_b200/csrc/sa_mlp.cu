@@ -155,7 +155,8 @@ extern "C" int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const f
                                     const float *new_xyz, const int *new_xyz_batch_cnt, int uniform_n,
                                     int uniform_m, const float *features, const int *idx,
                                     const unsigned char *empty_mask, int n_layers, const int *channels_host,
-                                    const float *params, float *out, int ld_out, int pool_avg, void *stream) {
+                                    const float *params, float *out, int ld_out, int pool_avg, void *workspace,
+                                    size_t workspace_bytes, void *stream) {
     MGAR_REQUIRE(B >= 1 && M >= 0 && nsample >= 1 && C_in >= 0, "sa_mlp: bad size");
     MGAR_REQUIRE(n_layers >= 1 && n_layers <= kMaxLayers, "sa_mlp: 1..%d layers supported", kMaxLayers);
     if (M == 0) return MGAR_OK;
@@ -186,7 +187,7 @@ extern "C" int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const f
     cudaStream_t st = (cudaStream_t)stream;
     PrefixWs ws;
     if (!uniform) {
-        if (int rc = ws.alloc(B, st)) return rc;
+        if (int rc = ws.bind(workspace, workspace_bytes, B, "sa_mlp_fwd_fp32")) return rc;
         if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     }
     MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

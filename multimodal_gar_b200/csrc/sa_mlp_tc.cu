@@ -441,7 +441,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     cudaStream_t st = (cudaStream_t)stream;
     PrefixWs ws;
     if (!uniform) {
-        if (int rc = ws.alloc(B, st)) return rc;
+        if (int rc = ws.bind(workspace, workspace_bytes, B, "sa_mlp_fwd_tc")) return rc;
         if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     }
     TcArgs A;

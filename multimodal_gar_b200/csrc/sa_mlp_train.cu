@@ -389,8 +389,9 @@ extern "C" int mgar_sa_mlp_fwd_train(int B, int M, int nsample, int C_in, const 
                                empty_mask, weights, gamma_beta, eps, out, ld_out, batch_stats, workspace, ws_bytes, st);
     if (ws_bytes < s.total) { set_error("sa_mlp_train: workspace %zu < %zu bytes", ws_bytes, s.total); return MGAR_ENOMEM; }
     PrefixWs ws;
-    if (!uniform) {
-        if (int rc = ws.alloc(B, st)) return rc;
+    if (!uniform) {   // ragged batches: the prefix arrays sit behind the training workspace (see the header)
+        const size_t off = (s.total + 15) & ~(size_t)15;
+        if (int rc = ws.bind(ws_bytes > off ? static_cast<char *>(workspace) + off : nullptr, ws_bytes > off ? ws_bytes - off : 0, B, "sa_mlp_fwd_train")) return rc;
         if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     }
     char *W = static_cast<char *>(workspace);
@@ -457,7 +458,8 @@ extern "C" int mgar_sa_mlp_bwd(int B, int M, int nsample, int C_in, const int *x
     MGAR_REQUIRE(uniform || (xyz_batch_cnt && new_xyz_batch_cnt), "sa_mlp_bwd: batch counts missing");
     PrefixWs ws;
     if (!uniform && grad_features && C_in > 0) {
-        if (int rc = ws.alloc(B, st)) return rc;
+        const size_t off = (s.total + 15) & ~(size_t)15;
+        if (int rc = ws.bind(ws_bytes > off ? static_cast<char *>(workspace) + off : nullptr, ws_bytes > off ? ws_bytes - off : 0, B, "sa_mlp_bwd")) return rc;
         if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     }
     char *W = static_cast<char *>(workspace);

@@ -1013,8 +1013,9 @@ int forward(int B, int M, int C_in, const float *xyz, const int *xyz_batch_cnt, 
     if (ws_bytes < l.total) { set_error("sa_mlp_train: workspace %zu < %zu bytes", ws_bytes, l.total); return MGAR_ENOMEM; }
     const bool uniform = uniform_n > 0;
     PrefixWs ws;
-    if (!uniform) {
-        if (int rc = ws.alloc(B, st)) return rc;
+    if (!uniform) {   // ragged batches: the prefix arrays sit behind the training workspace
+        const size_t off = (l.total + 15) & ~(size_t)15;
+        if (int rc = ws.bind(ws_bytes > off ? static_cast<char *>(workspace) + off : nullptr, ws_bytes > off ? ws_bytes - off : 0, B, "sa_mlp_fwd_train")) return rc;
         if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     }
     char *W = static_cast<char *>(workspace);
@@ -1036,7 +1037,8 @@ int backward(int B, int M, int C_in, const int *xyz_batch_cnt, const int *new_xy
     const bool uniform = uniform_n > 0;
     PrefixWs ws;
     if (!uniform && grad_features) {
-        if (int rc = ws.alloc(B, st)) return rc;
+        const size_t off = (l.total + 15) & ~(size_t)15;
+        if (int rc = ws.bind(ws_bytes > off ? static_cast<char *>(workspace) + off : nullptr, ws_bytes > off ? ws_bytes - off : 0, B, "sa_mlp_bwd")) return rc;
         if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     }
     char *W = static_cast<char *>(workspace);

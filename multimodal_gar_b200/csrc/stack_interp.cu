@@ -105,14 +105,15 @@ three_interpolate_grad_stack_kernel(long long total, int C, const float *__restr
 using namespace mgar;
 
 extern "C" int mgar_three_nn_stack(int B, int N, int M, const float *unknown, const int *unknown_batch_cnt,
-                                   const float *known, const int *known_batch_cnt, float *dist2, int *idx, void *stream) {
+                                   const float *known, const int *known_batch_cnt, float *dist2, int *idx, void *workspace,
+                                   size_t workspace_bytes, void *stream) {
     MGAR_REQUIRE(B >= 1 && N >= 0 && M >= 0, "three_nn_stack: bad size B=%d N=%d M=%d", B, N, M);
     if (N == 0) return MGAR_OK;
     MGAR_REQUIRE(unknown && unknown_batch_cnt && known_batch_cnt && dist2 && idx && (known || M == 0),
                  "three_nn_stack: null pointer");
     cudaStream_t st = (cudaStream_t)stream;
     PrefixWs ws;
-    if (int rc = ws.alloc(B, st)) return rc;
+    if (int rc = ws.bind(workspace, workspace_bytes, B, "three_nn_stack")) return rc;
     if (int rc = stack_prefix(unknown_batch_cnt, known_batch_cnt, B, kSnThreads, ws.a, ws.b, ws.t, st)) return rc;
     const int grid = div_up(N, kSnThreads) + B;      // upper bound of sum(ceil(n_b / tile)); surplus CTAs exit at once
     three_nn_stack_kernel<<<grid, kSnThreads, 0, st>>>(B, unknown, known, ws.a, ws.b, ws.t, dist2, idx);

@@ -282,7 +282,7 @@ using namespace mgar;
 extern "C" int mgar_ball_query_stack(int B, int M, float radius, int nsample, const float *new_xyz,
                                      const int *new_xyz_batch_cnt, const float *xyz, int xyz_stride,
                                      const int *xyz_batch_cnt, int uniform_n, int uniform_m, int *idx, int fill,
-                                     void *stream) {
+                                     void *workspace, size_t workspace_bytes, void *stream) {
     MGAR_REQUIRE(B >= 1 && M >= 0 && nsample >= 1, "ball_query: bad size B=%d M=%d nsample=%d", B, M, nsample);
     if (M == 0) return MGAR_OK;
     const bool uniform = uniform_n > 0;
@@ -310,7 +310,7 @@ extern "C" int mgar_ball_query_stack(int B, int M, float radius, int nsample, co
     if (uniform) {
         grid = B * div_up(uniform_m, kBqTile);
     } else {
-        if (int rc = ws.alloc(B, st)) return rc;
+        if (int rc = ws.bind(workspace, workspace_bytes, B, "ball_query")) return rc;
         if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, kBqTile, ws.a, ws.b, ws.t, st)) return rc;
         grid = div_up(M, kBqTile) + B;  // upper bound of sum_b ceil(M_b / tile)
     }
@@ -323,14 +323,14 @@ extern "C" int mgar_ball_query_stack(int B, int M, float radius, int nsample, co
 
 extern "C" int mgar_group_points_stack(int B, int M, int C, int nsample, const float *features,
                                        const int *features_batch_cnt, const int *idx, const int *idx_batch_cnt,
-                                       float *out, void *stream) {
+                                       float *out, void *workspace, size_t workspace_bytes, void *stream) {
     MGAR_REQUIRE(B >= 1 && M >= 0 && C >= 0 && nsample >= 0, "group_points: bad size");
     const long long total = (long long)M * C * nsample;
     if (total == 0) return MGAR_OK;
     MGAR_REQUIRE(features && features_batch_cnt && idx && idx_batch_cnt && out, "group_points: null pointer");
     cudaStream_t st = (cudaStream_t)stream;
     PrefixWs ws;
-    if (int rc = ws.alloc(B, st)) return rc;
+    if (int rc = ws.bind(workspace, workspace_bytes, B, "group_points")) return rc;
     if (int rc = stack_prefix(idx_batch_cnt, features_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     group_points_kernel<<<div_up(total, 256), 256, 0, st>>>(B, total, C, nsample, features, ws.b, ws.a, idx, out);
     count_launch();
@@ -339,7 +339,8 @@ extern "C" int mgar_group_points_stack(int B, int M, int C, int nsample, const f
 
 extern "C" int mgar_group_points_grad_stack(int B, int M, int C, int N, int nsample, const float *grad_out,
                                             const int *idx, const int *idx_batch_cnt,
-                                            const int *features_batch_cnt, float *grad_features, void *stream) {
+                                            const int *features_batch_cnt, float *grad_features, void *workspace,
+                                            size_t workspace_bytes, void *stream) {
     (void)N;
     MGAR_REQUIRE(B >= 1 && M >= 0 && C >= 0 && nsample >= 0, "group_points_grad: bad size");
     const long long total = (long long)M * C * nsample;
@@ -347,7 +348,7 @@ extern "C" int mgar_group_points_grad_stack(int B, int M, int C, int N, int nsam
     MGAR_REQUIRE(grad_out && features_batch_cnt && idx && idx_batch_cnt && grad_features, "group_points_grad: null pointer");
     cudaStream_t st = (cudaStream_t)stream;
     PrefixWs ws;
-    if (int rc = ws.alloc(B, st)) return rc;
+    if (int rc = ws.bind(workspace, workspace_bytes, B, "group_points_grad")) return rc;
     if (int rc = stack_prefix(idx_batch_cnt, features_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     group_points_grad_kernel<<<div_up(total, 256), 256, 0, st>>>(B, total, C, nsample, grad_out, ws.b, ws.a, idx, grad_features);
     count_launch();

@@ -9,24 +9,23 @@ namespace mgar {
 int stack_prefix(const int *cnt_a, const int *cnt_b, int B, int tile, int *pre_a, int *pre_b, int *pre_tile,
                  cudaStream_t st);
 
-// Stream-ordered scratch for the three prefix arrays (freed when the object goes out of scope,
-// after the consumers have been enqueued on the same stream).
+// The three prefix arrays live in CALLER-PROVIDED scratch (the binding passes workspace pointers; the
+// library allocates nothing): mgar_stack_workspace_bytes(B) bytes at `base`.  (Round 1 took them from
+// cudaMallocAsync per call: the pool hands its memory back at every synchronisation, so each ragged call paid a fresh
+// ~4 ms allocation - 26 of the 53 ms of a training step.)
+constexpr size_t stack_ws_bytes(int B) { return (3 * ((size_t)B + 1) * sizeof(int) + 15) & ~(size_t)15; }
 struct PrefixWs {
-    int *base = nullptr, *a = nullptr, *b = nullptr, *t = nullptr;
-    cudaStream_t st = nullptr;
-    int alloc(int B, cudaStream_t s) {
-        st = s;
-        const size_t n = (size_t)(B + 1);
-        cudaError_t e = cudaMallocAsync((void **)&base, 3 * n * sizeof(int), s);
-        if (e != cudaSuccess) {
-            set_error("stack op: cudaMallocAsync failed: %s", cudaGetErrorString(e));
-            base = nullptr;
+    int *a = nullptr, *b = nullptr, *t = nullptr;
+    int bind(void *base, size_t avail, int B, const char *who) {
+        if (!base || avail < stack_ws_bytes(B)) {
+            set_error("%s: ragged (stack-layout) batches need a workspace of mgar_stack_workspace_bytes(B=%d) = %zu bytes, got %zu",
+                      who, B, stack_ws_bytes(B), base ? avail : (size_t)0);
             return MGAR_ENOMEM;
         }
-        a = base; b = base + n; t = base + 2 * n;
+        const size_t n = (size_t)(B + 1);
+        a = static_cast<int *>(base); b = a + n; t = a + 2 * n;
         return MGAR_OK;
     }
-    ~PrefixWs() { if (base) cudaFreeAsync(base, st); }
 };
 
 // largest b in [0,B) with pre[b] <= v  (pre is a non-decreasing exclusive prefix, pre[B] = total).

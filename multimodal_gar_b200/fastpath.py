@@ -78,7 +78,7 @@ def ball_query_uniform(radius, nsample, xyz, new_xyz, n, m):
     idx = torch.empty((M, nsample), dtype=torch.int32, device=xyz.device)
     with on_device(xyz):
         _lib.check(_lib.lib().mgar_ball_query_stack(B, M, float(radius), int(nsample), ptr(new_xyz), 0, ptr(xyz), xs, 0,
-                                                    int(n), int(m), ptr(idx), 1, stream_of(xyz)), "ball_query_uniform")
+                                                    int(n), int(m), ptr(idx), 1, 0, 0, stream_of(xyz)), "ball_query_uniform")
     return idx
 
 

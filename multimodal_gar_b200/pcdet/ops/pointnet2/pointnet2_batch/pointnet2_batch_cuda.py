@@ -22,7 +22,7 @@ def ball_query_wrapper(b, n, m, radius, nsample, new_xyz, xyz, idx):
     if b == 0 or m == 0:
         return 1
     return _call(xyz, "mgar_ball_query_stack", "ball_query_wrapper", b, b * m, float(radius), nsample, ptr(new_xyz), 0,
-                 ptr(xyz), 3, 0, n, m, ptr(idx), 2) if n > 0 else 1
+                 ptr(xyz), 3, 0, n, m, ptr(idx), 2, 0, 0) if n > 0 else 1
 
 
 def group_points_wrapper(b, c, n, npoints, nsample, points, idx, out):

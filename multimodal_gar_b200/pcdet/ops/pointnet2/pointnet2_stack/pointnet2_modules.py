@@ -50,6 +50,7 @@ class StackSAModuleMSG(nn.Module):
         self.pool_method = pool_method
         self.use_xyz = use_xyz
         self._packed = None
+        self._packed_key = None
         self.stage_mark = None   # optional callable(name): profiling hook between ball query and the MLP
         self.init_weights()
 
@@ -67,13 +68,24 @@ class StackSAModuleMSG(nn.Module):
         self._packed = None  # parameters may change: re-fold on the next eval forward
         return super().train(mode)
 
+    def _pack_key(self, device):
+        # every tensor the folded parameters are made of: storage and in-place version, so that load_state_dict(), an EMA
+        # swap or any in-place edit of a weight / running statistic re-folds (a stale cache would silently compute with
+        # the old numbers)
+        key = [str(device)]
+        for t in list(self.mlps.parameters()) + list(self.mlps.buffers()):
+            key.append((t.data_ptr(), t._version))
+        return tuple(key)
+
     def _pack(self, device):
-        if self._packed is None or self._packed[0][1].device != device:
+        key = self._pack_key(device)
+        if self._packed is None or self._packed_key != key:
             self._packed = []
             for m in self.mlps:
                 channels, params = sa_mlp_fused.pack_shared_mlp(m)
                 host = params.cpu().contiguous()
                 self._packed.append((channels, host.to(device), host))
+            self._packed_key = key
         return self._packed
 
     def forward(self, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features=None, empty_voxel_set_zeros=True):

@@ -16,9 +16,10 @@ def ball_query_wrapper(B, M, radius, nsample, new_xyz, new_xyz_batch_cnt, xyz, x
     need_dtype(torch.float32, new_xyz=new_xyz, xyz=xyz)
     need_dtype(torch.int32, new_xyz_batch_cnt=new_xyz_batch_cnt, xyz_batch_cnt=xyz_batch_cnt, idx=idx)
     with on_device(xyz):
+        ws, nb = _lib.stack_workspace(B, xyz.device)      # the binding owns the scratch (torch's allocator), SURVEY 8b
         _lib.check(_lib.lib().mgar_ball_query_stack(int(B), int(M), float(radius), int(nsample), ptr(new_xyz),
                                                     ptr(new_xyz_batch_cnt), ptr(xyz), 3, ptr(xyz_batch_cnt), 0, 0,
-                                                    ptr(idx), 0, stream_of(xyz)), "ball_query_wrapper")
+                                                    ptr(idx), 0, ptr(ws), nb, stream_of(xyz)), "ball_query_wrapper")
     return 1
 
 
@@ -28,9 +29,10 @@ def group_points_wrapper(B, M, C, nsample, features, features_batch_cnt, idx, id
     need_dtype(torch.float32, features=features, out=out)
     need_dtype(torch.int32, features_batch_cnt=features_batch_cnt, idx=idx, idx_batch_cnt=idx_batch_cnt)
     with on_device(features):
+        ws, nb = _lib.stack_workspace(B, features.device)
         _lib.check(_lib.lib().mgar_group_points_stack(int(B), int(M), int(C), int(nsample), ptr(features),
                                                       ptr(features_batch_cnt), ptr(idx), ptr(idx_batch_cnt), ptr(out),
-                                                      stream_of(features)), "group_points_wrapper")
+                                                      ptr(ws), nb, stream_of(features)), "group_points_wrapper")
     return 1
 
 
@@ -41,9 +43,10 @@ def group_points_grad_wrapper(B, M, C, N, nsample, grad_out, idx, idx_batch_cnt,
     need_dtype(torch.float32, grad_out=grad_out, grad_features=grad_features)
     need_dtype(torch.int32, idx=idx, idx_batch_cnt=idx_batch_cnt, features_batch_cnt=features_batch_cnt)
     with on_device(grad_out):
+        ws, nb = _lib.stack_workspace(B, grad_out.device)
         _lib.check(_lib.lib().mgar_group_points_grad_stack(int(B), int(M), int(C), int(N), int(nsample), ptr(grad_out),
                                                            ptr(idx), ptr(idx_batch_cnt), ptr(features_batch_cnt),
-                                                           ptr(grad_features), stream_of(grad_out)),
+                                                           ptr(grad_features), ptr(ws), nb, stream_of(grad_out)),
                    "group_points_grad_wrapper")
     return 1
 
@@ -104,9 +107,10 @@ def three_nn_wrapper(unknown, unknown_batch_cnt, known, known_batch_cnt, dist2, 
     need_dtype(torch.float32, unknown=unknown, known=known, dist2=dist2)
     need_dtype(torch.int32, unknown_batch_cnt=unknown_batch_cnt, known_batch_cnt=known_batch_cnt, idx=idx)
     with on_device(unknown):
+        ws, nb = _lib.stack_workspace(unknown_batch_cnt.numel(), unknown.device)
         _lib.check(_lib.lib().mgar_three_nn_stack(unknown_batch_cnt.numel(), unknown.shape[0], known.shape[0], ptr(unknown),
                                                   ptr(unknown_batch_cnt), ptr(known), ptr(known_batch_cnt), ptr(dist2),
-                                                  ptr(idx), stream_of(unknown)), "three_nn_wrapper")
+                                                  ptr(idx), ptr(ws), nb, stream_of(unknown)), "three_nn_wrapper")
 
 
 def three_interpolate_wrapper(features, idx, weight, out):

@@ -90,6 +90,8 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
                 raise _lib.MgarError("the tensor-core path needs params_host (contiguous CPU copy of params)")
             skip = out is None and skip_zero_groups and group_max is not None
             ws_bytes = int(L.mgar_sa_mlp_tc_workspace_bytes(M, int(group_size))) if skip else 0
+            if uniform is None:                  # ragged batches: room for the prefix arrays (the live walk needs `uniform`)
+                ws_bytes = max(ws_bytes, int(L.mgar_stack_workspace_bytes(B)))
             ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz.device) if ws_bytes else None
             _lib.check(L.mgar_sa_mlp_fwd_tc(
                 B, M, nsample, C_in, ptr(xyz), xyz.stride(0), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt),
@@ -101,10 +103,11 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
         else:
             if not xyz.is_contiguous() or (features is not None and not features.is_contiguous()) or group_max is not None:
                 raise _lib.MgarError("the fp32 path needs contiguous xyz / features and has no group_max output")
+            ws, nb = _lib.stack_workspace(B, xyz.device) if uniform is None else (None, 0)
             _lib.check(L.mgar_sa_mlp_fwd_fp32(
                 B, M, nsample, C_in, ptr(xyz), ptr(xyz_batch_cnt), ptr(new_xyz), ptr(new_xyz_batch_cnt), un, um,
                 ptr(features), ptr(idx), ptr(empty_mask), len(channels) - 1, ctypes.addressof(ch), ptr(params),
-                ptr(out), out.stride(0), 1 if pool_avg else 0, stream_of(xyz)), "sa_mlp_fwd")
+                ptr(out), out.stride(0), 1 if pool_avg else 0, ptr(ws), nb, stream_of(xyz)), "sa_mlp_fwd")
     return out if want_out else group_max
 
 
@@ -138,7 +141,10 @@ class SAMlpTrainFunction(torch.autograd.Function):
         if empty_mask is not None:
             empty_mask = empty_mask.to(torch.uint8).contiguous()
         ch = (ctypes.c_int * len(channels))(*channels)
+        # the training workspace, + the prefix arrays of ragged batches behind it (include/mgar_lidar.h)
         ws_bytes = train_workspace_bytes(M, nsample, channels, pool_avg)
+        if uniform is None:
+            ws_bytes = ((ws_bytes + 15) & ~15) + int(_lib.lib().mgar_stack_workspace_bytes(B))
         ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=xyz.device)
         out = torch.empty((M, channels[-1]), dtype=torch.float32, device=xyz.device)
         stats = torch.empty((2 * sum(channels[1:]),), dtype=torch.float32, device=xyz.device)

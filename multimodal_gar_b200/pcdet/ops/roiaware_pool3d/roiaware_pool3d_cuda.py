@@ -31,7 +31,13 @@ def points_in_boxes_cpu(boxes, pts, pts_indices):
     need_dtype(torch.float32, boxes=boxes, pts=pts)
     need_dtype(torch.int32, pts_indices=pts_indices)
     M, N = boxes.size(0), pts.size(0)
-    _lib.check(_lib.lib().mgar_points_in_boxes_mask_host(ptr(boxes), ptr(pts), ptr(pts_indices), M, N),
+    L = _lib.lib()
+    if not torch.cuda.is_available():
+        raise _lib.MgarError("points_in_boxes_cpu computes on the GPU (host buffers in and out): no CUDA device, no fallback")
+    nb = int(L.mgar_points_in_boxes_mask_host_workspace_bytes(M, N))
+    # device staging on the CURRENT device, from torch's caching allocator (the library allocates nothing)
+    ws = torch.empty((max(nb, 16),), dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
+    _lib.check(L.mgar_points_in_boxes_mask_host(ptr(boxes), ptr(pts), ptr(pts_indices), M, N, ptr(ws), nb),
                "points_in_boxes_cpu")
     return 1
 

@@ -238,3 +238,41 @@ def test_person_features_do_not_depend_on_storing_sa_features(cuda):
     want = st["sa_features"].view(3 * 40, 512, -1).max(dim=1).values
     want = want * (st["empty"].view(-1, 1) == 0)
     assert torch.equal(a.view(3 * 40, -1), want)
+
+
+def test_folded_batchnorm_cache_follows_the_parameters(cuda):
+    """The eval path folds BatchNorm into packed parameters and caches them: after load_state_dict() or an in-place edit
+    (no .train()/.eval() in between) the next forward must use the NEW numbers."""
+    pts, boxes, xyz, feat, bx = _inputs(4, 1, 16384, 8, cuda, density_scale=0.5)
+    a, b = _enc(cuda), _enc(cuda)
+    with torch.no_grad():
+        for mod in b.sa.mlps[0]:
+            if isinstance(mod, torch.nn.BatchNorm2d):
+                mod.weight.normal_(0.3, 1.0)            # mixed-sign (and near-zero) scales: the sign-folded W2 rows
+                mod.weight[0] = 0.0
+                mod.running_mean.normal_(0, 0.3)
+            if isinstance(mod, torch.nn.Conv2d):
+                mod.weight.mul_(1.7)
+        ya = a(xyz, feat, bx)                           # caches a's folded parameters
+        want = b(xyz, feat, bx)
+        assert not torch.equal(ya, want)
+        a.load_state_dict(b.state_dict())               # in-place copy_: same storages, new versions
+        assert torch.equal(a(xyz, feat, bx), want)
+        a.sa.mlps[0][1].running_var.mul_(2.0)           # in-place edit of a buffer
+        got = a(xyz, feat, bx)
+        assert not torch.equal(got, want)
+        c = _enc(cuda)
+        c.load_state_dict(a.state_dict())
+        assert torch.equal(c(xyz, feat, bx), got)
+        # and the mixed-sign / zero BatchNorm scales agree with the exact-fp32 kernel and the oracle
+        st = b(xyz, feat, bx, return_stages=True)
+    cxyz = np.ascontiguousarray(st["pooled"].cpu().numpy()[..., :3])
+    fps = st["fps_idx"].cpu().numpy()
+    new_xyz = np.take_along_axis(cxyz, fps[..., None].astype(np.int64), axis=1).reshape(-1, 3)
+    M, S, P = 8, 512, 512
+    import copy
+    want_sa = O.stack_sa_module_msg([copy.deepcopy(b.sa.mlps[0]).cpu()], [0.3], [32], cxyz.reshape(-1, 3), np.full(M, S, np.int32),
+                                    new_xyz, np.full(M, P, np.int32),
+                                    np.ascontiguousarray(st["pooled"].cpu().numpy()[..., 3:]).reshape(-1, 1))
+    scale = max(1.0, float(np.abs(want_sa).max()))
+    np.testing.assert_allclose(st["sa_features"].cpu().numpy(), want_sa, rtol=1e-5, atol=1e-5 * scale)
