@@ -91,7 +91,26 @@ class PointPersonEncoder(nn.Module):
     def forward(self, points, point_features, boxes, return_stages=False, mark=None):
         """`mark(name)` (optional) is called after each stage has been enqueued - bench.py records a
         CUDA event there to time the stages inside the step."""
-        mark = mark or (lambda name: None)
+        user_mark = mark or (lambda name: None)
+        nvtx = torch.cuda.nvtx if points.is_cuda else None
+
+        def mark(name):
+            # one NVTX range per stage (SURVEY section 5: the profiler hooks of the path) - a stage ends where `mark` is called
+            if nvtx is not None:
+                nvtx.range_pop()
+                nvtx.range_push("mgar:after_" + name)
+            user_mark(name)
+        if nvtx is not None:
+            nvtx.range_push("mgar:lidar_branch")
+            nvtx.range_push("mgar:begin")
+        try:
+            return self._forward(points, point_features, boxes, return_stages, mark)
+        finally:
+            if nvtx is not None:
+                nvtx.range_pop()
+                nvtx.range_pop()
+
+    def _forward(self, points, point_features, boxes, return_stages, mark):
         B, M = boxes.shape[0], boxes.shape[1]
         S, P = self.num_sampled_points, self.npoint
         if self.fused_canonical and os.environ.get("MGAR_POOL", "mask") == "mask":
