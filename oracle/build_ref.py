@@ -8,7 +8,7 @@ into this repo) with torch.utils.cpp_extension for sm_100, producing
     oracle/_ref/pointnet2_stack_cuda.so      (ball_query / group_points / FPS / voxel_query wrappers)
     oracle/_ref/pointnet2_batch_cuda.so      (batch-layout ball_query / group / gather / FPS / three_nn / interpolate)
 
-    oracle/_ref/pywrap/*.pyc                 (the reference's own Python wrappers - pointnet2_utils.py, pointnet2_modules.py,
+    oracle/_ref/pywrap/*.pycode                 (the reference's own Python wrappers - pointnet2_utils.py, pointnet2_modules.py,
                                               roiaware_pool3d_utils.py, roipoint_pool3d_utils.py, box_utils.py, common_utils.py,
                                               voxel_query_utils.py, voxel_pool_modules.py - BYTE-COMPILED, unmodified: the
                                               drop-in tests import them over the stand-in extension modules)
@@ -73,7 +73,7 @@ def build_pywrap():
     out = os.path.join(OUT, "pywrap")
     os.makedirs(out, exist_ok=True)
     for mod, rel in PYWRAP.items():
-        dst = os.path.join(out, mod + ".pyc")
+        dst = os.path.join(out, mod + ".pycode")
         if not os.path.exists(dst):
             py_compile.compile(os.path.join(os.path.dirname(REF_OPS), rel), cfile=dst, doraise=True)
 

@@ -1,5 +1,5 @@
 """Loads the REFERENCE's own, unmodified Python wrappers (byte-compiled by oracle/build_ref.py into
-oracle/_ref/pywrap/*.pyc; read straight from /root/reference when that tree is present) as a package whose extension
+oracle/_ref/pywrap/*.pycode (python bytecode; the extension is not .pyc because snapshots drop those); read straight from /root/reference when that tree is present) as a package whose extension
 modules are chosen by the caller: the stand-ins of this repo (`which='new'`) or the reference's compiled extensions
 (`which='ref'`).  Same Python, two native back ends - the drop-in contract of SURVEY 8b."""
 import importlib.machinery
@@ -73,7 +73,7 @@ def load(which):
         if os.path.exists(src):
             loader = importlib.machinery.SourceFileLoader(full, src)
         else:
-            loader = importlib.machinery.SourcelessFileLoader(full, os.path.join(PYWRAP, name + ".pyc"))
+            loader = importlib.machinery.SourcelessFileLoader(full, os.path.join(PYWRAP, name + ".pycode"))
         spec = importlib.util.spec_from_loader(full, loader)
         m = importlib.util.module_from_spec(spec)
         m.__package__ = parent
