@@ -92,8 +92,11 @@ MGAR_API int mgar_roipoint_pool(const float *xyz, const float *boxes, const floa
  * arguments and outputs as mgar_roipoint_pool, plus pooled_cnt (B,M) int32, optional: min(in-box points, S) - the
  * number of DISTINCT rows of each pooled cloud (the scheduling weight of mgar_fps_ball_query). */
 MGAR_API size_t mgar_box_mask_words(int N);
+/* workspace (optional, mgar_box_masks_workspace_bytes(B, M) bytes of device scratch, 0 when M > 255): the per-frame box
+ * grid is then built once per frame by a small kernel instead of once per CTA in shared memory (same outputs). */
+MGAR_API size_t mgar_box_masks_workspace_bytes(int B, int M);
 MGAR_API int mgar_box_masks(const float *boxes_first, const float *boxes_pool, const float *pts, int *box_idx,
-                            unsigned *mask, int B, int M, int N, void *stream);
+                            unsigned *mask, int B, int M, int N, void *workspace, size_t workspace_bytes, void *stream);
 MGAR_API int mgar_roipoint_pool_from_masks(const float *xyz, const float *boxes, const float *feat, const unsigned *mask,
                                            float *pooled, int *empty, int *pts_idx, int *pooled_cnt, int B, int N, int M,
                                            int S, int C, int canonical, void *stream);

@@ -27,7 +27,8 @@ SIGNATURES = {
     "mgar_points_in_boxes_mask_host": [_p, _p, _p, _i, _i, _p, ctypes.c_size_t],
     "mgar_roipoint_pool": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
     "mgar_box_mask_words": [_i],
-    "mgar_box_masks": [_p, _p, _p, _p, _p, _i, _i, _i, _p],
+    "mgar_box_masks_workspace_bytes": [_i, _i],
+    "mgar_box_masks": [_p, _p, _p, _p, _p, _i, _i, _i, _p, ctypes.c_size_t, _p],
     "mgar_roipoint_pool_from_masks": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
     "mgar_roiaware_pool3d_workspace_bytes": [_i, _i],
     "mgar_roiaware_pool3d_fwd": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p],
@@ -97,6 +98,7 @@ def lib():
         L.mgar_sa_mlp_train_workspace_bytes_for.restype = ctypes.c_size_t
         L.mgar_box_mask_words.restype = ctypes.c_size_t
         L.mgar_stack_workspace_bytes.restype = ctypes.c_size_t
+        L.mgar_box_masks_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_points_in_boxes_mask_host_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_sa_mlp_tc_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_fps_ball_query_workspace_bytes.restype = ctypes.c_size_t

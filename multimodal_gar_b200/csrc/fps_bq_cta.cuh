@@ -74,6 +74,25 @@ __device__ __forceinline__ uint32_t bq_pin(uint32_t v) {
     return r;
 }
 
+// ---- bulk asynchronous copy (the TMA engine's 1-D form): one instruction moves a cloud's tile global -> shared -------
+__device__ __forceinline__ void bq_mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bq_bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bq_mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+
 template <int PPL>
 __device__ __forceinline__ void bq_store_masks(int on, uint32_t a, const unsigned (&hb)[PPL]) {
     if constexpr (PPL >= 4) {
@@ -97,6 +116,7 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     __shared__ __align__(16) unsigned s_key[2][W > 1 ? W : 2][2];    // per parity and warp: (max distance bits, ~rank)
     __shared__ __align__(16) unsigned s_ring[2 * kBqRing][16];       // hit masks of the last 16 centroids
     __shared__ int s_row0[64];
+    __shared__ __align__(8) unsigned long long s_mbar;
     float4 *sp = bq_sm4;                                   // [n] staged cloud
     int *sidx = reinterpret_cast<int *>(sp + n);           // [m] sampled indices
     int *rows = sidx + m;                                  // [W][2][K] rows being assembled
@@ -109,12 +129,18 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     ball_idx += (size_t)cloud * m * K;
 
     if (xs == 4 && (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) {
-        for (int k = tid; k < n; k += W * 32) sp[k] = __ldg(reinterpret_cast<const float4 *>(xyz) + k);
+        // the cloud is one contiguous tile of n x 16 bytes (the xyz | feature rows of the pooled array): staged by ONE
+        // bulk asynchronous copy (cp.async.bulk, the TMA engine) that signals an mbarrier - no per-thread LDG + STS
+        const uint32_t bar = bq_smem_u32(&s_mbar);
+        if (tid == 0) bq_mbar_init(bar, 1);
+        __syncthreads();
+        if (tid == 0) bq_bulk_load(bq_smem_u32(sp), xyz, (uint32_t)(n * sizeof(float4)), bar);
+        bq_mbar_wait(bar, 0);
     } else {
         for (int k = tid; k < n; k += W * 32)
             sp[k] = make_float4(xyz[(size_t)k * xs], xyz[(size_t)k * xs + 1], xyz[(size_t)k * xs + 2], 0.f);
+        __syncthreads();
     }
-    __syncthreads();
 
     const float r2 = __fmul_rn(radius, radius);
     const int rank0 = (int)bq_pin((uint32_t)((brev_n<5>(lane) << NB) | (w * PPL)));

@@ -145,7 +145,7 @@ extern "C" int mgar_roiaware_pool3d_fwd(const float *rois, const float *pts, con
     if (pts_num > 0) {
         MGAR_REQUIRE(rois && pts && workspace && (pts_feature || channels == 0), "roiaware_pool3d: null pointer");
         unsigned *mask = (unsigned *)workspace;
-        const int rc = mgar_box_masks(nullptr, rois, pts, nullptr, mask, 1, boxes_num, pts_num, stream);
+        const int rc = mgar_box_masks(nullptr, rois, pts, nullptr, mask, 1, boxes_num, pts_num, nullptr, 0, stream);
         if (rc != MGAR_OK) return rc;
         roiaware_collect_kernel<<<div_up(boxes_num, kRaWarps), kRaWarps * 32, 0, st>>>(
             rois, pts, mask, pts_idx_of_voxels, boxes_num, pts_num, (int)mgar_box_mask_words(pts_num), max_pts_each_voxel,

@@ -343,6 +343,137 @@ box_mask_grid_kernel(const float *__restrict__ boxes, const float *__restrict__ 
     }
 }
 
+// ---- the same pass with the box grid built ONCE PER FRAME -----------------------------------------------------------
+// box_mask_grid_kernel rebuilds the 64 x 64 grid in each of a frame's 16 CTAs (shared-memory atomics, two barriers, 52 KB
+// of shared memory -> 3 CTAs per SM, 31 % occupancy, 1.3 TB/s).  Here a one-CTA-per-frame kernel builds the frame's
+// grid in caller scratch (mgar_box_masks_workspace_bytes: per frame 4096 cell counts, 4096 x 8 box ids, the
+// pre-processed boxes, an overflow flag), and the streaming kernel only reads it: the cell of a point through the
+// read-only path (a frame's 36 KB of cells stay in L1 / L2), the boxes from a 1.3 KB shared-memory copy.  No grid build,
+// no barrier but the one after the box copy, ~2 KB of shared memory: the SM is full of warps with loads in flight.
+struct FrameGrid {                      // layout of one frame's scratch (bytes)
+    static __host__ __device__ size_t cnt_off() { return 0; }
+    static __host__ __device__ size_t ids_off() { return (size_t)kGridN * kGridN; }
+    static __host__ __device__ size_t flag_off() { return ids_off() + (size_t)kGridN * kGridN * kGridCap; }
+    static __host__ __device__ size_t box_off() { return flag_off() + 16; }
+    static __host__ __device__ size_t bytes(int M) { return (box_off() + (size_t)M * sizeof(BoxP) + 255) & ~(size_t)255; }
+};
+
+__global__ void __launch_bounds__(kMaskThreads)
+frame_grid_build_kernel(const float *__restrict__ boxes, unsigned char *__restrict__ ws, int M) {
+    extern __shared__ int grid_sm[];
+    int *scnt = grid_sm;                                                              // [cells]
+    __shared__ int s_overflow;
+    const int b = blockIdx.x;
+    boxes += (size_t)b * M * 7;
+    ws += (size_t)b * FrameGrid::bytes(M);
+    unsigned char *gcnt = ws + FrameGrid::cnt_off();
+    unsigned char *gids = ws + FrameGrid::ids_off();
+    BoxP *gbox = reinterpret_cast<BoxP *>(ws + FrameGrid::box_off());
+    for (int i = threadIdx.x; i < kGridN * kGridN; i += kMaskThreads) scnt[i] = 0;
+    if (threadIdx.x == 0) s_overflow = 0;
+    __syncthreads();
+    for (int k = threadIdx.x; k < M; k += kMaskThreads) {
+        const BoxP bp = make_boxp<false>(boxes + (size_t)k * 7, nullptr);
+        gbox[k] = bp;
+        const float R = sqrtf(bp.tx * bp.tx + bp.ty * bp.ty) * 1.001f + 1e-6f;
+        const int x0 = grid_cell(bp.cx - R), x1 = grid_cell(bp.cx + R), y0 = grid_cell(bp.cy - R), y1 = grid_cell(bp.cy + R);
+        if (!(R == R) || !(bp.cx == bp.cx) || !(bp.cy == bp.cy) || (x1 - x0 + 1) * (y1 - y0 + 1) > 64) {
+            s_overflow = 1;                                            // NaN box or a huge one: exhaustive loop
+        } else {
+            for (int cy = y0; cy <= y1; cy++)
+                for (int cx = x0; cx <= x1; cx++) {
+                    const int old = atomicAdd(&scnt[cy * kGridN + cx], 1);
+                    if (old >= kGridCap) s_overflow = 1;
+                    else gids[(size_t)(cy * kGridN + cx) * kGridCap + old] = (unsigned char)k;
+                }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < kGridN * kGridN; i += kMaskThreads) gcnt[i] = (unsigned char)min(scnt[i], kGridCap);
+    if (threadIdx.x == 0) *reinterpret_cast<int *>(ws + FrameGrid::flag_off()) = s_overflow;
+}
+
+constexpr int kGridLIters = 2;                              // point tiles (1024 points each) per CTA
+__global__ void __launch_bounds__(kMaskThreads)
+box_mask_framegrid_kernel(const unsigned char *__restrict__ ws, const float *__restrict__ pts, int *__restrict__ box_idx,
+                          unsigned *__restrict__ mask, int M, int N, int W, int vec_ok) {
+    extern __shared__ int grid_sm[];
+    BoxP *sbox = reinterpret_cast<BoxP *>(grid_sm);                                   // [M]
+    const int b = blockIdx.y;
+    ws += (size_t)b * FrameGrid::bytes(M);
+    const unsigned char *gcnt = ws + FrameGrid::cnt_off();
+    const uint2 *gids = reinterpret_cast<const uint2 *>(ws + FrameGrid::ids_off());  // 8 ids of a cell = one 8-byte load
+    const int overflow = __ldg(reinterpret_cast<const int *>(ws + FrameGrid::flag_off()));
+    pts += (size_t)b * N * 3;
+    mask += (size_t)b * M * W;
+    {
+        const float4 *src = reinterpret_cast<const float4 *>(ws + FrameGrid::box_off());
+        float4 *dst = reinterpret_cast<float4 *>(sbox);
+        for (int i = threadIdx.x; i < M * 2; i += kMaskThreads) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    for (int it = 0; it < kGridLIters; it++) {
+        const long long p0 = (((long long)blockIdx.x * kGridLIters + it) * kMaskThreads + threadIdx.x) * 4;
+        const int n_valid = p0 >= N ? 0 : (N - p0 >= 4 ? 4 : (int)(N - p0));
+        float x[4], y[4], z[4];
+        if (vec_ok && n_valid == 4) {
+            const float4 *v = reinterpret_cast<const float4 *>(pts + p0 * 3);
+            const float4 a = __ldg(v), bb = __ldg(v + 1), c = __ldg(v + 2);
+            x[0] = a.x; y[0] = a.y; z[0] = a.z;   x[1] = a.w; y[1] = bb.x; z[1] = bb.y;
+            x[2] = bb.z; y[2] = bb.w; z[2] = c.x; x[3] = c.y; y[3] = c.z; z[3] = c.w;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const bool ok = j < n_valid;
+                x[j] = ok ? __ldg(pts + (p0 + j) * 3 + 0) : nanf("");
+                y[j] = ok ? __ldg(pts + (p0 + j) * 3 + 1) : nanf("");
+                z[j] = ok ? __ldg(pts + (p0 + j) * 3 + 2) : nanf("");
+            }
+        }
+        int res[4] = {-1, -1, -1, -1};
+        if (overflow) {
+            for (int k = 0; k < M; k++) {
+                const BoxP bp = sbox[k];
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if (in_box<false>(x[j], y[j], z[j], bp)) {
+                        if (res[j] < 0) res[j] = k;
+                        atomicOr(mask + (size_t)k * W + ((p0 + j) >> 5), 1u << ((p0 + j) & 31));
+                    }
+            }
+        } else {
+            int cell[4], cnt[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {                     // the four cell counts in flight together
+                cell[j] = grid_cell(y[j]) * kGridN + grid_cell(x[j]);
+                cnt[j] = __ldg(gcnt + cell[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                if (cnt[j] == 0) continue;
+                const uint2 id8 = __ldg(gids + cell[j]);
+                for (int q = 0; q < cnt[j]; q++) {
+                    const int k = ((q < 4 ? id8.x : id8.y) >> (8 * (q & 3))) & 0xff;
+                    if (in_box<false>(x[j], y[j], z[j], sbox[k])) {
+                        res[j] = res[j] < 0 ? k : min(res[j], k);
+                        atomicOr(mask + (size_t)k * W + ((p0 + j) >> 5), 1u << ((p0 + j) & 31));
+                    }
+                }
+            }
+        }
+        if (box_idx) {
+            int *box_idx_f = box_idx + (size_t)b * N;
+            if (vec_ok && n_valid == 4) {
+                *reinterpret_cast<int4 *>(box_idx_f + p0) = make_int4(res[0], res[1], res[2], res[3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if (j < n_valid) box_idx_f[p0 + j] = res[j];
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 pool_from_mask_kernel(const float *__restrict__ xyz, const float *__restrict__ boxes, const float *__restrict__ feat,
                       const unsigned *__restrict__ mask, float *__restrict__ pooled, int *__restrict__ empty,
@@ -422,8 +553,14 @@ extern "C" int mgar_roipoint_pool(const float *xyz, const float *boxes, const fl
 
 extern "C" size_t mgar_box_mask_words(int N) { return (size_t)((N + 31) / 32); }
 
+// scratch of the per-frame box grids (optional: without it every CTA builds its frame's grid in shared memory)
+extern "C" size_t mgar_box_masks_workspace_bytes(int B, int M) {
+    if (B <= 0 || M <= 0 || M > kGridMaxBoxes) return 0;
+    return (size_t)B * FrameGrid::bytes(M);
+}
+
 extern "C" int mgar_box_masks(const float *boxes_first, const float *boxes_pool, const float *pts, int *box_idx,
-                              unsigned *mask, int B, int M, int N, void *stream) {
+                              unsigned *mask, int B, int M, int N, void *workspace, size_t workspace_bytes, void *stream) {
     MGAR_REQUIRE(B >= 0 && M >= 0 && N >= 0, "box_masks: negative size");
     if (B == 0 || N == 0 || M == 0) {
         if (box_idx && B > 0 && N > 0) MGAR_CUDA(cudaMemsetAsync(box_idx, 0xff, (size_t)B * N * 4, (cudaStream_t)stream));
@@ -438,7 +575,16 @@ extern "C" int mgar_box_masks(const float *boxes_first, const float *boxes_pool,
     const int vec_ok = ((reinterpret_cast<uintptr_t>(pts) & 15) == 0) && (!box_idx || (reinterpret_cast<uintptr_t>(box_idx) & 15) == 0) &&
                        (N % 4 == 0);
     dim3 grid(div_up(N, kMaskThreads * 4), B);
-    if ((!box_idx || boxes_first == boxes_pool) && M <= kGridMaxBoxes && !getenv("MGAR_NO_BOX_GRID"))
+    static_assert(sizeof(BoxP) == 32, "the frame grid copies boxes as two float4");
+    if ((!box_idx || boxes_first == boxes_pool) && M <= kGridMaxBoxes && !getenv("MGAR_NO_BOX_GRID") && workspace &&
+        workspace_bytes >= mgar_box_masks_workspace_bytes(B, M) && !getenv("MGAR_NO_FRAME_GRID")) {
+        frame_grid_build_kernel<<<B, kMaskThreads, kGridN * kGridN * sizeof(int), st>>>(boxes_pool, static_cast<unsigned char *>(workspace), M);
+        count_launch();
+        grid.x = div_up(N, kMaskThreads * 4 * kGridLIters);
+        box_mask_framegrid_kernel<<<grid, kMaskThreads, (size_t)M * sizeof(BoxP), st>>>(static_cast<const unsigned char *>(workspace),
+                                                                                          pts, box_idx, mask, M, N, W, vec_ok);
+    }
+    else if ((!box_idx || boxes_first == boxes_pool) && M <= kGridMaxBoxes && !getenv("MGAR_NO_BOX_GRID"))
     {
         MGAR_CUDA(cudaFuncSetAttribute(box_mask_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGridSmem));
         grid.x = div_up(N, kMaskThreads * 4 * kGridIters);

@@ -92,9 +92,11 @@ def box_masks(points, boxes, pool_boxes=None, want_box_idx=True):
     pool_boxes = boxes if pool_boxes is None else pool_boxes
     box_idx = torch.empty((B, N), dtype=torch.int32, device=points.device) if want_box_idx else None
     mask = torch.empty((B, M, (N + 31) // 32), dtype=torch.int32, device=points.device)
+    nb = int(_lib.lib().mgar_box_masks_workspace_bytes(B, M))
+    ws = torch.empty((nb,), dtype=torch.uint8, device=points.device) if nb else None     # per-frame box grids
     with on_device(points):
         _lib.check(_lib.lib().mgar_box_masks(ptr(boxes), ptr(pool_boxes), ptr(points), ptr(box_idx), ptr(mask), B, M, N,
-                                             stream_of(points)), "box_masks")
+                                             ptr(ws), nb, stream_of(points)), "box_masks")
     return box_idx, mask
 
 

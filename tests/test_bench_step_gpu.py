@@ -37,7 +37,7 @@ def step(cuda):
 
 
 def test_default_step_is_the_six_kernel_path_and_matches_the_all_rows_path(step):
-    assert step["launches"] == 6, "expected box masks, pool, cloud order, FPS+ball query, live tiles, MLP; got %d launches" % step["launches"]
+    assert step["launches"] == 7, "expected frame grid, box masks, pool, cloud order, FPS+ball query, live tiles, MLP; got %d launches" % step["launches"]
     assert step["person"].shape == (F, bench.CFG["M"], 128)
     assert torch.equal(step["person"], step["st"]["person_features"])
     sa = step["st"]["sa_features"].view(F * bench.CFG["M"], bench.CFG["P"], 128)
