@@ -308,6 +308,18 @@ MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float
                                 float *group_max, int group_size, const int *group_zero, const int *group_live_cnt,
                                 int pool_avg, void *workspace, size_t workspace_bytes, void *stream);
 
+/* ---- fp32-faithful GEMM on tcgen05 (3xTF32) --------------------------------------------------------------- */
+
+/* C (M,N) = act(A (M,K) . Bt (N,K)^T + bias): the dense linears around the hot path that the reference runs through
+ * torch (cuBLAS fp32): FusionAttention_mat's WQ/WK/WV products and FFN linears (model/gat_model.py:466-511), the
+ * 128 -> 512 LiDAR embedding (:883-894).  A row-major (lda floats per row), Bt = the weight as nn.Linear stores it
+ * ((out, in) row-major: K-major), bias (N) or NULL, relu != 0 applies max(., 0).  fp32 in / out; every product is
+ * evaluated as lo.hi + hi.lo + hi.hi of tf32 halves with fp32 accumulation (error ~2^-22 relative per product).
+ * Shapes: N % 128 == 0, K % 32 == 0 (mgar_gemm_tf32x3_supported); operands 16-byte aligned, ld* % 4 == 0. */
+MGAR_API int mgar_gemm_tf32x3_supported(int M, int N, int K);
+MGAR_API int mgar_gemm_tf32x3(int M, int N, int K, const float *A, int lda, const float *Bt, int ldb, const float *bias,
+                              int relu, float *C, int ldc, void *stream);
+
 /* ---- training: the same module with BatchNorm batch statistics, and its backward pass ------------------- */
 
 /* StackSAModuleMSG.forward in train() for ONE scale (pointnet2_modules.py:78-112; BatchNorm2d in training mode:

@@ -48,6 +48,8 @@ SIGNATURES = {
     "mgar_three_interpolate_grad_stack": [_i, _i, _p, _p, _p, _p, _p],
     "mgar_dafm_attention": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p],
     "mgar_dafm_add_layernorm": [_i, _i, _p, _p, _p, _p, _p, _f, _p, _p],
+    "mgar_gemm_tf32x3_supported": [_i, _i, _i],
+    "mgar_gemm_tf32x3": [_i, _i, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p],
     "mgar_fps_ball_query_supported": [_i, _i, _i, _i],
     "mgar_fps_ball_query_workspace_bytes": [_i],
     "mgar_fps_ball_query": [_i, _i, _i, _p, _i, _f, _i, _p, _p, _p, _p, _i, _p, _p, ctypes.c_size_t, _p],

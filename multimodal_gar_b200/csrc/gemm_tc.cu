@@ -1,0 +1,197 @@
+// fp32-faithful GEMM on tcgen05 (3xTF32):  C (M,N) = act(A (M,K) . Bt (N,K)^T + bias),  fp32 in, fp32 out.
+//
+// The dense contractions AROUND the LiDAR hot path that the reference leaves to cuBLAS / cuDNN in fp32:
+//   * the ten 512 x 512 linears of every FusionAttention_mat module (model/gat_model.py:466-511: WQ/WK/WV of both
+//     streams and the two FFN linears per stream) - batched here as (B*n, 512) x (512, 1536 | 512) products,
+//   * the 128 -> 512 embedding of the LiDAR feature (gat_model.py:883-894),
+//   * the [C_in -> C_out] 1x1 convolutions of NeighborVoxelSAModuleMSG (voxel_pool_modules.py:70-130) when their widths
+//     are multiples of 32 / 128.
+// torch runs them as SIMT sgemm (cutlass3x_sm100_simt_sgemm, profiles/r01_launches_config3.md: 21 % of the configs[2] step).
+//
+// Scheme (the one of sa_mlp_tc.cu, as a plain GEMM): every fp32 operand value is split v = hi + lo with hi = v truncated to
+// tf32 (exact: lo is the 13 dropped mantissa bits) and the product is accumulated as lo.hi + hi.lo + hi.hi in the tensor
+// core's fp32 accumulator; the dropped lo.lo term is 2^-22 relative.  kind::tf32, M = 128 (TMEM lanes = rows of A),
+// N = 128 (columns), K = 8 per instruction, both operands K-major in shared memory with the 128-byte swizzle (a K chunk =
+// 32 floats = one 128-byte row; hi and lo tiles of 16 KB each per operand), fp32 accumulator in 128 TMEM columns.
+//
+// CTA = one 128 x 128 output tile, 9 warps:  0-3 epilogue (tcgen05.ld, bias, ReLU, 512-byte row segments to global) |
+// 4 TMEM allocation + MMA issue (one elected lane) | 5-8 producers: thread = one row of the A tile and one row of the Bt
+// tile; it streams its 128-byte row segments of the next K chunk into registers (global -> register prefetch one chunk
+// ahead), splits them and stores hi / lo into a 3-stage shared-memory ring (full / empty mbarriers; the empty barrier is
+// armed by tcgen05.commit once the MMAs of the stage have read it).
+#include <stdlib.h>
+
+#include "mgar_common.cuh"
+#include "tc_ptx.cuh"
+
+namespace mgar {
+namespace {
+
+constexpr int kGmThreads = 9 * 32;
+constexpr int kGmStages = 3;
+constexpr int kGmKC = 32;                                 // floats per K chunk (one 128-byte swizzled row)
+constexpr uint32_t kGmTile = 128 * kGmKC * 4;             // 16 KB: one 128 x 32 fp32 tile
+constexpr uint32_t kGmStageBytes = 4 * kGmTile;           // A hi, A lo, B hi, B lo
+constexpr uint32_t kGmSmem = kGmStages * kGmStageBytes + 1024;
+
+__device__ __forceinline__ uint32_t gm_off(int r, int c16) {      // 16-byte chunk c16 of row r in a swizzled tile
+    return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c16 ^ (r & 7)) << 4));
+}
+
+__global__ void __launch_bounds__(kGmThreads, 1)
+gemm_tf32x3_kernel(int M, int N, int K, const float *__restrict__ A, int lda, const float *__restrict__ Bt, int ldb,
+                   const float *__restrict__ bias, int relu, float *__restrict__ C, int ldc) {
+    extern __shared__ uint8_t gm_smem[];
+    __shared__ __align__(8) uint64_t s_bar[2 * kGmStages + 1];
+    __shared__ uint32_t s_tmem;
+    const uint32_t base = (smem_u32(gm_smem) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024 B alignment
+    const uint32_t bar0 = smem_u32(s_bar);
+    auto FULL = [&](int s) { return bar0 + 8u * s; };
+    auto EMPTY = [&](int s) { return bar0 + 8u * (kGmStages + s); };
+    const uint32_t TFULL = bar0 + 8u * (2 * kGmStages);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n0 = blockIdx.x * 128, m0 = blockIdx.y * 128;
+    const int n_chunks = K / kGmKC;
+
+    if (tid == 0) {
+        for (int s = 0; s < kGmStages; s++) { mbar_init(FULL(s), 128); mbar_init(EMPTY(s), 1); }
+        mbar_init(TFULL, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(128u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (warp < 4) {
+        // ===== epilogue: thread = output row (TMEM lane), 4 x 32 columns ======================================
+        mbar_wait(TFULL, 0);
+        tc_fence_after();
+        const int m = m0 + warp * 32 + lane;
+        const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+        for (int q = 0; q < 4; q++) {
+            uint32_t v[32];
+            tc_ld32(taddr + (uint32_t)(q * 32), v);
+            tc_wait_ld();
+            if (m < M) {
+                float *out = C + (size_t)m * ldc + n0 + q * 32;
+                const float *bq = bias ? bias + n0 + q * 32 : nullptr;
+#pragma unroll
+                for (int c = 0; c < 32; c += 4) {
+                    float4 o = make_float4(__uint_as_float(v[c]), __uint_as_float(v[c + 1]), __uint_as_float(v[c + 2]),
+                                           __uint_as_float(v[c + 3]));
+                    if (bq) {
+                        const float4 bb = __ldg(reinterpret_cast<const float4 *>(bq + c));
+                        o.x = __fadd_rn(o.x, bb.x); o.y = __fadd_rn(o.y, bb.y); o.z = __fadd_rn(o.z, bb.z); o.w = __fadd_rn(o.w, bb.w);
+                    }
+                    if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+                    *reinterpret_cast<float4 *>(out + c) = o;
+                }
+            }
+        }
+        tc_fence_before();
+    } else if (warp == 4) {
+        // ===== MMA issue: per K chunk 3 terms x 4 K-steps of 128 x 128 x 8 ===================================
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        for (int kc = 0; kc < n_chunks; kc++) {
+            const int s = kc % kGmStages, j = kc / kGmStages;
+            mbar_wait(FULL(s), j & 1);
+            tc_fence_after();
+            const uint32_t st = base + (uint32_t)s * kGmStageBytes;
+            const uint64_t a_hi = make_desc(st), a_lo = make_desc(st + kGmTile);
+            const uint64_t b_hi = make_desc(st + 2 * kGmTile), b_lo = make_desc(st + 3 * kGmTile);
+            if (elect_one()) {
+#pragma unroll
+                for (int term = 0; term < 3; term++) {          // small terms first
+                    const uint64_t ad = term == 0 ? a_lo : a_hi;
+                    const uint64_t bd = term == 1 ? b_lo : b_hi;
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++)
+                        tc_mma_tf32(tmem, ad + (uint64_t)((kk * 32) >> 4), bd + (uint64_t)((kk * 32) >> 4), idesc,
+                                    (kc | term | kk) ? 1u : 0u);
+                }
+                tc_commit(EMPTY(s));
+                if (kc == n_chunks - 1) tc_commit(TFULL);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ===== producers: row r of the A tile and row r of the Bt tile ========================================
+        const int r = (warp - 5) * 32 + lane;
+        const bool a_ok = m0 + r < M;
+        const float4 *arow = reinterpret_cast<const float4 *>(A + (size_t)(a_ok ? m0 + r : 0) * lda);
+        const float4 *brow = reinterpret_cast<const float4 *>(Bt + (size_t)(n0 + r) * ldb);
+        float4 a[8], b[8];
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            a[c] = a_ok ? __ldg(arow + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            b[c] = __ldg(brow + c);
+        }
+        for (int kc = 0; kc < n_chunks; kc++) {
+            const int s = kc % kGmStages, j = kc / kGmStages;
+            float4 an[8], bn[8];
+            if (kc + 1 < n_chunks) {                            // next chunk in flight while this one is split and stored
+#pragma unroll
+                for (int c = 0; c < 8; c++) {
+                    an[c] = a_ok ? __ldg(arow + (kc + 1) * 8 + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    bn[c] = __ldg(brow + (kc + 1) * 8 + c);
+                }
+            }
+            mbar_wait(EMPTY(s), (j & 1) ^ 1);
+            const uint32_t st = base + (uint32_t)s * kGmStageBytes;
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const uint32_t off = gm_off(r, c);
+                const float va[4] = {a[c].x, a[c].y, a[c].z, a[c].w}, vb[4] = {b[c].x, b[c].y, b[c].z, b[c].w};
+                sts_split4(st + off, st + kGmTile + off, va);
+                sts_split4(st + 2 * kGmTile + off, st + 3 * kGmTile + off, vb);
+            }
+            fence_async_smem();                                 // generic-proxy stores -> visible to the tensor core
+            mbar_arrive(FULL(s));
+            if (kc + 1 < n_chunks) {
+#pragma unroll
+                for (int c = 0; c < 8; c++) { a[c] = an[c]; b[c] = bn[c]; }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(128u) : "memory");
+    }
+}
+
+}  // namespace
+}  // namespace mgar
+
+using namespace mgar;
+
+extern "C" int mgar_gemm_tf32x3_supported(int M, int N, int K) {
+    return M >= 1 && N >= 128 && N % 128 == 0 && K >= 32 && K % 32 == 0 && !getenv("MGAR_NO_TC_GEMM");
+}
+
+extern "C" int mgar_gemm_tf32x3(int M, int N, int K, const float *A, int lda, const float *Bt, int ldb, const float *bias,
+                                int relu, float *C, int ldc, void *stream) {
+    MGAR_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm_tf32x3: negative size");
+    if (M == 0 || N == 0) return MGAR_OK;
+    MGAR_REQUIRE(mgar_gemm_tf32x3_supported(M, N, K), "gemm_tf32x3: unsupported shape M=%d N=%d K=%d (N %% 128 == 0, K %% 32 == 0; "
+                 "ask mgar_gemm_tf32x3_supported first)", M, N, K);
+    MGAR_REQUIRE(A && Bt && C, "gemm_tf32x3: null pointer");
+    MGAR_REQUIRE(lda >= K && ldb >= K && ldc >= N && lda % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0,
+                 "gemm_tf32x3: leading dimensions must cover the rows and be multiples of 4 floats");
+    MGAR_REQUIRE(((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(Bt) | reinterpret_cast<uintptr_t>(C) |
+                   reinterpret_cast<uintptr_t>(bias)) & 15) == 0, "gemm_tf32x3: operands must be 16-byte aligned");
+    MGAR_REQUIRE((M + 127) / 128 <= 65535, "gemm_tf32x3: M=%d exceeds grid.y", M);
+    MGAR_CUDA(cudaFuncSetAttribute(gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGmSmem));
+    dim3 grid(N / 128, (M + 127) / 128);
+    gemm_tf32x3_kernel<<<grid, kGmThreads, kGmSmem, (cudaStream_t)stream>>>(M, N, K, A, lda, Bt, ldb, bias, relu, C, ldc);
+    count_launch();
+    return check_launch("gemm_tf32x3");
+}

@@ -64,6 +64,8 @@ class FusionAttentionMat(nn.Module):
             setattr(self, "LN_%s_1" % s, nn.LayerNorm([out_dim]))
             setattr(self, "FFN_%s" % s, nn.Sequential(nn.Linear(out_dim, out_dim), nn.ReLU(), nn.Linear(out_dim, out_dim)))
             setattr(self, "LN_%s_2" % s, nn.LayerNorm([out_dim]))
+        from . import tc_gemm
+        self._wl, self._wr = tc_gemm.CachedTranspose(), tc_gemm.CachedTranspose()   # K-major copies of the projections
 
     def _stream(self, q_src, kv_src, E, valid, s):
         WQ, WK, WV = getattr(self, "WQ_" + s), getattr(self, "WK_" + s), getattr(self, "WV_" + s)
@@ -85,12 +87,19 @@ class FusionAttentionMat(nn.Module):
     def _fused(self, R, L, E, valid):
         """Both streams through libmgar_lidar.so: 2 projection GEMMs, mgar_dafm_attention, FFN GEMMs,
         mgar_dafm_add_layernorm per stream."""
-        from . import _lib
+        from . import _lib, tc_gemm
         from ._torch_glue import on_device, ptr, stream_of
         B, n, D = R.shape
         R, L, E = R.contiguous(), L.contiguous(), E.contiguous()
-        PL = L.view(B * n, D) @ torch.cat([self.WQ_r, self.WK_l, self.WV_l], dim=1)     # Q_r | K_l | V_l
-        PR = R.view(B * n, D) @ torch.cat([self.WK_r, self.WV_r, self.WQ_l], dim=1)     # K_r | V_r | Q_l
+        # the six projections as two (B*n, D) x (D, 3D) products, the four FFN linears as they are: on tcgen05 (3xTF32,
+        # csrc/gemm_tc.cu) when the widths fit the kernel, else torch's fp32 GEMM (MGAR_NO_TC_GEMM=1 forces that)
+        tc = tc_gemm.usable(L, 3 * D, D)
+        if tc:
+            PL = tc_gemm.linear(L.view(B * n, D), self._wl.get((self.WQ_r, self.WK_l, self.WV_l)))   # Q_r | K_l | V_l
+            PR = tc_gemm.linear(R.view(B * n, D), self._wr.get((self.WK_r, self.WV_r, self.WQ_l)))   # K_r | V_r | Q_l
+        else:
+            PL = L.view(B * n, D) @ torch.cat([self.WQ_r, self.WK_l, self.WV_l], dim=1)
+            PR = R.view(B * n, D) @ torch.cat([self.WK_r, self.WV_r, self.WQ_l], dim=1)
         X = torch.empty((2, B, n, D), dtype=torch.float32, device=R.device)
         vmask = None if valid is None else valid.contiguous()
         pl, pr, f4 = PL.data_ptr(), PR.data_ptr(), 4 * D
@@ -109,7 +118,11 @@ class FusionAttentionMat(nn.Module):
             outs = []
             for i, s in enumerate(("r", "l")):
                 x = X[i].view(B * n, D)
-                y = getattr(self, "FFN_" + s)(x)
+                ffn = getattr(self, "FFN_" + s)
+                if tc:
+                    y = tc_gemm.linear(tc_gemm.linear(x, ffn[0].weight, ffn[0].bias, relu=True), ffn[2].weight, ffn[2].bias)
+                else:
+                    y = ffn(x)
                 ln = getattr(self, "LN_%s_2" % s)
                 o = torch.empty_like(x)
                 _lib.check(L_.mgar_dafm_add_layernorm(B * n, D, ptr(x), ptr(y), ptr(ln.weight), ptr(ln.bias), ptr(vmask),

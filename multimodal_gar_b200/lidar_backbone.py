@@ -63,7 +63,8 @@ class PointLiDARBackbone(nn.Module):
 
     data_dict: 'points' (B,N,3+C) float32, 'gt_bboxes3d' (B,MNP,7) (zero-padded rows allowed: they pool no
     points and get the embedding of a zero vector, exactly like any empty person; the fusion net slices them
-    away).  The 128 -> 512 `embedding` is a plain library GEMM (cuBLAS through torch)."""
+    away).  The 128 -> 512 `embedding` runs on tcgen05 (csrc/gemm_tc.cu, 3xTF32) in eval mode without autograd, through
+    torch's fp32 GEMM otherwise."""
 
     def __init__(self, point_feature_channels=1, num_sampled_points=512, npoint=512, radius=0.3, nsample=32,
                  mlp=(64, 128), out_dim=512):
@@ -77,4 +78,7 @@ class PointLiDARBackbone(nn.Module):
         pts = data_dict['points']
         boxes = data_dict['gt_bboxes3d']
         person = self.encoder(pts[..., 0:3].contiguous(), pts[..., 3:].contiguous(), boxes.contiguous())
+        from . import tc_gemm
+        if not self.training and tc_gemm.usable(person, self.embedding.out_features, self.embedding.in_features):
+            return tc_gemm.linear(person, self.embedding.weight, self.embedding.bias)     # tcgen05, fp32-faithful
         return self.embedding(person)                                   # (B, MNP, out_dim)

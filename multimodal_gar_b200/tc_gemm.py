@@ -1,0 +1,53 @@
+"""fp32-faithful linear layers on tcgen05 (libmgar_lidar.so: csrc/gemm_tc.cu, 3xTF32) for the dense products around the
+LiDAR hot path that the reference leaves to torch / cuBLAS fp32: the projections and FFN linears of
+`FusionAttention_mat` (/root/reference/model/gat_model.py:466-511) and the 128 -> 512 LiDAR embedding (:883-894).
+
+Inference only (no autograd node): callers keep torch's own `F.linear` whenever gradients are required, the tensors are
+not CUDA fp32, or the shape is outside the kernel's (out_features % 128 == 0, in_features % 32 == 0)."""
+import torch
+
+from . import _lib
+from ._torch_glue import on_device, ptr, stream_of
+
+
+def usable(x, out_features, in_features):
+    """True when `x` (.., in_features) can go through the tensor-core kernel right now."""
+    if not (x.is_cuda and x.dtype == torch.float32) or torch.is_grad_enabled() and x.requires_grad:
+        return False
+    rows = x.numel() // max(in_features, 1)
+    return rows > 0 and bool(_lib.lib().mgar_gemm_tf32x3_supported(int(rows), int(out_features), int(in_features)))
+
+
+def linear(x, weight, bias=None, relu=False, out=None):
+    """act(x @ weight.T + bias) with `weight` (out_features, in_features) as nn.Linear stores it.  x (.., in) fp32 CUDA;
+    returns (.., out).  Raises MgarError when the shape is unsupported (ask `usable` first)."""
+    K, N = weight.shape[1], weight.shape[0]
+    x2 = x.reshape(-1, K)
+    if x2.stride(1) != 1 or x2.stride(0) % 4 or x2.data_ptr() % 16:
+        x2 = x2.contiguous()
+    w = weight if (weight.stride(1) == 1 and weight.stride(0) % 4 == 0 and weight.data_ptr() % 16 == 0) else weight.contiguous()
+    M = x2.shape[0]
+    y = out if out is not None else torch.empty((M, N), dtype=torch.float32, device=x.device)
+    if y.stride(1) != 1 or y.stride(0) % 4 or y.data_ptr() % 16:
+        raise _lib.MgarError("linear: output must be a 16-byte aligned row-major fp32 tensor")
+    b = None if bias is None else bias.detach().contiguous()
+    with on_device(x):
+        _lib.check(_lib.lib().mgar_gemm_tf32x3(M, N, K, ptr(x2), x2.stride(0), ptr(w.detach()), w.stride(0), ptr(b),
+                                               1 if relu else 0, ptr(y), y.stride(0), stream_of(x)), "gemm_tf32x3")
+    return y if out is not None else y.view(*x.shape[:-1], N)
+
+
+class CachedTranspose:
+    """(K, N) parameters used as `x @ W` -> the (N, K) K-major copy the kernel wants, re-made when a parameter changes
+    (storage pointer + in-place version, as the folded-BatchNorm cache of the SA module)."""
+
+    def __init__(self):
+        self.key, self.value = None, None
+
+    def get(self, params):
+        key = tuple((p.data_ptr(), p._version, str(p.device)) for p in params)
+        if key != self.key:
+            with torch.no_grad():
+                self.value = torch.cat([p.detach() for p in params], dim=1).t().contiguous()
+            self.key = key
+        return self.value

@@ -56,10 +56,10 @@ def test_fused_module_matches_torch_composition(cuda, monkeypatch, B, n, D, full
         with torch.no_grad():
             n0 = _lib.launch_count()
             Rf, Lf = mod(R, L, None, De, None if full else valid)
-            assert _lib.launch_count() - n0 == 3
+            assert _lib.launch_count() - n0 == (9 if D % 128 == 0 else 3)   # + six tcgen05 GEMMs when the width fits
             monkeypatch.setenv("MGAR_DAFM", "torch")
             Rt, Lt = mod(R, L, None, De, None if full else valid)
-            assert _lib.launch_count() - n0 == 3
+            assert _lib.launch_count() - n0 == (9 if D % 128 == 0 else 3)   # + six tcgen05 GEMMs when the width fits
     finally:
         torch.backends.cuda.matmul.allow_tf32 = tf32
     for got, want in ((Rf, Rt), (Lf, Lt)):
