@@ -308,6 +308,24 @@ MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float
                                 float *group_max, int group_size, const int *group_zero, const int *group_live_cnt,
                                 int pool_avg, void *workspace, size_t workspace_bytes, void *stream);
 
+/* ---- NeighborVoxelSAModuleMSG, one scale, eval mode (voxel_pool_modules.py:70-130) ------------------------------ */
+
+/* out (M,C2) = ReLU(bn_out(W_out . pool_s ReLU(bn_in(W_in . features)[idx[m,s]] + bn_pos(W_pos . (xyz[idx[m,s]] - new_xyz[m])))))
+ * fused: no (M,C,nsample) tensor is materialised.  features (N,C_in), xyz (N,3), new_xyz (M,3), idx (M,nsample) GLOBAL
+ * rows as VoxelQuery returns them (rows of empty queries zeroed), empty_mask (M) uint8 (non-zero: the query found no
+ * voxel; its grouped features and offsets count as zeros, as the reference masks them), params = the three layers with
+ * BatchNorm folded, mgar_voxel_sa_param_floats(C_in, C1, C2) floats laid out
+ *   W_in^T [C_in][C1] | scale_in | shift_in | W_pos^T [3][C1] | scale_pos | shift_pos | W_out^T [C1][C2] | scale_out | shift_out.
+ * pool_avg: 0 = max over the samples, 1 = mean.  workspace: mgar_voxel_sa_workspace_bytes(N, C1) bytes (the (N,C1)
+ * output of the input layer).  Channels <= 128.  Exact fp32 FFMA (the widths are 32-wide: a CUDA-core job). */
+MGAR_API int mgar_voxel_sa_supported(int C_in, int C1, int C2, int nsample);
+MGAR_API size_t mgar_voxel_sa_param_floats(int C_in, int C1, int C2);
+MGAR_API size_t mgar_voxel_sa_workspace_bytes(int N, int C1);
+MGAR_API int mgar_voxel_sa_fwd(int N, int M, int C_in, int C1, int C2, int nsample, int pool_avg, const float *features,
+                               const float *xyz, const float *new_xyz, const int *idx, const unsigned char *empty_mask,
+                               const float *params, float *out, int ld_out, void *workspace, size_t workspace_bytes,
+                               void *stream);
+
 /* ---- fp32-faithful GEMM on tcgen05 (3xTF32) --------------------------------------------------------------- */
 
 /* C (M,N) = act(A (M,K) . Bt (N,K)^T + bias): the dense linears around the hot path that the reference runs through

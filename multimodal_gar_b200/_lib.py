@@ -48,6 +48,10 @@ SIGNATURES = {
     "mgar_three_interpolate_grad_stack": [_i, _i, _p, _p, _p, _p, _p],
     "mgar_dafm_attention": [_i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _f, _p, _p],
     "mgar_dafm_add_layernorm": [_i, _i, _p, _p, _p, _p, _p, _f, _p, _p],
+    "mgar_voxel_sa_supported": [_i, _i, _i, _i],
+    "mgar_voxel_sa_param_floats": [_i, _i, _i],
+    "mgar_voxel_sa_workspace_bytes": [_i, _i],
+    "mgar_voxel_sa_fwd": [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p, ctypes.c_size_t, _p],
     "mgar_gemm_tf32x3_supported": [_i, _i, _i],
     "mgar_gemm_tf32x3": [_i, _i, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p],
     "mgar_fps_ball_query_supported": [_i, _i, _i, _i],
@@ -100,6 +104,8 @@ def lib():
         L.mgar_sa_mlp_train_workspace_bytes_for.restype = ctypes.c_size_t
         L.mgar_box_mask_words.restype = ctypes.c_size_t
         L.mgar_stack_workspace_bytes.restype = ctypes.c_size_t
+        L.mgar_voxel_sa_param_floats.restype = ctypes.c_size_t
+        L.mgar_voxel_sa_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_box_masks_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_points_in_boxes_mask_host_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_sa_mlp_tc_workspace_bytes.restype = ctypes.c_size_t

@@ -104,10 +104,17 @@ def test_neighbor_voxel_sa_module_vs_reference_class_golden(cuda, pool):
 
 
 def _check_module(m, args, g, pool):
+    from multimodal_gar_b200 import _lib
     with torch.no_grad():
         m.eval()
+        n0 = _lib.launch_count()
         out = m(*args)
+        # eval mode: per scale the voxel query + the two fused kernels of csrc/voxel_sa.cu - no cuDNN convolution
+        assert _lib.launch_count() - n0 == 3 * len(m.groupers)
         scale = float(np.abs(g[pool + ".eval"]).max())
+        with torch.enable_grad():                            # the torch composition (autograd on) agrees with the fused path
+            comp = m(*args)
+        np.testing.assert_allclose(out.cpu().numpy(), comp.detach().cpu().numpy(), rtol=1e-5, atol=1e-5 * scale)
         np.testing.assert_allclose(out.cpu().numpy(), g[pool + ".eval"], rtol=1e-5, atol=1e-5 * scale)   # fp32 tolerance of north_star
         m.train()
         out = m(*args)
