@@ -122,5 +122,28 @@ class VoxelRCNNHead(nn.Module):
         """reference :191-239 as shipped: pooled_features (B*num_rois, grid^3, C) and shared_feature (B*num_rois, FC)."""
         pooled_features = self.roi_grid_pool(batch_dict)
         batch_dict['pooled_features'] = pooled_features
-        batch_dict['shared_feature'] = self.shared_fc_layer(pooled_features.view(pooled_features.size(0), -1))
+        batch_dict['shared_feature'] = self._shared_fc(pooled_features.view(pooled_features.size(0), -1))
         return batch_dict
+
+    def _shared_fc(self, x):
+        """[Linear (no bias), BatchNorm1d, ReLU(, Dropout)] x len(SHARED_FC).  Eval mode without autograd: BatchNorm folded
+        into the weight rows and every layer one tcgen05 GEMM with bias + ReLU epilogue (csrc/gemm_tc.cu, 3xTF32);
+        otherwise the reference's nn.Sequential."""
+        from .... import tc_gemm
+        layers = [m for m in self.shared_fc_layer if isinstance(m, (nn.Linear, nn.BatchNorm1d))]
+        pairs = list(zip(layers[0::2], layers[1::2]))
+        if self.training or torch.is_grad_enabled() or not all(
+                tc_gemm.usable(x, lin.out_features, lin.in_features) for lin, _ in pairs):
+            return self.shared_fc_layer(x)
+        tensors = [t for lin, bn in pairs for t in (lin.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var)]
+        key = tuple((t.data_ptr(), t._version, str(t.device)) for t in tensors)
+        if getattr(self, '_fc_key', None) != key:
+            self._fc_folded = []
+            for lin, bn in pairs:
+                scale = bn.weight.detach() / torch.sqrt(bn.running_var.detach() + bn.eps)
+                self._fc_folded.append(((lin.weight.detach() * scale.unsqueeze(1)).contiguous(),
+                                        (bn.bias.detach() - bn.running_mean.detach() * scale).contiguous()))
+            self._fc_key = key
+        for w, b in self._fc_folded:
+            x = tc_gemm.linear(x, w, b, relu=True)
+        return x

@@ -13,7 +13,7 @@ WANT = {"gpu__time_duration.sum": "ncu_us", "dram__bytes_read.sum": "dram_read",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active": "tensor_pipe_active_pct",
         "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active": "alu_pipe_active_pct",
         "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active": "fma_pipe_active_pct",
-        "smsp__issue_active.avg.pct": "issue_active_pct",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_active_pct",
         "sm__warps_active.avg.pct_of_peak_sustained_active": "achieved_occupancy_pct",
         "launch__registers_per_thread": "registers", "smsp__inst_executed.sum": "warp_instructions",
         "dram__throughput.avg.pct_of_peak_sustained_elapsed": "dram_throughput_pct"}
