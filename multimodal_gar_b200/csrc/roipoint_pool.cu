@@ -382,14 +382,16 @@ frame_grid_build_kernel(const float *__restrict__ boxes, unsigned char *__restri
         } else {
             for (int cy = y0; cy <= y1; cy++)
                 for (int cx = x0; cx <= x1; cx++) {
+                    // a cell with more than kGridCap boxes is marked (count 255): only the points that fall into it take
+                    // the exhaustive loop.  Zero-padded proposal slots are degenerate boxes at the origin and all land in
+                    // the same 2 x 2 cells - round 1 (and the shared-memory grid kernel) gave up the whole frame for them.
                     const int old = atomicAdd(&scnt[cy * kGridN + cx], 1);
-                    if (old >= kGridCap) s_overflow = 1;
-                    else gids[(size_t)(cy * kGridN + cx) * kGridCap + old] = (unsigned char)k;
+                    if (old < kGridCap) gids[(size_t)(cy * kGridN + cx) * kGridCap + old] = (unsigned char)k;
                 }
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < kGridN * kGridN; i += kMaskThreads) gcnt[i] = (unsigned char)min(scnt[i], kGridCap);
+    for (int i = threadIdx.x; i < kGridN * kGridN; i += kMaskThreads) gcnt[i] = (unsigned char)(scnt[i] > kGridCap ? 255 : scnt[i]);
     if (threadIdx.x == 0) *reinterpret_cast<int *>(ws + FrameGrid::flag_off()) = s_overflow;
 }
 
@@ -451,6 +453,14 @@ box_mask_framegrid_kernel(const unsigned char *__restrict__ ws, const float *__r
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 if (cnt[j] == 0) continue;
+                if (cnt[j] == 255) {                          // crowded cell: this point tests every box
+                    for (int k = 0; k < M; k++)
+                        if (in_box<false>(x[j], y[j], z[j], sbox[k])) {
+                            if (res[j] < 0) res[j] = k;
+                            atomicOr(mask + (size_t)k * W + ((p0 + j) >> 5), 1u << ((p0 + j) & 31));
+                        }
+                    continue;
+                }
                 const uint2 id8 = __ldg(gids + cell[j]);
                 for (int q = 0; q < cnt[j]; q++) {
                     const int k = ((q < 4 ? id8.x : id8.y) >> (8 * (q & 3))) & 0xff;

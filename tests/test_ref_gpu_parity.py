@@ -157,3 +157,32 @@ def test_ball_query_ragged_bit_exact_and_oracle(cuda):
                                    T(cnt, cuda), ib)
         assert torch.equal(ia, ib)
         np.testing.assert_array_equal(O.ball_query_raw(r, K, xyz, cnt, new_xyz, ncnt), ia.cpu().numpy())
+
+
+def test_box_masks_crowded_cells_and_padded_slots_bit_exact(cuda):
+    """More than 8 boxes over one grid cell (a crowd of overlapping persons; zero-padded proposal slots - degenerate boxes
+    that all sit at the origin): the per-frame box grid marks the cell and only ITS points test every box.  First-hit
+    indices and pooled rows against the reference extensions, bit for bit."""
+    from multimodal_gar_b200 import fastpath
+    roiaware, roipoint = _ref("roiaware_pool3d_cuda"), _ref("roipoint_pool3d_cuda")
+    B, N, M = 3, 32768, 24
+    pts, boxes = synthetic.make_batch(77, B, N=N, M=M)
+    rng = np.random.default_rng(5)
+    crowd = boxes[:, :12].copy()
+    crowd[..., 0:2] = boxes[:, :1, 0:2] + rng.uniform(-0.25, 0.25, (B, 12, 2)).astype(np.float32)   # 12 persons in one cell
+    boxes = np.concatenate([boxes, crowd, np.zeros((B, 20, 7), np.float32)], axis=1)                 # + 20 padded slots
+    pts[:, :64, :3] = rng.uniform(-2e-5, 2e-5, (B, 64, 3)).astype(np.float32)                         # points at the origin
+    pts[:, 64:128, :3] = 0.0
+    M2 = boxes.shape[1]
+    xyz, feat, bx = T(pts[..., :3], cuda), T(pts[..., 3:4], cuda), T(boxes, cuda)
+    want_idx = torch.full((B, N), -1, dtype=torch.int32, device=cuda)
+    roiaware.points_in_boxes_gpu(bx, xyz, want_idx)
+    pa = torch.zeros((B, M2, 128, 4), device=cuda)
+    ea = torch.zeros((B, M2), dtype=torch.int32, device=cuda)
+    roipoint.forward(xyz, bx, feat, pa, ea)
+    box_idx, mask = fastpath.box_masks(xyz, bx)
+    pooled, empty, cnt = fastpath.roipoint_pool_from_masks(xyz, feat, bx, mask, 128, canonical=False, want_cnt=True)
+    assert torch.equal(box_idx, want_idx)
+    assert torch.equal(pooled, pa) and torch.equal(empty, ea)
+    assert int((want_idx >= M).sum()) > 0                       # the crowd and / or the degenerate boxes really catch points
+    assert torch.equal((cnt == 0).int(), ea)
