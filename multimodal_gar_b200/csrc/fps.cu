@@ -21,6 +21,7 @@
 #include <stdlib.h>
 
 #include "fps_bq_cta.cuh"
+#include "fps_bq_dup.cuh"
 #include "mgar_common.cuh"
 
 namespace mgar {
@@ -639,6 +640,24 @@ extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xy
             count_launch();
             if (int rc = check_launch("fps_ball_query(order)")) return rc;
             order = static_cast<const int *>(workspace);
+        }
+        // pooled clouds are periodic (slot k = point k mod count): with the count as a (verified) hint only the distinct
+        // blocks take part in a round (fps_bq_dup.cuh).  Bit-identical, 35 % fewer point-rounds - and SLOWER on the bench
+        // step (0.338 ms at its best residency against 0.309 ms, profiles/r02_fps_bq_sweep.txt): the step lasts as long
+        // as the 512-round clouds, whose round is latency-bound and got a few instructions longer.  Opt-in
+        // (MGAR_FPS_BQ_DUP=1), kept with its tests as the record of the experiment.
+        if (n == kDupN && cloud_weight && getenv("MGAR_FPS_BQ_DUP") && !getenv("MGAR_FPS_BQ_GEOM")) {
+            size_t sm = (size_t)kDupN * sizeof(float4) + (size_t)m * sizeof(int) + (size_t)kDupW * 2 * nsample * sizeof(int);
+            int ctas_per_sm = 10;
+            if (const char *e = getenv("MGAR_FPS_BQ_CTAS")) { const int v = atoi(e); if (v >= 1 && v <= 32) ctas_per_sm = v; }
+            const size_t cap = ((size_t)227 * 1024) / ctas_per_sm - 1024;
+            if (b > kNumSMs * ctas_per_sm && cap > sm) sm = cap & ~(size_t)127;
+            if (sm > 48 * 1024)
+                MGAR_CUDA(cudaFuncSetAttribute(fps_bq_dup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+            fps_bq_dup_kernel<<<b, kDupW * 32, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, order,
+                                                         cloud_weight, live_cnt, write_dup_rows);
+            count_launch();
+            return check_launch("fps_ball_query(dup)");
         }
         int W = 2, PPL = n / 64;       // see fps_bq_cta.cuh: the kernel is ALU-issue bound, two warps per cloud cost the least
         if (const char *e = getenv("MGAR_FPS_BQ_GEOM")) {

@@ -494,3 +494,46 @@ def test_fused_fps_ball_query_geometries_schedule_and_partial_rows(cuda, monkeyp
     sel = torch.from_numpy(rows.reshape(-1)).to(cuda)
     assert torch.equal(part[2][sel], ball[sel])
     assert (lc[1::4] < n // 2).all() and (lc[0::2] == m).all()
+
+
+@pytest.mark.parametrize("m,K,radius", [(512, 32, 0.35), (512, 64, 0.6), (200, 16, 0.15), (512, 32, 5.0)])
+def test_fused_fps_ball_query_periodic_clouds(cuda, monkeypatch, m, K, radius):
+    """Wrapped clouds (slot k = point k mod p, what roipoint pooling produces) through the kernel that processes only the
+    distinct blocks (fps_bq_dup.cuh): every period class - p < 32, p a multiple of 32, p = 511 / 512, periods whose copies
+    straddle block boundaries, duplicated points INSIDE a period (ties between distinct slots) - with the true period, a
+    multiple of it, a wrong hint (verified and ignored) and no hint; bit-exact against the two separate kernels."""
+    from multimodal_gar_b200 import fastpath
+    monkeypatch.delenv("MGAR_FPS_BQ", raising=False)
+    monkeypatch.delenv("MGAR_FPS_BQ_GEOM", raising=False)
+    monkeypatch.setenv("MGAR_FPS_BQ_DUP", "1")          # opt-in kernel (not the default: slower on the bench step)
+    n = 512
+    periods = [1, 2, 5, 31, 32, 33, 63, 64, 65, 100, 145, 160, 200, 255, 256, 257, 300, 383, 384, 400, 479, 480, 481, 500, 511, 512]
+    rng = np.random.default_rng(m + K)
+    periods = periods + [int(v) for v in rng.integers(1, 513, 640 - len(periods))]
+    b = len(periods)
+    c = np.zeros((b, n, 3), np.float32)
+    for g, p in enumerate(periods):
+        base = rng.uniform(-1, 1, (p, 3)).astype(np.float32)
+        if g % 5 == 0 and p > 8:
+            base[p // 2:p // 2 + 4] = base[:4]                                   # exact duplicates inside the period
+        c[g] = base[np.arange(n) % p]
+    c4 = np.concatenate([c, rng.standard_normal((b, n, 1)).astype(np.float32)], axis=2)
+    t4 = T(c4, cuda)
+    x = t4[:, :, 0:3]
+    idx, new_xyz = fastpath.fps_gather(x, m)
+    ball = fastpath.ball_query_uniform(radius, K, t4.view(b * n, 4)[:, 0:3], new_xyz.view(b * m, 3), n, m)
+    true_p = T(np.array(periods, np.int32), cuda)
+    hints = {"true": true_p, "double": torch.clamp(true_p * 2, max=600), "wrong": T(rng.integers(1, 513, b).astype(np.int32), cuda),
+             "zero": torch.zeros_like(true_p)}
+    for name, h in hints.items():
+        got = fastpath.fps_ball_query(x, m, radius, K, cloud_weight=h)
+        assert torch.equal(got[0], idx), name
+        assert torch.equal(got[1], new_xyz), name
+        assert torch.equal(got[2], ball), name
+    none = fastpath.fps_ball_query(x, m, radius, K)
+    assert torch.equal(none[2], ball) and torch.equal(none[3], got[3])
+    part = fastpath.fps_ball_query(x, m, radius, K, all_rows=False, cloud_weight=true_p)
+    lc = part[3].cpu().numpy()
+    rows = np.arange(m)[None, :] < ((lc + 3) // 4 * 4)[:, None]
+    sel = torch.from_numpy(rows.reshape(-1)).to(cuda)
+    assert torch.equal(part[2][sel], ball[sel]) and torch.equal(part[0], idx)
