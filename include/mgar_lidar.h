@@ -337,6 +337,14 @@ MGAR_API int mgar_voxel_sa_fwd(int N, int M, int C_in, int C1, int C2, int nsamp
 MGAR_API int mgar_gemm_tf32x3_supported(int M, int N, int K);
 MGAR_API int mgar_gemm_tf32x3(int M, int N, int K, const float *A, int lda, const float *Bt, int ldb, const float *bias,
                               int relu, float *C, int ldc, void *stream);
+/* The same product with the weight operand prepared ONCE: mgar_gemm_pack_bt splits Bt into tf32 hi / lo and stores every
+ * (128 x 32) tile in the shared-memory image the MMA reads (mgar_gemm_packed_bytes(N, K) = 2 * N * K * 4 bytes, caller-
+ * owned); mgar_gemm_tf32x3_packed then fetches a K chunk's weight tiles with one cp.async.bulk and its producer warps
+ * only stream A.  Same results as mgar_gemm_tf32x3 bit for bit (same split, same accumulation order). */
+MGAR_API size_t mgar_gemm_packed_bytes(int N, int K);
+MGAR_API int mgar_gemm_pack_bt(int N, int K, const float *Bt, int ldb, float *packed, void *stream);
+MGAR_API int mgar_gemm_tf32x3_packed(int M, int N, int K, const float *A, int lda, const float *packed, const float *bias,
+                                     int relu, float *C, int ldc, void *stream);
 
 /* ---- training: the same module with BatchNorm batch statistics, and its backward pass ------------------- */
 

@@ -54,6 +54,9 @@ SIGNATURES = {
     "mgar_voxel_sa_fwd": [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p, ctypes.c_size_t, _p],
     "mgar_gemm_tf32x3_supported": [_i, _i, _i],
     "mgar_gemm_tf32x3": [_i, _i, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p],
+    "mgar_gemm_packed_bytes": [_i, _i],
+    "mgar_gemm_pack_bt": [_i, _i, _p, _i, _p, _p],
+    "mgar_gemm_tf32x3_packed": [_i, _i, _i, _p, _i, _p, _p, _i, _p, _i, _p],
     "mgar_fps_ball_query_supported": [_i, _i, _i, _i],
     "mgar_fps_ball_query_workspace_bytes": [_i],
     "mgar_fps_ball_query": [_i, _i, _i, _p, _i, _f, _i, _p, _p, _p, _p, _i, _p, _p, ctypes.c_size_t, _p],
@@ -104,6 +107,7 @@ def lib():
         L.mgar_sa_mlp_train_workspace_bytes_for.restype = ctypes.c_size_t
         L.mgar_box_mask_words.restype = ctypes.c_size_t
         L.mgar_stack_workspace_bytes.restype = ctypes.c_size_t
+        L.mgar_gemm_packed_bytes.restype = ctypes.c_size_t
         L.mgar_voxel_sa_param_floats.restype = ctypes.c_size_t
         L.mgar_voxel_sa_workspace_bytes.restype = ctypes.c_size_t
         L.mgar_box_masks_workspace_bytes.restype = ctypes.c_size_t

@@ -168,6 +168,163 @@ gemm_tf32x3_kernel(int M, int N, int K, const float *__restrict__ A, int lda, co
     }
 }
 
+// ---- the same GEMM with PRE-SPLIT, PRE-SWIZZLED weights ------------------------------------------------------------
+// The weight operand does not change between calls: mgar_gemm_pack_bt splits it once into tf32 hi / lo and lays every
+// (128 rows x 32 floats) tile out exactly as the MMA wants it in shared memory (128-byte swizzle), hi and lo tile back to
+// back: [n_tile][k_chunk][hi 16 KB | lo 16 KB].  The kernel then brings a chunk's 32 KB of B with ONE cp.async.bulk (the TMA
+// engine's bulk copy) that completes on the stage's full barrier - no registers, no split, no shared-memory stores for B -
+// and the four producer warps only stream A, two K chunks ahead in registers (a K chunk's MMAs last ~0.4 us, a trip to
+// L2 / HBM ~1 us: one chunk of prefetch, as the plain kernel has, leaves the tensor pipe waiting).
+__global__ void __launch_bounds__(256)
+gemm_pack_bt_kernel(int N, int K, const float *__restrict__ Bt, int ldb, float *__restrict__ packed) {
+    // one thread per 16-byte chunk of the source: row n, chunk c16 of K chunk kc
+    const long long total = (long long)N * (K / 4);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int n = (int)(i / (K / 4)), c = (int)(i % (K / 4));
+        const int kc = c >> 3, c16 = c & 7, r = n & 127, nt = n >> 7;
+        const float4 v = __ldg(reinterpret_cast<const float4 *>(Bt + (size_t)n * ldb) + c);
+        float4 hi, lo;
+        hi.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u); lo.x = __fsub_rn(v.x, hi.x);
+        hi.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u); lo.y = __fsub_rn(v.y, hi.y);
+        hi.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u); lo.z = __fsub_rn(v.z, hi.z);
+        hi.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u); lo.w = __fsub_rn(v.w, hi.w);
+        char *tile = reinterpret_cast<char *>(packed) + ((size_t)nt * (K / kGmKC) + kc) * 2 * kGmTile;
+        *reinterpret_cast<float4 *>(tile + gm_off(r, c16)) = hi;
+        *reinterpret_cast<float4 *>(tile + kGmTile + gm_off(r, c16)) = lo;
+    }
+}
+
+constexpr uint32_t kGpStageBytes = 4 * kGmTile;            // A hi, A lo (written by the producers) | B hi, B lo (bulk copy)
+constexpr int kGpStages = 3;
+constexpr uint32_t kGpSmem = kGpStages * kGpStageBytes + 1024;
+
+__global__ void __launch_bounds__(kGmThreads, 1)
+gemm_tf32x3_packed_kernel(int M, int N, int K, const float *__restrict__ A, int lda, const float *__restrict__ packed,
+                          const float *__restrict__ bias, int relu, float *__restrict__ C, int ldc) {
+    extern __shared__ uint8_t gm_smem[];
+    __shared__ __align__(8) uint64_t s_bar[2 * kGpStages + 1];
+    __shared__ uint32_t s_tmem;
+    const uint32_t base = (smem_u32(gm_smem) + 1023u) & ~1023u;
+    const uint32_t bar0 = smem_u32(s_bar);
+    auto FULL = [&](int s) { return bar0 + 8u * s; };
+    auto EMPTY = [&](int s) { return bar0 + 8u * (kGpStages + s); };
+    const uint32_t TFULL = bar0 + 8u * (2 * kGpStages);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n0 = blockIdx.x * 128, m0 = blockIdx.y * 128;
+    const int n_chunks = K / kGmKC;
+
+    if (tid == 0) {
+        for (int s = 0; s < kGpStages; s++) { mbar_init(FULL(s), 129); mbar_init(EMPTY(s), 1); }   // 128 producers + the bulk copy
+        mbar_init(TFULL, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(128u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (warp < 4) {
+        mbar_wait(TFULL, 0);
+        tc_fence_after();
+        const int m = m0 + warp * 32 + lane;
+        const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+        for (int q = 0; q < 4; q++) {
+            uint32_t v[32];
+            tc_ld32(taddr + (uint32_t)(q * 32), v);
+            tc_wait_ld();
+            if (m < M) {
+                float *out = C + (size_t)m * ldc + n0 + q * 32;
+                const float *bq = bias ? bias + n0 + q * 32 : nullptr;
+#pragma unroll
+                for (int c = 0; c < 32; c += 4) {
+                    float4 o = make_float4(__uint_as_float(v[c]), __uint_as_float(v[c + 1]), __uint_as_float(v[c + 2]),
+                                           __uint_as_float(v[c + 3]));
+                    if (bq) {
+                        const float4 bb = __ldg(reinterpret_cast<const float4 *>(bq + c));
+                        o.x = __fadd_rn(o.x, bb.x); o.y = __fadd_rn(o.y, bb.y); o.z = __fadd_rn(o.z, bb.z); o.w = __fadd_rn(o.w, bb.w);
+                    }
+                    if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+                    *reinterpret_cast<float4 *>(out + c) = o;
+                }
+            }
+        }
+        tc_fence_before();
+    } else if (warp == 4) {
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        for (int kc = 0; kc < n_chunks; kc++) {
+            const int s = kc % kGpStages, j = kc / kGpStages;
+            mbar_wait(FULL(s), j & 1);                          // A stored by the producers AND the B tiles landed
+            tc_fence_after();
+            const uint32_t st = base + (uint32_t)s * kGpStageBytes;
+            const uint64_t a_hi = make_desc(st), a_lo = make_desc(st + kGmTile);
+            const uint64_t b_hi = make_desc(st + 2 * kGmTile), b_lo = make_desc(st + 3 * kGmTile);
+            if (elect_one()) {
+#pragma unroll
+                for (int term = 0; term < 3; term++) {
+                    const uint64_t ad = term == 0 ? a_lo : a_hi;
+                    const uint64_t bd = term == 1 ? b_lo : b_hi;
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++)
+                        tc_mma_tf32(tmem, ad + (uint64_t)((kk * 32) >> 4), bd + (uint64_t)((kk * 32) >> 4), idesc,
+                                    (kc | term | kk) ? 1u : 0u);
+                }
+                tc_commit(EMPTY(s));
+                if (kc == n_chunks - 1) tc_commit(TFULL);
+            }
+            __syncwarp();
+        }
+    } else {
+        const int r = (warp - 5) * 32 + lane;
+        const bool a_ok = m0 + r < M;
+        const float4 *arow = reinterpret_cast<const float4 *>(A + (size_t)(a_ok ? m0 + r : 0) * lda);
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const char *btiles = reinterpret_cast<const char *>(packed) + (size_t)blockIdx.x * n_chunks * 2 * kGmTile;
+        float4 a[3][8];                                         // chunks kc, kc + 1, kc + 2 (rotating, fully unrolled by 3)
+#pragma unroll
+        for (int d = 0; d < 2; d++)
+#pragma unroll
+            for (int c = 0; c < 8; c++) a[d][c] = (a_ok && d < n_chunks) ? __ldg(arow + d * 8 + c) : z4;
+        auto step = [&](int kc, float4 (&cur)[8], float4 (&nxt2)[8]) {
+            const int s = kc % kGpStages, j = kc / kGpStages;
+            if (kc + 2 < n_chunks) {
+#pragma unroll
+                for (int c = 0; c < 8; c++) nxt2[c] = a_ok ? __ldg(arow + (kc + 2) * 8 + c) : z4;
+            }
+            mbar_wait(EMPTY(s), (j & 1) ^ 1);
+            const uint32_t st = base + (uint32_t)s * kGpStageBytes;
+            if (r == 0) {                                       // this chunk's weight tiles: one bulk copy onto the full barrier
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(FULL(s)), "r"(2 * kGmTile) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(st + 2 * kGmTile), "l"(btiles + (size_t)kc * 2 * kGmTile), "r"(2 * kGmTile), "r"(FULL(s)) : "memory");
+            }
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const uint32_t off = gm_off(r, c);
+                const float va[4] = {cur[c].x, cur[c].y, cur[c].z, cur[c].w};
+                sts_split4(st + off, st + kGmTile + off, va);
+            }
+            fence_async_smem();
+            mbar_arrive(FULL(s));
+        };
+        for (int kc = 0; kc < n_chunks; kc += 3) {
+            step(kc, a[0], a[2]);
+            if (kc + 1 < n_chunks) step(kc + 1, a[1], a[0]);
+            if (kc + 2 < n_chunks) step(kc + 2, a[2], a[1]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(128u) : "memory");
+    }
+}
+
 }  // namespace
 }  // namespace mgar
 
@@ -194,4 +351,37 @@ extern "C" int mgar_gemm_tf32x3(int M, int N, int K, const float *A, int lda, co
     gemm_tf32x3_kernel<<<grid, kGmThreads, kGmSmem, (cudaStream_t)stream>>>(M, N, K, A, lda, Bt, ldb, bias, relu, C, ldc);
     count_launch();
     return check_launch("gemm_tf32x3");
+}
+
+extern "C" size_t mgar_gemm_packed_bytes(int N, int K) {
+    return (N > 0 && K > 0 && N % 128 == 0 && K % 32 == 0) ? (size_t)N * K * 2 * sizeof(float) : 0;
+}
+
+extern "C" int mgar_gemm_pack_bt(int N, int K, const float *Bt, int ldb, float *packed, void *stream) {
+    MGAR_REQUIRE(N >= 128 && N % 128 == 0 && K >= 32 && K % 32 == 0, "gemm_pack_bt: N %% 128 == 0 and K %% 32 == 0 required (N=%d K=%d)", N, K);
+    MGAR_REQUIRE(Bt && packed && ldb >= K && ldb % 4 == 0, "gemm_pack_bt: bad operand");
+    MGAR_REQUIRE(((reinterpret_cast<uintptr_t>(Bt) | reinterpret_cast<uintptr_t>(packed)) & 15) == 0, "gemm_pack_bt: operands must be 16-byte aligned");
+    const long long total = (long long)N * (K / 4);
+    int grid = div_up(total, 256);
+    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    gemm_pack_bt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(N, K, Bt, ldb, packed);
+    count_launch();
+    return check_launch("gemm_pack_bt");
+}
+
+extern "C" int mgar_gemm_tf32x3_packed(int M, int N, int K, const float *A, int lda, const float *packed, const float *bias,
+                                       int relu, float *C, int ldc, void *stream) {
+    MGAR_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm_tf32x3_packed: negative size");
+    if (M == 0 || N == 0) return MGAR_OK;
+    MGAR_REQUIRE(mgar_gemm_tf32x3_supported(M, N, K), "gemm_tf32x3_packed: unsupported shape M=%d N=%d K=%d", M, N, K);
+    MGAR_REQUIRE(A && packed && C, "gemm_tf32x3_packed: null pointer");
+    MGAR_REQUIRE(lda >= K && ldc >= N && lda % 4 == 0 && ldc % 4 == 0, "gemm_tf32x3_packed: bad leading dimension");
+    MGAR_REQUIRE(((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(packed) | reinterpret_cast<uintptr_t>(C) |
+                   reinterpret_cast<uintptr_t>(bias)) & 15) == 0, "gemm_tf32x3_packed: operands must be 16-byte aligned");
+    MGAR_REQUIRE((M + 127) / 128 <= 65535, "gemm_tf32x3_packed: M=%d exceeds grid.y", M);
+    MGAR_CUDA(cudaFuncSetAttribute(gemm_tf32x3_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGpSmem));
+    dim3 grid(N / 128, (M + 127) / 128);
+    gemm_tf32x3_packed_kernel<<<grid, kGmThreads, kGpSmem, (cudaStream_t)stream>>>(M, N, K, A, lda, packed, bias, relu, C, ldc);
+    count_launch();
+    return check_launch("gemm_tf32x3_packed");
 }

@@ -4,6 +4,8 @@ LiDAR hot path that the reference leaves to torch / cuBLAS fp32: the projections
 
 Inference only (no autograd node): callers keep torch's own `F.linear` whenever gradients are required, the tensors are
 not CUDA fp32, or the shape is outside the kernel's (out_features % 128 == 0, in_features % 32 == 0)."""
+import weakref
+
 import torch
 
 from . import _lib
@@ -18,9 +20,36 @@ def usable(x, out_features, in_features):
     return rows > 0 and bool(_lib.lib().mgar_gemm_tf32x3_supported(int(rows), int(out_features), int(in_features)))
 
 
-def linear(x, weight, bias=None, relu=False, out=None):
+_PACKED = {}          # (data_ptr, version, shape, strides, device) -> packed weight tiles (mgar_gemm_pack_bt), small LRU
+
+
+def packed_weight(w):
+    """The weight (N, K) split into tf32 hi / lo and laid out tile by tile as the kernel reads it (csrc/gemm_tc.cu);
+    prepared once per weight VALUE: the key holds the storage pointer and the in-place version counter."""
+    key = (w.data_ptr(), w._version, tuple(w.shape), tuple(w.stride()), str(w.device))
+    hit = _PACKED.get(key)
+    if hit is not None and hit[0]() is not w:          # another tensor now lives at that address: not the same weight
+        hit = None
+    if hit is not None:
+        return hit[1]
+    N, K = w.shape
+    src = w.detach()
+    if src.stride(1) != 1 or src.stride(0) % 4 or src.data_ptr() % 16:
+        src = src.contiguous()
+    L = _lib.lib()
+    hit = torch.empty((int(L.mgar_gemm_packed_bytes(N, K)) // 4,), dtype=torch.float32, device=w.device)
+    with on_device(w):
+        _lib.check(L.mgar_gemm_pack_bt(N, K, ptr(src), src.stride(0), ptr(hit), stream_of(w)), "gemm_pack_bt")
+    if len(_PACKED) >= 64:
+        _PACKED.pop(next(iter(_PACKED)))
+    _PACKED[key] = (weakref.ref(w), hit)
+    return hit
+
+
+def linear(x, weight, bias=None, relu=False, out=None, packed=True):
     """act(x @ weight.T + bias) with `weight` (out_features, in_features) as nn.Linear stores it.  x (.., in) fp32 CUDA;
-    returns (.., out).  Raises MgarError when the shape is unsupported (ask `usable` first)."""
+    returns (.., out).  Raises MgarError when the shape is unsupported (ask `usable` first).  packed=True (default): the
+    weight goes through `packed_weight` (prepared once, bulk-copied by the kernel); False: the kernel splits it per call."""
     K, N = weight.shape[1], weight.shape[0]
     x2 = x.reshape(-1, K)
     if x2.stride(1) != 1 or x2.stride(0) % 4 or x2.data_ptr() % 16:
@@ -32,8 +61,13 @@ def linear(x, weight, bias=None, relu=False, out=None):
         raise _lib.MgarError("linear: output must be a 16-byte aligned row-major fp32 tensor")
     b = None if bias is None else bias.detach().contiguous()
     with on_device(x):
-        _lib.check(_lib.lib().mgar_gemm_tf32x3(M, N, K, ptr(x2), x2.stride(0), ptr(w.detach()), w.stride(0), ptr(b),
-                                               1 if relu else 0, ptr(y), y.stride(0), stream_of(x)), "gemm_tf32x3")
+        if packed:
+            pw = packed_weight(weight)
+            _lib.check(_lib.lib().mgar_gemm_tf32x3_packed(M, N, K, ptr(x2), x2.stride(0), ptr(pw), ptr(b), 1 if relu else 0,
+                                                          ptr(y), y.stride(0), stream_of(x)), "gemm_tf32x3_packed")
+        else:
+            _lib.check(_lib.lib().mgar_gemm_tf32x3(M, N, K, ptr(x2), x2.stride(0), ptr(w.detach()), w.stride(0), ptr(b),
+                                                   1 if relu else 0, ptr(y), y.stride(0), stream_of(x)), "gemm_tf32x3")
     return y if out is not None else y.view(*x.shape[:-1], N)
 
 

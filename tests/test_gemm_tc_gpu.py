@@ -17,9 +17,12 @@ def test_gemm_matches_fp64_product(cuda, M, N, K, bias, relu):
     x = (torch.randn((M, K), generator=g) * torch.logspace(-3, 3, K)).to(cuda)        # wide dynamic range along K
     w = torch.randn((N, K), generator=g).to(cuda) / K ** 0.5
     b = torch.randn((N,), generator=g).to(cuda) if bias else None
+    y0 = tc_gemm.linear(x, w, b, relu=relu, packed=False)
+    tc_gemm.linear(x, w, b, relu=relu)                     # (packs the weight on first use)
     n0 = _lib.launch_count()
     y = tc_gemm.linear(x, w, b, relu=relu)
-    assert _lib.launch_count() == n0 + 1
+    assert _lib.launch_count() == n0 + 1                   # packed weights are cached: one launch per call
+    assert torch.equal(y, y0)                              # same split, same accumulation order: same bits
     want = x.double() @ w.double().t()
     if bias:
         want = want + b.double()
@@ -38,8 +41,13 @@ def test_gemm_matches_fp64_product(cuda, M, N, K, bias, relu):
 def test_gemm_strided_rows_and_rejects_bad_shapes(cuda):
     x = torch.randn((70, 96), device=cuda)[:, :64]                                     # row stride 96
     w = torch.randn((128, 64), device=cuda)
-    y = tc_gemm.linear(x, w)
-    assert torch.allclose(y, x @ w.t(), rtol=1e-5, atol=1e-5)
+    def close(y, x, w):                                    # against the fp64 product, relative to a row's |x|.|w|
+        mag = (x.double().abs() @ w.double().abs().t()).amax(dim=1, keepdim=True)
+        return float(((y.double() - x.double() @ w.double().t()).abs() / mag).max()) < 4e-6
+    assert close(tc_gemm.linear(x, w), x, w)
+    assert close(tc_gemm.linear(x, w, packed=False), x, w)
+    w.mul_(2.0)                                            # in-place edit: the packed copy is keyed on the version
+    assert close(tc_gemm.linear(x, w), x, w)
     assert not tc_gemm.usable(x, 100, 64) and not tc_gemm.usable(x, 128, 40)
     with pytest.raises(_lib.MgarError):
         tc_gemm.linear(torch.randn((8, 40), device=cuda), torch.randn((128, 40), device=cuda))
@@ -56,6 +64,7 @@ def test_dafm_runs_its_linears_on_the_tensor_cores(cuda, monkeypatch):
     De = torch.cdist(ctr, ctr)
     valid = torch.arange(n, device=cuda).view(1, n) < torch.tensor([37, 20, 1, 36, 5], device=cuda).view(B, 1)
     with torch.no_grad():
+        mod(R, L, None, De, valid)                         # first call packs the weights
         n0 = _lib.launch_count()
         got = mod(R, L, None, De, valid)
         launches = _lib.launch_count() - n0
