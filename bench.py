@@ -351,7 +351,16 @@ def build_batches(F, rank, dev):
             xs.append(base[0][j][perm])
             fs.append(base[1][j][perm])
             bs.append(base[2][j])
-        h = [torch.from_numpy(np.ascontiguousarray(np.stack(a))).pin_memory() for a in (xs, fs, bs)]
+        if os.environ.get("MGAR_WC_HOST", "0") != "0":      # experiment: write-combined pinned staging (pipeline.pinned_empty)
+            from multimodal_gar_b200 import pipeline
+            h = []
+            for a in (xs, fs, bs):
+                src = torch.from_numpy(np.ascontiguousarray(np.stack(a)))
+                dst = pipeline.pinned_empty(tuple(src.shape), src.dtype, write_combined=True)
+                dst.copy_(src)
+                h.append(dst)
+        else:
+            h = [torch.from_numpy(np.ascontiguousarray(np.stack(a))).pin_memory() for a in (xs, fs, bs)]
         host.append(h)
         devb.append([t.to(dev) for t in h])
     return host, devb

@@ -47,6 +47,11 @@ MGAR_API unsigned long long mgar_launch_count(void);
  * The library never allocates device memory. */
 MGAR_API size_t mgar_stack_workspace_bytes(int B);
 
+/* Pinned host staging for the host-buffer front end: cudaHostAlloc (portable; write_combined != 0 adds
+ * cudaHostAllocWriteCombined - for buffers the CPU only writes and the copy engines read) / cudaFreeHost. */
+MGAR_API int mgar_host_alloc(void **ptr, size_t bytes, int write_combined);
+MGAR_API int mgar_host_free(void *ptr);
+
 /* ---- roiaware_pool3d: in-box tests -------------------------------------------------------- */
 
 /* points_in_boxes_gpu: roiaware_pool3d/src/roiaware_pool3d.cpp:98-118 (kernel .cu:313-336).

@@ -36,6 +36,8 @@ SIGNATURES = {
     "mgar_fps_batch": [_i, _i, _i, _p, _i, _p, _p, _p, _p],
     "mgar_fps_stack": [_i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_stack_workspace_bytes": [_i],
+    "mgar_host_alloc": [_p, ctypes.c_size_t, _i],
+    "mgar_host_free": [_p],
     "mgar_ball_query_stack": [_i, _i, _f, _i, _p, _p, _p, _i, _p, _i, _i, _p, _i, _p, ctypes.c_size_t, _p],
     "mgar_voxel_query_stack": [_i, _i, _i, _i, _i, _f, _i, _i, _i, _p, _p, _p, _p, _p, _p],
     "mgar_batch_group_points": [_i, _i, _i, _i, _i, _p, _p, _p, _p],

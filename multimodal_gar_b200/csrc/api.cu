@@ -38,4 +38,17 @@ const char *mgar_last_error(void) { return mgar::g_err; }
 unsigned long long mgar_launch_count(void) { return mgar::g_launches.load(); }
 size_t mgar_stack_workspace_bytes(int B) { return B > 0 ? mgar::stack_ws_bytes(B) : 0; }
 
+// Pinned HOST staging buffers for the host-buffer front end (pipeline.HostFramePipeline): page-locked, portable across
+// devices, optionally write-combined (the CPU only ever WRITES frames into them; the copy engines read them without
+// snooping the CPU caches).  Explicit, caller-driven: nothing is allocated behind an operator call.
+int mgar_host_alloc(void **ptr, size_t bytes, int write_combined) {
+    MGAR_REQUIRE(ptr && bytes > 0, "host_alloc: bad argument");
+    MGAR_CUDA(cudaHostAlloc(ptr, bytes, cudaHostAllocPortable | (write_combined ? cudaHostAllocWriteCombined : 0)));
+    return MGAR_OK;
+}
+int mgar_host_free(void *ptr) {
+    if (ptr) MGAR_CUDA(cudaFreeHost(ptr));
+    return MGAR_OK;
+}
+
 }  // extern "C"

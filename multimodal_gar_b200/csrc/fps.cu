@@ -659,7 +659,10 @@ extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xy
             count_launch();
             return check_launch("fps_ball_query(dup)");
         }
-        int W = 2, PPL = n / 64;       // see fps_bq_cta.cuh: the kernel is ALU-issue bound, two warps per cloud cost the least
+        // Two warps per cloud cost the fewest instructions (throughput: many clouds per SM); four warps have the shorter
+        // round (latency: 511 against 771 cycles per round when a cloud has the SM to itself,
+        // profiles/r02_fps_round_latency.json) - used while there are fewer than 8 clouds per SM (a single frame: 40).
+        int W = b < 8 * kNumSMs ? 4 : 2, PPL = n / (32 * W);
         if (const char *e = getenv("MGAR_FPS_BQ_GEOM")) {
             int w = 0, p = 0;
             if (sscanf(e, "%d,%d", &w, &p) == 2 && 32 * w * p == n) { W = w; PPL = p; }

@@ -7,7 +7,29 @@ This is what a dataloader-fed caller uses (the reference feeds `LiDAR_Backbone` 
 encoder on device tensors, frame order preserved, no extra copies (inputs land in per-slot device buffers that the
 kernels read in place).
 """
+import ctypes
+import weakref
+
 import torch
+
+from . import _lib
+
+
+def pinned_empty(shape, dtype=torch.float32, write_combined=False):
+    """A page-locked host tensor from the library's allocator (cudaHostAlloc, portable): what a dataloader writes its frames
+    into.  write_combined=True asks for write-combined memory - the CPU must only WRITE it (reads are uncached and slow);
+    the copy engines read it without snooping the CPU caches, which can raise host-to-device throughput when several GPUs
+    pull from one host.  Freed when the tensor is garbage-collected."""
+    n = 1
+    for d in shape:
+        n *= int(d)
+    nbytes = max(1, n * torch.empty((), dtype=dtype).element_size())
+    p = ctypes.c_void_p()
+    _lib.check(_lib.lib().mgar_host_alloc(ctypes.addressof(p), nbytes, 1 if write_combined else 0), "host_alloc")
+    buf = (ctypes.c_char * nbytes).from_address(p.value)
+    t = torch.frombuffer(buf, dtype=dtype, count=n).view(*shape)
+    weakref.finalize(buf, lambda addr=p.value: _lib.lib().mgar_host_free(addr))
+    return t
 
 
 class HostFramePipeline:
