@@ -7,6 +7,7 @@ import torch
 
 import cases
 from multimodal_gar_b200 import lidar_branch, synthetic
+from multimodal_gar_b200.pcdet.ops.roiaware_pool3d import roiaware_pool3d_utils
 from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -276,3 +277,29 @@ def test_folded_batchnorm_cache_follows_the_parameters(cuda):
                                     np.ascontiguousarray(st["pooled"].cpu().numpy()[..., 3:]).reshape(-1, 1))
     scale = max(1.0, float(np.abs(want_sa).max()))
     np.testing.assert_allclose(st["sa_features"].cpu().numpy(), want_sa, rtol=1e-5, atol=1e-5 * scale)
+
+
+def test_single_process_two_devices(cuda):
+    """One process driving two GPUs (the reference's own launcher is nn.DataParallel, train_func.py:512): shared-memory
+    opt-ins and scratch are per device / caller-owned, so the second device must give the first one's bits."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs in one process")
+    from multimodal_gar_b200 import dafm
+    pts, boxes = synthetic.make_batch(9, 2, N=32768, M=24)
+    outs = []
+    for d in (0, 1):
+        dev = torch.device("cuda", d)
+        enc = _enc(dev)
+        torch.manual_seed(4)
+        fus = dafm.FusionAttentionMat(512, 512).to(dev).eval()
+        R = torch.randn((2, 24, 512), generator=torch.Generator().manual_seed(1)).to(dev)
+        L = torch.randn((2, 24, 512), generator=torch.Generator().manual_seed(2)).to(dev)
+        De = torch.cdist(T(boxes[..., :3], dev), T(boxes[..., :3], dev))
+        with torch.no_grad():
+            st = enc(T(pts[..., :3], dev), T(pts[..., 3:4], dev), T(boxes, dev), return_stages=True)
+            m = roiaware_pool3d_utils.points_in_boxes_cpu(torch.from_numpy(np.ascontiguousarray(pts[0, :, :3])), torch.from_numpy(boxes[0]))
+            f = fus(R, L, None, De)
+        outs.append((st["box_idx"].cpu(), st["pooled"].cpu(), st["fps_idx"].cpu(), st["person_features"].cpu(), m.cpu(),
+                     f[0].cpu(), f[1].cpu()))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
