@@ -176,6 +176,11 @@ def _cpu_init(threads):
     O.lib()
     _CPU_STATE["mlp"] = make_encoder().sa.mlps[0]
     _CPU_STATE["O"] = O
+    # the one stage the reference itself implements for the CPU: its compiled points_in_boxes_cpu (roiaware_pool3d.cpp:143-168)
+    try:
+        _CPU_STATE["ref_roiaware"] = O.load_ref("roiaware_pool3d_cuda")
+    except Exception:
+        _CPU_STATE["ref_roiaware"] = None
 
 
 def cpu_frame(args):
@@ -186,7 +191,13 @@ def cpu_frame(args):
     O, mlp = _CPU_STATE["O"], _CPU_STATE["mlp"]
     S, P, K, r, M = CFG["S"], CFG["P"], CFG["K"], CFG["radius"], boxes.shape[0]
     t0 = time.perf_counter()
-    O.points_in_boxes_gpu(xyz[None], boxes[None])
+    ref = _CPU_STATE.get("ref_roiaware")
+    if ref is not None:        # the reference's own CPU function: the full (M,N) in-box matrix, one thread
+        import torch
+        m = torch.zeros((M, xyz.shape[0]), dtype=torch.int32)
+        ref.points_in_boxes_cpu(torch.from_numpy(boxes), torch.from_numpy(xyz), m)
+    else:
+        O.points_in_boxes_gpu(xyz[None], boxes[None])
     t1 = time.perf_counter()
     pooled, empty = O.roipoint_pool3d(xyz[None], feat[None], boxes[None], (0.0, 0.0, 0.0), S)
     pooled = O.canonical_transform(pooled, boxes[None], empty)
@@ -228,8 +239,11 @@ def cpu_baseline_inline(frames, n_frames):
         stage = [a + b for a, b in zip(stage, st)]
     dt = time.perf_counter() - t0
     names = ["points_in_boxes", "roipoint_pool", "fps", "ball_query+group", "sa_mlp(torch-cpu)"]
-    return dict(value=n_frames / dt, unit="frames/s", cores=1, kind="port",
-                sample="%d configs[1] frame(s), oracle C port + torch-CPU shared MLP, 1 thread, %.1f s" % (n_frames, dt),
+    kind = "reference+port" if _CPU_STATE.get("ref_roiaware") is not None else "port"
+    return dict(value=n_frames / dt, unit="frames/s", cores=1, kind=kind,
+                sample="%d configs[1] frame(s): %s, oracle C port for pooling / FPS / ball query / grouping, the reference's "
+                       "nn.Sequential on torch-CPU for the shared MLP, 1 thread, %.1f s"
+                       % (n_frames, "the reference's compiled points_in_boxes_cpu" if kind != "port" else "oracle C port for the in-box test", dt),
                 stage_seconds_per_frame={k: round(v / n_frames, 4) for k, v in zip(names, stage)})
 
 
@@ -305,12 +319,16 @@ def run_reference(args, rank, world):
             list(ex.map(cpu_frames, chunks))
         dt = time.perf_counter() - t0
     value = sample * args.steps / dt
+    have_ref = os.path.exists(os.path.join(ROOT, "oracle", "_ref", "roiaware_pool3d_cuda.so"))
+    kind = "reference+port" if have_ref else "port"
     txt = ("%d of the step's %d frames per timed step (a bounded sample; frames are independent, value is frames/s), "
-           "%d worker processes x 1 thread, oracle C port + torch-CPU shared MLP" % (sample, F * world, workers))
+           "%d worker processes x 1 thread; in-box test = %s, pooling / FPS / ball query / grouping = oracle C port, shared MLP = "
+           "the reference's nn.Sequential on torch-CPU" % (sample, F * world, workers,
+           "the reference's compiled points_in_boxes_cpu (oracle/_ref)" if have_ref else "oracle C port"))
     line = dict(metric=METRIC, value=value, unit="frames/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
                 ms_per_step=1e3 * F * world / value, higher_is_better=True, scaling="weak", vs_baseline=None,
                 dtype="f32", data="synthetic", impl="reference", config=bench_config(F, world),
-                cpu_baseline=dict(value=value, unit="frames/s", cores=workers, kind="port", sample=txt,
+                cpu_baseline=dict(value=value, unit="frames/s", cores=workers, kind=kind, sample=txt,
                                   host_cores=cores, sample_frames_per_step=sample,
                                   note="the reference has a CPU implementation only for points_in_boxes_cpu (timed as "
                                        "configs[0] in the native arm's line); its CUDA kernels cannot run on host cores, "
