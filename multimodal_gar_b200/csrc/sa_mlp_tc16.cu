@@ -745,6 +745,7 @@ int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cu
         MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<4, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
         sa_mlp_tc16_kernel<4, false, 2><<<grid, kThreads, kSmem, st>>>(L1, BD, A);
         count_launch();
+        TC16_TRACE_DUMP
         return check_launch("sa_mlp_tc16 (live tiles)");
     }
     if (A.live_groups && C0 == 4) {      // live-person walk (the LiDAR branch: xyz + intensity)
