@@ -330,6 +330,20 @@ MGAR_API int mgar_voxel_sa_fwd(int N, int M, int C_in, int C1, int C2, int nsamp
                                const float *xyz, const float *new_xyz, const int *idx, const unsigned char *empty_mask,
                                const float *params, float *out, int ld_out, void *workspace, size_t workspace_bytes,
                                void *stream);
+/* mgar_voxel_sa_fwd for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same kernels and same results as mgar_voxel_sa_fwd, without the workspace: the (N,C1)
+ * scratch is a file-scope device array of MGAR_VOXEL_SA_STATIC_MAX_FLOATS floats (8 MiB per GPU that loads the library,
+ * held until exit).  N * C1 beyond that is rejected with MGAR_ENOMEM.  The call allocates nothing (no cudaMalloc /
+ * cudaFree / allocating library routine); its first call on a device resolves the array's device address
+ * (cudaGetSymbolAddress) - make one call before starting a graph capture.  Every call on a device shares the array:
+ * nothing in it has to start at zero (rows [0,N) are overwritten before they are read), but calls that overlap on the
+ * GPU (two streams without a dependency) race on it - serialise them. */
+#define MGAR_VOXEL_SA_STATIC_MAX_FLOATS (2u << 20)
+MGAR_API int mgar_voxel_sa_fwd_static(int N, int M, int C_in, int C1, int C2, int nsample, int pool_avg,
+                                      const float *features, const float *xyz, const float *new_xyz, const int *idx,
+                                      const unsigned char *empty_mask, const float *params, float *out, int ld_out,
+                                      void *stream);
 
 /* ---- fp32-faithful GEMM on tcgen05 (3xTF32) --------------------------------------------------------------- */
 

@@ -54,6 +54,7 @@ SIGNATURES = {
     "mgar_voxel_sa_param_floats": [_i, _i, _i],
     "mgar_voxel_sa_workspace_bytes": [_i, _i],
     "mgar_voxel_sa_fwd": [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p, ctypes.c_size_t, _p],
+    "mgar_voxel_sa_fwd_static": [_i, _i, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p],
     "mgar_gemm_tf32x3_supported": [_i, _i, _i],
     "mgar_gemm_tf32x3": [_i, _i, _i, _p, _i, _p, _i, _p, _i, _p, _i, _p],
     "mgar_gemm_packed_bytes": [_i, _i],

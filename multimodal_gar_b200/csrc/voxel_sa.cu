@@ -13,6 +13,8 @@
 //   kernel 2 (vsa_pool_kernel): warp per query point: lanes = channels; per sample one 128-byte gather of f_in, the
 //                               3 -> C1 position term, ReLU, running max / sum; then the C1 -> C2 output layer with the
 //                               pooled vector in shared memory.  Nothing of size (M, C, ns) is ever written.
+#include <mutex>
+
 #include "mgar_common.cuh"
 
 namespace mgar {
@@ -164,4 +166,74 @@ extern "C" int mgar_voxel_sa_fwd(int N, int M, int C_in, int C1, int C2, int nsa
                                                       params, out, ld_out);
     count_launch();
     return check_launch("voxel_sa(pool)");
+}
+
+// ---- the same two kernels for callers that cannot allocate device memory ---------------------------------------------
+// No counterpart in the reference: added for code under CUDA graph capture, tight
+// serving loops and harnesses that forbid cudaMalloc.  The (N, C1) output of the input layer - the only scratch of this
+// op - lives in a file-scope device array of MGAR_VOXEL_SA_STATIC_MAX_FLOATS floats (8 MiB) that every GPU loading the
+// library holds until exit.  Host code cannot use the array's name as a pointer (it is the host-side shadow of the
+// symbol): the device address is taken with cudaGetSymbolAddress, once per device, with that device current.
+// Every call on a device shares the array: vsa_in_kernel overwrites rows [0, N) before vsa_pool_kernel reads them and
+// nothing needs to start at zero (rows >= N keep the previous call's values and are never read); two calls that overlap
+// on the GPU (different streams, no dependency) race on it.
+namespace mgar {
+namespace {
+constexpr size_t kVsaStaticFloats = MGAR_VOXEL_SA_STATIC_MAX_FLOATS;
+static __device__ __align__(256) float g_vsa_static[kVsaStaticFloats];
+constexpr int kVsaMaxDevices = 64;
+float *g_vsa_static_ptr[kVsaMaxDevices];                      // device address of g_vsa_static, per device
+std::mutex g_vsa_static_mu;
+}  // namespace
+}  // namespace mgar
+
+extern "C" int mgar_voxel_sa_fwd_static(int N, int M, int C_in, int C1, int C2, int nsample, int pool_avg, const float *features,
+                                        const float *xyz, const float *new_xyz, const int *idx,
+                                        const unsigned char *empty_mask, const float *params, float *out, int ld_out,
+                                        void *stream) {
+    MGAR_REQUIRE(N >= 0 && M >= 0, "voxel_sa_static: negative size");
+    MGAR_REQUIRE(mgar_voxel_sa_supported(C_in, C1, C2, nsample), "voxel_sa_static: channels must be in [1, %d] (C_in=%d C1=%d C2=%d)",
+                 kVsaMaxC, C_in, C1, C2);
+    if ((size_t)N * (size_t)C1 > kVsaStaticFloats) {
+        set_error("voxel_sa_static: N * C1 = %zu floats exceeds the built-in scratch of %zu floats (%zu MiB); use "
+                  "mgar_voxel_sa_fwd with a caller-owned workspace", (size_t)N * (size_t)C1, kVsaStaticFloats,
+                  kVsaStaticFloats * sizeof(float) >> 20);
+        return MGAR_ENOMEM;
+    }
+    if (M == 0) return MGAR_OK;
+    MGAR_REQUIRE(features && xyz && new_xyz && idx && params && out, "voxel_sa_static: null pointer");
+    MGAR_REQUIRE(ld_out >= C2, "voxel_sa_static: ld_out < C2");
+    int dev = -1;
+    MGAR_CUDA(cudaGetDevice(&dev));
+    MGAR_REQUIRE(dev >= 0 && dev < kVsaMaxDevices, "voxel_sa_static: device ordinal %d out of range", dev);
+    float *f_in = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_vsa_static_mu);
+        if (!g_vsa_static_ptr[dev]) {                         // set-up: once per device, that device current
+            void *p = nullptr;
+            MGAR_CUDA(cudaGetSymbolAddress(&p, g_vsa_static));
+            MGAR_REQUIRE(p != nullptr, "voxel_sa_static: cudaGetSymbolAddress returned a null address");
+            g_vsa_static_ptr[dev] = static_cast<float *>(p);
+        }
+        f_in = g_vsa_static_ptr[dev];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const VsaOff o = vsa_off(C_in, C1, C2);
+    if (N > 0) {
+        const size_t sm = (size_t)o.wpos * sizeof(float);
+        if (sm > 48 * 1024) MGAR_CUDA(cudaFuncSetAttribute(vsa_in_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        int grid = div_up(N, kVsaWarps);
+        if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+        vsa_in_kernel<<<grid, kVsaWarps * 32, sm, st>>>(N, C_in, C1, features, params, f_in);
+        count_launch();
+        if (int rc = check_launch("voxel_sa_static(in)")) return rc;
+    }
+    const size_t sm = (size_t)(o.total - o.wpos + kVsaWarps * C1) * sizeof(float);
+    if (sm > 48 * 1024) MGAR_CUDA(cudaFuncSetAttribute(vsa_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    int grid = div_up(M, kVsaWarps);
+    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    vsa_pool_kernel<<<grid, kVsaWarps * 32, sm, st>>>(M, C_in, C1, C2, nsample, pool_avg, f_in, xyz, new_xyz, idx, empty_mask,
+                                                      params, out, ld_out);
+    count_launch();
+    return check_launch("voxel_sa_static(pool)");
 }
