@@ -590,7 +590,8 @@ def block_config4(ctx):
                 for (_, a), (n1, b) in zip(evs, evs[1:]):
                     stage[n1] = stage.get(n1, 0.0) + a.elapsed_time(b) / 3
         rows.append(dict(radius=r, nsample=K, ms_per_frame=round(ms, 4), frames_per_s=round(1e3 / ms, 1),
-                         mlp_kernel="tcgen05 3xFP16" if K == 32 else "fp32 CUDA cores (nsample != 32)",
+                         mlp_kernel="tcgen05 3xFP16" if K == 32 else ("tcgen05 3xFP16 (blocks of 32 positions)" if "fps_ball_query" in stage
+                                                                      else "fp32 CUDA cores (nsample != 32)"),
                          stages_ms={k: round(v, 4) for k, v in stage.items()}))
     return dict(workload="configs[4]: 250000 pts x 200 boxes, one frame, S=512 P=512 MLP 4-64-128", sweep=rows)
 

@@ -305,6 +305,10 @@ MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const flo
  * layout), NULL / 0 otherwise; the library allocates nothing. */
 MGAR_API size_t mgar_sa_mlp_tc_workspace_bytes(int M, int group_size);
 MGAR_API int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg);
+/* nsample 16 and 64 also run on the tensor cores when ONLY group_max is wanted (out == NULL, uniform layout, whole
+ * 32-position blocks per group): the kernel walks blocks of 32 positions - two 16-sample centroids or half a 64-sample
+ * one - and the max over blocks equals the max over centroids.  This query answers for that call shape. */
+MGAR_API int mgar_sa_mlp_tc_group_max_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg);
 MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float *xyz, int xyz_stride,
                                 const int *xyz_batch_cnt, const float *new_xyz, const int *new_xyz_batch_cnt,
                                 int uniform_n, int uniform_m, const float *features, int feat_stride, const int *idx,

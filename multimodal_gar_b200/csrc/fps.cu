@@ -463,8 +463,9 @@ fps_bq_warp_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs
         __syncwarp();
         for (int l = lane; l < K; l += 32) row[l] = ball_idx[l];   // written by this warp (same lanes) in round 1
         __syncwarp();
-        // dup_rows == 0: the caller only walks the distinct centroids (live_cnt), rounded up to a tile of four
-        const int lim = dup_rows ? m : min(m, (j + 3) & ~3);
+        // dup_rows == 0: the caller only walks the distinct centroids (live_cnt), rounded up to eight
+        // (a tile of the MLP kernel = 128 positions = 4 centroids of 32 samples, 8 of 16)
+        const int lim = dup_rows ? m : min(m, (j + 7) & ~7);
         for (int e = lane; e < (lim - j) * K; e += 32) ball_idx[(size_t)j * K + e] = row[e % K];
     }
     // number of DISTINCT samples: centroids live .. m-1 repeat centroid 0 (same ball, same features)

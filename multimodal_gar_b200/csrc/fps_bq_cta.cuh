@@ -262,8 +262,9 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     __syncthreads();
     if (done) {                                          // samples j .. m-1 are point 0 = sample 0: their balls are row 0
         for (int q = j + tid; q < m; q += W * 32) sidx[q] = 0;
-        // dup_rows == 0: the caller only walks the distinct centroids (live_cnt), rounded up to a tile of four
-        const int lim = dup_rows ? m : min(m, (j + 3) & ~3);
+        // dup_rows == 0: the caller only walks the distinct centroids (live_cnt), rounded up to eight
+        // (a tile of the MLP kernel = 128 positions = 4 centroids of 32 samples, 8 of 16)
+        const int lim = dup_rows ? m : min(m, (j + 7) & ~7);
         for (int q = j + w; q < lim; q += W)
             for (int l = lane; l < K; l += 32) ball_idx[(size_t)q * K + l] = s_row0[l];
         __syncthreads();

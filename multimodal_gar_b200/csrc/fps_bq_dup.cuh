@@ -186,7 +186,7 @@ __device__ __forceinline__ void bq_dup_body(const DupCtx &C) {
     __syncthreads();
     if (done) {
         for (int q = j + tid; q < m; q += kDupW * 32) C.sidx[q] = 0;
-        const int lim = C.dup_rows ? m : min(m, (j + 3) & ~3);
+        const int lim = C.dup_rows ? m : min(m, (j + 7) & ~7);
         for (int q = j + w; q < lim; q += kDupW)
             for (int l = lane; l < K; l += 32) C.ball_idx[(size_t)q * K + l] = C.s_row0[l];
         __syncthreads();

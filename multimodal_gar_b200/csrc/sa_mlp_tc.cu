@@ -405,13 +405,24 @@ using namespace mgar;
 extern "C" size_t mgar_sa_mlp_tc_workspace_bytes(int M, int group_size) {
     if (M <= 0 || group_size <= 0) return 0;
     const size_t groups = ((size_t)M + group_size - 1) / group_size;
-    const size_t tiles = groups * (size_t)((group_size + 3) / 4);
+    const size_t tiles = groups * (size_t)((2 * group_size + 3) / 4);    // nsample 64: two blocks of 32 positions per centroid
     return (4 + (tiles > groups ? tiles : groups)) * sizeof(int);
 }
 
 extern "C" int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg) {
     return nsample == kTcNS && C_in >= 0 && C_in <= 4 && n_layers == 2 && channels_host && channels_host[0] == 3 + C_in &&
            channels_host[1] == kTcC1 && channels_host[2] == kTcC2 && !pool_avg;
+}
+
+// nsample 16 / 64 when ONLY the per-group max is wanted (out == NULL): the 3xFP16 kernel walks blocks of 32 positions
+// (TcArgs::ns).  MGAR_TC_NS32_ONLY=1 switches it off (A/B runs against the fp32 kernel).
+extern "C" int mgar_sa_mlp_tc_group_max_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg) {
+    if (nsample == kTcNS) return mgar_sa_mlp_tc_supported(nsample, C_in, n_layers, channels_host, pool_avg);
+    if (nsample != 16 && nsample != 64) return 0;
+    if (getenv("MGAR_TC_NS32_ONLY")) return 0;
+    const char *mode = getenv("MGAR_TC_MODE");
+    if (mode && mode[0] == 't') return 0;
+    return mgar_sa_mlp_tc_supported(kTcNS, C_in, n_layers, channels_host, pool_avg);
 }
 
 extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float *xyz, int xyz_stride,
@@ -422,8 +433,11 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
                                   float *group_max, int group_size, const int *group_zero, const int *group_live_cnt,
                                   int pool_avg, void *workspace, size_t workspace_bytes, void *stream) {
     MGAR_REQUIRE(B >= 1 && M >= 0, "sa_mlp_tc: bad size");
-    MGAR_REQUIRE(mgar_sa_mlp_tc_supported(nsample, C_in, n_layers, channels_host, pool_avg),
-                 "sa_mlp_tc: only nsample=32, C_in<=4, channels [3+C_in,64,128], max-pool run on the tensor-core path");
+    const bool ns32 = nsample == kTcNS;
+    MGAR_REQUIRE(ns32 ? mgar_sa_mlp_tc_supported(nsample, C_in, n_layers, channels_host, pool_avg)
+                      : (!out && group_max && mgar_sa_mlp_tc_group_max_supported(nsample, C_in, n_layers, channels_host, pool_avg)),
+                 "sa_mlp_tc: only nsample=32 (16 / 64 with out == NULL and a group_max), C_in<=4, channels [3+C_in,64,128], "
+                 "max-pool run on the tensor-core path");
     if (M == 0) return MGAR_OK;
     MGAR_REQUIRE(xyz && new_xyz && idx && params && params_host && (out || group_max), "sa_mlp_tc: null pointer");
     MGAR_REQUIRE(features || C_in == 0, "sa_mlp_tc: features missing");
@@ -431,6 +445,12 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     MGAR_REQUIRE(!group_max || group_size >= 1, "sa_mlp_tc: group_size must be >= 1");
     const bool uniform = uniform_n > 0;
     MGAR_REQUIRE(uniform || (xyz_batch_cnt && new_xyz_batch_cnt), "sa_mlp_tc: batch counts missing");
+    // nsample != 32: the kernel's unit is a block of 32 positions - Mv blocks, gsv per group, muv per cloud
+    MGAR_REQUIRE(ns32 || (uniform && ((long long)group_size * nsample) % 32 == 0 && ((long long)uniform_m * nsample) % 32 == 0 &&
+                          M % group_size == 0),
+                 "sa_mlp_tc: nsample %d needs the uniform layout with whole 32-position blocks per group", nsample);
+    const int Mv = ns32 ? M : (int)((long long)M * nsample / 32);
+    const int gsv = ns32 ? group_size : group_size * nsample / 32, muv = ns32 ? uniform_m : uniform_m * nsample / 32;
     const int C0 = 3 + C_in;
     TcLayer1 L1;
     for (int o = 0; o < kTcC1; o++) {
@@ -445,15 +465,15 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
         if (int rc = stack_prefix(new_xyz_batch_cnt, xyz_batch_cnt, B, 1, ws.a, ws.b, nullptr, st)) return rc;
     }
     TcArgs A;
-    A.B = B; A.M = M; A.C_in = C_in;
+    A.B = B; A.M = Mv; A.C_in = C_in; A.ns = nsample;
     A.xyz = xyz; A.xyz_stride = xyz_stride; A.new_xyz = new_xyz;
     A.features = features; A.feat_stride = feat_stride;
-    A.pre_xyz = ws.b; A.pre_new = ws.a; A.uniform = uniform ? 1 : 0; A.n_u = uniform_n; A.m_u = uniform_m;
+    A.pre_xyz = ws.b; A.pre_new = ws.a; A.uniform = uniform ? 1 : 0; A.n_u = uniform_n; A.m_u = muv;
     A.idx = idx; A.empty_mask = empty_mask;
     A.w2t = params + C0 * kTcC1 + 2 * kTcC1;
     A.sc2 = A.w2t + kTcC1 * kTcC2; A.sh2 = A.sc2 + kTcC2;
     A.out = out; A.ld_out = ld_out;
-    A.gmax = group_max; A.group_size = group_size > 0 ? group_size : 1; A.group_zero = group_zero;
+    A.gmax = group_max; A.group_size = gsv > 0 ? gsv : 1; A.group_zero = group_zero;
     A.tr_zext = nullptr; A.tr_arg = nullptr; A.tr_sum = nullptr; A.tr_sq = nullptr;
     A.live_groups = nullptr; A.n_live = nullptr; A.live_tiles = nullptr; A.m_shift = -1;
     A.packed4 = (C0 == 4 && xyz_stride == 4 && feat_stride == 4 && features == xyz + 3 &&
@@ -465,10 +485,10 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     A.trace = d_trace;
 #endif
     if (group_max) {
-        const size_t groups = ((size_t)M + A.group_size - 1) / A.group_size;
+        const size_t groups = ((size_t)Mv + A.group_size - 1) / A.group_size;
         MGAR_CUDA(cudaMemsetAsync(group_max, 0, groups * kTcC2 * sizeof(float), st));
     }
-    const int n_tiles = (M + 3) / 4;
+    const int n_tiles = (Mv + 3) / 4;
     const int grid = n_tiles < kNumSMs ? n_tiles : kNumSMs;     // persistent: one CTA per SM
 #ifndef MGAR_TC_TRACE
     {   // default: the fp16-split kernel (same accuracy, half the tensor cycles); MGAR_TC_MODE=tf32 keeps 3xTF32
@@ -479,7 +499,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
             // Asked for with ld_out == -1 (see the header); MGAR_TC_SKIP_EMPTY=0/1 overrides for A/B runs.
             const char *skip = getenv("MGAR_TC_SKIP_EMPTY");
             const bool want = skip ? skip[0] == '1' : ld_out == -1;
-            if (want && C0 == 4 && !out && group_max && group_zero && uniform && uniform_m == group_size && group_size % 4 == 0 &&
+            if (want && C0 == 4 && !out && group_max && group_zero && uniform && uniform_m == group_size && gsv % 4 == 0 &&
                 M % group_size == 0) {
                 const int G = M / group_size;
                 int *live = static_cast<int *>(workspace);
@@ -490,9 +510,9 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
                 }
                 if (group_live_cnt && !getenv("MGAR_TC_NO_LIVE_TILES")) {
                     // distinct centroids only (see TcArgs::live_tiles): the sampling kernel reported how many each person has
-                    if (int rc = tc_build_live_tiles(group_zero, group_live_cnt, G, group_size, live + 4, live, st)) return rc;
+                    if (int rc = tc_build_live_tiles(group_zero, group_live_cnt, G, gsv, nsample, live + 4, live, st)) return rc;
                     A.live_tiles = live + 4; A.n_live = live;
-                    for (int sft = 0; sft < 31; sft++) if ((1 << sft) == group_size) A.m_shift = sft;
+                    for (int sft = 0; sft < 31; sft++) if ((1 << sft) == gsv) A.m_shift = sft;
                 } else {
                     if (int rc = tc_compact_live_groups(group_zero, G, live + 4, live, st)) return rc;
                     A.live_groups = live + 4; A.n_live = live;
@@ -517,6 +537,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
 #else
 #define MGAR_TC_TRACE_DUMP
 #endif
+    MGAR_REQUIRE(ns32, "sa_mlp_tc: MGAR_TC_MODE=tf32 runs nsample 32 only");
 #define MGAR_TC_CASE(c0)                                                                                        \
     if (C0 == c0) {                                                                                             \
         MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc_kernel<c0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmem)); \

@@ -47,15 +47,21 @@ struct TcArgs {
     // so the centroids live_cnt .. group_size-1 repeat centroid 0 and cannot change the person's max).  Same
     // preconditions as live_groups; m_shift = log2(group_size) or -1.
     const int *live_tiles; int m_shift;
+    // samples per centroid: 32 (a TMEM lane quarter = one centroid), or - sa_mlp_tc16 with out == null only - 16 / 64.
+    // The kernel always walks BLOCKS of 32 consecutive positions of the flat (M * ns) sample array: a block is two
+    // centroids (ns = 16) or half a centroid (ns = 64), and M, m_u, group_size, live_tiles, m_shift count blocks.  The max
+    // over a block, the folded BatchNorm + ReLU (monotone) and the max over a person's blocks commute with the
+    // reference's max over a centroid's samples followed by the max over the person's centroids.
+    int ns;
 };
 
 // sa_mlp_tc16.cu: the 3xFP16 kernel (default); sa_mlp_tc.cu keeps the 3xTF32 kernel (MGAR_TC_MODE=tf32)
 int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);
 // live[0 .. *n_live) = ascending indices g < G with group_zero[g] == 0 (one small launch)
 int tc_compact_live_groups(const int *group_zero, int G, int *live, int *n_live, cudaStream_t st);
-// tiles[0 .. *n_tiles) = g * group_size + 4 q for every g < G with group_zero[g] == 0 and q < ceil(live_cnt[g] / 4),
-// ascending (one small launch)
-int tc_build_live_tiles(const int *group_zero, const int *live_cnt, int G, int group_size, int *tiles, int *n_tiles,
+// tiles[0 .. *n_tiles) = g * group_size + 4 q for every g < G with group_zero[g] == 0 and q < ceil(blocks / 4), blocks =
+// ceil(live_cnt[g] * ns / 32) position blocks of 32 (group_size counts blocks), ascending (one small launch)
+int tc_build_live_tiles(const int *group_zero, const int *live_cnt, int G, int group_size, int ns, int *tiles, int *n_tiles,
                         cudaStream_t st);
 int sa_mlp_tc16_launch_train(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);   // C0 = 4, 5
 

@@ -463,6 +463,10 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             u_delta = i_delta = (real - u_cloud) * A.m_u;
             u_start = (long long)real * A.n_u;
         }
+        // ns != 32: the walk's unit m is a BLOCK of 32 positions (TcArgs::ns); cen(m) = the centroid this lane's position
+        // belongs to (ns = 16: per half warp)
+        const int ns = A.ns;
+        auto cen = [&](int m) { return ns == kTcNS ? m : (ns == 64 ? (m >> 1) : 2 * m + (lane >> 4)); };
         auto load_idx = [&](int i, int &iv, int &em, int &mr) {   // local tile i -> this lane's sample index (mr: real centroid)
             int m = (t_beg + i) * 4 + pw;
             iv = -1; em = 0; mr = 0;
@@ -470,7 +474,8 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
                 if (i < my_tiles) {
                     mr = __ldg(A.live_tiles + t_beg + i) + pw;
                     iv = __ldg(A.idx + (size_t)mr * kTcNS + lane);
-                    if (A.empty_mask) em = A.empty_mask[mr];
+                    if (A.empty_mask) em = A.empty_mask[cen(mr)];
+                    if (ns == 64 && (mr & 1) && __ldg(A.idx + (size_t)(mr >> 1) * 64) < 0) em = 1;
                 }
                 return;
             }
@@ -483,12 +488,15 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
                     m += i_delta;
                 }
                 iv = __ldg(A.idx + (size_t)m * kTcNS + lane);
-                if (A.empty_mask) em = A.empty_mask[m];
+                if (A.empty_mask) em = A.empty_mask[cen(m)];
+                if (ns == 64 && (m & 1) && __ldg(A.idx + (size_t)(m >> 1) * 64) < 0) em = 1;
             }
         };
         auto load_pt = [&](int i, int iv, int em, int mr, float (&v)[C0], float (&q)[3], bool &live) {
             int m = tiled ? mr : (t_beg + i) * 4 + pw;
-            const int first = __shfl_sync(0xffffffffu, iv, 0);
+            // slot 0 of the centroid's row (-1: empty ball): lane 0 of a whole centroid, lane 0 / 16 of a pair of
+            // 16-sample centroids; the second block of a 64-sample centroid got it as `em` from load_idx
+            const int first = __shfl_sync(0xffffffffu, iv, ns == 16 ? (lane & 16) : 0);
             live = (i < my_tiles) && (tiled || m < M) && first >= 0 && !em;
             if (live) {
                 long long start;
@@ -509,7 +517,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
                         start = (long long)u_cloud * A.n_u;
                     }
                 } else {
-                    start = __ldg(A.pre_xyz + find_batch_tc(A.pre_new, A.B, m));
+                    start = __ldg(A.pre_xyz + find_batch_tc(A.pre_new, A.B, cen(m)));
                 }
                 const long long p = start + (iv < 0 ? 0 : iv);
                 if (C0 == 4 && A.packed4) {
@@ -522,9 +530,10 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
 #pragma unroll
                     for (int cc = 3; cc < C0; cc++) v[cc] = __ldg(A.features + p * A.feat_stride + (cc - 3));
                 }
-                q[0] = __ldg(A.new_xyz + (size_t)m * 3 + 0);
-                q[1] = __ldg(A.new_xyz + (size_t)m * 3 + 1);
-                q[2] = __ldg(A.new_xyz + (size_t)m * 3 + 2);
+                const size_t mc = (size_t)cen(m) * 3;
+                q[0] = __ldg(A.new_xyz + mc + 0);
+                q[1] = __ldg(A.new_xyz + mc + 1);
+                q[2] = __ldg(A.new_xyz + mc + 2);
             }
         };
         // layer-1 input row of local tile i -> x stage i & 1, scaled by the centroid's 2^-e
@@ -668,14 +677,14 @@ int tc_compact_live_groups(const int *group_zero, int G, int *live, int *n_live,
 // counts and writes its tile rows, a warp per person, lanes = consecutive tiles.  (The first version - one CTA looping
 // over all persons - took 27 us per step, 3 % of it.)
 constexpr int kTilesCta = 256;
-__device__ __forceinline__ int person_tiles(const int *__restrict__ group_zero, const int *__restrict__ live_cnt, int g, int gs) {
+__device__ __forceinline__ int person_tiles(const int *__restrict__ group_zero, const int *__restrict__ live_cnt, int g, int gs, int ns) {
     if (__ldg(group_zero + g) != 0) return 0;
-    int lc = __ldg(live_cnt + g);
+    int lc = (__ldg(live_cnt + g) * ns + 31) >> 5;                   // centroids -> blocks of 32 positions (gs counts blocks)
     lc = lc < 1 ? 1 : (lc > gs ? gs : lc);
     return (lc + 3) >> 2;
 }
 __global__ void __launch_bounds__(kTilesCta)
-build_live_tiles_kernel(const int *__restrict__ group_zero, const int *__restrict__ live_cnt, int G, int gs,
+build_live_tiles_kernel(const int *__restrict__ group_zero, const int *__restrict__ live_cnt, int G, int gs, int ns,
                         int *__restrict__ tiles, int *__restrict__ n_tiles) {
     __shared__ int s_warp[kTilesCta / 32];
     __shared__ int s_first[kTilesCta], s_cnt[kTilesCta];
@@ -683,13 +692,13 @@ build_live_tiles_kernel(const int *__restrict__ group_zero, const int *__restric
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g0 = blockIdx.x * kTilesCta;
     int before = 0;
-    for (int g = tid; g < g0; g += kTilesCta) before += person_tiles(group_zero, live_cnt, g, gs);
+    for (int g = tid; g < g0; g += kTilesCta) before += person_tiles(group_zero, live_cnt, g, gs, ns);
     before = __reduce_add_sync(0xffffffffu, before);
     if (tid == 0) s_base = 0;
     __syncthreads();
     if (lane == 0 && before) atomicAdd(&s_base, before);
     const int g = g0 + tid;
-    const int c = g < G ? person_tiles(group_zero, live_cnt, g, gs) : 0;
+    const int c = g < G ? person_tiles(group_zero, live_cnt, g, gs, ns) : 0;
     int incl = c;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -710,10 +719,10 @@ build_live_tiles_kernel(const int *__restrict__ group_zero, const int *__restric
     if (g == G - 1) *n_tiles = first + c;
 }
 
-int tc_build_live_tiles(const int *group_zero, const int *live_cnt, int G, int group_size, int *tiles, int *n_tiles,
+int tc_build_live_tiles(const int *group_zero, const int *live_cnt, int G, int group_size, int ns, int *tiles, int *n_tiles,
                         cudaStream_t st) {
     if (G <= 0) return MGAR_OK;
-    build_live_tiles_kernel<<<(G + kTilesCta - 1) / kTilesCta, kTilesCta, 0, st>>>(group_zero, live_cnt, G, group_size, tiles, n_tiles);
+    build_live_tiles_kernel<<<(G + kTilesCta - 1) / kTilesCta, kTilesCta, 0, st>>>(group_zero, live_cnt, G, group_size, ns, tiles, n_tiles);
     count_launch();
     return check_launch("build_live_tiles");
 }

@@ -134,10 +134,13 @@ class PointPersonEncoder(nn.Module):
         ball_idx = live_cnt = None
         packed = None if (self.training or torch.is_grad_enabled()) else self.sa._pack(pooled.device)[0]
         C = pooled.shape[2] - 3
-        if packed is not None and sa_mlp_fused.tc_supported(packed[0], g.nsample, C):
+        want_out = return_stages or self.keep_sa_features
+        # nsample 16 / 64 run on the tensor cores too when only the person max is wanted (blocks of 32 positions)
+        if packed is not None and (sa_mlp_fused.tc_supported(packed[0], g.nsample, C) or
+                                   (not want_out and (P * g.nsample) % 32 == 0 and
+                                    sa_mlp_fused.tc_group_max_supported(packed[0], g.nsample, C))):
             # fused path: every kernel reads the pooled (.., 3+C) rows in place; 5 launches per step
             flat = pooled.view(B * M * S, 3 + C)
-            want_out = return_stages or self.keep_sa_features
             # distinct-centroid walk: pooled clouds repeat their points, the sampling kernel reports how many distinct
             # samples each person has and the MLP computes only those (the others repeat centroid 0: same max)
             walk = self.skip_empty_persons and self.skip_repeated_centroids and not want_out

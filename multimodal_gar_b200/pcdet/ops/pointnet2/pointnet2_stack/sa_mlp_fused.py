@@ -45,6 +45,14 @@ def tc_supported(channels, nsample, C_in, pool_avg=False):
                                                     1 if pool_avg else 0))
 
 
+def tc_group_max_supported(channels, nsample, C_in, pool_avg=False):
+    """True when the tcgen05 path can produce the per-group max for this shape WITHOUT the per-centroid features
+    (want_out=False): nsample 32 as above, and also 16 / 64 (mgar_sa_mlp_tc_group_max_supported)."""
+    ch = (ctypes.c_int * len(channels))(*channels)
+    return bool(_lib.lib().mgar_sa_mlp_tc_group_max_supported(int(nsample), int(C_in), len(channels) - 1,
+                                                              ctypes.addressof(ch), 1 if pool_avg else 0))
+
+
 def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features, idx,
                    empty_mask=None, out=None, pool_avg=False, uniform=None, params_host=None, impl=None,
                    group_max=None, group_size=0, group_zero=None, want_out=True, skip_zero_groups=False,
