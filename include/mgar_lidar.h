@@ -300,6 +300,14 @@ MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const flo
  * with the skip above in force the kernel walks, per live group, only the tiles of four centroids that cover its first
  * group_live_cnt[g] centroids - the others repeat centroid 0 (same ball, same feature row) and cannot change the
  * group's max, so group_max holds the same bits.
+ * Distinct-sample walk: group_point_cnt (ceil(M/group_size)) int32, optional (nsample 32, with group_live_cnt):
+ * group_point_cnt[g] = p states that group g's cloud holds p DISTINCT points and slot k repeats point k mod p - what
+ * RoIPointPool3d's wrap produces (roipoint_pool3d_kernel.cu:86-97; min(in-box points, S), exported by
+ * mgar_roipoint_pool_from_masks).  A ball row of such a cloud repeats its hits once it runs out of distinct ones (the
+ * copies with index >= p, then the first hit as padding, ball_query_gpu.cu:49-60); the kernel then computes only the
+ * octets of sample slots that start with a distinct sample, packed sixteen to a tile.  group_max holds the same maxima
+ * to fp32 rounding of the operand split (<= 1e-6 relative, not the same bits: the power-of-two operand scale is shared
+ * by different rows); a count that is not the cloud's period makes the result wrong - pass NULL when in doubt.
  * workspace: device scratch of mgar_sa_mlp_tc_workspace_bytes(M, group_size) bytes when the skip is asked for, of
  * mgar_stack_workspace_bytes(B) bytes with ragged batch counts (the two never combine: the skip needs the uniform
  * layout), NULL / 0 otherwise; the library allocates nothing. */
@@ -315,7 +323,8 @@ MGAR_API int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const float
                                 const unsigned char *empty_mask, int n_layers, const int *channels_host,
                                 const float *params, const float *params_host, float *out, int ld_out,
                                 float *group_max, int group_size, const int *group_zero, const int *group_live_cnt,
-                                int pool_avg, void *workspace, size_t workspace_bytes, void *stream);
+                                const int *group_point_cnt, int pool_avg, void *workspace, size_t workspace_bytes,
+                                void *stream);
 
 /* ---- NeighborVoxelSAModuleMSG, one scale, eval mode (voxel_pool_modules.py:70-130) ------------------------------ */
 

@@ -405,8 +405,9 @@ using namespace mgar;
 extern "C" size_t mgar_sa_mlp_tc_workspace_bytes(int M, int group_size) {
     if (M <= 0 || group_size <= 0) return 0;
     const size_t groups = ((size_t)M + group_size - 1) / group_size;
-    const size_t tiles = groups * (size_t)((2 * group_size + 3) / 4);    // nsample 64: two blocks of 32 positions per centroid
-    return (4 + (tiles > groups ? tiles : groups)) * sizeof(int);
+    // the longest list is the live-unit one: up to four octets per centroid, a person's padded to a multiple of 16
+    const size_t units = groups * (size_t)((4 * group_size + 15) / 16 * 16);
+    return (4 + units) * sizeof(int);
 }
 
 extern "C" int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg) {
@@ -431,7 +432,8 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
                                   const unsigned char *empty_mask, int n_layers, const int *channels_host,
                                   const float *params, const float *params_host, float *out, int ld_out,
                                   float *group_max, int group_size, const int *group_zero, const int *group_live_cnt,
-                                  int pool_avg, void *workspace, size_t workspace_bytes, void *stream) {
+                                  const int *group_point_cnt, int pool_avg, void *workspace, size_t workspace_bytes,
+                                  void *stream) {
     MGAR_REQUIRE(B >= 1 && M >= 0, "sa_mlp_tc: bad size");
     const bool ns32 = nsample == kTcNS;
     MGAR_REQUIRE(ns32 ? mgar_sa_mlp_tc_supported(nsample, C_in, n_layers, channels_host, pool_avg)
@@ -475,7 +477,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     A.out = out; A.ld_out = ld_out;
     A.gmax = group_max; A.group_size = gsv > 0 ? gsv : 1; A.group_zero = group_zero;
     A.tr_zext = nullptr; A.tr_arg = nullptr; A.tr_sum = nullptr; A.tr_sq = nullptr;
-    A.live_groups = nullptr; A.n_live = nullptr; A.live_tiles = nullptr; A.m_shift = -1;
+    A.live_groups = nullptr; A.n_live = nullptr; A.live_tiles = nullptr; A.live_units = nullptr; A.m_shift = -1;
     A.packed4 = (C0 == 4 && xyz_stride == 4 && feat_stride == 4 && features == xyz + 3 &&
                  (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) ? 1 : 0;
 #ifdef MGAR_TC_TRACE
@@ -508,7 +510,14 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
                               "= %zu bytes, got %zu", mgar_sa_mlp_tc_workspace_bytes(M, group_size), workspace ? workspace_bytes : (size_t)0);
                     return MGAR_ENOMEM;
                 }
-                if (group_live_cnt && !getenv("MGAR_TC_NO_LIVE_TILES")) {
+                if (group_live_cnt && group_point_cnt && ns32 && M < (1 << 29) && !getenv("MGAR_TC_NO_LIVE_TILES") &&
+                    !getenv("MGAR_TC_NO_LIVE_UNITS")) {
+                    // distinct samples of the distinct centroids only (see TcArgs::live_units)
+                    if (int rc = tc_build_live_units(group_zero, group_live_cnt, group_point_cnt, idx, G, gsv, uniform_n, live + 4,
+                                                     live, st)) return rc;
+                    A.live_units = live + 4; A.n_live = live;
+                    for (int sft = 0; sft < 31; sft++) if ((1 << sft) == gsv) A.m_shift = sft;
+                } else if (group_live_cnt && !getenv("MGAR_TC_NO_LIVE_TILES")) {
                     // distinct centroids only (see TcArgs::live_tiles): the sampling kernel reported how many each person has
                     if (int rc = tc_build_live_tiles(group_zero, group_live_cnt, G, gsv, nsample, live + 4, live, st)) return rc;
                     A.live_tiles = live + 4; A.n_live = live;

@@ -47,6 +47,15 @@ struct TcArgs {
     // so the centroids live_cnt .. group_size-1 repeat centroid 0 and cannot change the person's max).  Same
     // preconditions as live_groups; m_shift = log2(group_size) or -1.
     const int *live_tiles; int m_shift;
+    // distinct-sample walk (sa_mlp_tc16 only, ns = 32, out == null; null = off): live_units[16 t + u], t < *n_live, u < 16 =
+    // (centroid << 2 | octet) [| 1 << 31: empty ball]: tile t is sixteen OCTETS of sample slots (slots 8 o .. 8 o + 7 of the
+    // centroid's ball row) of ONE person, instead of four whole centroids.  A ball row repeats its hits once it runs out
+    // of distinct ones (copies of a wrapped cloud, then the first hit as padding); the list holds only the octets that
+    // start with a distinct sample.  A TMEM lane quarter (32 positions) then mixes up to four centroids: the epilogue's
+    // max over the quarter, the folded BatchNorm + ReLU (monotone) and the running person max still commute with the
+    // reference's max over a centroid's samples followed by the max over the person's centroids; the power-of-two
+    // operand scale is per quarter either way.
+    const int *live_units;
     // samples per centroid: 32 (a TMEM lane quarter = one centroid), or - sa_mlp_tc16 with out == null only - 16 / 64.
     // The kernel always walks BLOCKS of 32 consecutive positions of the flat (M * ns) sample array: a block is two
     // centroids (ns = 16) or half a centroid (ns = 64), and M, m_u, group_size, live_tiles, m_shift count blocks.  The max
@@ -63,6 +72,10 @@ int tc_compact_live_groups(const int *group_zero, int G, int *live, int *n_live,
 // ceil(live_cnt[g] * ns / 32) position blocks of 32 (group_size counts blocks), ascending (one small launch)
 int tc_build_live_tiles(const int *group_zero, const int *live_cnt, int G, int group_size, int ns, int *tiles, int *n_tiles,
                         cudaStream_t st);
+// units[16 t + u] as TcArgs::live_units describes, *n_tiles = number of tiles (zeroed here; one small launch).  point_cnt[g] =
+// number of DISTINCT points of group g's cloud (slot k of the cloud holds point k mod point_cnt[g]).
+int tc_build_live_units(const int *group_zero, const int *live_cnt, const int *point_cnt, const int *idx, int G, int group_size,
+                        int n_u, int *units, int *n_tiles, cudaStream_t st);
 int sa_mlp_tc16_launch_train(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);   // C0 = 4, 5
 
 }  // namespace mgar

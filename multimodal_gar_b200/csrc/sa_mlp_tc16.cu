@@ -144,7 +144,8 @@ __device__ __forceinline__ void sts_pack2_w(uint32_t a0, uint32_t a1, uint32_t b
     sts4(b0, lo[0], lo[1], lo[2], lo[3]); sts4(b1, lo[4], hi[3], hi[4], 0.f);
 }
 
-// kCompact: 0 = every centroid; 1 = live-person list (TcArgs::live_groups); 2 = live-TILE list (TcArgs::live_tiles)
+// kCompact: 0 = every centroid; 1 = live-person list (TcArgs::live_groups); 2 = live-TILE list (TcArgs::live_tiles);
+//           3 = live-UNIT list (TcArgs::live_units): a tile is 16 octets of sample slots, all of one person
 template <int C0, bool kTrain = false, int kCompact = 0>
 __global__ void __launch_bounds__(kThreads, 1)
 sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ TcBound BD, const __grid_constant__ TcArgs A) {
@@ -176,7 +177,8 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // M counts "virtual" centroids when the live-person list is in use (TcArgs::live_groups): only they are walked
     constexpr bool compact = kCompact == 1;
-    constexpr bool tiled = kCompact == 2;      // tile i of the walk = the four real centroids live_tiles[i] .. +3 of ONE person
+    constexpr bool units = kCompact == 3;      // tile i of the walk = the 16 (centroid, octet) entries live_units[16 i ..] of ONE person
+    constexpr bool tiled = kCompact == 2 || units;   // tile i = the four real centroids live_tiles[i] .. +3 of ONE person
     const int M = tiled ? __ldg(A.n_live) * 4 : (compact ? __ldg(A.n_live) * A.group_size : A.M);
     const int n_tiles = (M + 3) >> 2;
     // contiguous tile range per CTA: consecutive tiles belong to the same person, so the running
@@ -316,8 +318,11 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         for (int i = 0; i < my_tiles; i++) {
             const int t = i % kAcc, u = i / kAcc;
             int tile_person = 0;
-            if (tiled) tile_person = A.m_shift >= 0 ? __ldg(A.live_tiles + t_beg + i) >> A.m_shift
-                                                    : __ldg(A.live_tiles + t_beg + i) / gs;
+            if (tiled) {
+                const int c0 = units ? (__ldg(A.live_units + (size_t)(t_beg + i) * 16) & 0x7fffffff) >> 2
+                                     : __ldg(A.live_tiles + t_beg + i);
+                tile_person = A.m_shift >= 0 ? c0 >> A.m_shift : c0 / gs;
+            }
             mbar_wait(TFULL(t), u & 1);
             if (warp == 0) TR(12, i);
             tc_fence_after();
@@ -467,9 +472,23 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         // belongs to (ns = 16: per half warp)
         const int ns = A.ns;
         auto cen = [&](int m) { return ns == kTcNS ? m : (ns == 64 ? (m >> 1) : 2 * m + (lane >> 4)); };
+        int ent_next = 0;                                        // live-unit walk: this lane's list entry of the next load_idx call
+        if (units && g < my_tiles) ent_next = __ldg(A.live_units + (size_t)(t_beg + g) * 16 + pw * 4 + (lane >> 3));
         auto load_idx = [&](int i, int &iv, int &em, int &mr) {   // local tile i -> this lane's sample index (mr: real centroid)
             int m = (t_beg + i) * 4 + pw;
             iv = -1; em = 0; mr = 0;
+            if (units) {                                      // lane -> octet pw * 4 + lane / 8 of the tile, slot lane % 8 of it
+                // the entry was fetched by the previous call (the calls walk this group's tiles in order, i += 2): a tile's
+                // sixteen entries are a 64-byte line of their own, i.e. a trip to L2 that must not sit in front of the index load
+                const int e = ent_next;
+                if (i + 2 < my_tiles) ent_next = __ldg(A.live_units + (size_t)(t_beg + i + 2) * 16 + pw * 4 + (lane >> 3));
+                if (i < my_tiles) {
+                    mr = (e & 0x7fffffff) >> 2;
+                    em = e < 0;                               // bit 31: empty ball (the builder saw -1 in slot 0)
+                    iv = __ldg(A.idx + (size_t)mr * kTcNS + (e & 3) * 8 + (lane & 7));
+                }
+                return;
+            }
             if (tiled) {
                 if (i < my_tiles) {
                     mr = __ldg(A.live_tiles + t_beg + i) + pw;
@@ -496,7 +515,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             int m = tiled ? mr : (t_beg + i) * 4 + pw;
             // slot 0 of the centroid's row (-1: empty ball): lane 0 of a whole centroid, lane 0 / 16 of a pair of
             // 16-sample centroids; the second block of a 64-sample centroid got it as `em` from load_idx
-            const int first = __shfl_sync(0xffffffffu, iv, ns == 16 ? (lane & 16) : 0);
+            const int first = units ? 0 : __shfl_sync(0xffffffffu, iv, ns == 16 ? (lane & 16) : 0);
             live = (i < my_tiles) && (tiled || m < M) && first >= 0 && !em;
             if (live) {
                 long long start;
@@ -727,6 +746,93 @@ int tc_build_live_tiles(const int *group_zero, const int *live_cnt, int G, int g
     return check_launch("build_live_tiles");
 }
 
+// ---- live-UNIT list (TcArgs::live_units) ------------------------------------------------------------------------------
+// One CTA per person g.  A ball row holds the first hits in index order, then - in a wrapped cloud of p distinct points
+// - the COPIES of those hits (indices >= p), then the first hit again as padding (ball_query_gpu.cu:49-60): only the
+// leading entries that are < p and differ from entry 0 are distinct samples, the others repeat one of them and cannot
+// change a max.  So centroid k needs u_k = 1 + [slot 8 distinct] + [slot 16 distinct] + [slot 24 distinct] octets of
+// its 32 slots (distinct entries are a prefix of the row).  The person's octets are packed 16 to a tile (padded with
+// copies of its first octet), the tiles appended to the list with one atomicAdd per person: the order of the persons in
+// the list is whatever the atomics give - it shapes the schedule, never a result (per-person maxima are atomicMax'ed).
+constexpr int kUnitThreads = 128, kUnitCache = 1024;
+// octets of centroid row r (32 slots) in a cloud of p distinct points; e0 = slot 0 (-1: empty ball -> one octet of zeros)
+__device__ __forceinline__ int row_octets(const int *__restrict__ r, int p, int &e0) {
+    e0 = __ldg(r);
+    const int e8 = __ldg(r + 8), e16 = __ldg(r + 16), e24 = __ldg(r + 24);
+    if (e0 < 0 || e8 >= p || e8 == e0) return 1;
+    if (e16 >= p || e16 == e0) return 2;
+    return (e24 >= p || e24 == e0) ? 3 : 4;
+}
+__global__ void __launch_bounds__(kUnitThreads)
+build_live_units_kernel(const int *__restrict__ group_zero, const int *__restrict__ live_cnt, const int *__restrict__ point_cnt,
+                        const int *__restrict__ idx, int gs, int n_u, int *__restrict__ units, int *__restrict__ n_tiles) {
+    __shared__ int s_warp[kUnitThreads / 32];
+    __shared__ int s_base, s_total;
+    __shared__ unsigned char s_u[kUnitCache];
+    const int g = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (__ldg(group_zero + g) != 0) return;
+    int lc = __ldg(live_cnt + g);
+    lc = lc < 1 ? 1 : (lc > gs ? gs : lc);
+    int p = __ldg(point_cnt + g);
+    p = p < 1 ? 1 : (p > n_u ? n_u : p);
+    const int *rows = idx + (size_t)g * gs * kTcNS;
+    // sweep 1: octets per centroid (kept in shared memory: bits 0-2 the count, bit 7 the empty-ball flag) and the
+    // person's total -> its place in the list (one atomic per person)
+    int mine = 0, e0;
+    for (int k = tid; k < lc; k += kUnitThreads) {
+        const int u = row_octets(rows + (size_t)k * kTcNS, p, e0);
+        if (k < kUnitCache) s_u[k] = (unsigned char)(u | (e0 < 0 ? 0x80 : 0));
+        mine += u;
+    }
+    mine = __reduce_add_sync(0xffffffffu, mine);
+    if (tid == 0) s_total = 0;
+    __syncthreads();
+    if (lane == 0) atomicAdd(&s_total, mine);
+    __syncthreads();
+    const int total = s_total;
+    if (tid == 0) s_base = atomicAdd(n_tiles, (total + 15) >> 4) * 16;
+    __syncthreads();
+    const int base = s_base;
+    // sweep 2: the counts scanned, the entries written
+    int running = 0;
+    for (int k0 = 0; k0 < lc; k0 += kUnitThreads) {
+        const int k = k0 + tid;
+        int u = 0;
+        bool dead = false;
+        if (k < lc) {
+            if (k < kUnitCache) { u = s_u[k] & 7; dead = (s_u[k] & 0x80) != 0; }
+            else { u = row_octets(rows + (size_t)k * kTcNS, p, e0); dead = e0 < 0; }
+        }
+        int incl = u;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        __syncthreads();                                   // s_warp of the previous pass has been read
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        int pos = running + incl - u;
+        for (int w = 0; w < warp; w++) pos += s_warp[w];
+        for (int w = 0; w < kUnitThreads / 32; w++) running += s_warp[w];
+        const int ent = (int)(((unsigned)(g * gs + k) << 2) | (dead ? 0x80000000u : 0u));
+        for (int o = 0; o < u; o++) units[base + pos + o] = ent | o;
+    }
+    // padding of the last tile: copies of the person's first octet
+    const int f0 = __ldg(rows);
+    const int ent0 = (int)(((unsigned)(g * gs) << 2) | (f0 < 0 ? 0x80000000u : 0u));
+    for (int q = total + tid; q < ((total + 15) & ~15); q += kUnitThreads) units[base + q] = ent0;
+}
+
+int tc_build_live_units(const int *group_zero, const int *live_cnt, const int *point_cnt, const int *idx, int G, int group_size,
+                        int n_u, int *units, int *n_tiles, cudaStream_t st) {
+    if (G <= 0) return MGAR_OK;
+    MGAR_CUDA(cudaMemsetAsync(n_tiles, 0, sizeof(int), st));
+    build_live_units_kernel<<<G, kUnitThreads, 0, st>>>(group_zero, live_cnt, point_cnt, idx, group_size, n_u, units, n_tiles);
+    count_launch();
+    return check_launch("build_live_units");
+}
+
 int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st) {
     TcBound BD;
     BD.shmax = 0.f;
@@ -750,6 +856,13 @@ int sa_mlp_tc16_launch(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cu
 #else
 #define TC16_TRACE_DUMP
 #endif
+    if (A.live_units && C0 == 4) {       // live-unit walk: only the distinct samples of the distinct centroids of the live persons
+        MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<4, false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+        sa_mlp_tc16_kernel<4, false, 3><<<grid, kThreads, kSmem, st>>>(L1, BD, A);
+        count_launch();
+        TC16_TRACE_DUMP
+        return check_launch("sa_mlp_tc16 (live units)");
+    }
     if (A.live_tiles && C0 == 4) {       // live-tile walk: only the distinct centroids of the persons that pooled points
         MGAR_CUDA(cudaFuncSetAttribute(sa_mlp_tc16_kernel<4, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
         sa_mlp_tc16_kernel<4, false, 2><<<grid, kThreads, kSmem, st>>>(L1, BD, A);

@@ -924,7 +924,7 @@ int forward_t(int B, int M, const float *xyz, const float *new_xyz, const float 
             L1.sh[o] = h_ss[kC1 + o];
         }
         TcArgs A;
-        A.live_groups = nullptr; A.n_live = nullptr; A.live_tiles = nullptr; A.m_shift = -1; A.ns = kTcNS;
+        A.live_groups = nullptr; A.n_live = nullptr; A.live_tiles = nullptr; A.live_units = nullptr; A.m_shift = -1; A.ns = kTcNS;
         A.B = B; A.M = M; A.C_in = C0 - 3;
         A.xyz = xyz; A.xyz_stride = 3; A.new_xyz = new_xyz;
         A.features = features; A.feat_stride = C0 - 3;

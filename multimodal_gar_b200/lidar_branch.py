@@ -60,6 +60,9 @@ class PointPersonEncoder(nn.Module):
         # True: ... and of those persons only the distinct centroids (a person that pooled c < P points has c distinct
         # samples; farthest point sampling returns index 0 for the rest, whose features repeat centroid 0's)
         self.skip_repeated_centroids = os.environ.get('MGAR_TC_NO_LIVE_TILES', '0') == '0'
+        # True: ... and of those centroids only the distinct samples of each ball (a ball row repeats its hits once it
+        # runs out of distinct ones: the copies of the wrapped cloud, then the first hit as padding - same maxima)
+        self.skip_repeated_samples = os.environ.get('MGAR_TC_NO_LIVE_UNITS', '0') == '0'
         self.num_sampled_points, self.npoint = num_sampled_points, npoint
         self.pool_extra_width = tuple(pool_extra_width)
         self.fused_canonical = fused_canonical
@@ -162,7 +165,9 @@ class PointPersonEncoder(nn.Module):
                                                   params_host=packed[2], impl='tc', group_max=person, group_size=P,
                                                   group_zero=empty.view(-1), want_out=want_out,
                                                   skip_zero_groups=self.skip_empty_persons,
-                                                  group_live_cnt=live_cnt if walk else None)
+                                                  group_live_cnt=live_cnt if walk else None,
+                                                  group_point_cnt=(pooled_cnt.view(-1) if (walk and self.skip_repeated_samples and
+                                                                                          pooled_cnt is not None) else None))
             mark('sa_mlp')
             person = person.view(B, M, -1)
         else:

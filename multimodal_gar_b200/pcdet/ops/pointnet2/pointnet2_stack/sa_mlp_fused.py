@@ -56,7 +56,7 @@ def tc_group_max_supported(channels, nsample, C_in, pool_avg=False):
 def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_xyz_batch_cnt, features, idx,
                    empty_mask=None, out=None, pool_avg=False, uniform=None, params_host=None, impl=None,
                    group_max=None, group_size=0, group_zero=None, want_out=True, skip_zero_groups=False,
-                   group_live_cnt=None):
+                   group_live_cnt=None, group_point_cnt=None):
     """-> (M, channels[-1]) fp32.  `idx` as returned by ball_query (or the raw kernel output);
     `uniform=(n, m)` skips the ragged bookkeeping when every cloud has n points and m centroids.
 
@@ -67,10 +67,12 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
     consecutive centroids (rows with group_zero[g] != 0 stay zero); want_out=False skips the (M, C_out) result;
     skip_zero_groups (with want_out=False) lets the kernel walk only the groups whose flag is 0 - same result, flagged
     groups (empty or zero-padded person slots) cost nothing; group_live_cnt (per group, int32, from
-    fastpath.fps_ball_query) additionally restricts the walk to each group's distinct centroids (same maxima)."""
+    fastpath.fps_ball_query) additionally restricts the walk to each group's distinct centroids (same maxima);
+    group_point_cnt (per group, int32: the cloud holds that many distinct points, slot k = point k mod count, as
+    roipoint pooling wraps them) further restricts it to the distinct samples of every ball (same maxima to 1e-6)."""
     need_cuda(new_xyz=new_xyz, idx=idx, params=params, empty_mask=empty_mask, group_max=group_max, group_zero=group_zero,
-              group_live_cnt=group_live_cnt)
-    need_dtype(torch.int32, group_live_cnt=group_live_cnt, group_zero=group_zero)
+              group_live_cnt=group_live_cnt, group_point_cnt=group_point_cnt)
+    need_dtype(torch.int32, group_live_cnt=group_live_cnt, group_zero=group_zero, group_point_cnt=group_point_cnt)
     need_dtype(torch.float32, xyz=xyz, new_xyz=new_xyz, features=features, params=params)
     need_dtype(torch.int32, idx=idx)
     if not xyz.is_cuda or xyz.dim() != 2 or xyz.stride(1) != 1:
@@ -107,6 +109,7 @@ def sa_mlp_forward(channels, params, nsample, xyz, xyz_batch_cnt, new_xyz, new_x
                 len(channels) - 1, ctypes.addressof(ch), ptr(params), ptr(params_host), ptr(out),
                 (-1 if skip_zero_groups else 0) if out is None else out.stride(0), ptr(group_max), int(group_size),
                 ptr(group_zero), ptr(group_live_cnt) if skip else 0,
+                ptr(group_point_cnt) if (skip and group_live_cnt is not None and group_point_cnt is not None) else 0,
                 1 if pool_avg else 0, ptr(ws), ws_bytes, stream_of(xyz)), "sa_mlp_fwd_tc")
         else:
             if not xyz.is_contiguous() or (features is not None and not features.is_contiguous()) or group_max is not None:

@@ -226,11 +226,14 @@ def test_config3_lidar_branch_plus_dafm_forward_is_frame_sharded(cuda):
 
 def test_person_features_do_not_depend_on_storing_sa_features(cuda):
     """The (B*M*P, C) per-centroid SA features are an intermediate: with them kept on chip (default) the person
-    features are the bits of max-over-centroids of the stored tensor."""
+    features are the bits of max-over-centroids of the stored tensor with the distinct-centroid walk, and within 2e-6
+    of them with the distinct-sample walk (the default; tests/test_live_units_gpu.py)."""
     _, _, xyz, feat, bx = _inputs(5, 3, 65536, 40, cuda)
     enc = _enc(cuda)
     with torch.no_grad():
         enc.keep_sa_features = False
+        u = enc(xyz, feat, bx)
+        enc.skip_repeated_samples = False
         a = enc(xyz, feat, bx)
         enc.keep_sa_features = True
         b = enc(xyz, feat, bx)
@@ -239,6 +242,8 @@ def test_person_features_do_not_depend_on_storing_sa_features(cuda):
     want = st["sa_features"].view(3 * 40, 512, -1).max(dim=1).values
     want = want * (st["empty"].view(-1, 1) == 0)
     assert torch.equal(a.view(3 * 40, -1), want)
+    scale = max(1.0, float(want.abs().max()))
+    assert torch.allclose(u.view(3 * 40, -1), want, rtol=2e-6, atol=2e-6 * scale)
 
 
 def test_folded_batchnorm_cache_follows_the_parameters(cuda):

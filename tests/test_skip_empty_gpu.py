@@ -14,6 +14,7 @@ pytestmark = pytest.mark.gpu
 def _enc(dev):
     torch.manual_seed(7)
     enc = lidar_branch.PointPersonEncoder(1).to(dev).eval()
+    enc.skip_repeated_samples = False        # whole centroids per TMEM lane quarter: the walks below keep the bits
     with torch.no_grad():
         for mod in enc.sa.mlps[0]:
             if isinstance(mod, torch.nn.BatchNorm2d):
