@@ -189,7 +189,13 @@ MGAR_API int mgar_fps_ball_query_supported(int b, int n, int m, int nsample);
  * cloud_weight (b) int32, optional: an estimate of each cloud's sampling rounds (its number of distinct points, e.g.
  * pooled_cnt of mgar_roipoint_pool_from_masks).  The clouds are then scheduled heaviest first (a one-CTA counting sort
  * into `workspace`, mgar_fps_ball_query_workspace_bytes(b) bytes of device scratch) so that the long clouds do not
- * form a tail; results do not depend on it.  NULL: clouds run in index order, no workspace needed. */
+ * form a tail; results do not depend on it.  NULL: clouds run in index order, no workspace needed.
+ * With n = 512 and b >= 1184 weighted clouds the call issues TWO kernels side by side: four warps per cloud for the
+ * clouds with >= 336 distinct points (the critical path: the shortest round), and for the others a kernel that treats
+ * cloud_weight[c] as the cloud's PERIOD (slot k = point k mod weight, what roipoint pooling's wrap produces) and spends a
+ * round only on the distinct 32-slot blocks; the period is verified on the device and ignored when it does not hold, so
+ * results never depend on it.  The second kernel runs on a stream owned by the library (one per device, created on
+ * first use), forked from and joined to `stream` by events - legal under stream capture. */
 MGAR_API size_t mgar_fps_ball_query_workspace_bytes(int b);
 MGAR_API int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xyz_stride, float radius, int nsample,
                                  int *fps_idx, float *new_xyz, int *ball_idx, int *live_cnt, int write_dup_rows,

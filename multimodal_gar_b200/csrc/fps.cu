@@ -21,6 +21,8 @@
 #include <stdlib.h>
 
 #include "fps_bq_cta.cuh"
+#include <mutex>
+
 #include "fps_bq_dup.cuh"
 #include "mgar_common.cuh"
 
@@ -599,7 +601,31 @@ extern "C" int mgar_fps_ball_query_supported(int b, int n, int m, int nsample) {
     return n == 32 || n == 64 || n == 128 || n == 256 || n == 512;
 }
 
-extern "C" size_t mgar_fps_ball_query_workspace_bytes(int b) { return b > 0 ? (size_t)b * sizeof(int) : 0; }
+extern "C" size_t mgar_fps_ball_query_workspace_bytes(int b) { return b > 0 ? ((size_t)b + 4) * sizeof(int) : 0; }   // order + n_heavy
+
+// The library's side stream of the current device (the split launch below runs two kernels side by side): created on first
+// use, one per device, never destroyed.  Not memory: the "no hidden allocation" rule of the boundary is about buffers.
+namespace {
+struct SideStream { cudaStream_t stream; cudaEvent_t fork, join; bool ok; };
+SideStream *side_stream() {
+    static SideStream table[64];
+    static std::mutex mu;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("fps_ball_query: no current device"); return nullptr; }
+    std::lock_guard<std::mutex> lock(mu);
+    SideStream &s = table[dev];
+    if (!s.ok) {
+        if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess) {
+            set_error("fps_ball_query: could not create the side stream: %s", cudaGetErrorString(cudaGetLastError()));
+            return nullptr;
+        }
+        s.ok = true;
+    }
+    return &s;
+}
+}  // namespace
 
 template <int W, int PPL>
 static int launch_bq_cta(int b, int m, const float *xyz, int xs, float radius, int K, int *fps_idx, float *new_xyz,
@@ -631,28 +657,37 @@ extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xy
     cudaStream_t st = (cudaStream_t)stream;
     if (bq_use_cta(n)) {
         const int *order = nullptr;
+        bool order_pending = false;                  // the sort is launched by whichever path below runs
         if (cloud_weight && b > kNumSMs) {          // longest clouds first (with <= one CTA per SM the order is moot)
             if (!workspace || workspace_bytes < mgar_fps_ball_query_workspace_bytes(b)) {
                 set_error("fps_ball_query: cloud_weight needs a workspace of mgar_fps_ball_query_workspace_bytes(b) = %zu bytes",
                           mgar_fps_ball_query_workspace_bytes(b));
                 return MGAR_ENOMEM;
             }
-            order_clouds_kernel<<<1, 1024, 0, st>>>(cloud_weight, b, static_cast<int *>(workspace));
-            count_launch();
-            if (int rc = check_launch("fps_ball_query(order)")) return rc;
             order = static_cast<const int *>(workspace);
+            order_pending = true;
         }
         // pooled clouds are periodic (slot k = point k mod count): with the count as a (verified) hint only the distinct
-        // blocks take part in a round (fps_bq_dup.cuh).  Bit-identical, 35 % fewer point-rounds - and SLOWER on the bench
-        // step (0.338 ms at its best residency against 0.309 ms, profiles/r02_fps_bq_sweep.txt): the step lasts as long
-        // as the 512-round clouds, whose round is latency-bound and got a few instructions longer.  Opt-in
-        // (MGAR_FPS_BQ_DUP=1), kept with its tests as the record of the experiment.
-        if (n == kDupN && cloud_weight && getenv("MGAR_FPS_BQ_DUP") && !getenv("MGAR_FPS_BQ_GEOM")) {
+        // blocks take part in a round (fps_bq_dup.cuh).  Bit-identical, 35 % fewer point-rounds - and on its own SLOWER on the
+        // bench step (0.338 ms at its best residency against 0.309 ms, profiles/r02_fps_bq_sweep.txt): the step lasts as long
+        // as the 512-round clouds, whose round is latency-bound and got a few instructions longer.  MGAR_FPS_BQ_DUP=1 runs
+        // it alone (the record of that experiment).
+        auto sort_clouds = [&](int *n_heavy, int heavy_from) -> int {
+            order_clouds_kernel<<<1, 1024, 0, st>>>(cloud_weight, b, static_cast<int *>(workspace), n_heavy, heavy_from);
+            count_launch();
+            return check_launch("fps_ball_query(order)");
+        };
+        const bool dup_ok = n == kDupN && cloud_weight && order && !getenv("MGAR_FPS_BQ_GEOM");
+        auto dup_smem = [&](int ctas_per_sm) {
             size_t sm = (size_t)kDupN * sizeof(float4) + (size_t)m * sizeof(int) + (size_t)kDupW * 2 * nsample * sizeof(int);
-            int ctas_per_sm = 10;
             if (const char *e = getenv("MGAR_FPS_BQ_CTAS")) { const int v = atoi(e); if (v >= 1 && v <= 32) ctas_per_sm = v; }
             const size_t cap = ((size_t)227 * 1024) / ctas_per_sm - 1024;
             if (b > kNumSMs * ctas_per_sm && cap > sm) sm = cap & ~(size_t)127;
+            return sm;
+        };
+        if (dup_ok && getenv("MGAR_FPS_BQ_DUP")) {
+            if (int rc = sort_clouds(nullptr, 0)) return rc;
+            const size_t sm = dup_smem(10);
             if (sm > 48 * 1024)
                 MGAR_CUDA(cudaFuncSetAttribute(fps_bq_dup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
             fps_bq_dup_kernel<<<b, kDupW * 32, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, order,
@@ -660,9 +695,53 @@ extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xy
             count_launch();
             return check_launch("fps_ball_query(dup)");
         }
+        // SPLIT (the default for many wrapped 512-slot clouds): the two kernels side by side, each on the clouds it is good
+        // at.  The clouds with >= split_from distinct points (the first n_heavy entries of `order`) go to the four-warp
+        // kernel, whose round is the shortest (511 against 771 cycles with the SM to itself,
+        // profiles/r02_fps_round_latency.json) - they are the step's critical path; all the others go to the periodic-cloud
+        // kernel, which spends instructions only on their distinct blocks - they are the step's instruction count.  The
+        // second launch runs on a side stream of the library (fork / join by events, legal under stream capture too).
+        int split_from = 336;                    // sweep: profiles/r02_fps_split_sweep.txt
+        if (const char *e = getenv("MGAR_FPS_BQ_SPLIT")) split_from = atoi(e);
+        if (dup_ok && split_from > 0 && b >= 8 * kNumSMs) {
+            SideStream *side = side_stream();
+            if (!side) return MGAR_ECUDA;
+            int *n_heavy = static_cast<int *>(workspace) + b;
+            if (int rc = sort_clouds(n_heavy, split_from)) return rc;
+            MGAR_CUDA(cudaEventRecord(side->fork, st));
+            MGAR_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
+            {   // long clouds: four warps each, on the caller's stream
+                const size_t sm = (size_t)kDupN * sizeof(float4) + (size_t)m * sizeof(int) + (size_t)4 * 2 * nsample * sizeof(int);
+                if (sm > 48 * 1024)
+                    MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+                // both kernels ask for the same shared-memory carve-out: CTAs of kernels with different L1 / shared splits
+                // do not share an SM, and the two launches would run one after the other
+                MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<4, 4>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                               (int)cudaSharedmemCarveoutMaxShared));
+                fps_bq_cta_kernel<4, 4><<<b, 128, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, order,
+                                                            live_cnt, write_dup_rows, n_heavy);
+                count_launch();
+                if (int rc = check_launch("fps_ball_query(long clouds)")) return rc;
+            }
+            {   // every other cloud: the periodic-cloud kernel, on the side stream
+                const size_t sm = dup_smem(10);
+                if (sm > 48 * 1024)
+                    MGAR_CUDA(cudaFuncSetAttribute(fps_bq_dup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+                MGAR_CUDA(cudaFuncSetAttribute(fps_bq_dup_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                               (int)cudaSharedmemCarveoutMaxShared));
+                fps_bq_dup_kernel<<<b, kDupW * 32, sm, side->stream>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b,
+                                                                       m, order, cloud_weight, live_cnt, write_dup_rows, n_heavy);
+                count_launch();
+                if (int rc = check_launch("fps_ball_query(wrapped clouds)")) return rc;
+            }
+            MGAR_CUDA(cudaEventRecord(side->join, side->stream));
+            MGAR_CUDA(cudaStreamWaitEvent(st, side->join, 0));
+            return MGAR_OK;
+        }
         // Two warps per cloud cost the fewest instructions (throughput: many clouds per SM); four warps have the shorter
         // round (latency: 511 against 771 cycles per round when a cloud has the SM to itself,
         // profiles/r02_fps_round_latency.json) - used while there are fewer than 8 clouds per SM (a single frame: 40).
+        if (order_pending) if (int rc = sort_clouds(nullptr, 0)) return rc;
         int W = b < 8 * kNumSMs ? 4 : 2, PPL = n / (32 * W);
         if (const char *e = getenv("MGAR_FPS_BQ_GEOM")) {
             int w = 0, p = 0;

@@ -109,7 +109,7 @@ template <int W, int PPL>
 __global__ void __launch_bounds__(W * 32)
 fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs, float *__restrict__ new_xyz,
                   int *__restrict__ ball_idx, float radius, int K, int b, int m, const int *__restrict__ order,
-                  int *__restrict__ live_cnt, int dup_rows) {
+                  int *__restrict__ live_cnt, int dup_rows, const int *__restrict__ n_split = nullptr) {
     constexpr int NBLK = W * PPL, NB = CtLog2<NBLK>::v, n = 32 * NBLK, L = 5 + NB;
     static_assert(NBLK <= 16 && (NBLK & (NBLK - 1)) == 0, "a cloud is at most 16 blocks of 32 points");
     extern __shared__ float4 bq_sm4[];
@@ -122,6 +122,9 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     int *rows = sidx + m;                                  // [W][2][K] rows being assembled
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    // n_split: this launch takes only the first *n_split entries of `order` (the long clouds; the others belong to the
+    // periodic-cloud kernel running beside it, fps_bq_dup.cuh)
+    if (n_split && (int)blockIdx.x >= __ldg(n_split)) return;
     const int cloud = order ? __ldg(order + blockIdx.x) : (int)blockIdx.x;
     if (cloud < 0 || cloud >= b) return;
     xyz += (size_t)cloud * n * xs; idxs += (size_t)cloud * m;
@@ -280,8 +283,10 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
 
 // order[0 .. b) = the clouds sorted by weight, heaviest first (counting sort over weights clamped to [0, 1023]; the
 // order inside a weight class is whatever the atomics give - it only shapes the schedule, never a result).  One CTA.
+// n_heavy (optional) = number of clouds with weight >= heavy_from: they are the first n_heavy entries of order.
 __global__ void __launch_bounds__(1024)
-order_clouds_kernel(const int *__restrict__ weight, int b, int *__restrict__ order) {
+order_clouds_kernel(const int *__restrict__ weight, int b, int *__restrict__ order, int *__restrict__ n_heavy = nullptr,
+                    int heavy_from = 0) {
     __shared__ int s_hist[1024];
     __shared__ int s_warp[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -305,6 +310,8 @@ order_clouds_kernel(const int *__restrict__ weight, int b, int *__restrict__ ord
     for (int q = 0; q < warp; q++) before += s_warp[q];
     __syncthreads();
     s_hist[tid] = before + incl - h;                     // exclusive start of the bucket
+    // bucket t holds weight 1023 - t: the heavy clouds are the buckets 0 .. 1023 - heavy_from
+    if (n_heavy && tid == min(max(1023 - heavy_from, 0), 1023)) *n_heavy = heavy_from > 1023 ? 0 : before + incl;
     __syncthreads();
     for (int c = tid; c < b; c += 1024) {
         const int wv = min(max(__ldg(weight + c), 0), 1023);

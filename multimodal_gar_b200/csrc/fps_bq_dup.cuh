@@ -203,7 +203,8 @@ __device__ __forceinline__ void bq_dup_body(const DupCtx &C) {
 __global__ void __launch_bounds__(kDupW * 32)
 fps_bq_dup_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs, float *__restrict__ new_xyz,
                   int *__restrict__ ball_idx, float radius, int K, int b, int m, const int *__restrict__ order,
-                  const int *__restrict__ period, int *__restrict__ live_cnt, int dup_rows) {
+                  const int *__restrict__ period, int *__restrict__ live_cnt, int dup_rows,
+                  const int *__restrict__ n_split = nullptr) {
     extern __shared__ float4 bq_sm4[];
     __shared__ __align__(16) unsigned s_key[2][2][2];
     __shared__ __align__(16) unsigned s_ring[2 * kBqRing][16];
@@ -212,7 +213,10 @@ fps_bq_dup_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     float4 *sp = bq_sm4;
     int *sidx = reinterpret_cast<int *>(sp + kDupN);
     const int tid = threadIdx.x;
-    const int cloud = order ? __ldg(order + blockIdx.x) : (int)blockIdx.x;
+    // n_split: the first *n_split entries of `order` (the long clouds) belong to fps_bq_cta_kernel<4, 4> running beside this launch
+    const int slot = (int)blockIdx.x + (n_split ? __ldg(n_split) : 0);
+    if (slot >= b) return;
+    const int cloud = order ? __ldg(order + slot) : slot;
     if (cloud < 0 || cloud >= b) return;
     xyz += (size_t)cloud * kDupN * xs;
     if (xs == 4 && (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) {

@@ -22,8 +22,8 @@
 // Layer 1 itself stays 3xTF32 (K = 8, three small MMAs).
 //
 // Warp roles, barriers and the software pipeline are those of sa_mlp_tc.cu:
-//   warps 0-3 epilogue | 4, 14 layer-2 issue (even / odd tiles) | 13 layer-1 issue |
-//   warps 5-8 / 9-12 gather + convert of the even / odd tiles (a tile's whole serial chain belongs to one group)
+//   warps 0-3 epilogue | 4-7 / 8-11 gather + convert of the even / odd tiles (a tile's whole serial chain belongs to one
+//   group of four warps) | 12, 13 layer-2 issue (even / odd tiles) | 14 layer-1 issue
 #include <cuda_fp16.h>
 #include <stdlib.h>
 
@@ -35,15 +35,45 @@ namespace mgar {
 
 namespace {
 
-constexpr int kThreads = 15 * 32;
+// converter groups (four warps each; group g owns the tiles i = g mod kGroups) and layer-2 issuing warps
+#ifndef MGAR_TC16_GROUPS
+#define MGAR_TC16_GROUPS 2
+#endif
+#ifndef MGAR_TC16_ISSUERS
+#define MGAR_TC16_ISSUERS 2
+#endif
+// Measured on the bench step (MLP stage, ms per 64 frames): groups x issuers 2x2 0.408 | 2x1 0.455 | 3x1 0.465 | 3x2 0.409 (112
+// registers, a few spilled words): a third converter group buys nothing - the stage is not paced by the converters' own
+// instruction count - while a second issuing warp is worth 10 %.
+constexpr int kGroups = MGAR_TC16_GROUPS, kIssuers = MGAR_TC16_ISSUERS;
+// an issuer must always meet the same accumulator stage: with kIssuers not dividing kAcc two issuers would wait on one
+// mbarrier for different phases, and a parity wait cannot tell phases two apart (this hangs)
+static_assert(kIssuers == 1 || kIssuers == 2, "layer-2 issuers: 1 or 2 (kAcc = 2 accumulator stages)");
+constexpr int kWarpL2 = 4 + 4 * kGroups, kWarpL1 = kWarpL2 + kIssuers;      // warps 0-3 epilogue, 4 .. kWarpL2-1 converters
+constexpr int kThreads = (kWarpL1 + 1) * 32;
 constexpr int kStages = 4;                      // shared-memory stages of the h1 operand (hi + lo = 32 KB each)
 constexpr int kAcc = 2;                         // TMEM stages of the layer-2 accumulator (128 columns each)
-// TMEM columns: layer-2 accumulators 0,128; layer-1 accumulators 256,320 (64 each); W2 fp16 hi 384, lo 416 (32 each)
-constexpr uint32_t kTmD1 = 256, kTmW2Hi = 384, kTmW2Lo = 416;
+// TMEM columns: layer-2 accumulators 0,128; W2 fp16 hi 256, lo 288 (32 each); layer-1 accumulators 320 + 64 g (64 each)
+constexpr uint32_t kTmW2Hi = 256, kTmW2Lo = 288, kTmD1 = 320;
+// MGAR_TC16_XTMEM=1: the layer-1 input tile travels registers -> TENSOR MEMORY (tcgen05.st, the A operand of the
+// layer-1 MMA is read from TMEM) instead of registers -> shared memory -> async-proxy fence: 16 columns per stage behind D1
+// Measured: no gain (MLP stage 0.410 against 0.407 ms) - the default stays shared memory.
+#ifndef MGAR_TC16_XTMEM
+#define MGAR_TC16_XTMEM 0
+#endif
+constexpr bool kXTmem = MGAR_TC16_XTMEM != 0;
+// MGAR_TC16_DEFER_X=1: the x tile's async-proxy fence + XFULL arrive wait until the group has read the previous D1 (the
+// stores have long completed by then).  Measured: no gain either (0.4045 against 0.4025 ms).
+#ifndef MGAR_TC16_DEFER_X
+#define MGAR_TC16_DEFER_X 0
+#endif
+constexpr bool kDeferX = MGAR_TC16_DEFER_X != 0;
+constexpr uint32_t kTmX = kTmD1 + 64 * kGroups;
+static_assert(kTmX + (kXTmem ? 16 * kGroups : 0) <= 512, "TMEM holds 512 columns");
 constexpr uint32_t kXBytes = 128 * 8 * 4;       // one 128 x 8 fp32 layer-1 input tile (no swizzle): 4 KB
 constexpr uint32_t kW1Bytes = 64 * 8 * 4;       // W1^T operand, 64 x 8: 2 KB
 constexpr uint32_t kHBytes = 128 * 64 * 2;      // one 128 x 64 fp16 operand tile (one 128-byte swizzled row per position): 16 KB
-constexpr uint32_t kSmem = kStages * 2 * kHBytes + 2 * 2 * kXBytes + 2 * kW1Bytes + 1024;
+constexpr uint32_t kSmem = kStages * 2 * kHBytes + kGroups * 2 * kXBytes + 2 * kW1Bytes + 1024;   // (the x stages are unused with kXTmem)
 constexpr int kRing = 16;                       // per-centroid scale ring (gather runs at most ~9 tiles ahead of the epilogue)
 
 __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
@@ -51,6 +81,14 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, 
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
                  ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+__device__ __forceinline__ void tc_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+                 "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+                 : "memory");
 }
 
 // ReLU(a), ReLU(b) -> packed fp16 pairs hi, lo (a in the low half) with hi + lo = ReLU(.) to 22 bits.
@@ -111,6 +149,12 @@ __device__ __forceinline__ void tr_reduce32(const uint32_t (&v)[32], float &mx, 
     near = mx - fmaxf(r0, r1) <= 6.1035156e-5f * sqrtf(q * 0.03125f);
 }
 
+// MGAR_TC16_EXP=n: timing-only experiment builds (results WRONG by construction; never the shipped library):
+//   1 no h1 stores (converters keep the TMEM read and the split)   2 eight instead of twelve layer-2 MMAs
+//   3 no x-tile stores   4 one instead of two layer-1 MMAs
+#ifndef MGAR_TC16_EXP
+#define MGAR_TC16_EXP 0
+#endif
 #ifdef MGAR_TC16_TRACE
 __device__ long long g_tc16_trace[32 * 16];        // timeline of CTA 0, local tiles 100..131 (debug build only)
 #define TR(slot, i) do { if (blockIdx.x == 0 && lane == 0 && (i) >= 100 && (i) < 132) g_tc16_trace[((i) - 100) * 16 + (slot)] = clock64(); } while (0)
@@ -155,24 +199,24 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
     //                            tile B = [xh0..xh4, xl3, xl4, 0  ] . [wl0..wl4, wh3, wh4, 0  ]
     constexpr bool kPack2 = C0 + 1 <= 5;
     extern __shared__ uint8_t smem_raw[];
-    // full[4] empty[4] | tfull[2] tempty[2] | xfull[2] xempty[2] | dfull[2] dempty[2]
-    __shared__ __align__(8) uint64_t s_bar[2 * kStages + 12];
+    // full[4] empty[4] | tfull[2] tempty[2] | xfull[G] xempty[G] | dfull[G] dempty[G]
+    __shared__ __align__(8) uint64_t s_bar[2 * kStages + 4 + 4 * kGroups];
     __shared__ __align__(16) float s_inv[kRing][4];     // 2^e of the four centroids of tile (i mod kRing)
     __shared__ uint32_t s_tmem;
 
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024 B alignment
     const uint32_t b_stage0 = base;                                 // h1 stage s: hi at +s*2*kHBytes, lo at +kHBytes more
     const uint32_t x_stage0 = base + kStages * 2 * kHBytes;         // x stage: hi at +xs*2*kXBytes, lo at +kXBytes more
-    const uint32_t w1_hi = x_stage0 + 2 * 2 * kXBytes, w1_lo = w1_hi + kW1Bytes;
+    const uint32_t w1_hi = x_stage0 + kGroups * 2 * kXBytes, w1_lo = w1_hi + kW1Bytes;
     const uint32_t bar0 = smem_u32(s_bar);
     auto FULL = [&](int s) { return bar0 + 8u * s; };
     auto EMPTY = [&](int s) { return bar0 + 8u * (kStages + s); };
     auto TFULL = [&](int t) { return bar0 + 8u * (2 * kStages + t); };
     auto TEMPTY = [&](int t) { return bar0 + 8u * (2 * kStages + 2 + t); };
     auto XFULL = [&](int x) { return bar0 + 8u * (2 * kStages + 4 + x); };
-    auto XEMPTY = [&](int x) { return bar0 + 8u * (2 * kStages + 6 + x); };
-    auto DFULL = [&](int x) { return bar0 + 8u * (2 * kStages + 8 + x); };
-    auto DEMPTY = [&](int x) { return bar0 + 8u * (2 * kStages + 10 + x); };
+    auto XEMPTY = [&](int x) { return bar0 + 8u * (2 * kStages + 4 + kGroups + x); };
+    auto DFULL = [&](int x) { return bar0 + 8u * (2 * kStages + 4 + 2 * kGroups + x); };
+    auto DEMPTY = [&](int x) { return bar0 + 8u * (2 * kStages + 4 + 3 * kGroups + x); };
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // M counts "virtual" centroids when the live-person list is in use (TcArgs::live_groups): only they are walked
@@ -191,7 +235,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
     if (tid == 0) {
         for (int s = 0; s < kStages; s++) { mbar_init(FULL(s), 128); mbar_init(EMPTY(s), 1); }
         for (int t = 0; t < kAcc; t++) { mbar_init(TFULL(t), 1); mbar_init(TEMPTY(t), 128); }
-        for (int x = 0; x < 2; x++) {
+        for (int x = 0; x < kGroups; x++) {
             mbar_init(XFULL(x), 128); mbar_init(XEMPTY(x), 1);
             mbar_init(DFULL(x), 1); mbar_init(DEMPTY(x), 128);
         }
@@ -203,7 +247,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
     }
     // W1^T (64 channels x K=8: C0 folded weights, the folded BatchNorm shift in column C0, zeros) as the
     // B operand of the layer-1 MMA, tf32 hi/lo split, no-swizzle K-major
-    if (tid >= 160 && tid < 224) {
+    if (tid >= 160 && tid < 224) {                     // (two converter warps)
         const int ch = tid - 160;
         float k0[4], k1[4];
 #pragma unroll
@@ -385,14 +429,14 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         }
         if (A.gmax && my_tiles > 0) flush();
         }
-    } else if (warp == 4 || warp == 14) {
+    } else if (warp >= kWarpL2 && warp < kWarpL1) {
         // ===== layer-2 MMA issuers: warp 4 takes the even tiles, warp 14 the odd ones.  Per tile 12 x (128x128x16):
         // small terms first (W2lo*h1hi, W2hi*h1lo), then W2hi*h1hi.  K step kk: 8 TMEM columns of W2, 32 bytes
         // inside the 128B-swizzled row of h1.  The whole warp runs the warp-uniform control flow; only the
         // tcgen05 instructions are predicated on one elected lane.
         const uint32_t idesc2 = (1u << 4) /* D fp32 */ | (0u << 7) /* A fp16 */ | (0u << 10) /* B fp16 */ |
                                 ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-        for (int i = (warp == 4 ? 0 : 1); i < my_tiles; i += 2) {
+        for (int i = warp - kWarpL2; i < my_tiles; i += kIssuers) {
             const int s = i % kStages, j = i / kStages, t = i % kAcc, u = i / kAcc;
             mbar_wait(FULL(s), j & 1);
             TR(10, i);
@@ -404,24 +448,25 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             const uint32_t d = tmem + (uint32_t)(t * 128);
             if (elect_one()) {
 #pragma unroll
-                for (int term = 0; term < 3; term++) {
+                for (int term = (MGAR_TC16_EXP == 2 ? 1 : 0); term < 3; term++) {
                     const uint32_t a0 = tmem + (term == 0 ? kTmW2Lo : kTmW2Hi);
                     const uint64_t b0 = term == 1 ? bd_lo : bd_hi;
 #pragma unroll
                     for (int kk = 0; kk < 4; kk++)
-                        tc_mma_f16_ts(d, a0 + (uint32_t)(kk * 8), b0 + (uint64_t)((kk * 32) >> 4), idesc2, (term | kk) ? 1u : 0u);
+                        tc_mma_f16_ts(d, a0 + (uint32_t)(kk * 8), b0 + (uint64_t)((kk * 32) >> 4), idesc2,
+                                      ((term - (MGAR_TC16_EXP == 2 ? 1 : 0)) | kk) ? 1u : 0u);
                 }
                 tc_commit(EMPTY(s));     // smem stage reusable once these MMAs have read it
                 tc_commit(TFULL(t));     // accumulator ready for the epilogue
             }
             __syncwarp();
         }
-    } else if (warp == 13) {
+    } else if (warp == kWarpL1) {
         // ===== layer-1 MMA issuer (3xTF32, K = 8): D1[pos, ch] = x[pos, 0:8] . W1^T[ch, 0:8] ===================
         const uint32_t idesc1 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         const uint64_t w1d_hi = make_desc_k8(w1_hi), w1d_lo = make_desc_k8(w1_lo);
         for (int i = 0; i < my_tiles; i++) {
-            const int xs = i & 1, jx = i >> 1;
+            const int xs = i % kGroups, jx = i / kGroups;
             mbar_wait(XFULL(xs), jx & 1);
             TR(8, i);
             mbar_wait(DEMPTY(xs), (jx & 1) ^ 1);
@@ -431,9 +476,19 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             const uint64_t xd_hi = make_desc_k8(x_hi), xd_lo = make_desc_k8(x_hi + kXBytes);
             const uint32_t d1 = tmem + kTmD1 + (uint32_t)(xs * 64);
             if (elect_one()) {
-                if (kPack2) {                                   // 15 products in 2 x 8 K-slots (see sts_pack2_x)
+                if (kXTmem) {                                   // x tile in TMEM: columns 0-7 = "hi" tile, 8-15 = "lo" tile
+                    const uint32_t xa = tmem + kTmX + (uint32_t)(xs * 16);
+                    if (kPack2) {
+                        tc_mma_tf32_ts(d1, xa + 8, w1d_lo, idesc1, 0);
+                        tc_mma_tf32_ts(d1, xa, w1d_hi, idesc1, 1);
+                    } else {
+                        tc_mma_tf32_ts(d1, xa + 8, w1d_hi, idesc1, 0);
+                        tc_mma_tf32_ts(d1, xa, w1d_lo, idesc1, 1);
+                        tc_mma_tf32_ts(d1, xa, w1d_hi, idesc1, 1);
+                    }
+                } else if (kPack2) {                            // 15 products in 2 x 8 K-slots (see sts_pack2_x)
                     tc_mma_tf32(d1, xd_lo, w1d_lo, idesc1, 0);
-                    tc_mma_tf32(d1, xd_hi, w1d_hi, idesc1, 1);
+                    if (MGAR_TC16_EXP != 4) tc_mma_tf32(d1, xd_hi, w1d_hi, idesc1, 1);
                 } else {
                     tc_mma_tf32(d1, xd_lo, w1d_hi, idesc1, 0);
                     tc_mma_tf32(d1, xd_hi, w1d_lo, idesc1, 1);
@@ -454,7 +509,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         //       gather itself is software-pipelined two more own tiles ahead in registers;
         //   (b) read the position's 64 layer-1 outputs back from TMEM (D1 stage g), ReLU, split into fp16
         //       hi/lo and store the 128B-swizzled K-major h1 operand of the layer-2 MMA.
-        const int pw = warp & 3, g = (warp - 5) >> 2;
+        const int pw = warp & 3, g = (warp - 4) >> 2;
         const int r = pw * 32 + lane;
 
         int u_cloud = A.uniform ? (t_beg * 4 + pw) / A.m_u : 0, u_end = (u_cloud + 1) * A.m_u;
@@ -478,10 +533,10 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             int m = (t_beg + i) * 4 + pw;
             iv = -1; em = 0; mr = 0;
             if (units) {                                      // lane -> octet pw * 4 + lane / 8 of the tile, slot lane % 8 of it
-                // the entry was fetched by the previous call (the calls walk this group's tiles in order, i += 2): a tile's
+                // the entry was fetched by the previous call (the calls walk this group's tiles in order, i += kGroups): a tile's
                 // sixteen entries are a 64-byte line of their own, i.e. a trip to L2 that must not sit in front of the index load
                 const int e = ent_next;
-                if (i + 2 < my_tiles) ent_next = __ldg(A.live_units + (size_t)(t_beg + i + 2) * 16 + pw * 4 + (lane >> 3));
+                if (i + kGroups < my_tiles) ent_next = __ldg(A.live_units + (size_t)(t_beg + i + kGroups) * 16 + pw * 4 + (lane >> 3));
                 if (i < my_tiles) {
                     mr = (e & 0x7fffffff) >> 2;
                     em = e < 0;                               // bit 31: empty ball (the builder saw -1 in slot 0)
@@ -556,8 +611,13 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             }
         };
         // layer-1 input row of local tile i -> x stage i & 1, scaled by the centroid's 2^-e
-        auto store_x = [&](int i, const float (&v)[C0], const float (&q)[3], bool live) {
-            const int xs = i & 1, jx = i >> 1;               // xs == g for this group's tiles
+        // publish = false (kDeferX): the caller makes the tile visible later (publish_x), once the stores have long completed
+        auto publish_x = [&](int i) {
+            if (!kXTmem) fence_async_smem();
+            mbar_arrive(XFULL(i % kGroups));
+        };
+        auto store_x = [&](int i, const float (&v)[C0], const float (&q)[3], bool live, bool publish) {
+            const int xs = i % kGroups, jx = i / kGroups;    // xs == g for this group's tiles
             float x[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (live) {
                 x[0] = __fsub_rn(v[0], q[0]); x[1] = __fsub_rn(v[1], q[1]); x[2] = __fsub_rn(v[2], q[2]);
@@ -580,14 +640,35 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             if (pw == 0) TR(0, i);
             mbar_wait(XEMPTY(xs), (jx & 1) ^ 1);
             if (pw == 0) TR(1, i);
-            if (kPack2) sts_pack2_x(x_hi + k8_off(r, 0), x_hi + k8_off(r, 1), x_lo + k8_off(r, 0), x_lo + k8_off(r, 1), k0, k1[0]);
+            if (kXTmem) {
+                tc_fence_after();                                // the MMA that read this stage has completed (XEMPTY)
+                uint32_t xv[16];
+                if (kPack2) {                                    // the two packed tiles of sts_pack2_x, one row each
+                    float hi[5], lo[5];
+                    split5(k0, k1[0], hi, lo);
+                    const float ta[8] = {hi[0], hi[1], hi[2], hi[3], hi[4], lo[0], lo[1], lo[2]};
+                    const float tb[8] = {hi[0], hi[1], hi[2], hi[3], hi[4], lo[3], lo[4], 0.f};
+#pragma unroll
+                    for (int q = 0; q < 8; q++) { xv[q] = __float_as_uint(ta[q]); xv[8 + q] = __float_as_uint(tb[q]); }
+                } else {                                         // tf32 truncation / exact remainder, as sts_split4
+#pragma unroll
+                    for (int q = 0; q < 8; q++) {
+                        const float hq = __uint_as_float(__float_as_uint(x[q]) & 0xffffe000u);
+                        xv[q] = __float_as_uint(hq);
+                        xv[8 + q] = __float_as_uint(__fsub_rn(x[q], hq));
+                    }
+                }
+                tc_st16(tmem + ((uint32_t)(pw * 32) << 16) + kTmX + (uint32_t)(xs * 16), xv);
+                tc_wait_st();
+                tc_fence_before();
+            } else if (MGAR_TC16_EXP == 3) asm volatile("" ::"f"(k0[0] + k0[1] + k0[2] + k0[3] + k1[0]));
+            else if (kPack2) sts_pack2_x(x_hi + k8_off(r, 0), x_hi + k8_off(r, 1), x_lo + k8_off(r, 0), x_lo + k8_off(r, 1), k0, k1[0]);
             else {
                 sts_split4(x_hi + k8_off(r, 0), x_lo + k8_off(r, 0), k0);
                 sts_split4(x_hi + k8_off(r, 1), x_lo + k8_off(r, 1), k1);
             }
             if (lane == 0) s_inv[i % kRing][pw] = up;
-            fence_async_smem();
-            mbar_arrive(XFULL(xs));
+            if (publish) publish_x(i);
             if (pw == 0) TR(2, i);
         };
 
@@ -596,16 +677,16 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         bool live_b = false;
         load_idx(g, iv_b, em_b, mr_b);
         load_pt(g, iv_b, em_b, mr_b, vb, qb, live_b);
-        load_idx(g + 2, iv_b, em_b, mr_b);
-        load_idx(g + 4, iv_a, em_a, mr_a);
-        if (g < my_tiles) store_x(g, vb, qb, live_b);
-        load_pt(g + 2, iv_b, em_b, mr_b, vb, qb, live_b);
-        for (int i = g, k = 0; i < my_tiles; i += 2, k++) {
-            if (i + 2 < my_tiles) {
-                store_x(i + 2, vb, qb, live_b);                 // gathered during the previous iteration
+        load_idx(g + kGroups, iv_b, em_b, mr_b);
+        load_idx(g + 2 * kGroups, iv_a, em_a, mr_a);
+        if (g < my_tiles) store_x(g, vb, qb, live_b, true);
+        load_pt(g + kGroups, iv_b, em_b, mr_b, vb, qb, live_b);
+        for (int i = g, k = 0; i < my_tiles; i += kGroups, k++) {
+            if (i + kGroups < my_tiles) {
+                store_x(i + kGroups, vb, qb, live_b, !kDeferX); // gathered during the previous iteration
                 iv_b = iv_a; em_b = em_a; mr_b = mr_a;
-                load_pt(i + 4, iv_b, em_b, mr_b, vb, qb, live_b);   // points two own tiles ahead
-                load_idx(i + 6, iv_a, em_a, mr_a);                  // indices three own tiles ahead
+                load_pt(i + 2 * kGroups, iv_b, em_b, mr_b, vb, qb, live_b);   // points two own tiles ahead
+                load_idx(i + 3 * kGroups, iv_a, em_a, mr_a);                  // indices three own tiles ahead
             }
             const int s = i % kStages, j = i / kStages;
             if (pw == 0) TR(3, i);
@@ -619,6 +700,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             tc_wait_ld();
             tc_fence_before();
             mbar_arrive_relaxed(DEMPTY(g));                     // layer 1 of tile i+2 may overwrite D1 now
+            if (kDeferX && i + kGroups < my_tiles) publish_x(i + kGroups);   // ... and its input tile, stored at the top of this iteration
             if (pw == 0) TR(5, i);
 
             const uint32_t b_hi = b_stage0 + (uint32_t)s * 2 * kHBytes, b_lo = b_hi + kHBytes;
@@ -638,6 +720,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
 #pragma unroll
                 for (int c4 = 0; c4 < 4; c4++) {
                     const uint32_t off = h_off(r, half * 4 + c4);
+                    if (MGAR_TC16_EXP == 1) { asm volatile("" ::"r"(hi[4 * c4] ^ lo[4 * c4 + 1] ^ hi[4 * c4 + 2] ^ lo[4 * c4 + 3] ^ hi[4 * c4 + 1] ^ lo[4 * c4] ^ hi[4 * c4 + 3] ^ lo[4 * c4 + 2])); continue; }
                     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(b_hi + off), "r"(hi[4 * c4]), "r"(hi[4 * c4 + 1]),
                                  "r"(hi[4 * c4 + 2]), "r"(hi[4 * c4 + 3]) : "memory");
                     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(b_lo + off), "r"(lo[4 * c4]), "r"(lo[4 * c4 + 1]),

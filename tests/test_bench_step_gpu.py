@@ -1,5 +1,6 @@
 """-m gpu: THE step bench.py times - 64 configs[1] frames through PointPersonEncoder with its defaults - pinned end
-to end: (a) it really runs the six-kernel path (box-mask grid, pool-from-mask, cloud order, fused FPS + ball query, live-tile
+to end: (a) it really runs the eight-kernel path (frame grid, box masks, pool-from-mask, cloud order, fused FPS + ball query
+as two kernels side by side - four warps per long cloud, the periodic-cloud kernel for the wrapped ones - live-unit
 list, tcgen05 MLP walking the distinct samples of the distinct centroids), (b) its person features are those of the
 all-rows path (every ball row written, every centroid through the MLP: the same bits with the distinct-centroid walk, within
 2e-6 with the distinct-sample walk whose 32-position blocks share their power-of-two operand scale differently), (c) every index / pooled value of that batch equals the
@@ -38,7 +39,7 @@ def step(cuda):
 
 
 def test_default_step_is_the_six_kernel_path_and_matches_the_all_rows_path(step):
-    assert step["launches"] == 7, "expected frame grid, box masks, pool, cloud order, FPS+ball query, live tiles, MLP; got %d launches" % step["launches"]
+    assert step["launches"] == 8, "expected frame grid, box masks, pool, cloud order, FPS+ball query (long | wrapped clouds), live units, MLP; got %d launches" % step["launches"]
     assert step["person"].shape == (F, bench.CFG["M"], 128)
     sa = step["st"]["sa_features"].view(F * bench.CFG["M"], bench.CFG["P"], 128)
     want = sa.max(dim=1).values * (step["st"]["empty"].view(-1, 1) == 0)
