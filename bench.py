@@ -691,17 +691,30 @@ def run_native(args, rank, world, local_rank):
         # how much of the MLP's nominal work the distinct-centroid walk executes (reported, never hidden)
         st = enc(*devb[0], return_stages=True)
         live = st["live_cnt"]
-        walked = None
+        walked = walked_centroids = None
         if live is not None:
-            tiles = ((live.view(-1) + 3) // 4) * (st["empty"].view(-1) == 0)
-            walked = float(tiles.sum().item()) * 4 / float(live.numel() * CFG["P"])
+            ok = st["empty"].view(-1) == 0
+            tiles = ((live.view(-1) + 3) // 4) * ok
+            walked = walked_centroids = float(tiles.sum().item()) * 4 / float(live.numel() * CFG["P"])
+            if getattr(enc, "skip_repeated_samples", False) and CFG["K"] == 32 and st["ball_idx"] is not None:
+                # distinct-sample walk: octets of sample slots per distinct centroid, sixteen to a tile (the rule of
+                # build_live_units_kernel; the cloud's period = its number of distinct samples on this data)
+                G, P = live.numel(), CFG["P"]
+                rows = st["ball_idx"].view(G, P, 32)
+                per = live.view(G, 1).clamp(1, P)
+                e0 = rows[:, :, 0]
+                real = [(rows[:, :, s] < per) & (rows[:, :, s] != e0) & (e0 >= 0) for s in (8, 16, 24)]
+                u = 1 + real[0].int() + (real[0] & real[1]).int() + (real[0] & real[1] & real[2]).int()
+                u = u * (torch.arange(P, device=u.device).view(1, P) < per)
+                utiles = ((u.sum(dim=1) + 15) // 16) * ok
+                walked = float(utiles.sum().item()) * 4 / float(G * P)
         del st
     stage_ms = {}
     for evs in marks:
         for (_, a), (name, b) in zip(evs, evs[1:]):
             stage_ms[name] = stage_ms.get(name, 0.0) + a.elapsed_time(b) / len(marks)
     r = dict(keep_sa=enc.keep_sa_features, F=F, ms_total=ms_total, stage_ms=stage_ms, launches=launches, clocks=clocks,
-             work=work, host=host, walked=walked)
+             work=work, host=host, walked=walked, walked_centroids=walked_centroids)
 
     # ---- end to end through the public API with HOST buffers: `e2e` ---------------------------------
     r["e2e"] = block_e2e(ctx, enc, host, F, args.steps, args.warmup)
@@ -765,13 +778,17 @@ def main():
                         peak_burst=pk["bf16"], peak_sustained=pk["bf16_sustained"],
                         traffic=kprof.get("dram_bytes"), kernel=dom,
                         executed_fraction=walked, executed_TFLOPs=ach * walked, executed_frac_burst=ach * walked / pk["bf16"],
+                        executed_fraction_distinct_centroids=r.get("walked_centroids"),
                         tensor_pipe_active_pct=kprof.get("tensor_pipe_active_pct"),
                         note="achieved = ALGORITHMIC fp32 FLOPs (SURVEY 8d: 2*M*P*K*8448 per frame) over the kernel's "
                              "CUDA-event time, against the %s bf16 tensor peak (burst: the timed region is tens of ms). "
                              "Two things make it differ from tensor-pipe utilisation, both stated here: (1) the kernel "
                              "walks only the DISTINCT centroids of every person (a person that pooled c < 512 points has "
-                             "c distinct samples; the rest repeat centroid 0 and cannot change the person's max): "
-                             "executed_fraction of the nominal tiles run, executed_TFLOPs = achieved x that; (2) each "
+                             "c distinct samples; the rest repeat centroid 0 and cannot change the person's max) and of "
+                             "those only the DISTINCT samples of each ball, in octets (a ball row repeats its hits once it "
+                             "runs out of distinct ones): executed_fraction of the nominal 128-position tiles run "
+                             "(executed_fraction_distinct_centroids = with the first skip alone), executed_TFLOPs = "
+                             "achieved x that, so frac can exceed 1 - executed_frac_burst cannot exceed 1/3; (2) each "
                              "executed product costs 3 fp16 MMAs (3xFP16 split, fp32-faithful), so the pipe does 3x "
                              "executed_TFLOPs - tensor_pipe_active_pct is ncu's sm__pipe_tensor_cycles_active of the "
                              "committed capture (profiles/r02_traffic.json), traffic its dram bytes per launch" % pk["source"])

@@ -7,8 +7,10 @@ import json
 import subprocess
 import sys
 
-STAGE = {"box_mask": "points_in_boxes", "pool_from_mask": "roipoint_pool", "fps_bq": "fps_ball_query",
-         "order_clouds": "fps_ball_query(order)", "build_live_tiles": "sa_mlp(tile list)", "sa_mlp_tc16": "sa_mlp"}
+STAGE = {"frame_grid_build": "points_in_boxes(grid)", "box_mask": "points_in_boxes", "pool_from_mask": "roipoint_pool",
+         "fps_bq_dup": "fps_ball_query", "fps_bq_cta": "fps_ball_query(long clouds)", "fps_bq": "fps_ball_query",
+         "order_clouds": "fps_ball_query(order)", "build_live_tiles": "sa_mlp(tile list)",
+         "build_live_units": "sa_mlp(unit list)", "sa_mlp_tc16": "sa_mlp"}
 WANT = {"gpu__time_duration.sum": "ncu_us", "dram__bytes_read.sum": "dram_read", "dram__bytes_write.sum": "dram_write",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active": "tensor_pipe_active_pct",
         "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active": "alu_pipe_active_pct",
