@@ -608,7 +608,7 @@ def block_train(ctx, frames_per_rank, steps=6):
     net = TS.LidarFusionNet().to(dev).train()
     batch = TS.synthetic_batch(300 + ctx.rank, frames_per_rank, N=CFG["N"], M=80, MNP=100, device=dev)
     model = TS.make_ddp(net, dev) if ctx.world > 1 else net
-    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4, fused=True)      # train_func.py:552 (Adam); one kernel per step
     losses = []
     n0 = _lib.launch_count()
     ms = ctx.timed(lambda: losses.append(TS.train_step(model, opt, batch)), steps, warm=2)

@@ -42,20 +42,31 @@ def pairwise_euclidean_distance(x, zero_diagonal=True):
     return d
 
 
+class _DafmInputs(dict):
+    """The dict `dafm_lidar_inputs` returns; 'person_num' (list[int]) is read back from the device only when somebody
+    asks for it - the fused path needs the counts on the device only ('person_count'), and a host read in every step
+    stalls the launch queue (the training step lost a third of its time to it)."""
+
+    def __missing__(self, key):
+        if key != 'person_num':
+            raise KeyError(key)
+        self[key] = self['person_count'].tolist()
+        return self[key]
+
+
 def dafm_lidar_inputs(lidar_feature, bboxes3d, person_id):
     """Batched form of the per-frame slicing at gat_model.py:1396-1405 and :1467-1471.
 
-    -> dict(person_num list[int], valid (B,MNP) bool, feature (B,MNP,D) with padded rows zeroed,
-            De (B,MNP,MNP) with rows/columns of padded persons zeroed).
+    -> dict(person_count (B) int64 on the device, person_num list[int] (read back on first access), valid (B,MNP) bool,
+            feature (B,MNP,D) with padded rows zeroed, De (B,MNP,MNP) with rows/columns of padded persons zeroed).
     `out['feature'][b, :n]` and `out['De'][b, :n, :n]` are the reference's LiDAR_feature_b and De."""
     B, MNP = person_id.shape
     n = count_persons(person_id).to(lidar_feature.device)
     valid = torch.arange(MNP, device=lidar_feature.device).view(1, MNP) < n.view(B, 1)
-    person_num = n.tolist()                                              # the one host read of this step
     feat = lidar_feature * valid.unsqueeze(-1).to(lidar_feature.dtype)
     De = pairwise_euclidean_distance(bboxes3d[..., :3])
     pair = (valid.unsqueeze(1) & valid.unsqueeze(2)).to(De.dtype)
-    return dict(person_num=person_num, valid=valid, feature=feat, De=De * pair)
+    return _DafmInputs(person_count=n, valid=valid, feature=feat, De=De * pair)
 
 
 class PointLiDARBackbone(nn.Module):
