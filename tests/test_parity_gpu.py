@@ -6,7 +6,7 @@ import pytest
 import torch
 
 import cases
-from multimodal_gar_b200 import synthetic
+from multimodal_gar_b200 import _lib, synthetic
 from multimodal_gar_b200.pcdet.ops.pointnet2.pointnet2_stack import pointnet2_modules, pointnet2_utils, sa_mlp_fused
 from multimodal_gar_b200.pcdet.ops.roiaware_pool3d import roiaware_pool3d_utils
 from multimodal_gar_b200.pcdet.ops.roipoint_pool3d import roipoint_pool3d_cuda, roipoint_pool3d_utils
@@ -496,20 +496,28 @@ def test_fused_fps_ball_query_geometries_schedule_and_partial_rows(cuda, monkeyp
     assert (lc[1::4] < n // 2).all() and (lc[0::2] == m).all()
 
 
+@pytest.mark.parametrize("split", [False, True])
 @pytest.mark.parametrize("m,K,radius", [(512, 32, 0.35), (512, 64, 0.6), (200, 16, 0.15), (512, 32, 5.0)])
-def test_fused_fps_ball_query_periodic_clouds(cuda, monkeypatch, m, K, radius):
+def test_fused_fps_ball_query_periodic_clouds(cuda, monkeypatch, m, K, radius, split):
     """Wrapped clouds (slot k = point k mod p, what roipoint pooling produces) through the kernel that processes only the
     distinct blocks (fps_bq_dup.cuh): every period class - p < 32, p a multiple of 32, p = 511 / 512, periods whose copies
     straddle block boundaries, duplicated points INSIDE a period (ties between distinct slots) - with the true period, a
-    multiple of it, a wrong hint (verified and ignored) and no hint; bit-exact against the two separate kernels."""
+    multiple of it, a wrong hint (verified and ignored) and no hint; bit-exact against the two separate kernels.
+    split: >= 1184 weighted clouds, the default launch - the clouds the hint calls long go to the four-warp kernel, the
+    others to the periodic-cloud kernel beside it (a wrong hint only moves a cloud to the other kernel; "zero" sends every
+    cloud to the periodic kernel, "double" most of them to the four-warp one)."""
     from multimodal_gar_b200 import fastpath
     monkeypatch.delenv("MGAR_FPS_BQ", raising=False)
     monkeypatch.delenv("MGAR_FPS_BQ_GEOM", raising=False)
-    monkeypatch.setenv("MGAR_FPS_BQ_DUP", "1")          # opt-in kernel (not the default: slower on the bench step)
+    monkeypatch.delenv("MGAR_FPS_BQ_SPLIT", raising=False)
+    if split:
+        monkeypatch.delenv("MGAR_FPS_BQ_DUP", raising=False)
+    else:
+        monkeypatch.setenv("MGAR_FPS_BQ_DUP", "1")      # the periodic-cloud kernel alone
     n = 512
     periods = [1, 2, 5, 31, 32, 33, 63, 64, 65, 100, 145, 160, 200, 255, 256, 257, 300, 383, 384, 400, 479, 480, 481, 500, 511, 512]
     rng = np.random.default_rng(m + K)
-    periods = periods + [int(v) for v in rng.integers(1, 513, 640 - len(periods))]
+    periods = periods + [int(v) for v in rng.integers(1, 513, (1300 if split else 640) - len(periods))]
     b = len(periods)
     c = np.zeros((b, n, 3), np.float32)
     for g, p in enumerate(periods):
@@ -526,7 +534,9 @@ def test_fused_fps_ball_query_periodic_clouds(cuda, monkeypatch, m, K, radius):
     hints = {"true": true_p, "double": torch.clamp(true_p * 2, max=600), "wrong": T(rng.integers(1, 513, b).astype(np.int32), cuda),
              "zero": torch.zeros_like(true_p)}
     for name, h in hints.items():
+        n0 = _lib.launch_count()
         got = fastpath.fps_ball_query(x, m, radius, K, cloud_weight=h)
+        assert _lib.launch_count() - n0 == (3 if split else 2), "order + %s" % ("two kernels side by side" if split else "one kernel")
         assert torch.equal(got[0], idx), name
         assert torch.equal(got[1], new_xyz), name
         assert torch.equal(got[2], ball), name
