@@ -396,11 +396,36 @@ frame_grid_build_kernel(const float *__restrict__ boxes, unsigned char *__restri
 }
 
 constexpr int kGridLIters = 2;                              // point tiles (1024 points each) per CTA
+constexpr int kTileBytes = kMaskThreads * 4 * 3 * (int)sizeof(float);   // one tile of xyz rows: 12 KB
+
+// ---- bulk asynchronous copy (the TMA engine's 1-D form): a CTA's point tiles are in flight before it does anything else --
+__device__ __forceinline__ uint32_t pm_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void pm_bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void pm_mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+
+// kBulk: the CTA's kGridLIters tiles of 1024 points (12 KB each) are brought into shared memory by cp.async.bulk copies
+// issued before anything else (one mbarrier per tile); a thread then reads its four points with three conflict-free
+// 128-bit shared loads.  Needs 16-byte aligned rows and whole tiles (the launcher checks; partial tiles use the other
+// instantiation's loads).
+template <bool kBulk>
 __global__ void __launch_bounds__(kMaskThreads)
 box_mask_framegrid_kernel(const unsigned char *__restrict__ ws, const float *__restrict__ pts, int *__restrict__ box_idx,
                           unsigned *__restrict__ mask, int M, int N, int W, int vec_ok) {
-    extern __shared__ int grid_sm[];
-    BoxP *sbox = reinterpret_cast<BoxP *>(grid_sm);                                   // [M]
+    extern __shared__ __align__(16) int grid_sm[];
+    __shared__ __align__(8) unsigned long long s_bar[kGridLIters];
+    // [kBulk: kGridLIters point tiles] [M boxes]
+    BoxP *sbox = reinterpret_cast<BoxP *>(reinterpret_cast<unsigned char *>(grid_sm) + (kBulk ? kGridLIters * kTileBytes : 0));
     const int b = blockIdx.y;
     ws += (size_t)b * FrameGrid::bytes(M);
     const unsigned char *gcnt = ws + FrameGrid::cnt_off();
@@ -408,6 +433,21 @@ box_mask_framegrid_kernel(const unsigned char *__restrict__ ws, const float *__r
     const int overflow = __ldg(reinterpret_cast<const int *>(ws + FrameGrid::flag_off()));
     pts += (size_t)b * N * 3;
     mask += (size_t)b * M * W;
+    if (kBulk) {
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int it = 0; it < kGridLIters; it++)
+                asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(pm_smem_u32(&s_bar[it])), "r"(1) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+#pragma unroll
+            for (int it = 0; it < kGridLIters; it++) {
+                const long long t0 = ((long long)blockIdx.x * kGridLIters + it) * kMaskThreads * 4;       // first point of the tile
+                if (t0 < N)
+                    pm_bulk_load(pm_smem_u32(reinterpret_cast<unsigned char *>(grid_sm) + it * kTileBytes), pts + t0 * 3, kTileBytes,
+                                 pm_smem_u32(&s_bar[it]));
+            }
+        }
+    }
     {
         const float4 *src = reinterpret_cast<const float4 *>(ws + FrameGrid::box_off());
         float4 *dst = reinterpret_cast<float4 *>(sbox);
@@ -418,7 +458,14 @@ box_mask_framegrid_kernel(const unsigned char *__restrict__ ws, const float *__r
         const long long p0 = (((long long)blockIdx.x * kGridLIters + it) * kMaskThreads + threadIdx.x) * 4;
         const int n_valid = p0 >= N ? 0 : (N - p0 >= 4 ? 4 : (int)(N - p0));
         float x[4], y[4], z[4];
-        if (vec_ok && n_valid == 4) {
+        if (kBulk) {
+            if (n_valid == 0) continue;                       // (whole tiles only: the tile is either complete or absent)
+            pm_mbar_wait(pm_smem_u32(&s_bar[it]), 0);
+            const float4 *v = reinterpret_cast<const float4 *>(reinterpret_cast<unsigned char *>(grid_sm) + it * kTileBytes) + threadIdx.x * 3;
+            const float4 a = v[0], bb = v[1], c = v[2];
+            x[0] = a.x; y[0] = a.y; z[0] = a.z;   x[1] = a.w; y[1] = bb.x; z[1] = bb.y;
+            x[2] = bb.z; y[2] = bb.w; z[2] = c.x; x[3] = c.y; y[3] = c.z; z[3] = c.w;
+        } else if (vec_ok && n_valid == 4) {
             const float4 *v = reinterpret_cast<const float4 *>(pts + p0 * 3);
             const float4 a = __ldg(v), bb = __ldg(v + 1), c = __ldg(v + 2);
             x[0] = a.x; y[0] = a.y; z[0] = a.z;   x[1] = a.w; y[1] = bb.x; z[1] = bb.y;
@@ -591,8 +638,20 @@ extern "C" int mgar_box_masks(const float *boxes_first, const float *boxes_pool,
         frame_grid_build_kernel<<<B, kMaskThreads, kGridN * kGridN * sizeof(int), st>>>(boxes_pool, static_cast<unsigned char *>(workspace), M);
         count_launch();
         grid.x = div_up(N, kMaskThreads * 4 * kGridLIters);
-        box_mask_framegrid_kernel<<<grid, kMaskThreads, (size_t)M * sizeof(BoxP), st>>>(static_cast<const unsigned char *>(workspace),
-                                                                                          pts, box_idx, mask, M, N, W, vec_ok);
+        // MGAR_BOX_MASK_BULK=1 (whole 1024-point tiles of 16-byte aligned rows): the tiles are staged by the TMA engine's
+        // bulk copies.  Measured on the bench step: 0.0525-0.0534 ms for the stage against 0.0515-0.0529 with per-thread
+        // 128-bit loads - the kernel is bound by its ~4 instructions per point (cell arithmetic, byte load, test), not by
+        // memory latency, so the deeper memory parallelism buys nothing; per-thread loads stay the default.
+        const char *bulk_env = getenv("MGAR_BOX_MASK_BULK");
+        const bool bulk = vec_ok && N % (kMaskThreads * 4) == 0 && ((size_t)N * 12) % 16 == 0 && bulk_env && bulk_env[0] == '1';
+        if (bulk) {
+            const size_t sm = (size_t)kGridLIters * kTileBytes + (size_t)M * sizeof(BoxP);
+            box_mask_framegrid_kernel<true><<<grid, kMaskThreads, sm, st>>>(static_cast<const unsigned char *>(workspace), pts, box_idx,
+                                                                          mask, M, N, W, vec_ok);
+        } else {
+            box_mask_framegrid_kernel<false><<<grid, kMaskThreads, (size_t)M * sizeof(BoxP), st>>>(
+                static_cast<const unsigned char *>(workspace), pts, box_idx, mask, M, N, W, vec_ok);
+        }
     }
     else if ((!box_idx || boxes_first == boxes_pool) && M <= kGridMaxBoxes && !getenv("MGAR_NO_BOX_GRID"))
     {

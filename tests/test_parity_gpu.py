@@ -142,6 +142,21 @@ def test_mask_pooling_equals_single_kernel_pooling_and_points_in_boxes(cuda, N, 
         assert torch.equal(pooled, p2)
 
 
+@pytest.mark.parametrize("N", [65536, 3072, 1024])
+def test_box_masks_bulk_staged_tiles_equal_the_per_thread_loads(cuda, monkeypatch, N):
+    """MGAR_BOX_MASK_BULK=1: the point tiles travel by cp.async.bulk + mbarrier (opt-in; measured no faster) - same
+    first-hit indices and bit masks, incl. an odd number of tiles per frame (the CTA's second tile is absent)."""
+    from multimodal_gar_b200 import fastpath
+    pts, boxes = synthetic.make_batch(N, 3, N=N, M=40, density_scale=0.5 if N < 60000 else 1.0)
+    xyz, bx = T(pts[..., :3], cuda), T(boxes, cuda)
+    monkeypatch.delenv("MGAR_BOX_MASK_BULK", raising=False)
+    idx0, mask0 = fastpath.box_masks(xyz, bx, None)
+    monkeypatch.setenv("MGAR_BOX_MASK_BULK", "1")
+    idx1, mask1 = fastpath.box_masks(xyz, bx, None)
+    assert torch.equal(idx0, idx1) and torch.equal(mask0, mask1)
+    assert int((idx0 >= 0).sum()) > 0
+
+
 def test_mask_pooling_box_grid_adversarial(cuda):
     """The box-grid pass must never lose a hit: boxes stacked in one cell (overflow -> exhaustive loop), boxes and points
     beyond the grid's +-32 m (border cells), boxes straddling cell borders, a huge box, a zero-padded box."""
