@@ -358,12 +358,25 @@ struct FrameGrid {                      // layout of one frame's scratch (bytes)
     static __host__ __device__ size_t bytes(int M) { return (box_off() + (size_t)M * sizeof(BoxP) + 255) & ~(size_t)255; }
 };
 
+// grid (1 + kZeroCtas, B): CTA 0 of a frame builds its grid; the others zero-fill the frame's in-box bit masks (mask != null:
+// the masks are OR-ed into afterwards) - one launch instead of a memset node + a 64-CTA kernel one after the other.
+constexpr int kZeroCtas = 16;
 __global__ void __launch_bounds__(kMaskThreads)
-frame_grid_build_kernel(const float *__restrict__ boxes, unsigned char *__restrict__ ws, int M) {
+frame_grid_build_kernel(const float *__restrict__ boxes, unsigned char *__restrict__ ws, int M, unsigned *__restrict__ mask,
+                        long long mask_words) {
     extern __shared__ int grid_sm[];
     int *scnt = grid_sm;                                                              // [cells]
     __shared__ int s_overflow;
-    const int b = blockIdx.x;
+    const int b = blockIdx.y;
+    if (blockIdx.x > 0) {
+        if (!mask) return;
+        uint4 *dst = reinterpret_cast<uint4 *>(mask + (size_t)b * mask_words);          // (the launcher checked the alignment)
+        const long long n16 = mask_words / 4;
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        for (long long i = (long long)(blockIdx.x - 1) * kMaskThreads + threadIdx.x; i < n16; i += (long long)kZeroCtas * kMaskThreads)
+            dst[i] = z;
+        return;
+    }
     boxes += (size_t)b * M * 7;
     ws += (size_t)b * FrameGrid::bytes(M);
     unsigned char *gcnt = ws + FrameGrid::cnt_off();
@@ -395,7 +408,10 @@ frame_grid_build_kernel(const float *__restrict__ boxes, unsigned char *__restri
     if (threadIdx.x == 0) *reinterpret_cast<int *>(ws + FrameGrid::flag_off()) = s_overflow;
 }
 
-constexpr int kGridLIters = 2;                              // point tiles (1024 points each) per CTA
+#ifndef MGAR_GRID_ITERS
+#define MGAR_GRID_ITERS 2
+#endif
+constexpr int kGridLIters = MGAR_GRID_ITERS;                // point tiles (1024 points each) per CTA
 constexpr int kTileBytes = kMaskThreads * 4 * 3 * (int)sizeof(float);   // one tile of xyz rows: 12 KB
 
 // ---- bulk asynchronous copy (the TMA engine's 1-D form): a CTA's point tiles are in flight before it does anything else --
@@ -424,8 +440,9 @@ box_mask_framegrid_kernel(const unsigned char *__restrict__ ws, const float *__r
                           unsigned *__restrict__ mask, int M, int N, int W, int vec_ok) {
     extern __shared__ __align__(16) int grid_sm[];
     __shared__ __align__(8) unsigned long long s_bar[kGridLIters];
-    // [kBulk: kGridLIters point tiles] [M boxes]
-    BoxP *sbox = reinterpret_cast<BoxP *>(reinterpret_cast<unsigned char *>(grid_sm) + (kBulk ? kGridLIters * kTileBytes : 0));
+    // [kBulk: kGridLIters point tiles] [cell counts: kGridN^2 bytes] [M boxes]
+    unsigned char *scnt = reinterpret_cast<unsigned char *>(grid_sm) + (kBulk ? kGridLIters * kTileBytes : 0);
+    BoxP *sbox = reinterpret_cast<BoxP *>(scnt + kGridN * kGridN);
     const int b = blockIdx.y;
     ws += (size_t)b * FrameGrid::bytes(M);
     const unsigned char *gcnt = ws + FrameGrid::cnt_off();
@@ -452,6 +469,11 @@ box_mask_framegrid_kernel(const unsigned char *__restrict__ ws, const float *__r
         const float4 *src = reinterpret_cast<const float4 *>(ws + FrameGrid::box_off());
         float4 *dst = reinterpret_cast<float4 *>(sbox);
         for (int i = threadIdx.x; i < M * 2; i += kMaskThreads) dst[i] = __ldg(src + i);
+        // the frame's cell counts (4 KB) into shared memory: a point's lookup is then a shared byte load instead of a
+        // dependent global one (the kernel's top stall was the long scoreboard on exactly these loads)
+        const uint4 *csrc = reinterpret_cast<const uint4 *>(gcnt);
+        uint4 *cdst = reinterpret_cast<uint4 *>(scnt);
+        for (int i = threadIdx.x; i < kGridN * kGridN / 16; i += kMaskThreads) cdst[i] = __ldg(csrc + i);
     }
     __syncthreads();
     for (int it = 0; it < kGridLIters; it++) {
@@ -495,7 +517,7 @@ box_mask_framegrid_kernel(const unsigned char *__restrict__ ws, const float *__r
 #pragma unroll
             for (int j = 0; j < 4; j++) {                     // the four cell counts in flight together
                 cell[j] = grid_cell(y[j]) * kGridN + grid_cell(x[j]);
-                cnt[j] = __ldg(gcnt + cell[j]);
+                cnt[j] = scnt[cell[j]];
             }
 #pragma unroll
             for (int j = 0; j < 4; j++) {
@@ -628,14 +650,19 @@ extern "C" int mgar_box_masks(const float *boxes_first, const float *boxes_pool,
     MGAR_REQUIRE(B <= 65535, "box_masks: B=%d exceeds grid.y limit", B);
     cudaStream_t st = (cudaStream_t)stream;
     const int W = (N + 31) / 32;
-    MGAR_CUDA(cudaMemsetAsync(mask, 0, (size_t)B * M * W * sizeof(unsigned), st));
     const int vec_ok = ((reinterpret_cast<uintptr_t>(pts) & 15) == 0) && (!box_idx || (reinterpret_cast<uintptr_t>(box_idx) & 15) == 0) &&
                        (N % 4 == 0);
     dim3 grid(div_up(N, kMaskThreads * 4), B);
     static_assert(sizeof(BoxP) == 32, "the frame grid copies boxes as two float4");
-    if ((!box_idx || boxes_first == boxes_pool) && M <= kGridMaxBoxes && !getenv("MGAR_NO_BOX_GRID") && workspace &&
-        workspace_bytes >= mgar_box_masks_workspace_bytes(B, M) && !getenv("MGAR_NO_FRAME_GRID")) {
-        frame_grid_build_kernel<<<B, kMaskThreads, kGridN * kGridN * sizeof(int), st>>>(boxes_pool, static_cast<unsigned char *>(workspace), M);
+    const bool frame_grid = (!box_idx || boxes_first == boxes_pool) && M <= kGridMaxBoxes && !getenv("MGAR_NO_BOX_GRID") && workspace &&
+        workspace_bytes >= mgar_box_masks_workspace_bytes(B, M) && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0 &&
+        !getenv("MGAR_NO_FRAME_GRID");
+    // the masks are cleared by the grid-building launch when a frame's words are whole 16-byte groups, by a memset otherwise
+    const bool zero_in_kernel = frame_grid && ((size_t)M * W) % 4 == 0 && (reinterpret_cast<uintptr_t>(mask) & 15) == 0;
+    if (!zero_in_kernel) MGAR_CUDA(cudaMemsetAsync(mask, 0, (size_t)B * M * W * sizeof(unsigned), st));
+    if (frame_grid) {
+        frame_grid_build_kernel<<<dim3(1 + (zero_in_kernel ? kZeroCtas : 0), B), kMaskThreads, kGridN * kGridN * sizeof(int), st>>>(
+            boxes_pool, static_cast<unsigned char *>(workspace), M, zero_in_kernel ? mask : nullptr, (long long)M * W);
         count_launch();
         grid.x = div_up(N, kMaskThreads * 4 * kGridLIters);
         // MGAR_BOX_MASK_BULK=1 (whole 1024-point tiles of 16-byte aligned rows): the tiles are staged by the TMA engine's
@@ -645,11 +672,11 @@ extern "C" int mgar_box_masks(const float *boxes_first, const float *boxes_pool,
         const char *bulk_env = getenv("MGAR_BOX_MASK_BULK");
         const bool bulk = vec_ok && N % (kMaskThreads * 4) == 0 && ((size_t)N * 12) % 16 == 0 && bulk_env && bulk_env[0] == '1';
         if (bulk) {
-            const size_t sm = (size_t)kGridLIters * kTileBytes + (size_t)M * sizeof(BoxP);
+            const size_t sm = (size_t)kGridLIters * kTileBytes + (size_t)kGridN * kGridN + (size_t)M * sizeof(BoxP);
             box_mask_framegrid_kernel<true><<<grid, kMaskThreads, sm, st>>>(static_cast<const unsigned char *>(workspace), pts, box_idx,
                                                                           mask, M, N, W, vec_ok);
         } else {
-            box_mask_framegrid_kernel<false><<<grid, kMaskThreads, (size_t)M * sizeof(BoxP), st>>>(
+            box_mask_framegrid_kernel<false><<<grid, kMaskThreads, (size_t)kGridN * kGridN + (size_t)M * sizeof(BoxP), st>>>(
                 static_cast<const unsigned char *>(workspace), pts, box_idx, mask, M, N, W, vec_ok);
         }
     }
