@@ -710,16 +710,27 @@ extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xy
             if (int rc = sort_clouds(n_heavy, split_from)) return rc;
             MGAR_CUDA(cudaEventRecord(side->fork, st));
             MGAR_CUDA(cudaStreamWaitEvent(side->stream, side->fork, 0));
-            {   // long clouds: four warps each, on the caller's stream
-                const size_t sm = (size_t)kDupN * sizeof(float4) + (size_t)m * sizeof(int) + (size_t)4 * 2 * nsample * sizeof(int);
-                if (sm > 48 * 1024)
-                    MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-                // both kernels ask for the same shared-memory carve-out: CTAs of kernels with different L1 / shared splits
-                // do not share an SM, and the two launches would run one after the other
-                MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<4, 4>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                               (int)cudaSharedmemCarveoutMaxShared));
-                fps_bq_cta_kernel<4, 4><<<b, 128, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, order,
-                                                            live_cnt, write_dup_rows, n_heavy);
+            {   // long clouds: four warps each, on the caller's stream (MGAR_FPS_BQ_LONG=2: two warps, for A/B runs)
+                const char *lg = getenv("MGAR_FPS_BQ_LONG");
+                const int lw = (lg && lg[0] == '2') ? 2 : 4;
+                const size_t sm = (size_t)kDupN * sizeof(float4) + (size_t)m * sizeof(int) + (size_t)lw * 2 * nsample * sizeof(int);
+                if (lw == 4) {
+                    if (sm > 48 * 1024)
+                        MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+                    // both kernels ask for the same shared-memory carve-out: CTAs of kernels with different L1 / shared splits
+                    // do not share an SM, and the two launches would run one after the other
+                    MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<4, 4>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                                   (int)cudaSharedmemCarveoutMaxShared));
+                    fps_bq_cta_kernel<4, 4><<<b, 128, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, order,
+                                                                live_cnt, write_dup_rows, n_heavy);
+                } else {
+                    if (sm > 48 * 1024)
+                        MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+                    MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<2, 8>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                                   (int)cudaSharedmemCarveoutMaxShared));
+                    fps_bq_cta_kernel<2, 8><<<b, 64, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, order,
+                                                               live_cnt, write_dup_rows, n_heavy);
+                }
                 count_launch();
                 if (int rc = check_launch("fps_ball_query(long clouds)")) return rc;
             }
