@@ -730,6 +730,32 @@ def run_native(args, rank, world, local_rank):
         l1.record()
         torch.cuda.synchronize()
         r["lat_ms"] = l0.elapsed_time(l1) / 20
+    # the same two steps replayed from CUDA graphs (multimodal_gar_b200/graphs.py): one cudaGraphLaunch per step
+    r["graph"] = None
+    if not args.quick or os.environ.get("MGAR_BENCH_GRAPH"):
+        from multimodal_gar_b200 import graphs
+        try:
+            out = {}
+            for name, inputs, n in (("latency_1frame_ms", [one], 50), ("ms_per_step", [list(devb[0]), list(devb[1])], args.steps)):
+                gs = [graphs.GraphedPersonEncoder(enc, *inp) for inp in inputs]       # one graph per resident input batch
+                for i in range(4):
+                    gs[i % len(gs)].graph.replay()
+                torch.cuda.synchronize()
+                l0, l1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                l0.record()
+                for i in range(n):
+                    gs[i % len(gs)].graph.replay()
+                l1.record()
+                torch.cuda.synchronize()
+                out[name] = ctx.max_over_ranks(l0.elapsed_time(l1) / n)
+                del gs
+            out["frames_per_s"] = F * ctx.world / (out["ms_per_step"] * 1e-3)
+            out["note"] = ("the configs[1] step (%d frames; two graphs over the two alternating input batches, as `value`) and the "
+                           "single-frame step captured once and replayed" % F)
+            r["graph"] = out
+        except Exception as e:                      # a capture failure must not take the bench line down
+            r["graph"] = dict(unavailable="%s: %s" % (type(e).__name__, str(e)[:200]))
+        torch.cuda.empty_cache()
     if not args.quick:
         r["steady"] = block_steady_state(ctx, enc, devb, F, args.steady_seconds, ms_total / args.steps)
         del devb
@@ -810,7 +836,7 @@ def main():
                              h2d_bytes_per_step=e["h2d"], d2h_bytes_per_step=e["d2h"], **e["extra"]),
                     gpu_launches=r["launches"], clocks=r["clocks"], roofline=roof, stages=stages,
                     pipeline_algorithmic_GBps=pipeline_GBps, pipeline_hbm_frac=pipeline_GBps / pk["hbm"] / world,
-                    latency_1frame_ms=r["lat_ms"])
+                    latency_1frame_ms=r["lat_ms"], cuda_graph=r["graph"])
         if "steady" in r:
             line["steady_state"] = r["steady"]
             cfgs = {"configs[2]": r["config2"]}

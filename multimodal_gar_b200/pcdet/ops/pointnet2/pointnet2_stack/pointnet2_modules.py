@@ -65,7 +65,11 @@ class StackSAModuleMSG(nn.Module):
                 nn.init.constant_(m.bias, 0)
 
     def train(self, mode=True):
-        self._packed = None  # parameters may change: re-fold on the next eval forward
+        # parameters may change in train(): re-fold on the next eval forward.  A repeated eval() keeps the folded tensors:
+        # a CUDA graph captured over the eval path (multimodal_gar_b200/graphs.py) holds their device addresses, and the
+        # version key below catches every real change of a parameter or buffer anyway.
+        if mode or self.training:
+            self._packed = None
         return super().train(mode)
 
     def _pack_key(self, device):
