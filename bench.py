@@ -630,6 +630,29 @@ def block_train(ctx, frames_per_rank, steps=6):
         out["ms_per_step_no_allreduce"] = round(ms0, 3)
         out["exposed_comm_ms"] = round(max(0.0, ms - ms0), 3)
         model(batch).backward()      # leave DDP's reducer in a consistent state (grads synchronised once more)
+    # the same step captured into a CUDA graph (train_step.GraphedTrainStep): the eager step is launch-bound
+    try:
+        del model, opt
+        torch.manual_seed(1994)
+        net2 = TS.LidarFusionNet().to(dev).train()
+        if ctx.world > 1:
+            side = torch.cuda.Stream(device=dev)                # torch's rule for graphed DDP: build the wrapper in a side stream
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                model2 = TS.make_ddp(net2, dev)
+            torch.cuda.current_stream(dev).wait_stream(side)
+        else:
+            model2 = net2
+        opt2 = torch.optim.Adam(model2.parameters(), lr=1e-4, fused=True, capturable=True)
+        step = TS.GraphedTrainStep(model2, opt2, batch, warmup=11 if ctx.world > 1 else 3)
+        gl = []
+        msg = ctx.timed(lambda: gl.append(step(batch).clone()), steps, warm=2)
+        out["cuda_graph"] = dict(ms_per_step=round(msg, 3), value=frames_per_rank * ctx.world / (msg * 1e-3), unit="frames/s",
+                                 loss_last=float(gl[-1]),
+                                 note="zero_grad + forward + backward%s + Adam replayed from one CUDA graph"
+                                      % (" + NCCL all-reduce" if ctx.world > 1 else ""))
+    except Exception as e:
+        out["cuda_graph"] = dict(unavailable="%s: %s" % (type(e).__name__, str(e)[:200]))
     return out
 
 

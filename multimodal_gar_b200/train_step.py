@@ -101,3 +101,40 @@ def train_step(model, optimizer, batch):
     loss.backward()
     optimizer.step()
     return loss.detach()
+
+
+class GraphedTrainStep:
+    """`train_step` for ONE fixed batch shape captured into a CUDA graph: zero_grad + forward + backward + optimizer step
+    replayed with one `cudaGraphLaunch`.  The eager step is launch-bound (5.6 ms of kernels in a 6.4 ms step: ~400 small
+    launches of the fusion module's forward / backward around the library's few large ones); nothing in it reads the device
+    back, so it is capturable as it is.  The optimizer must be capturable (`torch.optim.Adam(..., capturable=True)`); under
+    DistributedDataParallel follow torch's rules for graphed DDP (construct the wrapper in a side stream, >= 11 warm-up steps).
+
+        step = GraphedTrainStep(model, optimizer, batch)      # warm-up steps (they DO train) + capture
+        loss = step(next_batch)                               # static tensor, overwritten by the next replay"""
+
+    def __init__(self, model, optimizer, batch, warmup=3):
+        dev = next(iter(batch.values())).device
+        self.model, self.optimizer = model, optimizer
+        self.static_batch = {k: v.clone() for k, v in batch.items()}
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                train_step(model, optimizer, self.static_batch)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        optimizer.zero_grad(set_to_none=True)
+        with torch.cuda.graph(self.graph):
+            self.static_loss = model(self.static_batch)
+            self.static_loss.backward()
+            optimizer.step()
+
+    def __call__(self, batch):
+        for k, dst in self.static_batch.items():
+            src = batch[k]
+            if dst.data_ptr() != src.data_ptr():
+                dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        return self.static_loss.detach()
