@@ -677,7 +677,8 @@ extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xy
             count_launch();
             return check_launch("fps_ball_query(order)");
         };
-        const bool dup_ok = n == kDupN && cloud_weight && order && !getenv("MGAR_FPS_BQ_GEOM");
+        // (radius < 1e9: the periodic kernel parks its unused register slots 1e18 away, beyond any sane radius)
+        const bool dup_ok = n == kDupN && cloud_weight && order && !getenv("MGAR_FPS_BQ_GEOM") && radius < 1e9f;
         auto dup_smem = [&](int ctas_per_sm) {
             size_t sm = (size_t)kDupN * sizeof(float4) + (size_t)m * sizeof(int) + (size_t)kDupW * 2 * nsample * sizeof(int);
             if (const char *e = getenv("MGAR_FPS_BQ_CTAS")) { const int v = atoi(e); if (v >= 1 && v <= 32) ctas_per_sm = v; }
@@ -701,7 +702,7 @@ extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xy
         // profiles/r02_fps_round_latency.json) - they are the step's critical path; all the others go to the periodic-cloud
         // kernel, which spends instructions only on their distinct blocks - they are the step's instruction count.  The
         // second launch runs on a side stream of the library (fork / join by events, legal under stream capture too).
-        int split_from = 336;                    // sweep: profiles/r02_fps_split_sweep.txt
+        int split_from = 320;                    // sweeps: profiles/r02_fps_split_sweep.txt
         if (const char *e = getenv("MGAR_FPS_BQ_SPLIT")) split_from = atoi(e);
         if (dup_ok && split_from > 0 && b >= 8 * kNumSMs) {
             SideStream *side = side_stream();
@@ -721,8 +722,17 @@ extern "C" int mgar_fps_ball_query(int b, int n, int m, const float *xyz, int xy
                     // do not share an SM, and the two launches would run one after the other
                     MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<4, 4>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                                    (int)cudaSharedmemCarveoutMaxShared));
-                    fps_bq_cta_kernel<4, 4><<<b, 128, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, order,
-                                                                live_cnt, write_dup_rows, n_heavy);
+                    if (getenv("MGAR_FPS_BQ_NO_REDUX")) {
+                        fps_bq_cta_kernel<4, 4><<<b, 128, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m, order,
+                                                                    live_cnt, write_dup_rows, n_heavy);
+                    } else {
+                        MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<4, 4, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                                       (int)cudaSharedmemCarveoutMaxShared));
+                        if (sm > 48 * 1024)
+                            MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<4, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+                        fps_bq_cta_kernel<4, 4, true><<<b, 128, sm, st>>>(xyz, xyz_stride, fps_idx, new_xyz, ball_idx, radius, nsample, b, m,
+                                                                          order, live_cnt, write_dup_rows, n_heavy);
+                    }
                 } else {
                     if (sm > 48 * 1024)
                         MGAR_CUDA(cudaFuncSetAttribute(fps_bq_cta_kernel<2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));

@@ -105,7 +105,11 @@ __device__ __forceinline__ void bq_store_masks(int on, uint32_t a, const unsigne
     }
 }
 
-template <int W, int PPL>
+// kRedux: the W (value, ~rank) keys are combined by two warp reductions over lanes that each hold one key instead of a
+// compare tree over all W keys in every lane: ~9 fewer instructions per warp and round at ~25 cycles more latency - for
+// the loaded case (many clouds per SM: a round costs its instruction count times the resident warps), not for a single
+// frame (few clouds: a round costs its latency).
+template <int W, int PPL, bool kRedux = false>
 __global__ void __launch_bounds__(W * 32)
 fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs, float *__restrict__ new_xyz,
                   int *__restrict__ ball_idx, float radius, int K, int b, int m, const int *__restrict__ order,
@@ -117,6 +121,7 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
     __shared__ __align__(16) unsigned s_ring[2 * kBqRing][16];       // hit masks of the last 16 centroids
     __shared__ int s_row0[64];
     __shared__ __align__(8) unsigned long long s_mbar;
+    __shared__ __align__(8) unsigned s_pin[W * 32][2];
     float4 *sp = bq_sm4;                                   // [n] staged cloud
     int *sidx = reinterpret_cast<int *>(sp + n);           // [m] sampled indices
     int *rows = sidx + m;                                  // [W][2][K] rows being assembled
@@ -145,8 +150,18 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
         __syncthreads();
     }
 
-    const float r2 = __fmul_rn(radius, radius);
-    const int rank0 = (int)bq_pin((uint32_t)((brev_n<5>(lane) << NB) | (w * PPL)));
+    // Per-thread loop constants go THROUGH shared memory once: ptxas sees through `mov` pins and rematerialises such values
+    // inside the round (r^2 from the constant bank + an FMUL, the rank from S2R / BREV / SHF / LOP3: 8 of ~100 instructions
+    // per round); a value loaded from shared memory it has to keep.
+    float r2 = __fmul_rn(radius, radius);
+    int rank0 = (brev_n<5>(lane) << NB) | (w * PPL);
+    {
+        s_pin[tid][0] = (unsigned)rank0; s_pin[tid][1] = __float_as_uint(r2);
+        __syncwarp();
+        unsigned pv[2];
+        bq_lds_u2(bq_smem_u32(&s_pin[tid][0]), pv);
+        rank0 = (int)pv[0]; r2 = __uint_as_float(pv[1]);
+    }
     const int lane0 = (int)bq_pin(lane == 0 ? 1u : 0u), thread0 = (int)bq_pin(tid == 0 ? 1u : 0u);
     const uint32_t sp_a = bq_pin(bq_smem_u32(sp)), sidx_a = bq_pin(bq_smem_u32(sidx));
     const uint32_t key_a = bq_pin(bq_smem_u32(&s_key[0][0][0]));
@@ -231,6 +246,12 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
             const uint32_t ka = key_a + (uint32_t)(j & 1) * (uint32_t)(W * 8);
             bq_sts_u2_if(lane0, key_w + (uint32_t)(j & 1) * (uint32_t)(W * 8), ~(unsigned)rmin_w, (unsigned)vmax_w);
             __syncthreads();
+            if constexpr (kRedux) {
+                unsigned kk[2];                            // lane l holds the key of warp l mod W: kk[0] = ~rank, kk[1] = value
+                bq_lds_u2(ka + (uint32_t)(lane & (W - 1)) * 8u, kk);
+                vmax = __reduce_max_sync(0xffffffffu, kk[1]);
+                nrank = __reduce_max_sync(0xffffffffu, kk[1] == vmax ? kk[0] : 0u);
+            } else {
             // (value << 32 | ~rank) as one unsigned 64-bit key per warp: the largest key wins
             unsigned long long key = 0;
 #pragma unroll
@@ -243,6 +264,7 @@ fps_bq_cta_kernel(const float *__restrict__ xyz, int xs, int *__restrict__ idxs,
                 key = kq > key ? kq : key;
             }
             vmax = (unsigned)(key >> 32); nrank = (unsigned)key;
+            }
         }
         if (((j & (kBqRing - 1)) == 0) | (vmax == 0)) {
             if constexpr (W == 1) __syncwarp();

@@ -60,8 +60,11 @@ __device__ __forceinline__ void bq_dup_body(const DupCtx &C) {
         const int blk = 2 * i + w, k = blk * 32 + lane;
         act[i] = blk < nb;                                   // warp-uniform
         const float4 q = C.sp[act[i] ? k : 0];
-        px[i] = q.x; py[i] = q.y; pz[i] = q.z;
-        t[i] = act[i] ? 1e10f : -1.f;                        // -1 never wins (distances are >= 0)
+        // a slot without a block sits 1e18 away (its squared distance, ~3e36, is finite and beyond any radius: never a
+        // hit) with a running minimum of -1 (fminf keeps it; distances are >= 0, so it never wins): the round needs no
+        // per-slot activity test
+        px[i] = act[i] ? q.x : 1e18f; py[i] = act[i] ? q.y : 1e18f; pz[i] = act[i] ? q.z : 1e18f;
+        t[i] = act[i] ? 1e10f : -1.f;
         int best = INT_MAX;
         if (act[i])
             for (int kk = k % p; kk < kDupN; kk += p) best = min(best, brev_n<9>(kk));     // once per cloud
@@ -142,9 +145,8 @@ __device__ __forceinline__ void bq_dup_body(const DupCtx &C) {
 #pragma unroll
         for (int i = 0; i < PE; i++) {
             const float d = sqdist(__fsub_rn(px[i], c.x), __fsub_rn(py[i], c.y), __fsub_rn(pz[i], c.z));
-            const unsigned bal = __ballot_sync(0xffffffffu, d < r2);
-            hb[i] = act[i] ? bal : 0u;
-            t[i] = act[i] ? fminf(d, t[i]) : -1.f;
+            hb[i] = __ballot_sync(0xffffffffu, d < r2);
+            t[i] = fminf(d, t[i]);
         }
         float mx = t[0];
 #pragma unroll
@@ -176,8 +178,7 @@ __device__ __forceinline__ void bq_dup_body(const DupCtx &C) {
         unsigned hb[PE];
 #pragma unroll
         for (int i = 0; i < PE; i++) {
-            const unsigned bal = __ballot_sync(0xffffffffu, sqdist(__fsub_rn(px[i], c.x), __fsub_rn(py[i], c.y), __fsub_rn(pz[i], c.z)) < r2);
-            hb[i] = act[i] ? bal : 0u;
+            hb[i] = __ballot_sync(0xffffffffu, sqdist(__fsub_rn(px[i], c.x), __fsub_rn(py[i], c.y), __fsub_rn(pz[i], c.z)) < r2);
         }
         store_masks(m - 1, hb);
         __syncthreads();
