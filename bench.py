@@ -720,16 +720,21 @@ def run_native(args, rank, world, local_rank):
             tiles = ((live.view(-1) + 3) // 4) * ok
             walked = walked_centroids = float(tiles.sum().item()) * 4 / float(live.numel() * CFG["P"])
             if getattr(enc, "skip_repeated_samples", False) and CFG["K"] == 32 and st["ball_idx"] is not None:
-                # distinct-sample walk: octets of sample slots per distinct centroid, sixteen to a tile (the rule of
+                # distinct-sample walk: units of `us` sample slots per distinct centroid, 128 / us to a tile (the rule of
                 # build_live_units_kernel; the cloud's period = its number of distinct samples on this data)
+                us = int(_lib.lib().mgar_sa_mlp_tc_unit_slots())
                 G, P = live.numel(), CFG["P"]
                 rows = st["ball_idx"].view(G, P, 32)
                 per = live.view(G, 1).clamp(1, P)
                 e0 = rows[:, :, 0]
-                real = [(rows[:, :, s] < per) & (rows[:, :, s] != e0) & (e0 >= 0) for s in (8, 16, 24)]
-                u = 1 + real[0].int() + (real[0] & real[1]).int() + (real[0] & real[1] & real[2]).int()
+                on = e0 >= 0
+                u = torch.ones_like(e0)
+                for sl in range(us, 32, us):
+                    on = on & (rows[:, :, sl] < per) & (rows[:, :, sl] != e0)
+                    u = u + on.int()
                 u = u * (torch.arange(P, device=u.device).view(1, P) < per)
-                utiles = ((u.sum(dim=1) + 15) // 16) * ok
+                upt = 128 // us
+                utiles = ((u.sum(dim=1) + upt - 1) // upt) * ok
                 walked = float(utiles.sum().item()) * 4 / float(G * P)
         del st
     stage_ms = {}

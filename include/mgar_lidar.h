@@ -318,6 +318,9 @@ MGAR_API int mgar_sa_mlp_fwd_fp32(int B, int M, int nsample, int C_in, const flo
  * mgar_stack_workspace_bytes(B) bytes with ragged batch counts (the two never combine: the skip needs the uniform
  * layout), NULL / 0 otherwise; the library allocates nothing. */
 MGAR_API size_t mgar_sa_mlp_tc_workspace_bytes(int M, int group_size);
+/* sample slots per list entry of the distinct-sample walk (8: a tile is 16 octets of one person) - for callers that want
+ * to predict how many tiles a batch executes (bench.py's executed_fraction) */
+MGAR_API int mgar_sa_mlp_tc_unit_slots(void);
 MGAR_API int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg);
 /* nsample 16 and 64 also run on the tensor cores when ONLY group_max is wanted (out == NULL, uniform layout, whole
  * 32-position blocks per group): the kernel walks blocks of 32 positions - two 16-sample centroids or half a 64-sample

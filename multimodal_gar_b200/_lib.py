@@ -68,6 +68,7 @@ SIGNATURES = {
     "mgar_sa_mlp_tc_supported": [_i, _i, _i, _p, _i],
     "mgar_sa_mlp_tc_group_max_supported": [_i, _i, _i, _p, _i],
     "mgar_sa_mlp_tc_workspace_bytes": [_i, _i],
+    "mgar_sa_mlp_tc_unit_slots": [],
     "mgar_sa_mlp_fwd_tc": [_i, _i, _i, _i, _p, _i, _p, _p, _p, _i, _i, _p, _i, _p, _p, _i, _p, _p, _p, _p, _i, _p, _i, _p, _p,
                            _p, _i, _p, ctypes.c_size_t, _p],
     "mgar_sa_mlp_fwd_fp32": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _i, _i, _p, ctypes.c_size_t, _p],

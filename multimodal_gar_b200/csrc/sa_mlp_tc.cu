@@ -406,9 +406,12 @@ extern "C" size_t mgar_sa_mlp_tc_workspace_bytes(int M, int group_size) {
     if (M <= 0 || group_size <= 0) return 0;
     const size_t groups = ((size_t)M + group_size - 1) / group_size;
     // the longest list is the live-unit one: up to four octets per centroid, a person's padded to a multiple of 16
-    const size_t units = groups * (size_t)((4 * group_size + 15) / 16 * 16);
+    const size_t upt = (size_t)tc_units_per_tile();
+    const size_t units = groups * (((size_t)tc_units_per_row() * group_size + upt - 1) / upt * upt);
     return (4 + units) * sizeof(int);
 }
+
+extern "C" int mgar_sa_mlp_tc_unit_slots() { return kTcNS / tc_units_per_row(); }
 
 extern "C" int mgar_sa_mlp_tc_supported(int nsample, int C_in, int n_layers, const int *channels_host, int pool_avg) {
     return nsample == kTcNS && C_in >= 0 && C_in <= 4 && n_layers == 2 && channels_host && channels_host[0] == 3 + C_in &&
@@ -510,7 +513,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
                               "= %zu bytes, got %zu", mgar_sa_mlp_tc_workspace_bytes(M, group_size), workspace ? workspace_bytes : (size_t)0);
                     return MGAR_ENOMEM;
                 }
-                if (group_live_cnt && group_point_cnt && ns32 && M < (1 << 29) && !getenv("MGAR_TC_NO_LIVE_TILES") &&
+                if (group_live_cnt && group_point_cnt && ns32 && M < (1 << 28) && !getenv("MGAR_TC_NO_LIVE_TILES") &&
                     !getenv("MGAR_TC_NO_LIVE_UNITS")) {
                     // distinct samples of the distinct centroids only (see TcArgs::live_units)
                     if (int rc = tc_build_live_units(group_zero, group_live_cnt, group_point_cnt, idx, G, gsv, uniform_n, live + 4,

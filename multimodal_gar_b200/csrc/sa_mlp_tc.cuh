@@ -47,9 +47,10 @@ struct TcArgs {
     // so the centroids live_cnt .. group_size-1 repeat centroid 0 and cannot change the person's max).  Same
     // preconditions as live_groups; m_shift = log2(group_size) or -1.
     const int *live_tiles; int m_shift;
-    // distinct-sample walk (sa_mlp_tc16 only, ns = 32, out == null; null = off): live_units[16 t + u], t < *n_live, u < 16 =
-    // (centroid << 2 | octet) [| 1 << 31: empty ball]: tile t is sixteen OCTETS of sample slots (slots 8 o .. 8 o + 7 of the
-    // centroid's ball row) of ONE person, instead of four whole centroids.  A ball row repeats its hits once it runs out
+    // distinct-sample walk (sa_mlp_tc16 only, ns = 32, out == null; null = off): live_units[U t + u], t < *n_live, u < U =
+    // (centroid << log2(32 / s) | unit) [| 1 << 31: empty ball]: tile t is U = 128 / s UNITS of s sample slots (slots
+    // s o .. s o + s - 1 of the centroid's ball row; s = 4, or 8 - "octets" - in the first version) of ONE person, instead
+    // of four whole centroids.  A ball row repeats its hits once it runs out
     // of distinct ones (copies of a wrapped cloud, then the first hit as padding); the list holds only the octets that
     // start with a distinct sample.  A TMEM lane quarter (32 positions) then mixes up to four centroids: the epilogue's
     // max over the quarter, the folded BatchNorm + ReLU (monotone) and the running person max still commute with the
@@ -74,6 +75,8 @@ int tc_build_live_tiles(const int *group_zero, const int *live_cnt, int G, int g
                         cudaStream_t st);
 // units[16 t + u] as TcArgs::live_units describes, *n_tiles = number of tiles (zeroed here; one small launch).  point_cnt[g] =
 // number of DISTINCT points of group g's cloud (slot k of the cloud holds point k mod point_cnt[g]).
+int tc_units_per_row();        // list entries a centroid can take (32 / slots per entry)
+int tc_units_per_tile();       // entries per 128-position tile
 int tc_build_live_units(const int *group_zero, const int *live_cnt, const int *point_cnt, const int *idx, int G, int group_size,
                         int n_u, int *units, int *n_tiles, cudaStream_t st);
 int sa_mlp_tc16_launch_train(const TcLayer1 &L1, const TcArgs &A, int C0, int grid, cudaStream_t st);   // C0 = 4, 5

@@ -74,7 +74,17 @@ constexpr uint32_t kXBytes = 128 * 8 * 4;       // one 128 x 8 fp32 layer-1 inpu
 constexpr uint32_t kW1Bytes = 64 * 8 * 4;       // W1^T operand, 64 x 8: 2 KB
 constexpr uint32_t kHBytes = 128 * 64 * 2;      // one 128 x 64 fp16 operand tile (one 128-byte swizzled row per position): 16 KB
 constexpr uint32_t kSmem = kStages * 2 * kHBytes + kGroups * 2 * kXBytes + 2 * kW1Bytes + 1024;   // (the x stages are unused with kXTmem)
-constexpr int kRing = 16;                       // per-centroid scale ring (gather runs at most ~9 tiles ahead of the epilogue)
+constexpr int kRing = 16;
+// distinct-sample walk: a list entry covers kUnitSlots consecutive sample slots of a centroid's ball row, a tile holds
+// kUnitsPerTile = 128 / kUnitSlots of them (TcArgs::live_units).  8 slots: tiles x 0.824 of the distinct-centroid walk on the
+// bench data, 4 slots: x 0.793 - and the same stage time (0.396 ms either way: twice the list entries and row probes, up
+// to eight centroids per gather warp), so 8 stays.
+#ifndef MGAR_TC16_UNIT_SLOTS
+#define MGAR_TC16_UNIT_SLOTS 8
+#endif
+constexpr int kUnitSlots = MGAR_TC16_UNIT_SLOTS, kUnitsPerTile = 128 / kUnitSlots, kUnitsPerRow = kTcNS / kUnitSlots;
+constexpr int kUnitShift = kUnitSlots == 4 ? 3 : 2;          // log2(kUnitsPerRow): entry = centroid << kUnitShift | unit
+static_assert(kUnitSlots == 4 || kUnitSlots == 8, "units of 4 or 8 sample slots");                       // per-centroid scale ring (gather runs at most ~9 tiles ahead of the epilogue)
 
 __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
                                               uint32_t accumulate) {   // fp16 operands, A read from TMEM
@@ -363,7 +373,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
             const int t = i % kAcc, u = i / kAcc;
             int tile_person = 0;
             if (tiled) {
-                const int c0 = units ? (__ldg(A.live_units + (size_t)(t_beg + i) * 16) & 0x7fffffff) >> 2
+                const int c0 = units ? (__ldg(A.live_units + (size_t)(t_beg + i) * kUnitsPerTile) & 0x7fffffff) >> kUnitShift
                                      : __ldg(A.live_tiles + t_beg + i);
                 tile_person = A.m_shift >= 0 ? c0 >> A.m_shift : c0 / gs;
             }
@@ -528,7 +538,7 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         const int ns = A.ns;
         auto cen = [&](int m) { return ns == kTcNS ? m : (ns == 64 ? (m >> 1) : 2 * m + (lane >> 4)); };
         int ent_next = 0;                                        // live-unit walk: this lane's list entry of the next load_idx call
-        if (units && g < my_tiles) ent_next = __ldg(A.live_units + (size_t)(t_beg + g) * 16 + pw * 4 + (lane >> 3));
+        if (units && g < my_tiles) ent_next = __ldg(A.live_units + (size_t)(t_beg + g) * kUnitsPerTile + pw * (kUnitsPerTile / 4) + lane / kUnitSlots);
         auto load_idx = [&](int i, int &iv, int &em, int &mr) {   // local tile i -> this lane's sample index (mr: real centroid)
             int m = (t_beg + i) * 4 + pw;
             iv = -1; em = 0; mr = 0;
@@ -536,11 +546,12 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
                 // the entry was fetched by the previous call (the calls walk this group's tiles in order, i += kGroups): a tile's
                 // sixteen entries are a 64-byte line of their own, i.e. a trip to L2 that must not sit in front of the index load
                 const int e = ent_next;
-                if (i + kGroups < my_tiles) ent_next = __ldg(A.live_units + (size_t)(t_beg + i + kGroups) * 16 + pw * 4 + (lane >> 3));
+                if (i + kGroups < my_tiles)
+                    ent_next = __ldg(A.live_units + (size_t)(t_beg + i + kGroups) * kUnitsPerTile + pw * (kUnitsPerTile / 4) + lane / kUnitSlots);
                 if (i < my_tiles) {
-                    mr = (e & 0x7fffffff) >> 2;
+                    mr = (e & 0x7fffffff) >> kUnitShift;
                     em = e < 0;                               // bit 31: empty ball (the builder saw -1 in slot 0)
-                    iv = __ldg(A.idx + (size_t)mr * kTcNS + (e & 3) * 8 + (lane & 7));
+                    iv = __ldg(A.idx + (size_t)mr * kTcNS + (e & (kUnitsPerRow - 1)) * kUnitSlots + (lane & (kUnitSlots - 1)));
                 }
                 return;
             }
@@ -841,10 +852,17 @@ constexpr int kUnitThreads = 128, kUnitCache = 1024;
 // octets of centroid row r (32 slots) in a cloud of p distinct points; e0 = slot 0 (-1: empty ball -> one octet of zeros)
 __device__ __forceinline__ int row_octets(const int *__restrict__ r, int p, int &e0) {
     e0 = __ldg(r);
-    const int e8 = __ldg(r + 8), e16 = __ldg(r + 16), e24 = __ldg(r + 24);
-    if (e0 < 0 || e8 >= p || e8 == e0) return 1;
-    if (e16 >= p || e16 == e0) return 2;
-    return (e24 >= p || e24 == e0) ? 3 : 4;
+    int e[kUnitsPerRow];
+#pragma unroll
+    for (int q = 1; q < kUnitsPerRow; q++) e[q] = __ldg(r + q * kUnitSlots);       // (all in flight together)
+    int u = 1;
+    bool on = e0 >= 0;
+#pragma unroll
+    for (int q = 1; q < kUnitsPerRow; q++) {
+        on = on && e[q] < p && e[q] != e0;                  // distinct entries are a prefix of the row
+        u += on ? 1 : 0;
+    }
+    return u;
 }
 __global__ void __launch_bounds__(kUnitThreads)
 build_live_units_kernel(const int *__restrict__ group_zero, const int *__restrict__ live_cnt, const int *__restrict__ point_cnt,
@@ -873,7 +891,7 @@ build_live_units_kernel(const int *__restrict__ group_zero, const int *__restric
     if (lane == 0) atomicAdd(&s_total, mine);
     __syncthreads();
     const int total = s_total;
-    if (tid == 0) s_base = atomicAdd(n_tiles, (total + 15) >> 4) * 16;
+    if (tid == 0) s_base = atomicAdd(n_tiles, (total + kUnitsPerTile - 1) / kUnitsPerTile) * kUnitsPerTile;
     __syncthreads();
     const int base = s_base;
     // sweep 2: the counts scanned, the entries written
@@ -883,7 +901,7 @@ build_live_units_kernel(const int *__restrict__ group_zero, const int *__restric
         int u = 0;
         bool dead = false;
         if (k < lc) {
-            if (k < kUnitCache) { u = s_u[k] & 7; dead = (s_u[k] & 0x80) != 0; }
+            if (k < kUnitCache) { u = s_u[k] & 15; dead = (s_u[k] & 0x80) != 0; }
             else { u = row_octets(rows + (size_t)k * kTcNS, p, e0); dead = e0 < 0; }
         }
         int incl = u;
@@ -898,14 +916,17 @@ build_live_units_kernel(const int *__restrict__ group_zero, const int *__restric
         int pos = running + incl - u;
         for (int w = 0; w < warp; w++) pos += s_warp[w];
         for (int w = 0; w < kUnitThreads / 32; w++) running += s_warp[w];
-        const int ent = (int)(((unsigned)(g * gs + k) << 2) | (dead ? 0x80000000u : 0u));
+        const int ent = (int)(((unsigned)(g * gs + k) << kUnitShift) | (dead ? 0x80000000u : 0u));
         for (int o = 0; o < u; o++) units[base + pos + o] = ent | o;
     }
     // padding of the last tile: copies of the person's first octet
     const int f0 = __ldg(rows);
-    const int ent0 = (int)(((unsigned)(g * gs) << 2) | (f0 < 0 ? 0x80000000u : 0u));
-    for (int q = total + tid; q < ((total + 15) & ~15); q += kUnitThreads) units[base + q] = ent0;
+    const int ent0 = (int)(((unsigned)(g * gs) << kUnitShift) | (f0 < 0 ? 0x80000000u : 0u));
+    for (int q = total + tid; q < (total + kUnitsPerTile - 1) / kUnitsPerTile * kUnitsPerTile; q += kUnitThreads) units[base + q] = ent0;
 }
+
+int tc_units_per_row() { return kUnitsPerRow; }
+int tc_units_per_tile() { return kUnitsPerTile; }
 
 int tc_build_live_units(const int *group_zero, const int *live_cnt, const int *point_cnt, const int *idx, int G, int group_size,
                         int n_u, int *units, int *n_tiles, cudaStream_t st) {
