@@ -549,6 +549,14 @@ def block_config2(ctx, F_total=64, M=80, MNP=100):
         total = F_total if tag == "strong" else frames
         out[tag] = dict(frames_per_rank=hi - lo, frames_total=total, ms_per_step=round(ms, 4),
                         value=total / (ms * 1e-3), unit="frames/s", stages_ms_rank0={k: round(v, 4) for k, v in stage.items()})
+        try:                                        # the same step replayed from one CUDA graph (launch-bound at few frames per rank)
+            from multimodal_gar_b200 import graphs
+            gc = graphs.GraphedCallable(whole, dev)
+            msg = ctx.timed(gc, 8)
+            out[tag]["cuda_graph"] = dict(ms_per_step=round(msg, 4), value=total / (msg * 1e-3), unit="frames/s")
+            del gc
+        except Exception as e:
+            out[tag]["cuda_graph"] = dict(unavailable="%s: %s" % (type(e).__name__, str(e)[:160]))
     lo, hi = lidar_branch.shard_frames(F_total, ctx.world, ctx.rank)
     run(lo, hi, "strong")
     if ctx.world > 1:
