@@ -842,7 +842,12 @@ def main():
                         executed_fraction=walked, executed_TFLOPs=ach * walked, executed_frac_burst=ach * walked / pk["bf16"],
                         executed_fraction_distinct_centroids=r.get("walked_centroids"),
                         tensor_pipe_active_pct=kprof.get("tensor_pipe_active_pct"),
-                        note="achieved = ALGORITHMIC fp32 FLOPs (SURVEY 8d: 2*M*P*K*8448 per frame) over the kernel's "
+                        note="frac can exceed 1: the formula counts FLOPs the kernel proves redundant - the reference's own "
+                             "wrap-around pooling (roipoint_pool3d_kernel.cu:86-97) repeats points, so centroids and ball samples "
+                             "repeat; the outputs are pinned against the FULL computation and the reference extensions "
+                             "(tests/test_bench_step_gpu.py, tests/test_live_units_gpu.py); executed_frac_burst is the "
+                             "utilisation figure (<= 1/3 for a three-term fp32-faithful split).  "
+                             "achieved = ALGORITHMIC fp32 FLOPs (SURVEY 8d: 2*M*P*K*8448 per frame) over the kernel's "
                              "CUDA-event time, against the %s bf16 tensor peak (burst: the timed region is tens of ms). "
                              "Two things make it differ from tensor-pipe utilisation, both stated here: (1) the kernel "
                              "walks only the DISTINCT centroids of every person (a person that pooled c < 512 points has "
