@@ -308,3 +308,13 @@ def test_single_process_two_devices(cuda):
                      f[0].cpu(), f[1].cpu()))
     for a, b in zip(*outs):
         assert torch.equal(a, b)
+    # the default batch path on the second device too: 1280 clouds -> the two sampling kernels side by side on the
+    # library's per-device side stream, the live-unit list, the tcgen05 MLP
+    pts, boxes = synthetic.make_batch(10, 32, N=32768, M=40)
+    big = []
+    for d in (0, 1):
+        dev = torch.device("cuda", d)
+        enc = _enc(dev)
+        with torch.no_grad():
+            big.append(enc(T(pts[..., :3], dev), T(pts[..., 3:4], dev), T(boxes, dev)).cpu())
+    assert torch.equal(big[0], big[1]) and big[0].abs().sum() > 0
