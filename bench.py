@@ -661,6 +661,27 @@ def block_train(ctx, frames_per_rank, steps=6):
                                       % (" + NCCL all-reduce" if ctx.world > 1 else ""))
     except Exception as e:
         out["cuda_graph"] = dict(unavailable="%s: %s" % (type(e).__name__, str(e)[:200]))
+    # ... and with the SA MLP's statistics pass on the tensor cores (MGAR_SA_TRAIN_KERNELS=tc, opt-in: its arg-max ties are
+    # re-evaluated in exact fp32, a hostile-gamma test of the default path is tighter than it meets), N = 1 only
+    if ctx.world == 1:
+        old = os.environ.get("MGAR_SA_TRAIN_KERNELS")
+        os.environ["MGAR_SA_TRAIN_KERNELS"] = "tc"
+        try:
+            torch.manual_seed(1994)
+            net3 = TS.LidarFusionNet().to(dev).train()
+            opt3 = torch.optim.Adam(net3.parameters(), lr=1e-4, fused=True, capturable=True)
+            step3 = TS.GraphedTrainStep(net3, opt3, batch, warmup=3)
+            gl3 = []
+            ms3 = ctx.timed(lambda: gl3.append(step3(batch).clone()), steps, warm=2)
+            out["cuda_graph_tc_statistics"] = dict(ms_per_step=round(ms3, 3), value=frames_per_rank / (ms3 * 1e-3), unit="frames/s",
+                                                   loss_last=float(gl3[-1]))
+        except Exception as e:
+            out["cuda_graph_tc_statistics"] = dict(unavailable="%s: %s" % (type(e).__name__, str(e)[:200]))
+        finally:
+            if old is None:
+                os.environ.pop("MGAR_SA_TRAIN_KERNELS", None)
+            else:
+                os.environ["MGAR_SA_TRAIN_KERNELS"] = old
     return out
 
 

@@ -480,6 +480,7 @@ extern "C" int mgar_sa_mlp_fwd_tc(int B, int M, int nsample, int C_in, const flo
     A.out = out; A.ld_out = ld_out;
     A.gmax = group_max; A.group_size = gsv > 0 ? gsv : 1; A.group_zero = group_zero;
     A.tr_zext = nullptr; A.tr_arg = nullptr; A.tr_sum = nullptr; A.tr_sq = nullptr;
+    A.l1_dev = nullptr;
     A.live_groups = nullptr; A.n_live = nullptr; A.live_tiles = nullptr; A.live_units = nullptr; A.m_shift = -1;
     A.packed4 = (C0 == 4 && xyz_stride == 4 && feat_stride == 4 && features == xyz + 3 &&
                  (reinterpret_cast<uintptr_t>(xyz) & 15) == 0) ? 1 : 0;

@@ -35,6 +35,10 @@ struct TcArgs {
     // ReLU in the epilogue; per (centroid, channel) the extreme of sign * z2 over the samples and the first sample
     // attaining it, per channel sum z2 and sum z2^2 (fp64 atomics)
     float *tr_zext; int *tr_arg; double *tr_sum, *tr_sq;
+    // training variant only (null elsewhere): layer 1 on the DEVICE - 8 x 64 folded weights [c_in][c_out] | 64 shifts |
+    // wmax[8], shmax (the TcLayer1 / TcBound contents, written by f_bn1_kernel) - so that the statistics pass needs no
+    // device-to-host copy of BatchNorm 1's batch scale / shift (and is capturable into a CUDA graph)
+    const float *l1_dev;
     // empty-person skip (sa_mlp_tc16 only; null = off): live_groups[0 .. *n_live) = indices of the groups (persons)
     // whose group_zero flag is 0, ascending.  The kernel then walks only n_live * group_size centroids ("virtual"
     // centroid v -> real centroid live_groups[v / group_size] * group_size + v % group_size).  Needs out == null,

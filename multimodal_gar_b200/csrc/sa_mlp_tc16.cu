@@ -262,7 +262,10 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         float k0[4], k1[4];
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            const float v = k < C0 ? L1.w[k][ch] : (k == C0 ? L1.sh[ch] : 0.f);
+            // (training statistics pass: BatchNorm 1's batch scale / shift only exist on the device - TcArgs::l1_dev)
+            const float v = (kTrain && A.l1_dev)
+                                ? (k < C0 ? __ldg(A.l1_dev + k * kTcC1 + ch) : (k == C0 ? __ldg(A.l1_dev + 8 * kTcC1 + ch) : 0.f))
+                                : (k < C0 ? L1.w[k][ch] : (k == C0 ? L1.sh[ch] : 0.f));
             if (k < 4) k0[k] = v; else k1[k - 4] = v;
         }
         if (kPack2) sts_pack2_w(w1_hi + k8_off(ch, 0), w1_hi + k8_off(ch, 1), w1_lo + k8_off(ch, 0), w1_lo + k8_off(ch, 1), k0, k1[0]);
@@ -537,6 +540,14 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
         // belongs to (ns = 16: per half warp)
         const int ns = A.ns;
         auto cen = [&](int m) { return ns == kTcNS ? m : (ns == 64 ? (m >> 1) : 2 * m + (lane >> 4)); };
+        // bound of |layer-1 pre-activation| (TcBound): kernel arguments, or - training - the nine floats behind l1_dev's W / shift
+        float bd_w[C0], bd_sh;
+        {
+            const bool dev = kTrain && A.l1_dev;
+#pragma unroll
+            for (int cc = 0; cc < C0; cc++) bd_w[cc] = dev ? __ldg(A.l1_dev + 9 * kTcC1 + cc) : BD.wmax[cc];
+            bd_sh = dev ? __ldg(A.l1_dev + 9 * kTcC1 + 8) : BD.shmax;
+        }
         int ent_next = 0;                                        // live-unit walk: this lane's list entry of the next load_idx call
         if (units && g < my_tiles) ent_next = __ldg(A.live_units + (size_t)(t_beg + g) * kUnitsPerTile + pw * (kUnitsPerTile / 4) + lane / kUnitSlots);
         auto load_idx = [&](int i, int &iv, int &em, int &mr) {   // local tile i -> this lane's sample index (mr: real centroid)
@@ -635,9 +646,9 @@ sa_mlp_tc16_kernel(const __grid_constant__ TcLayer1 L1, const __grid_constant__ 
 #pragma unroll
                 for (int cc = 3; cc < C0; cc++) x[cc] = v[cc];
             }
-            float bound = BD.shmax;
+            float bound = bd_sh;
 #pragma unroll
-            for (int cc = 0; cc < C0; cc++) bound = __fmaf_rn(BD.wmax[cc], fabsf(x[cc]), bound);
+            for (int cc = 0; cc < C0; cc++) bound = __fmaf_rn(bd_w[cc], fabsf(x[cc]), bound);
             // bound >= 0: the bit patterns order like the values.  bound < 2^(eb - 126); 2^(141 - eb) puts it below 2^15.
             int eb = (int)(__reduce_max_sync(0xffffffffu, __float_as_uint(bound)) >> 23);
             eb = eb < 15 ? 15 : (eb > 254 ? 254 : eb);
@@ -998,9 +1009,11 @@ int sa_mlp_tc16_launch_train(const TcLayer1 &L1, const TcArgs &A, int C0, int gr
     TcBound BD;
     BD.shmax = 0.f;
     for (int c = 0; c < 8; c++) BD.wmax[c] = 0.f;
-    for (int o = 0; o < kTcC1; o++) {
-        for (int c = 0; c < C0; c++) BD.wmax[c] = fmaxf(BD.wmax[c], fabsf(L1.w[c][o]));
-        BD.shmax = fmaxf(BD.shmax, fabsf(L1.sh[o]));
+    if (!A.l1_dev) {                     // (with l1_dev the kernel reads layer 1 and its bound from the device: L1 is unused)
+        for (int o = 0; o < kTcC1; o++) {
+            for (int c = 0; c < C0; c++) BD.wmax[c] = fmaxf(BD.wmax[c], fabsf(L1.w[c][o]));
+            BD.shmax = fmaxf(BD.shmax, fabsf(L1.sh[o]));
+        }
     }
 #define MGAR_TC16_TRAIN_CASE(c0)                                                                                          \
     if (C0 == c0) {                                                                                                       \

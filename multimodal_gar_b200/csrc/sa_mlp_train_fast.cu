@@ -48,7 +48,7 @@ constexpr int dS1 = 328, dS2 = 456, dD = 584, dS11 = 1096, dRed = 1160, dTotal =
 // fp32 block (indices in floats)
 constexpr int fMean1 = 0, fInv1 = 64, fSc1 = 128, fSh1 = 192, fAlpha = 768, fMean2 = 1088, fInv2 = 1216,
               fSc2 = 1344, fSh2 = 1472, fQ = 1600, fCvec = 5696, fE = 5760, fU = 5888, fQf = 6016, fCf = 6056,
-              fSgn2 = 6064, fZero2 = 6192, fTotal = 6320;
+              fSgn2 = 6064, fZero2 = 6192, fL1 = 6320 /* 8 x 64 folded W1 | 64 shifts | wmax[8], shmax, pad */, fTotal = 6320 + 9 * 64 + 16;
 
 struct Layout {
     size_t x0, zmax, gs, arg, t, lst, lgs, lcnt, part, dbl, flt, w2t, total;
@@ -202,6 +202,27 @@ __global__ void f_bn1_kernel(long long P, float eps, const float *__restrict__ W
         flt[fSgn2 + k] = gamma_beta[2 * kC1 + k] < 0.f ? -1.f : 1.f;
         flt[fZero2 + k] = 0.f;
     }
+    // ... and its layer 1 (TcLayer1 / TcBound of sa_mlp_tc.cuh) on the device: W1 with BatchNorm 1's batch scale folded in,
+    // the shift, and the per-input-column bound max_c |w[k][c]|, max_c |shift[c]|
+    __shared__ float s_red[2][9];
+    const float scf = (float)sc, shf = (float)((double)gamma_beta[kC1 + c] - mean * sc);
+    float wm[9];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const float v = k < C0 ? __fmul_rn(Wt1[k * kC1 + c], scf) : 0.f;
+        flt[fL1 + k * kC1 + c] = v;
+        wm[k] = fabsf(v);
+    }
+    flt[fL1 + 8 * kC1 + c] = shf;
+    wm[8] = fabsf(shf);
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) wm[k] = fmaxf(wm[k], __shfl_xor_sync(0xffffffffu, wm[k], o));
+        if ((c & 31) == 0) s_red[c >> 5][k] = wm[k];
+    }
+    __syncthreads();
+    if (c < 9) flt[fL1 + 9 * kC1 + c] = fmaxf(s_red[0][c], s_red[1][c]);
 }
 
 // h1 rows of one 128-position tile: thread (c1 = t & 63, q = t >> 6) writes channel c1 of the 32 rows of centroid q.
@@ -912,17 +933,9 @@ int forward_t(int B, int M, const float *xyz, const float *new_xyz, const float 
         count_launch();
     } else {
         // layer 2 on the tensor cores: the inference kernel (sa_mlp_tc16.cu, tcgen05 3xFP16) with the statistics
-        // epilogue.  Its layer-1 parameters are kernel arguments, so BatchNorm 1's batch scale / shift (256 B) and
-        // W1 come back to the host first: one small D2H copy and a stream synchronisation per step.
-        float h_ss[2 * kC1], h_w1[8 * kC1];
-        MGAR_CUDA(cudaMemcpyAsync(h_ss, flt + fSc1, sizeof(h_ss), cudaMemcpyDeviceToHost, st));
-        MGAR_CUDA(cudaMemcpyAsync(h_w1, weights, (size_t)C0 * kC1 * 4, cudaMemcpyDeviceToHost, st));
-        MGAR_CUDA(cudaStreamSynchronize(st));
-        TcLayer1 L1;
-        for (int o = 0; o < kC1; o++) {
-            for (int c = 0; c < 8; c++) L1.w[c][o] = c < C0 ? h_w1[c * kC1 + o] * h_ss[o] : 0.f;
-            L1.sh[o] = h_ss[kC1 + o];
-        }
+        // epilogue.  Its layer 1 (W1 with BatchNorm 1's batch scale folded in, the shift, the bound of the pre-activation)
+        // is read from the device (f_bn1_kernel wrote it behind the other coefficients): no copy back, no synchronisation.
+        TcLayer1 L1 = {};
         TcArgs A;
         A.live_groups = nullptr; A.n_live = nullptr; A.live_tiles = nullptr; A.live_units = nullptr; A.m_shift = -1; A.ns = kTcNS;
         A.B = B; A.M = M; A.C_in = C0 - 3;
@@ -937,6 +950,7 @@ int forward_t(int B, int M, const float *xyz, const float *new_xyz, const float 
         A.trace = nullptr;
 #endif
         A.tr_zext = zmax; A.tr_arg = arg; A.tr_sum = dbl + dSum2; A.tr_sq = dbl + dSq2;
+        A.l1_dev = flt + fL1;
         const int n_tiles = (M + 3) / 4;
         if (int rc = sa_mlp_tc16_launch_train(L1, A, C0, n_tiles < kNumSMs ? n_tiles : kNumSMs, st)) return rc;
         int gf = div_up((long long)M * kC2, kThreads * 4);

@@ -9,7 +9,15 @@ from multimodal_gar_b200 import train_step as TS
 pytestmark = pytest.mark.gpu
 
 
-def test_graphed_training_step_follows_the_eager_trajectory(cuda):
+@pytest.mark.parametrize("kernels", ["", "tc"])
+def test_graphed_training_step_follows_the_eager_trajectory(cuda, monkeypatch, kernels):
+    """kernels = "tc": the statistics pass of the SA MLP on tcgen05 (MGAR_SA_TRAIN_KERNELS=tc) - its layer-1 parameters are
+    read from the device, so it is capturable too."""
+    if kernels:
+        monkeypatch.setenv("MGAR_SA_TRAIN_KERNELS", kernels)
+    else:
+        monkeypatch.delenv("MGAR_SA_TRAIN_KERNELS", raising=False)
+
     def run(graphed, steps=4):
         torch.manual_seed(5)
         net = TS.LidarFusionNet().to(cuda).train()
