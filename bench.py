@@ -406,6 +406,11 @@ class Ctx:
             return float(t.item())
         return v
 
+    def all_ok(self, ok):
+        """True when `ok` holds on EVERY rank (a collective: ranks that failed to set something up still take part, so the
+        ranks that succeeded do not wait for them inside the next collective)."""
+        return self.max_over_ranks(0.0 if ok else 1.0) == 0.0
+
     def timed(self, fn, iters, warm=2):
         """ms per call: CUDA events around `iters` calls, barrier + synchronize on both sides, max over ranks."""
         import torch
@@ -551,7 +556,13 @@ def block_config2(ctx, F_total=64, M=80, MNP=100):
                         value=total / (ms * 1e-3), unit="frames/s", stages_ms_rank0={k: round(v, 4) for k, v in stage.items()})
         try:                                        # the same step replayed from one CUDA graph (launch-bound at few frames per rank)
             from multimodal_gar_b200 import graphs
-            gc = graphs.GraphedCallable(whole, dev)
+            gc, err = None, None
+            try:
+                gc = graphs.GraphedCallable(whole, dev)
+            except Exception as e:
+                err = e
+            if not ctx.all_ok(gc is not None):
+                raise err or RuntimeError("capture failed on another rank")
             msg = ctx.timed(gc, 8)
             out[tag]["cuda_graph"] = dict(ms_per_step=round(msg, 4), value=total / (msg * 1e-3), unit="frames/s")
             del gc
@@ -652,7 +663,13 @@ def block_train(ctx, frames_per_rank, steps=6):
         else:
             model2 = net2
         opt2 = torch.optim.Adam(model2.parameters(), lr=1e-4, fused=True, capturable=True)
-        step = TS.GraphedTrainStep(model2, opt2, batch, warmup=11 if ctx.world > 1 else 3)
+        step, err = None, None
+        try:
+            step = TS.GraphedTrainStep(model2, opt2, batch, warmup=11 if ctx.world > 1 else 3)
+        except Exception as e:
+            err = e
+        if not ctx.all_ok(step is not None):
+            raise err or RuntimeError("capture failed on another rank")
         gl = []
         msg = ctx.timed(lambda: gl.append(step(batch).clone()), steps, warm=2)
         out["cuda_graph"] = dict(ms_per_step=round(msg, 3), value=frames_per_rank * ctx.world / (msg * 1e-3), unit="frames/s",
@@ -794,7 +811,13 @@ def run_native(args, rank, world, local_rank):
         try:
             out = {}
             for name, inputs, n in (("latency_1frame_ms", [one], 50), ("ms_per_step", [list(devb[0]), list(devb[1])], args.steps)):
-                gs = [graphs.GraphedPersonEncoder(enc, *inp) for inp in inputs]       # one graph per resident input batch
+                gs, err = None, None
+                try:
+                    gs = [graphs.GraphedPersonEncoder(enc, *inp) for inp in inputs]   # one graph per resident input batch
+                except Exception as e:
+                    err = e
+                if not ctx.all_ok(gs is not None):
+                    raise err or RuntimeError("capture failed on another rank")
                 for i in range(4):
                     gs[i % len(gs)].graph.replay()
                 torch.cuda.synchronize()
