@@ -386,6 +386,12 @@ MGAR_API size_t mgar_gemm_packed_bytes(int N, int K);
 MGAR_API int mgar_gemm_pack_bt(int N, int K, const float *Bt, int ldb, float *packed, void *stream);
 MGAR_API int mgar_gemm_tf32x3_packed(int M, int N, int K, const float *A, int lda, const float *packed, const float *bias,
                                      int relu, float *C, int ldc, void *stream);
+/* `groups` (1 .. 4) independent products of ONE shape in ONE launch (host arrays of per-group operands; bias may be NULL, or
+ * hold NULL entries): their tiles fill the SMs together - a (6400 x 512) x 512 product alone is 200 tiles on 148 SMs, two
+ * waves for 1.35 waves of work.  The linears of FusionAttention_mat come in such pairs (the two streams; gat_model.py:466-511). */
+MGAR_API int mgar_gemm_tf32x3_packed_grouped(int groups, int M, int N, int K, const float *const *A, const int *lda,
+                                             const float *const *packed, const float *const *bias, int relu,
+                                             float *const *C, const int *ldc, void *stream);
 
 /* ---- training: the same module with BatchNorm batch statistics, and its backward pass ------------------- */
 

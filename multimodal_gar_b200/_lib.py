@@ -60,6 +60,7 @@ SIGNATURES = {
     "mgar_gemm_packed_bytes": [_i, _i],
     "mgar_gemm_pack_bt": [_i, _i, _p, _i, _p, _p],
     "mgar_gemm_tf32x3_packed": [_i, _i, _i, _p, _i, _p, _p, _i, _p, _i, _p],
+    "mgar_gemm_tf32x3_packed_grouped": [_i, _i, _i, _i, _p, _p, _p, _p, _i, _p, _p, _p],
     "mgar_fps_ball_query_supported": [_i, _i, _i, _i],
     "mgar_fps_ball_query_workspace_bytes": [_i],
     "mgar_fps_ball_query": [_i, _i, _i, _p, _i, _f, _i, _p, _p, _p, _p, _i, _p, _p, ctypes.c_size_t, _p],

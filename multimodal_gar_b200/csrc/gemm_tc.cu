@@ -198,9 +198,22 @@ constexpr uint32_t kGpStageBytes = 4 * kGmTile;            // A hi, A lo (writte
 constexpr int kGpStages = 3;
 constexpr uint32_t kGpSmem = kGpStages * kGpStageBytes + 1024;
 
+// Up to kGmGroups independent products of ONE shape in a launch (grid.z = group): the tiles of all of them fill the SMs
+// together - a (6400 x 512) x 512 product alone is 200 tiles on 148 SMs, i.e. two waves for 1.35 waves of work.
+constexpr int kGmGroups = 4;
+struct GemmGroups {
+    const float *A[kGmGroups], *packed[kGmGroups], *bias[kGmGroups];
+    float *C[kGmGroups];
+    int lda[kGmGroups], ldc[kGmGroups];
+};
+
 __global__ void __launch_bounds__(kGmThreads, 1)
-gemm_tf32x3_packed_kernel(int M, int N, int K, const float *__restrict__ A, int lda, const float *__restrict__ packed,
-                          const float *__restrict__ bias, int relu, float *__restrict__ C, int ldc) {
+gemm_tf32x3_packed_kernel(int M, int N, int K, const __grid_constant__ GemmGroups G, int relu) {
+    const float *__restrict__ A = G.A[blockIdx.z];
+    const float *__restrict__ packed = G.packed[blockIdx.z];
+    const float *__restrict__ bias = G.bias[blockIdx.z];
+    float *__restrict__ C = G.C[blockIdx.z];
+    const int lda = G.lda[blockIdx.z], ldc = G.ldc[blockIdx.z];
     extern __shared__ uint8_t gm_smem[];
     __shared__ __align__(8) uint64_t s_bar[2 * kGpStages + 1];
     __shared__ uint32_t s_tmem;
@@ -381,7 +394,34 @@ extern "C" int mgar_gemm_tf32x3_packed(int M, int N, int K, const float *A, int 
     MGAR_REQUIRE((M + 127) / 128 <= 65535, "gemm_tf32x3_packed: M=%d exceeds grid.y", M);
     MGAR_CUDA(cudaFuncSetAttribute(gemm_tf32x3_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGpSmem));
     dim3 grid(N / 128, (M + 127) / 128);
-    gemm_tf32x3_packed_kernel<<<grid, kGmThreads, kGpSmem, (cudaStream_t)stream>>>(M, N, K, A, lda, packed, bias, relu, C, ldc);
+    GemmGroups G = {};
+    G.A[0] = A; G.packed[0] = packed; G.bias[0] = bias; G.C[0] = C; G.lda[0] = lda; G.ldc[0] = ldc;
+    gemm_tf32x3_packed_kernel<<<grid, kGmThreads, kGpSmem, (cudaStream_t)stream>>>(M, N, K, G, relu);
     count_launch();
     return check_launch("gemm_tf32x3_packed");
+}
+
+extern "C" int mgar_gemm_tf32x3_packed_grouped(int groups, int M, int N, int K, const float *const *A, const int *lda,
+                                               const float *const *packed, const float *const *bias, int relu,
+                                               float *const *C, const int *ldc, void *stream) {
+    MGAR_REQUIRE(groups >= 1 && groups <= kGmGroups, "gemm_tf32x3_packed_grouped: 1 .. %d groups, got %d", kGmGroups, groups);
+    MGAR_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm_tf32x3_packed_grouped: negative size");
+    if (M == 0 || N == 0) return MGAR_OK;
+    MGAR_REQUIRE(mgar_gemm_tf32x3_supported(M, N, K), "gemm_tf32x3_packed_grouped: unsupported shape M=%d N=%d K=%d", M, N, K);
+    MGAR_REQUIRE(A && lda && packed && C && ldc, "gemm_tf32x3_packed_grouped: null pointer");
+    GemmGroups G = {};
+    for (int g = 0; g < groups; g++) {
+        MGAR_REQUIRE(A[g] && packed[g] && C[g], "gemm_tf32x3_packed_grouped: null operand in group %d", g);
+        MGAR_REQUIRE(lda[g] >= K && ldc[g] >= N && lda[g] % 4 == 0 && ldc[g] % 4 == 0, "gemm_tf32x3_packed_grouped: bad leading dimension");
+        const float *bg = bias ? bias[g] : nullptr;
+        MGAR_REQUIRE(((reinterpret_cast<uintptr_t>(A[g]) | reinterpret_cast<uintptr_t>(packed[g]) | reinterpret_cast<uintptr_t>(C[g]) |
+                       reinterpret_cast<uintptr_t>(bg)) & 15) == 0, "gemm_tf32x3_packed_grouped: operands must be 16-byte aligned");
+        G.A[g] = A[g]; G.packed[g] = packed[g]; G.bias[g] = bg; G.C[g] = C[g]; G.lda[g] = lda[g]; G.ldc[g] = ldc[g];
+    }
+    MGAR_REQUIRE((M + 127) / 128 <= 65535, "gemm_tf32x3_packed_grouped: M=%d exceeds grid.y", M);
+    MGAR_CUDA(cudaFuncSetAttribute(gemm_tf32x3_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGpSmem));
+    dim3 grid(N / 128, (M + 127) / 128, groups);
+    gemm_tf32x3_packed_kernel<<<grid, kGmThreads, kGpSmem, (cudaStream_t)stream>>>(M, N, K, G, relu);
+    count_launch();
+    return check_launch("gemm_tf32x3_packed_grouped");
 }

@@ -95,8 +95,9 @@ class FusionAttentionMat(nn.Module):
         # csrc/gemm_tc.cu) when the widths fit the kernel, else torch's fp32 GEMM (MGAR_NO_TC_GEMM=1 forces that)
         tc = tc_gemm.usable(L, 3 * D, D)
         if tc:
-            PL = tc_gemm.linear(L.view(B * n, D), self._wl.get((self.WQ_r, self.WK_l, self.WV_l)))   # Q_r | K_l | V_l
-            PR = tc_gemm.linear(R.view(B * n, D), self._wr.get((self.WK_r, self.WV_r, self.WQ_l)))   # K_r | V_r | Q_l
+            # (the products of the two streams have one shape: one grouped launch each, their tiles fill the SMs together)
+            PL, PR = tc_gemm.linear_grouped([(L.view(B * n, D), self._wl.get((self.WQ_r, self.WK_l, self.WV_l)), None),    # Q_r | K_l | V_l
+                                             (R.view(B * n, D), self._wr.get((self.WK_r, self.WV_r, self.WQ_l)), None)])   # K_r | V_r | Q_l
         else:
             PL = L.view(B * n, D) @ torch.cat([self.WQ_r, self.WK_l, self.WV_l], dim=1)
             PR = R.view(B * n, D) @ torch.cat([self.WK_r, self.WV_r, self.WQ_l], dim=1)
@@ -116,13 +117,16 @@ class FusionAttentionMat(nn.Module):
                                               arr(ptr(self.LN_r_1.bias), ptr(self.LN_l_1.bias)), float(self.LN_r_1.eps),
                                               arr(X[0].data_ptr(), X[1].data_ptr()), st), "dafm_attention")
             outs = []
+            ys = None
+            if tc:
+                xs = [X[i].view(B * n, D) for i in range(2)]
+                ffns = [self.FFN_r, self.FFN_l]
+                hs = tc_gemm.linear_grouped([(x, f[0].weight, f[0].bias) for x, f in zip(xs, ffns)], relu=True)
+                ys = tc_gemm.linear_grouped([(h, f[2].weight, f[2].bias) for h, f in zip(hs, ffns)])
             for i, s in enumerate(("r", "l")):
                 x = X[i].view(B * n, D)
                 ffn = getattr(self, "FFN_" + s)
-                if tc:
-                    y = tc_gemm.linear(tc_gemm.linear(x, ffn[0].weight, ffn[0].bias, relu=True), ffn[2].weight, ffn[2].bias)
-                else:
-                    y = ffn(x)
+                y = ys[i] if tc else ffn(x)
                 ln = getattr(self, "LN_%s_2" % s)
                 o = torch.empty_like(x)
                 _lib.check(L_.mgar_dafm_add_layernorm(B * n, D, ptr(x), ptr(y), ptr(ln.weight), ptr(ln.bias), ptr(vmask),

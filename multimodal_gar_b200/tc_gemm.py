@@ -71,6 +71,35 @@ def linear(x, weight, bias=None, relu=False, out=None, packed=True):
     return y if out is not None else y.view(*x.shape[:-1], N)
 
 
+def linear_grouped(items, relu=False):
+    """[act(x_g @ W_g.T + b_g)] for up to four (x, weight, bias) triples of ONE shape in one launch
+    (mgar_gemm_tf32x3_packed_grouped): the tiles of all products fill the SMs together.  Falls back to `linear` per item
+    when the shapes differ."""
+    import ctypes
+    if len(items) == 1 or len(items) > 4 or len({(tuple(x.shape), tuple(w.shape)) for x, w, _ in items}) != 1:
+        return [linear(x, w, b, relu=relu) for x, w, b in items]
+    K, N = items[0][1].shape[1], items[0][1].shape[0]
+    xs, ys, pws, bs = [], [], [], []
+    for x, w, b in items:
+        x2 = x.reshape(-1, K)
+        if x2.stride(1) != 1 or x2.stride(0) % 4 or x2.data_ptr() % 16:
+            x2 = x2.contiguous()
+        xs.append(x2)
+        ys.append(torch.empty((x2.shape[0], N), dtype=torch.float32, device=x.device))
+        pws.append(packed_weight(w))
+        bs.append(None if b is None else b.detach().contiguous())
+    M, G = xs[0].shape[0], len(items)
+    vp, ip = ctypes.c_void_p * G, ctypes.c_int * G
+    a_ = vp(*[ptr(t) for t in xs]); p_ = vp(*[ptr(t) for t in pws]); b_ = vp(*[ptr(t) for t in bs]); c_ = vp(*[ptr(t) for t in ys])
+    lda = ip(*[t.stride(0) for t in xs]); ldc = ip(*[t.stride(0) for t in ys])
+    with on_device(xs[0]):
+        _lib.check(_lib.lib().mgar_gemm_tf32x3_packed_grouped(G, M, N, K, ctypes.addressof(a_), ctypes.addressof(lda),
+                                                              ctypes.addressof(p_), ctypes.addressof(b_), 1 if relu else 0,
+                                                              ctypes.addressof(c_), ctypes.addressof(ldc), stream_of(xs[0])),
+                   "gemm_tf32x3_packed_grouped")
+    return [y.view(*x.shape[:-1], N) for y, (x, _, _) in zip(ys, items)]
+
+
 class CachedTranspose:
     """(K, N) parameters used as `x @ W` -> the (N, K) K-major copy the kernel wants, re-made when a parameter changes
     (storage pointer + in-place version, as the folded-BatchNorm cache of the SA module)."""

@@ -57,10 +57,10 @@ def test_fused_module_matches_torch_composition(cuda, monkeypatch, B, n, D, full
             mod(R, L, None, De, None if full else valid)        # (the first call packs the weights for the tcgen05 GEMM)
             n0 = _lib.launch_count()
             Rf, Lf = mod(R, L, None, De, None if full else valid)
-            assert _lib.launch_count() - n0 == (9 if D % 128 == 0 else 3)   # + six tcgen05 GEMMs when the width fits
+            assert _lib.launch_count() - n0 == (6 if D % 128 == 0 else 3)   # + three grouped tcgen05 launches (six products) when the width fits
             monkeypatch.setenv("MGAR_DAFM", "torch")
             Rt, Lt = mod(R, L, None, De, None if full else valid)
-            assert _lib.launch_count() - n0 == (9 if D % 128 == 0 else 3)   # + six tcgen05 GEMMs when the width fits
+            assert _lib.launch_count() - n0 == (6 if D % 128 == 0 else 3)   # + three grouped tcgen05 launches (six products) when the width fits
     finally:
         torch.backends.cuda.matmul.allow_tf32 = tf32
     for got, want in ((Rf, Rt), (Lf, Lt)):

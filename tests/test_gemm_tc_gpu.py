@@ -54,8 +54,8 @@ def test_gemm_strided_rows_and_rejects_bad_shapes(cuda):
 
 
 def test_dafm_runs_its_linears_on_the_tensor_cores(cuda, monkeypatch):
-    """The fused DAFM path launches 6 tcgen05 GEMMs per module (2 projections + 4 FFN linears) and no library GEMM, and
-    agrees with the torch composition at 1e-5."""
+    """The fused DAFM path runs its 6 products per module (2 projections + 4 FFN linears) as 3 grouped tcgen05 launches (the
+    two streams of a layer share a launch) and no library GEMM, and agrees with the torch composition at 1e-5."""
     torch.manual_seed(2)
     B, n, D = 5, 37, 512
     mod = dafm.FusionAttentionMat(D, D).to(cuda).eval()
@@ -71,7 +71,7 @@ def test_dafm_runs_its_linears_on_the_tensor_cores(cuda, monkeypatch):
         monkeypatch.setenv("MGAR_DAFM", "torch")
         torch.backends.cuda.matmul.allow_tf32 = False
         want = mod(R, L, None, De, valid)
-    assert launches == 6 + 1 + 2, launches                                             # GEMMs + attention + 2 add-LayerNorm
+    assert launches == 3 + 1 + 2, launches                                             # grouped GEMMs + attention + 2 add-LayerNorm
     for a, b in zip(got, want):
         scale = float(b.abs().max())
         assert torch.allclose(a, b, rtol=1e-5, atol=2e-5 * scale), float((a - b).abs().max()) / scale
@@ -84,3 +84,28 @@ def test_dafm_runs_its_linears_on_the_tensor_cores(cuda, monkeypatch):
         want2 = mod(R, L, None, De, valid)
     assert not torch.equal(again[0], got[0])
     assert torch.allclose(again[0], want2[0], rtol=1e-5, atol=2e-5 * float(want2[0].abs().max()))
+
+
+def test_grouped_launch_equals_the_single_products(cuda):
+    """mgar_gemm_tf32x3_packed_grouped: up to four products of one shape in one launch - the same bits as one launch each;
+    mixed shapes fall back to single launches."""
+    from multimodal_gar_b200 import tc_gemm
+    g = torch.Generator(device="cpu").manual_seed(4)
+    M, K, N = 777, 512, 512
+    items = []
+    for i in range(4):
+        x = torch.randn((M, K), generator=g).to(cuda)
+        w = torch.randn((N, K), generator=g).to(cuda)
+        b = None if i == 2 else torch.randn((N,), generator=g).to(cuda)
+        items.append((x, w, b))
+        tc_gemm.packed_weight(w)                           # (the first use of a weight packs it: one more launch)
+    for relu in (False, True):
+        for cnt in (2, 3, 4):
+            n0 = _lib.launch_count()
+            got = tc_gemm.linear_grouped(items[:cnt], relu=relu)
+            assert _lib.launch_count() - n0 == 1
+            for (x, w, b), y in zip(items[:cnt], got):
+                assert torch.equal(y, tc_gemm.linear(x, w, b, relu=relu))
+    mixed = items[:1] + [(items[1][0][:100], items[1][1], items[1][2])]
+    got = tc_gemm.linear_grouped(mixed)
+    assert torch.equal(got[1], tc_gemm.linear(*mixed[1]))
